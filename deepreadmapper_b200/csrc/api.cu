@@ -1,0 +1,343 @@
+// extern "C" boundary of libdrm_cuda.so (declared in include/drm_b200.h).  Host-pointer entry points
+// copy in, run the kernels, copy out and report the three times separately; "_device" entry points
+// only enqueue kernels on the caller's stream.
+#include "common.h"
+
+#include <algorithm>
+#include <cstring>
+#include <thread>
+
+struct drm_index {
+    std::vector<drm::DeviceIndex> rep;
+    int64_t info[12];
+};
+
+struct drm_ref {
+    std::vector<drm::DeviceRef> rep;
+};
+
+namespace {
+
+using namespace drm;
+
+struct DevBuf {  // RAII device allocation on the current device
+    void *p = nullptr;
+    ~DevBuf() { if (p) cudaFree(p); }
+    int alloc(size_t bytes) { DRM_CUDA_TRY(cudaMalloc(&p, bytes ? bytes : 16)); return DRM_OK; }
+    template <class T> T *as() { return static_cast<T *>(p); }
+};
+
+struct Timer {
+    cudaEvent_t a = nullptr, b = nullptr;
+    Timer() { cudaEventCreate(&a); cudaEventCreate(&b); }
+    ~Timer() { if (a) cudaEventDestroy(a); if (b) cudaEventDestroy(b); }
+    void start(cudaStream_t s) { cudaEventRecord(a, s); }
+    void stop(cudaStream_t s) { cudaEventRecord(b, s); }
+    double ms() { float t = 0; cudaEventSynchronize(b); cudaEventElapsedTime(&t, a, b); return t; }
+};
+
+// queries [q0, q1) of one host-pointer search call on one replica
+int search_slice(const DeviceIndex &dx, const float *q, int64_t n, int d, int k, int ef, float *D, int64_t *I,
+                 drm_search_stats *st)
+{
+    DRM_CUDA_TRY(cudaSetDevice(dx.device));
+    cudaStream_t s;
+    DRM_CUDA_TRY(cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking));
+    DevBuf dq, dD, dI;
+    int rc;
+    if ((rc = dq.alloc((size_t)n * d * sizeof(float))) || (rc = dD.alloc((size_t)n * k * sizeof(float))) ||
+        (rc = dI.alloc((size_t)n * k * sizeof(int64_t)))) { cudaStreamDestroy(s); return rc; }
+    Timer th, tk, td;
+    cudaMemsetAsync(dx.counters, 0, 3 * sizeof(int64_t), s);
+    th.start(s);
+    cudaMemcpyAsync(dq.p, q, (size_t)n * d * sizeof(float), cudaMemcpyHostToDevice, s);
+    th.stop(s);
+    tk.start(s);
+    rc = launch_search(dx, dq.as<float>(), n, k, ef, dD.as<float>(), dI.as<int64_t>(), dx.counters, s);
+    tk.stop(s);
+    if (rc != DRM_OK) { cudaStreamDestroy(s); return rc; }
+    td.start(s);
+    cudaMemcpyAsync(D, dD.p, (size_t)n * k * sizeof(float), cudaMemcpyDeviceToHost, s);
+    cudaMemcpyAsync(I, dI.p, (size_t)n * k * sizeof(int64_t), cudaMemcpyDeviceToHost, s);
+    td.stop(s);
+    int64_t cnt[3] = {0, 0, 0};
+    cudaMemcpyAsync(cnt, dx.counters, sizeof cnt, cudaMemcpyDeviceToHost, s);
+    cudaError_t e = cudaStreamSynchronize(s);
+    if (e != cudaSuccess) { cudaStreamDestroy(s); return fail(DRM_ECUDA, std::string("search: ") + cudaGetErrorString(e)); }
+    if (st) {
+        st->nhops0 = cnt[0]; st->nhops_up = cnt[1]; st->ndis_eval = cnt[2];
+        st->h2d_ms = th.ms(); st->device_ms = tk.ms(); st->d2h_ms = td.ms();
+    }
+    cudaStreamDestroy(s);
+    return DRM_OK;
+}
+
+int open_ref(const char *bytes, int64_t len_bytes, int64_t len, int form, int ref_len, const int *devices, int n_dev, drm_ref **out)
+{
+    if (!out) return fail(DRM_EINVAL, "null output handle");
+    *out = nullptr;
+    if (!bytes || len < 0 || ref_len <= 0 || n_dev < 1 || !devices) return fail(DRM_EINVAL, "bad reference arguments");
+    drm_ref *r = new drm_ref();
+    for (int i = 0; i < n_dev; ++i) {
+        DeviceRef dr;
+        dr.device = devices[i]; dr.form = form; dr.ref_len = ref_len; dr.len = len;
+        cudaError_t e = cudaSetDevice(dr.device);
+        int *flag = nullptr;
+        if (e == cudaSuccess) e = cudaMalloc(&dr.raw, len_bytes ? len_bytes : 16);
+        if (e == cudaSuccess) e = cudaMalloc(&dr.data, len_bytes ? len_bytes : 16);
+        if (e == cudaSuccess) e = cudaMalloc(&flag, sizeof(int));
+        if (e == cudaSuccess) e = cudaMemset(flag, 0, sizeof(int));
+        if (e == cudaSuccess && len_bytes) e = cudaMemcpy(dr.raw, bytes, (size_t)len_bytes, cudaMemcpyHostToDevice);
+        int rc = DRM_OK;
+        if (e == cudaSuccess) rc = launch_classify(dr.raw, dr.data, len_bytes, flag, 0);
+        int other = 0;
+        if (e == cudaSuccess && rc == DRM_OK) e = cudaMemcpy(&other, flag, sizeof(int), cudaMemcpyDeviceToHost);
+        cudaFree(flag);
+        dr.has_other = other != 0;
+        r->rep.push_back(dr);
+        if (e != cudaSuccess || rc != DRM_OK) {
+            if (e != cudaSuccess) rc = fail(DRM_ECUDA, std::string("reference upload: ") + cudaGetErrorString(e));
+            drm_ref_close(r);
+            return rc;
+        }
+    }
+    *out = r;
+    return DRM_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+const char *drm_last_error(void) { return drm::last_error_string().c_str(); }
+const char *drm_version(void) { return "drm-b200 0.1 (sm_100a)"; }
+
+int drm_device_count(void)
+{
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+    return n;
+}
+
+int drm_index_open(const char *index_file, const int *devices, int n_dev, drm_index **out)
+{
+    if (!out) return fail(DRM_EINVAL, "null output handle");
+    *out = nullptr;
+    if (!index_file || !devices || n_dev < 1) return fail(DRM_EINVAL, "bad arguments to drm_index_open");
+    HostIndex h;
+    int rc = read_index_file(index_file, h);
+    if (rc != DRM_OK) return rc;
+    if (drm_device_count() < 1) return fail(DRM_ECUDA, "no CUDA device: libdrm_cuda has no CPU fallback");
+    drm_index *ix = new drm_index();
+    for (int i = 0; i < n_dev; ++i) {
+        DeviceIndex dx;
+        rc = build_device_index(h, devices[i], dx);
+        if (rc != DRM_OK) { drm_index_close(ix); return rc; }
+        ix->rep.push_back(dx);
+    }
+    int64_t info[12] = {h.d, h.ntotal, (int64_t)h.M, (int64_t)h.nbits, h.M_hnsw(), h.entry_point, h.max_level,
+                        h.efConstruction, h.efSearch, (int64_t)h.neighbors.size(), n_dev, (int64_t)ix->rep[0].bytes};
+    memcpy(ix->info, info, sizeof info);
+    *out = ix;
+    return DRM_OK;
+}
+
+void drm_index_close(drm_index *ix)
+{
+    if (!ix) return;
+    for (auto &dx : ix->rep) free_device_index(dx);
+    delete ix;
+}
+
+int drm_index_info(const drm_index *ix, int64_t *info)
+{
+    if (!ix || !info) return fail(DRM_EINVAL, "null argument");
+    memcpy(info, ix->info, sizeof ix->info);
+    return DRM_OK;
+}
+
+int drm_search(drm_index *ix, const float *q, int64_t n, int d, int k, int ef, float *D, int64_t *I, drm_search_stats *stats)
+{
+    if (!ix) return fail(DRM_EINVAL, "null index");
+    if (n <= 0 || !q) return fail(DRM_EEMPTY, "Query data is empty");
+    if (d != ix->rep[0].d) return fail(DRM_EINVAL, "query dimension " + std::to_string(d) + " does not match index dimension " + std::to_string(ix->rep[0].d));
+    if (!D || !I || k <= 0 || ef <= 0) return fail(DRM_EINVAL, "bad arguments to drm_search");
+    const int R = (int)ix->rep.size();
+    std::vector<drm_search_stats> st((size_t)R);
+    std::vector<int> rcs((size_t)R, DRM_OK);
+    std::vector<std::string> errs((size_t)R);
+    auto work = [&](int g) {
+        int64_t q0 = n * g / R, q1 = n * (g + 1) / R;
+        memset(&st[(size_t)g], 0, sizeof(drm_search_stats));
+        if (q1 <= q0) return;
+        rcs[(size_t)g] = search_slice(ix->rep[(size_t)g], q + q0 * d, q1 - q0, d, k, ef, D + q0 * k, I + q0 * k, &st[(size_t)g]);
+        if (rcs[(size_t)g] != DRM_OK) errs[(size_t)g] = drm::last_error_string();
+    };
+    if (R == 1) work(0);
+    else {
+        std::vector<std::thread> th;
+        for (int g = 0; g < R; ++g) th.emplace_back(work, g);
+        for (auto &t : th) t.join();
+    }
+    for (int g = 0; g < R; ++g)
+        if (rcs[(size_t)g] != DRM_OK) return fail(rcs[(size_t)g], errs[(size_t)g]);
+    if (stats) {
+        memset(stats, 0, sizeof *stats);
+        for (auto &s : st) {
+            stats->nhops0 += s.nhops0; stats->nhops_up += s.nhops_up; stats->ndis_eval += s.ndis_eval;
+            stats->device_ms = std::max(stats->device_ms, s.device_ms);
+            stats->h2d_ms = std::max(stats->h2d_ms, s.h2d_ms);
+            stats->d2h_ms = std::max(stats->d2h_ms, s.d2h_ms);
+        }
+    }
+    return DRM_OK;
+}
+
+int drm_search_device(drm_index *ix, int slot, const float *q_dev, int64_t n, int d, int k, int ef, float *D_dev,
+                      int64_t *I_dev, int64_t *counters_dev, void *stream)
+{
+    if (!ix || slot < 0 || slot >= (int)ix->rep.size()) return fail(DRM_EINVAL, "bad index handle or replica slot");
+    if (d != ix->rep[(size_t)slot].d) return fail(DRM_EINVAL, "query dimension does not match index dimension");
+    DRM_CUDA_TRY(cudaSetDevice(ix->rep[(size_t)slot].device));
+    return launch_search(ix->rep[(size_t)slot], q_dev, n, k, ef, D_dev, I_dev, counters_dev, static_cast<cudaStream_t>(stream));
+}
+
+int drm_ref_open_genome(const char *genome, int64_t len, int ref_len, const int *devices, int n_dev, drm_ref **out)
+{
+    return open_ref(genome, len, len, 0, ref_len, devices, n_dev, out);
+}
+
+int drm_ref_open_windows(const char *windows_flat, int64_t n_windows, int ref_len, const int *devices, int n_dev, drm_ref **out)
+{
+    if (n_windows < 0 || ref_len <= 0) return fail(DRM_EINVAL, "bad window table");
+    return open_ref(windows_flat, n_windows * ref_len, n_windows, 1, ref_len, devices, n_dev, out);
+}
+
+void drm_ref_close(drm_ref *r)
+{
+    if (!r) return;
+    for (auto &dr : r->rep) {
+        if (dr.device >= 0) cudaSetDevice(dr.device);
+        cudaFree(dr.data); cudaFree(dr.raw);
+    }
+    delete r;
+}
+
+int drm_sw_pairs(const char *a_flat, const int64_t *a_off, const char *b_flat, const int64_t *b_off, int64_t n, int32_t *scores)
+{
+    if (n < 0 || (n > 0 && (!a_flat || !a_off || !b_flat || !b_off || !scores))) return fail(DRM_EINVAL, "bad arguments to drm_sw_pairs");
+    if (n == 0) return DRM_OK;
+    if (drm_device_count() < 1) return fail(DRM_ECUDA, "no CUDA device: libdrm_cuda has no CPU fallback");
+    int64_t max_b = 0;
+    for (int64_t i = 0; i < n; ++i) max_b = std::max(max_b, b_off[i + 1] - b_off[i]);
+    const int64_t abytes = a_off[n], bbytes = b_off[n];
+    DevBuf da, dao, db, dbo, ds;
+    int rc;
+    if ((rc = da.alloc((size_t)abytes)) || (rc = dao.alloc((size_t)(n + 1) * 8)) || (rc = db.alloc((size_t)bbytes)) ||
+        (rc = dbo.alloc((size_t)(n + 1) * 8)) || (rc = ds.alloc((size_t)n * 4))) return rc;
+    DRM_CUDA_TRY(cudaMemcpy(da.p, a_flat, (size_t)abytes, cudaMemcpyHostToDevice));
+    DRM_CUDA_TRY(cudaMemcpy(dao.p, a_off, (size_t)(n + 1) * 8, cudaMemcpyHostToDevice));
+    DRM_CUDA_TRY(cudaMemcpy(db.p, b_flat, (size_t)bbytes, cudaMemcpyHostToDevice));
+    DRM_CUDA_TRY(cudaMemcpy(dbo.p, b_off, (size_t)(n + 1) * 8, cudaMemcpyHostToDevice));
+    rc = launch_sw_pairs(da.as<char>(), dao.as<int64_t>(), db.as<char>(), dbo.as<int64_t>(), n, (int)max_b, ds.as<int32_t>(), 0);
+    if (rc != DRM_OK) return rc;
+    DRM_CUDA_TRY(cudaMemcpy(scores, ds.p, (size_t)n * 4, cudaMemcpyDeviceToHost));
+    return DRM_OK;
+}
+
+int drm_sw_rerank_device(drm_ref *r, int slot, int mode, const int64_t *neighbors_dev, int64_t n, int64_t k_in,
+                         const char *q_flat_dev, const int64_t *q_off_dev, int max_qlen, int64_t stride, int64_t k,
+                         int64_t k_clusters, int32_t *out_scores_dev, uint64_t *out_ids_dev, int32_t *n_cands_dev,
+                         int32_t *min_cands_dev, int64_t *cells_dev, void *stream)
+{
+    if (!r || slot < 0 || slot >= (int)r->rep.size()) return fail(DRM_EINVAL, "bad reference handle or replica slot");
+    const DeviceRef &dr = r->rep[(size_t)slot];
+    DRM_CUDA_TRY(cudaSetDevice(dr.device));
+    RerankArgs a{mode, neighbors_dev, n, k_in, q_flat_dev, q_off_dev, max_qlen, stride, k, k_clusters,
+                 out_scores_dev, out_ids_dev, n_cands_dev, min_cands_dev, cells_dev};
+    return launch_rerank(dr, a, static_cast<cudaStream_t>(stream));
+}
+
+int drm_sw_rerank(drm_ref *r, int mode, const int64_t *neighbors, int64_t n, int64_t k_in, const char *q_flat,
+                  const int64_t *q_off, int64_t stride, int64_t k, int64_t k_clusters, int32_t *out_scores,
+                  uint64_t *out_ids, int32_t *n_cands, double *device_ms)
+{
+    if (!r) return fail(DRM_EINVAL, "null reference handle");
+    if (n < 0 || (n > 0 && (!neighbors || !q_flat || !q_off || !out_scores || !out_ids))) return fail(DRM_EINVAL, "bad arguments to drm_sw_rerank");
+    if (device_ms) *device_ms = 0;
+    if (n == 0) return DRM_OK;
+    const int R = (int)r->rep.size();
+    std::vector<int> rcs((size_t)R, DRM_OK);
+    std::vector<std::string> errs((size_t)R);
+    std::vector<double> ms((size_t)R, 0.0);
+    std::vector<int> mins((size_t)R, 0x7fffffff);
+    auto work = [&](int g) {
+        int64_t r0 = n * g / R, r1 = n * (g + 1) / R, m = r1 - r0;
+        if (m <= 0) return;
+        auto body = [&]() -> int {
+            const DeviceRef &dr = r->rep[(size_t)g];
+            DRM_CUDA_TRY(cudaSetDevice(dr.device));
+            int64_t qb = q_off[r0], qe = q_off[r1];
+            int max_qlen = 0;
+            std::vector<int64_t> off((size_t)m + 1);
+            for (int64_t i = 0; i <= m; ++i) off[(size_t)i] = q_off[r0 + i] - qb;
+            for (int64_t i = 0; i < m; ++i) max_qlen = std::max<int64_t>(max_qlen, off[(size_t)i + 1] - off[(size_t)i]);
+            DevBuf dn, dq, dqo, dsc, did, dnc, dmin;
+            int rc;
+            if ((rc = dn.alloc((size_t)m * k_in * 8)) || (rc = dq.alloc((size_t)(qe - qb))) || (rc = dqo.alloc((size_t)(m + 1) * 8)) ||
+                (rc = dsc.alloc((size_t)m * k * 4)) || (rc = did.alloc((size_t)m * k * 8)) || (rc = dnc.alloc((size_t)m * 4)) ||
+                (rc = dmin.alloc(4))) return rc;
+            cudaStream_t s;
+            DRM_CUDA_TRY(cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking));
+            int big = 0x7fffffff;
+            cudaMemcpyAsync(dn.p, neighbors + r0 * k_in, (size_t)m * k_in * 8, cudaMemcpyHostToDevice, s);
+            cudaMemcpyAsync(dq.p, q_flat + qb, (size_t)(qe - qb), cudaMemcpyHostToDevice, s);
+            cudaMemcpyAsync(dqo.p, off.data(), (size_t)(m + 1) * 8, cudaMemcpyHostToDevice, s);
+            cudaMemcpyAsync(dmin.p, &big, 4, cudaMemcpyHostToDevice, s);
+            Timer t;
+            t.start(s);
+            RerankArgs a{mode, dn.as<int64_t>(), m, k_in, dq.as<char>(), dqo.as<int64_t>(), max_qlen, stride, k, k_clusters,
+                         dsc.as<int32_t>(), did.as<uint64_t>(), dnc.as<int32_t>(), dmin.as<int32_t>(), nullptr};
+            rc = launch_rerank(dr, a, s);
+            t.stop(s);
+            if (rc == DRM_OK) {
+                cudaMemcpyAsync(out_scores + r0 * k, dsc.p, (size_t)m * k * 4, cudaMemcpyDeviceToHost, s);
+                cudaMemcpyAsync(out_ids + r0 * k, did.p, (size_t)m * k * 8, cudaMemcpyDeviceToHost, s);
+                if (n_cands) cudaMemcpyAsync(n_cands + r0, dnc.p, (size_t)m * 4, cudaMemcpyDeviceToHost, s);
+                cudaMemcpyAsync(&mins[(size_t)g], dmin.p, 4, cudaMemcpyDeviceToHost, s);
+            }
+            cudaError_t e = cudaStreamSynchronize(s);
+            if (rc == DRM_OK) ms[(size_t)g] = t.ms();
+            cudaStreamDestroy(s);
+            if (rc != DRM_OK) return rc;
+            if (e != cudaSuccess) return fail(DRM_ECUDA, std::string("rerank: ") + cudaGetErrorString(e));
+            return DRM_OK;
+        };
+        rcs[(size_t)g] = body();
+        if (rcs[(size_t)g] != DRM_OK) errs[(size_t)g] = drm::last_error_string();
+    };
+    if (R == 1) work(0);
+    else {
+        std::vector<std::thread> th;
+        for (int g = 0; g < R; ++g) th.emplace_back(work, g);
+        for (auto &t : th) t.join();
+    }
+    int min_c = 0x7fffffff;
+    for (int g = 0; g < R; ++g) {
+        if (rcs[(size_t)g] != DRM_OK) return fail(rcs[(size_t)g], errs[(size_t)g]);
+        min_c = std::min(min_c, mins[(size_t)g]);
+        if (device_ms) *device_ms = std::max(*device_ms, ms[(size_t)g]);
+    }
+    if (k > 0 && min_c < k)
+        return fail(DRM_ENOTENOUGH, "Not enough candidates (" + std::to_string(min_c) + " < " + std::to_string(k) + ")");
+    return DRM_OK;
+}
+
+int drm_merge_topk_device(int device, const float *D_all, const int64_t *I_all, int n_shards, int64_t n, int k,
+                          float *D_out, int64_t *I_out, void *stream)
+{
+    DRM_CUDA_TRY(cudaSetDevice(device));
+    return launch_merge_topk(D_all, I_all, n_shards, n, k, D_out, I_out, static_cast<cudaStream_t>(stream));
+}
+
+}  // extern "C"

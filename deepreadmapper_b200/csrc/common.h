@@ -1,0 +1,108 @@
+// Shared declarations of libdrm_cuda.so (internal; the public boundary is include/drm_b200.h).
+#pragma once
+#include <cuda_runtime.h>
+#include <cstdint>
+#include <cstdio>
+#include <string>
+#include <vector>
+
+#include "../../include/drm_b200.h"
+
+namespace drm {
+
+void set_error(const std::string &msg);
+int fail(int code, const std::string &msg);
+const std::string &last_error_string();
+
+#define DRM_CUDA_TRY(expr)                                                                              \
+    do {                                                                                                \
+        cudaError_t e__ = (expr);                                                                       \
+        if (e__ != cudaSuccess)                                                                         \
+            return ::drm::fail(DRM_ECUDA, std::string(#expr) + ": " + cudaGetErrorString(e__));         \
+    } while (0)
+
+// ---------------------------------------------------------------------------------------------
+// Host image of a FAISS IndexHNSWPQ ("IHNp") file — the arrays exactly as FAISS serialises them
+// (layout: SURVEY.md §8c item 1; reference call site src/main.cpp:236-237).
+struct HostIndex {
+    int32_t d = 0;
+    int64_t ntotal = 0;
+    int32_t metric = 1;
+    std::vector<double> assign_probas;
+    std::vector<int32_t> cum;        // cum_nneighbor_per_level
+    std::vector<int32_t> levels;     // top level + 1 per vertex
+    std::vector<uint64_t> offsets;   // ntotal + 1
+    std::vector<int32_t> neighbors;  // -1 padded per level slot
+    int32_t entry_point = -1, max_level = -1, efConstruction = 40, efSearch = 16, upper_beam = 1;
+    uint64_t M = 0, nbits = 0, ksub = 0, dsub = 0, code_size = 0;
+    std::vector<float> centroids;  // [M][ksub][dsub]
+    std::vector<uint8_t> codes;    // ntotal x code_size
+    int32_t search_type = 0;       // PQ search_type (ST_PQ)
+    uint8_t encode_signs = 0;
+    int32_t polysemous_ht = 0;
+    int M_hnsw() const { return cum.size() > 1 ? cum[1] / 2 : 0; }
+};
+
+int read_index_file(const char *path, HostIndex &ix);         // DRM_OK or error (message set)
+int write_index_file(const char *path, const HostIndex &ix);  // same layout, used by the builder
+
+// ---------------------------------------------------------------------------------------------
+// Device image of the index, laid out for one-round-trip hops (DESIGN.md "data layout in HBM"):
+//   rows0 : ntotal rows; row v = [W0 x int32 level-0 neighbour ids (-1 padded)]
+//                                [W0 x code_size bytes: the PQ code of each of those neighbours]
+//   up    : one row per (vertex, level>=1), the levels of a vertex contiguous and ascending;
+//           row = [int32 vertex id, int32 level, 8 pad bytes][Wu x int32 neighbour ROW indices at the
+//                  same level (-1 padded)][Wu x code_size bytes of neighbour codes]
+struct DeviceIndex {
+    int device = -1;
+    int d = 0, M = 0, ksub = 0, dsub = 0, code_size = 0;
+    int W0 = 0, Wu = 0;        // row widths: 2*M_hnsw and M_hnsw
+    int row0_bytes = 0, rowu_bytes = 0;
+    int code0_off = 0, codeu_off = 0;  // byte offset of the code block inside a row (16-byte aligned)
+    int64_t ntotal = 0;
+    int max_level = 0;
+    int64_t entry_vertex = -1;
+    int64_t entry_row = -1;    // upper row of the entry point at max_level; -1 when max_level == 0
+    uint8_t entry_code[64] = {0};
+    float *centroids = nullptr;
+    uint8_t *rows0 = nullptr;
+    uint8_t *up = nullptr;
+    int64_t n_up_rows = 0;
+    int64_t *counters = nullptr;  // 3 x int64 scratch for host-pointer calls
+    size_t bytes = 0;
+};
+
+int build_device_index(const HostIndex &h, int device, DeviceIndex &out);
+void free_device_index(DeviceIndex &dx);
+
+// Kernel launchers (search_kernel.cu)
+int launch_search(const DeviceIndex &dx, const float *q_dev, int64_t n, int k, int ef, float *D_dev, int64_t *I_dev,
+                  int64_t *counters_dev, cudaStream_t stream);
+
+// ---------------------------------------------------------------------------------------------
+// Reference windows on the device (sw_kernel.cu)
+struct DeviceRef {
+    int device = -1;
+    int form = 0;            // 0 = genome, 1 = window table
+    int ref_len = 0;
+    int64_t len = 0;         // genome bases, or number of windows
+    uint8_t *data = nullptr; // base classes 0..4 (A,C,G,T,N), 7 = any other byte (table form keeps raw too)
+    uint8_t *raw = nullptr;  // raw bytes (only kept when has_other: the generic byte-equality path)
+    bool has_other = false;  // some byte outside ACGTN -> generic kernel
+};
+
+struct RerankArgs {
+    int mode;  // 0 static bound rule, 1 dynamic
+    const int64_t *neighbors; int64_t n, k_in;
+    const char *q_flat; const int64_t *q_off; int max_qlen;
+    int64_t stride, k, k_clusters;
+    int32_t *out_scores; uint64_t *out_ids; int32_t *n_cands; int32_t *min_cands; int64_t *cells;
+};
+int launch_rerank(const DeviceRef &r, const RerankArgs &a, cudaStream_t stream);
+int launch_sw_pairs(const char *a_flat, const int64_t *a_off, const char *b_flat, const int64_t *b_off, int64_t n,
+                    int max_len_b, int32_t *scores, cudaStream_t stream);
+int launch_merge_topk(const float *D_all, const int64_t *I_all, int n_shards, int64_t n, int k, float *D_out,
+                      int64_t *I_out, cudaStream_t stream);
+int launch_classify(const uint8_t *raw, uint8_t *cls, int64_t n, int *has_other_dev, cudaStream_t stream);
+
+}  // namespace drm

@@ -1,0 +1,368 @@
+// HNSW-PQ search on sm_100a: one warp per query.
+//
+// Replaces faiss::IndexHNSWPQ::search as called by the reference's faiss_search
+// (src/hnswpq/search.cpp:13,39-40).  Algorithm = FAISS HNSW::search (greedy descent on the upper
+// levels + ef-bounded level-0 search with the MinimaxHeap stop rule) under the CANONICAL tie rule of
+// oracle/hnswpq_oracle.cpp (orc_search tie_rule=1): candidates and results are ordered by the total
+// order (distance, id).  Under that order
+//   * the candidate MinimaxHeap is "the cap = max(ef,k) smallest evaluated vertices", kept here as
+//     a SORTED POOL of 64-bit keys  (float_bits(dis) << 32 | id << 1 | expanded)  in shared memory;
+//   * the result heap is the first k pool entries;
+//   * FAISS's VisitedTable is redundant: a vertex seen before is either still in the pool (found by
+//     the same binary search that gives its insert position) or was rejected/evicted with a key
+//     above the pool maximum, which only decreases - so it is rejected again.  No per-query visited
+//     structure exists, which is what lets 24 queries share one SM.
+//
+// Memory: one hop = ONE contiguous row read (neighbour ids + the PQ codes of those neighbours,
+// fused at index-open time, see index_image.cu); the ADC table (M x 256 fp32) lives in shared
+// memory.  All fp32 arithmetic uses explicit round-to-nearest intrinsics in the oracle's order, so
+// distances are bit-identical to the oracle's.
+#include "common.h"
+
+#include <cfloat>
+
+namespace drm {
+
+namespace {
+
+constexpr int WARPS_PER_CTA = 4;
+constexpr unsigned FULL = 0xffffffffu;
+typedef unsigned long long u64;
+
+struct SearchParams {
+    const float *q;
+    long long n;
+    int d, M, dsub;
+    const float *centroids;
+    const uint8_t *rows0;
+    const uint8_t *up;
+    int row0_bytes, rowu_bytes, W0, Wu, c0_off, cu_off;
+    long long entry_vertex, entry_row;
+    int max_level;
+    int k, ef, cap;
+    float *D;
+    long long *I;
+    u64 *counters;        // nhops0, nhops_up, ndis_eval (nullable)
+    unsigned *next_query; // work counter, zeroed before launch
+    uint8_t entry_code[64];
+};
+
+template <int CS> struct Code;
+template <> struct Code<8> { uint2 v; };
+template <> struct Code<16> { uint4 v; };
+
+template <int CS> __device__ __forceinline__ Code<CS> load_code(const uint8_t *p);
+template <> __device__ __forceinline__ Code<8> load_code<8>(const uint8_t *p)
+{
+    Code<8> c; c.v = __ldg(reinterpret_cast<const uint2 *>(p)); return c;
+}
+template <> __device__ __forceinline__ Code<16> load_code<16>(const uint8_t *p)
+{
+    Code<16> c; c.v = __ldg(reinterpret_cast<const uint4 *>(p)); return c;
+}
+
+// dis = sum_m T[m][code[m]], m ascending, sequential fp32 adds (oracle adc_dis).
+__device__ __forceinline__ float adc_word(const float *T, unsigned w, int m0, float acc, bool first)
+{
+#pragma unroll
+    for (int b = 0; b < 4; ++b) {
+        float t = T[(m0 + b) * 256 + ((w >> (8 * b)) & 0xffu)];
+        acc = (first && b == 0) ? t : __fadd_rn(acc, t);
+    }
+    return acc;
+}
+__device__ __forceinline__ float adc(const float *T, const Code<8> &c)
+{
+    float a = adc_word(T, c.v.x, 0, 0.f, true);
+    return adc_word(T, c.v.y, 4, a, false);
+}
+__device__ __forceinline__ float adc(const float *T, const Code<16> &c)
+{
+    float a = adc_word(T, c.v.x, 0, 0.f, true);
+    a = adc_word(T, c.v.y, 4, a, false);
+    a = adc_word(T, c.v.z, 8, a, false);
+    return adc_word(T, c.v.w, 12, a, false);
+}
+template <int CS> __device__ __forceinline__ float adc_bytes(const float *T, const uint8_t *code)
+{
+    float a = T[code[0]];
+    for (int m = 1; m < CS; ++m) a = __fadd_rn(a, T[m * 256 + code[m]]);
+    return a;
+}
+
+__device__ __forceinline__ u64 make_key(float d, int id) { return ((u64)__float_as_uint(d) << 32) | ((u64)(unsigned)id << 1); }
+
+// T[m][j] = sum_t (x[m*dsub+t] - c[m][j][t])^2, t ascending, one fma per term (oracle adc_table).
+__device__ __forceinline__ void build_lut(float *T, const float *__restrict__ x, const float *__restrict__ cent, int M, int dsub, int lane)
+{
+    for (int m = 0; m < M; ++m) {
+        const float *xm = x + m * dsub;
+        for (int j = lane; j < 256; j += 32) {
+            const float *c = cent + ((size_t)(m * 256 + j)) * dsub;
+            float acc = 0.f;
+            if ((dsub & 3) == 0) {
+                for (int t = 0; t < dsub; t += 4) {
+                    float4 cv = __ldg(reinterpret_cast<const float4 *>(c + t));
+                    float4 xv = __ldg(reinterpret_cast<const float4 *>(xm + t));
+                    float e0 = __fsub_rn(xv.x, cv.x); acc = __fmaf_rn(e0, e0, acc);
+                    float e1 = __fsub_rn(xv.y, cv.y); acc = __fmaf_rn(e1, e1, acc);
+                    float e2 = __fsub_rn(xv.z, cv.z); acc = __fmaf_rn(e2, e2, acc);
+                    float e3 = __fsub_rn(xv.w, cv.w); acc = __fmaf_rn(e3, e3, acc);
+                }
+            } else {
+                for (int t = 0; t < dsub; ++t) {
+                    float e = __fsub_rn(__ldg(xm + t), __ldg(c + t));
+                    acc = __fmaf_rn(e, e, acc);
+                }
+            }
+            T[m * 256 + j] = acc;
+        }
+    }
+}
+
+__device__ __forceinline__ u64 warp_min_u64(u64 v)
+{
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        u64 other = __shfl_xor_sync(FULL, v, o);
+        v = other < v ? other : v;
+    }
+    return v;
+}
+
+// NPL = neighbours per lane at level 0 (W0 <= 32*NPL).
+template <int CS, int NPL>
+__global__ void __launch_bounds__(WARPS_PER_CTA * 32) hnswpq_search_kernel(const SearchParams p)
+{
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const size_t per_warp = (size_t)p.M * 256 * sizeof(float) + (size_t)p.cap * sizeof(u64);
+    float *T = reinterpret_cast<float *>(smem_raw + warp * per_warp);
+    u64 *pool = reinterpret_cast<u64 *>(smem_raw + warp * per_warp + (size_t)p.M * 256 * sizeof(float));
+    const int cap = p.cap;
+
+    for (;;) {
+        unsigned qi = 0;
+        if (lane == 0) qi = atomicAdd(p.next_query, 1u);
+        qi = __shfl_sync(FULL, qi, 0);
+        if ((long long)qi >= p.n) break;
+
+        __syncwarp();
+        build_lut(T, p.q + (size_t)qi * p.d, p.centroids, p.M, p.dsub, lane);
+        __syncwarp();
+
+        unsigned nhops0 = 0, nhops_up = 0, ndis = 0;
+
+        // ---------------- greedy descent, levels max_level .. 1 (FAISS greedy_update_nearest)
+        float d_near = adc_bytes<CS>(T, p.entry_code);
+        long long vertex = p.entry_vertex;
+        if (p.max_level >= 1) {
+            long long r = p.entry_row;
+            for (int level = p.max_level; level >= 1; --level) {
+                for (;;) {
+                    const uint8_t *row = p.up + (size_t)r * p.rowu_bytes;
+                    int nr = -1;
+                    float dj = __uint_as_float(0x7f800000u);
+                    if (lane < p.Wu) nr = __ldg(reinterpret_cast<const int *>(row + 16) + lane);
+                    unsigned neg = __ballot_sync(FULL, lane < p.Wu && nr < 0);
+                    int first_neg = neg ? (__ffs(neg) - 1) : p.Wu;
+                    if (lane < first_neg) dj = adc(T, load_code<CS>(row + p.cu_off + CS * lane));
+                    u64 best = warp_min_u64(((u64)__float_as_uint(dj) << 32) | (unsigned)lane);
+                    float dmin = __uint_as_float((unsigned)(best >> 32));
+                    ++nhops_up;
+                    if (dmin < d_near) {
+                        d_near = dmin;
+                        r = __shfl_sync(FULL, nr, (int)(best & 31u));
+                    } else break;
+                }
+                if (level > 1) r -= 1;  // same vertex, one level down (rows of a vertex are contiguous)
+            }
+            vertex = __ldg(reinterpret_cast<const int *>(p.up + (size_t)r * p.rowu_bytes));
+        }
+
+        // ---------------- level 0: sorted-pool search
+        int size = 1, cur = 0;
+        if (lane == 0) pool[0] = make_key(d_near, (int)vertex);
+        __syncwarp();
+        while (cur >= 0) {
+            const u64 k0 = pool[cur];
+            const unsigned v0 = (unsigned)(k0 & 0xffffffffu) >> 1;
+            if (cap > p.ef) {
+                // MinimaxHeap::count_below(d0) >= efSearch (only reachable when k > ef)
+                const unsigned d0 = (unsigned)(k0 >> 32);
+                int below = 0;
+                for (int b = 0; b < size; b += 32) {
+                    int i = b + lane;
+                    below += __popc(__ballot_sync(FULL, i < size && (unsigned)(pool[i] >> 32) < d0));
+                }
+                if (below >= p.ef) break;
+            }
+            const uint8_t *row = p.rows0 + (size_t)v0 * p.row0_bytes;
+            int nid[NPL];
+            Code<CS> code[NPL];
+#pragma unroll
+            for (int c = 0; c < NPL; ++c) {
+                int slot = lane + 32 * c;
+                nid[c] = slot < p.W0 ? __ldg(reinterpret_cast<const int *>(row) + slot) : -1;
+                if (slot < p.W0) code[c] = load_code<CS>(row + p.c0_off + CS * slot);
+            }
+            __syncwarp();
+            if (lane == 0) pool[cur] = k0 | 1ull;  // expanded
+            // speculative L2 prefetch of the likeliest next row (first unexpanded entry after cur)
+            {
+                int i = cur + 1 + lane;
+                u64 kk = i < size ? pool[i] : 1ull;
+                unsigned m = __ballot_sync(FULL, !(kk & 1ull));
+                if (m) {
+                    unsigned nv = (unsigned)(__shfl_sync(FULL, kk, __ffs(m) - 1) & 0xffffffffu) >> 1;
+                    const uint8_t *nrow = p.rows0 + (size_t)nv * p.row0_bytes;
+                    if (lane * 128 < p.row0_bytes) asm volatile("prefetch.global.L2 [%0];" ::"l"(nrow + lane * 128));
+                }
+            }
+            __syncwarp();
+            ++nhops0;
+
+            u64 key[NPL];
+            int lo[NPL];
+            bool cand[NPL];
+            bool row_open = true;
+#pragma unroll
+            for (int c = 0; c < NPL; ++c) {
+                unsigned neg = __ballot_sync(FULL, nid[c] < 0);
+                int first_neg = neg ? (__ffs(neg) - 1) : 32;
+                bool valid = row_open && lane < first_neg;
+                if (neg) row_open = false;
+                ndis += __popc(__ballot_sync(FULL, valid));
+                key[c] = 0;
+                if (valid) key[c] = make_key(adc(T, code[c]), nid[c]);
+                cand[c] = valid;
+            }
+            const bool full = size == cap;
+            const u64 maxkey = full ? (pool[cap - 1] & ~1ull) : ~0ull;
+            const int iters = 32 - __clz(size);
+#pragma unroll
+            for (int c = 0; c < NPL; ++c) {
+                cand[c] = cand[c] && key[c] < maxkey;
+                int l = 0, h = size;
+                for (int it = 0; it < iters; ++it) {
+                    if (l < h) {
+                        int mid = (l + h) >> 1;
+                        if ((pool[mid] & ~1ull) < key[c]) l = mid + 1; else h = mid;
+                    }
+                }
+                lo[c] = l;
+                if (cand[c] && l < size && (pool[l] & ~1ull) == key[c]) cand[c] = false;  // already in the pool
+            }
+            int hint = cur + 1;
+#pragma unroll
+            for (int c = 0; c < NPL; ++c) {
+                unsigned mask = __ballot_sync(FULL, cand[c]);
+                while (mask) {
+                    const int src = __ffs(mask) - 1;
+                    mask &= mask - 1;
+                    const u64 kin = __shfl_sync(FULL, key[c], src);
+                    const int pin = __shfl_sync(FULL, lo[c], src);
+                    if (pin >= cap) continue;
+                    if (pin < size && (pool[pin] & ~1ull) == kin) continue;  // duplicate id inside one row
+                    const int nsz = size < cap ? size + 1 : cap;
+                    for (int top = nsz; top > pin + 1; top -= 32) {
+                        int i = top - 1 - lane;
+                        u64 tmp = 0;
+                        if (i > pin) tmp = pool[i - 1];
+                        __syncwarp();
+                        if (i > pin) pool[i] = tmp;
+                        __syncwarp();
+                    }
+                    if (lane == 0) pool[pin] = kin;
+                    __syncwarp();
+                    size = nsz;
+#pragma unroll
+                    for (int c2 = 0; c2 < NPL; ++c2)
+                        if (key[c2] > kin) lo[c2] += 1;
+                    hint = pin < hint ? pin : hint;
+                }
+            }
+            cur = -1;
+            for (int b = hint; b < size; b += 32) {
+                int i = b + lane;
+                unsigned m = __ballot_sync(FULL, i < size && !(pool[i] & 1ull));
+                if (m) { cur = b + __ffs(m) - 1; break; }
+            }
+        }
+
+        // ---------------- results: the first k pool entries, ascending (distance, id)
+        float *Dq = p.D + (size_t)qi * p.k;
+        long long *Iq = p.I + (size_t)qi * p.k;
+        for (int i = lane; i < p.k; i += 32) {
+            if (i < size) {
+                u64 kk = pool[i];
+                Dq[i] = __uint_as_float((unsigned)(kk >> 32));
+                Iq[i] = (long long)((unsigned)(kk & 0xffffffffu) >> 1);
+            } else {
+                Dq[i] = FLT_MAX;
+                Iq[i] = -1;
+            }
+        }
+        if (p.counters && lane == 0) {
+            atomicAdd(p.counters + 0, (u64)nhops0);
+            atomicAdd(p.counters + 1, (u64)nhops_up);
+            atomicAdd(p.counters + 2, (u64)ndis);
+        }
+    }
+}
+
+template <int CS, int NPL>
+int launch_t(const SearchParams &p, size_t smem, int device, cudaStream_t stream)
+{
+    auto kern = hnswpq_search_kernel<CS, NPL>;
+    DRM_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int per_sm = 0, sms = 0;
+    DRM_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, WARPS_PER_CTA * 32, smem));
+    DRM_CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device));
+    if (per_sm < 1) return fail(DRM_EUNSUPPORTED, "search kernel does not fit on an SM with these parameters");
+    long long want = (p.n + WARPS_PER_CTA - 1) / WARPS_PER_CTA;
+    long long grid = (long long)per_sm * sms;
+    if (want < grid) grid = want;
+    kern<<<(unsigned)grid, WARPS_PER_CTA * 32, smem, stream>>>(p);
+    DRM_CUDA_TRY(cudaGetLastError());
+    return DRM_OK;
+}
+
+}  // namespace
+
+// Scratch for the work counter: one unsigned per device, allocated lazily.
+static unsigned *g_work_counter[64] = {nullptr};
+
+int launch_search(const DeviceIndex &dx, const float *q_dev, int64_t n, int k, int ef, float *D_dev, int64_t *I_dev,
+                  int64_t *counters_dev, cudaStream_t stream)
+{
+    if (n <= 0) return fail(DRM_EEMPTY, "Query data is empty");
+    if (k <= 0 || ef <= 0) return fail(DRM_EINVAL, "k and ef must be positive");
+    if (n > 0xfffffff0ll) return fail(DRM_EINVAL, "more than 2^32 queries in one call");
+    if (dx.ksub != 256) return fail(DRM_EUNSUPPORTED, "only nbits == 8 product quantizers are supported by the search kernel");
+    if (dx.W0 > 64 || dx.Wu > 32) return fail(DRM_EUNSUPPORTED, "M_hnsw > 32 is not supported by the search kernel");
+    if (dx.code_size != 8 && dx.code_size != 16) return fail(DRM_EUNSUPPORTED, "only M_pq of 8 or 16 (nbits 8) is supported by the search kernel");
+    int cap = ef > k ? ef : k;
+    cap = (cap + 31) / 32 * 32;
+    if (cap > 2048) return fail(DRM_EUNSUPPORTED, "max(ef, k) above 2048 is not supported");
+    if (dx.device < 0 || dx.device >= 64) return fail(DRM_EINVAL, "bad device ordinal");
+    if (!g_work_counter[dx.device]) DRM_CUDA_TRY(cudaMalloc(&g_work_counter[dx.device], 256));
+    DRM_CUDA_TRY(cudaMemsetAsync(g_work_counter[dx.device], 0, sizeof(unsigned), stream));
+
+    SearchParams p{};
+    p.q = q_dev; p.n = n; p.d = dx.d; p.M = dx.M; p.dsub = dx.dsub;
+    p.centroids = dx.centroids; p.rows0 = dx.rows0; p.up = dx.up;
+    p.row0_bytes = dx.row0_bytes; p.rowu_bytes = dx.rowu_bytes; p.W0 = dx.W0; p.Wu = dx.Wu; p.c0_off = dx.code0_off; p.cu_off = dx.codeu_off;
+    p.entry_vertex = dx.entry_vertex; p.entry_row = dx.entry_row; p.max_level = dx.max_level;
+    p.k = k; p.ef = ef; p.cap = cap;
+    p.D = D_dev; p.I = reinterpret_cast<long long *>(I_dev);
+    p.counters = reinterpret_cast<u64 *>(counters_dev);
+    p.next_query = g_work_counter[dx.device];
+    for (int i = 0; i < 64; ++i) p.entry_code[i] = dx.entry_code[i];
+    size_t smem = (size_t)WARPS_PER_CTA * ((size_t)dx.M * 256 * sizeof(float) + (size_t)cap * sizeof(u64));
+    const bool wide = dx.W0 > 32;
+    if (dx.code_size == 8) return wide ? launch_t<8, 2>(p, smem, dx.device, stream) : launch_t<8, 1>(p, smem, dx.device, stream);
+    return wide ? launch_t<16, 2>(p, smem, dx.device, stream) : launch_t<16, 1>(p, smem, dx.device, stream);
+}
+
+}  // namespace drm

@@ -1,0 +1,513 @@
+// Smith-Waterman rerank on sm_100a.
+//
+// Replaces post_process_sw_static / post_process_sw_dynamic (src/utils/post_processor.cpp:357-549) with
+// its callees find_sequences (:74-336), find_sequence (:47-66), sw_reranker (src/utils/reranker.cpp:3-51)
+// and calc_sw_score (src/utils/metrics.cpp:10-45): match +1, mismatch -1, linear gap -1, byte equality,
+// score = max over all cells.
+//
+// Fast kernel (sw_rerank_kernel): one CTA per read.  Candidate windows are scored two at a time in
+// the two 16-bit halves of a register (inter-task SIMD, native VIMNMX3.S16x2 / VIADDMNMX.S16x2.RELU on
+// sm_100a), each pair by a QUAD of lanes: lane l of the quad owns query columns [38l, 38l+38) in
+// registers and the window rows flow through the quad as a 4-deep software pipeline (one shuffle per
+// row).  Per cell pair:  s2 = PRMT(profile[j], sel_row)   (0 / 2 for mismatch / match)
+//                        m  = max3(diag + s2, up, left)   (= H + 1 before clamping)
+//                        h  = max(m - 1, 0)
+//                        best = max3(best, m_j, m_j+1)    (every other column)
+// The genome is held as 1-byte base classes (A,C,G,T,N = 0..4); reverse-complement windows are
+// produced by index arithmetic (3 - c), never materialised.
+//
+// Generic kernel (sw_generic_kernel): one thread per pair, int32, raw byte equality; used for
+// drm_sw_pairs and whenever the fast path's preconditions fail (query longer than 152, ref_len above
+// 256, bytes outside ACGTN in the reference).  Both are CUDA; there is no host path.
+#include "common.h"
+
+namespace drm {
+
+namespace {
+
+typedef unsigned long long u64;
+constexpr unsigned FULL = 0xffffffffu;
+constexpr int CPL = 38;             // query columns per lane
+constexpr int QCOLS = 4 * CPL;      // 152 = 150 + the '<' '>' decoration of format_fastq
+constexpr int MAX_FAST_REFLEN = 256;
+constexpr int MAXC = 1024;          // candidates per read handled in shared memory
+constexpr int MAXTAKE = 1024;
+constexpr int RERANK_THREADS = 256;
+constexpr int PAIRS_PER_PASS = RERANK_THREADS / 4;  // 64 pairs = 128 candidates per pass
+
+__device__ __forceinline__ int base_class(unsigned char c)
+{
+    switch (c) {
+    case 'A': return 0;
+    case 'C': return 1;
+    case 'G': return 2;
+    case 'T': return 3;
+    case 'N': return 4;
+    default: return 7;
+    }
+}
+
+__global__ void classify_kernel(const uint8_t *__restrict__ raw, uint8_t *__restrict__ cls, long long n, int *has_other)
+{
+    long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    long long step = (long long)gridDim.x * blockDim.x;
+    int other = 0;
+    for (; i < n; i += step) {
+        int c = base_class(raw[i]);
+        cls[i] = (uint8_t)c;
+        other |= c == 7;
+    }
+    if (__any_sync(FULL, other) && (threadIdx.x & 31) == 0) atomicExch(has_other, 1);
+}
+
+// ---- candidate expansion: find_sequences + the re-expansion in post_process_sw_* (src/utils/post_processor.cpp
+// :96-102,117-125,215-236,249-257,404-413,501-510), in size_t arithmetic like the reference.
+struct ExpandRule { int mode; u64 stride, bound; };
+__device__ __forceinline__ void expand_one(const ExpandRule &e, u64 s, u64 &first, int &count)
+{
+    if (e.stride == 1) {
+        first = s;
+        count = (e.mode == 1 || s < e.bound) ? 1 : 0;
+        return;
+    }
+    u64 p = s * e.stride;
+    if (p >= e.bound) { first = 0; count = 0; return; }
+    u64 start = p >= e.stride - 1 ? p - e.stride + 1 : 0;
+    u64 end = p + e.stride < e.bound ? p + e.stride : e.bound;
+    first = start;
+    count = (int)(end - start);
+}
+
+struct RerankDev {
+    const uint8_t *ref; int form; long long ref_n; int ref_len;  // classes; genome length or window count
+    ExpandRule rule;
+    const long long *neighbors; long long n, k_in; int take;
+    const char *q_flat; const long long *q_off;
+    short *scr_scores; u64 *scr_ids; int C;   // scratch for the batch: [n][C]
+    int *n_cands; int *min_cands; u64 *cells;
+};
+
+// class of base `i` of window `id`, 6 = "never matches" (window overruns / outside the table)
+__device__ __forceinline__ int window_base(const RerankDev &p, u64 id, bool valid, int i)
+{
+    if (!valid) return 6;
+    if (p.form == 1) return p.ref[id * (u64)p.ref_len + (u64)i];
+    u64 pos = id >> 1;
+    if (id & 1) {
+        int c = p.ref[pos + (u64)(p.ref_len - 1 - i)];
+        return c < 4 ? 3 - c : c;
+    }
+    return p.ref[pos + (u64)i];
+}
+__device__ __forceinline__ bool window_valid(const RerankDev &p, u64 id)
+{
+    if (p.form == 1) return id < (u64)p.ref_n;
+    u64 pos = id >> 1;
+    return pos + (u64)p.ref_len <= (u64)p.ref_n;  // find_sequence returns "" otherwise
+}
+
+template <bool QN>
+__device__ __forceinline__ unsigned sw_quad(const uint8_t *selrow, int rows, const unsigned *Qs, const unsigned *QNs, int lane)
+{
+    const int l = lane & 3;
+    unsigned Q[CPL], H[CPL];
+#pragma unroll
+    for (int j = 0; j < CPL; ++j) { Q[j] = Qs[CPL * l + j]; H[j] = 0; }
+    unsigned best = 0, last_out = 0, prev_recv = 0;
+    const unsigned NEG1 = 0xffffffffu;
+    for (int t = 0; t < rows + 3; ++t) {
+        unsigned recv = __shfl_up_sync(FULL, last_out, 1, 4);
+        if (l == 0) recv = 0;
+        const unsigned x8 = selrow[t - l + 3];
+        const unsigned sel = (x8 & 7u) | ((x8 & 0x70u) << 4) | 0x5050u;
+        unsigned diag = prev_recv, left = recv, mprev = 0;
+#pragma unroll
+        for (int j = 0; j < CPL; ++j) {
+            const unsigned s2 = __byte_perm(Q[j], QN ? QNs[CPL * l + j] : 0u, sel);
+            const unsigned x = diag + s2;
+            const unsigned up = H[j];
+            const unsigned m = __vimax3_s16x2(x, up, left);
+            const unsigned h = __viaddmax_s16x2_relu(m, NEG1, 0u);
+            if (j & 1) best = __vimax3_s16x2(best, m, mprev);
+            mprev = m;
+            diag = up;
+            left = h;
+            H[j] = h;
+        }
+        prev_recv = recv;
+        last_out = left;
+    }
+    best = __vmaxs2(best, __shfl_xor_sync(FULL, best, 1));
+    best = __vmaxs2(best, __shfl_xor_sync(FULL, best, 2));
+    return best;  // per half: max(H) + 1 (or 0)
+}
+
+__global__ void __launch_bounds__(RERANK_THREADS, 2) sw_rerank_kernel(const RerankDev p)
+{
+    __shared__ u64 s_cand[MAXC];
+    __shared__ u64 s_first[MAXTAKE];
+    __shared__ int s_count[MAXTAKE + 1];
+    __shared__ unsigned s_Q[QCOLS], s_QN[QCOLS];
+    __shared__ __align__(4) uint8_t s_sel[PAIRS_PER_PASS][MAX_FAST_REFLEN + 8];
+    __shared__ int s_nc, s_hasN;
+
+    const int tid = threadIdx.x, lane = tid & 31;
+    const long long r = blockIdx.x;
+    const long long qb = p.q_off[r];
+    const int lq = (int)(p.q_off[r + 1] - qb);
+    const int rows = p.ref_len;
+
+    // query profile: byte c of s_Q[j] = 2 when query base j is class c (0..3), s_QN[j] byte 0 = 2 for 'N'
+    if (tid == 0) s_hasN = 0;
+    __syncthreads();
+    for (int j = tid; j < QCOLS; j += RERANK_THREADS) {
+        unsigned q = 0, qn = 0;
+        if (j < lq) {
+            int c = base_class((unsigned char)p.q_flat[qb + j]);
+            if (c < 4) q = 2u << (8 * c);
+            else if (c == 4) { qn = 2u; s_hasN = 1; }
+        }
+        s_Q[j] = q;
+        s_QN[j] = qn;
+    }
+    // candidate list
+    const long long *nb = p.neighbors + r * p.k_in;
+    for (int i = tid; i < p.take; i += RERANK_THREADS) {
+        u64 first; int count;
+        expand_one(p.rule, (u64)nb[i], first, count);
+        s_first[i] = first;
+        s_count[i] = count;
+    }
+    __syncthreads();
+    if (tid == 0) {
+        int acc = 0;
+        for (int i = 0; i < p.take; ++i) { int c = s_count[i]; s_count[i] = acc; acc += c; }
+        s_count[p.take] = acc;
+        s_nc = acc;
+    }
+    __syncthreads();
+    const int nc = s_nc;  // host guarantees take * per <= MAXC
+    for (int i = tid; i < p.take; i += RERANK_THREADS) {
+        int b = s_count[i], e = s_count[i + 1];
+        u64 f = s_first[i];
+        for (int c = b; c < e; ++c) s_cand[c] = f + (u64)(c - b);
+    }
+    if (tid == 0) {
+        if (p.n_cands) p.n_cands[r] = nc;
+        if (p.min_cands) atomicMin(p.min_cands, nc);
+        if (p.cells) atomicAdd(p.cells, (u64)nc * (u64)rows * (u64)lq);
+    }
+    __syncthreads();
+
+    const bool hasN = s_hasN != 0;
+    const int pair = tid >> 2;
+    for (int c0 = 0; c0 < nc; c0 += 2 * PAIRS_PER_PASS) {
+        // stage the (base_a | base_b << 4) rows of this pass, 3 never-match rows of padding either side
+        const int npairs = min(PAIRS_PER_PASS, (nc - c0 + 1) / 2);
+        for (int e = tid; e < npairs * (rows + 6); e += RERANK_THREADS) {
+            int pr = e / (rows + 6), i = e % (rows + 6) - 3;
+            int ca = c0 + 2 * pr, cb = ca + 1;
+            unsigned v = 0x66;
+            if (i >= 0 && i < rows) {
+                u64 ida = s_cand[ca];
+                int a = window_base(p, ida, window_valid(p, ida), i);
+                int b = 6;
+                if (cb < nc) { u64 idb = s_cand[cb]; b = window_base(p, idb, window_valid(p, idb), i); }
+                v = (unsigned)a | ((unsigned)b << 4);
+            }
+            s_sel[pr][i + 3] = (uint8_t)v;
+        }
+        __syncthreads();
+        // warps whose 8 pairs are all beyond npairs skip the DP (warp-uniform)
+        if ((tid >> 5) * 8 < npairs) {
+            const uint8_t *selrow = s_sel[pair < npairs ? pair : 0];
+            unsigned best = hasN ? sw_quad<true>(selrow, rows, s_Q, s_QN, lane) : sw_quad<false>(selrow, rows, s_Q, s_QN, lane);
+            if ((lane & 3) == 0 && pair < npairs) {
+                int sa = (int)(short)(best & 0xffffu) - 1, sb = (int)(short)(best >> 16) - 1;
+                int ca = c0 + 2 * pair;
+                size_t base = (size_t)r * p.C;
+                p.scr_scores[base + ca] = (short)(sa > 0 ? sa : 0);
+                p.scr_ids[base + ca] = s_cand[ca];
+                if (ca + 1 < nc) {
+                    p.scr_scores[base + ca + 1] = (short)(sb > 0 ? sb : 0);
+                    p.scr_ids[base + ca + 1] = s_cand[ca + 1];
+                }
+            }
+        }
+        __syncthreads();
+    }
+}
+
+// ---- top-k: std::partial_sort(idx, idx+k, idx+n, scores[a] > scores[b]) exactly as libstdc++ runs it
+// (heap-select over [0,k) + sort_heap), so equal scores come out in the reference's order
+// (src/utils/reranker.cpp:35-48).  One thread per read.
+#define SW_COMP(a, b) (sc[(a)] > sc[(b)])
+__device__ void ps_push_heap(unsigned short *first, int hole, int top, unsigned short value, const short *sc)
+{
+    int parent = (hole - 1) / 2;
+    while (hole > top && SW_COMP(first[parent], value)) {
+        first[hole] = first[parent];
+        hole = parent;
+        parent = (hole - 1) / 2;
+    }
+    first[hole] = value;
+}
+__device__ void ps_adjust_heap(unsigned short *first, int hole, int len, unsigned short value, const short *sc)
+{
+    const int top = hole;
+    int child = hole;
+    while (child < (len - 1) / 2) {
+        child = 2 * (child + 1);
+        if (SW_COMP(first[child], first[child - 1])) child--;
+        first[hole] = first[child];
+        hole = child;
+    }
+    if ((len & 1) == 0 && child == (len - 2) / 2) {
+        child = 2 * (child + 1);
+        first[hole] = first[child - 1];
+        hole = child - 1;
+    }
+    ps_push_heap(first, hole, top, value, sc);
+}
+
+__global__ void sw_select_kernel(const short *__restrict__ scr_scores, const u64 *__restrict__ scr_ids, int C,
+                                 const int *__restrict__ n_cands, long long n, int k, int *out_scores, u64 *out_ids)
+{
+    long long r = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (r >= n) return;
+    const int nc = n_cands[r];
+    if (nc < k || nc == 0) return;  // the host raises "Not enough candidates" for the batch
+    unsigned short idx[MAXC];
+    short sc[MAXC];
+    const short *src = scr_scores + (size_t)r * C;
+    for (int i = 0; i < nc; ++i) { idx[i] = (unsigned short)i; sc[i] = src[i]; }
+    if (k >= 2) {
+        int parent = (k - 2) / 2;
+        for (;;) {
+            unsigned short value = idx[parent];
+            ps_adjust_heap(idx, parent, k, value, sc);
+            if (parent == 0) break;
+            parent--;
+        }
+    }
+    for (int i = k; i < nc; ++i) {
+        if (SW_COMP(idx[i], idx[0])) {
+            unsigned short value = idx[i];
+            idx[i] = idx[0];
+            ps_adjust_heap(idx, 0, k, value, sc);
+        }
+    }
+    int last = k;
+    while (last > 1) {
+        --last;
+        unsigned short value = idx[last];
+        idx[last] = idx[0];
+        ps_adjust_heap(idx, 0, last, value, sc);
+    }
+    const u64 *ids = scr_ids + (size_t)r * C;
+    for (int i = 0; i < k; ++i) {
+        out_scores[r * k + i] = sc[idx[i]];
+        out_ids[r * k + i] = ids[idx[i]];
+    }
+}
+#undef SW_COMP
+
+
+// ---------------------------------------------------------------------------------------------
+// Generic scorer: one thread per pair, int32, raw byte equality (calc_sw_score verbatim semantics).
+// The rolling row lives in a global scratch laid out [column][thread] so that a warp's accesses to
+// one column are coalesced.
+__device__ __forceinline__ unsigned char comp_raw(unsigned char c)
+{
+    switch (c & 0x7f) {  // the reference's table has 128 entries (src/utils/parse_inputs.cpp:5-14)
+    case 'A': return 'T';
+    case 'T': return 'A';
+    case 'C': return 'G';
+    case 'G': return 'C';
+    case 'N': return 'N';
+    default: return 0;
+    }
+}
+
+struct PairView { const uint8_t *a; int la; bool rc; const uint8_t *b; int lb; long long out; };
+
+struct FlatPairs {  // drm_sw_pairs
+    const char *a_flat; const long long *a_off; const char *b_flat; const long long *b_off;
+    __device__ bool get(long long i, PairView &v) const
+    {
+        v.a = reinterpret_cast<const uint8_t *>(a_flat) + a_off[i]; v.la = (int)(a_off[i + 1] - a_off[i]); v.rc = false;
+        v.b = reinterpret_cast<const uint8_t *>(b_flat) + b_off[i]; v.lb = (int)(b_off[i + 1] - b_off[i]);
+        v.out = i;
+        return true;
+    }
+};
+
+struct RerankPairs {  // fallback rerank: pair = (read, candidate slot)
+    const uint8_t *raw; int form; long long ref_n; int ref_len;
+    const char *q_flat; const long long *q_off; const u64 *scr_ids; const int *n_cands; int C;
+    __device__ bool get(long long i, PairView &v) const
+    {
+        long long r = i / C;
+        int c = (int)(i % C);
+        if (c >= n_cands[r]) return false;
+        u64 id = scr_ids[i];
+        v.b = reinterpret_cast<const uint8_t *>(q_flat) + q_off[r]; v.lb = (int)(q_off[r + 1] - q_off[r]);
+        v.out = i; v.rc = false; v.la = ref_len;
+        if (form == 1) {
+            if (id >= (u64)ref_n) v.la = 0;
+            v.a = raw + id * (u64)ref_len;
+        } else {
+            u64 pos = id >> 1;
+            if (pos + (u64)ref_len > (u64)ref_n) v.la = 0;
+            v.a = raw + pos; v.rc = (id & 1) != 0;
+        }
+        return true;
+    }
+};
+
+template <class Src>
+__global__ void sw_generic_kernel(const Src src, long long npairs, int *__restrict__ Hs, short *out16, int *out32)
+{
+    const long long T = (long long)gridDim.x * blockDim.x;
+    const long long tid = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    int *H = Hs + tid;
+    for (long long i = tid; i < npairs; i += T) {
+        PairView v;
+        if (!src.get(i, v)) continue;
+        for (int j = 0; j <= v.lb; ++j) H[(long long)j * T] = 0;
+        int best = 0;
+        for (int ia = 0; ia < v.la; ++ia) {
+            const unsigned char ca = v.rc ? comp_raw(v.a[v.la - 1 - ia]) : v.a[ia];
+            int diag = 0, left = 0;
+            for (int j = 1; j <= v.lb; ++j) {
+                const int up = H[(long long)j * T];
+                int h = diag + (ca == v.b[j - 1] ? 1 : -1);
+                h = max(h, up - 1);
+                h = max(h, left - 1);
+                h = max(h, 0);
+                H[(long long)j * T] = h;
+                best = max(best, h);
+                diag = up;
+                left = h;
+            }
+        }
+        if (out16) out16[v.out] = (short)best;
+        if (out32) out32[v.out] = best;
+    }
+}
+
+// candidate lists for the fallback rerank: one thread per read
+__global__ void expand_kernel(const RerankDev p)
+{
+    long long r = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (r >= p.n) return;
+    const long long *nb = p.neighbors + r * p.k_in;
+    int nc = 0;
+    for (int i = 0; i < p.take; ++i) {
+        u64 first; int count;
+        expand_one(p.rule, (u64)nb[i], first, count);
+        for (int c = 0; c < count; ++c) p.scr_ids[(size_t)r * p.C + nc + c] = first + (u64)c;
+        nc += count;
+    }
+    if (p.n_cands) p.n_cands[r] = nc;
+    if (p.min_cands) atomicMin(p.min_cands, nc);
+    if (p.cells) atomicAdd(p.cells, (u64)nc * (u64)p.ref_len * (u64)(p.q_off[r + 1] - p.q_off[r]));
+}
+
+}  // namespace
+
+int launch_classify(const uint8_t *raw, uint8_t *cls, int64_t n, int *has_other_dev, cudaStream_t stream)
+{
+    if (n <= 0) return DRM_OK;
+    long long blocks = (n + 255) / 256;
+    if (blocks > 148 * 16) blocks = 148 * 16;
+    classify_kernel<<<(unsigned)blocks, 256, 0, stream>>>(raw, cls, n, has_other_dev);
+    DRM_CUDA_TRY(cudaGetLastError());
+    return DRM_OK;
+}
+
+int launch_sw_pairs(const char *a_flat, const int64_t *a_off, const char *b_flat, const int64_t *b_off, int64_t n,
+                    int max_len_b, int32_t *scores, cudaStream_t stream)
+{
+    if (n <= 0) return DRM_OK;
+    long long threads = n < 148LL * 1024 ? (n + 127) / 128 * 128 : 148LL * 1024;
+    int *H = nullptr;
+    DRM_CUDA_TRY(cudaMallocAsync(&H, (size_t)threads * (size_t)(max_len_b + 1) * sizeof(int), stream));
+    FlatPairs src{a_flat, reinterpret_cast<const long long *>(a_off), b_flat, reinterpret_cast<const long long *>(b_off)};
+    sw_generic_kernel<FlatPairs><<<(unsigned)(threads / 128), 128, 0, stream>>>(src, n, H, nullptr, scores);
+    DRM_CUDA_TRY(cudaGetLastError());
+    DRM_CUDA_TRY(cudaFreeAsync(H, stream));
+    return DRM_OK;
+}
+
+// One batch of reads.  All pointers are device pointers; q_off holds absolute offsets into q_flat.
+int launch_rerank(const DeviceRef &ref, const RerankArgs &a, cudaStream_t stream)
+{
+    if (a.n <= 0) return DRM_OK;
+    if (a.k < 0 || a.k_clusters <= 0 || a.stride <= 0 || a.k_in <= 0) return fail(DRM_EINVAL, "bad rerank arguments");
+    if ((uint64_t)a.k > (uint64_t)a.k_clusters * 2u * (uint64_t)a.stride)
+        return fail(DRM_EKTOOLARGE, "Final k too large. Ensure k < k_clusters * 2 * stride to have enough candidates.");
+    if (ref.form == 1 && a.mode == 1) return fail(DRM_EINVAL, "dynamic mode needs a genome reference (drm_ref_open_genome)");
+    const int take = (int)(a.k_clusters < a.k_in ? a.k_clusters : a.k_in);
+    const long long per = a.stride == 1 ? 1 : 2 * a.stride - 1;
+    const long long C = (long long)take * per;
+    if (C > MAXC || take > MAXTAKE) return fail(DRM_EUNSUPPORTED, "more than 1024 candidates per read (k_clusters * (2*stride-1))");
+    if (a.k > C) return fail(DRM_ENOTENOUGH, "Not enough candidates (" + std::to_string(C) + " < " + std::to_string(a.k) + ")");
+
+    RerankDev p{};
+    p.form = ref.form; p.ref_n = ref.len; p.ref_len = ref.ref_len;
+    p.rule.mode = a.mode; p.rule.stride = (u64)a.stride;
+    if (a.mode == 1) p.rule.bound = (u64)ref.len;                       // genome length in bases
+    else if (ref.form == 1) p.rule.bound = (u64)ref.len;                // number of windows
+    else p.rule.bound = ref.len >= ref.ref_len ? 2ull * (u64)(ref.len - ref.ref_len + 1) : 0ull;
+    p.k_in = a.k_in; p.take = take;
+    p.q_flat = a.q_flat;
+    p.C = (int)C;
+    p.min_cands = a.min_cands; p.cells = reinterpret_cast<u64 *>(a.cells);
+
+    const bool fast = !ref.has_other && a.max_qlen <= QCOLS && ref.ref_len <= MAX_FAST_REFLEN;
+    const long long batch_max = 131072;
+    short *scr_scores = nullptr; u64 *scr_ids = nullptr; int *ncand_tmp = nullptr; int *H = nullptr;
+    const long long B = a.n < batch_max ? a.n : batch_max;
+    DRM_CUDA_TRY(cudaMallocAsync(&scr_scores, (size_t)B * C * sizeof(short), stream));
+    DRM_CUDA_TRY(cudaMallocAsync(&scr_ids, (size_t)B * C * sizeof(u64), stream));
+    if (!a.n_cands) DRM_CUDA_TRY(cudaMallocAsync(&ncand_tmp, (size_t)a.n * sizeof(int), stream));
+    int *n_cands = a.n_cands ? a.n_cands : ncand_tmp;
+    const long long gthreads = 148LL * 1024;
+    if (!fast) DRM_CUDA_TRY(cudaMallocAsync(&H, (size_t)gthreads * (size_t)(a.max_qlen + 1) * sizeof(int), stream));
+    if (a.k > 0) {
+        DRM_CUDA_TRY(cudaMemsetAsync(a.out_scores, 0, (size_t)a.n * a.k * sizeof(int32_t), stream));
+        DRM_CUDA_TRY(cudaMemsetAsync(a.out_ids, 0, (size_t)a.n * a.k * sizeof(uint64_t), stream));
+    }
+    for (long long b0 = 0; b0 < a.n; b0 += B) {
+        const long long nb = a.n - b0 < B ? a.n - b0 : B;
+        p.n = nb;
+        p.neighbors = reinterpret_cast<const long long *>(a.neighbors) + b0 * a.k_in;
+        p.q_off = reinterpret_cast<const long long *>(a.q_off) + b0;
+        p.scr_scores = scr_scores; p.scr_ids = scr_ids;
+        p.n_cands = n_cands + b0;
+        if (fast) {
+            p.ref = ref.data;
+            sw_rerank_kernel<<<(unsigned)nb, RERANK_THREADS, 0, stream>>>(p);
+            DRM_CUDA_TRY(cudaGetLastError());
+        } else {
+            expand_kernel<<<(unsigned)((nb + 127) / 128), 128, 0, stream>>>(p);
+            DRM_CUDA_TRY(cudaGetLastError());
+            RerankPairs src{ref.raw, ref.form, ref.len, ref.ref_len, a.q_flat, p.q_off, scr_ids, p.n_cands, (int)C};
+            sw_generic_kernel<RerankPairs><<<(unsigned)(gthreads / 128), 128, 0, stream>>>(src, nb * C, H, scr_scores, nullptr);
+            DRM_CUDA_TRY(cudaGetLastError());
+        }
+        if (a.k > 0) {
+            sw_select_kernel<<<(unsigned)((nb + 63) / 64), 64, 0, stream>>>(scr_scores, scr_ids, (int)C, p.n_cands, nb, (int)a.k,
+                                                                           a.out_scores + b0 * a.k, reinterpret_cast<u64 *>(a.out_ids) + b0 * a.k);
+            DRM_CUDA_TRY(cudaGetLastError());
+        }
+    }
+    DRM_CUDA_TRY(cudaFreeAsync(scr_scores, stream));
+    DRM_CUDA_TRY(cudaFreeAsync(scr_ids, stream));
+    if (ncand_tmp) DRM_CUDA_TRY(cudaFreeAsync(ncand_tmp, stream));
+    if (H) DRM_CUDA_TRY(cudaFreeAsync(H, stream));
+    return DRM_OK;
+}
+
+}  // namespace drm

@@ -1,0 +1,125 @@
+/*
+ * drm_b200.h — C ABI of libdrm_cuda.so, the B200 (sm_100a) implementation of DeepReadMapper's
+ * search-time hot path: batched HNSW-PQ search + Smith-Waterman rerank.
+ *
+ * The reference has no FFI layer; its hot path sits behind three C++ call sites.  Each entry point
+ * below names the reference interface it replaces (paths relative to the reference repository):
+ *
+ *   drm_index_open / drm_index_close   faiss::read_index + dynamic_cast<IndexHNSWPQ*> + delete
+ *                                      src/main.cpp:236-237,299 ; src/hnswpq/test_search.cpp:68-76
+ *   drm_search                         faiss_search -> IndexHNSWPQ::search
+ *                                      src/hnswpq/search.cpp:6-57 ; includes/hnswpq/search.hpp:18-22
+ *   drm_ref_open_*                     ref_seqs / ref_genome arguments of post_process_sw_{static,dynamic}
+ *                                      src/main.cpp:178-199 ; src/utils/post_processor.cpp:47-71
+ *   drm_sw_rerank                      post_process_sw_static / post_process_sw_dynamic (+ find_sequences,
+ *                                      sw_reranker)  src/utils/post_processor.cpp:357-549 ;
+ *                                      src/utils/reranker.cpp:3-51
+ *   drm_sw_pairs                       calc_sw_score over a batch of pairs (the test_sw_score workload)
+ *                                      src/utils/metrics.cpp:10-45 ; src/test_sw_score.cpp:44-52
+ *   drm_merge_topk_device              (new) per-read K-way merge for a position-sharded index
+ *
+ * Conventions: every function returns 0 on success and a negative DRM_E* code on failure;
+ * drm_last_error() returns the thread-local message for the last failure on the calling thread.
+ * The caller owns every host buffer; handles own device memory.  No C++ types, exceptions or torch
+ * types cross this boundary.  There is NO CPU fallback: without a CUDA device every compute entry
+ * point fails with DRM_ECUDA.
+ *
+ * "_device" variants take DEVICE pointers (already resident in HBM on the handle's device) and a
+ * cudaStream_t passed as void*; they enqueue work and return without synchronising.
+ */
+#ifndef DRM_B200_H
+#define DRM_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define DRM_OK 0
+#define DRM_EINVAL (-1)      /* bad argument */
+#define DRM_EIO (-2)         /* file missing / unreadable / not an IHNp index */
+#define DRM_ECUDA (-3)       /* CUDA runtime error, or no device */
+#define DRM_EUNSUPPORTED (-4) /* index parameters outside what the kernels implement */
+#define DRM_ENOTENOUGH (-5)  /* "Not enough candidates (a < k)" — src/utils/reranker.cpp:26-29 */
+#define DRM_EKTOOLARGE (-6)  /* "Final k too large..." — src/utils/post_processor.cpp:389-392,486-489 */
+#define DRM_EEMPTY (-7)      /* "Query data is empty" — src/hnswpq/search.cpp:16-19 */
+
+typedef struct drm_index drm_index;
+typedef struct drm_ref drm_ref;
+
+/* Counters summed over the queries of one call (same definitions as FAISS hnsw_stats). */
+typedef struct drm_search_stats {
+    int64_t nhops0;    /* level-0 expansions */
+    int64_t nhops_up;  /* upper-level row scans */
+    int64_t ndis_eval; /* level-0 ADC evaluations performed by the kernel (>= FAISS ndis: the kernel
+                          has no visited table) */
+    double device_ms;  /* kernel time, CUDA events (host-pointer calls only; 0 for _device calls) */
+    double h2d_ms;     /* host->device copy time (host-pointer calls only) */
+    double d2h_ms;     /* device->host copy time (host-pointer calls only) */
+} drm_search_stats;
+
+const char *drm_last_error(void);
+int drm_device_count(void);
+const char *drm_version(void);
+
+/* ------------------------------------------------------------------ index (FAISS IHNp file) */
+/* devices: CUDA ordinals to load a full replica on (n_dev >= 1).  Host-pointer search calls shard
+ * the query batch contiguously over the replicas; _device calls address one replica by slot. */
+int drm_index_open(const char *index_file, const int *devices, int n_dev, drm_index **out);
+void drm_index_close(drm_index *ix);
+/* info[0..11] = d, ntotal, M_pq, nbits, M_hnsw, entry_point, max_level, efConstruction, efSearch,
+ *               n_links, n_replicas, device bytes per replica */
+int drm_index_info(const drm_index *ix, int64_t *info);
+
+/* q: n x d row-major fp32 (host).  D: n x k fp32 ascending ADC squared-L2; I: n x k int64 labels,
+ * unfilled slots D = FLT_MAX, I = -1.  stats may be NULL. */
+int drm_search(drm_index *ix, const float *q, int64_t n, int d, int k, int ef, float *D, int64_t *I,
+               drm_search_stats *stats);
+/* Same on device pointers of replica `slot`; counters (3 x int64: nhops0, nhops_up, ndis_eval) are
+ * accumulated into counters_dev when non-NULL. */
+int drm_search_device(drm_index *ix, int slot, const float *q_dev, int64_t n, int d, int k, int ef,
+                      float *D_dev, int64_t *I_dev, int64_t *counters_dev, void *stream);
+
+/* ------------------------------------------------------------------ reference windows */
+/* Genome form: window id -> (pos = id/2, reverse-complement = id%2), src/utils/post_processor.cpp:47-66.
+ * genome bytes must be the cleaned sequence the reference holds (extract_FASTA_sequence). */
+int drm_ref_open_genome(const char *genome, int64_t len, int ref_len, const int *devices, int n_dev,
+                        drm_ref **out);
+/* Table form: n_windows strings of ref_len bytes each (ref_seqs[id], find_sequence_static). */
+int drm_ref_open_windows(const char *windows_flat, int64_t n_windows, int ref_len, const int *devices,
+                         int n_dev, drm_ref **out);
+void drm_ref_close(drm_ref *r);
+
+/* ------------------------------------------------------------------ Smith-Waterman */
+/* scores[i] = calc_sw_score(a_i, b_i); a_i = a_flat[a_off[i] .. a_off[i+1]). */
+int drm_sw_pairs(const char *a_flat, const int64_t *a_off, const char *b_flat, const int64_t *b_off,
+                 int64_t n, int32_t *scores);
+
+/* mode 0 = static bound rule (bound = number of dense windows), 1 = dynamic (bound = genome length;
+ * stride == 1 keeps every id, windows that overrun the genome score 0).
+ * neighbors: n x k_in int64 search labels; the first min(k_clusters, k_in) of each row are used.
+ * Outputs: out_scores n x k (int32, descending, libstdc++ partial_sort tie order), out_ids n x k
+ * (dense window ids, uint64), n_cands[n] (nullable).  Errors: DRM_EKTOOLARGE, DRM_ENOTENOUGH. */
+int drm_sw_rerank(drm_ref *r, int mode, const int64_t *neighbors, int64_t n, int64_t k_in,
+                  const char *q_flat, const int64_t *q_off, int64_t stride, int64_t k, int64_t k_clusters,
+                  int32_t *out_scores, uint64_t *out_ids, int32_t *n_cands, double *device_ms);
+/* Device form (replica `slot`): q_flat_dev/q_off_dev/neighbors_dev/out_* all device pointers;
+ * max_qlen = max query length (host knows it).  min_cands_dev (int32, nullable) receives the minimum
+ * candidate count over the batch so the caller can raise DRM_ENOTENOUGH after synchronising.
+ * cells_dev (int64, nullable) accumulates the DP cell updates performed. */
+int drm_sw_rerank_device(drm_ref *r, int slot, int mode, const int64_t *neighbors_dev, int64_t n, int64_t k_in,
+                         const char *q_flat_dev, const int64_t *q_off_dev, int max_qlen, int64_t stride,
+                         int64_t k, int64_t k_clusters, int32_t *out_scores_dev, uint64_t *out_ids_dev,
+                         int32_t *n_cands_dev, int32_t *min_cands_dev, int64_t *cells_dev, void *stream);
+
+/* ------------------------------------------------------------------ sharded-index merge */
+/* D_all/I_all: n_shards x n x k (the all-gathered per-shard results, each row ascending, I already
+ * offset to global ids); writes the global top-k per read to D_out/I_out (n x k), ordered by (D, I). */
+int drm_merge_topk_device(int device, const float *D_all, const int64_t *I_all, int n_shards, int64_t n, int k,
+                          float *D_out, int64_t *I_out, void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DRM_B200_H */
