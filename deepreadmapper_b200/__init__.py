@@ -1,0 +1,11 @@
+"""drm-b200: B200-native HNSW-PQ search + Smith-Waterman rerank (DeepReadMapper's search-time hot path).
+
+The product is the C-ABI shared library ``deepreadmapper_b200/lib/libdrm_cuda.so`` (include/drm_b200.h) and
+the C++ host binaries built on it.  This Python package is the thin ctypes mirror of the reference's
+call sites used by tests/ and bench.py.  It never imports ``oracle`` and has no CPU compute path:
+without the built library, or without a CUDA device, the compute calls raise.
+"""
+from .api import (  # noqa: F401
+    DrmError, Index, Reference, build_index, calc_sw_score, faiss_search, lib, lib_path, merge_topk_device,
+    post_process_sw_dynamic, post_process_sw_static, sw_pairs, sw_reranker,
+)

@@ -1,0 +1,252 @@
+"""ctypes mirror of the reference's hot-path call sites over libdrm_cuda.so (include/drm_b200.h).
+
+Names and argument meaning follow the reference (paths relative to the reference repository):
+  faiss_search(index, query_data, k, ef)            src/hnswpq/search.cpp:6-57
+  post_process_sw_static / post_process_sw_dynamic  src/utils/post_processor.cpp:357-549
+  sw_reranker(cand_seqs, cand_ids, query_seq, k)    src/utils/reranker.cpp:3-51
+  calc_sw_score(seq1, seq2)                         src/utils/metrics.cpp:10-45
+Errors the reference throws as std::runtime_error are raised as DrmError with the same message.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB_PATH = os.path.join(_HERE, "lib", "libdrm_cuda.so")
+_lib = None
+
+
+class DrmError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__(msg)
+        self.code = code
+
+
+class SearchStats(C.Structure):
+    _fields_ = [("nhops0", C.c_int64), ("nhops_up", C.c_int64), ("ndis_eval", C.c_int64),
+                ("device_ms", C.c_double), ("h2d_ms", C.c_double), ("d2h_ms", C.c_double)]
+
+
+EXPORTS = ["drm_last_error", "drm_device_count", "drm_version", "drm_index_open", "drm_index_close", "drm_index_info",
+           "drm_search", "drm_search_device", "drm_ref_open_genome", "drm_ref_open_windows", "drm_ref_close",
+           "drm_sw_pairs", "drm_sw_rerank", "drm_sw_rerank_device", "drm_merge_topk_device", "drm_build_index"]
+
+
+def lib_path() -> str:
+    return _LIB_PATH
+
+
+def lib():
+    """Load libdrm_cuda.so.  Fails loudly when it has not been built: there is no fallback."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(_LIB_PATH):
+            raise DrmError(-3, f"{_LIB_PATH} is missing: run `make lib` (or __graft_entry__.build()); there is no CPU fallback")
+        L = C.CDLL(_LIB_PATH)
+        vp, i64, i32 = C.c_void_p, C.c_int64, C.c_int
+        L.drm_last_error.restype = C.c_char_p
+        L.drm_version.restype = C.c_char_p
+        L.drm_device_count.restype = i32
+        L.drm_index_open.argtypes = [C.c_char_p, C.POINTER(i32), i32, C.POINTER(vp)]
+        L.drm_index_close.argtypes = [vp]
+        L.drm_index_close.restype = None
+        L.drm_index_info.argtypes = [vp, vp]
+        L.drm_search.argtypes = [vp, vp, i64, i32, i32, i32, vp, vp, C.POINTER(SearchStats)]
+        L.drm_search_device.argtypes = [vp, i32, vp, i64, i32, i32, i32, vp, vp, vp, vp]
+        L.drm_ref_open_genome.argtypes = [C.c_char_p, i64, i32, C.POINTER(i32), i32, C.POINTER(vp)]
+        L.drm_ref_open_windows.argtypes = [C.c_char_p, i64, i32, C.POINTER(i32), i32, C.POINTER(vp)]
+        L.drm_ref_close.argtypes = [vp]
+        L.drm_ref_close.restype = None
+        L.drm_sw_pairs.argtypes = [C.c_char_p, vp, C.c_char_p, vp, i64, vp]
+        L.drm_sw_rerank.argtypes = [vp, i32, vp, i64, i64, C.c_char_p, vp, i64, i64, i64, vp, vp, vp, C.POINTER(C.c_double)]
+        L.drm_sw_rerank_device.argtypes = [vp, i32, i32, vp, i64, i64, vp, vp, i32, i64, i64, i64, vp, vp, vp, vp, vp, vp]
+        L.drm_merge_topk_device.argtypes = [i32, vp, vp, i32, i64, i32, vp, vp, vp]
+        L.drm_build_index.argtypes = [vp, i64, i32, vp, i64, i32, i32, i32, i32, i32, C.c_uint32, C.c_char_p]
+        _lib = L
+    return _lib
+
+
+def _check(rc):
+    if rc != 0:
+        raise DrmError(rc, lib().drm_last_error().decode())
+
+
+def _devs(devices):
+    devices = [0] if devices is None else list(devices)
+    return (C.c_int * len(devices))(*devices), len(devices)
+
+
+def flatten(seqs):
+    bs = [s.encode() if isinstance(s, str) else bytes(s) for s in seqs]
+    off = np.zeros(len(bs) + 1, dtype=np.int64)
+    if bs:
+        off[1:] = np.cumsum([len(b) for b in bs])
+    return b"".join(bs), off
+
+
+class Index:
+    """Handle on an IHNp index resident on one or more GPUs (faiss::read_index + cast, src/main.cpp:236-237)."""
+
+    def __init__(self, index_file: str, devices=None):
+        arr, n = _devs(devices)
+        h = C.c_void_p()
+        _check(lib().drm_index_open(os.fsencode(index_file), arr, n, C.byref(h)))
+        self._h = h
+        info = np.zeros(12, dtype=np.int64)
+        _check(lib().drm_index_info(self._h, info.ctypes.data))
+        (self.d, self.ntotal, self.M_pq, self.nbits, self.M_hnsw, self.entry_point, self.max_level,
+         self.efConstruction, self.efSearch, self.n_links, self.n_replicas, self.device_bytes) = (int(v) for v in info)
+
+    def close(self):
+        if getattr(self, "_h", None):
+            lib().drm_index_close(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def search(self, x, k, ef, return_stats=False):
+        x = np.ascontiguousarray(x, dtype=np.float32)
+        if x.ndim != 2:
+            raise DrmError(-1, "Error: Expected 2D array")
+        n, d = x.shape
+        D = np.empty((n, k), dtype=np.float32)
+        I = np.empty((n, k), dtype=np.int64)
+        st = SearchStats()
+        _check(lib().drm_search(self._h, x.ctypes.data, n, d, k, ef, D.ctypes.data, I.ctypes.data, C.byref(st)))
+        if return_stats:
+            return D, I, {f: getattr(st, f) for f, _ in SearchStats._fields_}
+        return D, I
+
+    def search_device(self, q_ptr, n, k, ef, D_ptr, I_ptr, counters_ptr=0, stream=0, slot=0):
+        _check(lib().drm_search_device(self._h, slot, q_ptr, n, self.d, k, ef, D_ptr, I_ptr, counters_ptr or None,
+                                       stream or None))
+
+
+def faiss_search(index: Index, query_data, k=128, ef=128):
+    """(neighbors, distances) exactly like the reference's faiss_search: labels int64 (-1 = unfilled)."""
+    q = np.asarray(query_data, dtype=np.float32)
+    if q.size == 0:
+        raise DrmError(-7, "Query data is empty")
+    D, I = index.search(q, k, ef)
+    return I, D
+
+
+class Reference:
+    """Reference windows on the GPU: a genome (dynamic fetch, id -> pos/strand) or a window table (static)."""
+
+    def __init__(self, genome=None, windows=None, ref_len=150, devices=None):
+        arr, n = _devs(devices)
+        h = C.c_void_p()
+        self.ref_len = ref_len
+        if genome is not None:
+            g = genome.encode() if isinstance(genome, str) else bytes(genome)
+            self.form, self.length = 0, len(g)
+            _check(lib().drm_ref_open_genome(g, len(g), ref_len, arr, n, C.byref(h)))
+        else:
+            flat = b"".join(w.encode() if isinstance(w, str) else bytes(w) for w in windows) if not isinstance(windows, (bytes, bytearray)) else bytes(windows)
+            nw = len(flat) // ref_len
+            self.form, self.length = 1, nw
+            _check(lib().drm_ref_open_windows(flat, nw, ref_len, arr, n, C.byref(h)))
+        self._h = h
+
+    def close(self):
+        if getattr(self, "_h", None):
+            lib().drm_ref_close(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def rerank(self, mode, neighbors, query_seqs, stride, k, k_clusters, return_extra=False):
+        nb = np.ascontiguousarray(neighbors, dtype=np.int64)
+        n, k_in = nb.shape
+        q_flat, q_off = flatten(query_seqs)
+        scores = np.zeros((n, k), dtype=np.int32)
+        ids = np.zeros((n, k), dtype=np.uint64)
+        ncand = np.zeros(n, dtype=np.int32)
+        ms = C.c_double(0)
+        _check(lib().drm_sw_rerank(self._h, mode, nb.ctypes.data, n, k_in, q_flat, q_off.ctypes.data, stride, k, k_clusters,
+                                   scores.ctypes.data, ids.ctypes.data, ncand.ctypes.data, C.byref(ms)))
+        if return_extra:
+            return scores, ids, ncand, ms.value
+        return scores, ids
+
+    def rerank_device(self, mode, nb_ptr, n, k_in, qflat_ptr, qoff_ptr, max_qlen, stride, k, k_clusters, scores_ptr, ids_ptr,
+                      ncand_ptr=0, min_ptr=0, cells_ptr=0, stream=0, slot=0):
+        _check(lib().drm_sw_rerank_device(self._h, slot, mode, nb_ptr, n, k_in, qflat_ptr, qoff_ptr, max_qlen, stride, k,
+                                          k_clusters, scores_ptr, ids_ptr, ncand_ptr or None, min_ptr or None,
+                                          cells_ptr or None, stream or None))
+
+
+def _post_process(mode, neighbors, ref: Reference, query_seqs, ref_len, stride, k, k_clusters):
+    if ref.ref_len != ref_len:
+        raise DrmError(-1, "ref_len does not match the Reference handle")
+    scores, ids = ref.rerank(mode, neighbors, query_seqs, stride, k, k_clusters)
+    return scores.reshape(-1), ids.reshape(-1)
+
+
+def post_process_sw_static(neighbors, distances, ref: Reference, query_seqs, ref_len, stride, k, k_clusters=5):
+    """(scores[n*k], ids[n*k]) — the int / size_t halves of the reference's returned tuple (sequences are
+    recoverable from ids; strings never leave the host)."""
+    return _post_process(0, neighbors, ref, query_seqs, ref_len, stride, k, k_clusters)
+
+
+def post_process_sw_dynamic(neighbors, distances, ref: Reference, query_seqs, ref_len, stride, k, k_clusters=5):
+    return _post_process(1, neighbors, ref, query_seqs, ref_len, stride, k, k_clusters)
+
+
+def sw_pairs(a_list, b_list):
+    a_flat, a_off = flatten(a_list)
+    b_flat, b_off = flatten(b_list)
+    out = np.zeros(len(a_list), dtype=np.int32)
+    _check(lib().drm_sw_pairs(a_flat, a_off.ctypes.data, b_flat, b_off.ctypes.data, len(a_list), out.ctypes.data))
+    return out
+
+
+def calc_sw_score(seq1, seq2) -> int:
+    return int(sw_pairs([seq1], [seq2])[0])
+
+
+def sw_reranker(cand_seqs, cand_ids, query_seq, k):
+    """(top_scores, top_ids) for one query over explicit candidate strings (src/utils/reranker.cpp:3-51)."""
+    n = len(cand_seqs)
+    if n == 0 or k == 0:
+        return np.zeros(0, np.int32), np.zeros(0, np.uint64)
+    if n < k:
+        raise DrmError(-5, f"Not enough candidates ({n} < {k})")
+    lens = {len(c) for c in cand_seqs}
+    if len(lens) != 1:
+        raise DrmError(-1, "sw_reranker needs equal-length candidate windows")
+    ref = Reference(windows=list(cand_seqs), ref_len=lens.pop())
+    try:
+        nb = np.arange(n, dtype=np.int64)[None, :]
+        scores, idx = ref.rerank(0, nb, [query_seq], 1, k, n)
+    finally:
+        ref.close()
+    return scores[0], np.asarray(cand_ids, dtype=np.uint64)[idx[0].astype(np.int64)]
+
+
+def merge_topk_device(device, D_all_ptr, I_all_ptr, n_shards, n, k, D_out_ptr, I_out_ptr, stream=0):
+    _check(lib().drm_merge_topk_device(device, D_all_ptr, I_all_ptr, n_shards, n, k, D_out_ptr, I_out_ptr, stream or None))
+
+
+def build_index(x, out_path, M_pq=8, nbits=8, M_hnsw=16, efc=200, train=None, threads=0, seed=1234):
+    """hnswpq_index's build_faiss_index (src/hnswpq/index.cpp:86-193) for .npy embeddings."""
+    x = np.ascontiguousarray(x, dtype=np.float32)
+    n, d = x.shape
+    if train is None:
+        step = 2  # Config::Build::SAMPLE_RATE = 0.5, evenly strided (src/hnswpq/index.cpp:57-84,99)
+        train = x[::step]
+    train = np.ascontiguousarray(train, dtype=np.float32)
+    _check(lib().drm_build_index(x.ctypes.data, n, d, train.ctypes.data, train.shape[0], M_pq, nbits, M_hnsw, efc, threads,
+                                 seed, os.fsencode(out_path)))

@@ -39,7 +39,7 @@ struct SearchParams {
     int row0_bytes, rowu_bytes, W0, Wu, c0_off, cu_off;
     long long entry_vertex, entry_row;
     int max_level;
-    int k, ef, cap;
+    int k, ef, cap, cap_alloc;
     float *D;
     long long *I;
     u64 *counters;        // nhops0, nhops_up, ndis_eval (nullable)
@@ -136,7 +136,7 @@ __global__ void __launch_bounds__(WARPS_PER_CTA * 32) hnswpq_search_kernel(const
 {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const size_t per_warp = (size_t)p.M * 256 * sizeof(float) + (size_t)p.cap * sizeof(u64);
+    const size_t per_warp = (size_t)p.M * 256 * sizeof(float) + (size_t)p.cap_alloc * sizeof(u64);
     float *T = reinterpret_cast<float *>(smem_raw + warp * per_warp);
     u64 *pool = reinterpret_cast<u64 *>(smem_raw + warp * per_warp + (size_t)p.M * 256 * sizeof(float));
     const int cap = p.cap;
@@ -342,8 +342,8 @@ int launch_search(const DeviceIndex &dx, const float *q_dev, int64_t n, int k, i
     if (dx.ksub != 256) return fail(DRM_EUNSUPPORTED, "only nbits == 8 product quantizers are supported by the search kernel");
     if (dx.W0 > 64 || dx.Wu > 32) return fail(DRM_EUNSUPPORTED, "M_hnsw > 32 is not supported by the search kernel");
     if (dx.code_size != 8 && dx.code_size != 16) return fail(DRM_EUNSUPPORTED, "only M_pq of 8 or 16 (nbits 8) is supported by the search kernel");
-    int cap = ef > k ? ef : k;
-    cap = (cap + 31) / 32 * 32;
+    const int cap = ef > k ? ef : k;              // logical capacity: exactly FAISS's max(efSearch, k)
+    const int cap_alloc = (cap + 31) / 32 * 32;
     if (cap > 2048) return fail(DRM_EUNSUPPORTED, "max(ef, k) above 2048 is not supported");
     if (dx.device < 0 || dx.device >= 64) return fail(DRM_EINVAL, "bad device ordinal");
     if (!g_work_counter[dx.device]) DRM_CUDA_TRY(cudaMalloc(&g_work_counter[dx.device], 256));
@@ -354,12 +354,12 @@ int launch_search(const DeviceIndex &dx, const float *q_dev, int64_t n, int k, i
     p.centroids = dx.centroids; p.rows0 = dx.rows0; p.up = dx.up;
     p.row0_bytes = dx.row0_bytes; p.rowu_bytes = dx.rowu_bytes; p.W0 = dx.W0; p.Wu = dx.Wu; p.c0_off = dx.code0_off; p.cu_off = dx.codeu_off;
     p.entry_vertex = dx.entry_vertex; p.entry_row = dx.entry_row; p.max_level = dx.max_level;
-    p.k = k; p.ef = ef; p.cap = cap;
+    p.k = k; p.ef = ef; p.cap = cap; p.cap_alloc = cap_alloc;
     p.D = D_dev; p.I = reinterpret_cast<long long *>(I_dev);
     p.counters = reinterpret_cast<u64 *>(counters_dev);
     p.next_query = g_work_counter[dx.device];
     for (int i = 0; i < 64; ++i) p.entry_code[i] = dx.entry_code[i];
-    size_t smem = (size_t)WARPS_PER_CTA * ((size_t)dx.M * 256 * sizeof(float) + (size_t)cap * sizeof(u64));
+    size_t smem = (size_t)WARPS_PER_CTA * ((size_t)dx.M * 256 * sizeof(float) + (size_t)cap_alloc * sizeof(u64));
     const bool wide = dx.W0 > 32;
     if (dx.code_size == 8) return wide ? launch_t<8, 2>(p, smem, dx.device, stream) : launch_t<8, 1>(p, smem, dx.device, stream);
     return wide ? launch_t<16, 2>(p, smem, dx.device, stream) : launch_t<16, 1>(p, smem, dx.device, stream);

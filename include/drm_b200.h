@@ -113,11 +113,32 @@ int drm_sw_rerank_device(drm_ref *r, int slot, int mode, const int64_t *neighbor
                          int64_t k, int64_t k_clusters, int32_t *out_scores_dev, uint64_t *out_ids_dev,
                          int32_t *n_cands_dev, int32_t *min_cands_dev, int64_t *cells_dev, void *stream);
 
+/* ------------------------------------------------------------------ the whole stage in one call */
+/* Search + SW rerank as the pipeline runs them back to back (src/main.cpp:270-296 then :301-354 with the
+ * SW variants of :333-341): labels never return to the host between the two stages.  Reads are cut into
+ * chunks that are double-buffered over two streams per replica, so host<->device copies overlap the
+ * kernels (pass pinned host buffers for that to be effective).  The search asks for k_search labels
+ * (K when stride == 1, K_clusters otherwise, src/main.cpp:55-63,278); the rerank uses the first
+ * min(k_clusters, k_search) of them.  D/I (n x k_search) are the raw search output that the reference
+ * saves as distances.npy / indices.npy; sw_scores/sw_ids (n x k) are the rerank output.  Any of the four
+ * output pointers may be NULL to skip that copy.  timing_ms[0..1] (nullable) = {device span, wall}. */
+int drm_search_rerank(drm_index *ix, drm_ref *ref, int mode, const float *q, int64_t n, int d, int k_search, int ef,
+                      const char *q_flat, const int64_t *q_off, int64_t stride, int64_t k, int64_t k_clusters,
+                      float *D, int64_t *I, int32_t *sw_scores, uint64_t *sw_ids, drm_search_stats *stats,
+                      double *timing_ms);
+
 /* ------------------------------------------------------------------ sharded-index merge */
 /* D_all/I_all: n_shards x n x k (the all-gathered per-shard results, each row ascending, I already
  * offset to global ids); writes the global top-k per read to D_out/I_out (n x k), ordered by (D, I). */
 int drm_merge_topk_device(int device, const float *D_all, const int64_t *I_all, int n_shards, int64_t n, int k,
                           float *D_out, int64_t *I_out, void *stream);
+
+/* ------------------------------------------------------------------ index build (host, OpenMP) */
+/* build_faiss_index (src/hnswpq/index.cpp:86-193): train the product quantizer on `train`
+ * (n_train x d; NULL = use x), encode x (n x d), build the HNSW graph with efConstruction = efc and
+ * write a FAISS IHNp file.  Not part of the timed search path. */
+int drm_build_index(const float *x, int64_t n, int d, const float *train, int64_t n_train, int M_pq, int nbits,
+                    int M_hnsw, int efc, int threads, uint32_t seed, const char *out_path);
 
 #ifdef __cplusplus
 }

@@ -20,11 +20,12 @@
  * One deliberate knob: `tie_rule`.
  *   0 = FAISS    MinimaxHeap::pop_min breaks exact distance ties by the highest slot of FAISS's
  *                binary-heap array (layout dependent).
- *   1 = CANONICAL  pop_min breaks exact ties by (smallest id); everything else identical.  This is
- *                the rule the CUDA kernel implements (a layout-free sorted pool), so GPU == oracle(1)
- *                bit for bit, and oracle(0) vs oracle(1) measures what the tie rule changes (only
- *                queries where two live candidates have bit-equal PQ distances — BASELINE.json's
- *                "identical except where PQ distances tie").
+ *   1 = CANONICAL  every distance comparison is made on the total order (distance, id) — see
+ *                search_one_canonical below.  This is the rule the CUDA kernel implements (a
+ *                layout-free sorted pool), so GPU == oracle(1) bit for bit, and oracle(0) vs
+ *                oracle(1) measures what the tie rule changes (only queries where two candidates
+ *                have bit-equal PQ distances — BASELINE.json's "identical except where PQ
+ *                distances tie").
  * The ADC table uses a fixed summation order with fmaf so that CPU and GPU agree to the last bit
  * (real FAISS uses SIMD reductions whose last ulp differs).
  */
@@ -328,6 +329,78 @@ void search_one(const OrcIndex &ix, const float *x, int k, int efSearch, int tie
     heap_reorder<int64_t>((size_t)k, D, I);
 }
 
+// CANONICAL tie rule (tie_rule = 1): the same search, but every comparison that FAISS makes on the
+// distance alone is made on the total order (distance, id), and a popped candidate keeps its id:
+//   push      : a full candidate set rejects v unless (d, v) < its largest (d, id) entry;
+//   pop_min   : the unexpanded entry with the smallest (d, id);
+//   count_below(d0): entries with d < d0 (unchanged);
+//   results   : the k smallest (d, id) among all evaluated vertices.
+// Written out, the candidate MinimaxHeap becomes a sorted array of at most cap = max(ef, k) entries
+// and - because cap >= k - the result heap is simply its first k entries.  Wherever no two distances
+// are bit-equal this is exactly FAISS's procedure; it differs from tie_rule 0 only in which of
+// several equal-distance vertices survive at a full boundary.  The CUDA kernel implements this rule.
+void search_one_canonical(const OrcIndex &ix, const float *x, int k, int efSearch, VisitedTable &vt,
+                          std::vector<float> &T, float *D, int64_t *I, Stats &st)
+{
+    for (int j = 0; j < k; ++j) { D[j] = FLT_MAX; I[j] = -1; }
+    if (ix.entry_point < 0 || ix.ntotal == 0) return;
+    adc_table(ix, x, T.data());
+    int32_t nearest = ix.entry_point;
+    float d_nearest = adc_dis(ix, T.data(), nearest);
+    for (int level = ix.max_level; level >= 1; --level) {
+        for (;;) {
+            int32_t prev = nearest;
+            uint64_t o = ix.offsets[(size_t)nearest];
+            uint64_t begin = o + (uint64_t)ix.cum[(size_t)level], end = o + (uint64_t)ix.cum[(size_t)level + 1];
+            for (uint64_t j = begin; j < end; ++j) {
+                int32_t v = ix.neighbors[j];
+                if (v < 0) break;
+                float dis = adc_dis(ix, T.data(), v);
+                st.ndis_up++;
+                if (dis < d_nearest) { nearest = v; d_nearest = dis; }
+            }
+            st.nhops_up++;
+            if (nearest == prev) break;
+        }
+    }
+    struct Ent { float d; int32_t id; bool expanded; };
+    auto less = [](float d1, int32_t i1, float d2, int32_t i2) { return d1 < d2 || (d1 == d2 && i1 < i2); };
+    const size_t cap = (size_t)std::max(efSearch, k);
+    std::vector<Ent> pool;
+    pool.reserve(cap + 1);
+    pool.push_back({d_nearest, nearest, false});
+    vt.set(nearest);
+    for (;;) {
+        size_t cur = 0;
+        while (cur < pool.size() && pool[cur].expanded) ++cur;
+        if (cur == pool.size()) break;
+        const float d0 = pool[cur].d;
+        const int32_t v0 = pool[cur].id;
+        pool[cur].expanded = true;
+        int below = 0;
+        for (const Ent &e : pool) below += e.d < d0;
+        if (below >= efSearch) break;
+        uint64_t o = ix.offsets[(size_t)v0];
+        uint64_t begin = o + (uint64_t)ix.cum[0], end = o + (uint64_t)ix.cum[1];
+        for (uint64_t j = begin; j < end; ++j) {
+            int32_t v1 = ix.neighbors[j];
+            if (v1 < 0) break;
+            if (vt.get(v1)) continue;
+            vt.set(v1);
+            float dd = adc_dis(ix, T.data(), v1);
+            st.ndis++;
+            if (pool.size() == cap && !less(dd, v1, pool.back().d, pool.back().id)) continue;
+            size_t pos = 0;
+            while (pos < pool.size() && less(pool[pos].d, pool[pos].id, dd, v1)) ++pos;
+            pool.insert(pool.begin() + (ptrdiff_t)pos, Ent{dd, v1, false});
+            if (pool.size() > cap) pool.pop_back();
+        }
+        st.nhops++;
+    }
+    vt.advance();
+    for (size_t j = 0; j < pool.size() && j < (size_t)k; ++j) { D[j] = pool[j].d; I[j] = pool[j].id; }
+}
+
 }  // namespace
 
 extern "C" {
@@ -405,7 +478,8 @@ int orc_search(void *h, const float *x, int64_t n, int k, int ef, int tie_rule, 
 #pragma omp for schedule(guided)
         for (int64_t i = 0; i < n; ++i) {
             Stats st;
-            search_one(*ix, x + i * ix->d, k, ef, tie_rule, vt, T, D + i * k, I + i * k, st);
+            if (tie_rule == 1) search_one_canonical(*ix, x + i * ix->d, k, ef, vt, T, D + i * k, I + i * k, st);
+            else search_one(*ix, x + i * ix->d, k, ef, tie_rule, vt, T, D + i * k, I + i * k, st);
             s0 += st.ndis; s1 += st.nhops; s2 += st.ndis_up; s3 += st.nhops_up;
             if (per_query) { per_query[2 * i] = (int32_t)st.ndis; per_query[2 * i + 1] = (int32_t)st.nhops; }
         }

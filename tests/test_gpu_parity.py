@@ -1,0 +1,259 @@
+"""GPU parity tests: the CUDA path, called through the C ABI (deepreadmapper_b200.api -> libdrm_cuda.so),
+against the CPU oracle and the committed golden vectors.  Bit-exact for SW scores, ids and search (D, I)."""
+import os
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def drm():
+    import deepreadmapper_b200 as d
+    assert d.lib().drm_device_count() >= 1, "no CUDA device"
+    return d
+
+
+# ------------------------------------------------------------------ Smith-Waterman
+def test_sw_pairs100_golden(golden, drm):
+    q = golden["fixtures"]["quer"]
+    got = drm.sw_pairs(q[:100], q[1:101]).tolist()
+    assert got == golden["sw_pairs100"] and sum(got) == 2696
+
+
+def test_sw_named_known_answers(golden, fixtures, drm):
+    q0, w, n = fixtures["quer"][0], fixtures["windows"], golden["sw_named"]
+    a = [q0, w[561], w[560], w[561], "", q0, "NNNN", "acgt", w[10][:97]]
+    b = [q0, q0, q0, "<" + q0 + ">", q0, "", "NNNN", "ACGT", q0[13:140]]
+    want = [n["q0_q0"], n["w561_q0"], n["w560_q0"], n["w561_q0_decorated"], n["empty_q0"], n["q0_empty"], n["N_vs_N"],
+            n["lower_vs_upper"], n["ragged"]]
+    assert drm.sw_pairs(a, b).tolist() == want
+    assert drm.calc_sw_score(w[561], q0) == 138
+
+
+def test_sw_matrix_checksum(golden, fixtures, drm):
+    m, w = golden["sw_matrix"], fixtures["windows"]
+    tot = 0
+    for r in range(m["n_reads"]):
+        row = drm.sw_pairs(w, [fixtures["quer"][r]] * len(w))
+        assert int(row.sum()) == m["row_sums"][r] and int(row.argmax()) == m["argmax"][r]
+        if r < 4:
+            assert row.tolist() == m["rows4"][r]
+        tot += int(row.sum())
+    assert tot == m["checksum"]
+
+
+def test_sw_pairs_random_vs_oracle(drm, ob):
+    rng = np.random.default_rng(5)
+    alpha = np.frombuffer(b"ACGTN", dtype=np.uint8)
+    a, b = [], []
+    for _ in range(600):
+        la, lb = rng.integers(0, 260, 2)
+        x = alpha[rng.integers(0, 5 if rng.random() < .3 else 4, la)].tobytes()
+        if rng.random() < .5 and la > 10:
+            y = bytearray(x[: max(1, lb)])
+            for p in rng.integers(0, len(y), max(1, len(y) // 12)):
+                y[p] = alpha[rng.integers(0, 4)]
+            y = bytes(y)
+        else:
+            y = alpha[rng.integers(0, 4, lb)].tobytes()
+        if rng.random() < .1:
+            y = y.lower()
+        a.append(x)
+        b.append(y)
+    assert drm.sw_pairs(a, b).tolist() == ob.sw_pairs(a, b).tolist()
+
+
+def _refs(drm, fixtures):
+    return {0: drm.Reference(windows=fixtures["windows"], ref_len=150), 1: drm.Reference(genome=fixtures["genome"], ref_len=150),
+            "g0": drm.Reference(genome=fixtures["genome"], ref_len=150)}
+
+
+def test_rerank_goldens(golden, fixtures, drm):
+    refs = _refs(drm, fixtures)
+    for case in golden["rerank"]:
+        nb = np.array(case["neighbors"], dtype=np.int64)
+        # static mode is checked on both device forms: the uploaded window table and the genome + static bound rule
+        for ref in ([refs[0], refs["g0"]] if case["mode"] == 0 else [refs[1]]):
+            if "error" in case:
+                with pytest.raises(drm.DrmError) as e:
+                    ref.rerank(case["mode"], nb, case["queries"], case["stride"], case["k"], case["k_clusters"])
+                if case["error"].startswith("Final k too large"):
+                    assert e.value.code == -6 and str(e.value) == case["error"]
+                else:
+                    assert e.value.code == -5 and str(e.value).startswith("Not enough candidates")
+                continue
+            s, ids, nc, _ = ref.rerank(case["mode"], nb, case["queries"], case["stride"], case["k"], case["k_clusters"], return_extra=True)
+            assert s.tolist() == case["scores"], case["tag"]
+            assert [[int(v) for v in r] for r in ids] == case["ids"], case["tag"]
+            assert nc.tolist() == case["n_cands"], case["tag"]
+
+
+def test_rerank_random_vs_oracle(fixtures, drm, ob):
+    """Random neighbour tables, decorated and ragged queries, N-containing queries, both modes, strides 1..16."""
+    rng = np.random.default_rng(3)
+    refs = _refs(drm, fixtures)
+    reads = list(fixtures["reads"][:40])
+    reads[3] = reads[3][1:-1]
+    reads[5] = reads[5][:97]
+    reads[7] = reads[7][:60] + "N" * 5 + reads[7][65:]
+    reads[9] = reads[9].lower()
+    g = fixtures["genome"].encode()
+    wins = "".join(fixtures["windows"]).encode()
+    for mode in (0, 1):
+        for stride, kc, k in [(1, 128, 128), (1, 64, 10), (4, 20, 50), (8, 32, 128), (8, 5, 20), (16, 8, 60), (2, 100, 33)]:
+            hi = fixtures["n_windows"] // stride if mode == 0 else len(fixtures["genome"]) // stride
+            hi = max(hi - (1 if mode == 1 else 0), kc + 1)
+            nb = np.stack([rng.permutation(hi)[:kc] for _ in reads]).astype(np.int64)
+            refb, nref = (wins, fixtures["n_windows"]) if mode == 0 else (g, len(g))
+            rc, s1, i1, nc1 = ob.post_process_sw(mode, nb, refb, nref, 150, reads, stride, k, kc)
+            if rc != 0:
+                with pytest.raises(drm.DrmError):
+                    refs[mode].rerank(mode, nb, reads, stride, k, kc)
+                continue
+            s2, i2, nc2, _ = refs[mode].rerank(mode, nb, reads, stride, k, kc, return_extra=True)
+            assert s2.tolist() == s1.tolist(), (mode, stride, kc, k)
+            assert i2.tolist() == i1.tolist(), (mode, stride, kc, k)
+            assert nc2.tolist() == nc1.tolist()
+
+
+def test_rerank_generic_path_long_queries(fixtures, drm, ob):
+    """Queries longer than the fast kernel's 152 columns take the generic CUDA kernel; same answers."""
+    rng = np.random.default_rng(9)
+    ref = drm.Reference(genome=fixtures["genome"], ref_len=150)
+    reads = [r + r[:30] for r in fixtures["reads"][:6]]
+    nb = np.stack([rng.permutation(1600)[:32] for _ in reads]).astype(np.int64)
+    g = fixtures["genome"].encode()
+    rc, s1, i1, _ = ob.post_process_sw(1, nb, g, len(g), 150, reads, 1, 32, 32)
+    assert rc == 0
+    s2, i2 = ref.rerank(1, nb, reads, 1, 32, 32)
+    assert s2.tolist() == s1.tolist() and i2.tolist() == i1.tolist()
+
+
+def test_sw_reranker_and_empty(fixtures, drm, ob):
+    w, q = fixtures["windows"][500:560], fixtures["quer"][0]
+    sc, ids = drm.sw_reranker(w, list(range(1000, 1060)), q, 20)
+    full = ob.sw_pairs(w, [q] * len(w))
+    idx = ob.partial_sort_desc(full, 20)
+    assert sc.tolist() == full[idx].tolist() and ids.tolist() == (1000 + idx).tolist()
+    with pytest.raises(drm.DrmError):
+        drm.sw_reranker(w[:5], list(range(5)), q, 20)
+    assert len(drm.sw_reranker([], [], q, 3)[0]) == 0
+
+
+# ------------------------------------------------------------------ HNSW-PQ search
+@pytest.fixture(scope="module")
+def small_index(tmp_path_factory, fixtures):
+    """BASELINE config 1: the 1000-bp fixture genome, 1702 windows, M_pq=8 nbits=8 M_hnsw=16 EFC=200."""
+    import deepreadmapper_b200 as d
+    from deepreadmapper_b200 import synth
+    p = str(tmp_path_factory.mktemp("idx") / "ecoli_150.index")
+    E = synth.embed_windows(fixtures["genome"].encode())
+    d.build_index(E, p, efc=200, seed=1)
+    reads = np.frombuffer("".join(r[1:-1] for r in fixtures["reads"]).encode(), dtype=np.uint8).reshape(150, 150)
+    return p, synth.embed_reads(reads)
+
+
+@pytest.fixture(scope="module")
+def mid_index(tmp_path_factory):
+    import deepreadmapper_b200 as d
+    from deepreadmapper_b200 import synth
+    p = str(tmp_path_factory.mktemp("idx") / "mid.index")
+    g = synth.random_genome(60000, 42)
+    d.build_index(synth.embed_windows(g), p, efc=100, seed=2)
+    reads, ids = synth.simulate_reads(g, 3000)
+    return p, synth.embed_reads(reads), ids
+
+
+def _check_search(drm, ob, path, Q, k, ef):
+    oix = ob.OracleIndex(path)
+    D0, I0, st = oix.search(Q, k, ef, tie_rule=1)
+    ix = drm.Index(path)
+    D1, I1, gst = ix.search(Q, k, ef, return_stats=True)
+    ix.close()
+    assert np.array_equal(I1, I0), f"ids differ in {np.mean((I1 != I0).any(1)):.4f} of rows (k={k}, ef={ef})"
+    assert np.array_equal(D1.view(np.uint32), D0.view(np.uint32)), "distances not bit-identical"
+    assert gst["nhops0"] == st["nhops"] and gst["nhops_up"] == st["nhops_up"]
+    assert gst["ndis_eval"] >= st["ndis"]
+    return oix, D1, I1
+
+
+def test_search_config1_bit_exact(drm, ob, small_index):
+    path, Q = small_index
+    oix, D, I = _check_search(drm, ob, path, Q, 128, 128)
+    # invariants that do not depend on the oracle's traversal: ascending D, unique ids, D == dis(I)
+    assert (np.diff(D, axis=1) >= 0).all()
+    for i in range(0, len(Q), 7):
+        ids = I[i][I[i] >= 0]
+        assert len(set(ids.tolist())) == len(ids)
+        assert np.array_equal(oix.adc_distances(Q[i], I[i]).view(np.uint32), D[i].view(np.uint32))
+
+
+@pytest.mark.parametrize("k,ef", [(128, 128), (8, 32), (32, 64), (128, 512), (64, 256), (200, 128), (1, 16)])
+def test_search_ef_k_sweep_bit_exact(drm, ob, mid_index, k, ef):
+    path, Q, _ = mid_index
+    _check_search(drm, ob, path, Q[:1500], k, ef)
+
+
+def test_search_overlap_with_faiss_tie_rule(drm, ob, mid_index):
+    """north_star: recall@K overlap with the reference >= 0.99; rows that differ do so only through PQ-distance ties."""
+    path, Q, _ = mid_index
+    oix = ob.OracleIndex(path)
+    D0, I0, _ = oix.search(Q, 128, 128, tie_rule=0)
+    ix = drm.Index(path)
+    D1, I1 = ix.search(Q, 128, 128)
+    ix.close()
+    overlap = np.mean([len(set(I0[i].tolist()) & set(I1[i].tolist())) / 128 for i in range(len(Q))])
+    assert overlap >= 0.99, overlap
+
+
+def test_search_errors(drm, small_index):
+    path, Q = small_index
+    ix = drm.Index(path)
+    with pytest.raises(drm.DrmError) as e:
+        drm.faiss_search(ix, np.zeros((0, 128), np.float32))
+    assert str(e.value) == "Query data is empty"
+    with pytest.raises(drm.DrmError):
+        ix.search(np.zeros((3, 64), np.float32), 8, 16)
+    ix.close()
+    with pytest.raises(drm.DrmError) as e:
+        drm.Index(path + ".missing")
+    assert "Index file does not exist" in str(e.value)
+
+
+def test_search_then_rerank_pipeline(drm, ob, fixtures, small_index):
+    """The whole stage on config 1: search -> SW rerank, vs oracle search -> oracle rerank."""
+    path, Q = small_index
+    ix = drm.Index(path)
+    I, D = drm.faiss_search(ix, Q, 128, 128)
+    ix.close()
+    ref = drm.Reference(genome=fixtures["genome"], ref_len=150)
+    reads = list(fixtures["reads"])  # already carry the '<' '>' of format_fastq
+    s, ids = drm.post_process_sw_dynamic(I, D, ref, reads, 150, 1, 128, 128)
+    g = fixtures["genome"].encode()
+    rc, s0, i0, _ = ob.post_process_sw(1, I, g, len(g), 150, reads, 1, 128, 128)
+    assert rc == 0
+    assert s.tolist() == s0.reshape(-1).tolist() and ids.tolist() == i0.reshape(-1).tolist()
+
+
+def test_merge_topk(drm):
+    import torch
+    rng = np.random.default_rng(1)
+    S, n, k = 8, 300, 128
+    D = np.sort(rng.integers(0, 50, (S, n, k)).astype(np.float32), axis=2)  # tie-heavy
+    I = rng.permutation(S * n * k).reshape(S, n, k).astype(np.int64)
+    D[3, 5, 100:] = np.finfo(np.float32).max
+    I[3, 5, 100:] = -1
+    for s in range(S):  # rows must be ordered by (D, I)
+        for r in range(n):
+            o = np.lexsort((I[s, r].astype(np.uint64), D[s, r]))
+            D[s, r], I[s, r] = D[s, r][o], I[s, r][o]
+    dD, dI = torch.from_numpy(D).cuda(), torch.from_numpy(I).cuda()
+    oD, oI = torch.empty((n, k), dtype=torch.float32, device="cuda"), torch.empty((n, k), dtype=torch.int64, device="cuda")
+    drm.merge_topk_device(0, dD.data_ptr(), dI.data_ptr(), S, n, k, oD.data_ptr(), oI.data_ptr(), torch.cuda.current_stream().cuda_stream)
+    torch.cuda.synchronize()
+    for r in range(n):
+        d, i = D[:, r].reshape(-1), I[:, r].reshape(-1)
+        o = np.lexsort((i.astype(np.uint64), d))[:k]
+        assert np.array_equal(oD[r].cpu().numpy(), d[o]) and np.array_equal(oI[r].cpu().numpy(), i[o])
