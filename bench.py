@@ -1,0 +1,369 @@
+#!/usr/bin/env python
+"""bench.py - reads/sec of the search-time hot path (HNSW-PQ search + Smith-Waterman rerank) on B200.
+
+Workload (BASELINE.json configs[1]): full E. coli-sized dense index - a random 4 641 652-bp genome (the real
+tests/ecoli.fna is not shipped), both strands, N = 9 283 006 windows, stride 1, M_pq=8 nbits=8 M_hnsw=16 EFC=200 -
+searched with 1 000 000 synthetic 150-bp reads per GPU at EF=128 K=128, each read reranked against its 128
+candidate windows with Smith-Waterman.  One "step" = one pass of the path over the read batch.
+
+  value   device-timed: inputs resident in HBM, CUDA events on the launching stream, max over ranks
+  e2e     the same through the host-buffer C-ABI call drm_search_rerank (pinned host memory, copies inside)
+  --impl reference   the reference's CPU path on the host cores (FAISS-rule search restatement + the reference's
+                     own post_process_sw compiled unmodified when oracle/_ref is present), bounded sample
+N > 1: launched by torchrun, one rank per GPU, index replicated, reads sharded (each rank has its own batch):
+no data-path collective, weak scaling.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+GENOME_BASES = 4_641_652
+REF_LEN = 150
+EF = 128
+K = 128
+METRIC = "reads/sec (search+SW rerank)"
+
+
+def log(*a):
+    print("[bench]", *a, file=sys.stderr, flush=True)
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--reads", type=int, default=1_000_000, help="reads per GPU per step")
+    ap.add_argument("--genome-bases", type=int, default=GENOME_BASES)
+    ap.add_argument("--efc", type=int, default=200)
+    ap.add_argument("--cache", default=os.environ.get("DRM_CACHE", os.path.join(tempfile.gettempdir(), "drm_b200_cache")))
+    ap.add_argument("--cpu-sample", type=int, default=0, help="reads in the CPU baseline sample (0 = 600 per host core)")
+    ap.add_argument("--skip-cpu", action="store_true")
+    return ap.parse_args()
+
+
+def workload_paths(args):
+    os.makedirs(args.cache, exist_ok=True)
+    tag = f"g{args.genome_bases}_efc{args.efc}"
+    return os.path.join(args.cache, f"ecoli_dense_{tag}.index")
+
+
+def make_genome(args):
+    from deepreadmapper_b200 import synth
+    return synth.random_genome(args.genome_bases, 42)
+
+
+def ensure_index(args, genome, device=None):
+    """Builds the config's index once per box (hnswpq_index's job - outside the timed path) and caches the file."""
+    import deepreadmapper_b200 as drm
+    from deepreadmapper_b200 import synth
+    path = workload_paths(args)
+    if os.path.exists(path):
+        return path, 0.0
+    t0 = time.time()
+    if device is not None:
+        E = synth.embed_windows_torch(genome, device)
+    else:
+        E = synth.embed_windows(genome)
+    log(f"embedded {E.shape[0]} windows in {time.time() - t0:.1f}s; building HNSW-PQ index (EFC={args.efc}) on {os.cpu_count()} host cores")
+    t1 = time.time()
+    tmp = path + f".tmp{os.getpid()}"
+    drm.build_index(E, tmp, M_pq=8, nbits=8, M_hnsw=16, efc=args.efc, seed=1234)
+    os.replace(tmp, path)
+    log(f"index built in {time.time() - t1:.1f}s -> {path}")
+    return path, time.time() - t0
+
+
+def make_reads(genome, n, seed):
+    from deepreadmapper_b200 import synth
+    reads, truth = synth.simulate_reads(genome, n, REF_LEN, seed=seed)
+    Q = synth.embed_reads(reads)
+    return reads, truth, Q
+
+
+class ClockSampler:
+    Q = "clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, index):
+        self.f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-i", str(index), "-lms", "100"],
+                                      stdout=self.f, stderr=subprocess.DEVNULL)
+        except OSError:
+            self.p = None
+
+    def stop(self):
+        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": []}
+        if self.p is None:
+            return out
+        self.p.terminate()
+        try:
+            self.p.wait(timeout=5)
+        except Exception:
+            self.p.kill()
+        self.f.flush()
+        self.f.seek(0)
+        rows = [r.strip().split(", ") for r in self.f.read().strip().splitlines() if r.strip()]
+        self.f.close()
+        os.unlink(self.f.name)
+        rows = [r for r in rows if len(r) >= 7 and r[0].strip().isdigit()]
+        if not rows:
+            return out
+        sm = np.array([float(r[0]) for r in rows])
+        busy = sm[sm > 0.5 * sm.max()] if len(sm) else sm
+        out["sm_mhz"] = float(np.median(busy))
+        out["sm_max_mhz"] = float(rows[0][1])
+        out["power_w_max"] = max(float(r[2]) for r in rows if r[2].replace(".", "").isdigit()) if rows else None
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        out["reasons"] = [nm for i, nm in enumerate(names) if any(r[3 + i].strip().lower() == "active" for r in rows)]
+        out["samples"] = len(rows)
+        return out
+
+
+def cpu_reference_run(args, genome, index_path, reads, Q, n_sample, threads):
+    """The reference's CPU path on a bounded sample: FAISS-rule (tie_rule 0) HNSW-PQ search restatement, OpenMP over
+    queries with all host threads, then SW rerank - oracle/_ref (the reference's post_process_sw_dynamic, unmodified)
+    when present, else the oracle's C port.  Returns (reads/sec, seconds, kind, per-query counters)."""
+    from oracle import bindings as ob
+    oix = ob.OracleIndex(index_path)
+    qs = Q[:n_sample]
+    seqs = [bytes(r) for r in reads[:n_sample]]
+    t0 = time.perf_counter()
+    D, I, st = oix.search(qs, K, EF, tie_rule=0, threads=threads)
+    t1 = time.perf_counter()
+    use_ref = ob.have_ref()
+    rc, s, ids, _ = ob.post_process_sw(1, I, genome, len(genome), REF_LEN, seqs, 1, K, K, threads=threads, use_ref=use_ref)
+    t2 = time.perf_counter()
+    assert rc == 0, (rc, s)
+    counters = {k2: v / n_sample for k2, v in st.items()}
+    return n_sample / (t2 - t0), (t1 - t0, t2 - t1), ("reference" if use_ref else "port"), counters, (D, I, s, ids)
+
+
+def base_config(args, n_gpus):
+    return {"workload": "configs[1]: E. coli-sized dense index (random genome, both strands) + synthetic reads, search EF=128 K=128 + SW rerank of K candidates",
+            "genome_bases": args.genome_bases, "n_vectors": 2 * (args.genome_bases - REF_LEN + 1), "ref_len": REF_LEN, "stride": 1,
+            "M_pq": 8, "nbits": 8, "M_hnsw": 16, "EFC": args.efc, "EF": EF, "K": K, "reads_per_gpu": args.reads,
+            "sharding": f"reads sharded over {n_gpus} GPU(s), index replicated, no collective",
+            "l2": "inputs larger than L2 (index image 3.6 GB, read batch 0.66 GB); no explicit flush"}
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    threads = os.cpu_count() or 1
+    genome = make_genome(args)
+    dev = None
+    try:
+        import torch
+        if torch.cuda.is_available():
+            dev = "cuda:0"
+    except Exception:
+        pass
+    index_path, _ = ensure_index(args, genome, dev)
+    n_sample = args.cpu_sample or 600 * threads
+    reads, truth, Q = make_reads(genome, n_sample, seed=7)
+    times = []
+    kind = "port"
+    for it in range(args.warmup + args.steps):
+        rps, (ts, tw), kind, counters, _ = cpu_reference_run(args, genome, index_path, reads, Q, n_sample, threads)
+        log(f"reference step {it}: {rps:.1f} reads/s (search {ts:.2f}s, SW {tw:.2f}s)")
+        if it >= args.warmup:
+            times.append(ts + tw)
+    ms = 1e3 * float(np.mean(times))
+    value = n_sample / (ms / 1e3)
+    sample = (f"{n_sample} reads per step (same generator as the GPU arm); search = CPU restatement of FAISS IndexHNSWPQ::search "
+              f"(FAISS itself is not installable here), SW = " + ("the reference's post_process_sw_dynamic compiled unmodified (oracle/_ref)"
+                                                                  if kind == "reference" else "oracle C port of calc_sw_score/sw_reranker"))
+    line = {"impl": "reference", "metric": METRIC, "value": value, "unit": "reads/s", "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32 ADC distances + int32 SW", "data": "synthetic", "config": base_config(args, args.gpus),
+            "cpu_baseline": {"value": value, "unit": "reads/s", "cores": threads, "kind": kind, "sample": sample},
+            "e2e": {"value": value, "unit": "reads/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+    return 0
+
+
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+
+    import deepreadmapper_b200 as drm
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the hot path has no CPU fallback")
+    torch.cuda.set_device(local)
+    if world > 1:
+        import datetime
+        dist.init_process_group("nccl", timeout=datetime.timedelta(minutes=60), device_id=torch.device(f"cuda:{local}"))
+    barrier = (lambda: dist.barrier()) if world > 1 else (lambda: None)
+
+    genome = make_genome(args)
+    if rank == 0:
+        index_path, build_s = ensure_index(args, genome, f"cuda:{local}")
+    barrier()
+    index_path = workload_paths(args)
+    t0 = time.time()
+    ix = drm.Index(index_path, devices=[local])
+    ref = drm.Reference(genome=genome, ref_len=REF_LEN, devices=[local])
+    log(f"rank {rank}: index image on device in {time.time() - t0:.1f}s ({ix.device_bytes / 1e9:.2f} GB, N={ix.ntotal})")
+    n = args.reads
+    reads, truth, Q = make_reads(genome, n, seed=7 + rank)
+    q_off = np.arange(n + 1, dtype=np.int64) * REF_LEN
+    stream = torch.cuda.current_stream()
+    sp = stream.cuda_stream
+
+    # ---------------- device-resident arm
+    dQ = torch.from_numpy(Q).cuda()
+    dreads = torch.from_numpy(reads.reshape(-1)).cuda()
+    doff = torch.from_numpy(q_off).cuda()
+    dD = torch.empty((n, K), dtype=torch.float32, device="cuda")
+    dI = torch.empty((n, K), dtype=torch.int64, device="cuda")
+    dS = torch.empty((n, K), dtype=torch.int32, device="cuda")
+    dIds = torch.empty((n, K), dtype=torch.int64, device="cuda")
+    dcnt = torch.zeros(4, dtype=torch.int64, device="cuda")
+    dcells = torch.zeros(1, dtype=torch.int64, device="cuda")
+    dmin = torch.full((1,), 2**31 - 1, dtype=torch.int32, device="cuda")
+
+    def step():
+        ix.search_device(dQ.data_ptr(), n, K, EF, dD.data_ptr(), dI.data_ptr(), dcnt.data_ptr(), sp)
+        mid = torch.cuda.Event(enable_timing=True)
+        mid.record(stream)
+        ref.rerank_device(1, dI.data_ptr(), n, K, dreads.data_ptr(), doff.data_ptr(), REF_LEN, 1, K, K, dS.data_ptr(), dIds.data_ptr(),
+                          0, dmin.data_ptr(), dcells.data_ptr(), sp)
+        return mid
+
+    for _ in range(args.warmup):
+        step()
+    torch.cuda.synchronize()
+    dcnt.zero_()
+    dcells.zero_()
+    barrier()
+    torch.cuda.synchronize()
+    sampler = ClockSampler(local) if rank == 0 else None
+    evs = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps + 1)]
+    mids = []
+    evs[0].record(stream)
+    for i in range(args.steps):
+        mids.append(step())
+        evs[i + 1].record(stream)
+    torch.cuda.synchronize()
+    barrier()
+    clocks = sampler.stop() if sampler else None
+    total_ms = evs[0].elapsed_time(evs[-1])
+    search_ms = float(np.mean([evs[i].elapsed_time(mids[i]) for i in range(args.steps)]))
+    sw_ms = float(np.mean([mids[i].elapsed_time(evs[i + 1]) for i in range(args.steps)]))
+    assert int(dmin.item()) >= K, "rerank saw fewer than K candidates"
+    cnt = dcnt.cpu().numpy() / args.steps
+    cells = float(dcells.item()) / args.steps
+    launches_per_step = 1 + 2 * ((n + 131071) // 131072)
+
+    # ---------------- end-to-end arm: host buffers through drm_search_rerank
+    hQ = torch.from_numpy(Q).pin_memory()
+    hreads = torch.from_numpy(reads.reshape(-1)).pin_memory()
+    hD = torch.empty((n, K), dtype=torch.float32).pin_memory()
+    hI = torch.empty((n, K), dtype=torch.int64).pin_memory()
+    hS = torch.empty((n, K), dtype=torch.int32).pin_memory()
+    hIds = torch.empty((n, K), dtype=torch.int64).pin_memory()
+
+    def e2e_step():
+        return drm.search_rerank(ix, ref, 1, hQ.numpy(), hreads.data_ptr(), q_off, 1, K, K, K, EF, D=hD.numpy(), I=hI.numpy(),
+                                 sw_scores=hS.numpy(), sw_ids=hIds.numpy().view(np.uint64))
+
+    for _ in range(min(args.warmup, 2)):
+        e2e_step()
+    torch.cuda.synchronize()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        e2e_step()
+    torch.cuda.synchronize()
+    e2e_s = time.perf_counter() - t0
+    barrier()
+    h2d = Q.nbytes + reads.nbytes + q_off.nbytes
+    d2h = hD.numel() * 4 + hI.numel() * 8 + hS.numel() * 4 + hIds.numel() * 8
+    # the two arms must agree bit for bit
+    assert torch.equal(hI, dI.cpu()) and torch.equal(hS, dS.cpu()) and torch.equal(hIds, dIds.cpu()), "e2e arm differs from the device arm"
+
+    t = torch.tensor([total_ms, e2e_s * 1e3, search_ms, sw_ms], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    total_ms, e2e_ms, search_ms, sw_ms = (float(v) for v in t.cpu())
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return 0
+
+    ms_per_step = total_ms / args.steps
+    value = world * n / (ms_per_step / 1e3)
+    e2e_value = world * n / (e2e_ms / 1e3 / args.steps)
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    hbm_peak, peak_src = (peaks["hbm_gbs"], "measured (MEASURED_PEAKS.json)") if "hbm_gbs" in peaks else (6650.0, "fallback (B200_PROFILING.md)")
+    sm_max = (clocks or {}).get("sm_max_mhz") or 1965.0
+    sms = torch.cuda.get_device_properties(local).multi_processor_count
+    recall_truth = float((dIds[:, 0].cpu().numpy() >> 1 == (truth >> 1)).mean())
+
+    line = {"metric": METRIC, "value": value, "unit": "reads/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32 ADC distances + s16x2 SW", "data": "synthetic", "config": base_config(args, world),
+            "e2e": {"value": e2e_value, "unit": "reads/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h)},
+            "gpu_launches": int(launches_per_step * args.steps), "clocks": clocks,
+            "stages_ms": {"search": search_ms, "sw_rerank": sw_ms},
+            "sw_gcups": cells / (sw_ms / 1e3) / 1e9,
+            "top1_is_planted_position": recall_truth}
+    # per-query counters of the ORACLE (FAISS definitions) come from the cpu_baseline leg; the kernel's own are reported too
+    line["kernel_counters_per_read"] = {"nhops0": cnt[0] / n, "nhops_up": cnt[1] / n, "ndis_eval": cnt[2] / n}
+    cpu = None
+    if world == 1 and not args.skip_cpu:
+        threads = os.cpu_count() or 1
+        ns = args.cpu_sample or 600 * threads
+        rps, (ts, tw), kind, counters, (D0, I0, s0, ids0) = cpu_reference_run(args, genome, index_path, reads, Q, ns, threads)
+        overlap = float(np.mean([len(set(I0[i].tolist()) & set(hI[i].tolist())) / K for i in range(ns)]))
+        # SW parity on the sample: rerank the CPU labels on the GPU -> must equal the CPU rerank bit for bit
+        s1, ids1 = ref.rerank(1, I0, [bytes(r) for r in reads[:ns]], 1, K, K)
+        sw_equal = bool(np.array_equal(s1, s0) and np.array_equal(ids1, ids0))
+        cpu = {"value": rps, "unit": "reads/s", "cores": threads, "kind": kind,
+               "sample": f"{ns} reads of the same batch: search {ts:.2f}s (FAISS-rule CPU restatement, {threads} threads) + SW {tw:.2f}s "
+                         f"({'reference post_process_sw_dynamic unmodified' if kind == 'reference' else 'oracle C port'})",
+               "recall_overlap_vs_reference_rule": overlap, "sw_bit_exact_on_sample": sw_equal}
+        line["cpu_baseline"] = cpu
+        bytes_per_read = 128 * counters["nhops"] + 64 * counters["nhops_up"] + 8 * counters["ndis"] + 512 + 1536
+        line["oracle_counters_per_read"] = counters
+    else:
+        bytes_per_read = 128 * cnt[0] / n + 64 * cnt[1] / n + 8 * cnt[2] / n + 512 + 1536
+    ach = bytes_per_read * n / (search_ms / 1e3) / 1e9
+    line["roofline_search"] = {"kernel": "hnswpq_search_kernel", "bound": "hbm", "achieved": ach, "peak": hbm_peak, "unit": "GB/s",
+                               "frac": ach / hbm_peak, "traffic": None, "peak_source": peak_src,
+                               "algorithmic_bytes_per_read": bytes_per_read, "ms_per_launch": search_ms}
+    int_peak = sms * 128 * sm_max * 1e6 * 2 / 5 / 1e9  # 5 int-ops per cell, 128 lanes/clk/SM, two cells per s16x2 op
+    g = line["sw_gcups"]
+    line["roofline"] = {"kernel": "sw_rerank_kernel (dominant: %.0f%% of the step)" % (100 * sw_ms / (sw_ms + search_ms)), "bound": "int-alu",
+                        "achieved": g, "peak": int_peak, "unit": "GCUPS", "frac": g / int_peak, "traffic": None,
+                        "peak_source": "SURVEY §8d integer roofline at clocks.max.sm (no tensor/HBM bound applies); see DESIGN.md for the measured per-instruction issue rates",
+                        "cells_per_launch": cells, "ms_per_step": sw_ms}
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    a = parse()
+    sys.exit(run_reference(a) if a.impl == "reference" else run_ours(a))

@@ -32,7 +32,8 @@ class SearchStats(C.Structure):
 
 EXPORTS = ["drm_last_error", "drm_device_count", "drm_version", "drm_index_open", "drm_index_close", "drm_index_info",
            "drm_search", "drm_search_device", "drm_ref_open_genome", "drm_ref_open_windows", "drm_ref_close",
-           "drm_sw_pairs", "drm_sw_rerank", "drm_sw_rerank_device", "drm_merge_topk_device", "drm_build_index"]
+           "drm_sw_pairs", "drm_sw_rerank", "drm_sw_rerank_device", "drm_merge_topk_device", "drm_build_index",
+           "drm_search_rerank"]
 
 
 def lib_path() -> str:
@@ -65,6 +66,8 @@ def lib():
         L.drm_sw_rerank_device.argtypes = [vp, i32, i32, vp, i64, i64, vp, vp, i32, i64, i64, i64, vp, vp, vp, vp, vp, vp]
         L.drm_merge_topk_device.argtypes = [i32, vp, vp, i32, i64, i32, vp, vp, vp]
         L.drm_build_index.argtypes = [vp, i64, i32, vp, i64, i32, i32, i32, i32, i32, C.c_uint32, C.c_char_p]
+        L.drm_search_rerank.argtypes = [vp, vp, i32, vp, i64, i32, i32, i32, vp, vp, i64, i64, i64, vp, vp, vp, vp,
+                                        C.POINTER(SearchStats), vp]
         _lib = L
     return _lib
 
@@ -234,6 +237,26 @@ def sw_reranker(cand_seqs, cand_ids, query_seq, k):
     finally:
         ref.close()
     return scores[0], np.asarray(cand_ids, dtype=np.uint64)[idx[0].astype(np.int64)]
+
+
+def search_rerank(index: Index, ref: Reference, mode, q, q_flat_ptr, q_off, stride, k, k_clusters, k_search, ef,
+                  D=None, I=None, sw_scores=None, sw_ids=None):
+    """The pipeline's search + SW-rerank stage in one C-ABI call on HOST buffers (src/main.cpp:270-354).
+    q: (n, d) float32 ndarray; q_flat_ptr: address (or bytes) of the concatenated read sequences; q_off: int64
+    ndarray (n+1).  Output arrays may be preallocated (e.g. pinned) ndarrays; missing ones are created.
+    Returns (D, I, sw_scores, sw_ids, stats dict, [device_span_ms, wall_ms])."""
+    n, d = q.shape
+    D = np.empty((n, k_search), np.float32) if D is None else D
+    I = np.empty((n, k_search), np.int64) if I is None else I
+    sw_scores = np.empty((n, k), np.int32) if sw_scores is None else sw_scores
+    sw_ids = np.empty((n, k), np.uint64) if sw_ids is None else sw_ids
+    st = SearchStats()
+    tm = np.zeros(2, dtype=np.float64)
+    qf = q_flat_ptr if isinstance(q_flat_ptr, int) else C.cast(C.c_char_p(q_flat_ptr), C.c_void_p).value
+    _check(lib().drm_search_rerank(index._h, ref._h, mode, q.ctypes.data, n, d, k_search, ef, qf, q_off.ctypes.data, stride, k,
+                                   k_clusters, D.ctypes.data, I.ctypes.data, sw_scores.ctypes.data, sw_ids.ctypes.data,
+                                   C.byref(st), tm.ctypes.data))
+    return D, I, sw_scores, sw_ids, {f: getattr(st, f) for f, _ in SearchStats._fields_}, tm
 
 
 def merge_topk_device(device, D_all_ptr, I_all_ptr, n_shards, n, k, D_out_ptr, I_out_ptr, stream=0):

@@ -5,6 +5,7 @@
 
 #include <algorithm>
 #include <cstring>
+#include <chrono>
 #include <thread>
 
 struct drm_index {
@@ -327,6 +328,115 @@ int drm_sw_rerank(drm_ref *r, int mode, const int64_t *neighbors, int64_t n, int
         if (rcs[(size_t)g] != DRM_OK) return fail(rcs[(size_t)g], errs[(size_t)g]);
         min_c = std::min(min_c, mins[(size_t)g]);
         if (device_ms) *device_ms = std::max(*device_ms, ms[(size_t)g]);
+    }
+    if (k > 0 && min_c < k)
+        return fail(DRM_ENOTENOUGH, "Not enough candidates (" + std::to_string(min_c) + " < " + std::to_string(k) + ")");
+    return DRM_OK;
+}
+
+int drm_search_rerank(drm_index *ix, drm_ref *ref, int mode, const float *q, int64_t n, int d, int k_search, int ef,
+                      const char *q_flat, const int64_t *q_off, int64_t stride, int64_t k, int64_t k_clusters, float *D,
+                      int64_t *I, int32_t *sw_scores, uint64_t *sw_ids, drm_search_stats *stats, double *timing_ms)
+{
+    if (!ix || !ref) return fail(DRM_EINVAL, "null handle");
+    if (n <= 0 || !q) return fail(DRM_EEMPTY, "Query data is empty");
+    if (!q_flat || !q_off) return fail(DRM_EINVAL, "query sequences are required for the SW rerank");
+    if (d != ix->rep[0].d) return fail(DRM_EINVAL, "query dimension does not match index dimension");
+    if (ix->rep.size() != ref->rep.size()) return fail(DRM_EINVAL, "index and reference must be opened on the same devices");
+    const int R = (int)ix->rep.size();
+    constexpr int64_t CH = 32768;
+    std::vector<int> rcs((size_t)R, DRM_OK), mins((size_t)R, 0x7fffffff);
+    std::vector<std::string> errs((size_t)R);
+    std::vector<drm_search_stats> st((size_t)R);
+    std::vector<double> span((size_t)R, 0.0);
+    auto t_begin = std::chrono::steady_clock::now();
+    auto work = [&](int g) {
+        const int64_t r0 = n * g / R, r1 = n * (g + 1) / R;
+        memset(&st[(size_t)g], 0, sizeof(drm_search_stats));
+        if (r1 <= r0) return;
+        auto body = [&]() -> int {
+            const DeviceIndex &dx = ix->rep[(size_t)g];
+            const DeviceRef &dr = ref->rep[(size_t)g];
+            if (dx.device != dr.device) return fail(DRM_EINVAL, "index and reference replicas are on different devices");
+            DRM_CUDA_TRY(cudaSetDevice(dx.device));
+            int64_t max_qbytes = 0;
+            int max_qlen = 0;
+            for (int64_t c0 = r0; c0 < r1; c0 += CH) {
+                int64_t c1 = std::min(r1, c0 + CH);
+                max_qbytes = std::max(max_qbytes, q_off[c1] - q_off[c0]);
+            }
+            for (int64_t i = r0; i < r1; ++i) max_qlen = std::max<int64_t>(max_qlen, q_off[i + 1] - q_off[i]);
+            struct Slot { cudaStream_t s = nullptr; DevBuf q, D, I, qs, qo, sc, id; std::vector<int64_t> off; } slot[2];
+            DevBuf cnt, dmin;
+            int rc;
+            if ((rc = cnt.alloc(4 * sizeof(int64_t))) || (rc = dmin.alloc(4))) return rc;
+            for (auto &s : slot) {
+                DRM_CUDA_TRY(cudaStreamCreateWithFlags(&s.s, cudaStreamNonBlocking));
+                if ((rc = s.q.alloc((size_t)CH * d * 4)) || (rc = s.D.alloc((size_t)CH * k_search * 4)) || (rc = s.I.alloc((size_t)CH * k_search * 8)) ||
+                    (rc = s.qs.alloc((size_t)max_qbytes)) || (rc = s.qo.alloc((size_t)(CH + 1) * 8)) ||
+                    (rc = s.sc.alloc((size_t)CH * k * 4)) || (rc = s.id.alloc((size_t)CH * k * 8))) return rc;
+                s.off.resize((size_t)CH + 1);
+            }
+            int big = 0x7fffffff;
+            DRM_CUDA_TRY(cudaMemset(cnt.p, 0, 4 * sizeof(int64_t)));
+            DRM_CUDA_TRY(cudaMemcpy(dmin.p, &big, 4, cudaMemcpyHostToDevice));
+            Timer span_t;
+            span_t.start(slot[0].s);
+            int which = 0;
+            for (int64_t c0 = r0; c0 < r1; c0 += CH, which ^= 1) {
+                Slot &s = slot[which];
+                const int64_t m = std::min(r1, c0 + CH) - c0;
+                DRM_CUDA_TRY(cudaStreamSynchronize(s.s));  // the slot's previous chunk (and its host offsets) are done
+                const int64_t qb = q_off[c0];
+                for (int64_t i = 0; i <= m; ++i) s.off[(size_t)i] = q_off[c0 + i] - qb;
+                cudaMemcpyAsync(s.q.p, q + c0 * d, (size_t)m * d * 4, cudaMemcpyHostToDevice, s.s);
+                cudaMemcpyAsync(s.qs.p, q_flat + qb, (size_t)(q_off[c0 + m] - qb), cudaMemcpyHostToDevice, s.s);
+                cudaMemcpyAsync(s.qo.p, s.off.data(), (size_t)(m + 1) * 8, cudaMemcpyHostToDevice, s.s);
+                rc = launch_search(dx, s.q.as<float>(), m, k_search, ef, s.D.as<float>(), s.I.as<int64_t>(), cnt.as<int64_t>(), s.s);
+                if (rc != DRM_OK) return rc;
+                RerankArgs a{mode, s.I.as<int64_t>(), m, k_search, s.qs.as<char>(), s.qo.as<int64_t>(), max_qlen, stride, k, k_clusters,
+                             s.sc.as<int32_t>(), s.id.as<uint64_t>(), nullptr, dmin.as<int32_t>(), nullptr};
+                rc = launch_rerank(dr, a, s.s);
+                if (rc != DRM_OK) return rc;
+                if (D) cudaMemcpyAsync(D + c0 * k_search, s.D.p, (size_t)m * k_search * 4, cudaMemcpyDeviceToHost, s.s);
+                if (I) cudaMemcpyAsync(I + c0 * k_search, s.I.p, (size_t)m * k_search * 8, cudaMemcpyDeviceToHost, s.s);
+                if (sw_scores) cudaMemcpyAsync(sw_scores + c0 * k, s.sc.p, (size_t)m * k * 4, cudaMemcpyDeviceToHost, s.s);
+                if (sw_ids) cudaMemcpyAsync(sw_ids + c0 * k, s.id.p, (size_t)m * k * 8, cudaMemcpyDeviceToHost, s.s);
+            }
+            cudaError_t e = cudaStreamSynchronize(slot[0].s);
+            if (e == cudaSuccess) e = cudaStreamSynchronize(slot[1].s);
+            span_t.stop(slot[0].s);
+            if (e != cudaSuccess) return fail(DRM_ECUDA, std::string("search_rerank: ") + cudaGetErrorString(e));
+            span[(size_t)g] = span_t.ms();
+            int64_t c[4];
+            DRM_CUDA_TRY(cudaMemcpy(c, cnt.p, sizeof c, cudaMemcpyDeviceToHost));
+            DRM_CUDA_TRY(cudaMemcpy(&mins[(size_t)g], dmin.p, 4, cudaMemcpyDeviceToHost));
+            st[(size_t)g].nhops0 = c[0]; st[(size_t)g].nhops_up = c[1]; st[(size_t)g].ndis_eval = c[2];
+            for (auto &s : slot) cudaStreamDestroy(s.s);
+            return DRM_OK;
+        };
+        rcs[(size_t)g] = body();
+        if (rcs[(size_t)g] != DRM_OK) errs[(size_t)g] = drm::last_error_string();
+    };
+    if (R == 1) work(0);
+    else {
+        std::vector<std::thread> th;
+        for (int g = 0; g < R; ++g) th.emplace_back(work, g);
+        for (auto &t : th) t.join();
+    }
+    int min_c = 0x7fffffff;
+    if (stats) memset(stats, 0, sizeof *stats);
+    double dev_span = 0;
+    for (int g = 0; g < R; ++g) {
+        if (rcs[(size_t)g] != DRM_OK) return fail(rcs[(size_t)g], errs[(size_t)g]);
+        min_c = std::min(min_c, mins[(size_t)g]);
+        dev_span = std::max(dev_span, span[(size_t)g]);
+        if (stats) { stats->nhops0 += st[(size_t)g].nhops0; stats->nhops_up += st[(size_t)g].nhops_up; stats->ndis_eval += st[(size_t)g].ndis_eval; }
+    }
+    if (stats) stats->device_ms = dev_span;
+    if (timing_ms) {
+        timing_ms[0] = dev_span;
+        timing_ms[1] = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_begin).count();
     }
     if (k > 0 && min_c < k)
         return fail(DRM_ENOTENOUGH, "Not enough candidates (" + std::to_string(min_c) + " < " + std::to_string(k) + ")");

@@ -19,6 +19,7 @@
 // distances are bit-identical to the oracle's.
 #include "common.h"
 
+#include <atomic>
 #include <cfloat>
 
 namespace drm {
@@ -331,7 +332,9 @@ int launch_t(const SearchParams &p, size_t smem, int device, cudaStream_t stream
 }  // namespace
 
 // Scratch for the work counter: one unsigned per device, allocated lazily.
+// Work counters: a ring of 1024 slots per device so that launches in flight on different streams never share one.
 static unsigned *g_work_counter[64] = {nullptr};
+static std::atomic<unsigned> g_work_slot[64];
 
 int launch_search(const DeviceIndex &dx, const float *q_dev, int64_t n, int k, int ef, float *D_dev, int64_t *I_dev,
                   int64_t *counters_dev, cudaStream_t stream)
@@ -346,8 +349,9 @@ int launch_search(const DeviceIndex &dx, const float *q_dev, int64_t n, int k, i
     const int cap_alloc = (cap + 31) / 32 * 32;
     if (cap > 2048) return fail(DRM_EUNSUPPORTED, "max(ef, k) above 2048 is not supported");
     if (dx.device < 0 || dx.device >= 64) return fail(DRM_EINVAL, "bad device ordinal");
-    if (!g_work_counter[dx.device]) DRM_CUDA_TRY(cudaMalloc(&g_work_counter[dx.device], 256));
-    DRM_CUDA_TRY(cudaMemsetAsync(g_work_counter[dx.device], 0, sizeof(unsigned), stream));
+    if (!g_work_counter[dx.device]) DRM_CUDA_TRY(cudaMalloc(&g_work_counter[dx.device], 1024 * sizeof(unsigned)));
+    unsigned *work = g_work_counter[dx.device] + (g_work_slot[dx.device].fetch_add(1) & 1023u);
+    DRM_CUDA_TRY(cudaMemsetAsync(work, 0, sizeof(unsigned), stream));
 
     SearchParams p{};
     p.q = q_dev; p.n = n; p.d = dx.d; p.M = dx.M; p.dsub = dx.dsub;
@@ -357,7 +361,7 @@ int launch_search(const DeviceIndex &dx, const float *q_dev, int64_t n, int k, i
     p.k = k; p.ef = ef; p.cap = cap; p.cap_alloc = cap_alloc;
     p.D = D_dev; p.I = reinterpret_cast<long long *>(I_dev);
     p.counters = reinterpret_cast<u64 *>(counters_dev);
-    p.next_query = g_work_counter[dx.device];
+    p.next_query = work;
     for (int i = 0; i < 64; ++i) p.entry_code[i] = dx.entry_code[i];
     size_t smem = (size_t)WARPS_PER_CTA * ((size_t)dx.M * 256 * sizeof(float) + (size_t)cap_alloc * sizeof(u64));
     const bool wide = dx.W0 > 32;

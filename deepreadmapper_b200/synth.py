@@ -71,6 +71,34 @@ def embed_windows(genome: bytes, ref_len: int = 150, stride: int = 1, chunk: int
     return out
 
 
+def embed_windows_torch(genome: bytes, device, ref_len: int = 150, stride: int = 1, chunk: int = 1 << 20) -> np.ndarray:
+    """Same as embed_windows with the prefix sums on a torch device (data generation for bench.py; equal to the
+    numpy version up to float32 rounding of the float64 sums)."""
+    import torch
+    Pt = torch.from_numpy(projection().T.astype(np.float64)).to(device)
+    g = _codes(np.frombuffer(genome, dtype=np.uint8))
+    L = len(g)
+    n_pos = (L - ref_len) // stride + 1 if L >= ref_len else 0
+    out = np.empty((2 * n_pos, DIM), dtype=np.float32)
+    K = torch.from_numpy(_kmer_codes(g).astype(np.int64)).to(device)
+    rck = torch.from_numpy(_RC_KMER.astype(np.int64)).to(device)
+    for w0 in range(0, n_pos, chunk):
+        w1 = min(n_pos, w0 + chunk)
+        b0, b1 = w0 * stride, (w1 - 1) * stride + ref_len
+        kk = K[b0:b1 - 3]
+        zero = torch.zeros((1, DIM), dtype=torch.float64, device=device)
+        cf = torch.cat([zero, torch.cumsum(Pt[kk], dim=0)])
+        cr = torch.cat([zero, torch.cumsum(Pt[rck[kk]], dim=0)])
+        s = torch.arange(w0, w1, device=device) * stride - b0
+        t = s + (ref_len - EMB_BASES)
+        blk = torch.empty((2 * (w1 - w0), DIM), dtype=torch.float32, device=device)
+        blk[0::2] = (cf[s + N_KMERS] - cf[s]).float()
+        blk[1::2] = (cr[t + N_KMERS] - cr[t]).float()
+        out[2 * w0:2 * w1] = blk.cpu().numpy()
+        del cf, cr, blk
+    return out
+
+
 def embed_reads(reads: np.ndarray, chunk: int = 1 << 16, proj=None) -> np.ndarray:
     """reads: (n, L) uint8 ASCII, L >= 122."""
     P = projection() if proj is None else proj
@@ -80,8 +108,8 @@ def embed_reads(reads: np.ndarray, chunk: int = 1 << 16, proj=None) -> np.ndarra
         c = _codes(reads[i0:i0 + chunk, :EMB_BASES])
         kk = _kmer_codes(c)  # m x 119
         m = kk.shape[0]
-        cnt = np.zeros((m, 256), dtype=np.float32)
-        np.add.at(cnt, (np.repeat(np.arange(m), kk.shape[1]), kk.reshape(-1)), 1.0)
+        flat = (np.arange(m, dtype=np.int64)[:, None] * 256 + kk).reshape(-1)
+        cnt = np.bincount(flat, minlength=m * 256).reshape(m, 256).astype(np.float32)
         out[i0:i0 + m] = cnt @ P.T
     return out
 
