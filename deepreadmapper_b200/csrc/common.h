@@ -65,6 +65,7 @@ struct DeviceIndex {
     int64_t entry_row = -1;    // upper row of the entry point at max_level; -1 when max_level == 0
     uint8_t entry_code[64] = {0};
     float *centroids = nullptr;
+    float *centroids_t = nullptr;  // transposed copy [M][dsub/4][ksub][4] for coalesced LUT builds (dsub % 4 == 0)
     uint8_t *rows0 = nullptr;
     uint8_t *up = nullptr;
     int64_t n_up_rows = 0;

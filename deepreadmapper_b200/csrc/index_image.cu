@@ -80,8 +80,8 @@ inline int round16(int x) { return (x + 15) / 16 * 16; }
 void free_device_index(DeviceIndex &dx)
 {
     if (dx.device >= 0) cudaSetDevice(dx.device);
-    cudaFree(dx.centroids); cudaFree(dx.rows0); cudaFree(dx.up); cudaFree(dx.counters);
-    dx.centroids = nullptr; dx.rows0 = nullptr; dx.up = nullptr; dx.counters = nullptr;
+    cudaFree(dx.centroids); cudaFree(dx.centroids_t); cudaFree(dx.rows0); cudaFree(dx.up); cudaFree(dx.counters);
+    dx.centroids = nullptr; dx.centroids_t = nullptr; dx.rows0 = nullptr; dx.up = nullptr; dx.counters = nullptr;
 }
 
 int build_device_index(const HostIndex &h, int device, DeviceIndex &dx)
@@ -134,6 +134,15 @@ int build_device_index(const HostIndex &h, int device, DeviceIndex &dx)
 #define STEP(x) do { rc = (x); if (rc != DRM_OK) { cleanup(); free_device_index(dx); return rc; } } while (0)
 #define CU(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) { cleanup(); free_device_index(dx); return fail(DRM_ECUDA, std::string(#x) + ": " + cudaGetErrorString(e_)); } } while (0)
     STEP(upload(&dx.centroids, h.centroids.data(), h.centroids.size() * sizeof(float)));
+    if (h.dsub % 4 == 0) {  // [m][j][t] -> [m][t/4][j][t%4]
+        std::vector<float> ct(h.centroids.size());
+        const size_t q4 = h.dsub / 4;
+        for (size_t m = 0; m < h.M; ++m)
+            for (size_t j = 0; j < h.ksub; ++j)
+                for (size_t t = 0; t < h.dsub; ++t)
+                    ct[((m * q4 + t / 4) * h.ksub + j) * 4 + t % 4] = h.centroids[(m * h.ksub + j) * h.dsub + t];
+        STEP(upload(&dx.centroids_t, ct.data(), ct.size() * sizeof(float)));
+    }
     STEP(upload(&d_nb, h.neighbors.data(), h.neighbors.size() * sizeof(int32_t)));
     STEP(upload(&d_off, h.offsets.data(), h.offsets.size() * sizeof(uint64_t)));
     STEP(upload(&d_codes, h.codes.data(), h.codes.size()));

@@ -21,6 +21,8 @@
 
 #include <atomic>
 #include <cfloat>
+#include <cstdlib>
+#include <cstring>
 
 namespace drm {
 
@@ -35,6 +37,7 @@ struct SearchParams {
     long long n;
     int d, M, dsub;
     const float *centroids;
+    const float4 *centroids_t;  // [M][dsub/4][256] float4, nullptr when dsub is not a multiple of 4
     const uint8_t *rows0;
     const uint8_t *up;
     int row0_bytes, rowu_bytes, W0, Wu, c0_off, cu_off;
@@ -312,6 +315,221 @@ __global__ void __launch_bounds__(WARPS_PER_CTA * 32) hnswpq_search_kernel(const
     }
 }
 
+// ---------------------------------------------------------------------------------------------
+// Register-pool kernel: the same algorithm with the sorted pool held in REGISTERS, NS keys per lane
+// (pool position i lives in lane i / NS, slot i % NS; cap <= 32 * NS).  Inserting a key is a rank
+// computation (per-lane compares + one REDUX add) and a one-position shift (selects + one shuffle for the
+// lane boundary) - no shared-memory traffic, no loops over the pool, no __syncwarp.  It also reads the
+// row of the likeliest next vertex (the first unexpanded pool entry) before it processes the current row, so the DRAM
+// latency of the next hop overlaps the ADC evaluations and insertions of this one; when an insertion
+// overtakes that entry the row is simply fetched again later (by then it is an L2 hit).
+// Preconditions (launch_search falls back to the shared-memory kernel otherwise): W0 <= 32, k <= ef <= 256.
+constexpr u64 POOL_INF = ~0ull;
+
+template <int NS> __device__ __forceinline__ bool pool_first_unexpanded(const u64 (&k)[NS], int lane, int &L, u64 &key)
+{
+    u64 mine = POOL_INF;
+#pragma unroll
+    for (int s = NS - 1; s >= 0; --s)
+        if (!(k[s] & 1ull)) mine = k[s];
+    const unsigned bal = __ballot_sync(FULL, !(mine & 1ull));
+    if (!bal) return false;
+    L = __ffs(bal) - 1;
+    key = __shfl_sync(FULL, mine, L);
+    return true;
+}
+
+__device__ __forceinline__ void build_lut_t(float *T, const float *__restrict__ x, const float4 *__restrict__ cent_t, int M, int dsub, int lane)
+{
+    const int q4 = dsub >> 2;
+    for (int m = 0; m < M; ++m) {
+        const float *xm = x + m * dsub;
+        for (int j = lane; j < 256; j += 32) {
+            float acc = 0.f;
+            for (int t4 = 0; t4 < q4; ++t4) {
+                const float4 cv = __ldg(cent_t + ((size_t)(m * q4 + t4) * 256 + j));
+                const float4 xv = __ldg(reinterpret_cast<const float4 *>(xm) + t4);
+                float e0 = __fsub_rn(xv.x, cv.x); acc = __fmaf_rn(e0, e0, acc);
+                float e1 = __fsub_rn(xv.y, cv.y); acc = __fmaf_rn(e1, e1, acc);
+                float e2 = __fsub_rn(xv.z, cv.z); acc = __fmaf_rn(e2, e2, acc);
+                float e3 = __fsub_rn(xv.w, cv.w); acc = __fmaf_rn(e3, e3, acc);
+            }
+            T[m * 256 + j] = acc;
+        }
+    }
+}
+
+template <int CS, int NS>
+__global__ void __launch_bounds__(WARPS_PER_CTA * 32) hnswpq_search_reg_kernel(const SearchParams p)
+{
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    float *T = reinterpret_cast<float *>(smem_raw) + (size_t)warp * p.M * 256;
+    const int cap = p.cap;
+    const int base = lane * NS;
+    const int max_lane = (cap - 1) / NS, max_slot = (cap - 1) % NS;
+
+    for (;;) {
+        unsigned qi = 0;
+        if (lane == 0) qi = atomicAdd(p.next_query, 1u);
+        qi = __shfl_sync(FULL, qi, 0);
+        if ((long long)qi >= p.n) break;
+
+        __syncwarp();
+        if (p.centroids_t) build_lut_t(T, p.q + (size_t)qi * p.d, p.centroids_t, p.M, p.dsub, lane);
+        else build_lut(T, p.q + (size_t)qi * p.d, p.centroids, p.M, p.dsub, lane);
+        __syncwarp();
+
+        unsigned nhops0 = 0, nhops_up = 0, ndis = 0;
+
+        // ---------------- greedy descent, levels max_level .. 1 (FAISS greedy_update_nearest)
+        float d_near = adc_bytes<CS>(T, p.entry_code);
+        long long vertex = p.entry_vertex;
+        if (p.max_level >= 1) {
+            long long r = p.entry_row;
+            for (int level = p.max_level; level >= 1; --level) {
+                for (;;) {
+                    const uint8_t *row = p.up + (size_t)r * p.rowu_bytes;
+                    int nr = -1;
+                    float dj = __uint_as_float(0x7f800000u);
+                    if (lane < p.Wu) nr = __ldg(reinterpret_cast<const int *>(row + 16) + lane);
+                    unsigned neg = __ballot_sync(FULL, lane < p.Wu && nr < 0);
+                    int first_neg = neg ? (__ffs(neg) - 1) : p.Wu;
+                    if (lane < first_neg) dj = adc(T, load_code<CS>(row + p.cu_off + CS * lane));
+                    u64 best = warp_min_u64(((u64)__float_as_uint(dj) << 32) | (unsigned)lane);
+                    float dmin = __uint_as_float((unsigned)(best >> 32));
+                    ++nhops_up;
+                    if (dmin < d_near) {
+                        d_near = dmin;
+                        r = __shfl_sync(FULL, nr, (int)(best & 31u));
+                    } else break;
+                }
+                if (level > 1) r -= 1;
+            }
+            vertex = __ldg(reinterpret_cast<const int *>(p.up + (size_t)r * p.rowu_bytes));
+        }
+
+        // ---------------- level 0
+        u64 k[NS];
+#pragma unroll
+        for (int s = 0; s < NS; ++s) k[s] = POOL_INF;
+        if (lane == 0) k[0] = make_key(d_near, (int)vertex);
+        u64 maxkey = POOL_INF & ~1ull;
+        unsigned spec_v = 0xffffffffu;
+        int nid_s = -1;
+        Code<CS> code_s;
+        code_s.v = {};
+        for (;;) {
+            int L; u64 k0;
+            if (!pool_first_unexpanded<NS>(k, lane, L, k0)) break;
+            const unsigned v0 = (unsigned)(k0 & 0xffffffffu) >> 1;
+            {   // mark it expanded
+                bool done = lane != L;
+#pragma unroll
+                for (int s = 0; s < NS; ++s) {
+                    const bool hit = !done && !(k[s] & 1ull);
+                    if (hit) k[s] |= 1ull;
+                    done = done || hit;
+                }
+            }
+            int nid; Code<CS> code;
+            if (v0 == spec_v) { nid = nid_s; code = code_s; }
+            else {
+                const uint8_t *row = p.rows0 + (size_t)v0 * p.row0_bytes;
+                nid = lane < p.W0 ? __ldg(reinterpret_cast<const int *>(row) + lane) : -1;
+                code.v = {};
+                if (lane < p.W0) code = load_code<CS>(row + p.c0_off + CS * lane);
+            }
+            {   // read ahead: the row of the next entry in line
+                int L2; u64 k2;
+                if (pool_first_unexpanded<NS>(k, lane, L2, k2)) {
+                    spec_v = (unsigned)(k2 & 0xffffffffu) >> 1;
+                    const uint8_t *nrow = p.rows0 + (size_t)spec_v * p.row0_bytes;
+                    nid_s = lane < p.W0 ? __ldg(reinterpret_cast<const int *>(nrow) + lane) : -1;
+                    if (lane < p.W0) code_s = load_code<CS>(nrow + p.c0_off + CS * lane);
+                } else spec_v = 0xffffffffu;
+            }
+            ++nhops0;
+
+            const unsigned neg = __ballot_sync(FULL, nid < 0);
+            const int first_neg = neg ? (__ffs(neg) - 1) : 32;
+            const bool valid = lane < first_neg;
+            ndis += (unsigned)first_neg;
+            u64 key = 0;
+            if (valid) key = make_key(adc(T, code), nid);
+            unsigned mask = __ballot_sync(FULL, valid && key < maxkey);
+            while (mask) {
+                const int src = __ffs(mask) - 1;
+                mask &= mask - 1;
+                const u64 kin = __shfl_sync(FULL, key, src);
+                if (kin >= maxkey) continue;
+                int cnt = 0;
+                bool dup = false;
+#pragma unroll
+                for (int s = 0; s < NS; ++s) {
+                    const u64 ks = k[s] & ~1ull;
+                    cnt += ks < kin;
+                    dup = dup || ks == kin;
+                }
+                if (__any_sync(FULL, dup)) continue;  // already in the pool (or the same id twice in one row)
+                const int pos = (int)__reduce_add_sync(FULL, (unsigned)cnt);
+                const u64 prevlast = __shfl_up_sync(FULL, k[NS - 1], 1);
+#pragma unroll
+                for (int s = NS - 1; s >= 1; --s)
+                    if (base + s > pos) k[s] = k[s - 1];
+                if (base > pos) k[0] = prevlast;
+#pragma unroll
+                for (int s = 0; s < NS; ++s) {
+                    if (base + s == pos) k[s] = kin;
+                    if (base + s >= cap) k[s] = POOL_INF;
+                }
+                u64 lastk = k[0];
+#pragma unroll
+                for (int s = 1; s < NS; ++s)
+                    if (s == max_slot) lastk = k[s];
+                maxkey = __shfl_sync(FULL, lastk, max_lane) & ~1ull;
+            }
+        }
+
+        // ---------------- results: the first k pool entries, ascending (distance, id)
+        float *Dq = p.D + (size_t)qi * p.k;
+        long long *Iq = p.I + (size_t)qi * p.k;
+#pragma unroll
+        for (int s = 0; s < NS; ++s) {
+            const int i = base + s;
+            if (i < p.k) {
+                const u64 kk = k[s];
+                const bool filled = kk != POOL_INF;
+                Dq[i] = filled ? __uint_as_float((unsigned)(kk >> 32)) : FLT_MAX;
+                Iq[i] = filled ? (long long)((unsigned)(kk & 0xffffffffu) >> 1) : -1ll;
+            }
+        }
+        // positions beyond the register pool (k > 32 * NS cannot happen: k <= cap <= 32 * NS)
+        if (p.counters && lane == 0) {
+            atomicAdd(p.counters + 0, (u64)nhops0);
+            atomicAdd(p.counters + 1, (u64)nhops_up);
+            atomicAdd(p.counters + 2, (u64)ndis);
+        }
+    }
+}
+
+template <int CS, int NS>
+int launch_reg_t(const SearchParams &p, size_t smem, int device, cudaStream_t stream)
+{
+    auto kern = hnswpq_search_reg_kernel<CS, NS>;
+    DRM_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int per_sm = 0, sms = 0;
+    DRM_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, WARPS_PER_CTA * 32, smem));
+    DRM_CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device));
+    if (per_sm < 1) return fail(DRM_EUNSUPPORTED, "search kernel does not fit on an SM with these parameters");
+    long long want = (p.n + WARPS_PER_CTA - 1) / WARPS_PER_CTA;
+    long long grid = (long long)per_sm * sms;
+    if (want < grid) grid = want;
+    kern<<<(unsigned)grid, WARPS_PER_CTA * 32, smem, stream>>>(p);
+    DRM_CUDA_TRY(cudaGetLastError());
+    return DRM_OK;
+}
+
 template <int CS, int NPL>
 int launch_t(const SearchParams &p, size_t smem, int device, cudaStream_t stream)
 {
@@ -355,7 +573,7 @@ int launch_search(const DeviceIndex &dx, const float *q_dev, int64_t n, int k, i
 
     SearchParams p{};
     p.q = q_dev; p.n = n; p.d = dx.d; p.M = dx.M; p.dsub = dx.dsub;
-    p.centroids = dx.centroids; p.rows0 = dx.rows0; p.up = dx.up;
+    p.centroids = dx.centroids; p.centroids_t = reinterpret_cast<const float4 *>(dx.centroids_t); p.rows0 = dx.rows0; p.up = dx.up;
     p.row0_bytes = dx.row0_bytes; p.rowu_bytes = dx.rowu_bytes; p.W0 = dx.W0; p.Wu = dx.Wu; p.c0_off = dx.code0_off; p.cu_off = dx.codeu_off;
     p.entry_vertex = dx.entry_vertex; p.entry_row = dx.entry_row; p.max_level = dx.max_level;
     p.k = k; p.ef = ef; p.cap = cap; p.cap_alloc = cap_alloc;
@@ -363,6 +581,16 @@ int launch_search(const DeviceIndex &dx, const float *q_dev, int64_t n, int k, i
     p.counters = reinterpret_cast<u64 *>(counters_dev);
     p.next_query = work;
     for (int i = 0; i < 64; ++i) p.entry_code[i] = dx.entry_code[i];
+    // Kernel choice: the register-pool kernel when its preconditions hold (DRM_SEARCH_KERNEL=smem forces the other one,
+    // for A/B measurements and the parity tests); both implement the same rule and return identical bits.
+    const char *force = getenv("DRM_SEARCH_KERNEL");
+    const bool want_smem = force && !strcmp(force, "smem");
+    if (!want_smem && dx.W0 <= 32 && k <= ef && cap <= 256) {
+        const size_t smem_r = (size_t)WARPS_PER_CTA * (size_t)dx.M * 256 * sizeof(float);
+        const int ns = cap <= 64 ? 2 : cap <= 128 ? 4 : 8;
+        if (dx.code_size == 8) return ns == 2 ? launch_reg_t<8, 2>(p, smem_r, dx.device, stream) : ns == 4 ? launch_reg_t<8, 4>(p, smem_r, dx.device, stream) : launch_reg_t<8, 8>(p, smem_r, dx.device, stream);
+        return ns == 2 ? launch_reg_t<16, 2>(p, smem_r, dx.device, stream) : ns == 4 ? launch_reg_t<16, 4>(p, smem_r, dx.device, stream) : launch_reg_t<16, 8>(p, smem_r, dx.device, stream);
+    }
     size_t smem = (size_t)WARPS_PER_CTA * ((size_t)dx.M * 256 * sizeof(float) + (size_t)cap_alloc * sizeof(u64));
     const bool wide = dx.W0 > 32;
     if (dx.code_size == 8) return wide ? launch_t<8, 2>(p, smem, dx.device, stream) : launch_t<8, 1>(p, smem, dx.device, stream);

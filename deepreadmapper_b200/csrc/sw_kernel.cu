@@ -21,6 +21,11 @@
 // 256, bytes outside ACGTN in the reference).  Both are CUDA; there is no host path.
 #include "common.h"
 
+#include <cuda_fp16.h>
+
+#include <cstdlib>
+#include <cstring>
+
 namespace drm {
 
 namespace {
@@ -142,7 +147,9 @@ __device__ __forceinline__ unsigned sw_quad(const uint8_t *selrow, int rows, con
     return best;  // per half: max(H) + 1 (or 0)
 }
 
-__global__ void __launch_bounds__(RERANK_THREADS, 2) sw_rerank_kernel(const RerankDev p)
+// list == nullptr: one CTA per read (r = blockIdx.x).  Otherwise the CTAs stride over list[0 .. *list_n): the reads the
+// profile kernel handed back (those containing N).
+__global__ void __launch_bounds__(RERANK_THREADS, 2) sw_rerank_kernel(const RerankDev p, const int *list, const int *list_n)
 {
     __shared__ u64 s_cand[MAXC];
     __shared__ u64 s_first[MAXTAKE];
@@ -152,12 +159,15 @@ __global__ void __launch_bounds__(RERANK_THREADS, 2) sw_rerank_kernel(const Rera
     __shared__ int s_nc, s_hasN;
 
     const int tid = threadIdx.x, lane = tid & 31;
-    const long long r = blockIdx.x;
+    const int n_list = list ? *list_n : 1;
+    for (int li = list ? (int)blockIdx.x : 0; li < n_list; li += list ? (int)gridDim.x : 1) {
+    const long long r = list ? (long long)list[li] : (long long)blockIdx.x;
     const long long qb = p.q_off[r];
     const int lq = (int)(p.q_off[r + 1] - qb);
     const int rows = p.ref_len;
 
     // query profile: byte c of s_Q[j] = 2 when query base j is class c (0..3), s_QN[j] byte 0 = 2 for 'N'
+    __syncthreads();
     if (tid == 0) s_hasN = 0;
     __syncthreads();
     for (int j = tid; j < QCOLS; j += RERANK_THREADS) {
@@ -222,6 +232,261 @@ __global__ void __launch_bounds__(RERANK_THREADS, 2) sw_rerank_kernel(const Rera
         if ((tid >> 5) * 8 < npairs) {
             const uint8_t *selrow = s_sel[pair < npairs ? pair : 0];
             unsigned best = hasN ? sw_quad<true>(selrow, rows, s_Q, s_QN, lane) : sw_quad<false>(selrow, rows, s_Q, s_QN, lane);
+            if ((lane & 3) == 0 && pair < npairs) {
+                int sa = (int)(short)(best & 0xffffu) - 1, sb = (int)(short)(best >> 16) - 1;
+                int ca = c0 + 2 * pair;
+                size_t base = (size_t)r * p.C;
+                p.scr_scores[base + ca] = (short)(sa > 0 ? sa : 0);
+                p.scr_ids[base + ca] = s_cand[ca];
+                if (ca + 1 < nc) {
+                    p.scr_scores[base + ca + 1] = (short)(sb > 0 ? sb : 0);
+                    p.scr_ids[base + ca + 1] = s_cand[ca + 1];
+                }
+            }
+        }
+        __syncthreads();
+    }
+    }  // reads of this CTA
+}
+
+// ---------------------------------------------------------------------------------------------
+// Profile kernel (sw_rerank_profile_kernel): same quad pipeline, but the substitution term comes from a
+// per-read QUERY PROFILE in shared memory instead of a PRMT per cell pair, which moves the lookup off the
+// ALU pipe (PRMT issues at half the VIMNMX rate on sm_100a, tools/ubench_alu.cu) onto the LSU:
+//   tab[ab][g][slot] : uint4 = the four packed terms (0 / 2 per 16-bit half) of query columns
+//                      40*(slot&3) + 4g .. +3 against the window-base pair ab = 5a + b (a, b in A,C,G,T,none)
+// One LDS.128 feeds four cell pairs.  `slot` = lane & 7 replicates the table for the two quads of a
+// quarter-warp, so the eight 16-byte addresses of every LDS.128 wavefront fall in eight different bank
+// groups whatever base pairs the lanes are looking up: conflict-free by construction.
+// Used when neither the read nor (effectively) the windows contain N: a window N can only match a read N.
+constexpr int PCPL = 40;             // query columns per lane (10 groups of 4)
+constexpr int PGROUPS = PCPL / 4;
+constexpr int PQCOLS = 4 * PCPL;     // 160 >= 152
+constexpr int PTAB_ENTRIES = 25 * PGROUPS * 8;
+
+// The recurrence runs on s16x2 integers whose values stay below 2048.  Such an integer k has the same bit pattern as the
+// fp16 number k * 2^-24 (a subnormal below 1024, a normal with ulp 2^-24 above), on which fp16 addition is exact, so
+// every step exists in two interchangeable forms that produce identical bits:
+//     add     x = s + diag      IMAD (fma pipe)              |  HADD2 / HFMA2 (fma pipe)
+//     clamp   h = max(m-1, 0)   VIADDMNMX.S16x2.RELU (alu)   |  HFMA2.RELU(m, 1.0, -2^-24) (fma pipe)
+//     max3    m = max(x,up,left) VIMNMX3.S16x2 (alu) only
+// ALU_EVERY picks the mix so that the alu and fma pipes (each one warp instruction per 2 clocks per SMSP) carry
+// equal shares:  1 = every clamp on the alu pipe (integer form throughout), 0 = every clamp on the fma pipe,
+// n >= 2 = every n-th clamp on the alu pipe, the rest on the fma pipe.
+template <int ALU_EVERY>
+__device__ __forceinline__ unsigned sw_quad_profile(const uint8_t *selrow, int rows, const uint4 *tab, int lane, unsigned one)
+{
+    const int l = lane & 3;
+    const uint4 *tslot = tab + (lane & 7);
+    unsigned H[PCPL];
+#pragma unroll
+    for (int j = 0; j < PCPL; ++j) H[j] = 0;
+    unsigned best = 0, last_out = 0, prev_recv = 0;
+    const unsigned NEG1 = 0xffffffffu;
+    const unsigned H_ONE = 0x3c003c00u, H_NEGULP = 0x80018001u;  // (1.0h, 1.0h), (-2^-24, -2^-24)
+#pragma unroll 2
+    for (int t = 0; t < rows + 3; ++t) {
+        unsigned recv = __shfl_up_sync(FULL, last_out, 1, 4);
+        if (l == 0) recv = 0;
+        const uint4 *prow = tslot + (unsigned)selrow[t - l + 3] * (PGROUPS * 8);
+        unsigned diag = prev_recv, left = recv, mprev = 0;
+#pragma unroll
+        for (int g = 0; g < PGROUPS; ++g) {
+            const uint4 pr = prow[g * 8];
+            const unsigned s4[4] = {pr.x, pr.y, pr.z, pr.w};
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+                const int j = 4 * g + c;
+                const unsigned up = H[j];
+                unsigned x, h;
+                if (ALU_EVERY == 1) x = s4[c] * one + diag;
+                else asm("add.rn.f16x2 %0, %1, %2;" : "=r"(x) : "r"(s4[c]), "r"(diag));
+                const unsigned m = __vimax3_s16x2(x, up, left);
+                const bool on_alu = ALU_EVERY == 1 || (ALU_EVERY >= 2 && (j % ALU_EVERY) == ALU_EVERY - 1);
+                if (on_alu) h = __viaddmax_s16x2_relu(m, NEG1, 0u);
+                else asm("fma.rn.relu.f16x2 %0, %1, %2, %3;" : "=r"(h) : "r"(m), "r"(H_ONE), "r"(H_NEGULP));
+                if (j & 1) best = __vimax3_s16x2(best, m, mprev);
+                mprev = m;
+                diag = up;
+                left = h;
+                H[j] = h;
+            }
+        }
+        prev_recv = recv;
+        last_out = left;
+    }
+    best = __vmaxs2(best, __shfl_xor_sync(FULL, best, 1));
+    best = __vmaxs2(best, __shfl_xor_sync(FULL, best, 2));
+    return best;  // per half: max(H) + 1 (or 0)
+}
+
+// Two window rows per iteration, skewed by one column: cell (r0, k) and cell (r0 + 1, k - 1) do not depend on each
+// other, so every thread carries TWO independent max3 -> clamp chains and the fixed latency of one hides behind the
+// other (the single-row form stalls on its own chain with 4 warps per scheduler: "stall_wait" in
+// profiles/r1_ncu_sw_rerank_profile_kernel_blend4.txt).  Row r0 + 1 reads its `up` values straight from the registers
+// row r0 has just produced, so H[] is still one register per column.  Row r0's clamps go to the fma pipe; row
+// r0 + 1's go to the alu pipe at every AE-th column (AE = 0: never).
+template <int AE>
+__device__ __forceinline__ unsigned sw_quad_profile2(const uint8_t *selrow, int rows, const uint4 *tab, int lane)
+{
+    const int l = lane & 3;
+    const uint4 *tslot = tab + (lane & 7);
+    unsigned H[PCPL];
+#pragma unroll
+    for (int j = 0; j < PCPL; ++j) H[j] = 0;
+    unsigned best = 0, out0 = 0, out1 = 0, prev_recv1 = 0;
+    const unsigned NEG1 = 0xffffffffu;
+    const unsigned H_ONE = 0x3c003c00u, H_NEGULP = 0x80018001u;
+    const int iters = (rows + 1) / 2 + 3;
+#pragma unroll 2
+    for (int u = 0; u < iters; ++u) {
+        unsigned recv0 = __shfl_up_sync(FULL, out0, 1, 4);
+        unsigned recv1 = __shfl_up_sync(FULL, out1, 1, 4);
+        if (l == 0) { recv0 = 0; recv1 = 0; }
+        const unsigned ab2 = *reinterpret_cast<const unsigned short *>(selrow + 2 * (u - l) + 6);
+        const uint4 *p0 = tslot + (ab2 & 0xffu) * (PGROUPS * 8);
+        const uint4 *p1 = tslot + (ab2 >> 8) * (PGROUPS * 8);
+        unsigned diag0 = prev_recv1, left0 = recv0;  // row r0: its diagonal neighbour is row r0 - 1's boundary
+        unsigned diag1 = recv0, left1 = recv1;       // row r0 + 1
+        unsigned h0_last = 0, m0 = 0;
+        uint4 q0 = p0[0], q1 = p1[0];
+#pragma unroll
+        for (int k = 0; k <= PCPL; ++k) {
+            unsigned m1 = 0;
+            if (k >= 1) {  // row r0 + 1, column k - 1 (uses row r0's column k - 1 from the previous stage)
+                const int j = k - 1;
+                const unsigned s1 = (j & 3) == 0 ? q1.x : (j & 3) == 1 ? q1.y : (j & 3) == 2 ? q1.z : q1.w;
+                unsigned x1, h1;
+                asm("add.rn.f16x2 %0, %1, %2;" : "=r"(x1) : "r"(s1), "r"(diag1));
+                const unsigned up1 = h0_last;
+                m1 = __vimax3_s16x2(x1, up1, left1);
+                if (AE >= 1 && (j % AE) == AE - 1) h1 = __viaddmax_s16x2_relu(m1, NEG1, 0u);
+                else asm("fma.rn.relu.f16x2 %0, %1, %2, %3;" : "=r"(h1) : "r"(m1), "r"(H_ONE), "r"(H_NEGULP));
+                diag1 = up1;
+                left1 = h1;
+                H[j] = h1;
+                if ((j & 3) == 3 && j + 1 < PCPL) q1 = p1[((j + 1) >> 2) * 8];
+            }
+            if (k < PCPL) {  // row r0, column k
+                const unsigned s0 = (k & 3) == 0 ? q0.x : (k & 3) == 1 ? q0.y : (k & 3) == 2 ? q0.z : q0.w;
+                unsigned x0, h0;
+                asm("add.rn.f16x2 %0, %1, %2;" : "=r"(x0) : "r"(s0), "r"(diag0));
+                const unsigned up0 = H[k];
+                m0 = __vimax3_s16x2(x0, up0, left0);
+                asm("fma.rn.relu.f16x2 %0, %1, %2, %3;" : "=r"(h0) : "r"(m0), "r"(H_ONE), "r"(H_NEGULP));
+                diag0 = up0;
+                left0 = h0;
+                h0_last = h0;
+                if ((k & 3) == 3 && k + 1 < PCPL) q0 = p0[((k + 1) >> 2) * 8];
+                best = __vimax3_s16x2(best, m0, m1);
+            } else {
+                best = __vmaxs2(best, m1);
+            }
+        }
+        prev_recv1 = recv1;
+        out0 = left0;
+        out1 = left1;
+    }
+    best = __vmaxs2(best, __shfl_xor_sync(FULL, best, 1));
+    best = __vmaxs2(best, __shfl_xor_sync(FULL, best, 2));
+    return best;
+}
+
+// Dynamic shared memory layout (bytes): tab | sel[PAIRS_PER_PASS][selw] | cand[C] | first[take] | count[take+1]
+template <int RPI, int ALU_EVERY>
+__global__ void __launch_bounds__(RERANK_THREADS, 2) sw_rerank_profile_kernel(const RerankDev p, int selw, unsigned one, int *fb_list, int *fb_n)
+{
+    extern __shared__ __align__(16) unsigned char dsm[];
+    uint4 *tab = reinterpret_cast<uint4 *>(dsm);
+    uint8_t *s_sel = dsm + PTAB_ENTRIES * sizeof(uint4);
+    u64 *s_cand = reinterpret_cast<u64 *>(s_sel + (size_t)PAIRS_PER_PASS * selw);
+    u64 *s_first = s_cand + p.C;
+    int *s_count = reinterpret_cast<int *>(s_first + p.take);
+    __shared__ unsigned char s_qcls[PQCOLS];
+    __shared__ int s_nc, s_hasN;
+
+    const int tid = threadIdx.x, lane = tid & 31;
+    const long long r = blockIdx.x;
+    const long long qb = p.q_off[r];
+    const int lq = (int)(p.q_off[r + 1] - qb);
+    const int rows = p.ref_len;
+
+    if (tid == 0) s_hasN = 0;
+    __syncthreads();
+    for (int j = tid; j < PQCOLS; j += RERANK_THREADS) {
+        int c = 5;  // beyond the read, or a byte outside ACGT: matches nothing
+        if (j < lq) {
+            c = base_class((unsigned char)p.q_flat[qb + j]);
+            if (c == 4) s_hasN = 1;
+        }
+        s_qcls[j] = (unsigned char)c;
+    }
+    const long long *nb = p.neighbors + r * p.k_in;
+    for (int i = tid; i < p.take; i += RERANK_THREADS) {
+        u64 first; int count;
+        expand_one(p.rule, (u64)nb[i], first, count);
+        s_first[i] = first;
+        s_count[i] = count;
+    }
+    __syncthreads();
+    if (s_hasN) {  // a read with N: left to the PRMT kernel (second launch over flagged reads)
+        if (tid == 0) fb_list[atomicAdd(fb_n, 1)] = (int)r;
+        return;
+    }
+    if (tid == 0) {
+        int acc = 0;
+        for (int i = 0; i < p.take; ++i) { int c = s_count[i]; s_count[i] = acc; acc += c; }
+        s_count[p.take] = acc;
+        s_nc = acc;
+    }
+    // query profile
+    for (int e = tid; e < PTAB_ENTRIES; e += RERANK_THREADS) {
+        const int slot = e & 7, g = (e >> 3) % PGROUPS, ab = (e >> 3) / PGROUPS;
+        const int a = ab / 5, b = ab % 5, col = PCPL * (slot & 3) + 4 * g;
+        unsigned w[4];
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+            const int q = s_qcls[col + c];
+            w[c] = (q == a ? 2u : 0u) | (q == b ? 0x20000u : 0u);  // a, b == 4 ("none") never equal q in 0..3 or 5
+        }
+        tab[e] = make_uint4(w[0], w[1], w[2], w[3]);
+    }
+    __syncthreads();
+    const int nc = s_nc;
+    for (int i = tid; i < p.take; i += RERANK_THREADS) {
+        int b = s_count[i], e = s_count[i + 1];
+        u64 f = s_first[i];
+        for (int c = b; c < e; ++c) s_cand[c] = f + (u64)(c - b);
+    }
+    if (tid == 0) {
+        if (p.n_cands) p.n_cands[r] = nc;
+        if (p.min_cands) atomicMin(p.min_cands, nc);
+        if (p.cells) atomicAdd(p.cells, (u64)nc * (u64)rows * (u64)lq);
+    }
+    __syncthreads();
+
+    const int pair = tid >> 2;
+    for (int c0 = 0; c0 < nc; c0 += 2 * PAIRS_PER_PASS) {
+        const int npairs = min(PAIRS_PER_PASS, (nc - c0 + 1) / 2);
+        constexpr int PAD = 3 * RPI;             // "none" rows either side: pipeline fill and drain of the quad
+        const int srows = rows + 2 * PAD + RPI;  // (+ RPI: the odd last row of a two-row iteration)
+        for (int e = tid; e < npairs * srows; e += RERANK_THREADS) {
+            int pr = e / srows, i = e % srows - PAD;
+            int ca = c0 + 2 * pr, cb = ca + 1;
+            unsigned v = 24;
+            if (i >= 0 && i < rows) {
+                u64 ida = s_cand[ca];
+                int a = window_base(p, ida, window_valid(p, ida), i);
+                int b = 6;
+                if (cb < nc) { u64 idb = s_cand[cb]; b = window_base(p, idb, window_valid(p, idb), i); }
+                v = (unsigned)(5 * min(a, 4) + min(b, 4));
+            }
+            s_sel[(size_t)pr * selw + i + PAD] = (uint8_t)v;
+        }
+        __syncthreads();
+        if ((tid >> 5) * 8 < npairs) {
+            const uint8_t *selrow = s_sel + (size_t)(pair < npairs ? pair : 0) * selw;
+            unsigned best = RPI == 2 ? sw_quad_profile2<ALU_EVERY>(selrow, rows, tab, lane) : sw_quad_profile<ALU_EVERY>(selrow, rows, tab, lane, one);
             if ((lane & 3) == 0 && pair < npairs) {
                 int sa = (int)(short)(best & 0xffffu) - 1, sb = (int)(short)(best >> 16) - 1;
                 int ca = c0 + 2 * pair;
@@ -475,6 +740,23 @@ int launch_rerank(const DeviceRef &ref, const RerankArgs &a, cudaStream_t stream
     int *n_cands = a.n_cands ? a.n_cands : ncand_tmp;
     const long long gthreads = 148LL * 1024;
     if (!fast) DRM_CUDA_TRY(cudaMallocAsync(&H, (size_t)gthreads * (size_t)(a.max_qlen + 1) * sizeof(int), stream));
+    // Kernel variant: 0 = PRMT lookup; query-profile kernels, one row per iteration: 1 = clamps on the alu
+    // pipe (integer form), 2 = clamps on the fma pipe (fp16 form), 3 / 4 = every 2nd / 4th clamp on the alu pipe; two rows
+    // per iteration: 10 / 11 / 12 / 14 = none / every / every 2nd / every 4th clamp of the second row on the alu pipe.
+    // DRM_SW_KERNEL overrides the default, for A/B measurements and the parity tests.
+    static const struct { const char *name; int v; } kVariants[] = {{"prmt", 0}, {"profile", 1}, {"profile16", 2}, {"blend2", 3},
+        {"blend4", 4}, {"r2a0", 10}, {"r2a1", 11}, {"r2a2", 12}, {"r2a4", 14}};
+    int variant = 3;
+    if (const char *e = getenv("DRM_SW_KERNEL"))
+        for (const auto &kv : kVariants)
+            if (!strcmp(e, kv.name)) variant = kv.v;
+    const int selw = (ref.ref_len + 14 + 3) / 4 * 4;  // rows + fill/drain padding of the two-row form (12) + 2
+    const size_t psmem = (size_t)PTAB_ENTRIES * sizeof(uint4) + (size_t)PAIRS_PER_PASS * selw + (size_t)C * sizeof(u64) +
+                         (size_t)take * sizeof(u64) + (size_t)(take + 1) * sizeof(int) + 16;
+    int *fb = nullptr;  // [0] = count, [1..] = reads handed back by the profile kernel
+    if (fast && variant != 0) {
+        DRM_CUDA_TRY(cudaMallocAsync(&fb, (size_t)(B + 1) * sizeof(int), stream));
+    }
     if (a.k > 0) {
         DRM_CUDA_TRY(cudaMemsetAsync(a.out_scores, 0, (size_t)a.n * a.k * sizeof(int32_t), stream));
         DRM_CUDA_TRY(cudaMemsetAsync(a.out_ids, 0, (size_t)a.n * a.k * sizeof(uint64_t), stream));
@@ -486,9 +768,32 @@ int launch_rerank(const DeviceRef &ref, const RerankArgs &a, cudaStream_t stream
         p.q_off = reinterpret_cast<const long long *>(a.q_off) + b0;
         p.scr_scores = scr_scores; p.scr_ids = scr_ids;
         p.n_cands = n_cands + b0;
-        if (fast) {
+        if (fast && variant != 0) {
             p.ref = ref.data;
-            sw_rerank_kernel<<<(unsigned)nb, RERANK_THREADS, 0, stream>>>(p);
+            DRM_CUDA_TRY(cudaMemsetAsync(fb, 0, sizeof(int), stream));
+#define DRM_PROFILE_LAUNCH(R, A)                                                                                                   \
+    do {                                                                                                                            \
+        DRM_CUDA_TRY(cudaFuncSetAttribute(sw_rerank_profile_kernel<R, A>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)psmem)); \
+        sw_rerank_profile_kernel<R, A><<<(unsigned)nb, RERANK_THREADS, psmem, stream>>>(p, selw, 1u, fb + 1, fb);                   \
+    } while (0)
+            switch (variant) {
+            case 1: DRM_PROFILE_LAUNCH(1, 1); break;
+            case 2: DRM_PROFILE_LAUNCH(1, 0); break;
+            case 3: DRM_PROFILE_LAUNCH(1, 2); break;
+            case 4: DRM_PROFILE_LAUNCH(1, 4); break;
+            case 10: DRM_PROFILE_LAUNCH(2, 0); break;
+            case 11: DRM_PROFILE_LAUNCH(2, 1); break;
+            case 12: DRM_PROFILE_LAUNCH(2, 2); break;
+            default: DRM_PROFILE_LAUNCH(2, 4); break;
+            }
+#undef DRM_PROFILE_LAUNCH
+            DRM_CUDA_TRY(cudaGetLastError());
+            // reads containing N were handed back: the PRMT kernel strides over that list (usually empty)
+            sw_rerank_kernel<<<(unsigned)(nb < 296 ? nb : 296), RERANK_THREADS, 0, stream>>>(p, fb + 1, fb);
+            DRM_CUDA_TRY(cudaGetLastError());
+        } else if (fast) {
+            p.ref = ref.data;
+            sw_rerank_kernel<<<(unsigned)nb, RERANK_THREADS, 0, stream>>>(p, nullptr, nullptr);
             DRM_CUDA_TRY(cudaGetLastError());
         } else {
             expand_kernel<<<(unsigned)((nb + 127) / 128), 128, 0, stream>>>(p);
@@ -507,6 +812,7 @@ int launch_rerank(const DeviceRef &ref, const RerankArgs &a, cudaStream_t stream
     DRM_CUDA_TRY(cudaFreeAsync(scr_ids, stream));
     if (ncand_tmp) DRM_CUDA_TRY(cudaFreeAsync(ncand_tmp, stream));
     if (H) DRM_CUDA_TRY(cudaFreeAsync(H, stream));
+    if (fb) DRM_CUDA_TRY(cudaFreeAsync(fb, stream));
     return DRM_OK;
 }
 

@@ -65,12 +65,22 @@ def test_sw_pairs_random_vs_oracle(drm, ob):
     assert drm.sw_pairs(a, b).tolist() == ob.sw_pairs(a, b).tolist()
 
 
+@pytest.fixture(params=["default", "prmt", "profile", "profile16", "blend2", "blend4", "r2a0", "r2a1", "r2a2", "r2a4"])
+def sw_variant(request, monkeypatch):
+    """Every rerank parity test runs on the three SW kernel variants (DESIGN.md "SW kernels")."""
+    if request.param == "default":
+        monkeypatch.delenv("DRM_SW_KERNEL", raising=False)
+    else:
+        monkeypatch.setenv("DRM_SW_KERNEL", request.param)
+    return request.param
+
+
 def _refs(drm, fixtures):
     return {0: drm.Reference(windows=fixtures["windows"], ref_len=150), 1: drm.Reference(genome=fixtures["genome"], ref_len=150),
             "g0": drm.Reference(genome=fixtures["genome"], ref_len=150)}
 
 
-def test_rerank_goldens(golden, fixtures, drm):
+def test_rerank_goldens(golden, fixtures, drm, sw_variant):
     refs = _refs(drm, fixtures)
     for case in golden["rerank"]:
         nb = np.array(case["neighbors"], dtype=np.int64)
@@ -90,7 +100,7 @@ def test_rerank_goldens(golden, fixtures, drm):
             assert nc.tolist() == case["n_cands"], case["tag"]
 
 
-def test_rerank_random_vs_oracle(fixtures, drm, ob):
+def test_rerank_random_vs_oracle(fixtures, drm, ob, sw_variant):
     """Random neighbour tables, decorated and ragged queries, N-containing queries, both modes, strides 1..16."""
     rng = np.random.default_rng(3)
     refs = _refs(drm, fixtures)
@@ -116,6 +126,32 @@ def test_rerank_random_vs_oracle(fixtures, drm, ob):
             assert s2.tolist() == s1.tolist(), (mode, stride, kc, k)
             assert i2.tolist() == i1.tolist(), (mode, stride, kc, k)
             assert nc2.tolist() == nc1.tolist()
+
+
+def test_rerank_genome_and_reads_with_N(drm, ob, sw_variant):
+    """N in the genome and in some reads: a window N matches only a read N (byte equality, src/utils/metrics.cpp:34);
+    reads with N are handed from the profile kernel back to the PRMT kernel inside one launch sequence."""
+    rng = np.random.default_rng(21)
+    g = bytearray(np.frombuffer(b"ACGT", dtype=np.uint8)[rng.integers(0, 4, 6000)].tobytes())
+    for p in rng.integers(0, len(g) - 8, 40):
+        g[p:p + int(rng.integers(1, 8))] = b"N" * 8
+    g = bytes(g[:6000])
+    reads = []
+    for i in range(64):
+        p = int(rng.integers(0, len(g) - 150))
+        r = bytearray(g[p:p + 150])
+        for q in rng.integers(0, 150, 5):
+            r[q] = b"ACGT"[int(rng.integers(0, 4))]
+        if i % 3 == 0:
+            r = bytearray(bytes(r).replace(b"N", b"A"))
+        reads.append(bytes(r))
+    assert any(b"N" in r for r in reads) and any(b"N" not in r for r in reads)
+    ref = drm.Reference(genome=g, ref_len=150)
+    nb = np.stack([rng.permutation(2 * (len(g) - 149))[:64] for _ in reads]).astype(np.int64)
+    rc, s1, i1, _ = ob.post_process_sw(1, nb, g, len(g), 150, reads, 1, 64, 64)
+    assert rc == 0
+    s2, i2 = ref.rerank(1, nb, reads, 1, 64, 64)
+    assert s2.tolist() == s1.tolist() and i2.tolist() == i1.tolist()
 
 
 def test_rerank_generic_path_long_queries(fixtures, drm, ob):
@@ -166,6 +202,13 @@ def mid_index(tmp_path_factory):
     return p, synth.embed_reads(reads), ids
 
 
+@pytest.fixture(params=["reg", "smem"])
+def search_variant(request, monkeypatch):
+    """Both search kernels (register pool / shared-memory pool) must return the oracle's bits."""
+    monkeypatch.setenv("DRM_SEARCH_KERNEL", request.param)
+    return request.param
+
+
 def _check_search(drm, ob, path, Q, k, ef):
     oix = ob.OracleIndex(path)
     D0, I0, st = oix.search(Q, k, ef, tie_rule=1)
@@ -179,7 +222,7 @@ def _check_search(drm, ob, path, Q, k, ef):
     return oix, D1, I1
 
 
-def test_search_config1_bit_exact(drm, ob, small_index):
+def test_search_config1_bit_exact(drm, ob, small_index, search_variant):
     path, Q = small_index
     oix, D, I = _check_search(drm, ob, path, Q, 128, 128)
     # invariants that do not depend on the oracle's traversal: ascending D, unique ids, D == dis(I)
@@ -191,7 +234,7 @@ def test_search_config1_bit_exact(drm, ob, small_index):
 
 
 @pytest.mark.parametrize("k,ef", [(128, 128), (8, 32), (32, 64), (128, 512), (64, 256), (200, 128), (1, 16)])
-def test_search_ef_k_sweep_bit_exact(drm, ob, mid_index, k, ef):
+def test_search_ef_k_sweep_bit_exact(drm, ob, mid_index, k, ef, search_variant):
     path, Q, _ = mid_index
     _check_search(drm, ob, path, Q[:1500], k, ef)
 
@@ -222,7 +265,7 @@ def test_search_errors(drm, small_index):
     assert "Index file does not exist" in str(e.value)
 
 
-def test_search_then_rerank_pipeline(drm, ob, fixtures, small_index):
+def test_search_then_rerank_pipeline(drm, ob, fixtures, small_index, sw_variant):
     """The whole stage on config 1: search -> SW rerank, vs oracle search -> oracle rerank."""
     path, Q = small_index
     ix = drm.Index(path)
