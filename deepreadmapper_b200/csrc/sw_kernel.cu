@@ -274,7 +274,7 @@ constexpr int PTAB_ENTRIES = 25 * PGROUPS * 8;
 // equal shares:  1 = every clamp on the alu pipe (integer form throughout), 0 = every clamp on the fma pipe,
 // n >= 2 = every n-th clamp on the alu pipe, the rest on the fma pipe.
 template <int ALU_EVERY>
-__device__ __forceinline__ unsigned sw_quad_profile(const uint8_t *selrow, int rows, const uint4 *tab, int lane, unsigned one)
+__device__ __forceinline__ unsigned sw_quad_profile(const uint8_t *rowA, const uint8_t *rowB, int rows, const uint4 *tab, int lane, unsigned one)
 {
     const int l = lane & 3;
     const uint4 *tslot = tab + (lane & 7);
@@ -288,7 +288,7 @@ __device__ __forceinline__ unsigned sw_quad_profile(const uint8_t *selrow, int r
     for (int t = 0; t < rows + 3; ++t) {
         unsigned recv = __shfl_up_sync(FULL, last_out, 1, 4);
         if (l == 0) recv = 0;
-        const uint4 *prow = tslot + (unsigned)selrow[t - l + 3] * (PGROUPS * 8);
+        const uint4 *prow = tslot + (5u * rowA[t - l + 3] + rowB[t - l + 3]) * (PGROUPS * 8);
         unsigned diag = prev_recv, left = recv, mprev = 0;
 #pragma unroll
         for (int g = 0; g < PGROUPS; ++g) {
@@ -327,7 +327,7 @@ __device__ __forceinline__ unsigned sw_quad_profile(const uint8_t *selrow, int r
 // row r0 has just produced, so H[] is still one register per column.  Row r0's clamps go to the fma pipe; row
 // r0 + 1's go to the alu pipe at every AE-th column (AE = 0: never).
 template <int AE>
-__device__ __forceinline__ unsigned sw_quad_profile2(const uint8_t *selrow, int rows, const uint4 *tab, int lane)
+__device__ __forceinline__ unsigned sw_quad_profile2(const uint8_t *rowA, const uint8_t *rowB, int rows, const uint4 *tab, int lane)
 {
     const int l = lane & 3;
     const uint4 *tslot = tab + (lane & 7);
@@ -343,9 +343,10 @@ __device__ __forceinline__ unsigned sw_quad_profile2(const uint8_t *selrow, int 
         unsigned recv0 = __shfl_up_sync(FULL, out0, 1, 4);
         unsigned recv1 = __shfl_up_sync(FULL, out1, 1, 4);
         if (l == 0) { recv0 = 0; recv1 = 0; }
-        const unsigned ab2 = *reinterpret_cast<const unsigned short *>(selrow + 2 * (u - l) + 6);
-        const uint4 *p0 = tslot + (ab2 & 0xffu) * (PGROUPS * 8);
-        const uint4 *p1 = tslot + (ab2 >> 8) * (PGROUPS * 8);
+        const unsigned a2 = *reinterpret_cast<const unsigned short *>(rowA + 2 * (u - l) + 6);
+        const unsigned b2 = *reinterpret_cast<const unsigned short *>(rowB + 2 * (u - l) + 6);
+        const uint4 *p0 = tslot + (5u * (a2 & 0xffu) + (b2 & 0xffu)) * (PGROUPS * 8);
+        const uint4 *p1 = tslot + (5u * (a2 >> 8) + (b2 >> 8)) * (PGROUPS * 8);
         unsigned diag0 = prev_recv1, left0 = recv0;  // row r0: its diagonal neighbour is row r0 - 1's boundary
         unsigned diag1 = recv0, left1 = recv1;       // row r0 + 1
         unsigned h0_last = 0, m0 = 0;
@@ -392,14 +393,14 @@ __device__ __forceinline__ unsigned sw_quad_profile2(const uint8_t *selrow, int 
     return best;
 }
 
-// Dynamic shared memory layout (bytes): tab | sel[PAIRS_PER_PASS][selw] | cand[C] | first[take] | count[take+1]
+// Dynamic shared memory layout (bytes): tab | sel[2 * PAIRS_PER_PASS][selw] (one byte row per candidate) | cand[C] | first[take] | count[take+1]
 template <int RPI, int ALU_EVERY>
 __global__ void __launch_bounds__(RERANK_THREADS, 2) sw_rerank_profile_kernel(const RerankDev p, int selw, unsigned one, int *fb_list, int *fb_n)
 {
     extern __shared__ __align__(16) unsigned char dsm[];
     uint4 *tab = reinterpret_cast<uint4 *>(dsm);
     uint8_t *s_sel = dsm + PTAB_ENTRIES * sizeof(uint4);
-    u64 *s_cand = reinterpret_cast<u64 *>(s_sel + (size_t)PAIRS_PER_PASS * selw);
+    u64 *s_cand = reinterpret_cast<u64 *>(s_sel + (size_t)2 * PAIRS_PER_PASS * selw);
     u64 *s_first = s_cand + p.C;
     int *s_count = reinterpret_cast<int *>(s_first + p.take);
     __shared__ unsigned char s_qcls[PQCOLS];
@@ -470,23 +471,36 @@ __global__ void __launch_bounds__(RERANK_THREADS, 2) sw_rerank_profile_kernel(co
         const int npairs = min(PAIRS_PER_PASS, (nc - c0 + 1) / 2);
         constexpr int PAD = 3 * RPI;             // "none" rows either side: pipeline fill and drain of the quad
         const int srows = rows + 2 * PAD + RPI;  // (+ RPI: the odd last row of a two-row iteration)
-        for (int e = tid; e < npairs * srows; e += RERANK_THREADS) {
-            int pr = e / srows, i = e % srows - PAD;
-            int ca = c0 + 2 * pr, cb = ca + 1;
-            unsigned v = 24;
-            if (i >= 0 && i < rows) {
-                u64 ida = s_cand[ca];
-                int a = window_base(p, ida, window_valid(p, ida), i);
-                int b = 6;
-                if (cb < nc) { u64 idb = s_cand[cb]; b = window_base(p, idb, window_valid(p, idb), i); }
-                v = (unsigned)(5 * min(a, 4) + min(b, 4));
+        // Stage the windows of this pass: one warp per candidate, lanes along the window, so a window is a few coalesced
+        // 32-byte reads of the class array (backwards for a reverse-complement id); the loads of different candidates are
+        // independent and batch up.  s_sel[c][r + PAD] = class of row r (0..3), 4 = matches nothing.
+        {
+            const int warp = tid >> 5, ncand = 2 * npairs;
+#pragma unroll 2
+            for (int c = warp; c < ncand; c += RERANK_THREADS / 32) {
+                const int ci = c0 + c;
+                u64 id = 0;
+                bool valid = false;
+                if (ci < nc) { id = s_cand[ci]; valid = window_valid(p, id); }
+                const bool rc = p.form == 0 && (id & 1);
+                const uint8_t *src = p.form == 1 ? p.ref + id * (u64)rows : p.ref + (id >> 1);
+                uint8_t *dst = s_sel + (size_t)c * selw;
+                for (int i = lane; i < srows; i += 32) {
+                    const int rr = i - PAD;
+                    unsigned v = 4;
+                    if (valid && rr >= 0 && rr < rows) {
+                        const unsigned cls = rc ? src[rows - 1 - rr] : src[rr];
+                        v = cls < 4 ? (rc ? 3 - cls : cls) : 4;
+                    }
+                    dst[i] = (uint8_t)v;
+                }
             }
-            s_sel[(size_t)pr * selw + i + PAD] = (uint8_t)v;
         }
         __syncthreads();
         if ((tid >> 5) * 8 < npairs) {
-            const uint8_t *selrow = s_sel + (size_t)(pair < npairs ? pair : 0) * selw;
-            unsigned best = RPI == 2 ? sw_quad_profile2<ALU_EVERY>(selrow, rows, tab, lane) : sw_quad_profile<ALU_EVERY>(selrow, rows, tab, lane, one);
+            const int pp = pair < npairs ? pair : 0;
+            const uint8_t *rowA = s_sel + (size_t)(2 * pp) * selw, *rowB = rowA + selw;
+            unsigned best = RPI == 2 ? sw_quad_profile2<ALU_EVERY>(rowA, rowB, rows, tab, lane) : sw_quad_profile<ALU_EVERY>(rowA, rowB, rows, tab, lane, one);
             if ((lane & 3) == 0 && pair < npairs) {
                 int sa = (int)(short)(best & 0xffffu) - 1, sb = (int)(short)(best >> 16) - 1;
                 int ca = c0 + 2 * pair;
@@ -751,7 +765,7 @@ int launch_rerank(const DeviceRef &ref, const RerankArgs &a, cudaStream_t stream
         for (const auto &kv : kVariants)
             if (!strcmp(e, kv.name)) variant = kv.v;
     const int selw = (ref.ref_len + 14 + 3) / 4 * 4;  // rows + fill/drain padding of the two-row form (12) + 2
-    const size_t psmem = (size_t)PTAB_ENTRIES * sizeof(uint4) + (size_t)PAIRS_PER_PASS * selw + (size_t)C * sizeof(u64) +
+    const size_t psmem = (size_t)PTAB_ENTRIES * sizeof(uint4) + (size_t)2 * PAIRS_PER_PASS * selw + (size_t)C * sizeof(u64) +
                          (size_t)take * sizeof(u64) + (size_t)(take + 1) * sizeof(int) + 16;
     int *fb = nullptr;  // [0] = count, [1..] = reads handed back by the profile kernel
     if (fast && variant != 0) {

@@ -1,0 +1,103 @@
+// Host side of the drop-in: the reference's C++ call signatures for the search-time hot path, implemented over
+// the C ABI of libdrm_cuda.so (include/drm_b200.h).  A `pipeline` built against this header keeps the structure of
+// the reference's src/main.cpp: read_index -> faiss_search -> post_process_sw_* -> save_results.
+//
+// Signatures mirrored (paths relative to the reference repository):
+//   faiss::read_index / faiss::IndexHNSWPQ                src/main.cpp:236-237,299
+//   faiss_search                                          includes/hnswpq/search.hpp:18-22, src/hnswpq/search.cpp:6-57
+//   post_process_sw_static / post_process_sw_dynamic      includes/utils/post_processor.hpp:79-103
+//   sw_reranker                                           includes/utils/reranker.hpp:19-23
+//   calc_sw_score                                         includes/utils/metrics.hpp:22
+//   load_config / save_config / save_results / read_file  includes/utils/utils.hpp:53-115
+//   reverse_complement / extract_FASTA_sequence / preprocess_fasta / preprocess_fastq   includes/utils/parse_inputs.hpp
+// Errors are std::runtime_error with the reference's messages; main catches once and prints "Error: <what>".
+#pragma once
+
+#include <cstddef>
+#include <cstdint>
+#include <string>
+#include <tuple>
+#include <unordered_map>
+#include <utility>
+#include <variant>
+#include <vector>
+
+struct drm_index;
+struct drm_ref;
+
+// includes/utils/config.hpp:6-57 (only the constants the path uses)
+namespace Config {
+namespace Build { constexpr int DIM = 128; constexpr int M_PQ = 8; constexpr int NBITS = 8; constexpr int M = 16; constexpr int EFC = 200;
+                  constexpr float SAMPLE_RATE = 0.5f; }
+namespace Search { constexpr int EF = 128; constexpr int K = 128; constexpr int K_CLUSTERS = 5; }
+}  // namespace Config
+
+namespace faiss {
+using idx_t = int64_t;
+// Handle on an IHNp index resident on the GPU(s).  `delete` releases the device memory, as src/main.cpp:299 expects.
+struct IndexHNSWPQ {
+    drm_index *handle = nullptr;
+    int d = 0;
+    int64_t ntotal = 0;
+    struct { int efSearch = 16; int efConstruction = 40; } hnsw;
+    ~IndexHNSWPQ();
+};
+// Devices: every visible GPU unless DRM_DEVICES="0,1,.." restricts them (index replicated, reads sharded).
+IndexHNSWPQ *read_index(const char *index_file);
+}  // namespace faiss
+
+std::pair<std::vector<std::vector<faiss::idx_t>>, std::vector<std::vector<float>>> faiss_search(
+    faiss::IndexHNSWPQ *index, const std::vector<std::vector<float>> &query_data, int k = Config::Search::K, int ef = Config::Search::EF);
+
+// Flat form used by the pipeline for large batches (no nested vectors): q is n x d row-major.
+void faiss_search_flat(faiss::IndexHNSWPQ *index, const float *q, int64_t n, int d, int k, int ef, std::vector<faiss::idx_t> &I, std::vector<float> &D);
+
+int calc_sw_score(const std::string &seq1, const std::string &seq2);
+
+std::tuple<std::vector<std::string>, std::vector<int>, std::vector<size_t>> sw_reranker(
+    const std::vector<std::string> &cand_seqs, const std::vector<size_t> &cand_ids, const std::string &query_seq, size_t k);
+
+template <typename NeighborType>
+std::tuple<std::vector<std::string>, std::vector<int>, std::vector<size_t>> post_process_sw_dynamic(
+    const std::vector<std::vector<NeighborType>> &neighbors, const std::vector<std::vector<float>> &distances, const std::string &ref_genome,
+    const std::vector<std::string> &query_seqs, size_t ref_len, size_t stride, size_t k, size_t k_clusters = 5);
+
+template <typename NeighborType>
+std::tuple<std::vector<std::string>, std::vector<int>, std::vector<size_t>> post_process_sw_static(
+    const std::vector<std::vector<NeighborType>> &neighbors, const std::vector<std::vector<float>> &distances,
+    const std::vector<std::string> &ref_seqs, const std::vector<std::string> &query_seqs, size_t ref_len, size_t stride, size_t k,
+    size_t k_clusters = 5);
+
+// Flat rerank for the pipeline: neighbours n x k_in (int64), returns scores / ids n x k; candidate strings are not built.
+// mode 0 = static bound rule, 1 = dynamic.  `genome` is the cleaned reference (extract_FASTA_sequence).
+void post_process_sw_flat(int mode, const std::string &genome, size_t ref_len, const std::vector<faiss::idx_t> &I, int64_t n, int64_t k_in,
+                          const std::vector<std::string> &query_seqs, size_t stride, size_t k, size_t k_clusters, std::vector<int> &scores,
+                          std::vector<size_t> &ids);
+
+// ---- parse_inputs
+std::string reverse_complement(const std::string &seq);
+std::string extract_FASTA_sequence(const std::string &fasta_file);
+std::pair<std::vector<std::string>, std::vector<size_t>> preprocess_fasta(const std::string &fasta_file, size_t ref_len, size_t stride, bool lookup_mode);
+std::pair<std::vector<std::string>, std::vector<std::string>> preprocess_fastq(const std::string &fastq_file);
+std::pair<std::vector<std::string>, std::vector<std::string>> read_file(const std::string &file_path, size_t ref_len = 150, size_t stride = 1, bool lookup_mode = false);
+std::string find_sequence(const std::string &ref_genome, size_t id, size_t ref_len);
+
+// ---- utils
+using ConfigValue = std::variant<size_t, float, std::string>;
+int save_config(const std::unordered_map<std::string, ConfigValue> &config, const std::string &folder_path, const std::string &config_file = "config.txt");
+std::unordered_map<std::string, ConfigValue> load_config(const std::string &config_file);
+int save_results(const std::vector<std::vector<size_t>> &neighbors, const std::vector<std::vector<float>> &distances, const std::string &indices_file,
+                 const std::string &distances_file, size_t k, const bool use_npy = true);
+int save_results(const std::vector<std::vector<long int>> &neighbors, const std::vector<std::vector<float>> &distances, const std::string &indices_file,
+                 const std::string &distances_file, size_t k, const bool use_npy = true);
+
+// ---- npy (cnpy-compatible v1.0 files: external/cnpy/cnpy.h:88-131,235-264, external/cnpy/cnpy.cpp:104-155)
+namespace npy {
+struct Array { std::vector<size_t> shape; size_t word_size = 0; char kind = '?'; bool fortran_order = false; std::vector<char> data; };
+Array load(const std::string &path);
+void save_raw(const std::string &path, const void *data, char kind, size_t word_size, const std::vector<size_t> &shape);
+inline void save(const std::string &p, const float *d, const std::vector<size_t> &s) { save_raw(p, d, 'f', 4, s); }
+inline void save(const std::string &p, const size_t *d, const std::vector<size_t> &s) { save_raw(p, d, 'u', 8, s); }
+inline void save(const std::string &p, const int *d, const std::vector<size_t> &s) { save_raw(p, d, 'i', 4, s); }
+inline void save(const std::string &p, const unsigned int *d, const std::vector<size_t> &s) { save_raw(p, d, 'u', 4, s); }
+}  // namespace npy

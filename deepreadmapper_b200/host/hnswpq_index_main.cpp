@@ -1,0 +1,82 @@
+// `hnswpq_index` — the reference's index builder CLI (src/hnswpq/index.cpp:195-316):
+//
+//   hnswpq_index <ref.(fna|fasta|fa|txt|npy)> <index_prefix> <ref_len> [stride=1] [M_pq=8] [nbits=8] [M_hnsw=16] [EFC=200]
+//
+// writes <prefix>/<prefix>.index (FAISS "IHNp" layout) and <prefix>/config.txt with the reference's keys
+// (index_type, stride, ref_len, n_vects, dim, M_hnsw, EFC, M_pq, nbits, index_file; src/hnswpq/index.cpp:289-304).
+// The embedder is outside this build, so a sequence reference needs its embeddings beside it as `<ref file>.npy`;
+// a .npy reference is used as-is, like the reference does (:236-265).  Training set = evenly strided
+// Config::Build::SAMPLE_RATE sample (create_training_set, :57-84,99).
+#include <algorithm>
+#include <filesystem>
+#include <iostream>
+#include <stdexcept>
+
+#include "../../include/drm_b200.h"
+#include "drm_host.hpp"
+
+int main(int argc, char *argv[])
+{
+    if (argc < 4 || argc > 9) {
+        std::cerr << "Usage: " << argv[0] << " <ref_seq.txt> <index_prefix> <ref_len> [stride] [M_pq] [nbits] [M_hnsw] [EFC]" << std::endl;
+        std::cerr << "  stride: step size for sliding window (default: 1)" << std::endl;
+        std::cerr << "  M_pq: number of PQ subquantizers (default: 8)" << std::endl;
+        std::cerr << "  nbits: bits per subquantizer (default: 8)" << std::endl;
+        std::cerr << "  M_hnsw: HNSW connectivity (default: 16)" << std::endl;
+        std::cerr << "  EFC: efConstruction parameter (default: 200)" << std::endl;
+        return 1;
+    }
+    try {
+        const std::string ref_file = argv[1];
+        const std::string index_prefix = argv[2];
+        const std::string index_file = index_prefix + "/" + index_prefix + ".index";  // the reference's rule (:212)
+        const size_t ref_len = (size_t)std::stoul(argv[3]);
+        const size_t stride = argc >= 5 ? (size_t)std::stoul(argv[4]) : 1;
+        const int M_pq = argc >= 6 ? std::stoi(argv[5]) : Config::Build::M_PQ;
+        const int nbits = argc >= 7 ? std::stoi(argv[6]) : Config::Build::NBITS;
+        const int M_hnsw = argc >= 8 ? std::stoi(argv[7]) : Config::Build::M;
+        const int EFC = argc >= 9 ? std::stoi(argv[8]) : Config::Build::EFC;
+
+        std::string emb_file = ref_file;
+        if (std::filesystem::path(ref_file).extension().string() != ".npy") {
+            emb_file = ref_file + ".npy";
+            if (!std::filesystem::exists(emb_file))
+                throw std::runtime_error("Embeddings not found: " + emb_file + " (the embedder is outside this build; run the reference's `inference` tool)");
+        }
+        std::cout << "[BUILD INDEX] Loading embeddings directly from .npy file: " << emb_file << std::endl;
+        npy::Array arr = npy::load(emb_file);
+        if (arr.shape.size() != 2) {
+            std::cerr << "Error: Expected 2D array in .npy file" << std::endl;
+            return 1;
+        }
+        if (arr.kind != 'f' || arr.word_size != 4 || arr.fortran_order) throw std::runtime_error("Error: embeddings must be C-order float32 ('<f4')");
+        const size_t n = arr.shape[0], d = arr.shape[1];
+        std::cout << "[BUILD INDEX] Loaded " << n << " embeddings of dimension " << d << std::endl;
+        if (n == 0) throw std::runtime_error("No sequences found in file: " + ref_file);
+        const float *x = reinterpret_cast<const float *>(arr.data.data());
+
+        std::cout << "[BUILD INDEX] Saving index config to folder: " << index_prefix << std::endl;
+        std::unordered_map<std::string, ConfigValue> config = {
+            {"index_type", std::string("HNSWPQ")}, {"stride", stride}, {"ref_len", ref_len}, {"n_vects", n}, {"dim", d},
+            {"M_hnsw", (size_t)M_hnsw}, {"EFC", (size_t)EFC}, {"M_pq", (size_t)M_pq}, {"nbits", (size_t)nbits}, {"index_file", index_file}};
+        save_config(config, index_prefix);
+        std::cout << "[BUILD INDEX] Config saved successfully." << std::endl;
+
+        std::cout << "[BUILD INDEX] Building IndexHNSWPQ..." << std::endl;
+        const size_t n_train = std::max<size_t>(1, (size_t)((double)n * Config::Build::SAMPLE_RATE));
+        std::vector<float> train(n_train * d);
+        const double step = (double)n / (double)n_train;
+        for (size_t i = 0; i < n_train; ++i) {
+            const size_t si = std::min((size_t)((double)i * step), n - 1);
+            std::copy(x + si * d, x + (si + 1) * d, train.begin() + (long)(i * d));
+        }
+        if (drm_build_index(x, (int64_t)n, (int)d, train.data(), (int64_t)n_train, M_pq, nbits, M_hnsw, EFC, 0, 1234u, index_file.c_str()) != DRM_OK)
+            throw std::runtime_error(drm_last_error());
+        std::cout << "[BUILD INDEX] Index saved to: " << index_file << std::endl;
+        std::cout << "[BUILD INDEX] Finished index building process." << std::endl;
+    } catch (const std::exception &e) {
+        std::cerr << "Error: " << e.what() << std::endl;
+        return 1;
+    }
+    return 0;
+}

@@ -1,0 +1,154 @@
+// `pipeline` — the reference's CLI (src/main.cpp:10-451) with the search and rerank stages on the GPU.
+//
+//   pipeline <index_prefix> <query_seqs.fastq|.fasta|.txt|.npy> <ref_seqs.fasta> [EF=128] [K=128] [K_clusters=5]
+//            [output_dir=.] [use_dynamic=0] [use_streaming=0]
+//
+// Same positional arguments, defaults, file layout (<prefix>/<basename>.index, <prefix>/config.txt), error messages and
+// outputs (<output_dir>/indices.npy '<u8', distances.npy '<f4' = the RAW search output, src/main.cpp:371-384).
+// Differences, all additive:
+//   * the embedder (OpenVINO BiLSTM) is outside this build: a sequence query file needs its embeddings as
+//     `<query file>.npy` (or env DRM_QUERY_EMB=<file.npy>); a bare .npy query = the reference's search-only behaviour;
+//   * the rerank is the Smith-Waterman variant the reference has implemented but commented out (src/main.cpp:333-341);
+//     its result goes to NEW files sw_scores.npy ('<i4', n x K) and sw_indices.npy ('<u8', n x K); DRM_RERANK=none skips it;
+//   * both modes rerank from the cleaned genome on the device: use_dynamic=0 applies the static bound rule (number of
+//     dense windows), use_dynamic=1 the dynamic one (genome length) - the two rules of find_sequences.
+#include <chrono>
+#include <cstdlib>
+#include <cstring>
+#include <filesystem>
+#include <iostream>
+#include <stdexcept>
+
+#include "drm_host.hpp"
+
+namespace {
+using Clock = std::chrono::high_resolution_clock;
+long ms_since(Clock::time_point t0) { return (long)std::chrono::duration_cast<std::chrono::milliseconds>(Clock::now() - t0).count(); }
+}  // namespace
+
+int main(int argc, char *argv[])
+{
+    if (argc < 4 || argc > 10) {
+        std::cerr << "Usage: " << argv[0]
+                  << " <index_prefix> <query_seqs.fastq> <ref_seqs.fasta> [EF] [K] [K_clusters] [output_dir] [use_dynamic] [use_streaming]" << std::endl;
+        std::cerr << "  - query input: FASTQ/FASTA/TXT file (with its embeddings in <file>.npy or $DRM_QUERY_EMB) or pre-computed embeddings in .npy format" << std::endl;
+        std::cerr << "  - EF: Optional HNSW search parameter (default: " << Config::Search::EF << ")" << std::endl;
+        std::cerr << "  - K: Optional number of nearest neighbors to return (default: " << Config::Search::K << ")" << std::endl;
+        std::cerr << "  - output_dir: Optional output directory (default: current directory)" << std::endl;
+        std::cerr << "  - use_dynamic: Optional flag to load reference sequences dynamically (1) or statically (0). Default: 0" << std::endl;
+        std::cerr << "  - use_streaming: accepted for compatibility; SAM streaming belongs to the L2 rerank, which is out of scope" << std::endl;
+        return 1;
+    }
+    try {
+        const auto master_start = Clock::now();
+        std::cout << "=== DeepAligner B200 Pipeline ===" << std::endl << std::endl;
+        const std::string index_prefix = argv[1];
+        const std::string basename = std::filesystem::path(index_prefix).filename().string();
+        const std::string index_file = index_prefix + "/" + basename + ".index";
+        const std::string config_file = index_prefix + "/" + "config.txt";
+        if (!std::filesystem::exists(config_file)) throw std::runtime_error("Config file does not exist: " + config_file);
+        auto config = load_config(config_file);
+        const size_t ref_len = std::get<size_t>(config["ref_len"]);
+        const size_t stride = std::get<size_t>(config["stride"]);
+        const std::string query_input_file = argv[2];
+        const std::string ref_seqs_file = argv[3];
+        const int ef = argc >= 5 ? std::stoi(argv[4]) : Config::Search::EF;
+        const int k = argc >= 6 ? std::stoi(argv[5]) : Config::Search::K;
+        int k_clusters = Config::Search::K_CLUSTERS;
+        if (stride == 1) k_clusters = k;
+        else if (argc >= 7) k_clusters = std::stoi(argv[6]);
+        const std::string output_dir = argc >= 8 ? argv[7] : ".";
+        const bool use_dynamic = argc >= 9 ? std::stoi(argv[8]) != 0 : false;
+        const char *rr = getenv("DRM_RERANK");
+        const bool rerank = !(rr && !strcmp(rr, "none"));
+
+        std::cout << "[MAIN] PIPELINE CONFIG:" << std::endl;
+        std::cout << "[MAIN] Input file: " << query_input_file << std::endl;
+        std::cout << "[MAIN] Reference file: " << ref_seqs_file << std::endl;
+
+        // ---------------- data loading
+        std::cout << "[MAIN] DATA LOADING STEP" << std::endl;
+        auto t0 = Clock::now();
+        const bool is_npy = std::filesystem::path(query_input_file).extension().string() == ".npy";
+        std::vector<std::string> query_sequences, query_ids;
+        std::string emb_file = query_input_file;
+        if (!is_npy) {
+            std::tie(query_sequences, query_ids) = read_file(query_input_file);
+            if (query_sequences.empty()) {
+                std::cerr << "No query_sequences found in input file!" << std::endl;
+                return 1;
+            }
+            const char *env = getenv("DRM_QUERY_EMB");
+            emb_file = env ? env : query_input_file + ".npy";
+            if (!std::filesystem::exists(emb_file))
+                throw std::runtime_error("Embeddings not found: " + emb_file + " (the embedder is outside this build; run the reference's `inference` tool)");
+        }
+        npy::Array arr = npy::load(emb_file);
+        if (arr.shape.size() != 2) throw std::runtime_error("Error: Expected 2D array in .npy file");
+        if (arr.kind != 'f' || arr.word_size != 4 || arr.fortran_order) throw std::runtime_error("Error: embeddings must be C-order float32 ('<f4')");
+        const size_t num_queries = arr.shape[0], dim = arr.shape[1];
+        std::cout << "[MAIN] Loaded " << num_queries << " embeddings of dimension " << dim << std::endl;
+        if (!is_npy && query_sequences.size() != num_queries) throw std::runtime_error("Error: number of embeddings differs from the number of query sequences");
+        std::string ref_genome;
+        if (!is_npy && rerank) {
+            std::cout << "[MAIN] Using " << (use_dynamic ? "DYNAMIC" : "STATIC") << " fetching for reference sequences" << std::endl;
+            ref_genome = extract_FASTA_sequence(ref_seqs_file);
+        } else {
+            std::cout << "[MAIN] Skipping reference loading (not needed for pre-computed embeddings)" << std::endl;
+        }
+        std::cout << "[MAIN] Total Data loading time: " << ms_since(t0) << " ms" << std::endl << std::endl;
+
+        // ---------------- index
+        std::cout << "[MAIN] HNSW INDEX LOADING STEP" << std::endl;
+        std::cout << "[MAIN] Index file: " << index_file << std::endl;
+        std::cout << "[MAIN] EF: " << ef << std::endl;
+        t0 = Clock::now();
+        if (!std::filesystem::exists(index_file)) throw std::runtime_error("Index file does not exist: " + index_file);
+        faiss::IndexHNSWPQ *alg_hnsw = faiss::read_index(index_file.c_str());
+        std::cout << "[MAIN] Index loading time: " << ms_since(t0) << " ms" << std::endl << std::endl;
+
+        // ---------------- search
+        std::cout << "[MAIN] HNSW SEARCH STEP" << std::endl;
+        t0 = Clock::now();
+        std::vector<faiss::idx_t> I;
+        std::vector<float> D;
+        faiss_search_flat(alg_hnsw, reinterpret_cast<const float *>(arr.data.data()), (int64_t)num_queries, (int)dim, k_clusters, ef, I, D);
+        std::cout << "[MAIN] HNSW search time: " << ms_since(t0) << " ms" << std::endl << std::endl;
+        delete alg_hnsw;
+
+        // ---------------- post-processing (Smith-Waterman rerank)
+        std::cout << "[MAIN] POST-PROCESSING STEP" << std::endl;
+        t0 = Clock::now();
+        std::vector<int> sw_scores;
+        std::vector<size_t> sw_ids;
+        if (!is_npy && rerank) {
+            post_process_sw_flat(use_dynamic ? 1 : 0, ref_genome, ref_len, I, (int64_t)num_queries, k_clusters, query_sequences, stride, (size_t)k,
+                                 (size_t)k_clusters, sw_scores, sw_ids);
+        } else {
+            std::cout << "[MAIN] Skipping post-processing (no sequence data available)" << std::endl;
+        }
+        std::cout << "[MAIN] Post-processing time: " << ms_since(t0) << " ms" << std::endl << std::endl;
+
+        // ---------------- output
+        std::cout << "[MAIN] OUTPUT SAVING STEP" << std::endl;
+        t0 = Clock::now();
+        std::filesystem::create_directories(output_dir);
+        {
+            std::vector<size_t> u(I.begin(), I.end());  // long -> size_t: -1 becomes 2^64-1 (src/utils/utils.cpp:323-330)
+            npy::save(output_dir + "/indices.npy", u.data(), {num_queries, (size_t)k_clusters});
+            npy::save(output_dir + "/distances.npy", D.data(), {num_queries, (size_t)k_clusters});
+        }
+        if (!sw_scores.empty()) {
+            npy::save(output_dir + "/sw_scores.npy", sw_scores.data(), {num_queries, (size_t)k});
+            npy::save(output_dir + "/sw_indices.npy", sw_ids.data(), {num_queries, (size_t)k});
+        }
+        std::cout << "[MAIN] Output saving time: " << ms_since(t0) << " ms" << std::endl;
+        std::cout << "[MAIN] Finished processing file: " << query_input_file << std::endl;
+        std::cout << "[MAIN] Index: " << index_prefix << std::endl;
+        std::cout << "[MAIN] Total pipeline time: " << ms_since(master_start) << " ms" << std::endl;
+    } catch (const std::exception &e) {
+        std::cerr << "Error: " << e.what() << std::endl;
+        return 1;
+    }
+    return 0;
+}

@@ -1,0 +1,253 @@
+// The two stages of the hot path behind the reference's own C++ signatures, over the C ABI (include/drm_b200.h).
+// No arithmetic of the path happens here: these functions flatten the STL containers the reference passes around,
+// call libdrm_cuda.so, and rebuild the containers the reference returns.
+#include "drm_host.hpp"
+
+#include <algorithm>
+#include <cstdlib>
+#include <cstring>
+#include <iostream>
+#include <sstream>
+#include <stdexcept>
+
+#include "../../include/drm_b200.h"
+
+namespace {
+
+[[noreturn]] void throw_last() { throw std::runtime_error(drm_last_error()); }
+
+std::vector<int> device_list()
+{
+    std::vector<int> devs;
+    if (const char *e = getenv("DRM_DEVICES")) {
+        std::stringstream ss(e);
+        std::string tok;
+        while (std::getline(ss, tok, ','))
+            if (!tok.empty()) devs.push_back(std::stoi(tok));
+    }
+    if (devs.empty()) {
+        const int n = drm_device_count();
+        for (int i = 0; i < n; ++i) devs.push_back(i);
+    }
+    if (devs.empty()) throw std::runtime_error("no CUDA device: the hot path has no CPU fallback");
+    return devs;
+}
+
+void flatten(const std::vector<std::string> &v, std::string &flat, std::vector<int64_t> &off)
+{
+    off.assign(v.size() + 1, 0);
+    size_t total = 0;
+    for (size_t i = 0; i < v.size(); ++i) { total += v[i].size(); off[i + 1] = (int64_t)total; }
+    flat.clear();
+    flat.reserve(total + 1);
+    for (const auto &s : v) flat += s;
+}
+
+// One reference handle is kept alive between calls: the pipeline reranks against the same genome / window table.
+struct RefCache {
+    drm_ref *h = nullptr;
+    const void *key = nullptr;
+    size_t len = 0, ref_len = 0;
+    int form = -1;
+    ~RefCache() { if (h) drm_ref_close(h); }
+} g_ref;
+
+drm_ref *genome_ref(const std::string &genome, size_t ref_len)
+{
+    if (g_ref.h && g_ref.form == 0 && g_ref.key == genome.data() && g_ref.len == genome.size() && g_ref.ref_len == ref_len) return g_ref.h;
+    if (g_ref.h) { drm_ref_close(g_ref.h); g_ref.h = nullptr; }
+    const std::vector<int> devs = device_list();
+    if (drm_ref_open_genome(genome.data(), (int64_t)genome.size(), (int)ref_len, devs.data(), (int)devs.size(), &g_ref.h) != DRM_OK) throw_last();
+    g_ref.form = 0; g_ref.key = genome.data(); g_ref.len = genome.size(); g_ref.ref_len = ref_len;
+    return g_ref.h;
+}
+
+drm_ref *table_ref(const std::vector<std::string> &ref_seqs, size_t ref_len)
+{
+    if (g_ref.h && g_ref.form == 1 && g_ref.key == ref_seqs.data() && g_ref.len == ref_seqs.size() && g_ref.ref_len == ref_len) return g_ref.h;
+    if (g_ref.h) { drm_ref_close(g_ref.h); g_ref.h = nullptr; }
+    std::string flat;
+    flat.reserve(ref_seqs.size() * ref_len);
+    for (const auto &s : ref_seqs) {
+        if (s.size() != ref_len) throw std::runtime_error("post_process_sw_static: reference windows must all be ref_len long");
+        flat += s;
+    }
+    const std::vector<int> devs = device_list();
+    if (drm_ref_open_windows(flat.data(), (int64_t)ref_seqs.size(), (int)ref_len, devs.data(), (int)devs.size(), &g_ref.h) != DRM_OK) throw_last();
+    g_ref.form = 1; g_ref.key = ref_seqs.data(); g_ref.len = ref_seqs.size(); g_ref.ref_len = ref_len;
+    return g_ref.h;
+}
+
+template <typename NeighborType>
+void flatten_neighbors(const std::vector<std::vector<NeighborType>> &nb, size_t k_clusters, std::vector<int64_t> &flat, int64_t &k_in)
+{
+    // post_process_sw_* uses the first min(k_clusters, |row|) ids of every row; rows are padded with -1 (never a valid id:
+    // as size_t it is >= every bound, so find_sequences drops it exactly like the reference drops out-of-range ids).
+    size_t w = 0;
+    for (const auto &r : nb) w = std::max(w, std::min(r.size(), k_clusters));
+    k_in = (int64_t)std::max<size_t>(w, 1);
+    flat.assign(nb.size() * (size_t)k_in, -1);
+    for (size_t i = 0; i < nb.size(); ++i)
+        for (size_t j = 0; j < std::min(nb[i].size(), (size_t)k_in); ++j) flat[i * (size_t)k_in + j] = (int64_t)nb[i][j];
+}
+
+template <typename NeighborType>
+std::tuple<std::vector<std::string>, std::vector<int>, std::vector<size_t>> post_process_sw(
+    int mode, drm_ref *ref, const std::vector<std::vector<NeighborType>> &neighbors, const std::vector<std::string> &query_seqs, size_t stride,
+    size_t k, size_t k_clusters, const std::string *genome, const std::vector<std::string> *table, size_t ref_len)
+{
+    if (k > k_clusters * 2 * stride)  // src/utils/post_processor.cpp:389-392,486-489
+        throw std::runtime_error("Final k too large. Ensure k < k_clusters * 2 * stride to have enough candidates.");
+    const size_t n = query_seqs.size();
+    if (neighbors.size() < n) throw std::runtime_error("post_process_sw: fewer neighbour rows than queries");
+    std::vector<int64_t> nb;
+    int64_t k_in = 1;
+    std::vector<std::vector<NeighborType>> head(neighbors.begin(), neighbors.begin() + (long)n);
+    flatten_neighbors(head, k_clusters, nb, k_in);
+    std::string qflat;
+    std::vector<int64_t> qoff;
+    flatten(query_seqs, qflat, qoff);
+    std::vector<int> scores(n * k);
+    std::vector<uint64_t> ids(n * k);
+    if (n && drm_sw_rerank(ref, mode, nb.data(), (int64_t)n, k_in, qflat.data(), qoff.data(), (int64_t)stride, (int64_t)k, (int64_t)k_clusters,
+                           scores.data(), ids.data(), nullptr, nullptr) != DRM_OK)
+        throw_last();
+    std::vector<std::string> seqs(n * k);
+    std::vector<size_t> out_ids(ids.begin(), ids.end());
+    for (size_t i = 0; i < n * k; ++i)
+        seqs[i] = genome ? find_sequence(*genome, out_ids[i], ref_len) : (out_ids[i] < table->size() ? (*table)[out_ids[i]] : std::string());
+    return {std::move(seqs), std::move(scores), std::move(out_ids)};
+}
+
+}  // namespace
+
+// ------------------------------------------------------------------------------------------ index + search
+namespace faiss {
+
+IndexHNSWPQ::~IndexHNSWPQ() { if (handle) drm_index_close(handle); }
+
+IndexHNSWPQ *read_index(const char *index_file)
+{
+    const std::vector<int> devs = device_list();
+    drm_index *h = nullptr;
+    if (drm_index_open(index_file, devs.data(), (int)devs.size(), &h) != DRM_OK) throw_last();
+    int64_t info[12];
+    drm_index_info(h, info);
+    auto *ix = new IndexHNSWPQ;
+    ix->handle = h;
+    ix->d = (int)info[0];
+    ix->ntotal = info[1];
+    ix->hnsw.efConstruction = (int)info[7];
+    ix->hnsw.efSearch = (int)info[8];
+    return ix;
+}
+
+}  // namespace faiss
+
+void faiss_search_flat(faiss::IndexHNSWPQ *index, const float *q, int64_t n, int d, int k, int ef, std::vector<faiss::idx_t> &I, std::vector<float> &D)
+{
+    if (!index || !index->handle) throw std::runtime_error("faiss_search: null index");
+    index->hnsw.efSearch = ef;  // src/hnswpq/search.cpp:13
+    if (n <= 0) throw std::runtime_error("Query data is empty");
+    I.resize((size_t)n * k);
+    D.resize((size_t)n * k);
+    if (drm_search(index->handle, q, n, d, k, ef, D.data(), I.data(), nullptr) != DRM_OK) throw_last();
+}
+
+std::pair<std::vector<std::vector<faiss::idx_t>>, std::vector<std::vector<float>>> faiss_search(
+    faiss::IndexHNSWPQ *index, const std::vector<std::vector<float>> &query_data, int k, int ef)
+{
+    if (query_data.empty()) throw std::runtime_error("Query data is empty");  // src/hnswpq/search.cpp:16-19
+    const size_t n = query_data.size(), d = query_data[0].size();
+    std::vector<float> flat(n * d);
+    for (size_t i = 0; i < n; ++i) {
+        if (query_data[i].size() != d) throw std::runtime_error("faiss_search: ragged query matrix");
+        memcpy(&flat[i * d], query_data[i].data(), d * sizeof(float));
+    }
+    std::vector<faiss::idx_t> I;
+    std::vector<float> D;
+    faiss_search_flat(index, flat.data(), (int64_t)n, (int)d, k, ef, I, D);
+    std::vector<std::vector<faiss::idx_t>> nb(n);
+    std::vector<std::vector<float>> ds(n);
+    for (size_t i = 0; i < n; ++i) {
+        nb[i].assign(I.begin() + (long)(i * k), I.begin() + (long)((i + 1) * k));
+        ds[i].assign(D.begin() + (long)(i * k), D.begin() + (long)((i + 1) * k));
+    }
+    return {std::move(nb), std::move(ds)};
+}
+
+// ------------------------------------------------------------------------------------------ Smith-Waterman
+int calc_sw_score(const std::string &seq1, const std::string &seq2)
+{
+    const int64_t a_off[2] = {0, (int64_t)seq1.size()}, b_off[2] = {0, (int64_t)seq2.size()};
+    int32_t score = 0;
+    if (drm_sw_pairs(seq1.data(), a_off, seq2.data(), b_off, 1, &score) != DRM_OK) throw_last();
+    return score;
+}
+
+std::tuple<std::vector<std::string>, std::vector<int>, std::vector<size_t>> sw_reranker(
+    const std::vector<std::string> &cand_seqs, const std::vector<size_t> &cand_ids, const std::string &query_seq, size_t k)
+{
+    const size_t n = cand_seqs.size();
+    if (n < k)  // src/utils/reranker.cpp:26-29
+        throw std::runtime_error("Not enough candidates (" + std::to_string(n) + " < " + std::to_string(k) + ")");
+    if (n == 0 || k == 0) return {};
+    std::string aflat, bflat;
+    std::vector<int64_t> aoff, boff(n + 1);
+    flatten(cand_seqs, aflat, aoff);
+    for (size_t i = 0; i <= n; ++i) boff[i] = (int64_t)(i * query_seq.size());
+    for (size_t i = 0; i < n; ++i) bflat += query_seq;
+    std::vector<int32_t> scores(n);
+    if (drm_sw_pairs(aflat.data(), aoff.data(), bflat.data(), boff.data(), (int64_t)n, scores.data()) != DRM_OK) throw_last();
+    // top-k by the same std::partial_sort call as the reference (src/utils/reranker.cpp:35-40): index order, not arithmetic
+    std::vector<size_t> idx(n);
+    for (size_t i = 0; i < n; ++i) idx[i] = i;
+    std::partial_sort(idx.begin(), idx.begin() + (long)k, idx.end(), [&](size_t a, size_t b) { return scores[a] > scores[b]; });
+    std::vector<std::string> s(k);
+    std::vector<int> sc(k);
+    std::vector<size_t> ids(k);
+    for (size_t i = 0; i < k; ++i) { s[i] = cand_seqs[idx[i]]; sc[i] = scores[idx[i]]; ids[i] = cand_ids[idx[i]]; }
+    return {std::move(s), std::move(sc), std::move(ids)};
+}
+
+template <typename NeighborType>
+std::tuple<std::vector<std::string>, std::vector<int>, std::vector<size_t>> post_process_sw_dynamic(
+    const std::vector<std::vector<NeighborType>> &neighbors, const std::vector<std::vector<float>> &, const std::string &ref_genome,
+    const std::vector<std::string> &query_seqs, size_t ref_len, size_t stride, size_t k, size_t k_clusters)
+{
+    return post_process_sw<NeighborType>(1, genome_ref(ref_genome, ref_len), neighbors, query_seqs, stride, k, k_clusters, &ref_genome, nullptr, ref_len);
+}
+
+template <typename NeighborType>
+std::tuple<std::vector<std::string>, std::vector<int>, std::vector<size_t>> post_process_sw_static(
+    const std::vector<std::vector<NeighborType>> &neighbors, const std::vector<std::vector<float>> &, const std::vector<std::string> &ref_seqs,
+    const std::vector<std::string> &query_seqs, size_t ref_len, size_t stride, size_t k, size_t k_clusters)
+{
+    return post_process_sw<NeighborType>(0, table_ref(ref_seqs, ref_len), neighbors, query_seqs, stride, k, k_clusters, nullptr, &ref_seqs, ref_len);
+}
+
+// explicit instantiations, as src/utils/post_processor.cpp:1169-1175
+template std::tuple<std::vector<std::string>, std::vector<int>, std::vector<size_t>> post_process_sw_dynamic<size_t>(
+    const std::vector<std::vector<size_t>> &, const std::vector<std::vector<float>> &, const std::string &, const std::vector<std::string> &, size_t, size_t, size_t, size_t);
+template std::tuple<std::vector<std::string>, std::vector<int>, std::vector<size_t>> post_process_sw_dynamic<long int>(
+    const std::vector<std::vector<long int>> &, const std::vector<std::vector<float>> &, const std::string &, const std::vector<std::string> &, size_t, size_t, size_t, size_t);
+template std::tuple<std::vector<std::string>, std::vector<int>, std::vector<size_t>> post_process_sw_static<size_t>(
+    const std::vector<std::vector<size_t>> &, const std::vector<std::vector<float>> &, const std::vector<std::string> &, const std::vector<std::string> &, size_t, size_t, size_t, size_t);
+template std::tuple<std::vector<std::string>, std::vector<int>, std::vector<size_t>> post_process_sw_static<long int>(
+    const std::vector<std::vector<long int>> &, const std::vector<std::vector<float>> &, const std::vector<std::string> &, const std::vector<std::string> &, size_t, size_t, size_t, size_t);
+
+void post_process_sw_flat(int mode, const std::string &genome, size_t ref_len, const std::vector<faiss::idx_t> &I, int64_t n, int64_t k_in,
+                          const std::vector<std::string> &query_seqs, size_t stride, size_t k, size_t k_clusters, std::vector<int> &scores,
+                          std::vector<size_t> &ids)
+{
+    if (k > k_clusters * 2 * stride) throw std::runtime_error("Final k too large. Ensure k < k_clusters * 2 * stride to have enough candidates.");
+    std::string qflat;
+    std::vector<int64_t> qoff;
+    flatten(query_seqs, qflat, qoff);
+    scores.assign((size_t)n * k, 0);
+    std::vector<uint64_t> u((size_t)n * k);
+    if (n && drm_sw_rerank(genome_ref(genome, ref_len), mode, I.data(), n, k_in, qflat.data(), qoff.data(), (int64_t)stride, (int64_t)k,
+                           (int64_t)k_clusters, scores.data(), u.data(), nullptr, nullptr) != DRM_OK)
+        throw_last();
+    ids.assign(u.begin(), u.end());
+}

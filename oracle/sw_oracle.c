@@ -131,18 +131,10 @@ void orc_partial_sort_desc(const int32_t *scores, int64_t n, int64_t k, int64_t 
 }
 
 /* ---- find_sequence (dynamic window fetch) ---- */
-static const unsigned char *orc_comp_table(void)
-{
-    static unsigned char table[256];
-    static int init = 0;
-    if (!init) {
-        /* parse_inputs.cpp:5-14: only A,T,C,G,N are mapped, every other byte complements to '\0'. */
-        memset(table, 0, sizeof table);
-        table['A'] = 'T'; table['T'] = 'A'; table['C'] = 'G'; table['G'] = 'C'; table['N'] = 'N';
-        init = 1;
-    }
-    return table;
-}
+/* parse_inputs.cpp:5-14: only A,T,C,G,N are mapped, every other byte complements to '\0'.  A constant table: the
+ * function is called from inside OpenMP loops, so nothing here may be initialised lazily. */
+static const unsigned char orc_comp[256] = {['A'] = 'T', ['T'] = 'A', ['C'] = 'G', ['G'] = 'C', ['N'] = 'N'};
+static const unsigned char *orc_comp_table(void) { return orc_comp; }
 
 /* Returns the window length written to out (ref_len, or 0 when the window overruns the genome). */
 int64_t orc_find_sequence(const char *genome, int64_t glen, uint64_t id, int64_t ref_len, char *out)
