@@ -49,6 +49,10 @@ def parse():
     ap.add_argument("--cache", default=os.environ.get("DRM_CACHE", os.path.join(tempfile.gettempdir(), "drm_b200_cache")))
     ap.add_argument("--cpu-sample", type=int, default=0, help="reads in the CPU baseline sample (0 = 600 per host core)")
     ap.add_argument("--skip-cpu", action="store_true")
+    ap.add_argument("--workload", default="dense", choices=["dense", "sharded"],
+                    help="dense = configs[1] (index replicated, reads sharded, no collective; the driver's run); "
+                         "sharded = configs[4] scaled down (index sharded by position, all-gather + merge)")
+    ap.add_argument("--chunk", type=int, default=262144, help="reads per exchange step of the sharded workload")
     return ap.parse_args()
 
 
@@ -269,7 +273,7 @@ def run_ours(args):
     assert int(dmin.item()) >= K, "rerank saw fewer than K candidates"
     cnt = dcnt.cpu().numpy() / args.steps
     cells = float(dcells.item()) / args.steps
-    launches_per_step = 1 + 2 * ((n + 131071) // 131072)
+    launches_per_step = 1 + 3 * ((n + 131071) // 131072)  # search; per 131072-read batch: profile SW kernel, N-read hand-back kernel, top-k select
 
     # ---------------- end-to-end arm: host buffers through drm_search_rerank
     hQ = torch.from_numpy(Q).pin_memory()
@@ -352,11 +356,13 @@ def run_ours(args):
     line["roofline_search"] = {"kernel": "hnswpq_search_kernel", "bound": "hbm", "achieved": ach, "peak": hbm_peak, "unit": "GB/s",
                                "frac": ach / hbm_peak, "traffic": None, "peak_source": peak_src,
                                "algorithmic_bytes_per_read": bytes_per_read, "ms_per_launch": search_ms}
-    int_peak = sms * 128 * sm_max * 1e6 * 2 / 5 / 1e9  # 5 int-ops per cell, 128 lanes/clk/SM, two cells per s16x2 op
+    # issue roofline of the recurrence: 3.5 math instructions per s16x2 cell PAIR (add, max3, clamp, half a best-max3)
+    # spread over the alu and fma pipes, each measured at 64 lanes/clk/SM (profiles/r1_ubench_pipes.txt) -> 2*64/3.5 pairs/clk/SM
+    int_peak = sms * (2 * 64 / 3.5) * 2 * sm_max * 1e6 / 1e9
     g = line["sw_gcups"]
-    line["roofline"] = {"kernel": "sw_rerank_kernel (dominant: %.0f%% of the step)" % (100 * sw_ms / (sw_ms + search_ms)), "bound": "int-alu",
+    line["roofline"] = {"kernel": "sw_rerank_profile_kernel (dominant: %.0f%% of the step)" % (100 * sw_ms / (sw_ms + search_ms)), "bound": "issue (alu + fma pipes; neither hbm nor tensor applies: DRAM traffic of this kernel is < 0.1 % of peak)",
                         "achieved": g, "peak": int_peak, "unit": "GCUPS", "frac": g / int_peak, "traffic": None,
-                        "peak_source": "SURVEY §8d integer roofline at clocks.max.sm (no tensor/HBM bound applies); see DESIGN.md for the measured per-instruction issue rates",
+                        "peak_source": "measured pipe rates (profiles/r1_ubench_pipes.txt, r1_ubench_alu.txt) x 3.5 instructions per cell pair at clocks.max.sm; DESIGN.md §4.3",
                         "cells_per_launch": cells, "ms_per_step": sw_ms}
     print(json.dumps(line), flush=True)
     if world > 1:
@@ -364,6 +370,117 @@ def run_ours(args):
     return 0
 
 
+def run_sharded(args):
+    """configs[4] scaled to what a CPU index build allows inside a bench run: the reference windows are split by position
+    into WORLD shards (one HNSW-PQ graph per GPU), every rank searches every read of a chunk against its shard, the
+    per-shard top-K lists are exchanged with ONE all-gather (NCCL over NVLink) and merged per read by the CUDA merge
+    kernel; the SW rerank of the merged candidates is read-sharded again (genome replicated).  Total work is fixed as
+    N grows ("strong")."""
+    import torch
+    import torch.distributed as dist
+
+    import deepreadmapper_b200 as drm
+    from deepreadmapper_b200 import sharded, synth
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    if world > 1:
+        import datetime
+        dist.init_process_group("nccl", timeout=datetime.timedelta(minutes=60), device_id=torch.device(f"cuda:{local}"))
+    barrier = (lambda: dist.barrier()) if world > 1 else (lambda: None)
+    genome = make_genome(args)
+    n_windows = 2 * (len(genome) - REF_LEN + 1)
+    lo, hi = sharded.shard_bounds(n_windows, world)[rank]
+    os.makedirs(args.cache, exist_ok=True)
+    path = os.path.join(args.cache, f"shard_g{args.genome_bases}_efc{args.efc}_w{world}_r{rank}.index")
+    if not os.path.exists(path):
+        t0 = time.time()
+        sub = genome[lo // 2: hi // 2 + REF_LEN - 1]
+        E = synth.embed_windows_torch(sub, f"cuda:{local}")
+        assert E.shape[0] == hi - lo, (E.shape, lo, hi)
+        drm.build_index(E, path + ".tmp", M_pq=8, nbits=8, M_hnsw=16, efc=args.efc, seed=1234 + rank, threads=max(1, (os.cpu_count() or 1) // world))
+        os.replace(path + ".tmp", path)
+        log(f"rank {rank}: shard [{lo}, {hi}) built in {time.time() - t0:.1f}s")
+    barrier()
+    ix = drm.Index(path, devices=[local])
+    ref = drm.Reference(genome=genome, ref_len=REF_LEN, devices=[local])
+    n = args.reads
+    reads, truth, Q = make_reads(genome, n, seed=7)  # the same batch on every rank
+    q_off = np.arange(n + 1, dtype=np.int64) * REF_LEN
+    dQ = torch.from_numpy(Q).cuda()
+    dreads = torch.from_numpy(reads.reshape(-1)).cuda()
+    doff = torch.from_numpy(q_off).cuda()
+    searcher = sharded.ShardedSearcher(ix, lo, local)
+    stream = torch.cuda.current_stream()
+    chunks = sharded.read_chunks(n, args.chunk)
+    my_rows = sum(sharded.read_slice(c1 - c0, rank, world)[1] - sharded.read_slice(c1 - c0, rank, world)[0] for c0, c1 in chunks)
+    dS = torch.empty((max(my_rows, 1), K), dtype=torch.int32, device="cuda")
+    dIds = torch.empty((max(my_rows, 1), K), dtype=torch.int64, device="cuda")
+    dmin = torch.full((1,), 2**31 - 1, dtype=torch.int32, device="cuda")
+    dcells = torch.zeros(1, dtype=torch.int64, device="cuda")
+    keep = {}
+
+    def step():
+        out = 0
+        for c0, c1 in chunks:
+            D, I = searcher.search_chunk(dQ[c0:c1], K, EF)
+            a, b = sharded.read_slice(c1 - c0, rank, world)
+            if b > a:
+                ref.rerank_device(1, I[a:b].data_ptr(), b - a, K, dreads.data_ptr(), doff[c0 + a:].data_ptr(), REF_LEN, 1, K, K,
+                                  dS[out:].data_ptr(), dIds[out:].data_ptr(), 0, dmin.data_ptr(), dcells.data_ptr(), stream.cuda_stream)
+                out += b - a
+            keep["first"] = (D, I) if c0 == 0 else keep.get("first")
+
+    for _ in range(args.warmup):
+        step()
+    torch.cuda.synchronize()
+    dcells.zero_()
+    barrier()
+    torch.cuda.synchronize()
+    sampler = ClockSampler(local) if rank == 0 else None
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(stream)
+    for _ in range(args.steps):
+        step()
+    e1.record(stream)
+    torch.cuda.synchronize()
+    barrier()
+    clocks = sampler.stop() if sampler else None
+    t = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device="cuda")
+    cells = dcells.to(torch.float64)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dist.all_reduce(cells, op=dist.ReduceOp.SUM)
+    assert int(dmin.item()) >= K
+    D0, I0 = keep["first"]
+    I0c = I0[:2048].cpu().numpy()
+    D0c = D0[:2048].cpu().numpy()
+    ok_sorted = bool((np.diff(D0c, axis=1) >= 0).all())
+    uniq = bool(all(len(set(r[r >= 0].tolist())) == int((r >= 0).sum()) for r in I0c))
+    top1 = float((I0c[:, 0] >> 1 == (truth[:2048] >> 1)).mean())
+    if rank == 0:
+        ms = float(t.item()) / args.steps
+        line = {"metric": METRIC, "value": n / (ms / 1e3), "unit": "reads/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+                "ms_per_step": ms, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32 ADC distances + s16x2 SW",
+                "data": "synthetic",
+                "config": {"workload": "configs[4] scaled down: reference windows sharded by position over the GPUs (one HNSW-PQ graph per GPU), "
+                                       "every read searched on every shard, per-shard top-K all-gathered (NCCL) and merged on the device, SW rerank read-sharded",
+                           "genome_bases": args.genome_bases, "n_vectors": n_windows, "shards": world, "EF": EF, "K": K, "EFC": args.efc,
+                           "reads_total": n, "chunk_reads": args.chunk,
+                           "all_gather_bytes_per_rank_per_chunk": int(min(args.chunk, n)) * K * 12},
+                "gpu_launches": int(args.steps * len(chunks) * (2 + 3 * ((args.chunk // world + 131071) // 131072))), "clocks": clocks,
+                "sw_gcups": float(cells.item()) / args.steps / (ms / 1e3) / 1e9,
+                "checks": {"merged_rows_sorted": ok_sorted, "merged_ids_unique": uniq, "merged_top1_is_planted_position": top1}}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
 if __name__ == "__main__":
     a = parse()
-    sys.exit(run_reference(a) if a.impl == "reference" else run_ours(a))
+    if a.impl == "reference":
+        sys.exit(run_reference(a))
+    sys.exit(run_sharded(a) if a.workload == "sharded" else run_ours(a))

@@ -314,7 +314,7 @@ def test_cli_hnswpq_index_then_pipeline_config1(drm, ob, fixtures, tmp_path):
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
     g = fixtures["genome"]
     open(tmp_path / "ref.fna", "w").write("> Fake DNA sequence\n" + "\n".join(g[i:i + 80] for i in range(0, len(g), 80)) + "\n")
-    np.save(tmp_path / "ref.fna.npy", synth.embed_windows(g))
+    np.save(tmp_path / "ref.fna.npy", synth.embed_windows(g.encode()))
     reads = [r.strip("<>") for r in fixtures["reads"][:64]]
     with open(tmp_path / "reads.fastq", "w") as f:
         for i, r in enumerate(reads):
@@ -350,3 +350,41 @@ def test_cli_hnswpq_index_then_pipeline_config1(drm, ob, fixtures, tmp_path):
     r = subprocess.run([os.path.join(root, "build/bin/test_search"), "idx1/idx1.index", "reads.fastq.npy", "64", "16"], cwd=tmp_path, capture_output=True, text=True)
     assert r.returncode == 0, r.stderr
     assert np.load(tmp_path / "indices.npy").dtype == np.dtype("<u4")
+
+
+def test_sharded_index_search_and_merge_vs_sharded_oracle(drm, ob, tmp_path):
+    """BASELINE.json configs[4] in miniature on one GPU: the windows are split by position into 3 shards (own graph, local
+    labels), every read is searched on every shard, labels are globalised and the per-shard lists merged by the CUDA
+    merge kernel.  Parity target = the oracle run the same sharded way + a (distance, id) merge."""
+    import torch
+    from deepreadmapper_b200 import sharded, synth
+    g = synth.random_genome(30000, 11)
+    n_windows = 2 * (len(g) - 149)
+    reads, truth = synth.simulate_reads(g, 400, seed=5)
+    Q = synth.embed_reads(reads)
+    k, ef, world = 32, 64, 3
+    dQ = torch.from_numpy(Q).cuda()
+    Ds, Is, Do, Io = [], [], [], []
+    for rank, (lo, hi) in enumerate(sharded.shard_bounds(n_windows, world)):
+        path = str(tmp_path / f"shard{rank}.index")
+        E = synth.embed_windows(g[lo // 2: hi // 2 + 149])
+        assert E.shape[0] == hi - lo
+        drm.build_index(E, path, efc=64, seed=20 + rank)
+        ix = drm.Index(path)
+        s = sharded.ShardedSearcher(ix, lo, 0)
+        D, I = s.search_chunk(dQ, k, ef)  # world size 1 here: local search + globalised labels
+        ix.close()
+        Ds.append(D)
+        Is.append(I)
+        D0, I0, _ = ob.OracleIndex(path).search(Q, k, ef, tie_rule=1)
+        Do.append(D0)
+        Io.append(np.where(I0 >= 0, I0 + lo, -1))
+        assert np.array_equal(I.cpu().numpy(), Io[-1]) and np.array_equal(D.cpu().numpy().view(np.uint32), D0.view(np.uint32))
+    Dm, Im = sharded.merge_topk(torch.stack(Ds), torch.stack(Is))
+    torch.cuda.synchronize()
+    Da, Ia = np.stack(Do), np.stack(Io)
+    for r in range(len(Q)):
+        d, i = Da[:, r].reshape(-1), Ia[:, r].reshape(-1)
+        o = np.lexsort((i.astype(np.uint64), d))[:k]
+        assert np.array_equal(Dm[r].cpu().numpy(), d[o]) and np.array_equal(Im[r].cpu().numpy(), i[o]), r
+    assert float(np.mean(np.any((Im.cpu().numpy() >> 1) == (truth[:, None] >> 1), axis=1))) > 0.5  # planted window is found
