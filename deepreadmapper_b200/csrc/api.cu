@@ -6,10 +6,28 @@
 #include <algorithm>
 #include <cstring>
 #include <chrono>
+#include <memory>
+#include <mutex>
 #include <thread>
+
+// Per-replica workspace of drm_search_rerank, kept in the index handle so that repeated calls reuse their streams,
+// device buffers and pinned offset staging instead of paying cudaMalloc / cudaFree on every call.
+struct StageSlot {
+    cudaStream_t s = nullptr;
+    void *q = nullptr, *D = nullptr, *I = nullptr, *qs = nullptr, *qo = nullptr, *sc = nullptr, *id = nullptr;
+    int64_t *off = nullptr;  // pinned host: chunk-relative read offsets
+};
+struct StageWorkspace {
+    static constexpr int NSLOT = 3;
+    StageSlot slot[NSLOT];
+    void *cnt = nullptr, *dmin = nullptr;
+    size_t cap_q = 0, cap_D = 0, cap_I = 0, cap_qs = 0, cap_qo = 0, cap_sc = 0, cap_id = 0;
+    std::mutex mu;
+};
 
 struct drm_index {
     std::vector<drm::DeviceIndex> rep;
+    std::vector<std::unique_ptr<StageWorkspace>> ws;  // one per replica, created on first use
     int64_t info[12];
 };
 
@@ -27,6 +45,39 @@ struct DevBuf {  // RAII device allocation on the current device
     int alloc(size_t bytes) { DRM_CUDA_TRY(cudaMalloc(&p, bytes ? bytes : 16)); return DRM_OK; }
     template <class T> T *as() { return static_cast<T *>(p); }
 };
+
+int grow(void **p, size_t *cap, size_t bytes)
+{
+    if (*p && *cap >= bytes) return DRM_OK;
+    if (*p) cudaFree(*p);
+    *p = nullptr; *cap = 0;
+    DRM_CUDA_TRY(cudaMalloc(p, bytes ? bytes : 16));
+    *cap = bytes;
+    return DRM_OK;
+}
+
+void free_workspace(StageWorkspace &w)
+{
+    for (auto &s : w.slot) {
+        if (s.s) cudaStreamDestroy(s.s);
+        cudaFree(s.q); cudaFree(s.D); cudaFree(s.I); cudaFree(s.qs); cudaFree(s.qo); cudaFree(s.sc); cudaFree(s.id);
+        if (s.off) cudaFreeHost(s.off);
+        s = StageSlot();
+    }
+    cudaFree(w.cnt); cudaFree(w.dmin);
+    w.cnt = w.dmin = nullptr;
+}
+
+// Keep the stream-ordered allocator's memory across synchronisations (the rerank launcher takes its scratch from it).
+void keep_pool_memory(int device)
+{
+    cudaMemPool_t mp;
+    if (cudaDeviceGetDefaultMemPool(&mp, device) == cudaSuccess) {
+        unsigned long long thr = ~0ull;
+        cudaMemPoolSetAttribute(mp, cudaMemPoolAttrReleaseThreshold, &thr);
+    }
+    cudaGetLastError();
+}
 
 struct Timer {
     cudaEvent_t a = nullptr, b = nullptr;
@@ -85,7 +136,9 @@ int open_ref(const char *bytes, int64_t len_bytes, int64_t len, int form, int re
         cudaError_t e = cudaSetDevice(dr.device);
         int *flag = nullptr;
         if (e == cudaSuccess) e = cudaMalloc(&dr.raw, len_bytes ? len_bytes : 16);
-        if (e == cudaSuccess) e = cudaMalloc(&dr.data, len_bytes ? len_bytes : 16);
+        if (e == cudaSuccess) e = cudaMalloc(&dr.data_alloc, (size_t)len_bytes + 2 * REF_PAD);
+        if (e == cudaSuccess) e = cudaMemset(dr.data_alloc, 4, (size_t)len_bytes + 2 * REF_PAD);
+        if (e == cudaSuccess) dr.data = dr.data_alloc + REF_PAD;
         if (e == cudaSuccess) e = cudaMalloc(&flag, sizeof(int));
         if (e == cudaSuccess) e = cudaMemset(flag, 0, sizeof(int));
         if (e == cudaSuccess && len_bytes) e = cudaMemcpy(dr.raw, bytes, (size_t)len_bytes, cudaMemcpyHostToDevice);
@@ -135,6 +188,8 @@ int drm_index_open(const char *index_file, const int *devices, int n_dev, drm_in
         rc = build_device_index(h, devices[i], dx);
         if (rc != DRM_OK) { drm_index_close(ix); return rc; }
         ix->rep.push_back(dx);
+        ix->ws.emplace_back(new StageWorkspace());
+        keep_pool_memory(devices[i]);
     }
     int64_t info[12] = {h.d, h.ntotal, (int64_t)h.M, (int64_t)h.nbits, h.M_hnsw(), h.entry_point, h.max_level,
                         h.efConstruction, h.efSearch, (int64_t)h.neighbors.size(), n_dev, (int64_t)ix->rep[0].bytes};
@@ -146,7 +201,11 @@ int drm_index_open(const char *index_file, const int *devices, int n_dev, drm_in
 void drm_index_close(drm_index *ix)
 {
     if (!ix) return;
-    for (auto &dx : ix->rep) free_device_index(dx);
+    for (size_t i = 0; i < ix->rep.size(); ++i) {
+        if (ix->rep[i].device >= 0) cudaSetDevice(ix->rep[i].device);
+        if (i < ix->ws.size() && ix->ws[i]) free_workspace(*ix->ws[i]);
+        free_device_index(ix->rep[i]);
+    }
     delete ix;
 }
 
@@ -219,7 +278,7 @@ void drm_ref_close(drm_ref *r)
     if (!r) return;
     for (auto &dr : r->rep) {
         if (dr.device >= 0) cudaSetDevice(dr.device);
-        cudaFree(dr.data); cudaFree(dr.raw);
+        cudaFree(dr.data_alloc); cudaFree(dr.raw);
     }
     delete r;
 }
@@ -344,7 +403,10 @@ int drm_search_rerank(drm_index *ix, drm_ref *ref, int mode, const float *q, int
     if (d != ix->rep[0].d) return fail(DRM_EINVAL, "query dimension does not match index dimension");
     if (ix->rep.size() != ref->rep.size()) return fail(DRM_EINVAL, "index and reference must be opened on the same devices");
     const int R = (int)ix->rep.size();
-    constexpr int64_t CH = 32768;
+    // Reads per pipeline chunk.  Small enough that the first upload / last download (not overlapped) are a few per cent
+    // of the call, large enough that the persistent search grid (3552 warps) sees >= 9 queries per warp.
+    int64_t CH = 32768;
+    if (const char *e = getenv("DRM_CHUNK")) { long long v = atoll(e); if (v >= 1024 && v <= (1 << 22)) CH = v; }
     std::vector<int> rcs((size_t)R, DRM_OK), mins((size_t)R, 0x7fffffff);
     std::vector<std::string> errs((size_t)R);
     std::vector<drm_search_stats> st((size_t)R);
@@ -359,6 +421,8 @@ int drm_search_rerank(drm_index *ix, drm_ref *ref, int mode, const float *q, int
             const DeviceRef &dr = ref->rep[(size_t)g];
             if (dx.device != dr.device) return fail(DRM_EINVAL, "index and reference replicas are on different devices");
             DRM_CUDA_TRY(cudaSetDevice(dx.device));
+            StageWorkspace &w = *ix->ws[(size_t)g];
+            std::lock_guard<std::mutex> lock(w.mu);
             int64_t max_qbytes = 0;
             int max_qlen = 0;
             for (int64_t c0 = r0; c0 < r1; c0 += CH) {
@@ -366,53 +430,69 @@ int drm_search_rerank(drm_index *ix, drm_ref *ref, int mode, const float *q, int
                 max_qbytes = std::max(max_qbytes, q_off[c1] - q_off[c0]);
             }
             for (int64_t i = r0; i < r1; ++i) max_qlen = std::max<int64_t>(max_qlen, q_off[i + 1] - q_off[i]);
-            struct Slot { cudaStream_t s = nullptr; DevBuf q, D, I, qs, qo, sc, id; std::vector<int64_t> off; } slot[2];
-            DevBuf cnt, dmin;
+            const int64_t chn = std::min<int64_t>(CH, r1 - r0);
             int rc;
-            if ((rc = cnt.alloc(4 * sizeof(int64_t))) || (rc = dmin.alloc(4))) return rc;
-            for (auto &s : slot) {
-                DRM_CUDA_TRY(cudaStreamCreateWithFlags(&s.s, cudaStreamNonBlocking));
-                if ((rc = s.q.alloc((size_t)CH * d * 4)) || (rc = s.D.alloc((size_t)CH * k_search * 4)) || (rc = s.I.alloc((size_t)CH * k_search * 8)) ||
-                    (rc = s.qs.alloc((size_t)max_qbytes)) || (rc = s.qo.alloc((size_t)(CH + 1) * 8)) ||
-                    (rc = s.sc.alloc((size_t)CH * k * 4)) || (rc = s.id.alloc((size_t)CH * k * 8))) return rc;
-                s.off.resize((size_t)CH + 1);
+            if (!w.cnt) DRM_CUDA_TRY(cudaMalloc(&w.cnt, 4 * sizeof(int64_t)));
+            if (!w.dmin) DRM_CUDA_TRY(cudaMalloc(&w.dmin, 16));
+            const bool regrow_off = w.cap_qo < (size_t)(chn + 1) * 8;
+            for (auto &s : w.slot) {
+                if (!s.s) DRM_CUDA_TRY(cudaStreamCreateWithFlags(&s.s, cudaStreamNonBlocking));
+                size_t cq = w.cap_q, cD = w.cap_D, cI = w.cap_I, cqs = w.cap_qs, cqo = w.cap_qo, csc = w.cap_sc, cid = w.cap_id;
+                if ((rc = grow(&s.q, &cq, (size_t)chn * d * 4)) || (rc = grow(&s.D, &cD, (size_t)chn * k_search * 4)) ||
+                    (rc = grow(&s.I, &cI, (size_t)chn * k_search * 8)) || (rc = grow(&s.qs, &cqs, (size_t)max_qbytes)) ||
+                    (rc = grow(&s.qo, &cqo, (size_t)(chn + 1) * 8)) || (rc = grow(&s.sc, &csc, (size_t)chn * k * 4)) ||
+                    (rc = grow(&s.id, &cid, (size_t)chn * k * 8))) return rc;
+                if (regrow_off || !s.off) {
+                    if (s.off) cudaFreeHost(s.off);
+                    s.off = nullptr;
+                    DRM_CUDA_TRY(cudaHostAlloc(&s.off, (size_t)(chn + 1) * 8, cudaHostAllocDefault));
+                }
+                if (&s == &w.slot[StageWorkspace::NSLOT - 1]) {
+                    w.cap_q = cq; w.cap_D = cD; w.cap_I = cI; w.cap_qs = cqs; w.cap_qo = cqo; w.cap_sc = csc; w.cap_id = cid;
+                }
             }
+            cudaStream_t s0 = w.slot[0].s;
             int big = 0x7fffffff;
-            DRM_CUDA_TRY(cudaMemset(cnt.p, 0, 4 * sizeof(int64_t)));
-            DRM_CUDA_TRY(cudaMemcpy(dmin.p, &big, 4, cudaMemcpyHostToDevice));
+            DRM_CUDA_TRY(cudaMemsetAsync(w.cnt, 0, 4 * sizeof(int64_t), s0));
+            DRM_CUDA_TRY(cudaMemcpyAsync(w.dmin, &big, 4, cudaMemcpyHostToDevice, s0));
+            DRM_CUDA_TRY(cudaStreamSynchronize(s0));
             Timer span_t;
-            span_t.start(slot[0].s);
+            span_t.start(s0);
             int which = 0;
-            for (int64_t c0 = r0; c0 < r1; c0 += CH, which ^= 1) {
-                Slot &s = slot[which];
+            for (int64_t c0 = r0; c0 < r1; c0 += CH, which = (which + 1) % StageWorkspace::NSLOT) {
+                StageSlot &s = w.slot[which];
                 const int64_t m = std::min(r1, c0 + CH) - c0;
                 DRM_CUDA_TRY(cudaStreamSynchronize(s.s));  // the slot's previous chunk (and its host offsets) are done
                 const int64_t qb = q_off[c0];
-                for (int64_t i = 0; i <= m; ++i) s.off[(size_t)i] = q_off[c0 + i] - qb;
-                cudaMemcpyAsync(s.q.p, q + c0 * d, (size_t)m * d * 4, cudaMemcpyHostToDevice, s.s);
-                cudaMemcpyAsync(s.qs.p, q_flat + qb, (size_t)(q_off[c0 + m] - qb), cudaMemcpyHostToDevice, s.s);
-                cudaMemcpyAsync(s.qo.p, s.off.data(), (size_t)(m + 1) * 8, cudaMemcpyHostToDevice, s.s);
-                rc = launch_search(dx, s.q.as<float>(), m, k_search, ef, s.D.as<float>(), s.I.as<int64_t>(), cnt.as<int64_t>(), s.s);
+                for (int64_t i = 0; i <= m; ++i) s.off[i] = q_off[c0 + i] - qb;
+                cudaMemcpyAsync(s.q, q + c0 * d, (size_t)m * d * 4, cudaMemcpyHostToDevice, s.s);
+                cudaMemcpyAsync(s.qs, q_flat + qb, (size_t)(q_off[c0 + m] - qb), cudaMemcpyHostToDevice, s.s);
+                cudaMemcpyAsync(s.qo, s.off, (size_t)(m + 1) * 8, cudaMemcpyHostToDevice, s.s);
+                rc = launch_search(dx, static_cast<float *>(s.q), m, k_search, ef, static_cast<float *>(s.D), static_cast<int64_t *>(s.I),
+                                   static_cast<int64_t *>(w.cnt), s.s);
                 if (rc != DRM_OK) return rc;
-                RerankArgs a{mode, s.I.as<int64_t>(), m, k_search, s.qs.as<char>(), s.qo.as<int64_t>(), max_qlen, stride, k, k_clusters,
-                             s.sc.as<int32_t>(), s.id.as<uint64_t>(), nullptr, dmin.as<int32_t>(), nullptr};
+                RerankArgs a{mode, static_cast<int64_t *>(s.I), m, k_search, static_cast<char *>(s.qs), static_cast<int64_t *>(s.qo), max_qlen,
+                             stride, k, k_clusters, static_cast<int32_t *>(s.sc), static_cast<uint64_t *>(s.id), nullptr,
+                             static_cast<int32_t *>(w.dmin), nullptr};
                 rc = launch_rerank(dr, a, s.s);
                 if (rc != DRM_OK) return rc;
-                if (D) cudaMemcpyAsync(D + c0 * k_search, s.D.p, (size_t)m * k_search * 4, cudaMemcpyDeviceToHost, s.s);
-                if (I) cudaMemcpyAsync(I + c0 * k_search, s.I.p, (size_t)m * k_search * 8, cudaMemcpyDeviceToHost, s.s);
-                if (sw_scores) cudaMemcpyAsync(sw_scores + c0 * k, s.sc.p, (size_t)m * k * 4, cudaMemcpyDeviceToHost, s.s);
-                if (sw_ids) cudaMemcpyAsync(sw_ids + c0 * k, s.id.p, (size_t)m * k * 8, cudaMemcpyDeviceToHost, s.s);
+                if (D) cudaMemcpyAsync(D + c0 * k_search, s.D, (size_t)m * k_search * 4, cudaMemcpyDeviceToHost, s.s);
+                if (I) cudaMemcpyAsync(I + c0 * k_search, s.I, (size_t)m * k_search * 8, cudaMemcpyDeviceToHost, s.s);
+                if (sw_scores) cudaMemcpyAsync(sw_scores + c0 * k, s.sc, (size_t)m * k * 4, cudaMemcpyDeviceToHost, s.s);
+                if (sw_ids) cudaMemcpyAsync(sw_ids + c0 * k, s.id, (size_t)m * k * 8, cudaMemcpyDeviceToHost, s.s);
             }
-            cudaError_t e = cudaStreamSynchronize(slot[0].s);
-            if (e == cudaSuccess) e = cudaStreamSynchronize(slot[1].s);
-            span_t.stop(slot[0].s);
+            cudaError_t e = cudaSuccess;
+            for (int i = StageWorkspace::NSLOT - 1; i >= 0; --i) {
+                cudaError_t ei = cudaStreamSynchronize(w.slot[i].s);
+                if (e == cudaSuccess) e = ei;
+            }
+            span_t.stop(s0);
             if (e != cudaSuccess) return fail(DRM_ECUDA, std::string("search_rerank: ") + cudaGetErrorString(e));
             span[(size_t)g] = span_t.ms();
             int64_t c[4];
-            DRM_CUDA_TRY(cudaMemcpy(c, cnt.p, sizeof c, cudaMemcpyDeviceToHost));
-            DRM_CUDA_TRY(cudaMemcpy(&mins[(size_t)g], dmin.p, 4, cudaMemcpyDeviceToHost));
+            DRM_CUDA_TRY(cudaMemcpy(c, w.cnt, sizeof c, cudaMemcpyDeviceToHost));
+            DRM_CUDA_TRY(cudaMemcpy(&mins[(size_t)g], w.dmin, 4, cudaMemcpyDeviceToHost));
             st[(size_t)g].nhops0 = c[0]; st[(size_t)g].nhops_up = c[1]; st[(size_t)g].ndis_eval = c[2];
-            for (auto &s : slot) cudaStreamDestroy(s.s);
             return DRM_OK;
         };
         rcs[(size_t)g] = body();

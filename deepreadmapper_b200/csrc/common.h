@@ -88,9 +88,13 @@ struct DeviceRef {
     int ref_len = 0;
     int64_t len = 0;         // genome bases, or number of windows
     uint8_t *data = nullptr; // base classes 0..4 (A,C,G,T,N), 7 = any other byte (table form keeps raw too)
+    uint8_t *data_alloc = nullptr; // the allocation behind `data`: REF_PAD bytes of class 4 either side, so the rerank kernel's
+                                   // aligned word reads around a window never leave it
     uint8_t *raw = nullptr;  // raw bytes (only kept when has_other: the generic byte-equality path)
     bool has_other = false;  // some byte outside ACGTN -> generic kernel
 };
+
+constexpr int REF_PAD = 32;
 
 struct RerankArgs {
     int mode;  // 0 static bound rule, 1 dynamic

@@ -359,8 +359,9 @@ __device__ __forceinline__ void build_lut_t(float *T, const float *__restrict__ 
     }
 }
 
-template <int CS, int NS>
-__global__ void __launch_bounds__(WARPS_PER_CTA * 32) hnswpq_search_reg_kernel(const SearchParams p)
+// FULLCAP: cap == 32 * NS (the pool fills the registers exactly: no tail to keep at POOL_INF, the maximum is lane 31's last slot).
+template <int CS, int NS, bool FULLCAP>
+__global__ void __launch_bounds__(WARPS_PER_CTA * 32, 6) hnswpq_search_reg_kernel(const SearchParams p)
 {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -463,31 +464,36 @@ __global__ void __launch_bounds__(WARPS_PER_CTA * 32) hnswpq_search_reg_kernel(c
                 mask &= mask - 1;
                 const u64 kin = __shfl_sync(FULL, key, src);
                 if (kin >= maxkey) continue;
-                int cnt = 0;
+                // Sorted insert without a rank computation.  kin has flag 0 and pool keys are (even base | flag), so
+                // `k[s] < kin` already ignores the flag; the pool is sorted, so lt[] is a prefix of the positions and
+                //   new[i] = lt[i] ? old[i] : (lt[i-1] ? kin : old[i-1])
+                // with position i-1 living in the previous lane for slot 0 (one 64-bit shuffle).
+                const u64 kin1 = kin | 1ull;
+                bool lt[NS];
                 bool dup = false;
 #pragma unroll
                 for (int s = 0; s < NS; ++s) {
-                    const u64 ks = k[s] & ~1ull;
-                    cnt += ks < kin;
-                    dup = dup || ks == kin;
+                    lt[s] = k[s] < kin;
+                    dup = dup || (k[s] | 1ull) == kin1;
                 }
                 if (__any_sync(FULL, dup)) continue;  // already in the pool (or the same id twice in one row)
-                const int pos = (int)__reduce_add_sync(FULL, (unsigned)cnt);
-                const u64 prevlast = __shfl_up_sync(FULL, k[NS - 1], 1);
+                const u64 pk = __shfl_up_sync(FULL, k[NS - 1], 1);
+                const bool plt = lane == 0 || pk < kin;
 #pragma unroll
-                for (int s = NS - 1; s >= 1; --s)
-                    if (base + s > pos) k[s] = k[s - 1];
-                if (base > pos) k[0] = prevlast;
+                for (int s = NS - 1; s >= 1; --s) k[s] = lt[s] ? k[s] : (lt[s - 1] ? kin : k[s - 1]);
+                k[0] = lt[0] ? k[0] : (plt ? kin : pk);
+                if (FULLCAP) {
+                    maxkey = __shfl_sync(FULL, k[NS - 1], 31) & ~1ull;
+                } else {
 #pragma unroll
-                for (int s = 0; s < NS; ++s) {
-                    if (base + s == pos) k[s] = kin;
-                    if (base + s >= cap) k[s] = POOL_INF;
+                    for (int s = 0; s < NS; ++s)
+                        if (base + s >= cap) k[s] = POOL_INF;
+                    u64 lastk = k[0];
+#pragma unroll
+                    for (int s = 1; s < NS; ++s)
+                        if (s == max_slot) lastk = k[s];
+                    maxkey = __shfl_sync(FULL, lastk, max_lane) & ~1ull;
                 }
-                u64 lastk = k[0];
-#pragma unroll
-                for (int s = 1; s < NS; ++s)
-                    if (s == max_slot) lastk = k[s];
-                maxkey = __shfl_sync(FULL, lastk, max_lane) & ~1ull;
             }
         }
 
@@ -513,10 +519,10 @@ __global__ void __launch_bounds__(WARPS_PER_CTA * 32) hnswpq_search_reg_kernel(c
     }
 }
 
-template <int CS, int NS>
-int launch_reg_t(const SearchParams &p, size_t smem, int device, cudaStream_t stream)
+template <int CS, int NS, bool FULLCAP>
+int launch_reg_tf(const SearchParams &p, size_t smem, int device, cudaStream_t stream)
 {
-    auto kern = hnswpq_search_reg_kernel<CS, NS>;
+    auto kern = hnswpq_search_reg_kernel<CS, NS, FULLCAP>;
     DRM_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int per_sm = 0, sms = 0;
     DRM_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, WARPS_PER_CTA * 32, smem));
@@ -528,6 +534,12 @@ int launch_reg_t(const SearchParams &p, size_t smem, int device, cudaStream_t st
     kern<<<(unsigned)grid, WARPS_PER_CTA * 32, smem, stream>>>(p);
     DRM_CUDA_TRY(cudaGetLastError());
     return DRM_OK;
+}
+
+template <int CS, int NS>
+int launch_reg_t(const SearchParams &p, size_t smem, int device, cudaStream_t stream)
+{
+    return p.cap == 32 * NS ? launch_reg_tf<CS, NS, true>(p, smem, device, stream) : launch_reg_tf<CS, NS, false>(p, smem, device, stream);
 }
 
 template <int CS, int NPL>

@@ -254,14 +254,14 @@ __global__ void __launch_bounds__(RERANK_THREADS, 2) sw_rerank_kernel(const Rera
 // per-read QUERY PROFILE in shared memory instead of a PRMT per cell pair, which moves the lookup off the
 // ALU pipe (PRMT issues at half the VIMNMX rate on sm_100a, tools/ubench_alu.cu) onto the LSU:
 //   tab[ab][g][slot] : uint4 = the four packed terms (0 / 2 per 16-bit half) of query columns
-//                      40*(slot&3) + 4g .. +3 against the window-base pair ab = 5a + b (a, b in A,C,G,T,none)
+//                      38*(slot&3) + 4g .. +3 against the window-base pair ab = 5a + b (a, b in A,C,G,T,none)
 // One LDS.128 feeds four cell pairs.  `slot` = lane & 7 replicates the table for the two quads of a
 // quarter-warp, so the eight 16-byte addresses of every LDS.128 wavefront fall in eight different bank
 // groups whatever base pairs the lanes are looking up: conflict-free by construction.
 // Used when neither the read nor (effectively) the windows contain N: a window N can only match a read N.
-constexpr int PCPL = 40;             // query columns per lane (10 groups of 4)
-constexpr int PGROUPS = PCPL / 4;
-constexpr int PQCOLS = 4 * PCPL;     // 160 >= 152
+constexpr int PCPL = 38;             // query columns per lane: 4 x 38 = 152 = 150 + the '<' '>' decoration of format_fastq
+constexpr int PGROUPS = (PCPL + 3) / 4;  // 10 table groups of 4 columns; the last one is half used
+constexpr int PQCOLS = 4 * PGROUPS * 4;  // 160: s_qcls is indexed up to 38 * 3 + 39
 constexpr int PTAB_ENTRIES = 25 * PGROUPS * 8;
 
 // The recurrence runs on s16x2 integers whose values stay below 2048.  Such an integer k has the same bit pattern as the
@@ -292,11 +292,14 @@ __device__ __forceinline__ unsigned sw_quad_profile(const uint8_t *rowA, const u
         unsigned diag = prev_recv, left = recv, mprev = 0;
 #pragma unroll
         for (int g = 0; g < PGROUPS; ++g) {
-            const uint4 pr = prow[g * 8];
+            uint4 pr;
+            if (4 * g + 2 < PCPL) pr = prow[g * 8];
+            else { const uint2 h2 = *reinterpret_cast<const uint2 *>(prow + g * 8); pr = make_uint4(h2.x, h2.y, 0u, 0u); }
             const unsigned s4[4] = {pr.x, pr.y, pr.z, pr.w};
 #pragma unroll
             for (int c = 0; c < 4; ++c) {
                 const int j = 4 * g + c;
+                if (j >= PCPL) continue;
                 const unsigned up = H[j];
                 unsigned x, h;
                 if (ALU_EVERY == 1) x = s4[c] * one + diag;
@@ -393,18 +396,48 @@ __device__ __forceinline__ unsigned sw_quad_profile2(const uint8_t *rowA, const 
     return best;
 }
 
-// Dynamic shared memory layout (bytes): tab | sel[2 * PAIRS_PER_PASS][selw] (one byte row per candidate) | cand[C] | first[take] | count[take+1]
-template <int RPI, int ALU_EVERY>
-__global__ void __launch_bounds__(RERANK_THREADS, 2) sw_rerank_profile_kernel(const RerankDev p, int selw, unsigned one, int *fb_list, int *fb_n)
+// Block-wide exclusive scan of s_count[0 .. n) in place (n <= MAXTAKE), total returned to every thread.  THREADS / 32 <= 32.
+template <int THREADS> __device__ __forceinline__ int block_exclusive_scan(int *s_count, int n, int *s_warp, int tid)
 {
+    const int per = (n + THREADS - 1) / THREADS, b0 = tid * per;
+    int sum = 0;
+    for (int i = b0; i < min(b0 + per, n); ++i) sum += s_count[i];
+    int inc = sum;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const int v = __shfl_up_sync(FULL, inc, o);
+        if ((tid & 31) >= o) inc += v;
+    }
+    if ((tid & 31) == 31) s_warp[tid >> 5] = inc;
+    __syncthreads();
+    int base = 0, total = 0;
+#pragma unroll
+    for (int w = 0; w < THREADS / 32; ++w) {
+        const int v = s_warp[w];
+        if (w < (tid >> 5)) base += v;
+        total += v;
+    }
+    int acc = base + inc - sum;
+    for (int i = b0; i < min(b0 + per, n); ++i) { const int c = s_count[i]; s_count[i] = acc; acc += c; }
+    if (tid == THREADS - 1) s_count[n] = total;
+    return total;
+}
+
+// Dynamic shared memory layout (bytes): tab | sel[2 * PAIRS][selw] (one byte row per candidate) | cand[C] | first[take] | count[take+1]
+// THREADS = 256 (2 CTAs / SM, 128 candidates per pass) or 128 (4 CTAs / SM, 64 per pass).
+template <int RPI, int ALU_EVERY, int THREADS>
+__global__ void __launch_bounds__(THREADS, 512 / THREADS) sw_rerank_profile_kernel(const RerankDev p, int selw, unsigned one, int *fb_list, int *fb_n)
+{
+    constexpr int PAIRS = THREADS / 4;
     extern __shared__ __align__(16) unsigned char dsm[];
     uint4 *tab = reinterpret_cast<uint4 *>(dsm);
     uint8_t *s_sel = dsm + PTAB_ENTRIES * sizeof(uint4);
-    u64 *s_cand = reinterpret_cast<u64 *>(s_sel + (size_t)2 * PAIRS_PER_PASS * selw);
+    u64 *s_cand = reinterpret_cast<u64 *>(s_sel + (size_t)2 * PAIRS * selw);
     u64 *s_first = s_cand + p.C;
     int *s_count = reinterpret_cast<int *>(s_first + p.take);
     __shared__ unsigned char s_qcls[PQCOLS];
-    __shared__ int s_nc, s_hasN;
+    __shared__ int s_warp[THREADS / 32];
+    __shared__ int s_hasN;
 
     const int tid = threadIdx.x, lane = tid & 31;
     const long long r = blockIdx.x;
@@ -414,7 +447,7 @@ __global__ void __launch_bounds__(RERANK_THREADS, 2) sw_rerank_profile_kernel(co
 
     if (tid == 0) s_hasN = 0;
     __syncthreads();
-    for (int j = tid; j < PQCOLS; j += RERANK_THREADS) {
+    for (int j = tid; j < PQCOLS; j += THREADS) {
         int c = 5;  // beyond the read, or a byte outside ACGT: matches nothing
         if (j < lq) {
             c = base_class((unsigned char)p.q_flat[qb + j]);
@@ -423,7 +456,7 @@ __global__ void __launch_bounds__(RERANK_THREADS, 2) sw_rerank_profile_kernel(co
         s_qcls[j] = (unsigned char)c;
     }
     const long long *nb = p.neighbors + r * p.k_in;
-    for (int i = tid; i < p.take; i += RERANK_THREADS) {
+    for (int i = tid; i < p.take; i += THREADS) {
         u64 first; int count;
         expand_one(p.rule, (u64)nb[i], first, count);
         s_first[i] = first;
@@ -434,14 +467,9 @@ __global__ void __launch_bounds__(RERANK_THREADS, 2) sw_rerank_profile_kernel(co
         if (tid == 0) fb_list[atomicAdd(fb_n, 1)] = (int)r;
         return;
     }
-    if (tid == 0) {
-        int acc = 0;
-        for (int i = 0; i < p.take; ++i) { int c = s_count[i]; s_count[i] = acc; acc += c; }
-        s_count[p.take] = acc;
-        s_nc = acc;
-    }
+    const int nc = block_exclusive_scan<THREADS>(s_count, p.take, s_warp, tid);  // host guarantees take * per <= MAXC
     // query profile
-    for (int e = tid; e < PTAB_ENTRIES; e += RERANK_THREADS) {
+    for (int e = tid; e < PTAB_ENTRIES; e += THREADS) {
         const int slot = e & 7, g = (e >> 3) % PGROUPS, ab = (e >> 3) / PGROUPS;
         const int a = ab / 5, b = ab % 5, col = PCPL * (slot & 3) + 4 * g;
         unsigned w[4];
@@ -453,8 +481,7 @@ __global__ void __launch_bounds__(RERANK_THREADS, 2) sw_rerank_profile_kernel(co
         tab[e] = make_uint4(w[0], w[1], w[2], w[3]);
     }
     __syncthreads();
-    const int nc = s_nc;
-    for (int i = tid; i < p.take; i += RERANK_THREADS) {
+    for (int i = tid; i < p.take; i += THREADS) {
         int b = s_count[i], e = s_count[i + 1];
         u64 f = s_first[i];
         for (int c = b; c < e; ++c) s_cand[c] = f + (u64)(c - b);
@@ -467,33 +494,47 @@ __global__ void __launch_bounds__(RERANK_THREADS, 2) sw_rerank_profile_kernel(co
     __syncthreads();
 
     const int pair = tid >> 2;
-    for (int c0 = 0; c0 < nc; c0 += 2 * PAIRS_PER_PASS) {
-        const int npairs = min(PAIRS_PER_PASS, (nc - c0 + 1) / 2);
+    const int wpr = selw >> 2;  // 32-bit words per staged row
+    for (int c0 = 0; c0 < nc; c0 += 2 * PAIRS) {
+        const int npairs = min(PAIRS, (nc - c0 + 1) / 2);
         constexpr int PAD = 3 * RPI;             // "none" rows either side: pipeline fill and drain of the quad
-        const int srows = rows + 2 * PAD + RPI;  // (+ RPI: the odd last row of a two-row iteration)
-        // Stage the windows of this pass: one warp per candidate, lanes along the window, so a window is a few coalesced
-        // 32-byte reads of the class array (backwards for a reverse-complement id); the loads of different candidates are
-        // independent and batch up.  s_sel[c][r + PAD] = class of row r (0..3), 4 = matches nothing.
+        // Stage the windows of this pass, four rows per thread-task: s_sel[c][r + PAD] = class of row r (0..3), 4 = matches
+        // nothing (outside the window, N, or an id whose window overruns the reference).  A task reads the two aligned words
+        // that cover its four source bases (the class array carries 16 bytes of padding either side), funnel-shifts them
+        // into place, and for a reverse-complement id reverses the bytes and complements them (c ^ 3).
         {
-            const int warp = tid >> 5, ncand = 2 * npairs;
+            const int ntask = 2 * npairs * wpr;
+            int c = tid / wpr, w = tid - c * wpr;
+            const int dc = THREADS / wpr, dw = THREADS - dc * wpr;
 #pragma unroll 2
-            for (int c = warp; c < ncand; c += RERANK_THREADS / 32) {
+            for (int e = tid; e < ntask; e += THREADS) {
                 const int ci = c0 + c;
-                u64 id = 0;
-                bool valid = false;
-                if (ci < nc) { id = s_cand[ci]; valid = window_valid(p, id); }
-                const bool rc = p.form == 0 && (id & 1);
-                const uint8_t *src = p.form == 1 ? p.ref + id * (u64)rows : p.ref + (id >> 1);
-                uint8_t *dst = s_sel + (size_t)c * selw;
-                for (int i = lane; i < srows; i += 32) {
-                    const int rr = i - PAD;
-                    unsigned v = 4;
-                    if (valid && rr >= 0 && rr < rows) {
-                        const unsigned cls = rc ? src[rows - 1 - rr] : src[rr];
-                        v = cls < 4 ? (rc ? 3 - cls : cls) : 4;
+                unsigned out = 0x04040404u;
+                if (ci < nc) {
+                    const u64 id = s_cand[ci];
+                    if (window_valid(p, id)) {
+                        const bool rc = p.form == 0 && (id & 1);
+                        const uint8_t *src = p.form == 1 ? p.ref + id * (u64)rows : p.ref + (id >> 1);
+                        const int rr0 = 4 * w - PAD;  // row of output byte 0
+                        const uint8_t *a = rc ? src + (rows - 4 - rr0) : src + rr0;  // lowest source address of the four
+                        const unsigned long long ai = reinterpret_cast<unsigned long long>(a);
+                        const unsigned *aw = reinterpret_cast<const unsigned *>(ai & ~3ull);
+                        const unsigned lo = __ldg(aw), hi = __ldg(aw + 1);
+                        unsigned v = __funnelshift_r(lo, hi, ((unsigned)ai & 3u) * 8u);
+                        if (rc) v = __byte_perm(v, 0u, 0x0123) ^ 0x03030303u;
+                        const unsigned big = ((v >> 2) & 0x01010101u) * 0xffu;  // bytes holding a class >= 4 (N, other)
+                        v = (v & ~big) | (0x04040404u & big);
+                        if (rr0 < 0 || rr0 + 4 > rows) {
+#pragma unroll
+                            for (int b = 0; b < 4; ++b)
+                                if ((unsigned)(rr0 + b) >= (unsigned)rows) v = (v & ~(0xffu << (8 * b))) | (4u << (8 * b));
+                        }
+                        out = v;
                     }
-                    dst[i] = (uint8_t)v;
                 }
+                *reinterpret_cast<unsigned *>(s_sel + (size_t)c * selw + 4 * w) = out;
+                c += dc; w += dw;
+                if (w >= wpr) { w -= wpr; ++c; }
             }
         }
         __syncthreads();
@@ -765,7 +806,11 @@ int launch_rerank(const DeviceRef &ref, const RerankArgs &a, cudaStream_t stream
         for (const auto &kv : kVariants)
             if (!strcmp(e, kv.name)) variant = kv.v;
     const int selw = (ref.ref_len + 14 + 3) / 4 * 4;  // rows + fill/drain padding of the two-row form (12) + 2
-    const size_t psmem = (size_t)PTAB_ENTRIES * sizeof(uint4) + (size_t)2 * PAIRS_PER_PASS * selw + (size_t)C * sizeof(u64) +
+    // CTA size of the profile kernel: 256 threads (128 candidates per pass, 2 CTAs/SM) or 128 (64 per pass, 4 CTAs/SM, so
+    // that more reads are in different phases on one SM).  DRM_SW_THREADS overrides, for A/B measurements.
+    int pthreads = 256;
+    if (const char *e = getenv("DRM_SW_THREADS")) pthreads = atoi(e) == 128 ? 128 : 256;
+    const size_t psmem = (size_t)PTAB_ENTRIES * sizeof(uint4) + (size_t)(pthreads / 2) * selw + (size_t)C * sizeof(u64) +
                          (size_t)take * sizeof(u64) + (size_t)(take + 1) * sizeof(int) + 16;
     int *fb = nullptr;  // [0] = count, [1..] = reads handed back by the profile kernel
     if (fast && variant != 0) {
@@ -785,10 +830,15 @@ int launch_rerank(const DeviceRef &ref, const RerankArgs &a, cudaStream_t stream
         if (fast && variant != 0) {
             p.ref = ref.data;
             DRM_CUDA_TRY(cudaMemsetAsync(fb, 0, sizeof(int), stream));
-#define DRM_PROFILE_LAUNCH(R, A)                                                                                                   \
-    do {                                                                                                                            \
-        DRM_CUDA_TRY(cudaFuncSetAttribute(sw_rerank_profile_kernel<R, A>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)psmem)); \
-        sw_rerank_profile_kernel<R, A><<<(unsigned)nb, RERANK_THREADS, psmem, stream>>>(p, selw, 1u, fb + 1, fb);                   \
+#define DRM_PROFILE_LAUNCH_T(R, A, T)                                                                                                 \
+    do {                                                                                                                               \
+        DRM_CUDA_TRY(cudaFuncSetAttribute(sw_rerank_profile_kernel<R, A, T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)psmem)); \
+        sw_rerank_profile_kernel<R, A, T><<<(unsigned)nb, T, psmem, stream>>>(p, selw, 1u, fb + 1, fb);                                \
+    } while (0)
+#define DRM_PROFILE_LAUNCH(R, A)                                      \
+    do {                                                              \
+        if (pthreads == 128) DRM_PROFILE_LAUNCH_T(R, A, 128);         \
+        else DRM_PROFILE_LAUNCH_T(R, A, 256);                         \
     } while (0)
             switch (variant) {
             case 1: DRM_PROFILE_LAUNCH(1, 1); break;
@@ -800,6 +850,7 @@ int launch_rerank(const DeviceRef &ref, const RerankArgs &a, cudaStream_t stream
             case 12: DRM_PROFILE_LAUNCH(2, 2); break;
             default: DRM_PROFILE_LAUNCH(2, 4); break;
             }
+#undef DRM_PROFILE_LAUNCH_T
 #undef DRM_PROFILE_LAUNCH
             DRM_CUDA_TRY(cudaGetLastError());
             // reads containing N were handed back: the PRMT kernel strides over that list (usually empty)
