@@ -49,9 +49,10 @@ def parse():
     ap.add_argument("--cache", default=os.environ.get("DRM_CACHE", os.path.join(tempfile.gettempdir(), "drm_b200_cache")))
     ap.add_argument("--cpu-sample", type=int, default=0, help="reads in the CPU baseline sample (0 = 600 per host core)")
     ap.add_argument("--skip-cpu", action="store_true")
-    ap.add_argument("--workload", default="dense", choices=["dense", "sharded"],
+    ap.add_argument("--workload", default="dense", choices=["dense", "sharded", "sparse"],
                     help="dense = configs[1] (index replicated, reads sharded, no collective; the driver's run); "
-                         "sharded = configs[4] scaled down (index sharded by position, all-gather + merge)")
+                         "sharded = configs[4] scaled down (index sharded by position, all-gather + merge); "
+                         "sparse = configs[2] (stride-8 index, K_clusters=32, window expansion + SW, use_dynamic 0 and 1)")
     ap.add_argument("--chunk", type=int, default=262144, help="reads per exchange step of the sharded workload")
     return ap.parse_args()
 
@@ -353,15 +354,21 @@ def run_ours(args):
     else:
         bytes_per_read = 128 * cnt[0] / n + 64 * cnt[1] / n + 8 * cnt[2] / n + 512 + 1536
     ach = bytes_per_read * n / (search_ms / 1e3) / 1e9
-    line["roofline_search"] = {"kernel": "hnswpq_search_kernel", "bound": "hbm", "achieved": ach, "peak": hbm_peak, "unit": "GB/s",
-                               "frac": ach / hbm_peak, "traffic": None, "peak_source": peak_src,
+    # DRAM traffic per launch: dram__bytes_read.sum + dram__bytes_write.sum of one `ncu --set full` capture of each kernel on this
+    # workload at 131072 reads (profiles/r1_ncu_*_v2.txt), scaled to this launch's read count
+    NCU_DRAM_BYTES_PER_READ = {"search": (7.236215e9 + 201.359e6) / 131072, "sw": (163.365e6 + 125.553e6) / 131072}
+    line["roofline_search"] = {"kernel": "hnswpq_search_reg_kernel", "bound": "hbm", "achieved": ach, "peak": hbm_peak, "unit": "GB/s",
+                               "frac": ach / hbm_peak, "traffic": NCU_DRAM_BYTES_PER_READ["search"] * n, "peak_source": peak_src,
+                               "traffic_source": "ncu capture at 131072 reads, scaled by reads (profiles/r1_ncu_hnswpq_search_reg_kernel_v2.txt)",
                                "algorithmic_bytes_per_read": bytes_per_read, "ms_per_launch": search_ms}
     # issue roofline of the recurrence: 3.5 math instructions per s16x2 cell PAIR (add, max3, clamp, half a best-max3)
     # spread over the alu and fma pipes, each measured at 64 lanes/clk/SM (profiles/r1_ubench_pipes.txt) -> 2*64/3.5 pairs/clk/SM
     int_peak = sms * (2 * 64 / 3.5) * 2 * sm_max * 1e6 / 1e9
     g = line["sw_gcups"]
     line["roofline"] = {"kernel": "sw_rerank_profile_kernel (dominant: %.0f%% of the step)" % (100 * sw_ms / (sw_ms + search_ms)), "bound": "issue (alu + fma pipes; neither hbm nor tensor applies: DRAM traffic of this kernel is < 0.1 % of peak)",
-                        "achieved": g, "peak": int_peak, "unit": "GCUPS", "frac": g / int_peak, "traffic": None,
+                        "achieved": g, "peak": int_peak, "unit": "GCUPS", "frac": g / int_peak,
+                        "traffic": NCU_DRAM_BYTES_PER_READ["sw"] * min(n, 131072),
+                        "traffic_source": "ncu capture of one 131072-read launch (profiles/r1_ncu_sw_rerank_profile_kernel_v2.txt): 2.2 KB/read, i.e. 4 GB/s - not an HBM-bound kernel",
                         "peak_source": "measured pipe rates (profiles/r1_ubench_pipes.txt, r1_ubench_alu.txt) x 3.5 instructions per cell pair at clocks.max.sm; DESIGN.md §4.3",
                         "cells_per_launch": cells, "ms_per_step": sw_ms}
     print(json.dumps(line), flush=True)
@@ -479,8 +486,111 @@ def run_sharded(args):
     return 0
 
 
+def window_table(genome: bytes) -> bytes:
+    """ref_seqs of the reference's static mode: window id 2p + rc = genome[p:p+150], reverse-complemented when rc
+    (src/utils/parse_inputs.cpp:345-355).  1.4 GB for the E. coli-sized genome; only the CPU parity check uses it."""
+    g = np.frombuffer(genome, dtype=np.uint8)
+    comp = np.zeros(256, dtype=np.uint8)
+    for a, b in zip(b"ACGTN", b"TGCAN"):
+        comp[a] = b
+    view = np.lib.stride_tricks.sliding_window_view(g, REF_LEN)
+    n_pos = view.shape[0]
+    wins = np.empty((2 * n_pos, REF_LEN), dtype=np.uint8)
+    for p0 in range(0, n_pos, 1 << 19):
+        p1 = min(n_pos, p0 + (1 << 19))
+        wins[2 * p0:2 * p1:2] = view[p0:p1]
+        wins[2 * p0 + 1:2 * p1:2] = comp[view[p0:p1, ::-1]]
+    return wins.tobytes()
+
+
+def run_sparse(args):
+    """configs[2]: E. coli-sized SPARSE index (every 8th window id, both strands), search k = K_clusters = 32 at EF = 128,
+    then the post-process expansion (each sparse id -> up to 15 dense window ids, src/utils/post_processor.cpp:117-125,
+    249-257) and the SW rerank of all of them, final K = 128; use_dynamic = 0 (bound = dense windows) and 1 (bound = genome
+    length, which drops the upper half of the id space like the reference does).  One GPU; a parity-and-throughput line,
+    not the headline."""
+    import torch
+
+    import deepreadmapper_b200 as drm
+    from deepreadmapper_b200 import synth
+    from oracle import bindings as ob
+
+    stride, kc, kfinal = 8, 32, 128
+    torch.cuda.set_device(0)
+    genome = make_genome(args)
+    os.makedirs(args.cache, exist_ok=True)
+    path = os.path.join(args.cache, f"ecoli_sparse{stride}_g{args.genome_bases}_efc{args.efc}.index")
+    if not os.path.exists(path):
+        t0 = time.time()
+        E = synth.embed_windows_torch(genome, "cuda:0", stride=stride)
+        drm.build_index(E, path + ".tmp", M_pq=8, nbits=8, M_hnsw=16, efc=args.efc, seed=1234)
+        os.replace(path + ".tmp", path)
+        log(f"sparse index ({E.shape[0]} vectors) built in {time.time() - t0:.1f}s")
+    ix = drm.Index(path, devices=[0])
+    ref = drm.Reference(genome=genome, ref_len=REF_LEN, devices=[0])
+    n = min(args.reads, 100_000)
+    reads, truth, Q = make_reads(genome, n, seed=7)
+    stream = torch.cuda.current_stream()
+    sp = stream.cuda_stream
+    dQ = torch.from_numpy(Q).cuda()
+    dreads = torch.from_numpy(reads.reshape(-1)).cuda()
+    doff = torch.from_numpy(np.arange(n + 1, dtype=np.int64) * REF_LEN).cuda()
+    dD = torch.empty((n, kc), dtype=torch.float32, device="cuda")
+    dI = torch.empty((n, kc), dtype=torch.int64, device="cuda")
+    dS = torch.empty((n, kfinal), dtype=torch.int32, device="cuda")
+    dIds = torch.empty((n, kfinal), dtype=torch.int64, device="cuda")
+    dN = torch.zeros(n, dtype=torch.int32, device="cuda")
+    dcells = torch.zeros(1, dtype=torch.int64, device="cuda")
+    out = {}
+    ns = min(2000, n)
+    wins = None
+    for mode in (0, 1):
+        ev = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
+        ts, tw = [], []
+        for it in range(args.warmup + args.steps):
+            dcells.zero_()
+            ev[0].record(stream)
+            ix.search_device(dQ.data_ptr(), n, kc, EF, dD.data_ptr(), dI.data_ptr(), 0, sp)
+            ev[1].record(stream)
+            ref.rerank_device(mode, dI.data_ptr(), n, kc, dreads.data_ptr(), doff.data_ptr(), REF_LEN, stride, kfinal, kc,
+                              dS.data_ptr(), dIds.data_ptr(), dN.data_ptr(), 0, dcells.data_ptr(), sp)
+            ev[2].record(stream)
+            torch.cuda.synchronize()
+            if it >= args.warmup:
+                ts.append(ev[0].elapsed_time(ev[1]))
+                tw.append(ev[1].elapsed_time(ev[2]))
+        cells = float(dcells.item())
+        ncand = dN.cpu().numpy()
+        ok_rows = ncand >= kfinal  # rows with fewer candidates than K raise "Not enough candidates" in the reference
+        # parity on a sample: the CPU path (FAISS-rule search is not needed here: rerank the GPU labels with the reference code)
+        I_s = dI[:ns].cpu().numpy()
+        rows = np.nonzero(ok_rows[:ns])[0]
+        if mode == 0:
+            if wins is None:
+                wins = window_table(genome)
+            refb, nref = wins, len(wins) // REF_LEN
+        else:
+            refb, nref = genome, len(genome)
+        rc, s0, i0, _ = ob.post_process_sw(mode, I_s[rows], refb, nref, REF_LEN, [bytes(r) for r in reads[rows]], stride, kfinal, kc,
+                                           threads=os.cpu_count() or 1, use_ref=ob.have_ref())
+        same = bool(rc == 0 and np.array_equal(s0, dS[:ns].cpu().numpy()[rows]) and np.array_equal(i0.astype(np.int64), dIds[:ns].cpu().numpy()[rows]))
+        out["use_dynamic=%d" % mode] = {"search_ms": float(np.mean(ts)), "sw_ms": float(np.mean(tw)), "reads_per_s": n / ((np.mean(ts) + np.mean(tw)) / 1e3),
+                                        "sw_gcups_raw": cells / (np.mean(tw) / 1e3) / 1e9, "candidates_per_read": float(ncand.mean()),
+                                        "reads_with_fewer_than_K_candidates": int((~ok_rows).sum()),
+                                        "sw_bit_exact_vs_reference_on_sample": same, "sample_rows": int(len(rows)),
+                                        "top1_is_planted_position": float(((dIds[:, 0].cpu().numpy() >> 1) == (truth >> 1))[ok_rows].mean())}
+    line = {"metric": METRIC, "value": out["use_dynamic=0"]["reads_per_s"], "unit": "reads/s", "n_gpus": 1, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": out["use_dynamic=0"]["search_ms"] + out["use_dynamic=0"]["sw_ms"], "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32 ADC distances + s16x2 SW", "data": "synthetic",
+            "config": {"workload": "configs[2]: E. coli-sized sparse index (stride 8) + post-process window expansion + SW rerank",
+                       "genome_bases": args.genome_bases, "n_vectors": int(ix.ntotal), "stride": stride, "K_clusters": kc, "K": kfinal, "EF": EF,
+                       "reads": n}, "modes": out}
+    print(json.dumps(line), flush=True)
+    return 0
+
+
 if __name__ == "__main__":
     a = parse()
     if a.impl == "reference":
         sys.exit(run_reference(a))
-    sys.exit(run_sharded(a) if a.workload == "sharded" else run_ours(a))
+    sys.exit(run_sharded(a) if a.workload == "sharded" else run_sparse(a) if a.workload == "sparse" else run_ours(a))

@@ -41,7 +41,7 @@ struct SearchParams {
     const uint8_t *rows0;
     const uint8_t *up;
     int row0_bytes, rowu_bytes, W0, Wu, c0_off, cu_off;
-    long long entry_vertex, entry_row;
+    long long entry_vertex, entry_row, ntotal;
     int max_level;
     int k, ef, cap, cap_alloc;
     float *D;
@@ -360,12 +360,19 @@ __device__ __forceinline__ void build_lut_t(float *T, const float *__restrict__ 
 }
 
 // FULLCAP: cap == 32 * NS (the pool fills the registers exactly: no tail to keep at POOL_INF, the maximum is lane 31's last slot).
-template <int CS, int NS, bool FULLCAP>
-__global__ void __launch_bounds__(WARPS_PER_CTA * 32, 6) hnswpq_search_reg_kernel(const SearchParams p)
+// VIS: a per-warp direct-mapped cache of evaluated vertex ids in shared memory (VIS_SLOTS 16-bit tags: slot = id % VIS_SLOTS,
+// tag = id / VIS_SLOTS, exact while ntotal <= VIS_SLOTS * 65535).  A hit means "evaluated before", and a vertex evaluated
+// before is either still in the pool or was rejected / evicted above the pool maximum (which only decreases), so it can be
+// skipped without changing the result; a miss after an eviction from the cache just re-evaluates, which the duplicate test
+// and the pool maximum handle as before.  It removes the repeat ADC evaluations and insert attempts (about a quarter).
+constexpr int VIS_SLOTS = 1024;
+template <int CS, int NS, bool FULLCAP, bool VIS>
+__global__ void __launch_bounds__(WARPS_PER_CTA * 32, VIS ? 5 : 6) hnswpq_search_reg_kernel(const SearchParams p)
 {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     float *T = reinterpret_cast<float *>(smem_raw) + (size_t)warp * p.M * 256;
+    unsigned short *vis = reinterpret_cast<unsigned short *>(smem_raw + (size_t)WARPS_PER_CTA * p.M * 256 * sizeof(float)) + (size_t)warp * VIS_SLOTS;
     const int cap = p.cap;
     const int base = lane * NS;
     const int max_lane = (cap - 1) / NS, max_slot = (cap - 1) % NS;
@@ -379,6 +386,11 @@ __global__ void __launch_bounds__(WARPS_PER_CTA * 32, 6) hnswpq_search_reg_kerne
         __syncwarp();
         if (p.centroids_t) build_lut_t(T, p.q + (size_t)qi * p.d, p.centroids_t, p.M, p.dsub, lane);
         else build_lut(T, p.q + (size_t)qi * p.d, p.centroids, p.M, p.dsub, lane);
+        if (VIS) {
+            uint4 *v4 = reinterpret_cast<uint4 *>(vis);
+#pragma unroll
+            for (int i = 0; i < VIS_SLOTS * 2 / 16 / 32; ++i) v4[lane + 32 * i] = make_uint4(~0u, ~0u, ~0u, ~0u);
+        }
         __syncwarp();
 
         unsigned nhops0 = 0, nhops_up = 0, ndis = 0;
@@ -411,6 +423,7 @@ __global__ void __launch_bounds__(WARPS_PER_CTA * 32, 6) hnswpq_search_reg_kerne
         }
 
         // ---------------- level 0
+        if (VIS && lane == 0) vis[(unsigned)vertex % VIS_SLOTS] = (unsigned short)((unsigned)vertex / VIS_SLOTS);
         u64 k[NS];
 #pragma unroll
         for (int s = 0; s < NS; ++s) k[s] = POOL_INF;
@@ -454,8 +467,20 @@ __global__ void __launch_bounds__(WARPS_PER_CTA * 32, 6) hnswpq_search_reg_kerne
 
             const unsigned neg = __ballot_sync(FULL, nid < 0);
             const int first_neg = neg ? (__ffs(neg) - 1) : 32;
-            const bool valid = lane < first_neg;
-            ndis += (unsigned)first_neg;
+            bool valid = lane < first_neg;
+            if (VIS) {
+                if (valid) {
+                    const unsigned slot = (unsigned)nid % VIS_SLOTS;
+                    const unsigned short tag = (unsigned short)((unsigned)nid / VIS_SLOTS);
+                    if (vis[slot] == tag) valid = false;
+                    else vis[slot] = tag;
+                }
+                const unsigned fresh = __ballot_sync(FULL, valid);
+                ndis += (unsigned)__popc(fresh);
+                if (!fresh) continue;
+            } else {
+                ndis += (unsigned)first_neg;
+            }
             u64 key = 0;
             if (valid) key = make_key(adc(T, code), nid);
             unsigned mask = __ballot_sync(FULL, valid && key < maxkey);
@@ -519,10 +544,11 @@ __global__ void __launch_bounds__(WARPS_PER_CTA * 32, 6) hnswpq_search_reg_kerne
     }
 }
 
-template <int CS, int NS, bool FULLCAP>
-int launch_reg_tf(const SearchParams &p, size_t smem, int device, cudaStream_t stream)
+template <int CS, int NS, bool FULLCAP, bool VIS>
+int launch_reg_tfv(const SearchParams &p, size_t smem, int device, cudaStream_t stream)
 {
-    auto kern = hnswpq_search_reg_kernel<CS, NS, FULLCAP>;
+    auto kern = hnswpq_search_reg_kernel<CS, NS, FULLCAP, VIS>;
+    if (VIS) smem += (size_t)WARPS_PER_CTA * VIS_SLOTS * sizeof(unsigned short);
     DRM_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int per_sm = 0, sms = 0;
     DRM_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, WARPS_PER_CTA * 32, smem));
@@ -534,6 +560,15 @@ int launch_reg_tf(const SearchParams &p, size_t smem, int device, cudaStream_t s
     kern<<<(unsigned)grid, WARPS_PER_CTA * 32, smem, stream>>>(p);
     DRM_CUDA_TRY(cudaGetLastError());
     return DRM_OK;
+}
+
+template <int CS, int NS, bool FULLCAP>
+int launch_reg_tf(const SearchParams &p, size_t smem, int device, cudaStream_t stream)
+{
+    // the visited cache's 16-bit tags are exact only below VIS_SLOTS * 65535 vertices; DRM_SEARCH_VIS=0 disables it (A/B)
+    const char *e = getenv("DRM_SEARCH_VIS");
+    const bool vis = p.ntotal < (long long)VIS_SLOTS * 65535 && !(e && e[0] == '0');
+    return vis ? launch_reg_tfv<CS, NS, FULLCAP, true>(p, smem, device, stream) : launch_reg_tfv<CS, NS, FULLCAP, false>(p, smem, device, stream);
 }
 
 template <int CS, int NS>
@@ -587,7 +622,7 @@ int launch_search(const DeviceIndex &dx, const float *q_dev, int64_t n, int k, i
     p.q = q_dev; p.n = n; p.d = dx.d; p.M = dx.M; p.dsub = dx.dsub;
     p.centroids = dx.centroids; p.centroids_t = reinterpret_cast<const float4 *>(dx.centroids_t); p.rows0 = dx.rows0; p.up = dx.up;
     p.row0_bytes = dx.row0_bytes; p.rowu_bytes = dx.rowu_bytes; p.W0 = dx.W0; p.Wu = dx.Wu; p.c0_off = dx.code0_off; p.cu_off = dx.codeu_off;
-    p.entry_vertex = dx.entry_vertex; p.entry_row = dx.entry_row; p.max_level = dx.max_level;
+    p.entry_vertex = dx.entry_vertex; p.entry_row = dx.entry_row; p.ntotal = dx.ntotal; p.max_level = dx.max_level;
     p.k = k; p.ef = ef; p.cap = cap; p.cap_alloc = cap_alloc;
     p.D = D_dev; p.I = reinterpret_cast<long long *>(I_dev);
     p.counters = reinterpret_cast<u64 *>(counters_dev);

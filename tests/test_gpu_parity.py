@@ -204,10 +204,11 @@ def mid_index(tmp_path_factory):
     return p, synth.embed_reads(reads), ids
 
 
-@pytest.fixture(params=["reg", "smem"])
+@pytest.fixture(params=["reg", "reg_novis", "smem"])
 def search_variant(request, monkeypatch):
-    """Both search kernels (register pool / shared-memory pool) must return the oracle's bits."""
-    monkeypatch.setenv("DRM_SEARCH_KERNEL", request.param)
+    """Every search kernel (register pool with / without the visited cache, shared-memory pool) must return the oracle's bits."""
+    monkeypatch.setenv("DRM_SEARCH_KERNEL", "smem" if request.param == "smem" else "reg")
+    monkeypatch.setenv("DRM_SEARCH_VIS", "0" if request.param == "reg_novis" else "1")
     return request.param
 
 
