@@ -63,6 +63,15 @@ def workload_paths(args):
     return os.path.join(args.cache, f"ecoli_dense_{tag}.index")
 
 
+def host_threads():
+    """Host cores this process may use.  torchrun exports OMP_NUM_THREADS=1 for its workers, which would make the one-off
+    index build (and the CPU arm) single-threaded: every OpenMP region here is given its thread count explicitly."""
+    try:
+        return max(1, len(os.sched_getaffinity(0)))
+    except AttributeError:
+        return max(1, os.cpu_count() or 1)
+
+
 def make_genome(args):
     from deepreadmapper_b200 import synth
     return synth.random_genome(args.genome_bases, 42)
@@ -80,10 +89,10 @@ def ensure_index(args, genome, device=None):
         E = synth.embed_windows_torch(genome, device)
     else:
         E = synth.embed_windows(genome)
-    log(f"embedded {E.shape[0]} windows in {time.time() - t0:.1f}s; building HNSW-PQ index (EFC={args.efc}) on {os.cpu_count()} host cores")
+    log(f"embedded {E.shape[0]} windows in {time.time() - t0:.1f}s; building HNSW-PQ index (EFC={args.efc}) on {host_threads()} host cores")
     t1 = time.time()
     tmp = path + f".tmp{os.getpid()}"
-    drm.build_index(E, tmp, M_pq=8, nbits=8, M_hnsw=16, efc=args.efc, seed=1234)
+    drm.build_index(E, tmp, M_pq=8, nbits=8, M_hnsw=16, efc=args.efc, seed=1234, threads=host_threads())
     os.replace(tmp, path)
     log(f"index built in {time.time() - t1:.1f}s -> {path}")
     return path, time.time() - t0
@@ -166,7 +175,7 @@ def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return 0
-    threads = os.cpu_count() or 1
+    threads = host_threads()
     genome = make_genome(args)
     dev = None
     try:
@@ -337,7 +346,7 @@ def run_ours(args):
     line["kernel_counters_per_read"] = {"nhops0": cnt[0] / n, "nhops_up": cnt[1] / n, "ndis_eval": cnt[2] / n}
     cpu = None
     if world == 1 and not args.skip_cpu:
-        threads = os.cpu_count() or 1
+        threads = host_threads()
         ns = args.cpu_sample or 600 * threads
         rps, (ts, tw), kind, counters, (D0, I0, s0, ids0) = cpu_reference_run(args, genome, index_path, reads, Q, ns, threads)
         overlap = float(np.mean([len(set(I0[i].tolist()) & set(hI[i].tolist())) / K for i in range(ns)]))
@@ -407,7 +416,7 @@ def run_sharded(args):
         sub = genome[lo // 2: hi // 2 + REF_LEN - 1]
         E = synth.embed_windows_torch(sub, f"cuda:{local}")
         assert E.shape[0] == hi - lo, (E.shape, lo, hi)
-        drm.build_index(E, path + ".tmp", M_pq=8, nbits=8, M_hnsw=16, efc=args.efc, seed=1234 + rank, threads=max(1, (os.cpu_count() or 1) // world))
+        drm.build_index(E, path + ".tmp", M_pq=8, nbits=8, M_hnsw=16, efc=args.efc, seed=1234 + rank, threads=max(1, host_threads() // world))
         os.replace(path + ".tmp", path)
         log(f"rank {rank}: shard [{lo}, {hi}) built in {time.time() - t0:.1f}s")
     barrier()
@@ -523,7 +532,7 @@ def run_sparse(args):
     if not os.path.exists(path):
         t0 = time.time()
         E = synth.embed_windows_torch(genome, "cuda:0", stride=stride)
-        drm.build_index(E, path + ".tmp", M_pq=8, nbits=8, M_hnsw=16, efc=args.efc, seed=1234)
+        drm.build_index(E, path + ".tmp", M_pq=8, nbits=8, M_hnsw=16, efc=args.efc, seed=1234, threads=host_threads())
         os.replace(path + ".tmp", path)
         log(f"sparse index ({E.shape[0]} vectors) built in {time.time() - t0:.1f}s")
     ix = drm.Index(path, devices=[0])
@@ -572,7 +581,7 @@ def run_sparse(args):
         else:
             refb, nref = genome, len(genome)
         rc, s0, i0, _ = ob.post_process_sw(mode, I_s[rows], refb, nref, REF_LEN, [bytes(r) for r in reads[rows]], stride, kfinal, kc,
-                                           threads=os.cpu_count() or 1, use_ref=ob.have_ref())
+                                           threads=host_threads(), use_ref=ob.have_ref())
         same = bool(rc == 0 and np.array_equal(s0, dS[:ns].cpu().numpy()[rows]) and np.array_equal(i0.astype(np.int64), dIds[:ns].cpu().numpy()[rows]))
         out["use_dynamic=%d" % mode] = {"search_ms": float(np.mean(ts)), "sw_ms": float(np.mean(tw)), "reads_per_s": n / ((np.mean(ts) + np.mean(tw)) / 1e3),
                                         "sw_gcups_raw": cells / (np.mean(tw) / 1e3) / 1e9, "candidates_per_read": float(ncand.mean()),

@@ -44,6 +44,7 @@ struct SearchParams {
     long long entry_vertex, entry_row, ntotal;
     int max_level;
     int k, ef, cap, cap_alloc;
+    int prefetch_depth;   // rows L2-prefetched beyond the register read-ahead (0..2)
     float *D;
     long long *I;
     u64 *counters;        // nhops0, nhops_up, ndis_eval (nullable)
@@ -326,17 +327,22 @@ __global__ void __launch_bounds__(WARPS_PER_CTA * 32) hnswpq_search_kernel(const
 // Preconditions (launch_search falls back to the shared-memory kernel otherwise): W0 <= 32, k <= ef <= 256.
 constexpr u64 POOL_INF = ~0ull;
 
-template <int NS> __device__ __forceinline__ bool pool_first_unexpanded(const u64 (&k)[NS], int lane, int &L, u64 &key)
+template <int NS> __device__ __forceinline__ bool pool_first_unexpanded(const u64 (&k)[NS], int lane, int &L, u64 &key, u64 &mine, unsigned &bal)
 {
-    u64 mine = POOL_INF;
+    mine = POOL_INF;
 #pragma unroll
     for (int s = NS - 1; s >= 0; --s)
         if (!(k[s] & 1ull)) mine = k[s];
-    const unsigned bal = __ballot_sync(FULL, !(mine & 1ull));
+    bal = __ballot_sync(FULL, !(mine & 1ull));
     if (!bal) return false;
     L = __ffs(bal) - 1;
     key = __shfl_sync(FULL, mine, L);
     return true;
+}
+template <int NS> __device__ __forceinline__ bool pool_first_unexpanded(const u64 (&k)[NS], int lane, int &L, u64 &key)
+{
+    u64 mine; unsigned bal;
+    return pool_first_unexpanded<NS>(k, lane, L, key, mine, bal);
 }
 
 __device__ __forceinline__ void build_lut_t(float *T, const float *__restrict__ x, const float4 *__restrict__ cent_t, int M, int dsub, int lane)
@@ -365,13 +371,14 @@ __device__ __forceinline__ void build_lut_t(float *T, const float *__restrict__ 
 // before is either still in the pool or was rejected / evicted above the pool maximum (which only decreases), so it can be
 // skipped without changing the result; a miss after an eviction from the cache just re-evaluates, which the duplicate test
 // and the pool maximum handle as before.  It removes the repeat ADC evaluations and insert attempts (about a quarter).
-constexpr int VIS_SLOTS = 1024;
-template <int CS, int NS, bool FULLCAP, bool VIS>
-__global__ void __launch_bounds__(WARPS_PER_CTA * 32, VIS ? 5 : 6) hnswpq_search_reg_kernel(const SearchParams p)
+// VIS = number of slots (0 = no cache): 1024 slots leave room for 5 CTAs per SM, 512 for 6.
+template <int CS, int NS, bool FULLCAP, int VIS>
+__global__ void __launch_bounds__(WARPS_PER_CTA * 32, VIS > 512 ? 5 : 6) hnswpq_search_reg_kernel(const SearchParams p)
 {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     float *T = reinterpret_cast<float *>(smem_raw) + (size_t)warp * p.M * 256;
+    constexpr int VIS_SLOTS = VIS > 0 ? VIS : 1;
     unsigned short *vis = reinterpret_cast<unsigned short *>(smem_raw + (size_t)WARPS_PER_CTA * p.M * 256 * sizeof(float)) + (size_t)warp * VIS_SLOTS;
     const int cap = p.cap;
     const int base = lane * NS;
@@ -389,7 +396,7 @@ __global__ void __launch_bounds__(WARPS_PER_CTA * 32, VIS ? 5 : 6) hnswpq_search
         if (VIS) {
             uint4 *v4 = reinterpret_cast<uint4 *>(vis);
 #pragma unroll
-            for (int i = 0; i < VIS_SLOTS * 2 / 16 / 32; ++i) v4[lane + 32 * i] = make_uint4(~0u, ~0u, ~0u, ~0u);
+            for (int i = 0; i < (VIS_SLOTS * 2 / 16 + 31) / 32; ++i) v4[lane + 32 * i] = make_uint4(~0u, ~0u, ~0u, ~0u);
         }
         __syncwarp();
 
@@ -455,12 +462,25 @@ __global__ void __launch_bounds__(WARPS_PER_CTA * 32, VIS ? 5 : 6) hnswpq_search
                 if (lane < p.W0) code = load_code<CS>(row + p.c0_off + CS * lane);
             }
             {   // read ahead: the row of the next entry in line
-                int L2; u64 k2;
-                if (pool_first_unexpanded<NS>(k, lane, L2, k2)) {
+                int L2; u64 k2, mine; unsigned bal;
+                if (pool_first_unexpanded<NS>(k, lane, L2, k2, mine, bal)) {
                     spec_v = (unsigned)(k2 & 0xffffffffu) >> 1;
                     const uint8_t *nrow = p.rows0 + (size_t)spec_v * p.row0_bytes;
                     nid_s = lane < p.W0 ? __ldg(reinterpret_cast<const int *>(nrow) + lane) : -1;
                     if (lane < p.W0) code_s = load_code<CS>(nrow + p.c0_off + CS * lane);
+                    if (p.prefetch_depth > 0) {
+                        // L2 prefetch of the rows further down the line (the first unexpanded entry of the next lanes that
+                        // have one): HBM has the headroom (8 % used), and a row that an insertion pushes back is still
+                        // expanded later, so the lines are rarely wasted.
+                        unsigned rest = bal & (bal - 1);  // drop lane L2
+                        const int la = rest ? __ffs(rest) - 1 : -1;
+                        rest &= rest - 1;
+                        const int lb = (rest && p.prefetch_depth > 1) ? __ffs(rest) - 1 : -1;
+                        if (lane == la || lane == lb) {
+                            const uint8_t *prow = p.rows0 + (size_t)((unsigned)(mine & 0xffffffffu) >> 1) * p.row0_bytes;
+                            for (int o = 0; o < p.row0_bytes; o += 128) asm volatile("prefetch.global.L2 [%0];" ::"l"(prow + o));
+                        }
+                    }
                 } else spec_v = 0xffffffffu;
             }
             ++nhops0;
@@ -544,11 +564,11 @@ __global__ void __launch_bounds__(WARPS_PER_CTA * 32, VIS ? 5 : 6) hnswpq_search
     }
 }
 
-template <int CS, int NS, bool FULLCAP, bool VIS>
+template <int CS, int NS, bool FULLCAP, int VIS>
 int launch_reg_tfv(const SearchParams &p, size_t smem, int device, cudaStream_t stream)
 {
     auto kern = hnswpq_search_reg_kernel<CS, NS, FULLCAP, VIS>;
-    if (VIS) smem += (size_t)WARPS_PER_CTA * VIS_SLOTS * sizeof(unsigned short);
+    smem += (size_t)WARPS_PER_CTA * VIS * sizeof(unsigned short);
     DRM_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int per_sm = 0, sms = 0;
     DRM_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, WARPS_PER_CTA * 32, smem));
@@ -565,10 +585,15 @@ int launch_reg_tfv(const SearchParams &p, size_t smem, int device, cudaStream_t 
 template <int CS, int NS, bool FULLCAP>
 int launch_reg_tf(const SearchParams &p, size_t smem, int device, cudaStream_t stream)
 {
-    // the visited cache's 16-bit tags are exact only below VIS_SLOTS * 65535 vertices; DRM_SEARCH_VIS=0 disables it (A/B)
+    // the visited cache's 16-bit tags are exact only below slots * 65535 vertices; DRM_SEARCH_VIS = 0 / 512 / 1024 picks (A/B)
     const char *e = getenv("DRM_SEARCH_VIS");
-    const bool vis = p.ntotal < (long long)VIS_SLOTS * 65535 && !(e && e[0] == '0');
-    return vis ? launch_reg_tfv<CS, NS, FULLCAP, true>(p, smem, device, stream) : launch_reg_tfv<CS, NS, FULLCAP, false>(p, smem, device, stream);
+    int slots = e ? atoi(e) : 1024;
+    if (slots == 1) slots = 1024;
+    if (slots != 512 && slots != 1024) slots = 0;
+    if (slots > 0 && p.ntotal >= (long long)slots * 65535) slots = p.ntotal < 1024ll * 65535 ? 1024 : 0;
+    if (slots == 1024) return launch_reg_tfv<CS, NS, FULLCAP, 1024>(p, smem, device, stream);
+    if (slots == 512) return launch_reg_tfv<CS, NS, FULLCAP, 512>(p, smem, device, stream);
+    return launch_reg_tfv<CS, NS, FULLCAP, 0>(p, smem, device, stream);
 }
 
 template <int CS, int NS>
@@ -624,6 +649,8 @@ int launch_search(const DeviceIndex &dx, const float *q_dev, int64_t n, int k, i
     p.row0_bytes = dx.row0_bytes; p.rowu_bytes = dx.rowu_bytes; p.W0 = dx.W0; p.Wu = dx.Wu; p.c0_off = dx.code0_off; p.cu_off = dx.codeu_off;
     p.entry_vertex = dx.entry_vertex; p.entry_row = dx.entry_row; p.ntotal = dx.ntotal; p.max_level = dx.max_level;
     p.k = k; p.ef = ef; p.cap = cap; p.cap_alloc = cap_alloc;
+    p.prefetch_depth = 0;
+    if (const char *e = getenv("DRM_SEARCH_PF")) p.prefetch_depth = atoi(e) < 0 ? 0 : atoi(e) > 2 ? 2 : atoi(e);
     p.D = D_dev; p.I = reinterpret_cast<long long *>(I_dev);
     p.counters = reinterpret_cast<u64 *>(counters_dev);
     p.next_query = work;

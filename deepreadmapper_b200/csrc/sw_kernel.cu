@@ -292,9 +292,7 @@ __device__ __forceinline__ unsigned sw_quad_profile(const uint8_t *rowA, const u
         unsigned diag = prev_recv, left = recv, mprev = 0;
 #pragma unroll
         for (int g = 0; g < PGROUPS; ++g) {
-            uint4 pr;
-            if (4 * g + 2 < PCPL) pr = prow[g * 8];
-            else { const uint2 h2 = *reinterpret_cast<const uint2 *>(prow + g * 8); pr = make_uint4(h2.x, h2.y, 0u, 0u); }
+            const uint4 pr = prow[g * 8];  // the last group uses two of its four columns (an LDS.64 there would be 2-way conflicted)
             const unsigned s4[4] = {pr.x, pr.y, pr.z, pr.w};
 #pragma unroll
             for (int c = 0; c < 4; ++c) {

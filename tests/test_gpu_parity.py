@@ -283,6 +283,41 @@ def test_search_then_rerank_pipeline(drm, ob, fixtures, small_index, sw_variant)
     assert s.tolist() == s0.reshape(-1).tolist() and ids.tolist() == i0.reshape(-1).tolist()
 
 
+def test_search_rerank_one_call_matches_two_calls_and_replicas(drm, ob, fixtures, mid_index):
+    """drm_search_rerank (host buffers, chunked, double-buffered) == drm_search followed by drm_sw_rerank, for chunk sizes
+    that do and do not divide the batch, twice on the same handle (workspace reuse), and - when the box has two GPUs - with
+    the batch fanned out over two replicas inside one process."""
+    import os
+    from deepreadmapper_b200 import synth
+    path, Q, _ = mid_index
+    g = synth.random_genome(60000, 42)       # the fixture's genome and reads (deterministic generators)
+    reads, _ = synth.simulate_reads(g, 3000)
+    n = 3000
+    Q = np.ascontiguousarray(Q[:n])
+    seqs = [bytes(r) for r in reads[:n]]
+    flat, off = drm.api.flatten(seqs)
+    devsets = [[0]] + ([[0, 1]] if drm.lib().drm_device_count() >= 2 else [])
+    want = None
+    for devs in devsets:
+        ix = drm.Index(path, devices=devs)
+        ref = drm.Reference(genome=g, ref_len=150, devices=devs)
+        D1, I1 = ix.search(Q, 64, 128)
+        s1, id1 = ref.rerank(1, I1, seqs, 1, 32, 64)
+        if want is None:
+            want = (D1, I1, s1, id1)
+        for chunk in ("1024", "1100", "1024"):
+            os.environ["DRM_CHUNK"] = chunk
+            try:
+                D2, I2, s2, id2, st, tm = drm.search_rerank(ix, ref, 1, Q, bytes(flat), off, 1, 32, 64, 64, 128)
+            finally:
+                del os.environ["DRM_CHUNK"]
+            for a, b in zip(want, (D2, I2, s2, id2)):
+                assert np.array_equal(np.asarray(a).reshape(-1), np.asarray(b).reshape(-1)), (devs, chunk)
+            assert st["nhops0"] > 0
+        ix.close()
+        ref.close()
+
+
 def test_merge_topk(drm):
     import torch
     rng = np.random.default_rng(1)
