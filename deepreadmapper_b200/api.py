@@ -33,7 +33,7 @@ class SearchStats(C.Structure):
 EXPORTS = ["drm_last_error", "drm_device_count", "drm_version", "drm_index_open", "drm_index_close", "drm_index_info",
            "drm_search", "drm_search_device", "drm_ref_open_genome", "drm_ref_open_windows", "drm_ref_close",
            "drm_sw_pairs", "drm_sw_rerank", "drm_sw_rerank_device", "drm_merge_topk_device", "drm_build_index",
-           "drm_search_rerank"]
+           "drm_search_rerank", "drm_build_index_gpu", "drm_build_index_gpu_device"]
 
 
 def lib_path() -> str:
@@ -66,6 +66,8 @@ def lib():
         L.drm_sw_rerank_device.argtypes = [vp, i32, i32, vp, i64, i64, vp, vp, i32, i64, i64, i64, vp, vp, vp, vp, vp, vp]
         L.drm_merge_topk_device.argtypes = [i32, vp, vp, i32, i64, i32, vp, vp, vp]
         L.drm_build_index.argtypes = [vp, i64, i32, vp, i64, i32, i32, i32, i32, i32, C.c_uint32, C.c_char_p]
+        L.drm_build_index_gpu.argtypes = [vp, i64, i32, vp, i64, i32, i32, i32, i32, i32, C.c_uint32, C.c_char_p, vp]
+        L.drm_build_index_gpu_device.argtypes = [vp, i64, i32, i64, i32, i32, i32, i32, i32, C.c_uint32, C.c_char_p, vp]
         L.drm_search_rerank.argtypes = [vp, vp, i32, vp, i64, i32, i32, i32, vp, vp, i64, i64, i64, vp, vp, vp, vp,
                                         C.POINTER(SearchStats), vp]
         _lib = L
@@ -273,3 +275,29 @@ def build_index(x, out_path, M_pq=8, nbits=8, M_hnsw=16, efc=200, train=None, th
     train = np.ascontiguousarray(train, dtype=np.float32)
     _check(lib().drm_build_index(x.ctypes.data, n, d, train.ctypes.data, train.shape[0], M_pq, nbits, M_hnsw, efc, threads,
                                  seed, os.fsencode(out_path)))
+
+
+BUILD_STAGES = ("upload", "pq_train", "encode", "graph", "export")
+
+
+def build_index_gpu(x, out_path, M_pq=8, nbits=8, M_hnsw=16, efc=200, train=None, device=0, seed=1234):
+    """build_faiss_index (src/hnswpq/index.cpp:86-193) on the GPU: PQ k-means, encoding and batched HNSW insertion
+    (csrc/build_gpu.cu).  x: host array n x d.  Returns {stage: seconds}."""
+    x = np.ascontiguousarray(x, dtype=np.float32)
+    n, d = x.shape
+    if train is None:
+        train = x[::2]  # Config::Build::SAMPLE_RATE = 0.5, evenly strided (src/hnswpq/index.cpp:57-84,99)
+    train = np.ascontiguousarray(train, dtype=np.float32)
+    tim = np.zeros(5, dtype=np.float64)
+    _check(lib().drm_build_index_gpu(x.ctypes.data, n, d, train.ctypes.data, train.shape[0], M_pq, nbits, M_hnsw, efc, device,
+                                     seed, os.fsencode(out_path), tim.ctypes.data))
+    return dict(zip(BUILD_STAGES, tim.tolist()))
+
+
+def build_index_gpu_device(x_dev_ptr, n, d, out_path, train_step=2, M_pq=8, nbits=8, M_hnsw=16, efc=200, device=0, seed=1234):
+    """Same with the vectors already resident on `device` (x_dev_ptr: device address of n x d fp32); the PQ training
+    sample is rows 0, train_step, 2*train_step, ...  Returns {stage: seconds}."""
+    tim = np.zeros(5, dtype=np.float64)
+    _check(lib().drm_build_index_gpu_device(x_dev_ptr, n, d, train_step, M_pq, nbits, M_hnsw, efc, device, seed,
+                                            os.fsencode(out_path), tim.ctypes.data))
+    return dict(zip(BUILD_STAGES, tim.tolist()))

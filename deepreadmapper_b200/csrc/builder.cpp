@@ -28,11 +28,9 @@ namespace {
 // ---------------------------------------------------------------- k-means for one sub-quantizer
 void kmeans(const float *x, int64_t n, int dsub, int k, int iters, uint32_t seed, float *cent)
 {
-    std::mt19937 rng(seed);
-    std::vector<int64_t> perm((size_t)n);
-    std::iota(perm.begin(), perm.end(), 0);
-    std::shuffle(perm.begin(), perm.end(), rng);
-    for (int c = 0; c < k; ++c) memcpy(cent + (size_t)c * dsub, x + (size_t)perm[(size_t)(c % n)] * dsub, sizeof(float) * dsub);
+    std::vector<int64_t> start;
+    builder_kmeans_init_rows(n, k, seed, start);
+    for (int c = 0; c < k; ++c) memcpy(cent + (size_t)c * dsub, x + (size_t)start[(size_t)c] * dsub, sizeof(float) * dsub);
     std::vector<int> assign((size_t)n);
     std::vector<double> sum((size_t)k * dsub);
     std::vector<int64_t> cnt((size_t)k);
@@ -56,22 +54,7 @@ void kmeans(const float *x, int64_t n, int dsub, int k, int iters, uint32_t seed
             cnt[(size_t)c]++;
             for (int t = 0; t < dsub; ++t) sum[(size_t)c * dsub + t] += x[(size_t)i * dsub + t];
         }
-        for (int c = 0; c < k; ++c)
-            if (cnt[(size_t)c])
-                for (int t = 0; t < dsub; ++t) cent[(size_t)c * dsub + t] = (float)(sum[(size_t)c * dsub + t] / (double)cnt[(size_t)c]);
-        // empty clusters: split the largest one with a small symmetric perturbation (as FAISS does)
-        for (int c = 0; c < k; ++c) {
-            if (cnt[(size_t)c]) continue;
-            int big = (int)(std::max_element(cnt.begin(), cnt.end()) - cnt.begin());
-            for (int t = 0; t < dsub; ++t) {
-                float v = cent[(size_t)big * dsub + t];
-                float eps = 1.f / 1024.f;
-                cent[(size_t)c * dsub + t] = v * (1 + ((t & 1) ? eps : -eps));
-                cent[(size_t)big * dsub + t] = v * (1 - ((t & 1) ? eps : -eps));
-            }
-            cnt[(size_t)c] = cnt[(size_t)big] / 2;
-            cnt[(size_t)big] -= cnt[(size_t)c];
-        }
+        builder_kmeans_update(sum.data(), cnt.data(), k, dsub, cent);
     }
 }
 
@@ -232,55 +215,11 @@ struct Worker {
 
 }  // namespace
 
-// x: n x d row-major.  train: n_train x d (the reference passes an evenly strided 50 % sample).
-int build_index_cpu(const float *x, int64_t n, int d, const float *train, int64_t n_train, int M_pq, int nbits, int M_hnsw,
-                    int efc, int threads, uint32_t seed, HostIndex &ix)
+// HNSW level law (HNSW::set_default_probas), random levels, offsets and the empty neighbour table.
+void builder_level_law(HostIndex &ix, int64_t n, int M_hnsw, uint32_t seed)
 {
-    if (n <= 0 || d <= 0 || M_pq <= 0 || d % M_pq) return fail(DRM_EINVAL, "bad index build arguments (d must be a multiple of M_pq)");
-    if (nbits != 8) return fail(DRM_EUNSUPPORTED, "only nbits == 8 is supported by the builder");
-    if (M_hnsw < 2 || efc < 1) return fail(DRM_EINVAL, "M_hnsw must be >= 2 and EFC >= 1");
-    if (n >= ((int64_t)1 << 31) - 1) return fail(DRM_EUNSUPPORTED, "more than 2^31 vectors");
-    if (threads <= 0) threads = omp_get_max_threads();
-    omp_set_num_threads(threads);
-    ix = HostIndex();
-    ix.d = d; ix.ntotal = n; ix.M = (uint64_t)M_pq; ix.nbits = 8; ix.ksub = 256; ix.dsub = (uint64_t)(d / M_pq); ix.code_size = (uint64_t)M_pq;
-    ix.efConstruction = efc; ix.efSearch = 16; ix.upper_beam = 1;
-    const int dsub = d / M_pq;
-
-    // ---- ProductQuantizer::train: k-means per sub-space on at most 256 points per centroid
-    ix.centroids.assign((size_t)M_pq * 256 * dsub, 0.f);
-    {
-        if (!train || n_train <= 0) { train = x; n_train = n; }
-        int64_t nt = std::min<int64_t>(n_train, 256 * 256);
-        std::vector<int64_t> pick((size_t)n_train);
-        std::iota(pick.begin(), pick.end(), 0);
-        std::mt19937 rng(seed);
-        if (nt < n_train) std::shuffle(pick.begin(), pick.end(), rng);
-        std::vector<float> sub((size_t)nt * dsub);
-        for (int m = 0; m < M_pq; ++m) {
-            for (int64_t i = 0; i < nt; ++i)
-                memcpy(&sub[(size_t)i * dsub], train + (size_t)pick[(size_t)i] * d + (size_t)m * dsub, sizeof(float) * dsub);
-            kmeans(sub.data(), nt, dsub, 256, 25, seed + 1 + (uint32_t)m, &ix.centroids[(size_t)m * 256 * dsub]);
-        }
-    }
-    // ---- IndexPQ::add: nearest centroid per sub-space
-    ix.codes.resize((size_t)n * M_pq);
-#pragma omp parallel for schedule(static)
-    for (int64_t i = 0; i < n; ++i)
-        for (int m = 0; m < M_pq; ++m) {
-            const float *xi = x + (size_t)i * d + (size_t)m * dsub;
-            float best = FLT_MAX; int bj = 0;
-            for (int j = 0; j < 256; ++j) {
-                const float *c = &ix.centroids[((size_t)m * 256 + j) * dsub];
-                float s = 0;
-                for (int t = 0; t < dsub; ++t) { float e = xi[t] - c[t]; s += e * e; }
-                if (s < best) { best = s; bj = j; }
-            }
-            ix.codes[(size_t)i * M_pq + m] = (uint8_t)bj;
-        }
-
-    // ---- HNSW level law (HNSW::set_default_probas) and storage
     const double level_mult = 1.0 / std::log((double)M_hnsw);
+    ix.assign_probas.clear();
     ix.cum.assign(1, 0);
     int nn = 0;
     for (int level = 0;; ++level) {
@@ -308,6 +247,106 @@ int build_index_cpu(const float *x, int64_t n, int d, const float *train, int64_
     ix.offsets[0] = 0;
     for (int64_t i = 0; i < n; ++i) ix.offsets[(size_t)i + 1] = ix.offsets[(size_t)i] + (uint64_t)ix.cum[(size_t)ix.levels[(size_t)i]];
     ix.neighbors.assign((size_t)ix.offsets[(size_t)n], -1);
+}
+
+// Insertion order: descending level, random inside a level (hnsw_add_vertices).
+void builder_insertion_order(const HostIndex &ix, uint32_t seed, std::vector<int64_t> &order)
+{
+    order.resize((size_t)ix.ntotal);
+    std::iota(order.begin(), order.end(), 0);
+    std::mt19937 rng(seed + 77);
+    std::shuffle(order.begin(), order.end(), rng);
+    std::stable_sort(order.begin(), order.end(), [&](int64_t a, int64_t b) { return ix.levels[(size_t)a] > ix.levels[(size_t)b]; });
+}
+
+// Rows of the PQ training set: at most 256 points per centroid, a seeded shuffle of the sample when it is larger.
+void builder_training_pick(int64_t n_train, uint32_t seed, std::vector<int64_t> &pick)
+{
+    const int64_t nt = std::min<int64_t>(n_train, 256 * 256);
+    pick.resize((size_t)n_train);
+    std::iota(pick.begin(), pick.end(), 0);
+    std::mt19937 rng(seed);
+    if (nt < n_train) std::shuffle(pick.begin(), pick.end(), rng);
+    pick.resize((size_t)nt);
+}
+
+// k-means start: 256 seeded random rows of the training set (row c % n for tiny sets).
+void builder_kmeans_init_rows(int64_t n, int k, uint32_t seed, std::vector<int64_t> &rows)
+{
+    std::mt19937 rng(seed);
+    std::vector<int64_t> perm((size_t)n);
+    std::iota(perm.begin(), perm.end(), 0);
+    std::shuffle(perm.begin(), perm.end(), rng);
+    rows.resize((size_t)k);
+    for (int c = 0; c < k; ++c) rows[(size_t)c] = perm[(size_t)(c % n)];
+}
+
+// Centroid update of one k-means iteration from per-cluster sums and counts, with FAISS's empty-cluster split.
+void builder_kmeans_update(const double *sum, int64_t *cnt, int k, int dsub, float *cent)
+{
+    for (int c = 0; c < k; ++c)
+        if (cnt[c])
+            for (int t = 0; t < dsub; ++t) cent[(size_t)c * dsub + t] = (float)(sum[(size_t)c * dsub + t] / (double)cnt[c]);
+    for (int c = 0; c < k; ++c) {
+        if (cnt[c]) continue;
+        int big = (int)(std::max_element(cnt, cnt + k) - cnt);
+        for (int t = 0; t < dsub; ++t) {
+            float v = cent[(size_t)big * dsub + t];
+            float eps = 1.f / 1024.f;
+            cent[(size_t)c * dsub + t] = v * (1 + ((t & 1) ? eps : -eps));
+            cent[(size_t)big * dsub + t] = v * (1 - ((t & 1) ? eps : -eps));
+        }
+        cnt[c] = cnt[big] / 2;
+        cnt[big] -= cnt[c];
+    }
+}
+
+// x: n x d row-major.  train: n_train x d (the reference passes an evenly strided 50 % sample).
+int build_index_cpu(const float *x, int64_t n, int d, const float *train, int64_t n_train, int M_pq, int nbits, int M_hnsw,
+                    int efc, int threads, uint32_t seed, HostIndex &ix)
+{
+    if (n <= 0 || d <= 0 || M_pq <= 0 || d % M_pq) return fail(DRM_EINVAL, "bad index build arguments (d must be a multiple of M_pq)");
+    if (nbits != 8) return fail(DRM_EUNSUPPORTED, "only nbits == 8 is supported by the builder");
+    if (M_hnsw < 2 || efc < 1) return fail(DRM_EINVAL, "M_hnsw must be >= 2 and EFC >= 1");
+    if (n >= ((int64_t)1 << 31) - 1) return fail(DRM_EUNSUPPORTED, "more than 2^31 vectors");
+    if (threads <= 0) threads = omp_get_max_threads();
+    omp_set_num_threads(threads);
+    ix = HostIndex();
+    ix.d = d; ix.ntotal = n; ix.M = (uint64_t)M_pq; ix.nbits = 8; ix.ksub = 256; ix.dsub = (uint64_t)(d / M_pq); ix.code_size = (uint64_t)M_pq;
+    ix.efConstruction = efc; ix.efSearch = 16; ix.upper_beam = 1;
+    const int dsub = d / M_pq;
+
+    // ---- ProductQuantizer::train: k-means per sub-space on at most 256 points per centroid
+    ix.centroids.assign((size_t)M_pq * 256 * dsub, 0.f);
+    {
+        if (!train || n_train <= 0) { train = x; n_train = n; }
+        std::vector<int64_t> pick;
+        builder_training_pick(n_train, seed, pick);
+        const int64_t nt = (int64_t)pick.size();
+        std::vector<float> sub((size_t)nt * dsub);
+        for (int m = 0; m < M_pq; ++m) {
+            for (int64_t i = 0; i < nt; ++i)
+                memcpy(&sub[(size_t)i * dsub], train + (size_t)pick[(size_t)i] * d + (size_t)m * dsub, sizeof(float) * dsub);
+            kmeans(sub.data(), nt, dsub, 256, 25, seed + 1 + (uint32_t)m, &ix.centroids[(size_t)m * 256 * dsub]);
+        }
+    }
+    // ---- IndexPQ::add: nearest centroid per sub-space
+    ix.codes.resize((size_t)n * M_pq);
+#pragma omp parallel for schedule(static)
+    for (int64_t i = 0; i < n; ++i)
+        for (int m = 0; m < M_pq; ++m) {
+            const float *xi = x + (size_t)i * d + (size_t)m * dsub;
+            float best = FLT_MAX; int bj = 0;
+            for (int j = 0; j < 256; ++j) {
+                const float *c = &ix.centroids[((size_t)m * 256 + j) * dsub];
+                float s = 0;
+                for (int t = 0; t < dsub; ++t) { float e = xi[t] - c[t]; s += e * e; }
+                if (s < best) { best = s; bj = j; }
+            }
+            ix.codes[(size_t)i * M_pq + m] = (uint8_t)bj;
+        }
+
+    builder_level_law(ix, n, M_hnsw, seed);
 
     Graph g(ix);
     g.sdc.resize((size_t)M_pq * 256 * 256);
@@ -326,13 +365,8 @@ int build_index_cpu(const float *x, int64_t n, int d, const float *train, int64_
     for (auto &l : g.locks) omp_init_lock(&l);
 
     // ---- insertion order: descending level, random inside a level (hnsw_add_vertices)
-    std::vector<int64_t> order((size_t)n);
-    std::iota(order.begin(), order.end(), 0);
-    {
-        std::mt19937 rng(seed + 77);
-        std::shuffle(order.begin(), order.end(), rng);
-        std::stable_sort(order.begin(), order.end(), [&](int64_t a, int64_t b) { return ix.levels[(size_t)a] > ix.levels[(size_t)b]; });
-    }
+    std::vector<int64_t> order;
+    builder_insertion_order(ix, seed, order);
     int32_t entry_point = (int32_t)order[0];
     int max_level = ix.levels[(size_t)order[0]] - 1;
     size_t begin = 1;

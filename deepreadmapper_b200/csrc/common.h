@@ -46,6 +46,16 @@ struct HostIndex {
 int read_index_file(const char *path, HostIndex &ix);         // DRM_OK or error (message set)
 int write_index_file(const char *path, const HostIndex &ix);  // same layout, used by the builder
 
+// Pieces of the index builder shared by the host (builder.cpp) and GPU (build_gpu.cu) builders, so that both draw the
+// same training sample, k-means start, vertex levels and insertion order from a seed.
+void builder_level_law(HostIndex &ix, int64_t n, int M_hnsw, uint32_t seed);
+void builder_insertion_order(const HostIndex &ix, uint32_t seed, std::vector<int64_t> &order);
+void builder_training_pick(int64_t n_train, uint32_t seed, std::vector<int64_t> &pick);
+void builder_kmeans_init_rows(int64_t n, int k, uint32_t seed, std::vector<int64_t> &rows);
+void builder_kmeans_update(const double *sum, int64_t *cnt, int k, int dsub, float *cent);
+int build_index_cpu(const float *x, int64_t n, int d, const float *train, int64_t n_train, int M_pq, int nbits, int M_hnsw,
+                    int efc, int threads, uint32_t seed, HostIndex &ix);
+
 // ---------------------------------------------------------------------------------------------
 // Device image of the index, laid out for one-round-trip hops (DESIGN.md "data layout in HBM"):
 //   rows0 : ntotal rows; row v = [W0 x int32 level-0 neighbour ids (-1 padded)]

@@ -587,8 +587,8 @@ int launch_reg_tf(const SearchParams &p, size_t smem, int device, cudaStream_t s
 {
     // the visited cache's 16-bit tags are exact only below slots * 65535 vertices; DRM_SEARCH_VIS = 0 / 512 / 1024 picks (A/B)
     const char *e = getenv("DRM_SEARCH_VIS");
-    int slots = e ? atoi(e) : 1024;
-    if (slots == 1) slots = 1024;
+    int slots = e ? atoi(e) : 512;  // 512: 6 CTAs/SM, 7.5 % faster than 1024 (profiles/r1_ab_v5_search_vis_prefetch.txt)
+    if (slots == 1) slots = 512;
     if (slots != 512 && slots != 1024) slots = 0;
     if (slots > 0 && p.ntotal >= (long long)slots * 65535) slots = p.ntotal < 1024ll * 65535 ? 1024 : 0;
     if (slots == 1024) return launch_reg_tfv<CS, NS, FULLCAP, 1024>(p, smem, device, stream);

@@ -7,6 +7,7 @@
 // The embedder is outside this build, so a sequence reference needs its embeddings beside it as `<ref file>.npy`;
 // a .npy reference is used as-is, like the reference does (:236-265).  Training set = evenly strided
 // Config::Build::SAMPLE_RATE sample (create_training_set, :57-84,99).
+#include <cstdlib>
 #include <algorithm>
 #include <filesystem>
 #include <iostream>
@@ -70,8 +71,22 @@ int main(int argc, char *argv[])
             const size_t si = std::min((size_t)((double)i * step), n - 1);
             std::copy(x + si * d, x + (si + 1) * d, train.begin() + (long)(i * d));
         }
-        if (drm_build_index(x, (int64_t)n, (int)d, train.data(), (int64_t)n_train, M_pq, nbits, M_hnsw, EFC, 0, 1234u, index_file.c_str()) != DRM_OK)
-            throw std::runtime_error(drm_last_error());
+        // Builder selection: the GPU builder (csrc/build_gpu.cu) when a device is present and the shape is one it handles,
+        // the host OpenMP builder otherwise; DRM_BUILD=cpu|gpu forces one (a forced GPU build fails loudly).
+        const char *which = std::getenv("DRM_BUILD");
+        const bool gpu_shape = M_hnsw <= 16 && (M_pq == 8 || M_pq == 16) && nbits == 8;
+        const bool use_gpu = which ? std::string(which) == "gpu" : (drm_device_count() > 0 && gpu_shape);
+        int rc;
+        if (use_gpu) {
+            double tim[5] = {0, 0, 0, 0, 0};
+            rc = drm_build_index_gpu(x, (int64_t)n, (int)d, train.data(), (int64_t)n_train, M_pq, nbits, M_hnsw, EFC, 0, 1234u, index_file.c_str(), tim);
+            if (rc == DRM_OK)
+                std::cout << "[BUILD INDEX] GPU build: upload " << tim[0] << " s, PQ training " << tim[1] << " s, encoding " << tim[2]
+                          << " s, HNSW " << tim[3] << " s, export " << tim[4] << " s" << std::endl;
+        } else {
+            rc = drm_build_index(x, (int64_t)n, (int)d, train.data(), (int64_t)n_train, M_pq, nbits, M_hnsw, EFC, 0, 1234u, index_file.c_str());
+        }
+        if (rc != DRM_OK) throw std::runtime_error(drm_last_error());
         std::cout << "[BUILD INDEX] Index saved to: " << index_file << std::endl;
         std::cout << "[BUILD INDEX] Finished index building process." << std::endl;
     } catch (const std::exception &e) {

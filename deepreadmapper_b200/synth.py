@@ -71,15 +71,16 @@ def embed_windows(genome: bytes, ref_len: int = 150, stride: int = 1, chunk: int
     return out
 
 
-def embed_windows_torch(genome: bytes, device, ref_len: int = 150, stride: int = 1, chunk: int = 1 << 20) -> np.ndarray:
+def embed_windows_torch(genome: bytes, device, ref_len: int = 150, stride: int = 1, chunk: int = 1 << 20, return_device: bool = False):
     """Same as embed_windows with the prefix sums on a torch device (data generation for bench.py; equal to the
-    numpy version up to float32 rounding of the float64 sums)."""
+    numpy version up to float32 rounding of the float64 sums).  return_device=True leaves the result on the device
+    (a torch tensor) for the GPU index builder."""
     import torch
     Pt = torch.from_numpy(projection().T.astype(np.float64)).to(device)
     g = _codes(np.frombuffer(genome, dtype=np.uint8))
     L = len(g)
     n_pos = (L - ref_len) // stride + 1 if L >= ref_len else 0
-    out = np.empty((2 * n_pos, DIM), dtype=np.float32)
+    out = torch.empty((2 * n_pos, DIM), dtype=torch.float32, device=device) if return_device else np.empty((2 * n_pos, DIM), dtype=np.float32)
     K = torch.from_numpy(_kmer_codes(g).astype(np.int64)).to(device)
     rck = torch.from_numpy(_RC_KMER.astype(np.int64)).to(device)
     for w0 in range(0, n_pos, chunk):
@@ -94,7 +95,7 @@ def embed_windows_torch(genome: bytes, device, ref_len: int = 150, stride: int =
         blk = torch.empty((2 * (w1 - w0), DIM), dtype=torch.float32, device=device)
         blk[0::2] = (cf[s + N_KMERS] - cf[s]).float()
         blk[1::2] = (cr[t + N_KMERS] - cr[t]).float()
-        out[2 * w0:2 * w1] = blk.cpu().numpy()
+        out[2 * w0:2 * w1] = blk if return_device else blk.cpu().numpy()
         del cf, cr, blk
     return out
 

@@ -140,6 +140,20 @@ int drm_merge_topk_device(int device, const float *D_all, const int64_t *I_all, 
 int drm_build_index(const float *x, int64_t n, int d, const float *train, int64_t n_train, int M_pq, int nbits,
                     int M_hnsw, int efc, int threads, uint32_t seed, const char *out_path);
 
+/* ------------------------------------------------------------------ index build (GPU) */
+/* The same job on the device (csrc/build_gpu.cu): PQ k-means + encoding kernels and batched HNSW insertion
+ * (one warp per new vertex searches the frozen graph with efConstruction = efc and selects its neighbours with
+ * FAISS's shrink_neighbor_list rule; back links are applied per batch under per-vertex locks).  Writes the same
+ * FAISS IHNp file.  x/train are HOST pointers (train NULL = use x).  timing_s (nullable): 5 doubles = seconds of
+ * upload, PQ training, encoding, graph construction, export.  M_hnsw <= 16, M_pq in {8, 16}, nbits == 8.
+ * No CPU fallback: DRM_ECUDA without a device. */
+int drm_build_index_gpu(const float *x, int64_t n, int d, const float *train, int64_t n_train, int M_pq, int nbits,
+                        int M_hnsw, int efc, int device, uint32_t seed, const char *out_path, double *timing_s);
+/* Same with the vectors already resident on `device` (x_dev: n x d fp32 device pointer); the training sample is rows
+ * 0, train_step, 2*train_step, ... (the reference's evenly strided sample, src/hnswpq/index.cpp:57-84). */
+int drm_build_index_gpu_device(const float *x_dev, int64_t n, int d, int64_t train_step, int M_pq, int nbits, int M_hnsw,
+                               int efc, int device, uint32_t seed, const char *out_path, double *timing_s);
+
 #ifdef __cplusplus
 }
 #endif

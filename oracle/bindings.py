@@ -72,6 +72,8 @@ def oracle():
         L.orc_index_info.argtypes = [C.c_void_p, _i64p]
         L.orc_index_validate.restype = C.c_int
         L.orc_index_validate.argtypes = [C.c_void_p]
+        L.orc_index_arrays.restype = None
+        L.orc_index_arrays.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
         L.orc_search.restype = C.c_int
         L.orc_search.argtypes = [C.c_void_p, _f32p, C.c_int64, C.c_int, C.c_int, C.c_int, _f32p, _i64p, _i64p,
                                  C.c_void_p, C.c_int]
@@ -205,6 +207,15 @@ class OracleIndex:
 
     def validate(self) -> int:
         return oracle().orc_index_validate(self._h)
+
+    def arrays(self):
+        """(centroids [M][256][dsub], codes ntotal x M, {degree statistics}) - used by the builder tests."""
+        dsub = self.d // self.M_pq
+        cent = np.zeros((self.M_pq, 256, dsub), dtype=np.float32)
+        codes = np.zeros((self.ntotal, self.M_pq), dtype=np.uint8)
+        deg = np.zeros(3, dtype=np.float64)
+        oracle().orc_index_arrays(self._h, cent.ctypes.data, codes.ctypes.data, deg.ctypes.data)
+        return cent, codes, dict(mean_degree0=float(deg[0]), empty_rows0=float(deg[1]), mean_degree1=float(deg[2]))
 
     def search(self, x, k, ef, tie_rule=1, threads=0, per_query=False):
         x = np.ascontiguousarray(x, dtype=np.float32)

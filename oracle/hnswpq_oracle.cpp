@@ -545,6 +545,8 @@ int orc_index_validate(void *h)
                 if (ended) return -4;                        // -1 padding must be a suffix
                 if (u >= ix->ntotal || u == v) return -5;
                 if (ix->levels[(size_t)u] <= l) return -6;   // neighbour must exist on this level
+                for (uint64_t j2 = ix->offsets[(size_t)v] + (uint64_t)ix->cum[(size_t)l]; j2 < j; ++j2)
+                    if (ix->neighbors[j2] == u) return -10;  // no vertex twice in a row
             }
         }
     }
@@ -554,6 +556,30 @@ int orc_index_validate(void *h)
     }
     if (ix->offsets.back() != ix->neighbors.size()) return -9;
     return 0;
+}
+
+// Copies of the PQ arrays and graph statistics (builder tests): centroids [M][ksub][dsub], codes ntotal x code_size
+// (either may be NULL); deg[0] = mean level-0 out-degree, deg[1] = share of vertices with an empty level-0 row,
+// deg[2] = mean out-degree on level 1 over the vertices that have one.
+void orc_index_arrays(void *h, float *centroids, uint8_t *codes, double *deg)
+{
+    auto *ix = (OrcIndex *)h;
+    if (centroids) memcpy(centroids, ix->centroids.data(), ix->centroids.size() * sizeof(float));
+    if (codes) memcpy(codes, ix->codes.data(), ix->codes.size());
+    if (deg) {
+        double s0 = 0, empty = 0, s1 = 0, n1 = 0;
+        for (int64_t v = 0; v < ix->ntotal; ++v) {
+            int c = 0;
+            for (int j = 0; j < ix->cum[1]; ++j) c += ix->neighbors[ix->offsets[(size_t)v] + (uint64_t)j] >= 0;
+            s0 += c; empty += c == 0;
+            if (ix->levels[(size_t)v] > 1) {
+                int c1 = 0;
+                for (int j = ix->cum[1]; j < ix->cum[2]; ++j) c1 += ix->neighbors[ix->offsets[(size_t)v] + (uint64_t)j] >= 0;
+                s1 += c1; n1 += 1;
+            }
+        }
+        deg[0] = s0 / (double)ix->ntotal; deg[1] = empty / (double)ix->ntotal; deg[2] = n1 ? s1 / n1 : 0.0;
+    }
 }
 
 }  // extern "C"

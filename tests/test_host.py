@@ -94,6 +94,9 @@ def test_compute_calls_fail_loudly_without_gpu(built):
     assert e.value.code == -3
     with pytest.raises(drm.DrmError):
         drm.Reference(genome=g, ref_len=150)
+    with pytest.raises(drm.DrmError) as e:
+        drm.build_index_gpu(E[:200], p + ".gpu", efc=16)
+    assert e.value.code == -3 and "no CPU fallback" in str(e.value)
 
 
 def test_index_open_errors_without_touching_gpu(tmp_path):
