@@ -37,6 +37,29 @@ def log(*a):
     print("[bench]", *a, file=sys.stderr, flush=True)
 
 
+_REAL_STDOUT = None
+
+
+def own_stdout():
+    """The contract is ONE JSON line on stdout.  Libraries write there too (NCCL prints its version banner on fd 1 when
+    NCCL_DEBUG is set in the environment), so fd 1 is pointed at stderr for the whole run and the JSON line goes to a
+    private duplicate of the original stdout."""
+    global _REAL_STDOUT
+    if _REAL_STDOUT is None:
+        sys.stdout.flush()
+        _REAL_STDOUT = os.dup(1)
+        os.dup2(2, 1)
+
+
+def emit(line):
+    data = (json.dumps(line) + "\n").encode()
+    if _REAL_STDOUT is None:
+        sys.stdout.write(data.decode())
+        sys.stdout.flush()
+    else:
+        os.write(_REAL_STDOUT, data)
+
+
 def parse():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -49,6 +72,8 @@ def parse():
     ap.add_argument("--cache", default=os.environ.get("DRM_CACHE", os.path.join(tempfile.gettempdir(), "drm_b200_cache")))
     ap.add_argument("--cpu-sample", type=int, default=0, help="reads in the CPU baseline sample (0 = 600 per host core)")
     ap.add_argument("--skip-cpu", action="store_true")
+    ap.add_argument("--builder", default="gpu", choices=["gpu", "cpu"],
+                    help="who builds the one-off index file: the GPU builder (csrc/build_gpu.cu) or the host OpenMP builder")
     ap.add_argument("--workload", default="dense", choices=["dense", "sharded", "sparse"],
                     help="dense = configs[1] (index replicated, reads sharded, no collective; the driver's run); "
                          "sharded = configs[4] scaled down (index sharded by position, all-gather + merge); "
@@ -59,7 +84,7 @@ def parse():
 
 def workload_paths(args):
     os.makedirs(args.cache, exist_ok=True)
-    tag = f"g{args.genome_bases}_efc{args.efc}"
+    tag = f"g{args.genome_bases}_efc{args.efc}_{getattr(args, 'builder', 'gpu')}"
     return os.path.join(args.cache, f"ecoli_dense_{tag}.index")
 
 
@@ -77,24 +102,49 @@ def make_genome(args):
     return synth.random_genome(args.genome_bases, 42)
 
 
-def ensure_index(args, genome, device=None):
-    """Builds the config's index once per box (hnswpq_index's job - outside the timed path) and caches the file."""
+def build_index_file(args, genome, path, device, stride=1, seed=1234, threads=None):
+    """hnswpq_index's job for one genome (slice): surrogate embeddings of every window, then the index file.  With a CUDA
+    device the embeddings stay on it and the GPU builder makes the file; the host OpenMP builder is used when asked for
+    (--builder cpu), when there is no device, or - loudly - when the GPU build fails.  Returns (n_vectors, 'gpu'|'cpu')."""
     import deepreadmapper_b200 as drm
     from deepreadmapper_b200 import synth
+    tmp = path + f".tmp{os.getpid()}"
+    if device is not None and getattr(args, "builder", "gpu") == "gpu":
+        import torch
+        E = synth.embed_windows_torch(genome, device, stride=stride, return_device=True)
+        try:
+            tim = drm.build_index_gpu_device(E.data_ptr(), E.shape[0], E.shape[1], tmp, train_step=2, M_pq=8, nbits=8, M_hnsw=16,
+                                             efc=args.efc, device=torch.device(device).index or 0, seed=seed)
+            os.replace(tmp, path)
+            nv = int(E.shape[0])
+            log(f"GPU index build of {nv} vectors (EFC={args.efc}): " + ", ".join(f"{k} {v:.2f}s" for k, v in tim.items()))
+            del E
+            torch.cuda.empty_cache()
+            return nv, "gpu"
+        except drm.DrmError as e:
+            log(f"GPU index build FAILED ({e}); falling back to the host builder")
+            E = E.cpu().numpy()
+    elif device is not None:
+        E = synth.embed_windows_torch(genome, device, stride=stride)
+    else:
+        E = synth.embed_windows(genome, stride=stride)
+    th = threads or host_threads()
+    log(f"host index build of {E.shape[0]} vectors (EFC={args.efc}) on {th} threads")
+    drm.build_index(E, tmp, M_pq=8, nbits=8, M_hnsw=16, efc=args.efc, seed=seed, threads=th)
+    os.replace(tmp, path)
+    return int(E.shape[0]), "cpu"
+
+
+def ensure_index(args, genome, device=None):
+    """Builds the config's index once per box (hnswpq_index's job - outside the timed path) and caches the file."""
     path = workload_paths(args)
     if os.path.exists(path):
         return path, 0.0
     t0 = time.time()
-    if device is not None:
-        E = synth.embed_windows_torch(genome, device)
-    else:
-        E = synth.embed_windows(genome)
-    log(f"embedded {E.shape[0]} windows in {time.time() - t0:.1f}s; building HNSW-PQ index (EFC={args.efc}) on {host_threads()} host cores")
-    t1 = time.time()
-    tmp = path + f".tmp{os.getpid()}"
-    drm.build_index(E, tmp, M_pq=8, nbits=8, M_hnsw=16, efc=args.efc, seed=1234, threads=host_threads())
-    os.replace(tmp, path)
-    log(f"index built in {time.time() - t1:.1f}s -> {path}")
+    n, who = build_index_file(args, genome, path, device)
+    with open(path + ".who", "w") as f:
+        f.write(who)
+    log(f"index of {n} vectors built by the {who} builder in {time.time() - t0:.1f}s -> {path}")
     return path, time.time() - t0
 
 
@@ -164,9 +214,13 @@ def cpu_reference_run(args, genome, index_path, reads, Q, n_sample, threads):
 
 
 def base_config(args, n_gpus):
+    try:
+        who = open(workload_paths(args) + ".who").read().strip()
+    except OSError:
+        who = getattr(args, "builder", "gpu")
     return {"workload": "configs[1]: E. coli-sized dense index (random genome, both strands) + synthetic reads, search EF=128 K=128 + SW rerank of K candidates",
             "genome_bases": args.genome_bases, "n_vectors": 2 * (args.genome_bases - REF_LEN + 1), "ref_len": REF_LEN, "stride": 1,
-            "M_pq": 8, "nbits": 8, "M_hnsw": 16, "EFC": args.efc, "EF": EF, "K": K, "reads_per_gpu": args.reads,
+            "M_pq": 8, "nbits": 8, "M_hnsw": 16, "EFC": args.efc, "index_built_by": who + " builder (outside the timed path)", "EF": EF, "K": K, "reads_per_gpu": args.reads,
             "sharding": f"reads sharded over {n_gpus} GPU(s), index replicated, no collective",
             "l2": "inputs larger than L2 (index image 3.6 GB, read batch 0.66 GB); no explicit flush"}
 
@@ -204,7 +258,7 @@ def run_reference(args):
             "dtype": "f32 ADC distances + int32 SW", "data": "synthetic", "config": base_config(args, args.gpus),
             "cpu_baseline": {"value": value, "unit": "reads/s", "cores": threads, "kind": kind, "sample": sample},
             "e2e": {"value": value, "unit": "reads/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}
-    print(json.dumps(line), flush=True)
+    emit(line)
     return 0
 
 
@@ -380,14 +434,15 @@ def run_ours(args):
                         "traffic_source": "ncu capture of one 131072-read launch (profiles/r1_ncu_sw_rerank_profile_kernel_v2.txt): 2.2 KB/read, i.e. 4 GB/s - not an HBM-bound kernel",
                         "peak_source": "measured pipe rates (profiles/r1_ubench_pipes.txt, r1_ubench_alu.txt) x 3.5 instructions per cell pair at clocks.max.sm; DESIGN.md §4.3",
                         "cells_per_launch": cells, "ms_per_step": sw_ms}
-    print(json.dumps(line), flush=True)
+    emit(line)
     if world > 1:
         dist.destroy_process_group()
     return 0
 
 
 def run_sharded(args):
-    """configs[4] scaled to what a CPU index build allows inside a bench run: the reference windows are split by position
+    """configs[4] (size set by --genome-bases; the default is the E. coli-sized genome, --genome-bases 31250000 at N = 1 is
+    one of the eight 62.5 M-vector shards of the 250 Mbp configuration): the reference windows are split by position
     into WORLD shards (one HNSW-PQ graph per GPU), every rank searches every read of a chunk against its shard, the
     per-shard top-K lists are exchanged with ONE all-gather (NCCL over NVLink) and merged per read by the CUDA merge
     kernel; the SW rerank of the merged candidates is read-sharded again (genome replicated).  Total work is fixed as
@@ -410,14 +465,12 @@ def run_sharded(args):
     n_windows = 2 * (len(genome) - REF_LEN + 1)
     lo, hi = sharded.shard_bounds(n_windows, world)[rank]
     os.makedirs(args.cache, exist_ok=True)
-    path = os.path.join(args.cache, f"shard_g{args.genome_bases}_efc{args.efc}_w{world}_r{rank}.index")
+    path = os.path.join(args.cache, f"shard_g{args.genome_bases}_efc{args.efc}_{args.builder}_w{world}_r{rank}.index")
     if not os.path.exists(path):
         t0 = time.time()
         sub = genome[lo // 2: hi // 2 + REF_LEN - 1]
-        E = synth.embed_windows_torch(sub, f"cuda:{local}")
-        assert E.shape[0] == hi - lo, (E.shape, lo, hi)
-        drm.build_index(E, path + ".tmp", M_pq=8, nbits=8, M_hnsw=16, efc=args.efc, seed=1234 + rank, threads=max(1, host_threads() // world))
-        os.replace(path + ".tmp", path)
+        nv, who = build_index_file(args, sub, path, f"cuda:{local}", seed=1234 + rank, threads=max(1, host_threads() // world))
+        assert nv == hi - lo, (nv, lo, hi)
         log(f"rank {rank}: shard [{lo}, {hi}) built in {time.time() - t0:.1f}s")
     barrier()
     ix = drm.Index(path, devices=[local])
@@ -489,7 +542,7 @@ def run_sharded(args):
                 "gpu_launches": int(args.steps * len(chunks) * (2 + 3 * ((args.chunk // world + 131071) // 131072))), "clocks": clocks,
                 "sw_gcups": float(cells.item()) / args.steps / (ms / 1e3) / 1e9,
                 "checks": {"merged_rows_sorted": ok_sorted, "merged_ids_unique": uniq, "merged_top1_is_planted_position": top1}}
-        print(json.dumps(line), flush=True)
+        emit(line)
     if world > 1:
         dist.destroy_process_group()
     return 0
@@ -528,13 +581,11 @@ def run_sparse(args):
     torch.cuda.set_device(0)
     genome = make_genome(args)
     os.makedirs(args.cache, exist_ok=True)
-    path = os.path.join(args.cache, f"ecoli_sparse{stride}_g{args.genome_bases}_efc{args.efc}.index")
+    path = os.path.join(args.cache, f"ecoli_sparse{stride}_g{args.genome_bases}_efc{args.efc}_{args.builder}.index")
     if not os.path.exists(path):
         t0 = time.time()
-        E = synth.embed_windows_torch(genome, "cuda:0", stride=stride)
-        drm.build_index(E, path + ".tmp", M_pq=8, nbits=8, M_hnsw=16, efc=args.efc, seed=1234, threads=host_threads())
-        os.replace(path + ".tmp", path)
-        log(f"sparse index ({E.shape[0]} vectors) built in {time.time() - t0:.1f}s")
+        nv, who = build_index_file(args, genome, path, "cuda:0", stride=stride)
+        log(f"sparse index ({nv} vectors) built by the {who} builder in {time.time() - t0:.1f}s")
     ix = drm.Index(path, devices=[0])
     ref = drm.Reference(genome=genome, ref_len=REF_LEN, devices=[0])
     n = min(args.reads, 100_000)
@@ -594,12 +645,13 @@ def run_sparse(args):
             "config": {"workload": "configs[2]: E. coli-sized sparse index (stride 8) + post-process window expansion + SW rerank",
                        "genome_bases": args.genome_bases, "n_vectors": int(ix.ntotal), "stride": stride, "K_clusters": kc, "K": kfinal, "EF": EF,
                        "reads": n}, "modes": out}
-    print(json.dumps(line), flush=True)
+    emit(line)
     return 0
 
 
 if __name__ == "__main__":
     a = parse()
+    own_stdout()
     if a.impl == "reference":
         sys.exit(run_reference(a))
     sys.exit(run_sharded(a) if a.workload == "sharded" else run_sparse(a) if a.workload == "sparse" else run_ours(a))

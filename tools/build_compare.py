@@ -49,6 +49,7 @@ def main():
     bench.log(f"GPU build: {files['gpu']['build_s']:.1f}s wall incl. file write; stages {tim}")
     if a.cpu:
         t0 = time.time()
+        a.builder = "cpu"
         cpath, _ = bench.ensure_index(a, genome, "cuda:0")
         files["cpu"] = dict(path=cpath, build_s=time.time() - t0)
     del E
