@@ -33,7 +33,9 @@ class SearchStats(C.Structure):
 EXPORTS = ["drm_last_error", "drm_device_count", "drm_version", "drm_index_open", "drm_index_close", "drm_index_info",
            "drm_search", "drm_search_device", "drm_ref_open_genome", "drm_ref_open_windows", "drm_ref_close",
            "drm_sw_pairs", "drm_sw_rerank", "drm_sw_rerank_device", "drm_merge_topk_device", "drm_build_index",
-           "drm_search_rerank", "drm_build_index_gpu", "drm_build_index_gpu_device"]
+           "drm_search_rerank", "drm_build_index_gpu", "drm_build_index_gpu_device", "drm_fasta_clean", "drm_ref_open_fasta",
+           "drm_reads_open_fastq", "drm_reads_close", "drm_reads_info", "drm_reads_copy_out", "drm_reads_device",
+           "drm_search_rerank_reads"]
 
 
 def lib_path() -> str:
@@ -66,6 +68,16 @@ def lib():
         L.drm_sw_rerank_device.argtypes = [vp, i32, i32, vp, i64, i64, vp, vp, i32, i64, i64, i64, vp, vp, vp, vp, vp, vp]
         L.drm_merge_topk_device.argtypes = [i32, vp, vp, i32, i64, i32, vp, vp, vp]
         L.drm_build_index.argtypes = [vp, i64, i32, vp, i64, i32, i32, i32, i32, i32, C.c_uint32, C.c_char_p]
+        L.drm_fasta_clean.argtypes = [vp, i64, i32, vp, i64, C.POINTER(i64)]
+        L.drm_ref_open_fasta.argtypes = [vp, i64, i32, C.POINTER(i32), i32, C.POINTER(vp), C.POINTER(i64)]
+        L.drm_reads_open_fastq.argtypes = [vp, i64, C.POINTER(i32), i32, C.POINTER(vp)]
+        L.drm_reads_close.argtypes = [vp]
+        L.drm_reads_close.restype = None
+        L.drm_reads_info.argtypes = [vp, vp]
+        L.drm_reads_copy_out.argtypes = [vp, vp, vp]
+        L.drm_reads_device.argtypes = [vp, i32, C.POINTER(vp), C.POINTER(vp)]
+        L.drm_search_rerank_reads.argtypes = [vp, vp, i32, vp, i64, i32, i32, i32, vp, i64, i64, i64, vp, vp, vp, vp,
+                                              C.POINTER(SearchStats), vp]
         L.drm_build_index_gpu.argtypes = [vp, i64, i32, vp, i64, i32, i32, i32, i32, i32, C.c_uint32, C.c_char_p, vp]
         L.drm_build_index_gpu_device.argtypes = [vp, i64, i32, i64, i32, i32, i32, i32, i32, C.c_uint32, C.c_char_p, vp]
         L.drm_search_rerank.argtypes = [vp, vp, i32, vp, i64, i32, i32, i32, vp, vp, i64, i64, i64, vp, vp, vp, vp,
@@ -146,11 +158,17 @@ def faiss_search(index: Index, query_data, k=128, ef=128):
 class Reference:
     """Reference windows on the GPU: a genome (dynamic fetch, id -> pos/strand) or a window table (static)."""
 
-    def __init__(self, genome=None, windows=None, ref_len=150, devices=None):
+    def __init__(self, genome=None, windows=None, ref_len=150, devices=None, fasta=None):
         arr, n = _devs(devices)
         h = C.c_void_p()
         self.ref_len = ref_len
-        if genome is not None:
+        if fasta is not None:  # the FASTA file's bytes: cleaned on the device (extract_FASTA_sequence)
+            data = bytes(fasta)
+            glen = C.c_int64(0)
+            buf = C.create_string_buffer(data, len(data)) if data else C.create_string_buffer(1)
+            _check(lib().drm_ref_open_fasta(C.addressof(buf), len(data), ref_len, arr, n, C.byref(h), C.byref(glen)))
+            self.form, self.length = 0, glen.value
+        elif genome is not None:
             g = genome.encode() if isinstance(genome, str) else bytes(genome)
             self.form, self.length = 0, len(g)
             _check(lib().drm_ref_open_genome(g, len(g), ref_len, arr, n, C.byref(h)))
@@ -258,6 +276,71 @@ def search_rerank(index: Index, ref: Reference, mode, q, q_flat_ptr, q_off, stri
     _check(lib().drm_search_rerank(index._h, ref._h, mode, q.ctypes.data, n, d, k_search, ef, qf, q_off.ctypes.data, stride, k,
                                    k_clusters, D.ctypes.data, I.ctypes.data, sw_scores.ctypes.data, sw_ids.ctypes.data,
                                    C.byref(st), tm.ctypes.data))
+    return D, I, sw_scores, sw_ids, {f: getattr(st, f) for f, _ in SearchStats._fields_}, tm
+
+
+def fasta_clean(data: bytes, device: int = 0) -> bytes:
+    """extract_FASTA_sequence (src/utils/parse_inputs.cpp:174-220) on the device: file bytes in, cleaned genome out."""
+    data = bytes(data)
+    src = C.create_string_buffer(data, len(data)) if data else C.create_string_buffer(1)
+    out = C.create_string_buffer(max(len(data), 1))
+    ln = C.c_int64(0)
+    _check(lib().drm_fasta_clean(C.addressof(src), len(data), device, C.addressof(out), len(data), C.byref(ln)))
+    return out.raw[:ln.value]
+
+
+class Reads:
+    """format_fastq (src/utils/parse_inputs.cpp:843-950) on the device: the reads of a FASTQ file ('<' + sequence + '>')
+    resident on every listed GPU."""
+
+    def __init__(self, fastq: bytes, devices=None):
+        arr, n = _devs(devices)
+        data = bytes(fastq)
+        src = C.create_string_buffer(data, len(data)) if data else C.create_string_buffer(1)
+        h = C.c_void_p()
+        _check(lib().drm_reads_open_fastq(C.addressof(src), len(data), arr, n, C.byref(h)))
+        self._h = h
+        info = np.zeros(4, dtype=np.int64)
+        _check(lib().drm_reads_info(h, info.ctypes.data))
+        self.n, self.nbytes, self.max_len, self.n_replicas = (int(v) for v in info)
+
+    def close(self):
+        if getattr(self, "_h", None):
+            lib().drm_reads_close(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def sequences(self):
+        """Host copy: list of bytes, one per read (decorated like the reference's query_seqs)."""
+        flat = C.create_string_buffer(max(self.nbytes, 1))
+        off = np.zeros(self.n + 1, dtype=np.int64)
+        _check(lib().drm_reads_copy_out(self._h, C.addressof(flat), off.ctypes.data))
+        raw = flat.raw
+        return [raw[off[i]:off[i + 1]] for i in range(self.n)]
+
+    def device_ptrs(self, slot=0):
+        f, o = C.c_void_p(), C.c_void_p()
+        _check(lib().drm_reads_device(self._h, slot, C.byref(f), C.byref(o)))
+        return f.value, o.value
+
+
+def search_rerank_reads(index: Index, ref: Reference, mode, q, reads: Reads, stride, k, k_clusters, k_search, ef):
+    """drm_search_rerank with the read sequences taken from a device-resident Reads handle."""
+    n, d = q.shape
+    D = np.empty((n, k_search), np.float32)
+    I = np.empty((n, k_search), np.int64)
+    sw_scores = np.empty((n, k), np.int32)
+    sw_ids = np.empty((n, k), np.uint64)
+    st = SearchStats()
+    tm = np.zeros(2, dtype=np.float64)
+    _check(lib().drm_search_rerank_reads(index._h, ref._h, mode, q.ctypes.data, n, d, k_search, ef, reads._h, stride, k, k_clusters,
+                                         D.ctypes.data, I.ctypes.data, sw_scores.ctypes.data, sw_ids.ctypes.data, C.byref(st),
+                                         tm.ctypes.data))
     return D, I, sw_scores, sw_ids, {f: getattr(st, f) for f, _ in SearchStats._fields_}, tm
 
 

@@ -35,6 +35,18 @@ struct drm_ref {
     std::vector<drm::DeviceRef> rep;
 };
 
+// FASTQ reads parsed on the device (input_kernels.cu): one copy per replica.
+struct ReadsRep {
+    int device = -1;
+    char *flat = nullptr;     // '<' + sequence + '>' of every read, back to back
+    int64_t *off = nullptr;   // n + 1 offsets into flat
+};
+struct drm_reads {
+    std::vector<ReadsRep> rep;
+    int64_t n = 0, bytes = 0;
+    int max_len = 0;
+};
+
 namespace {
 
 using namespace drm;
@@ -160,6 +172,11 @@ int open_ref(const char *bytes, int64_t len_bytes, int64_t len, int form, int re
 }
 
 }  // namespace
+
+static int search_rerank_impl(drm_index *ix, drm_ref *ref, int mode, const float *q, int64_t n, int d, int k_search, int ef,
+                              const char *q_flat, const int64_t *q_off, const drm_reads *reads, int64_t stride, int64_t k,
+                              int64_t k_clusters, float *D, int64_t *I, int32_t *sw_scores, uint64_t *sw_ids, drm_search_stats *stats,
+                              double *timing_ms);
 
 extern "C" {
 
@@ -397,9 +414,33 @@ int drm_search_rerank(drm_index *ix, drm_ref *ref, int mode, const float *q, int
                       const char *q_flat, const int64_t *q_off, int64_t stride, int64_t k, int64_t k_clusters, float *D,
                       int64_t *I, int32_t *sw_scores, uint64_t *sw_ids, drm_search_stats *stats, double *timing_ms)
 {
+    if (!q_flat || !q_off) return fail(DRM_EINVAL, "query sequences are required for the SW rerank");
+    return search_rerank_impl(ix, ref, mode, q, n, d, k_search, ef, q_flat, q_off, nullptr, stride, k, k_clusters, D, I, sw_scores,
+                              sw_ids, stats, timing_ms);
+}
+
+int drm_search_rerank_reads(drm_index *ix, drm_ref *ref, int mode, const float *q, int64_t n, int d, int k_search, int ef,
+                            const drm_reads *reads, int64_t stride, int64_t k, int64_t k_clusters, float *D, int64_t *I,
+                            int32_t *sw_scores, uint64_t *sw_ids, drm_search_stats *stats, double *timing_ms)
+{
+    if (!reads) return fail(DRM_EINVAL, "null reads handle");
+    if (n > reads->n) return fail(DRM_EINVAL, "more query embeddings than parsed reads");
+    return search_rerank_impl(ix, ref, mode, q, n, d, k_search, ef, nullptr, nullptr, reads, stride, k, k_clusters, D, I, sw_scores,
+                              sw_ids, stats, timing_ms);
+}
+
+}  // extern "C"
+
+// One implementation for both forms of the read sequences: host bytes + offsets (uploaded chunk by chunk), or a
+// drm_reads handle (already on every replica's device: nothing but the embeddings goes up).
+static int search_rerank_impl(drm_index *ix, drm_ref *ref, int mode, const float *q, int64_t n, int d, int k_search, int ef,
+                              const char *q_flat, const int64_t *q_off, const drm_reads *reads, int64_t stride, int64_t k,
+                              int64_t k_clusters, float *D, int64_t *I, int32_t *sw_scores, uint64_t *sw_ids, drm_search_stats *stats,
+                              double *timing_ms)
+{
     if (!ix || !ref) return fail(DRM_EINVAL, "null handle");
     if (n <= 0 || !q) return fail(DRM_EEMPTY, "Query data is empty");
-    if (!q_flat || !q_off) return fail(DRM_EINVAL, "query sequences are required for the SW rerank");
+    if (reads && reads->rep.size() != ix->rep.size()) return fail(DRM_EINVAL, "reads and index must be opened on the same devices");
     if (d != ix->rep[0].d) return fail(DRM_EINVAL, "query dimension does not match index dimension");
     if (ix->rep.size() != ref->rep.size()) return fail(DRM_EINVAL, "index and reference must be opened on the same devices");
     const int R = (int)ix->rep.size();
@@ -425,11 +466,16 @@ int drm_search_rerank(drm_index *ix, drm_ref *ref, int mode, const float *q, int
             std::lock_guard<std::mutex> lock(w.mu);
             int64_t max_qbytes = 0;
             int max_qlen = 0;
-            for (int64_t c0 = r0; c0 < r1; c0 += CH) {
-                int64_t c1 = std::min(r1, c0 + CH);
-                max_qbytes = std::max(max_qbytes, q_off[c1] - q_off[c0]);
+            if (reads) {
+                if (reads->rep[(size_t)g].device != dx.device) return fail(DRM_EINVAL, "reads and index replicas are on different devices");
+                max_qlen = reads->max_len;
+            } else {
+                for (int64_t c0 = r0; c0 < r1; c0 += CH) {
+                    int64_t c1 = std::min(r1, c0 + CH);
+                    max_qbytes = std::max(max_qbytes, q_off[c1] - q_off[c0]);
+                }
+                for (int64_t i = r0; i < r1; ++i) max_qlen = std::max<int64_t>(max_qlen, q_off[i + 1] - q_off[i]);
             }
-            for (int64_t i = r0; i < r1; ++i) max_qlen = std::max<int64_t>(max_qlen, q_off[i + 1] - q_off[i]);
             const int64_t chn = std::min<int64_t>(CH, r1 - r0);
             int rc;
             if (!w.cnt) DRM_CUDA_TRY(cudaMalloc(&w.cnt, 4 * sizeof(int64_t)));
@@ -463,15 +509,22 @@ int drm_search_rerank(drm_index *ix, drm_ref *ref, int mode, const float *q, int
                 StageSlot &s = w.slot[which];
                 const int64_t m = std::min(r1, c0 + CH) - c0;
                 DRM_CUDA_TRY(cudaStreamSynchronize(s.s));  // the slot's previous chunk (and its host offsets) are done
-                const int64_t qb = q_off[c0];
-                for (int64_t i = 0; i <= m; ++i) s.off[i] = q_off[c0 + i] - qb;
                 cudaMemcpyAsync(s.q, q + c0 * d, (size_t)m * d * 4, cudaMemcpyHostToDevice, s.s);
-                cudaMemcpyAsync(s.qs, q_flat + qb, (size_t)(q_off[c0 + m] - qb), cudaMemcpyHostToDevice, s.s);
-                cudaMemcpyAsync(s.qo, s.off, (size_t)(m + 1) * 8, cudaMemcpyHostToDevice, s.s);
+                const char *seq_dev = static_cast<char *>(s.qs);
+                const int64_t *off_dev = static_cast<int64_t *>(s.qo);
+                if (reads) {  // absolute offsets into the resident buffer
+                    seq_dev = reads->rep[(size_t)g].flat;
+                    off_dev = reads->rep[(size_t)g].off + c0;
+                } else {
+                    const int64_t qb = q_off[c0];
+                    for (int64_t i = 0; i <= m; ++i) s.off[i] = q_off[c0 + i] - qb;
+                    cudaMemcpyAsync(s.qs, q_flat + qb, (size_t)(q_off[c0 + m] - qb), cudaMemcpyHostToDevice, s.s);
+                    cudaMemcpyAsync(s.qo, s.off, (size_t)(m + 1) * 8, cudaMemcpyHostToDevice, s.s);
+                }
                 rc = launch_search(dx, static_cast<float *>(s.q), m, k_search, ef, static_cast<float *>(s.D), static_cast<int64_t *>(s.I),
                                    static_cast<int64_t *>(w.cnt), s.s);
                 if (rc != DRM_OK) return rc;
-                RerankArgs a{mode, static_cast<int64_t *>(s.I), m, k_search, static_cast<char *>(s.qs), static_cast<int64_t *>(s.qo), max_qlen,
+                RerankArgs a{mode, static_cast<int64_t *>(s.I), m, k_search, seq_dev, off_dev, max_qlen,
                              stride, k, k_clusters, static_cast<int32_t *>(s.sc), static_cast<uint64_t *>(s.id), nullptr,
                              static_cast<int32_t *>(w.dmin), nullptr};
                 rc = launch_rerank(dr, a, s.s);
@@ -520,6 +573,94 @@ int drm_search_rerank(drm_index *ix, drm_ref *ref, int mode, const float *q, int
     }
     if (k > 0 && min_c < k)
         return fail(DRM_ENOTENOUGH, "Not enough candidates (" + std::to_string(min_c) + " < " + std::to_string(k) + ")");
+    return DRM_OK;
+}
+
+extern "C" {
+
+/* ------------------------------------------------------------------ input side on the device */
+int drm_fasta_clean(const char *data, int64_t size, int device, char *out, int64_t cap, int64_t *len)
+{
+    if (!len) return fail(DRM_EINVAL, "null length output");
+    uint8_t *g = nullptr;
+    int rc = clean_fasta_device(data, size, device, &g, len);
+    if (rc != DRM_OK) return rc;
+    cudaError_t e = cudaSuccess;
+    if (out && *len <= cap && *len > 0) e = cudaMemcpy(out, g, (size_t)*len, cudaMemcpyDeviceToHost);
+    cudaFree(g);
+    if (e != cudaSuccess) return fail(DRM_ECUDA, std::string("drm_fasta_clean: ") + cudaGetErrorString(e));
+    if (out && *len > cap) return fail(DRM_EINVAL, "output buffer too small for the cleaned genome");
+    return DRM_OK;
+}
+
+int drm_ref_open_fasta(const char *data, int64_t size, int ref_len, const int *devices, int n_dev, drm_ref **out, int64_t *genome_len)
+{
+    if (!out) return fail(DRM_EINVAL, "null output handle");
+    *out = nullptr;
+    if (!devices || n_dev < 1) return fail(DRM_EINVAL, "bad reference arguments");
+    uint8_t *g = nullptr;
+    int64_t len = 0;
+    int rc = clean_fasta_device(data, size, devices[0], &g, &len);
+    if (rc != DRM_OK) return rc;
+    std::vector<char> host((size_t)std::max<int64_t>(len, 1));
+    cudaError_t e = len ? cudaMemcpy(host.data(), g, (size_t)len, cudaMemcpyDeviceToHost) : cudaSuccess;
+    cudaFree(g);
+    if (e != cudaSuccess) return fail(DRM_ECUDA, std::string("drm_ref_open_fasta: ") + cudaGetErrorString(e));
+    if (genome_len) *genome_len = len;
+    return open_ref(host.data(), len, len, 0, ref_len, devices, n_dev, out);
+}
+
+int drm_reads_open_fastq(const char *data, int64_t size, const int *devices, int n_dev, drm_reads **out)
+{
+    if (!out) return fail(DRM_EINVAL, "null output handle");
+    *out = nullptr;
+    if (!devices || n_dev < 1) return fail(DRM_EINVAL, "bad arguments to drm_reads_open_fastq");
+    drm_reads *r = new drm_reads();
+    for (int i = 0; i < n_dev; ++i) {
+        ReadsRep rep;
+        rep.device = devices[i];
+        int64_t n = 0, bytes = 0;
+        int max_len = 0;
+        int rc = parse_fastq_device(data, size, devices[i], &rep.flat, &rep.off, &n, &bytes, &max_len);
+        r->rep.push_back(rep);
+        if (rc != DRM_OK) { drm_reads_close(r); return rc; }
+        r->n = n; r->bytes = bytes; r->max_len = max_len;
+    }
+    *out = r;
+    return DRM_OK;
+}
+
+void drm_reads_close(drm_reads *r)
+{
+    if (!r) return;
+    for (auto &rep : r->rep) {
+        if (rep.device >= 0) cudaSetDevice(rep.device);
+        cudaFree(rep.flat); cudaFree(rep.off);
+    }
+    delete r;
+}
+
+int drm_reads_info(const drm_reads *r, int64_t *info)
+{
+    if (!r || !info) return fail(DRM_EINVAL, "null argument");
+    info[0] = r->n; info[1] = r->bytes; info[2] = r->max_len; info[3] = (int64_t)r->rep.size();
+    return DRM_OK;
+}
+
+int drm_reads_copy_out(const drm_reads *r, char *flat, int64_t *off)
+{
+    if (!r || r->rep.empty()) return fail(DRM_EINVAL, "null reads handle");
+    DRM_CUDA_TRY(cudaSetDevice(r->rep[0].device));
+    if (flat && r->bytes) DRM_CUDA_TRY(cudaMemcpy(flat, r->rep[0].flat, (size_t)r->bytes, cudaMemcpyDeviceToHost));
+    if (off) DRM_CUDA_TRY(cudaMemcpy(off, r->rep[0].off, (size_t)(r->n + 1) * sizeof(int64_t), cudaMemcpyDeviceToHost));
+    return DRM_OK;
+}
+
+int drm_reads_device(const drm_reads *r, int slot, const char **flat_dev, const int64_t **off_dev)
+{
+    if (!r || slot < 0 || slot >= (int)r->rep.size()) return fail(DRM_EINVAL, "bad reads handle or replica slot");
+    if (flat_dev) *flat_dev = r->rep[(size_t)slot].flat;
+    if (off_dev) *off_dev = r->rep[(size_t)slot].off;
     return DRM_OK;
 }
 

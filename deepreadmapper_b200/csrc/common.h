@@ -120,4 +120,9 @@ int launch_merge_topk(const float *D_all, const int64_t *I_all, int n_shards, in
                       int64_t *I_out, cudaStream_t stream);
 int launch_classify(const uint8_t *raw, uint8_t *cls, int64_t n, int *has_other_dev, cudaStream_t stream);
 
+// Input side on the device (input_kernels.cu).  Output buffers are fresh cudaMalloc allocations on `device` owned by the caller.
+int clean_fasta_device(const char *data, int64_t size, int device, uint8_t **d_genome, int64_t *len);
+int parse_fastq_device(const char *data, int64_t size, int device, char **d_flat, int64_t **d_off, int64_t *n_reads,
+                       int64_t *flat_bytes, int *max_len);
+
 }  // namespace drm

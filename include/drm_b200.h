@@ -47,6 +47,7 @@ extern "C" {
 
 typedef struct drm_index drm_index;
 typedef struct drm_ref drm_ref;
+typedef struct drm_reads drm_reads;
 
 /* Counters summed over the queries of one call (same definitions as FAISS hnsw_stats). */
 typedef struct drm_search_stats {
@@ -126,6 +127,31 @@ int drm_search_rerank(drm_index *ix, drm_ref *ref, int mode, const float *q, int
                       const char *q_flat, const int64_t *q_off, int64_t stride, int64_t k, int64_t k_clusters,
                       float *D, int64_t *I, int32_t *sw_scores, uint64_t *sw_ids, drm_search_stats *stats,
                       double *timing_ms);
+
+/* ------------------------------------------------------------------ input side on the device */
+/* extract_FASTA_sequence (src/utils/parse_inputs.cpp:174-220) as a device stream compaction: data = the FASTA file's
+ * bytes (host); the first line is dropped, every other byte is upper-cased and kept iff it is A, C, G, T or N.
+ * *len = cleaned length; out (host, nullable) receives the bytes when cap >= *len (cap >= size always suffices). */
+int drm_fasta_clean(const char *data, int64_t size, int device, char *out, int64_t cap, int64_t *len);
+/* The same, followed by drm_ref_open_genome on the result: the `ref_genome` of the dynamic mode
+ * (src/main.cpp:178-199) straight from the file bytes.  genome_len (nullable) = number of bases. */
+int drm_ref_open_fasta(const char *data, int64_t size, int ref_len, const int *devices, int n_dev, drm_ref **out,
+                       int64_t *genome_len);
+/* format_fastq (src/utils/parse_inputs.cpp:843-950) on the device: data = the FASTQ file's bytes (host); read r is
+ * line 4r+1 (lines end at '\n' only), stored as '<' + line + '>' like the reference's query_seqs.  The result lives
+ * on every listed device and feeds drm_sw_rerank_device (drm_reads_device) or drm_search_rerank_reads. */
+int drm_reads_open_fastq(const char *data, int64_t size, const int *devices, int n_dev, drm_reads **out);
+void drm_reads_close(drm_reads *r);
+/* info[0..3] = number of reads, bytes of the flat sequence buffer, longest sequence (with decoration), replicas */
+int drm_reads_info(const drm_reads *r, int64_t *info);
+/* host copies: flat (info[1] bytes, nullable) and off (info[0] + 1 offsets, nullable) */
+int drm_reads_copy_out(const drm_reads *r, char *flat, int64_t *off);
+int drm_reads_device(const drm_reads *r, int slot, const char **flat_dev, const int64_t **off_dev);
+/* drm_search_rerank with the read sequences taken from a drm_reads handle (opened on the same devices as the index):
+ * only the embeddings are uploaded.  n <= number of parsed reads; read i pairs with embedding row i. */
+int drm_search_rerank_reads(drm_index *ix, drm_ref *ref, int mode, const float *q, int64_t n, int d, int k_search, int ef,
+                            const drm_reads *reads, int64_t stride, int64_t k, int64_t k_clusters, float *D, int64_t *I,
+                            int32_t *sw_scores, uint64_t *sw_ids, drm_search_stats *stats, double *timing_ms);
 
 /* ------------------------------------------------------------------ sharded-index merge */
 /* D_all/I_all: n_shards x n x k (the all-gathered per-shard results, each row ascending, I already
