@@ -35,7 +35,7 @@ EXPORTS = ["drm_last_error", "drm_device_count", "drm_version", "drm_index_open"
            "drm_sw_pairs", "drm_sw_rerank", "drm_sw_rerank_device", "drm_merge_topk_device", "drm_build_index",
            "drm_search_rerank", "drm_build_index_gpu", "drm_build_index_gpu_device", "drm_fasta_clean", "drm_ref_open_fasta",
            "drm_reads_open_fastq", "drm_reads_close", "drm_reads_info", "drm_reads_copy_out", "drm_reads_device",
-           "drm_search_rerank_reads"]
+           "drm_search_rerank_reads", "drm_sw_align"]
 
 
 def lib_path() -> str:
@@ -68,6 +68,7 @@ def lib():
         L.drm_sw_rerank_device.argtypes = [vp, i32, i32, vp, i64, i64, vp, vp, i32, i64, i64, i64, vp, vp, vp, vp, vp, vp]
         L.drm_merge_topk_device.argtypes = [i32, vp, vp, i32, i64, i32, vp, vp, vp]
         L.drm_build_index.argtypes = [vp, i64, i32, vp, i64, i32, i32, i32, i32, i32, C.c_uint32, C.c_char_p]
+        L.drm_sw_align.argtypes = [vp, vp, i64, i32, vp, vp, i32, i32, vp, vp, vp, vp, vp, vp, vp, vp]
         L.drm_fasta_clean.argtypes = [vp, i64, i32, vp, i64, C.POINTER(i64)]
         L.drm_ref_open_fasta.argtypes = [vp, i64, i32, C.POINTER(i32), i32, C.POINTER(vp), C.POINTER(i64)]
         L.drm_reads_open_fastq.argtypes = [vp, i64, C.POINTER(i32), i32, C.POINTER(vp)]
@@ -203,6 +204,24 @@ class Reference:
         if return_extra:
             return scores, ids, ncand, ms.value
         return scores, ids
+
+    def align(self, ids, query_seqs, strip=0, max_ops=64):
+        """SW with traceback for (read i, window ids[i, s]) - the real CIGAR behind a rerank score (drm_sw_align).
+        ids: (n, per_read) window ids.  Returns dict of int32 arrays shaped (n, per_read): score, ref_beg, ref_end, q_beg,
+        q_end, n_ops, nm, and ops (n, per_read, max_ops) uint32 words (length << 4 | op; 0 = M, 1 = I, 2 = D)."""
+        ids = np.ascontiguousarray(ids, dtype=np.uint64)
+        if ids.ndim == 1:
+            ids = ids.reshape(-1, 1)
+        n, per = ids.shape
+        q_flat, q_off = flatten(query_seqs)
+        out = {k: np.zeros((n, per), dtype=np.int32) for k in ("score", "ref_beg", "ref_end", "q_beg", "q_end", "n_ops", "nm")}
+        ops = np.zeros((n, per, max_ops), dtype=np.uint32)
+        _check(lib().drm_sw_align(self._h, ids.ctypes.data, n, per, q_flat, q_off.ctypes.data, strip, max_ops,
+                                  out["score"].ctypes.data, out["ref_beg"].ctypes.data, out["ref_end"].ctypes.data,
+                                  out["q_beg"].ctypes.data, out["q_end"].ctypes.data, out["n_ops"].ctypes.data,
+                                  out["nm"].ctypes.data, ops.ctypes.data))
+        out["ops"] = ops
+        return out
 
     def rerank_device(self, mode, nb_ptr, n, k_in, qflat_ptr, qoff_ptr, max_qlen, stride, k, k_clusters, scores_ptr, ids_ptr,
                       ncand_ptr=0, min_ptr=0, cells_ptr=0, stream=0, slot=0):

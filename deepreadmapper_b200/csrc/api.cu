@@ -578,6 +578,40 @@ static int search_rerank_impl(drm_index *ix, drm_ref *ref, int mode, const float
 
 extern "C" {
 
+/* ------------------------------------------------------------------ SW traceback */
+int drm_sw_align(drm_ref *r, const uint64_t *ids, int64_t n, int per_read, const char *q_flat, const int64_t *q_off, int strip,
+                 int max_ops, int32_t *score, int32_t *ref_beg, int32_t *ref_end, int32_t *q_beg, int32_t *q_end, int32_t *n_ops,
+                 int32_t *nm, uint32_t *ops)
+{
+    if (!r || r->rep.empty()) return fail(DRM_EINVAL, "null reference handle");
+    if (n <= 0) return DRM_OK;
+    if (!ids || !q_flat || !q_off || per_read < 1 || max_ops < 1 || !score || !ref_beg || !ref_end || !q_beg || !q_end || !n_ops || !nm || !ops)
+        return fail(DRM_EINVAL, "bad arguments to drm_sw_align");
+    const DeviceRef &dr = r->rep[0];
+    DRM_CUDA_TRY(cudaSetDevice(dr.device));
+    const int64_t na = n * per_read, qbytes = q_off[n] - q_off[0];
+    int max_qlen = 0;
+    for (int64_t i = 0; i < n; ++i) max_qlen = std::max<int64_t>(max_qlen, q_off[i + 1] - q_off[i]);
+    std::vector<int64_t> rel((size_t)n + 1);
+    for (int64_t i = 0; i <= n; ++i) rel[(size_t)i] = q_off[i] - q_off[0];
+    DevBuf d_ids, d_q, d_off, d_out, d_ops;
+    int rc;
+    if ((rc = d_ids.alloc((size_t)na * 8)) || (rc = d_q.alloc((size_t)qbytes)) || (rc = d_off.alloc((size_t)(n + 1) * 8)) ||
+        (rc = d_out.alloc((size_t)na * 7 * sizeof(int))) || (rc = d_ops.alloc((size_t)na * max_ops * sizeof(unsigned)))) return rc;
+    DRM_CUDA_TRY(cudaMemcpy(d_ids.p, ids, (size_t)na * 8, cudaMemcpyHostToDevice));
+    if (qbytes) DRM_CUDA_TRY(cudaMemcpy(d_q.p, q_flat + q_off[0], (size_t)qbytes, cudaMemcpyHostToDevice));
+    DRM_CUDA_TRY(cudaMemcpy(d_off.p, rel.data(), (size_t)(n + 1) * 8, cudaMemcpyHostToDevice));
+    DRM_CUDA_TRY(cudaMemset(d_ops.p, 0, (size_t)na * max_ops * sizeof(unsigned)));
+    int *o = d_out.as<int>();
+    rc = launch_sw_align(dr, d_ids.as<unsigned long long>(), n, per_read, d_q.as<char>(), d_off.as<int64_t>(), max_qlen, strip, max_ops, o,
+                         o + na, o + 2 * na, o + 3 * na, o + 4 * na, o + 5 * na, o + 6 * na, d_ops.as<unsigned>(), 0);
+    if (rc != DRM_OK) return rc;
+    int32_t *dst[7] = {score, ref_beg, ref_end, q_beg, q_end, n_ops, nm};
+    for (int f = 0; f < 7; ++f) DRM_CUDA_TRY(cudaMemcpy(dst[f], o + (size_t)f * na, (size_t)na * sizeof(int), cudaMemcpyDeviceToHost));
+    DRM_CUDA_TRY(cudaMemcpy(ops, d_ops.p, (size_t)na * max_ops * sizeof(unsigned), cudaMemcpyDeviceToHost));
+    return DRM_OK;
+}
+
 /* ------------------------------------------------------------------ input side on the device */
 int drm_fasta_clean(const char *data, int64_t size, int device, char *out, int64_t cap, int64_t *len)
 {

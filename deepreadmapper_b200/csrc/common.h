@@ -120,6 +120,11 @@ int launch_merge_topk(const float *D_all, const int64_t *I_all, int n_shards, in
                       int64_t *I_out, cudaStream_t stream);
 int launch_classify(const uint8_t *raw, uint8_t *cls, int64_t n, int *has_other_dev, cudaStream_t stream);
 
+// SW with traceback (align_kernel.cu); every pointer is a device pointer.
+int launch_sw_align(const DeviceRef &ref, const unsigned long long *ids, int64_t n_reads, int per_read, const char *q_flat,
+                    const int64_t *q_off, int max_qlen, int strip, int max_ops, int *score, int *ref_beg, int *ref_end, int *q_beg,
+                    int *q_end, int *n_ops, int *nm, unsigned *ops, cudaStream_t stream);
+
 // Input side on the device (input_kernels.cu).  Output buffers are fresh cudaMalloc allocations on `device` owned by the caller.
 int clean_fasta_device(const char *data, int64_t size, int device, uint8_t **d_genome, int64_t *len);
 int parse_fastq_device(const char *data, int64_t size, int device, char **d_flat, int64_t **d_off, int64_t *n_reads,

@@ -12,6 +12,7 @@
 #include "common.h"
 
 #include <algorithm>
+#include <cstdlib>
 #include <cstring>
 
 namespace drm {
@@ -210,6 +211,25 @@ __global__ void fastq_copy_kernel(const unsigned char *__restrict__ data, const 
     for (int i = lane; i < len; i += 32) flat[o0 + 1 + i] = (char)data[b + i];
 }
 
+// DRM_INPUT_VERBOSE=1: host->device copy and kernel times of one call on stderr (measurement aid).
+struct PhaseTimer {
+    bool on;
+    cudaEvent_t e[3] = {nullptr, nullptr, nullptr};
+    PhaseTimer() : on(getenv("DRM_INPUT_VERBOSE") != nullptr) { if (on) for (auto &x : e) cudaEventCreate(&x); }
+    ~PhaseTimer() { if (on) for (auto &x : e) cudaEventDestroy(x); }
+    void mark(int i) { if (on) cudaEventRecord(e[i], 0); }
+    void report(const char *what, long long in_bytes, long long out_bytes)
+    {
+        if (!on) return;
+        cudaEventSynchronize(e[2]);
+        float h2d = 0, k = 0;
+        cudaEventElapsedTime(&h2d, e[0], e[1]);
+        cudaEventElapsedTime(&k, e[1], e[2]);
+        fprintf(stderr, "[drm input] %s: %lld bytes in, %lld bytes out, H2D %.3f ms, kernels %.3f ms (%.1f GB/s of input)\n", what, in_bytes,
+                out_bytes, h2d, k, k > 0 ? (double)in_bytes / k / 1e6 : 0.0);
+    }
+};
+
 template <class Pred>
 int compact(const unsigned char *d_data, long long size, Pred pred, int mode, unsigned char **out_bytes, long long **out_pos,
             long long *n_out, DevMem &mem)
@@ -253,7 +273,10 @@ int clean_fasta_device(const char *data, int64_t size, int device, uint8_t **d_g
     unsigned long long *d_first = nullptr;
     DRM_CUDA_TRY(mem.alloc(&d_data, (size_t)size));
     DRM_CUDA_TRY(mem.alloc(&d_first, sizeof(unsigned long long)));
+    PhaseTimer pt;
+    pt.mark(0);
     if (size) DRM_CUDA_TRY(cudaMemcpy(d_data, data, (size_t)size, cudaMemcpyHostToDevice));
+    pt.mark(1);
     unsigned long long first = (unsigned long long)size;
     DRM_CUDA_TRY(cudaMemcpy(d_first, &first, sizeof first, cudaMemcpyHostToDevice));
     if (size) {
@@ -266,7 +289,9 @@ int clean_fasta_device(const char *data, int64_t size, int device, uint8_t **d_g
     long long n = 0;
     int rc = compact(d_data, size, pred, 0, &out, nullptr, &n, mem);
     if (rc != DRM_OK) return rc;
+    pt.mark(2);
     DRM_CUDA_TRY(cudaDeviceSynchronize());
+    pt.report("FASTA clean", size, n);
     if (!out) DRM_CUDA_TRY(mem.alloc(&out, 16));
     mem.release(out);
     *d_genome = out;
@@ -286,7 +311,10 @@ int parse_fastq_device(const char *data, int64_t size, int device, char **d_flat
     DevMem mem;
     unsigned char *d_data = nullptr;
     DRM_CUDA_TRY(mem.alloc(&d_data, (size_t)size));
+    PhaseTimer pt;
+    pt.mark(0);
     if (size) DRM_CUDA_TRY(cudaMemcpy(d_data, data, (size_t)size, cudaMemcpyHostToDevice));
+    pt.mark(1);
     long long *nl = nullptr, n_nl = 0;
     int rc = compact(d_data, size, KeepNewline(), 1, nullptr, &nl, &n_nl, mem);
     if (rc != DRM_OK) return rc;
@@ -313,7 +341,9 @@ int parse_fastq_device(const char *data, int64_t size, int device, char **d_flat
         DRM_CUDA_TRY(cudaGetLastError());
     }
     DRM_CUDA_TRY(cudaMemcpy(max_len, d_max, sizeof(int), cudaMemcpyDeviceToHost));
+    pt.mark(2);
     DRM_CUDA_TRY(cudaDeviceSynchronize());
+    pt.report("FASTQ reads", size, total);
     mem.release(flat); mem.release(off);
     *d_flat = flat; *d_off = reinterpret_cast<int64_t *>(off); *n_reads = n; *flat_bytes = total;
     return DRM_OK;

@@ -52,6 +52,18 @@ std::pair<std::vector<std::vector<faiss::idx_t>>, std::vector<std::vector<float>
 // Flat form used by the pipeline for large batches (no nested vectors): q is n x d row-major.
 void faiss_search_flat(faiss::IndexHNSWPQ *index, const float *q, int64_t n, int d, int k, int ef, std::vector<faiss::idx_t> &I, std::vector<float> &D);
 
+// Search + SW rerank with the FASTQ reads and the FASTA genome parsed on the device (additive; `pipeline` uses it for
+// FASTQ queries unless DRM_INPUT=host).  Returns the number of reads; throws the reference's messages on mismatch.
+int64_t stage_device_inputs(faiss::IndexHNSWPQ *index, const std::string &fastq_file, const std::string &fasta_file, const float *emb,
+                            int64_t n_emb, int d, int k_search, int ef, int mode, size_t ref_len, size_t stride, size_t k, size_t k_clusters,
+                            std::vector<faiss::idx_t> &I, std::vector<float> &D, std::vector<int> &sw_scores, std::vector<size_t> &sw_ids);
+
+// write_sam (src/utils/utils.cpp:336-398) with real POS / CIGAR / NM (traceback kernel) and a score-gap MAPQ; the first n_out
+// reranked windows of every read are written (query_seqs carry the '<' '>' decoration like the reference's).
+void write_sam_aligned(const std::string &sam_file, const std::string &ref_name, const std::string &genome, size_t ref_len,
+                       const std::vector<std::string> &query_seqs, const std::vector<std::string> &query_ids, const std::vector<int> &sw_scores,
+                       const std::vector<size_t> &sw_ids, size_t k, size_t n_out);
+
 int calc_sw_score(const std::string &seq1, const std::string &seq2);
 
 std::tuple<std::vector<std::string>, std::vector<int>, std::vector<size_t>> sw_reranker(

@@ -72,11 +72,18 @@ int main(int argc, char *argv[])
         const bool is_npy = std::filesystem::path(query_input_file).extension().string() == ".npy";
         std::vector<std::string> query_sequences, query_ids;
         std::string emb_file = query_input_file;
+        // FASTQ queries: reads and genome are parsed on the device and both stages run as one call (DRM_INPUT=host keeps the
+        // reference's host parsing and the two separate stages).
+        const std::string qext = std::filesystem::path(query_input_file).extension().string();
+        const char *input_mode = getenv("DRM_INPUT");
+        const bool device_inputs = !is_npy && rerank && (qext == ".fastq" || qext == ".fq") && !(input_mode && !strcmp(input_mode, "host"));
         if (!is_npy) {
-            std::tie(query_sequences, query_ids) = read_file(query_input_file);
-            if (query_sequences.empty()) {
-                std::cerr << "No query_sequences found in input file!" << std::endl;
-                return 1;
+            if (!device_inputs) {
+                std::tie(query_sequences, query_ids) = read_file(query_input_file);
+                if (query_sequences.empty()) {
+                    std::cerr << "No query_sequences found in input file!" << std::endl;
+                    return 1;
+                }
             }
             const char *env = getenv("DRM_QUERY_EMB");
             emb_file = env ? env : query_input_file + ".npy";
@@ -88,9 +95,11 @@ int main(int argc, char *argv[])
         if (arr.kind != 'f' || arr.word_size != 4 || arr.fortran_order) throw std::runtime_error("Error: embeddings must be C-order float32 ('<f4')");
         const size_t num_queries = arr.shape[0], dim = arr.shape[1];
         std::cout << "[MAIN] Loaded " << num_queries << " embeddings of dimension " << dim << std::endl;
-        if (!is_npy && query_sequences.size() != num_queries) throw std::runtime_error("Error: number of embeddings differs from the number of query sequences");
+        if (!is_npy && !device_inputs && query_sequences.size() != num_queries) throw std::runtime_error("Error: number of embeddings differs from the number of query sequences");
         std::string ref_genome;
-        if (!is_npy && rerank) {
+        if (device_inputs) {
+            std::cout << "[MAIN] Reads and reference are parsed on the device (" << (use_dynamic ? "DYNAMIC" : "STATIC") << " bound rule)" << std::endl;
+        } else if (!is_npy && rerank) {
             std::cout << "[MAIN] Using " << (use_dynamic ? "DYNAMIC" : "STATIC") << " fetching for reference sequences" << std::endl;
             ref_genome = extract_FASTA_sequence(ref_seqs_file);
         } else {
@@ -112,16 +121,24 @@ int main(int argc, char *argv[])
         t0 = Clock::now();
         std::vector<faiss::idx_t> I;
         std::vector<float> D;
-        faiss_search_flat(alg_hnsw, reinterpret_cast<const float *>(arr.data.data()), (int64_t)num_queries, (int)dim, k_clusters, ef, I, D);
-        std::cout << "[MAIN] HNSW search time: " << ms_since(t0) << " ms" << std::endl << std::endl;
+        std::vector<int> sw_scores;
+        std::vector<size_t> sw_ids;
+        if (device_inputs) {
+            stage_device_inputs(alg_hnsw, query_input_file, ref_seqs_file, reinterpret_cast<const float *>(arr.data.data()), (int64_t)num_queries,
+                                (int)dim, k_clusters, ef, use_dynamic ? 1 : 0, ref_len, stride, (size_t)k, (size_t)k_clusters, I, D, sw_scores, sw_ids);
+            std::cout << "[MAIN] HNSW search + SW rerank time (one call, device-side inputs): " << ms_since(t0) << " ms" << std::endl << std::endl;
+        } else {
+            faiss_search_flat(alg_hnsw, reinterpret_cast<const float *>(arr.data.data()), (int64_t)num_queries, (int)dim, k_clusters, ef, I, D);
+            std::cout << "[MAIN] HNSW search time: " << ms_since(t0) << " ms" << std::endl << std::endl;
+        }
         delete alg_hnsw;
 
         // ---------------- post-processing (Smith-Waterman rerank)
         std::cout << "[MAIN] POST-PROCESSING STEP" << std::endl;
         t0 = Clock::now();
-        std::vector<int> sw_scores;
-        std::vector<size_t> sw_ids;
-        if (!is_npy && rerank) {
+        if (device_inputs) {
+            std::cout << "[MAIN] Post-processing ran inside the search call" << std::endl;
+        } else if (!is_npy && rerank) {
             post_process_sw_flat(use_dynamic ? 1 : 0, ref_genome, ref_len, I, (int64_t)num_queries, k_clusters, query_sequences, stride, (size_t)k,
                                  (size_t)k_clusters, sw_scores, sw_ids);
         } else {
@@ -141,6 +158,18 @@ int main(int argc, char *argv[])
         if (!sw_scores.empty()) {
             npy::save(output_dir + "/sw_scores.npy", sw_scores.data(), {num_queries, (size_t)k});
             npy::save(output_dir + "/sw_indices.npy", sw_ids.data(), {num_queries, (size_t)k});
+        }
+        // SAM with real alignments (the reference's write_sam call is commented out, src/main.cpp:395): DRM_SAM=<n> writes the
+        // first n reranked windows of every read to <output_dir>/alignments.sam.
+        if (const char *sam_n = getenv("DRM_SAM")) {
+            const long n_sam = atol(sam_n);
+            if (n_sam > 0 && !sw_scores.empty()) {
+                if (query_sequences.empty()) std::tie(query_sequences, query_ids) = read_file(query_input_file);
+                if (ref_genome.empty()) ref_genome = extract_FASTA_sequence(ref_seqs_file);
+                write_sam_aligned(output_dir + "/alignments.sam", "ref", ref_genome, ref_len, query_sequences, query_ids, sw_scores, sw_ids,
+                                  (size_t)k, (size_t)n_sam);
+                std::cout << "[MAIN] SAM written: " << output_dir << "/alignments.sam (" << n_sam << " alignment(s) per read)" << std::endl;
+            }
         }
         std::cout << "[MAIN] Output saving time: " << ms_since(t0) << " ms" << std::endl;
         std::cout << "[MAIN] Finished processing file: " << query_input_file << std::endl;

@@ -251,3 +251,150 @@ void post_process_sw_flat(int mode, const std::string &genome, size_t ref_len, c
         throw_last();
     ids.assign(u.begin(), u.end());
 }
+
+// ------------------------------------------------------------------------------------------ device-side inputs
+// The search + SW stage with both sequence inputs parsed on the device: the FASTQ file's
+// bytes become the resident read set (format_fastq), the FASTA file's bytes the class-coded genome
+// (extract_FASTA_sequence), and drm_search_rerank_reads runs both stages with only the embeddings going up.
+static std::string slurp_file(const std::string &path)
+{
+    FILE *f = fopen(path.c_str(), "rb");
+    if (!f) throw std::runtime_error("Could not open file: " + path);
+    std::string data;
+    fseek(f, 0, SEEK_END);
+    const long sz = ftell(f);
+    fseek(f, 0, SEEK_SET);
+    data.resize(sz > 0 ? (size_t)sz : 0);
+    if (sz > 0 && fread(&data[0], 1, (size_t)sz, f) != (size_t)sz) { fclose(f); throw std::runtime_error("Could not read file: " + path); }
+    fclose(f);
+    return data;
+}
+
+int64_t stage_device_inputs(faiss::IndexHNSWPQ *index, const std::string &fastq_file, const std::string &fasta_file, const float *emb,
+                            int64_t n_emb, int d, int k_search, int ef, int mode, size_t ref_len, size_t stride, size_t k, size_t k_clusters,
+                            std::vector<faiss::idx_t> &I, std::vector<float> &D, std::vector<int> &sw_scores, std::vector<size_t> &sw_ids)
+{
+    if (!index || !index->handle) throw std::runtime_error("faiss_search: null index");
+    if (k > k_clusters * 2 * stride) throw std::runtime_error("Final k too large. Ensure k < k_clusters * 2 * stride to have enough candidates.");
+    const std::vector<int> devs = device_list();
+    struct Handles {
+        drm_reads *reads = nullptr;
+        drm_ref *ref = nullptr;
+        ~Handles() { if (reads) drm_reads_close(reads); if (ref) drm_ref_close(ref); }
+    } h;
+    {
+        const std::string fq = slurp_file(fastq_file);
+        if (drm_reads_open_fastq(fq.data(), (int64_t)fq.size(), devs.data(), (int)devs.size(), &h.reads) != DRM_OK) throw_last();
+    }
+    int64_t info[4];
+    drm_reads_info(h.reads, info);
+    if (info[0] == 0) throw std::runtime_error("No query_sequences found in input file!");
+    if (info[0] != n_emb) throw std::runtime_error("Error: number of embeddings differs from the number of query sequences");
+    {
+        const std::string fa = slurp_file(fasta_file);
+        int64_t glen = 0;
+        if (drm_ref_open_fasta(fa.data(), (int64_t)fa.size(), (int)ref_len, devs.data(), (int)devs.size(), &h.ref, &glen) != DRM_OK) throw_last();
+    }
+    index->hnsw.efSearch = ef;
+    I.resize((size_t)n_emb * k_search);
+    D.resize((size_t)n_emb * k_search);
+    sw_scores.assign((size_t)n_emb * k, 0);
+    std::vector<uint64_t> u((size_t)n_emb * k);
+    if (drm_search_rerank_reads(index->handle, h.ref, mode, emb, n_emb, d, k_search, ef, h.reads, (int64_t)stride, (int64_t)k, (int64_t)k_clusters,
+                                D.data(), I.data(), sw_scores.data(), u.data(), nullptr, nullptr) != DRM_OK)
+        throw_last();
+    sw_ids.assign(u.begin(), u.end());
+    return info[0];
+}
+
+// ------------------------------------------------------------------------------------------ SAM with real alignments
+// write_sam (src/utils/utils.cpp:336-398) with its pseudo fields made real: POS, CIGAR and NM
+// come from the traceback kernel (drm_sw_align) run on the first `n_out` reranked windows of every read, MAPQ from the gap
+// to the best score at another locus.  Same columns and QNAME / FLAG rules as the reference; @SQ LN is the genome length
+// (the reference writes the window length there); AS:i / NM:i tags are appended.  A reverse-strand window (odd id) aligns
+// the read against the reverse complement, so the line carries the reverse-complemented read, the reversed CIGAR and the
+// forward-strand position, as SAM defines for flag 16.
+static std::string revcomp(const std::string &s)
+{
+    std::string r(s.rbegin(), s.rend());
+    for (char &c : r) {
+        switch (c) {
+        case 'A': c = 'T'; break; case 'T': c = 'A'; break; case 'C': c = 'G'; break; case 'G': c = 'C'; break;
+        case 'a': c = 't'; break; case 't': c = 'a'; break; case 'c': c = 'g'; break; case 'g': c = 'c'; break;
+        default: break;
+        }
+    }
+    return r;
+}
+
+void write_sam_aligned(const std::string &sam_file, const std::string &ref_name, const std::string &genome, size_t ref_len,
+                       const std::vector<std::string> &query_seqs, const std::vector<std::string> &query_ids, const std::vector<int> &sw_scores,
+                       const std::vector<size_t> &sw_ids, size_t k, size_t n_out)
+{
+    const size_t n = query_seqs.size();
+    if (n_out > k) n_out = k;
+    if (sw_ids.size() < n * k || sw_scores.size() < n * k) throw std::runtime_error("write_sam_aligned: rerank output is smaller than n x k");
+    FILE *f = fopen(sam_file.c_str(), "w");
+    if (!f) throw std::runtime_error("Failed to open SAM file: " + sam_file);
+    fprintf(f, "@HD\tVN:1.0\tSO:unsorted\n@SQ\tSN:%s\tLN:%zu\n", ref_name.c_str(), genome.size());
+    if (n == 0 || n_out == 0) { fclose(f); return; }
+    const int max_ops = 64;
+    std::vector<uint64_t> ids(n * n_out);
+    for (size_t i = 0; i < n; ++i)
+        for (size_t j = 0; j < n_out; ++j) ids[i * n_out + j] = (uint64_t)sw_ids[i * k + j];
+    std::string qflat;
+    std::vector<int64_t> qoff;
+    flatten(query_seqs, qflat, qoff);
+    const size_t na = n * n_out;
+    std::vector<int32_t> score(na), rb(na), re(na), qb(na), qe(na), nops(na), nm(na);
+    std::vector<uint32_t> ops(na * max_ops);
+    if (drm_sw_align(genome_ref(genome, ref_len), ids.data(), (int64_t)n, (int)n_out, qflat.data(), qoff.data(), 1, max_ops, score.data(), rb.data(),
+                     re.data(), qb.data(), qe.data(), nops.data(), nm.data(), ops.data()) != DRM_OK) {
+        fclose(f);
+        throw_last();
+    }
+    std::string line;
+    for (size_t i = 0; i < n; ++i) {
+        std::string clean = query_seqs[i];
+        if (clean.size() > 2) clean = clean.substr(1, clean.size() - 2);  // PREFIX / POSTFIX, as write_sam strips them
+        const std::string rc_clean = revcomp(clean);
+        const std::string qname = (i < query_ids.size() && !query_ids[i].empty()) ? query_ids[i] : "S1/" + std::to_string(i + 1) + "/0";
+        for (size_t j = 0; j < n_out; ++j) {
+            const size_t a = i * n_out + j;
+            const size_t id = sw_ids[i * k + j];
+            const size_t pos = id / 2;
+            const bool rev = id % 2 == 1;
+            int flag = j == 0 ? 0 : 256;
+            if (rev) flag |= 16;
+            line.clear();
+            if (score[a] <= 0 || nops[a] > max_ops) {  // nothing aligned (or an alignment with more than 64 runs): unmapped line
+                line = qname + "\t" + std::to_string(flag | 4) + "\t*\t0\t0\t*\t*\t0\t0\t" + clean + "\t*\tAS:i:0\n";
+                fputs(line.c_str(), f);
+                continue;
+            }
+            // MAPQ: relative gap to the best reranked score at another locus (no overlap with this window)
+            int other = 0;
+            for (size_t c = 0; c < k; ++c) {
+                const size_t p2 = sw_ids[i * k + c] / 2;
+                const size_t dist = p2 > pos ? p2 - pos : pos - p2;
+                if (dist >= ref_len && sw_scores[i * k + c] > other) other = sw_scores[i * k + c];
+            }
+            int mapq = (int)(60.0 * (double)(score[a] - other) / (double)score[a] + 0.5);
+            mapq = mapq < 0 ? 0 : (mapq > 60 ? 60 : mapq);
+            const int lq = (int)clean.size();
+            const int clip_l = rev ? lq - qe[a] : qb[a], clip_r = rev ? qb[a] : lq - qe[a];
+            const size_t sam_pos = rev ? pos + ref_len - (size_t)re[a] + 1 : pos + (size_t)rb[a] + 1;
+            std::string cigar;
+            if (clip_l > 0) cigar += std::to_string(clip_l) + "S";
+            for (int x = 0; x < nops[a]; ++x) {
+                const uint32_t w = ops[a * max_ops + (rev ? nops[a] - 1 - x : x)];
+                cigar += std::to_string(w >> 4) + "MID"[w & 15];
+            }
+            if (clip_r > 0) cigar += std::to_string(clip_r) + "S";
+            line = qname + "\t" + std::to_string(flag) + "\t" + ref_name + "\t" + std::to_string(sam_pos) + "\t" + std::to_string(mapq) + "\t" + cigar +
+                   "\t*\t0\t0\t" + (rev ? rc_clean : clean) + "\t*\tAS:i:" + std::to_string(score[a]) + "\tNM:i:" + std::to_string(nm[a]) + "\n";
+            fputs(line.c_str(), f);
+        }
+    }
+    fclose(f);
+}

@@ -128,6 +128,19 @@ int drm_search_rerank(drm_index *ix, drm_ref *ref, int mode, const float *q, int
                       float *D, int64_t *I, int32_t *sw_scores, uint64_t *sw_ids, drm_search_stats *stats,
                       double *timing_ms);
 
+/* ------------------------------------------------------------------ SW traceback (real CIGAR) */
+/* The alignment behind a rerank score - what the reference's write_sam leaves as "TODO: Implement real CIGAR - from SW
+ * ranker" (src/utils/utils.cpp:381-384).  ids: n x per_read window ids (e.g. the first columns of sw_ids); read i is
+ * q_flat[q_off[i] .. q_off[i+1]) with `strip` bytes dropped from each end when longer than 2*strip (write_sam strips the
+ * '<' '>' decoration the same way).  Scoring = calc_sw_score; end cell = first maximum in row-major order; traceback
+ * prefers diagonal, then D, then I.  Outputs per (read, slot): score, window interval [ref_beg, ref_end), read interval
+ * [q_beg, q_end) (0-based, in the orientation of the window: a reverse-strand window aligns the read as given against the
+ * reverse complement), n_ops (> max_ops = truncated: the words are then unspecified), nm (mismatches + gap bases) and ops[max_ops] words
+ * (length << 4 | op; 0 = M, 1 = I, 2 = D) in alignment order; soft clips are implied by the read interval. */
+int drm_sw_align(drm_ref *r, const uint64_t *ids, int64_t n, int per_read, const char *q_flat, const int64_t *q_off, int strip,
+                 int max_ops, int32_t *score, int32_t *ref_beg, int32_t *ref_end, int32_t *q_beg, int32_t *q_end, int32_t *n_ops,
+                 int32_t *nm, uint32_t *ops);
+
 /* ------------------------------------------------------------------ input side on the device */
 /* extract_FASTA_sequence (src/utils/parse_inputs.cpp:174-220) as a device stream compaction: data = the FASTA file's
  * bytes (host); the first line is dropped, every other byte is upper-cased and kept iff it is A, C, G, T or N.

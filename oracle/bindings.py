@@ -63,6 +63,8 @@ def oracle():
         L.orc_post_process_sw.restype = C.c_int64
         L.orc_post_process_sw.argtypes = [C.c_int, _i64p, C.c_int64, C.c_int64, C.c_char_p, C.c_int64, C.c_int64,
                                           C.c_char_p, _i64p, C.c_int64, C.c_int64, C.c_int64, _i32p, _u64p, _i64p, C.c_int]
+        L.orc_sw_align.restype = None
+        L.orc_sw_align.argtypes = [C.c_char_p, C.c_int64, C.c_char_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_int]
         L.orc_last_error.restype = C.c_char_p
         L.orc_index_read.restype = C.c_void_p
         L.orc_index_read.argtypes = [C.c_char_p]
@@ -158,6 +160,18 @@ def expand_ids(mode, ids, stride, bound):
     out = np.zeros(len(ids) * per + 1, dtype=np.uint64)
     m = oracle().orc_expand_ids(mode, ids, len(ids), stride, bound, out)
     return out[:m]
+
+
+def sw_align(window: bytes, read: bytes, max_ops: int = 64):
+    """SW with traceback (the definition in sw_oracle.c: orc_sw_align).  Returns dict(score, ref_beg, ref_end, q_beg, q_end,
+    n_ops, nm, ops=[(length, 'M'|'I'|'D')...])."""
+    out = np.zeros(7, dtype=np.int32)
+    ops = np.zeros(max_ops, dtype=np.uint32)
+    oracle().orc_sw_align(window, len(window), read, len(read), out.ctypes.data, ops.ctypes.data, max_ops)
+    keys = ("score", "ref_beg", "ref_end", "q_beg", "q_end", "n_ops", "nm")
+    d = {k: int(v) for k, v in zip(keys, out)}
+    d["ops"] = [(int(w) >> 4, "MID"[int(w) & 15]) for w in ops[:min(d["n_ops"], max_ops)]]
+    return d
 
 
 def post_process_sw(mode, neighbors, ref_bytes, n_ref, ref_len, queries, stride, k, k_clusters, threads=0, use_ref=False):

@@ -237,3 +237,51 @@ int64_t orc_post_process_sw(int mode, const int64_t *neighbors, int64_t n, int64
     }
     return fail;
 }
+
+/* ---- SW with traceback: the "real CIGAR" the reference's write_sam leaves as a TODO (src/utils/utils.cpp:381-384).
+ * The reference has no traceback, so this is a definition, not a restatement; it is pinned to the reference through its
+ * score: out[0] always equals calc_sw_score(s1, s2) and re-scoring the reported operations gives out[0] back
+ * (tests/test_oracle_sw.py).  Conventions: full matrix of calc_sw_score (rows = s1 = window, columns = s2 = read);
+ * end cell = first maximum in row-major order; walk back while H > 0 preferring diagonal, then up (D), then left (I).
+ * out[0..6] = score, ref_beg, ref_end, q_beg, q_end, n_ops, nm (0-based half-open intervals); ops = (len << 4 | op) in
+ * alignment order, op 0 = M, 1 = I, 2 = D; at most max_ops are written (n_ops > max_ops means truncated). */
+void orc_sw_align(const char *s1, int64_t len1, const char *s2, int64_t len2, int32_t *out, uint32_t *ops, int max_ops)
+{
+    const int64_t W = len2 + 1;
+    int *H = (int *)calloc((size_t)((len1 + 1) * W), sizeof(int));
+    int best = 0;
+    int64_t bi = 0, bj = 0;
+    for (int64_t i = 1; i <= len1; ++i)
+        for (int64_t j = 1; j <= len2; ++j) {
+            int d = H[(i - 1) * W + j - 1] + (s1[i - 1] == s2[j - 1] ? 1 : -1);
+            int u = H[(i - 1) * W + j] - 1, l = H[i * W + j - 1] - 1;
+            int h = d > u ? d : u;
+            if (l > h) h = l;
+            if (h < 0) h = 0;
+            H[i * W + j] = h;
+            if (h > best) { best = h; bi = i; bj = j; }
+        }
+    int64_t i = bi, j = bj;
+    int n_ops = 0, nm = 0, cur = -1, cur_len = 0;
+    uint32_t *rev = (uint32_t *)malloc(sizeof(uint32_t) * (size_t)(len1 + len2 + 2));
+    while (i > 0 && j > 0 && H[i * W + j] > 0) {
+        const int h = H[i * W + j];
+        int op;
+        if (h == H[(i - 1) * W + j - 1] + (s1[i - 1] == s2[j - 1] ? 1 : -1)) {
+            op = 0;
+            if (s1[i - 1] != s2[j - 1]) ++nm;
+            --i; --j;
+        } else if (h == H[(i - 1) * W + j] - 1) { op = 2; ++nm; --i; }
+        else { op = 1; ++nm; --j; }
+        if (op == cur) ++cur_len;
+        else {
+            if (cur >= 0) rev[n_ops++] = ((uint32_t)cur_len << 4) | (uint32_t)cur;
+            cur = op; cur_len = 1;
+        }
+    }
+    if (cur >= 0) rev[n_ops++] = ((uint32_t)cur_len << 4) | (uint32_t)cur;
+    for (int x = 0; x < n_ops && x < max_ops; ++x) ops[x] = rev[n_ops - 1 - x];
+    out[0] = best; out[1] = (int32_t)i; out[2] = (int32_t)bi; out[3] = (int32_t)j; out[4] = (int32_t)bj; out[5] = n_ops; out[6] = nm;
+    free(rev);
+    free(H);
+}

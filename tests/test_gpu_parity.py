@@ -360,11 +360,13 @@ def test_cli_hnswpq_index_then_pipeline_config1(drm, ob, fixtures, tmp_path):
     r = subprocess.run([os.path.join(root, "build/bin/hnswpq_index"), "ref.fna", "idx1", "150", "1", "8", "8", "16", "64"], cwd=tmp_path,
                        capture_output=True, text=True)
     assert r.returncode == 0, r.stderr
-    for dyn in ("0", "1"):
-        out = tmp_path / f"out{dyn}"
+    # FASTQ queries take the device-side input path (reads + genome parsed on the GPU, one fused call) unless DRM_INPUT=host
+    for dyn, inp in (("0", "device"), ("1", "device"), ("0", "host"), ("1", "host")):
+        out = tmp_path / f"out{dyn}{inp}"
         r = subprocess.run([os.path.join(root, "build/bin/pipeline"), "idx1", "reads.fastq", "ref.fna", "64", "32", "32", str(out), dyn], cwd=tmp_path,
-                           capture_output=True, text=True)
+                           capture_output=True, text=True, env=dict(os.environ, DRM_INPUT=inp))
         assert r.returncode == 0, r.stderr + r.stdout
+        assert ("device-side inputs" in r.stdout) == (inp == "device")
         I, D = np.load(out / "indices.npy"), np.load(out / "distances.npy")
         assert I.dtype == np.dtype("<u8") and D.dtype == np.dtype("<f4") and I.shape == D.shape == (len(reads), 32)
         oix = ob.OracleIndex(str(tmp_path / "idx1" / "idx1.index"))
@@ -378,7 +380,7 @@ def test_cli_hnswpq_index_then_pipeline_config1(drm, ob, fixtures, tmp_path):
         else:
             wins = "".join(fixtures["windows"]).encode()
             rc, s0, i0, _ = ob.post_process_sw(0, I0, wins, fixtures["n_windows"], 150, decorated, 1, 32, 32)
-        assert rc == 0 and np.array_equal(S, s0) and np.array_equal(SI, i0), dyn
+        assert rc == 0 and np.array_equal(S, s0) and np.array_equal(SI, i0), (dyn, inp)
     # test_sw_score batch mode = the reference's 100-pair known-answer vector (sum 2696)
     open(tmp_path / "quer.txt", "w").write("\n".join(fixtures["quer"]) + "\n")
     r = subprocess.run([os.path.join(root, "build/bin/test_sw_score"), "quer.txt", "scores.txt"], cwd=tmp_path, capture_output=True, text=True)

@@ -147,3 +147,37 @@ def test_expansion_and_window_fetch_vs_reference(fixtures, ob):
             rc2, s2, i2, _ = ob.post_process_sw(mode, nb, refb, nref, 150, reads, stride, k, kc, use_ref=True)
             assert rc2 == 0
             assert s1.tolist() == s2.tolist() and i1.tolist() == i2.tolist(), (mode, stride, kc, k)
+
+
+def test_traceback_oracle_is_pinned_by_the_score(ob, fixtures):
+    """orc_sw_align is a definition (the reference has no traceback): its score must equal calc_sw_score and re-scoring the
+    reported operations along the reported intervals must give that score back."""
+    rng = np.random.default_rng(4)
+    pairs = [(fixtures["windows"][i].encode(), fixtures["reads"][i % len(fixtures["reads"])].strip("<>").encode()) for i in range(0, 400, 7)]
+    for t in range(200):
+        la, lb = int(rng.integers(0, 80)), int(rng.integers(0, 80))
+        a = bytes(rng.choice(list(b"ACGTN"), la))
+        b = bytearray(a[:lb]) if t % 2 else bytearray(rng.choice(list(b"ACGT"), lb))
+        for _ in range(len(b) // 7):
+            b[int(rng.integers(0, len(b)))] = ord("C")
+        if t % 5 == 0 and len(b) > 10:
+            del b[5]
+        pairs.append((a, bytes(b)))
+    for a, b in pairs:
+        r = ob.sw_align(a, b, 256)
+        assert r["score"] == ob.sw_score(a, b)
+        if ob.have_ref():
+            assert r["score"] == ob.ref().ref_calc_sw_score(a, len(a), b, len(b))
+        i, j, s, nm = r["ref_beg"], r["q_beg"], 0, 0
+        for length, op in r["ops"]:
+            for _ in range(length):
+                if op == "M":
+                    s += 1 if a[i] == b[j] else -1
+                    nm += a[i] != b[j]
+                    i += 1
+                    j += 1
+                elif op == "D":
+                    s, nm, i = s - 1, nm + 1, i + 1
+                else:
+                    s, nm, j = s - 1, nm + 1, j + 1
+        assert (i, j, s, nm) == (r["ref_end"], r["q_end"], r["score"], r["nm"]), (a, b, r)
