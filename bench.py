@@ -428,12 +428,20 @@ def run_ours(args):
     # spread over the alu and fma pipes, each measured at 64 lanes/clk/SM (profiles/r1_ubench_pipes.txt) -> 2*64/3.5 pairs/clk/SM
     int_peak = sms * (2 * 64 / 3.5) * 2 * sm_max * 1e6 / 1e9
     g = line["sw_gcups"]
-    line["roofline"] = {"kernel": "sw_rerank_profile_kernel (dominant: %.0f%% of the step)" % (100 * sw_ms / (sw_ms + search_ms)), "bound": "issue (alu + fma pipes; neither hbm nor tensor applies: DRAM traffic of this kernel is < 0.1 % of peak)",
+    # the same kernel seen from HBM: algorithmic bytes per read = read (150) + K labels (8 B) + K windows (150 B, served by the
+    # L2-resident genome) + K results (12 B)
+    sw_bytes_per_read = REF_LEN + K * 8 + K * REF_LEN + K * 12
+    sw_gbps = sw_bytes_per_read * n / (sw_ms / 1e3) / 1e9
+    line["roofline"] = {"kernel": "sw_rerank_profile_kernel (dominant: %.0f%% of the step)" % (100 * sw_ms / (sw_ms + search_ms)), "bound": "issue",
+                        "bound_note": "integer issue roofline (alu + fma pipes); neither hbm nor tensor applies: the kernel moves %.0f GB/s of algorithmic "
+                                      "bytes (%.4f of the HBM peak) and has no dense contraction" % (sw_gbps, sw_gbps / hbm_peak),
                         "achieved": g, "peak": int_peak, "unit": "GCUPS", "frac": g / int_peak,
                         "traffic": NCU_DRAM_BYTES_PER_READ["sw"] * min(n, 131072),
                         "traffic_source": "ncu capture of one 131072-read launch (profiles/r1_ncu_sw_rerank_profile_kernel_v2.txt): 2.2 KB/read, i.e. 4 GB/s - not an HBM-bound kernel",
                         "peak_source": "measured pipe rates (profiles/r1_ubench_pipes.txt, r1_ubench_alu.txt) x 3.5 instructions per cell pair at clocks.max.sm; DESIGN.md §4.3",
-                        "cells_per_launch": cells, "ms_per_step": sw_ms}
+                        "cells_per_launch": cells, "ms_per_step": sw_ms,
+                        "hbm_view": {"bound": "hbm", "achieved": sw_gbps, "peak": hbm_peak, "unit": "GB/s", "frac": sw_gbps / hbm_peak,
+                                     "algorithmic_bytes_per_read": sw_bytes_per_read}}
     emit(line)
     if world > 1:
         dist.destroy_process_group()
