@@ -276,6 +276,8 @@ constexpr int PTAB_ENTRIES = 25 * PGROUPS * 8;
 template <int ALU_EVERY>
 __device__ __forceinline__ unsigned sw_quad_profile(const uint8_t *rowA, const uint8_t *rowB, int rows, const uint4 *tab, int lane, unsigned one)
 {
+    constexpr bool F32ADD = ALU_EVERY >= 100;  // ALU_EVERY = 100 + n: the add runs as an fp32 FADD, clamp mix n as below
+    constexpr int AE = ALU_EVERY % 100;
     const int l = lane & 3;
     const uint4 *tslot = tab + (lane & 7);
     unsigned H[PCPL];
@@ -300,10 +302,17 @@ __device__ __forceinline__ unsigned sw_quad_profile(const uint8_t *rowA, const u
                 if (j >= PCPL) continue;
                 const unsigned up = H[j];
                 unsigned x, h;
-                if (ALU_EVERY == 1) x = s4[c] * one + diag;
+                if (F32ADD) {
+                    // the packed pair (hi << 16 | lo, both < 256) is below 2^24, and an fp32 whose bit pattern p is below 2^24 has
+                    // the value p * 2^-149 (denormal, or exponent field 1 with the same ulp): a non-flushing fp32 add of two such
+                    // patterns IS the integer add - and FADD can issue on either fma pipe half, which HADD2 / IMAD cannot
+                    float xf;
+                    asm("add.rn.f32 %0, %1, %2;" : "=f"(xf) : "f"(__uint_as_float(s4[c])), "f"(__uint_as_float(diag)));
+                    x = __float_as_uint(xf);
+                } else if (AE == 1) x = s4[c] * one + diag;
                 else asm("add.rn.f16x2 %0, %1, %2;" : "=r"(x) : "r"(s4[c]), "r"(diag));
                 const unsigned m = __vimax3_s16x2(x, up, left);
-                const bool on_alu = ALU_EVERY == 1 || (ALU_EVERY >= 2 && (j % ALU_EVERY) == ALU_EVERY - 1);
+                const bool on_alu = AE == 1 || (AE >= 2 && (j % AE) == AE - 1);
                 if (on_alu) h = __viaddmax_s16x2_relu(m, NEG1, 0u);
                 else asm("fma.rn.relu.f16x2 %0, %1, %2, %3;" : "=r"(h) : "r"(m), "r"(H_ONE), "r"(H_NEGULP));
                 if (j & 1) best = __vimax3_s16x2(best, m, mprev);
@@ -798,7 +807,7 @@ int launch_rerank(const DeviceRef &ref, const RerankArgs &a, cudaStream_t stream
     // per iteration: 10 / 11 / 12 / 14 = none / every / every 2nd / every 4th clamp of the second row on the alu pipe.
     // DRM_SW_KERNEL overrides the default, for A/B measurements and the parity tests.
     static const struct { const char *name; int v; } kVariants[] = {{"prmt", 0}, {"profile", 1}, {"profile16", 2}, {"blend2", 3},
-        {"blend4", 4}, {"r2a0", 10}, {"r2a1", 11}, {"r2a2", 12}, {"r2a4", 14}};
+        {"blend4", 4}, {"r2a0", 10}, {"r2a1", 11}, {"r2a2", 12}, {"r2a4", 14}, {"f32p16", 20}, {"f32b2", 21}, {"f32b4", 22}, {"f32b3", 23}};
     int variant = 3;
     if (const char *e = getenv("DRM_SW_KERNEL"))
         for (const auto &kv : kVariants)
@@ -843,6 +852,10 @@ int launch_rerank(const DeviceRef &ref, const RerankArgs &a, cudaStream_t stream
             case 2: DRM_PROFILE_LAUNCH(1, 0); break;
             case 3: DRM_PROFILE_LAUNCH(1, 2); break;
             case 4: DRM_PROFILE_LAUNCH(1, 4); break;
+            case 20: DRM_PROFILE_LAUNCH(1, 100); break;
+            case 21: DRM_PROFILE_LAUNCH(1, 102); break;
+            case 22: DRM_PROFILE_LAUNCH(1, 104); break;
+            case 23: DRM_PROFILE_LAUNCH(1, 103); break;
             case 10: DRM_PROFILE_LAUNCH(2, 0); break;
             case 11: DRM_PROFILE_LAUNCH(2, 1); break;
             case 12: DRM_PROFILE_LAUNCH(2, 2); break;
