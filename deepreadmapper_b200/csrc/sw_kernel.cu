@@ -432,8 +432,9 @@ template <int THREADS> __device__ __forceinline__ int block_exclusive_scan(int *
 
 // Dynamic shared memory layout (bytes): tab | sel[2 * PAIRS][selw] (one byte row per candidate) | cand[C] | first[take] | count[take+1]
 // THREADS = 256 (2 CTAs / SM, 128 candidates per pass) or 128 (4 CTAs / SM, 64 per pass).
-template <int RPI, int ALU_EVERY, int THREADS>
-__global__ void __launch_bounds__(THREADS, 512 / THREADS) sw_rerank_profile_kernel(const RerankDev p, int selw, unsigned one, int *fb_list, int *fb_n)
+// DENSE: ask ptxas for 768 instead of 512 resident threads per SM (80 instead of 117 registers: 3 CTAs of 256 per SM).
+template <int RPI, int ALU_EVERY, int THREADS, bool DENSE>
+__global__ void __launch_bounds__(THREADS, (DENSE ? 768 : 512) / THREADS) sw_rerank_profile_kernel(const RerankDev p, int selw, unsigned one, int *fb_list, int *fb_n)
 {
     constexpr int PAIRS = THREADS / 4;
     extern __shared__ __align__(16) unsigned char dsm[];
@@ -808,7 +809,7 @@ int launch_rerank(const DeviceRef &ref, const RerankArgs &a, cudaStream_t stream
     // DRM_SW_KERNEL overrides the default, for A/B measurements and the parity tests.
     static const struct { const char *name; int v; } kVariants[] = {{"prmt", 0}, {"profile", 1}, {"profile16", 2}, {"blend2", 3},
         {"blend4", 4}, {"r2a0", 10}, {"r2a1", 11}, {"r2a2", 12}, {"r2a4", 14}, {"f32p16", 20}, {"f32b2", 21}, {"f32b4", 22}, {"f32b3", 23}};
-    int variant = 3;
+    int variant = 4;  // blend4 + the 80-register build: profiles/r1_ab_v7_sw_dense.txt
     if (const char *e = getenv("DRM_SW_KERNEL"))
         for (const auto &kv : kVariants)
             if (!strcmp(e, kv.name)) variant = kv.v;
@@ -817,6 +818,8 @@ int launch_rerank(const DeviceRef &ref, const RerankArgs &a, cudaStream_t stream
     // that more reads are in different phases on one SM).  DRM_SW_THREADS overrides, for A/B measurements.
     int pthreads = 256;
     if (const char *e = getenv("DRM_SW_THREADS")) pthreads = atoi(e) == 128 ? 128 : 256;
+    bool pdense = true;  // the 80-register build, 3 CTAs per SM; DRM_SW_DENSE=0 selects the 117-register build (A/B)
+    if (const char *e = getenv("DRM_SW_DENSE")) pdense = atoi(e) != 0;
     const size_t psmem = (size_t)PTAB_ENTRIES * sizeof(uint4) + (size_t)(pthreads / 2) * selw + (size_t)C * sizeof(u64) +
                          (size_t)take * sizeof(u64) + (size_t)(take + 1) * sizeof(int) + 16;
     int *fb = nullptr;  // [0] = count, [1..] = reads handed back by the profile kernel
@@ -837,15 +840,16 @@ int launch_rerank(const DeviceRef &ref, const RerankArgs &a, cudaStream_t stream
         if (fast && variant != 0) {
             p.ref = ref.data;
             DRM_CUDA_TRY(cudaMemsetAsync(fb, 0, sizeof(int), stream));
-#define DRM_PROFILE_LAUNCH_T(R, A, T)                                                                                                 \
-    do {                                                                                                                               \
-        DRM_CUDA_TRY(cudaFuncSetAttribute(sw_rerank_profile_kernel<R, A, T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)psmem)); \
-        sw_rerank_profile_kernel<R, A, T><<<(unsigned)nb, T, psmem, stream>>>(p, selw, 1u, fb + 1, fb);                                \
+#define DRM_PROFILE_LAUNCH_T(R, A, T, DN)                                                                                                 \
+    do {                                                                                                                                   \
+        DRM_CUDA_TRY(cudaFuncSetAttribute(sw_rerank_profile_kernel<R, A, T, DN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)psmem)); \
+        sw_rerank_profile_kernel<R, A, T, DN><<<(unsigned)nb, T, psmem, stream>>>(p, selw, 1u, fb + 1, fb);                                \
     } while (0)
-#define DRM_PROFILE_LAUNCH(R, A)                                      \
-    do {                                                              \
-        if (pthreads == 128) DRM_PROFILE_LAUNCH_T(R, A, 128);         \
-        else DRM_PROFILE_LAUNCH_T(R, A, 256);                         \
+#define DRM_PROFILE_LAUNCH(R, A)                                            \
+    do {                                                                    \
+        if (pthreads == 128) DRM_PROFILE_LAUNCH_T(R, A, 128, false);        \
+        else if (pdense) DRM_PROFILE_LAUNCH_T(R, A, 256, true);             \
+        else DRM_PROFILE_LAUNCH_T(R, A, 256, false);                        \
     } while (0)
             switch (variant) {
             case 1: DRM_PROFILE_LAUNCH(1, 1); break;
