@@ -569,33 +569,76 @@ __global__ void __launch_bounds__(THREADS, (DENSE ? 768 : 512) / THREADS) sw_rer
 // ---- top-k: std::partial_sort(idx, idx+k, idx+n, scores[a] > scores[b]) exactly as libstdc++ runs it
 // (heap-select over [0,k) + sort_heap), so equal scores come out in the reference's order
 // (src/utils/reranker.cpp:35-48).  One thread per read.
-#define SW_COMP(a, b) (sc[(a)] > sc[(b)])
-__device__ void ps_push_heap(unsigned short *first, int hole, int top, unsigned short value, const short *sc)
+// The heap routines are libstdc++'s __push_heap / __adjust_heap / __heap_select / __sort_heap over an index array, with the
+// storage abstracted: thread-local arrays (any candidate count), or shared memory laid out [position][thread] for the dense
+// case (<= 128 candidates), where random accesses cost a shared-memory transaction instead of a local-memory one and the
+// results leave the block as coalesced rows.
+struct SelLocal {
+    unsigned short *idx; const short *sc;
+    __device__ __forceinline__ unsigned short get(int i) const { return idx[i]; }
+    __device__ __forceinline__ void set(int i, unsigned short v) { idx[i] = v; }
+    __device__ __forceinline__ bool comp(unsigned short a, unsigned short b) const { return sc[a] > sc[b]; }
+};
+constexpr int SEL_T = 64, SEL_C = 128;
+struct SelShared {
+    unsigned short (*idx)[SEL_T]; short (*sc)[SEL_T]; int t;
+    __device__ __forceinline__ unsigned short get(int i) const { return idx[i][t]; }
+    __device__ __forceinline__ void set(int i, unsigned short v) { idx[i][t] = v; }
+    __device__ __forceinline__ bool comp(unsigned short a, unsigned short b) const { return sc[a][t] > sc[b][t]; }
+};
+template <class A> __device__ __forceinline__ void ps_push_heap(A &h, int hole, int top, unsigned short value)
 {
     int parent = (hole - 1) / 2;
-    while (hole > top && SW_COMP(first[parent], value)) {
-        first[hole] = first[parent];
+    while (hole > top && h.comp(h.get(parent), value)) {
+        h.set(hole, h.get(parent));
         hole = parent;
         parent = (hole - 1) / 2;
     }
-    first[hole] = value;
+    h.set(hole, value);
 }
-__device__ void ps_adjust_heap(unsigned short *first, int hole, int len, unsigned short value, const short *sc)
+template <class A> __device__ __forceinline__ void ps_adjust_heap(A &h, int hole, int len, unsigned short value)
 {
     const int top = hole;
     int child = hole;
     while (child < (len - 1) / 2) {
         child = 2 * (child + 1);
-        if (SW_COMP(first[child], first[child - 1])) child--;
-        first[hole] = first[child];
+        if (h.comp(h.get(child), h.get(child - 1))) child--;
+        h.set(hole, h.get(child));
         hole = child;
     }
     if ((len & 1) == 0 && child == (len - 2) / 2) {
         child = 2 * (child + 1);
-        first[hole] = first[child - 1];
+        h.set(hole, h.get(child - 1));
         hole = child - 1;
     }
-    ps_push_heap(first, hole, top, value, sc);
+    ps_push_heap(h, hole, top, value);
+}
+// std::partial_sort(idx, idx + k, idx + nc, comp): heap-select, then sort_heap
+template <class A> __device__ __forceinline__ void ps_partial_sort(A &h, int k, int nc)
+{
+    if (k >= 2) {
+        int parent = (k - 2) / 2;
+        for (;;) {
+            const unsigned short value = h.get(parent);
+            ps_adjust_heap(h, parent, k, value);
+            if (parent == 0) break;
+            parent--;
+        }
+    }
+    for (int i = k; i < nc; ++i) {
+        if (h.comp(h.get(i), h.get(0))) {
+            const unsigned short value = h.get(i);
+            h.set(i, h.get(0));
+            ps_adjust_heap(h, 0, k, value);
+        }
+    }
+    int last = k;
+    while (last > 1) {
+        --last;
+        const unsigned short value = h.get(last);
+        h.set(last, h.get(0));
+        ps_adjust_heap(h, 0, last, value);
+    }
 }
 
 __global__ void sw_select_kernel(const short *__restrict__ scr_scores, const u64 *__restrict__ scr_ids, int C,
@@ -609,36 +652,53 @@ __global__ void sw_select_kernel(const short *__restrict__ scr_scores, const u64
     short sc[MAXC];
     const short *src = scr_scores + (size_t)r * C;
     for (int i = 0; i < nc; ++i) { idx[i] = (unsigned short)i; sc[i] = src[i]; }
-    if (k >= 2) {
-        int parent = (k - 2) / 2;
-        for (;;) {
-            unsigned short value = idx[parent];
-            ps_adjust_heap(idx, parent, k, value, sc);
-            if (parent == 0) break;
-            parent--;
-        }
-    }
-    for (int i = k; i < nc; ++i) {
-        if (SW_COMP(idx[i], idx[0])) {
-            unsigned short value = idx[i];
-            idx[i] = idx[0];
-            ps_adjust_heap(idx, 0, k, value, sc);
-        }
-    }
-    int last = k;
-    while (last > 1) {
-        --last;
-        unsigned short value = idx[last];
-        idx[last] = idx[0];
-        ps_adjust_heap(idx, 0, last, value, sc);
-    }
+    SelLocal h{idx, sc};
+    ps_partial_sort(h, k, nc);
     const u64 *ids = scr_ids + (size_t)r * C;
     for (int i = 0; i < k; ++i) {
         out_scores[r * k + i] = sc[idx[i]];
         out_ids[r * k + i] = ids[idx[i]];
     }
 }
-#undef SW_COMP
+
+// C <= SEL_C: one thread per read again, storage in shared memory, cooperative loads and stores.
+__global__ void __launch_bounds__(SEL_T) sw_select_smem_kernel(const short *__restrict__ scr_scores, const u64 *__restrict__ scr_ids, int C,
+                                                               const int *__restrict__ n_cands, long long n, int k, int *out_scores, u64 *out_ids)
+{
+    __shared__ unsigned short s_idx[SEL_C][SEL_T];
+    __shared__ short s_sc[SEL_C][SEL_T];
+    __shared__ int s_nc[SEL_T];
+    const int t = threadIdx.x;
+    const long long r0 = (long long)blockIdx.x * SEL_T;
+    const int nreads = (int)(n - r0 < SEL_T ? n - r0 : SEL_T);
+    if (t < nreads) s_nc[t] = n_cands[r0 + t];
+    __syncthreads();
+    for (int rr = 0; rr < nreads; ++rr) {  // coalesced: the block reads one read's score row at a time
+        const int nc = s_nc[rr];
+        const short *src = scr_scores + (size_t)(r0 + rr) * C;
+        for (int i = t; i < nc; i += SEL_T) { s_sc[i][rr] = src[i]; s_idx[i][rr] = (unsigned short)i; }
+    }
+    __syncthreads();
+    if (t < nreads) {
+        const int nc = s_nc[t];
+        if (nc >= k && nc > 0) {
+            SelShared h{s_idx, s_sc, t};
+            ps_partial_sort(h, k, nc);
+        }
+    }
+    __syncthreads();
+    for (int rr = 0; rr < nreads; ++rr) {
+        const int nc = s_nc[rr];
+        if (nc < k || nc == 0) continue;
+        const u64 *ids = scr_ids + (size_t)(r0 + rr) * C;
+        for (int i = t; i < k; i += SEL_T) {
+            const unsigned short j = s_idx[i][rr];
+            out_scores[(r0 + rr) * k + i] = s_sc[j][rr];
+            out_ids[(r0 + rr) * k + i] = ids[j];
+        }
+    }
+}
+
 
 
 // ---------------------------------------------------------------------------------------------
@@ -883,8 +943,13 @@ int launch_rerank(const DeviceRef &ref, const RerankArgs &a, cudaStream_t stream
             DRM_CUDA_TRY(cudaGetLastError());
         }
         if (a.k > 0) {
-            sw_select_kernel<<<(unsigned)((nb + 63) / 64), 64, 0, stream>>>(scr_scores, scr_ids, (int)C, p.n_cands, nb, (int)a.k,
-                                                                           a.out_scores + b0 * a.k, reinterpret_cast<u64 *>(a.out_ids) + b0 * a.k);
+            static const bool select_local = getenv("DRM_SW_SELECT") && !strcmp(getenv("DRM_SW_SELECT"), "local");  // A/B
+            if (C <= SEL_C && !select_local)
+                sw_select_smem_kernel<<<(unsigned)((nb + SEL_T - 1) / SEL_T), SEL_T, 0, stream>>>(scr_scores, scr_ids, (int)C, p.n_cands, nb, (int)a.k,
+                                                                                              a.out_scores + b0 * a.k, reinterpret_cast<u64 *>(a.out_ids) + b0 * a.k);
+            else
+                sw_select_kernel<<<(unsigned)((nb + 63) / 64), 64, 0, stream>>>(scr_scores, scr_ids, (int)C, p.n_cands, nb, (int)a.k,
+                                                                               a.out_scores + b0 * a.k, reinterpret_cast<u64 *>(a.out_ids) + b0 * a.k);
             DRM_CUDA_TRY(cudaGetLastError());
         }
     }
