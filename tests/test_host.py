@@ -97,6 +97,11 @@ def test_compute_calls_fail_loudly_without_gpu(built):
     with pytest.raises(drm.DrmError) as e:
         drm.build_index_gpu(E[:200], p + ".gpu", efc=16)
     assert e.value.code == -3 and "no CPU fallback" in str(e.value)
+    for call in (lambda: drm.fasta_clean(b">h\nACGT\n"), lambda: drm.Reads(b"@r\nACGT\n+\nIIII\n"),
+                 lambda: drm.Reference(fasta=b">h\nACGT\n", ref_len=2)):
+        with pytest.raises(drm.DrmError) as e:
+            call()
+        assert e.value.code == -3 and "no CPU fallback" in str(e.value)
 
 
 def test_index_open_errors_without_touching_gpu(tmp_path):
