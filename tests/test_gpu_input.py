@@ -144,6 +144,14 @@ def test_reference_from_fasta_and_reads_from_fastq_feed_the_stage(drm, ob, tmp_p
     D2, I2, s2, id2, st, _ = drm.search_rerank_reads(ix, ref_b, 1, Q, rd, 1, 32, 64, 64, 128)
     for a, b in ((D1, D2), (I1, I2), (s1, s2), (id1, id2)):
         assert np.array_equal(a, b)
+    if drm.lib().drm_device_count() >= 2:  # the same with everything replicated on two GPUs (reads sharded inside the call)
+        ix2, ref2, rd2 = drm.Index(path, devices=[0, 1]), drm.Reference(fasta=fasta, ref_len=150, devices=[0, 1]), drm.Reads(fastq, devices=[0, 1])
+        assert rd2.n_replicas == 2
+        D3, I3, s3, id3, _, _ = drm.search_rerank_reads(ix2, ref2, 1, Q, rd2, 1, 32, 64, 64, 128)
+        for a, b in ((D1, D3), (I1, I3), (s1, s3), (id1, id3)):
+            assert np.array_equal(a, b)
+        for h in (rd2, ref2, ix2):
+            h.close()
     # and both equal the oracle on the undecorated reads (the decoration never changes a score)
     rc, s0, i0, _ = ob.post_process_sw(1, I1, g, len(g), 150, [bytes(r) for r in reads], 1, 32, 64)
     assert rc == 0 and np.array_equal(s0, s1) and np.array_equal(i0, id1)
