@@ -365,6 +365,60 @@ __device__ __forceinline__ void build_lut_t(float *T, const float *__restrict__ 
     }
 }
 
+template <int NS, bool FULLCAP>
+__device__ __forceinline__ void pool_insert_mask(u64 (&k)[NS], u64 &maxkey, const u64 key, unsigned mask, int lane, int base, int cap,
+                                                 int max_lane, int max_slot)
+{
+    while (mask) {
+        const int src = __ffs(mask) - 1;
+        mask &= mask - 1;
+        const u64 kin = __shfl_sync(FULL, key, src);
+        if (kin >= maxkey) continue;
+        // Sorted insert without a rank computation.  kin has flag 0 and pool keys are (even base | flag), so `k[s] < kin`
+        // already ignores the flag; the pool is sorted, so lt[] is a prefix of the positions and
+        //   new[i] = lt[i] ? old[i] : (lt[i-1] ? kin : old[i-1])
+        // with position i-1 living in the previous lane for slot 0 (one 64-bit shuffle).  Duplicate test on the low word
+        // only: (id << 1 | flag) identifies the vertex, and a vertex has one distance.
+        const unsigned id1 = (unsigned)kin | 1u;
+        bool lt[NS];
+        bool dup = false;
+#pragma unroll
+        for (int s = 0; s < NS; ++s) {
+            lt[s] = k[s] < kin;
+            dup = dup || ((unsigned)k[s] | 1u) == id1;
+        }
+        if (__any_sync(FULL, dup)) continue;  // already in the pool (or the same id twice in one row)
+        const u64 pk = __shfl_up_sync(FULL, k[NS - 1], 1);
+        const bool plt = lane == 0 || pk < kin;
+#pragma unroll
+        for (int s = NS - 1; s >= 1; --s) k[s] = lt[s] ? k[s] : (lt[s - 1] ? kin : k[s - 1]);
+        k[0] = lt[0] ? k[0] : (plt ? kin : pk);
+        if (FULLCAP) {
+            maxkey = __shfl_sync(FULL, k[NS - 1], 31) & ~1ull;
+        } else {
+#pragma unroll
+            for (int s = 0; s < NS; ++s)
+                if (base + s >= cap) k[s] = POOL_INF;
+            u64 lastk = k[0];
+#pragma unroll
+            for (int s = 1; s < NS; ++s)
+                if (s == max_slot) lastk = k[s];
+            maxkey = __shfl_sync(FULL, lastk, max_lane) & ~1ull;
+        }
+    }
+}
+
+template <int NS> __device__ __forceinline__ void pool_mark_first_unexpanded(u64 (&k)[NS], int lane, int L)
+{
+    bool done = lane != L;
+#pragma unroll
+    for (int s = 0; s < NS; ++s) {
+        const bool hit = !done && !(k[s] & 1ull);
+        if (hit) k[s] |= 1ull;
+        done = done || hit;
+    }
+}
+
 // FULLCAP: cap == 32 * NS (the pool fills the registers exactly: no tail to keep at POOL_INF, the maximum is lane 31's last slot).
 // VIS: a per-warp direct-mapped cache of evaluated vertex ids in shared memory (VIS_SLOTS 16-bit tags: slot = id % VIS_SLOTS,
 // tag = id / VIS_SLOTS, exact while ntotal <= VIS_SLOTS * 65535).  A hit means "evaluated before", and a vertex evaluated
@@ -444,15 +498,7 @@ __global__ void __launch_bounds__(WARPS_PER_CTA * 32, VIS > 512 ? 5 : 6) hnswpq_
             int L; u64 k0;
             if (!pool_first_unexpanded<NS>(k, lane, L, k0)) break;
             const unsigned v0 = (unsigned)(k0 & 0xffffffffu) >> 1;
-            {   // mark it expanded
-                bool done = lane != L;
-#pragma unroll
-                for (int s = 0; s < NS; ++s) {
-                    const bool hit = !done && !(k[s] & 1ull);
-                    if (hit) k[s] |= 1ull;
-                    done = done || hit;
-                }
-            }
+            pool_mark_first_unexpanded<NS>(k, lane, L);
             int nid; Code<CS> code;
             if (v0 == spec_v) { nid = nid_s; code = code_s; }
             else {
@@ -503,43 +549,8 @@ __global__ void __launch_bounds__(WARPS_PER_CTA * 32, VIS > 512 ? 5 : 6) hnswpq_
             }
             u64 key = 0;
             if (valid) key = make_key(adc(T, code), nid);
-            unsigned mask = __ballot_sync(FULL, valid && key < maxkey);
-            while (mask) {
-                const int src = __ffs(mask) - 1;
-                mask &= mask - 1;
-                const u64 kin = __shfl_sync(FULL, key, src);
-                if (kin >= maxkey) continue;
-                // Sorted insert without a rank computation.  kin has flag 0 and pool keys are (even base | flag), so
-                // `k[s] < kin` already ignores the flag; the pool is sorted, so lt[] is a prefix of the positions and
-                //   new[i] = lt[i] ? old[i] : (lt[i-1] ? kin : old[i-1])
-                // with position i-1 living in the previous lane for slot 0 (one 64-bit shuffle).
-                const u64 kin1 = kin | 1ull;
-                bool lt[NS];
-                bool dup = false;
-#pragma unroll
-                for (int s = 0; s < NS; ++s) {
-                    lt[s] = k[s] < kin;
-                    dup = dup || (k[s] | 1ull) == kin1;
-                }
-                if (__any_sync(FULL, dup)) continue;  // already in the pool (or the same id twice in one row)
-                const u64 pk = __shfl_up_sync(FULL, k[NS - 1], 1);
-                const bool plt = lane == 0 || pk < kin;
-#pragma unroll
-                for (int s = NS - 1; s >= 1; --s) k[s] = lt[s] ? k[s] : (lt[s - 1] ? kin : k[s - 1]);
-                k[0] = lt[0] ? k[0] : (plt ? kin : pk);
-                if (FULLCAP) {
-                    maxkey = __shfl_sync(FULL, k[NS - 1], 31) & ~1ull;
-                } else {
-#pragma unroll
-                    for (int s = 0; s < NS; ++s)
-                        if (base + s >= cap) k[s] = POOL_INF;
-                    u64 lastk = k[0];
-#pragma unroll
-                    for (int s = 1; s < NS; ++s)
-                        if (s == max_slot) lastk = k[s];
-                    maxkey = __shfl_sync(FULL, lastk, max_lane) & ~1ull;
-                }
-            }
+            const unsigned mask = __ballot_sync(FULL, valid && key < maxkey);
+            pool_insert_mask<NS, FULLCAP>(k, maxkey, key, mask, lane, base, cap, max_lane, max_slot);
         }
 
         // ---------------- results: the first k pool entries, ascending (distance, id)
@@ -562,6 +573,232 @@ __global__ void __launch_bounds__(WARPS_PER_CTA * 32, VIS > 512 ? 5 : 6) hnswpq_
             atomicAdd(p.counters + 2, (u64)ndis);
         }
     }
+}
+
+// ---------------------------------------------------------------------------------------------
+// PAIR variant of the register-pool kernel (DRM_SEARCH_KERNEL=pair): every iteration evaluates the rows of the first TWO
+// unexpanded pool entries at once - lanes 0..15 take the first 16 slots of the first row, lanes 16..31 those of the second -
+// then commits the first row's candidates and, if the second entry is still the first unexpanded one afterwards (56 % of the
+// hops on the bench workload, oracle/hnswpq_oracle.cpp: orc_spec2_counters), the second row's as well.  The sequence of pool
+// states is exactly the sequential one: a speculative row that is not next is dropped (it touched neither the pool nor the
+// visited cache), and one that is next sees the pool, the maximum and the duplicate test as they are after the first commit.
+// A first row with more than 16 live neighbours is re-read by all 32 lanes (no speculation in that iteration); a second row
+// with more than 16 is not committed.  Rows further down the queue are prefetched into L2.
+template <int CS, int NS, bool FULLCAP, int VIS>
+__global__ void __launch_bounds__(WARPS_PER_CTA * 32, VIS > 512 ? 5 : 6) hnswpq_search_pair_kernel(const SearchParams p)
+{
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    float *T = reinterpret_cast<float *>(smem_raw) + (size_t)warp * p.M * 256;
+    constexpr int VIS_SLOTS = VIS > 0 ? VIS : 1;
+    unsigned short *vis = reinterpret_cast<unsigned short *>(smem_raw + (size_t)WARPS_PER_CTA * p.M * 256 * sizeof(float)) + (size_t)warp * VIS_SLOTS;
+    const int cap = p.cap;
+    const int base = lane * NS;
+    const int max_lane = (cap - 1) / NS, max_slot = (cap - 1) % NS;
+    const int half = lane >> 4, hslot = lane & 15;
+
+    for (;;) {
+        unsigned qi = 0;
+        if (lane == 0) qi = atomicAdd(p.next_query, 1u);
+        qi = __shfl_sync(FULL, qi, 0);
+        if ((long long)qi >= p.n) break;
+
+        __syncwarp();
+        if (p.centroids_t) build_lut_t(T, p.q + (size_t)qi * p.d, p.centroids_t, p.M, p.dsub, lane);
+        else build_lut(T, p.q + (size_t)qi * p.d, p.centroids, p.M, p.dsub, lane);
+        if (VIS) {
+            uint4 *v4 = reinterpret_cast<uint4 *>(vis);
+#pragma unroll
+            for (int i = 0; i < (VIS_SLOTS * 2 / 16 + 31) / 32; ++i) v4[lane + 32 * i] = make_uint4(~0u, ~0u, ~0u, ~0u);
+        }
+        __syncwarp();
+
+        unsigned nhops0 = 0, nhops_up = 0, ndis = 0;
+
+        // ---------------- greedy descent, levels max_level .. 1 (as in the sequential kernel)
+        float d_near = adc_bytes<CS>(T, p.entry_code);
+        long long vertex = p.entry_vertex;
+        if (p.max_level >= 1) {
+            long long r = p.entry_row;
+            for (int level = p.max_level; level >= 1; --level) {
+                for (;;) {
+                    const uint8_t *row = p.up + (size_t)r * p.rowu_bytes;
+                    int nr = -1;
+                    float dj = __uint_as_float(0x7f800000u);
+                    if (lane < p.Wu) nr = __ldg(reinterpret_cast<const int *>(row + 16) + lane);
+                    unsigned neg = __ballot_sync(FULL, lane < p.Wu && nr < 0);
+                    int first_neg = neg ? (__ffs(neg) - 1) : p.Wu;
+                    if (lane < first_neg) dj = adc(T, load_code<CS>(row + p.cu_off + CS * lane));
+                    u64 best = warp_min_u64(((u64)__float_as_uint(dj) << 32) | (unsigned)lane);
+                    float dmin = __uint_as_float((unsigned)(best >> 32));
+                    ++nhops_up;
+                    if (dmin < d_near) {
+                        d_near = dmin;
+                        r = __shfl_sync(FULL, nr, (int)(best & 31u));
+                    } else break;
+                }
+                if (level > 1) r -= 1;
+            }
+            vertex = __ldg(reinterpret_cast<const int *>(p.up + (size_t)r * p.rowu_bytes));
+        }
+
+        // ---------------- level 0
+        if (VIS && lane == 0) vis[(unsigned)vertex % VIS_SLOTS] = (unsigned short)((unsigned)vertex / VIS_SLOTS);
+        u64 k[NS];
+#pragma unroll
+        for (int s = 0; s < NS; ++s) k[s] = POOL_INF;
+        if (lane == 0) k[0] = make_key(d_near, (int)vertex);
+        u64 maxkey = POOL_INF & ~1ull;
+        for (;;) {
+            // first and second unexpanded entry of every lane, then of the pool (positions are lane-major)
+            u64 mine = POOL_INF, mine2 = POOL_INF;
+#pragma unroll
+            for (int s = NS - 1; s >= 0; --s)
+                if (!(k[s] & 1ull)) { mine2 = mine; mine = k[s]; }
+            const unsigned bal = __ballot_sync(FULL, !(mine & 1ull));
+            if (!bal) break;
+            const int L1 = __ffs(bal) - 1;
+            const u64 k1 = __shfl_sync(FULL, mine, L1);
+            const u64 s2 = __shfl_sync(FULL, mine2, L1);
+            const unsigned rest = bal & (bal - 1);
+            const int Lb = rest ? __ffs(rest) - 1 : L1;
+            const u64 nb = __shfl_sync(FULL, mine, Lb);
+            const bool same_lane = !(s2 & 1ull);
+            const bool has2 = same_lane || rest != 0;
+            const u64 k2 = same_lane ? s2 : nb;
+            pool_mark_first_unexpanded<NS>(k, lane, L1);
+            const unsigned v1 = (unsigned)(k1 & 0xffffffffu) >> 1, v2 = (unsigned)(k2 & 0xffffffffu) >> 1;
+
+            // the two half rows
+            const bool load = hslot < p.W0 && (half == 0 || has2);
+            const uint8_t *row = p.rows0 + (size_t)(half ? v2 : v1) * p.row0_bytes;
+            int nid = -1;
+            Code<CS> code;
+            code.v = {};
+            if (load) {
+                nid = __ldg(reinterpret_cast<const int *>(row) + hslot);
+                code = load_code<CS>(row + p.c0_off + CS * hslot);
+            }
+            {   // L2 prefetch of the rows of the next entries in the queue (other lanes' first unexpanded entries)
+                unsigned q = same_lane ? rest : (rest & (rest - 1));
+                const int la = q ? __ffs(q) - 1 : -1;
+                q &= q - 1;
+                const int lb = q ? __ffs(q) - 1 : -1;
+                if (lane == la || lane == lb) {
+                    const uint8_t *prow = p.rows0 + (size_t)((unsigned)(mine & 0xffffffffu) >> 1) * p.row0_bytes;
+                    for (int o = 0; o < p.row0_bytes; o += 128) asm volatile("prefetch.global.L2 [%0];" ::"l"(prow + o));
+                }
+            }
+            ++nhops0;
+            const unsigned neg = __ballot_sync(FULL, nid < 0);
+            const unsigned neg1 = neg & 0xffffu, neg2 = neg >> 16;
+            const int fn1 = neg1 ? __ffs(neg1) - 1 : 16, fn2 = neg2 ? __ffs(neg2) - 1 : 16;
+
+            if (fn1 == 16 && p.W0 > 16) {
+                // the first row may have more than 16 live neighbours: all 32 lanes take it, nothing speculative this time
+                const uint8_t *r1 = p.rows0 + (size_t)v1 * p.row0_bytes;
+                nid = lane < p.W0 ? __ldg(reinterpret_cast<const int *>(r1) + lane) : -1;
+                code.v = {};
+                if (lane < p.W0) code = load_code<CS>(r1 + p.c0_off + CS * lane);
+                const unsigned ng = __ballot_sync(FULL, nid < 0);
+                const int first_neg = ng ? (__ffs(ng) - 1) : 32;
+                bool valid = lane < first_neg;
+                if (VIS) {
+                    if (valid) {
+                        const unsigned slot = (unsigned)nid % VIS_SLOTS;
+                        const unsigned short tag = (unsigned short)((unsigned)nid / VIS_SLOTS);
+                        if (vis[slot] == tag) valid = false;
+                        else vis[slot] = tag;
+                    }
+                }
+                const unsigned fresh = __ballot_sync(FULL, valid);
+                ndis += (unsigned)__popc(fresh);
+                u64 key = 0;
+                if (valid) key = make_key(adc(T, code), nid);
+                const unsigned mask = __ballot_sync(FULL, valid && key < maxkey);
+                pool_insert_mask<NS, FULLCAP>(k, maxkey, key, mask, lane, base, cap, max_lane, max_slot);
+                continue;
+            }
+
+            const bool spec_ok = has2 && !(fn2 == 16 && p.W0 > 16);
+            bool valid = half == 0 ? hslot < fn1 : (spec_ok && hslot < fn2);
+            unsigned slot = 0;
+            unsigned short tag = 0;
+            if (VIS) {
+                if (valid) {
+                    slot = (unsigned)nid % VIS_SLOTS;
+                    tag = (unsigned short)((unsigned)nid / VIS_SLOTS);
+                    if (vis[slot] == tag) valid = false;
+                }
+                __syncwarp();
+                if (valid && half == 0) vis[slot] = tag;  // the speculative half marks nothing until it is committed
+            }
+            const unsigned fresh = __ballot_sync(FULL, valid);
+            ndis += (unsigned)__popc(fresh & 0xffffu);
+            u64 key = 0;
+            if (valid) key = make_key(adc(T, code), nid);
+            {
+                const unsigned mask = __ballot_sync(FULL, valid && key < maxkey) & 0xffffu;
+                pool_insert_mask<NS, FULLCAP>(k, maxkey, key, mask, lane, base, cap, max_lane, max_slot);
+            }
+            if (spec_ok) {
+                int Lx; u64 kx;
+                if (pool_first_unexpanded<NS>(k, lane, Lx, kx) && kx == k2) {
+                    pool_mark_first_unexpanded<NS>(k, lane, Lx);
+                    ++nhops0;
+                    if (VIS && valid && half == 1) vis[slot] = tag;
+                    ndis += (unsigned)__popc(fresh >> 16);
+                    const unsigned mask = __ballot_sync(FULL, valid && key < maxkey) & 0xffff0000u;
+                    pool_insert_mask<NS, FULLCAP>(k, maxkey, key, mask, lane, base, cap, max_lane, max_slot);
+                }
+            }
+        }
+
+        // ---------------- results: the first k pool entries, ascending (distance, id)
+        float *Dq = p.D + (size_t)qi * p.k;
+        long long *Iq = p.I + (size_t)qi * p.k;
+#pragma unroll
+        for (int s = 0; s < NS; ++s) {
+            const int i = base + s;
+            if (i < p.k) {
+                const u64 kk = k[s];
+                const bool filled = kk != POOL_INF;
+                Dq[i] = filled ? __uint_as_float((unsigned)(kk >> 32)) : FLT_MAX;
+                Iq[i] = filled ? (long long)((unsigned)(kk & 0xffffffffu) >> 1) : -1ll;
+            }
+        }
+        if (p.counters && lane == 0) {
+            atomicAdd(p.counters + 0, (u64)nhops0);
+            atomicAdd(p.counters + 1, (u64)nhops_up);
+            atomicAdd(p.counters + 2, (u64)ndis);
+        }
+    }
+}
+
+template <int CS, int NS, bool FULLCAP, int VIS>
+int launch_pair_tfv(const SearchParams &p, size_t smem, int device, cudaStream_t stream)
+{
+    auto kern = hnswpq_search_pair_kernel<CS, NS, FULLCAP, VIS>;
+    smem += (size_t)WARPS_PER_CTA * VIS * sizeof(unsigned short);
+    DRM_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int per_sm = 0, sms = 0;
+    DRM_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, WARPS_PER_CTA * 32, smem));
+    DRM_CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device));
+    if (per_sm < 1) return fail(DRM_EUNSUPPORTED, "search kernel does not fit on an SM with these parameters");
+    long long want = (p.n + WARPS_PER_CTA - 1) / WARPS_PER_CTA;
+    long long grid = (long long)per_sm * sms;
+    if (want < grid) grid = want;
+    kern<<<(unsigned)grid, WARPS_PER_CTA * 32, smem, stream>>>(p);
+    DRM_CUDA_TRY(cudaGetLastError());
+    return DRM_OK;
+}
+
+template <int CS, int NS>
+int launch_pair_t(const SearchParams &p, size_t smem, int device, cudaStream_t stream)
+{
+    const bool vis = p.ntotal < 512ll * 65535;
+    if (p.cap == 32 * NS) return vis ? launch_pair_tfv<CS, NS, true, 512>(p, smem, device, stream) : launch_pair_tfv<CS, NS, true, 0>(p, smem, device, stream);
+    return vis ? launch_pair_tfv<CS, NS, false, 512>(p, smem, device, stream) : launch_pair_tfv<CS, NS, false, 0>(p, smem, device, stream);
 }
 
 template <int CS, int NS, bool FULLCAP, int VIS>
@@ -662,6 +899,10 @@ int launch_search(const DeviceIndex &dx, const float *q_dev, int64_t n, int k, i
     if (!want_smem && dx.W0 <= 32 && k <= ef && cap <= 256) {
         const size_t smem_r = (size_t)WARPS_PER_CTA * (size_t)dx.M * 256 * sizeof(float);
         const int ns = cap <= 64 ? 2 : cap <= 128 ? 4 : 8;
+        if (force && !strcmp(force, "pair")) {  // two rows per iteration (A/B; same bits)
+            if (dx.code_size == 8) return ns == 2 ? launch_pair_t<8, 2>(p, smem_r, dx.device, stream) : ns == 4 ? launch_pair_t<8, 4>(p, smem_r, dx.device, stream) : launch_pair_t<8, 8>(p, smem_r, dx.device, stream);
+            return ns == 2 ? launch_pair_t<16, 2>(p, smem_r, dx.device, stream) : ns == 4 ? launch_pair_t<16, 4>(p, smem_r, dx.device, stream) : launch_pair_t<16, 8>(p, smem_r, dx.device, stream);
+        }
         if (dx.code_size == 8) return ns == 2 ? launch_reg_t<8, 2>(p, smem_r, dx.device, stream) : ns == 4 ? launch_reg_t<8, 4>(p, smem_r, dx.device, stream) : launch_reg_t<8, 8>(p, smem_r, dx.device, stream);
         return ns == 2 ? launch_reg_t<16, 2>(p, smem_r, dx.device, stream) : ns == 4 ? launch_reg_t<16, 4>(p, smem_r, dx.device, stream) : launch_reg_t<16, 8>(p, smem_r, dx.device, stream);
     }

@@ -34,6 +34,7 @@
 #include <cmath>
 #include <cstdint>
 #include <cstdio>
+#include <atomic>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -339,6 +340,11 @@ void search_one(const OrcIndex &ix, const float *x, int k, int efSearch, int tie
 // and - because cap >= k - the result heap is simply its first k entries.  Wherever no two distances
 // are bit-equal this is exactly FAISS's procedure; it differs from tie_rule 0 only in which of
 // several equal-distance vertices survive at a full boundary.  The CUDA kernel implements this rule.
+// Analysis counters (tools only): how often the SECOND unexpanded pool entry at the start of a hop is the entry the next
+// hop expands - i.e. how often a kernel that evaluated two rows at once could keep both results without changing the
+// search (orc_spec2_counters).
+static std::atomic<long long> g_spec2_yes{0}, g_spec2_total{0};
+
 void search_one_canonical(const OrcIndex &ix, const float *x, int k, int efSearch, VisitedTable &vt,
                           std::vector<float> &T, float *D, int64_t *I, Stats &st)
 {
@@ -377,6 +383,14 @@ void search_one_canonical(const OrcIndex &ix, const float *x, int k, int efSearc
         const float d0 = pool[cur].d;
         const int32_t v0 = pool[cur].id;
         pool[cur].expanded = true;
+        {   // spec-2 analysis: was this hop's vertex the runner-up of the previous hop?
+            static thread_local int32_t runner_up = -1;
+            if (st.nhops > 0 || runner_up >= 0) { g_spec2_total++; if (runner_up == v0) g_spec2_yes++; }
+            size_t nx = cur + 1;
+            while (nx < pool.size() && pool[nx].expanded) ++nx;
+            runner_up = nx < pool.size() ? pool[nx].id : -1;
+            if (cur == 0 && pool.size() == 1) runner_up = -1;
+        }
         int below = 0;
         for (const Ent &e : pool) below += e.d < d0;
         if (below >= efSearch) break;
@@ -406,6 +420,11 @@ void search_one_canonical(const OrcIndex &ix, const float *x, int k, int efSearc
 extern "C" {
 
 const char *orc_last_error() { return g_err.c_str(); }
+void orc_spec2_counters(int64_t *out, int reset)
+{
+    out[0] = g_spec2_yes.load(); out[1] = g_spec2_total.load();
+    if (reset) { g_spec2_yes = 0; g_spec2_total = 0; }
+}
 
 void *orc_index_read(const char *path)
 {

@@ -204,10 +204,10 @@ def mid_index(tmp_path_factory):
     return p, synth.embed_reads(reads), ids
 
 
-@pytest.fixture(params=["reg", "reg_vis1024", "reg_novis", "smem"])
+@pytest.fixture(params=["reg", "reg_vis1024", "reg_novis", "smem", "pair"])
 def search_variant(request, monkeypatch):
     """Every search kernel (register pool with the 512- / 1024-slot visited cache or none, shared-memory pool) must return the oracle's bits."""
-    monkeypatch.setenv("DRM_SEARCH_KERNEL", "smem" if request.param == "smem" else "reg")
+    monkeypatch.setenv("DRM_SEARCH_KERNEL", request.param if request.param in ("smem", "pair") else "reg")
     monkeypatch.setenv("DRM_SEARCH_VIS", {"reg_novis": "0", "reg_vis1024": "1024"}.get(request.param, "512"))
     return request.param
 
