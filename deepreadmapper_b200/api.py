@@ -35,7 +35,9 @@ EXPORTS = ["drm_last_error", "drm_device_count", "drm_version", "drm_index_open"
            "drm_sw_pairs", "drm_sw_rerank", "drm_sw_rerank_device", "drm_merge_topk_device", "drm_build_index",
            "drm_search_rerank", "drm_build_index_gpu", "drm_build_index_gpu_device", "drm_fasta_clean", "drm_ref_open_fasta",
            "drm_reads_open_fastq", "drm_reads_close", "drm_reads_info", "drm_reads_copy_out", "drm_reads_device",
-           "drm_search_rerank_reads", "drm_sw_align"]
+           "drm_search_rerank_reads", "drm_sw_align", "drm_embedder_open_ir", "drm_embedder_open_raw", "drm_embedder_close",
+           "drm_embedder_ir_info", "drm_tokenize", "drm_embed", "drm_embed_reads", "drm_embed_windows", "drm_embed_device",
+           "drm_embed_windows_device"]
 
 
 def lib_path() -> str:
@@ -83,6 +85,17 @@ def lib():
         L.drm_build_index_gpu_device.argtypes = [vp, i64, i32, i64, i32, i32, i32, i32, i32, C.c_uint32, C.c_char_p, vp]
         L.drm_search_rerank.argtypes = [vp, vp, i32, vp, i64, i32, i32, i32, vp, vp, i64, i64, i64, vp, vp, vp, vp,
                                         C.POINTER(SearchStats), vp]
+        L.drm_embedder_open_ir.argtypes = [C.c_char_p, C.c_char_p, i32, C.POINTER(vp)]
+        L.drm_embedder_open_raw.argtypes = [vp, i32, vp, vp, vp, vp, vp, vp, i32, i32, C.POINTER(vp)]
+        L.drm_embedder_close.argtypes = [vp]
+        L.drm_embedder_close.restype = None
+        L.drm_embedder_ir_info.argtypes = [C.c_char_p, C.c_char_p, vp, vp]
+        L.drm_tokenize.argtypes = [C.c_char_p, vp, i64, i32, vp]
+        L.drm_embed.argtypes = [vp, C.c_char_p, vp, i64, vp]
+        L.drm_embed_reads.argtypes = [vp, vp, i64, i64, vp]
+        L.drm_embed_windows.argtypes = [vp, vp, C.c_uint64, C.c_uint64, i64, vp]
+        L.drm_embed_device.argtypes = [vp, vp, vp, i64, i64, vp, vp]
+        L.drm_embed_windows_device.argtypes = [vp, vp, C.c_uint64, C.c_uint64, i64, vp, vp]
         _lib = L
     return _lib
 
@@ -403,3 +416,87 @@ def build_index_gpu_device(x_dev_ptr, n, d, out_path, train_step=2, M_pq=8, nbit
     _check(lib().drm_build_index_gpu_device(x_dev_ptr, n, d, train_step, M_pq, nbits, M_hnsw, efc, device, seed,
                                             os.fsencode(out_path), tim.ctypes.data))
     return dict(zip(BUILD_STAGES, tim.tolist()))
+
+
+# ---- embedder -------------------------------------------------------------------------------------
+MAX_LEN = 123  # Config::Inference::MAX_LEN (includes/utils/config.hpp:21)
+
+
+def tokenize(seqs, max_len=MAX_LEN):
+    """Preprocessor::preprocessBatch (src/inference/preprocess.cpp:44-77): n x max_len vocabulary ids, 0-padded."""
+    flat, off = flatten(seqs)
+    out = np.zeros((len(off) - 1, max_len), dtype=np.uint16)
+    _check(lib().drm_tokenize(flat, off.ctypes.data, len(off) - 1, max_len, out.ctypes.data))
+    return out
+
+
+def embedder_ir_info(xml_path, bin_path):
+    """Host-side look at an OpenVINO IR pair: (vocabulary rows, element counts, sums) of emb, W1, R1, B1, W2, R2, B2."""
+    info = np.zeros(8, dtype=np.int64)
+    sums = np.zeros(7, dtype=np.float64)
+    _check(lib().drm_embedder_ir_info(os.fsencode(xml_path), os.fsencode(bin_path), info.ctypes.data, sums.ctypes.data))
+    return int(info[0]), info[1:].copy(), sums
+
+
+class Vectorizer:
+    """Vectorizer (src/inference/vectorize.cpp:4-141) on the GPU: tokeniser + token embedding + 2-layer bidirectional GRU.
+    Open it on the reference's model files (model_path = the .xml; the .bin sits next to it) or on a dict of fp16 arrays
+    {emb, W1, R1, B1, W2, R2, B2} in the IR's layout."""
+
+    def __init__(self, model_path=None, weights=None, max_len=MAX_LEN, device=0):
+        h = C.c_void_p()
+        if weights is not None:
+            a = {k: np.ascontiguousarray(weights[k], dtype=np.float16) for k in ("emb", "W1", "R1", "B1", "W2", "R2", "B2")}
+            want = {"W1": (2, 192, 64), "R1": (2, 192, 64), "B1": (2, 256), "W2": (2, 192, 128), "R2": (2, 192, 64), "B2": (2, 256)}
+            for k, shp in want.items():
+                if a[k].shape != shp:
+                    raise DrmError(-1, f"embedder weight {k} has shape {a[k].shape}, expected {shp}")
+            if a["emb"].ndim != 2 or a["emb"].shape[1] != 64:
+                raise DrmError(-1, "embedder weight emb must be [vocab, 64]")
+            _check(lib().drm_embedder_open_raw(a["emb"].ctypes.data, a["emb"].shape[0], a["W1"].ctypes.data, a["R1"].ctypes.data,
+                                               a["B1"].ctypes.data, a["W2"].ctypes.data, a["R2"].ctypes.data, a["B2"].ctypes.data,
+                                               max_len, device, C.byref(h)))
+        else:
+            if max_len != MAX_LEN:
+                raise DrmError(-1, "an IR model is opened with the reference's MAX_LEN")
+            xml = os.fspath(model_path)
+            _check(lib().drm_embedder_open_ir(os.fsencode(xml), os.fsencode(os.path.splitext(xml)[0] + ".bin"), device, C.byref(h)))
+        self._h = h
+        self.device = device
+        self.max_len = max_len
+
+    def close(self):
+        if getattr(self, "_h", None):
+            lib().drm_embedder_close(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def vectorize(self, seqs):
+        """Vectorizer::vectorize: byte strings (decorated or not, exactly as given) -> float32 [n, 128]."""
+        flat, off = flatten(seqs)
+        n = len(off) - 1
+        out = np.zeros((n, 128), dtype=np.float32)
+        _check(lib().drm_embed(self._h, flat, off.ctypes.data, n, out.ctypes.data))
+        return out
+
+    def vectorize_reads(self, reads: "Reads", first=0, n=None):
+        n = reads.n - first if n is None else n
+        out = np.zeros((n, 128), dtype=np.float32)
+        _check(lib().drm_embed_reads(self._h, reads._h, first, n, out.ctypes.data))
+        return out
+
+    def vectorize_windows(self, ref: "Reference", first_id, id_step, n):
+        out = np.zeros((n, 128), dtype=np.float32)
+        _check(lib().drm_embed_windows(self._h, ref._h, first_id, id_step, n, out.ctypes.data))
+        return out
+
+    def vectorize_device(self, flat_ptr, off_ptr, first, n, out_ptr, stream=0):
+        _check(lib().drm_embed_device(self._h, flat_ptr, off_ptr, first, n, out_ptr, stream))
+
+    def vectorize_windows_device(self, ref: "Reference", first_id, id_step, n, out_ptr, stream=0):
+        _check(lib().drm_embed_windows_device(self._h, ref._h, first_id, id_step, n, out_ptr, stream))

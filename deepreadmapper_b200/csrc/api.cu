@@ -47,6 +47,10 @@ struct drm_reads {
     int max_len = 0;
 };
 
+struct drm_embedder {
+    drm::DeviceEmbedder dev;
+};
+
 namespace {
 
 using namespace drm;
@@ -703,6 +707,188 @@ int drm_merge_topk_device(int device, const float *D_all, const int64_t *I_all, 
 {
     DRM_CUDA_TRY(cudaSetDevice(device));
     return launch_merge_topk(D_all, I_all, n_shards, n, k, D_out, I_out, static_cast<cudaStream_t>(stream));
+}
+
+/* ------------------------------------------------------------------ embedder */
+namespace {
+
+int open_embedder(const EmbedWeightsHost &w, int max_len, int device, drm_embedder **out)
+{
+    int count = 0;
+    if (cudaGetDeviceCount(&count) != cudaSuccess || count < 1) return fail(DRM_ECUDA, "no CUDA device: the embedder has no CPU fallback");
+    if (device < 0 || device >= count) return fail(DRM_EINVAL, "bad device for the embedder");
+    drm_embedder *e = new drm_embedder();
+    const int rc = embedder_upload(w, device, max_len, e->dev);
+    if (rc != DRM_OK) { embedder_free(e->dev); delete e; return rc; }
+    *out = e;
+    return DRM_OK;
+}
+
+const DeviceRef *ref_on_device(const drm_ref *r, int device)
+{
+    if (!r) return nullptr;
+    for (const DeviceRef &d : r->rep)
+        if (d.device == device) return &d;
+    return nullptr;
+}
+
+// runs a source through the embedder and copies the n x 128 result to the host
+int embed_to_host(drm_embedder *e, const EmbedSource &src, int64_t first, int64_t n, float *out)
+{
+    DevBuf d_out;
+    int rc;
+    if ((rc = d_out.alloc((size_t)n * 128 * sizeof(float)))) return rc;
+    if ((rc = launch_embed(e->dev, src, first, n, d_out.as<float>(), 0)) != DRM_OK) return rc;
+    DRM_CUDA_TRY(cudaMemcpy(out, d_out.p, (size_t)n * 128 * sizeof(float), cudaMemcpyDeviceToHost));
+    return DRM_OK;
+}
+
+int window_source(const drm_embedder *e, const drm_ref *ref, uint64_t first_id, uint64_t id_step, EmbedSource &src)
+{
+    const DeviceRef *dr = ref_on_device(ref, e->dev.device);
+    if (!dr) return fail(DRM_EINVAL, "the reference has no replica on the embedder's device");
+    src.mode = 1; src.cls = dr->data; src.form = dr->form; src.ref_n = dr->len; src.ref_len = dr->ref_len;
+    src.first_id = first_id; src.id_step = id_step;
+    return DRM_OK;
+}
+
+}  // namespace
+
+int drm_embedder_open_ir(const char *xml_path, const char *bin_path, int device, drm_embedder **out)
+{
+    if (!out) return fail(DRM_EINVAL, "null output handle");
+    *out = nullptr;
+    if (!xml_path || !bin_path) return fail(DRM_EINVAL, "null model path");
+    EmbedWeightsHost w;
+    const int rc = read_ir_model(xml_path, bin_path, w);
+    if (rc != DRM_OK) return rc;
+    return open_embedder(w, 123, device, out);
+}
+
+int drm_embedder_open_raw(const uint16_t *emb, int vocab, const uint16_t *W1, const uint16_t *R1, const uint16_t *B1,
+                          const uint16_t *W2, const uint16_t *R2, const uint16_t *B2, int max_len, int device, drm_embedder **out)
+{
+    if (!out) return fail(DRM_EINVAL, "null output handle");
+    *out = nullptr;
+    if (!emb || vocab < 1 || !W1 || !R1 || !B1 || !W2 || !R2 || !B2) return fail(DRM_EINVAL, "bad embedder weights");
+    EmbedWeightsHost w;
+    w.vocab = vocab;
+    auto conv = [](const uint16_t *src, size_t n, std::vector<float> &dst) {
+        dst.resize(n);
+        for (size_t i = 0; i < n; ++i) dst[i] = half_bits_to_float(src[i]);
+    };
+    conv(emb, (size_t)vocab * 64, w.emb);
+    conv(W1, 2u * 192 * 64, w.W1); conv(R1, 2u * 192 * 64, w.R1); conv(B1, 2u * 256, w.B1);
+    conv(W2, 2u * 192 * 128, w.W2); conv(R2, 2u * 192 * 64, w.R2); conv(B2, 2u * 256, w.B2);
+    return open_embedder(w, max_len, device, out);
+}
+
+void drm_embedder_close(drm_embedder *e)
+{
+    if (!e) return;
+    embedder_free(e->dev);
+    delete e;
+}
+
+int drm_embedder_ir_info(const char *xml_path, const char *bin_path, int64_t *info, double *sums)
+{
+    if (!xml_path || !bin_path || !info) return fail(DRM_EINVAL, "null argument");
+    EmbedWeightsHost w;
+    const int rc = read_ir_model(xml_path, bin_path, w);
+    if (rc != DRM_OK) return rc;
+    const std::vector<float> *t[7] = {&w.emb, &w.W1, &w.R1, &w.B1, &w.W2, &w.R2, &w.B2};
+    info[0] = w.vocab;
+    for (int i = 0; i < 7; ++i) {
+        info[1 + i] = (int64_t)t[i]->size();
+        if (sums) {
+            double s = 0.0;
+            for (float v : *t[i]) s += v;
+            sums[i] = s;
+        }
+    }
+    return DRM_OK;
+}
+
+int drm_tokenize(const char *seq_flat, const int64_t *seq_off, int64_t n, int max_len, uint16_t *tokens)
+{
+    if (n <= 0) return DRM_OK;
+    if (!seq_flat || !seq_off || !tokens || max_len < 2 || max_len > 128) return fail(DRM_EINVAL, "bad arguments to drm_tokenize");
+    tokenize_host(seq_flat, seq_off, n, max_len, tokens);
+    return DRM_OK;
+}
+
+int drm_embed(drm_embedder *e, const char *seq_flat, const int64_t *seq_off, int64_t n, float *out)
+{
+    if (!e) return fail(DRM_EINVAL, "null embedder handle");
+    if (n <= 0) return DRM_OK;
+    if (!seq_flat || !seq_off || !out) return fail(DRM_EINVAL, "bad arguments to drm_embed");
+    DRM_CUDA_TRY(cudaSetDevice(e->dev.device));
+    const int64_t bytes = seq_off[n] - seq_off[0];
+    std::vector<int64_t> rel((size_t)n + 1);
+    for (int64_t i = 0; i <= n; ++i) {
+        rel[(size_t)i] = seq_off[i] - seq_off[0];
+        if (i && rel[(size_t)i] < rel[(size_t)i - 1]) return fail(DRM_EINVAL, "sequence offsets must not decrease");
+    }
+    DevBuf d_flat, d_off;
+    int rc;
+    if ((rc = d_flat.alloc((size_t)bytes)) || (rc = d_off.alloc((size_t)(n + 1) * 8))) return rc;
+    if (bytes) DRM_CUDA_TRY(cudaMemcpy(d_flat.p, seq_flat + seq_off[0], (size_t)bytes, cudaMemcpyHostToDevice));
+    DRM_CUDA_TRY(cudaMemcpy(d_off.p, rel.data(), (size_t)(n + 1) * 8, cudaMemcpyHostToDevice));
+    EmbedSource src;
+    src.mode = 0; src.flat = d_flat.as<char>(); src.off = d_off.as<int64_t>();
+    return embed_to_host(e, src, 0, n, out);
+}
+
+int drm_embed_reads(drm_embedder *e, const drm_reads *reads, int64_t first, int64_t n, float *out)
+{
+    if (!e || !reads) return fail(DRM_EINVAL, "null handle");
+    if (n <= 0) return DRM_OK;
+    if (!out || first < 0 || first + n > reads->n) return fail(DRM_EINVAL, "bad read range for drm_embed_reads");
+    const ReadsRep *rep = nullptr;
+    for (const ReadsRep &r : reads->rep)
+        if (r.device == e->dev.device) rep = &r;
+    if (!rep) return fail(DRM_EINVAL, "the reads have no replica on the embedder's device");
+    DRM_CUDA_TRY(cudaSetDevice(e->dev.device));
+    EmbedSource src;
+    src.mode = 0; src.flat = rep->flat; src.off = rep->off;
+    return embed_to_host(e, src, first, n, out);
+}
+
+int drm_embed_windows(drm_embedder *e, const drm_ref *ref, uint64_t first_id, uint64_t id_step, int64_t n, float *out)
+{
+    if (!e || !ref) return fail(DRM_EINVAL, "null handle");
+    if (n <= 0) return DRM_OK;
+    if (!out) return fail(DRM_EINVAL, "null output");
+    EmbedSource src;
+    int rc = window_source(e, ref, first_id, id_step, src);
+    if (rc != DRM_OK) return rc;
+    DRM_CUDA_TRY(cudaSetDevice(e->dev.device));
+    return embed_to_host(e, src, 0, n, out);
+}
+
+int drm_embed_device(drm_embedder *e, const char *seq_flat_dev, const int64_t *seq_off_dev, int64_t first, int64_t n,
+                     float *out_dev, void *stream)
+{
+    if (!e) return fail(DRM_EINVAL, "null embedder handle");
+    if (n <= 0) return DRM_OK;
+    if (!seq_flat_dev || !seq_off_dev || !out_dev || first < 0) return fail(DRM_EINVAL, "bad arguments to drm_embed_device");
+    DRM_CUDA_TRY(cudaSetDevice(e->dev.device));
+    EmbedSource src;
+    src.mode = 0; src.flat = seq_flat_dev; src.off = seq_off_dev;
+    return launch_embed(e->dev, src, first, n, out_dev, static_cast<cudaStream_t>(stream));
+}
+
+int drm_embed_windows_device(drm_embedder *e, const drm_ref *ref, uint64_t first_id, uint64_t id_step, int64_t n,
+                             float *out_dev, void *stream)
+{
+    if (!e || !ref) return fail(DRM_EINVAL, "null handle");
+    if (n <= 0) return DRM_OK;
+    if (!out_dev) return fail(DRM_EINVAL, "null output");
+    EmbedSource src;
+    int rc = window_source(e, ref, first_id, id_step, src);
+    if (rc != DRM_OK) return rc;
+    DRM_CUDA_TRY(cudaSetDevice(e->dev.device));
+    return launch_embed(e->dev, src, 0, n, out_dev, static_cast<cudaStream_t>(stream));
 }
 
 }  // extern "C"

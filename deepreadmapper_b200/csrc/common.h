@@ -130,4 +130,41 @@ int clean_fasta_device(const char *data, int64_t size, int device, uint8_t **d_g
 int parse_fastq_device(const char *data, int64_t size, int device, char **d_flat, int64_t **d_off, int64_t *n_reads,
                        int64_t *flat_bytes, int *max_len);
 
+// ---------------------------------------------------------------------------------------------
+// Embedder: 3-mer tokeniser + token embedding + 2-layer bidirectional GRU (hidden 64) -> 128-d,
+// the network in the reference's models/*.xml that src/inference/vectorize.cpp:34-141 runs through OpenVINO.
+// ir_model.cpp reads the IR; embed_kernel.cu holds the device side.
+struct EmbedWeightsHost {  // fp32, gate order z, r, h as GRUSequence stores them
+    int vocab = 0;
+    std::vector<float> emb;         // [vocab][64]
+    std::vector<float> W1, R1, B1;  // [2][192][64], [2][192][64], [2][256]
+    std::vector<float> W2, R2, B2;  // [2][192][128], [2][192][64], [2][256]
+};
+int read_ir_model(const char *xml_path, const char *bin_path, EmbedWeightsHost &w);
+float half_bits_to_float(uint16_t h);
+
+struct DeviceEmbedder {
+    int device = -1;
+    int max_len = 123;  // Config::Inference::MAX_LEN (includes/utils/config.hpp:21)
+    float *P1 = nullptr;   // [2][97][192] layer-1 input projection of every token the tokeniser can emit (+ bias)
+    float *R1 = nullptr, *bR1 = nullptr;  // [2][192][64], [2][64]
+    float *W2 = nullptr, *b2 = nullptr;   // [2][192][128], [2][192]
+    float *R2 = nullptr, *bR2 = nullptr;  // [2][192][64], [2][64]
+    int64_t chunk = 0;     // sequences per pass; the scratch below is sized for it
+    float *Y1 = nullptr;   // [chunk][max_len][128] layer-1 states, forward | backward
+    float *X2 = nullptr;   // [chunk][max_len][2][192] layer-2 input projections
+    float *out = nullptr;  // [chunk][128] staging for host-pointer calls
+};
+struct EmbedSource {
+    int mode = 0;  // 0: byte strings flat/off; 1: '<' + reference window + '>' by window id (find_sequence ids)
+    const char *flat = nullptr; const int64_t *off = nullptr;
+    const uint8_t *cls = nullptr; int form = 0; int64_t ref_n = 0; int ref_len = 0;  // DeviceRef::data
+    unsigned long long first_id = 0, id_step = 1;
+};
+int embedder_upload(const EmbedWeightsHost &w, int device, int max_len, DeviceEmbedder &e);
+void embedder_free(DeviceEmbedder &e);
+// Embeds sequences [first, first + n) of `src` into out_dev (n x 128 floats on the embedder's device).
+void tokenize_host(const char *flat, const int64_t *off, int64_t n, int T, uint16_t *tokens);
+int launch_embed(DeviceEmbedder &e, const EmbedSource &src, int64_t first, int64_t n, float *out_dev, cudaStream_t stream);
+
 }  // namespace drm

@@ -166,6 +166,45 @@ int drm_search_rerank_reads(drm_index *ix, drm_ref *ref, int mode, const float *
                             const drm_reads *reads, int64_t stride, int64_t k, int64_t k_clusters, float *D, int64_t *I,
                             int32_t *sw_scores, uint64_t *sw_ids, drm_search_stats *stats, double *timing_ms);
 
+/* ------------------------------------------------------------------ embedder (sequence -> 128-d vector) */
+/* Vectorizer::vectorize (src/inference/vectorize.cpp:34-141) on the device: the 3-mer tokeniser
+ * (Preprocessor::preprocess src/inference/preprocess.cpp:20-42, truncation to max_len = 123 tokens, pad id 0 as
+ * prepareBatch src/inference/vectorize.cpp:345-366) and the network of models/finetuned_sgn33-new-a-Apr6.xml
+ * (token embedding -> 2 bidirectional GRU layers, hidden 64 -> [forward | backward] final state of layer 2), in fp32.
+ * Sequences are tokenised as given - pass them with the '<' ... '>' decoration where the reference does
+ * (src/main.cpp:249-257 embeds its decorated query strings; drm_reads holds reads in that form).
+ * Where the reference is undefined (fewer than 2 bytes; a token whose hash lands outside its 96-entry table, which
+ * takes a byte other than ACGTacgt<>) the token is the pad id 0; other bytes hash as hashToken's arithmetic says
+ * (includes/inference/preprocess.hpp:33-52, char2Val = 7).  No CPU fallback: DRM_ECUDA without a device. */
+typedef struct drm_embedder drm_embedder;
+/* Reads an OpenVINO IR pair the way ov::Core::read_model would (src/inference/fast_model.cpp:3-40). */
+int drm_embedder_open_ir(const char *xml_path, const char *bin_path, int device, drm_embedder **out);
+/* Weights by pointer (host, fp16 bit patterns as the IR stores them): emb [vocab][64]; W1, R1 [2][192][64]; B1 [2][256];
+ * W2 [2][192][128]; R2 [2][192][64]; B2 [2][256]; gate order z, r, h; B = [Wb_z+Rb_z, Wb_r+Rb_r, Wb_h, Rb_h]. */
+int drm_embedder_open_raw(const uint16_t *emb, int vocab, const uint16_t *W1, const uint16_t *R1, const uint16_t *B1,
+                          const uint16_t *W2, const uint16_t *R2, const uint16_t *B2, int max_len, int device, drm_embedder **out);
+void drm_embedder_close(drm_embedder *e);
+/* Host-only check of an IR pair (no device needed): info[0] = vocabulary rows, info[1..7] = element counts of
+ * emb, W1, R1, B1, W2, R2, B2; sums (nullable, 7 doubles) = the sum of each tensor's values. */
+int drm_embedder_ir_info(const char *xml_path, const char *bin_path, int64_t *info, double *sums);
+/* Preprocessor::preprocess on the host (the same code the kernel's prologue runs; format-level helper, no device):
+ * tokens = n x max_len vocabulary ids, 0-padded. */
+int drm_tokenize(const char *seq_flat, const int64_t *seq_off, int64_t n, int max_len, uint16_t *tokens);
+/* n byte strings (host; string i = seq_flat[seq_off[i] .. seq_off[i+1])) -> out (host, n x 128 floats). */
+int drm_embed(drm_embedder *e, const char *seq_flat, const int64_t *seq_off, int64_t n, float *out);
+/* Reads [first, first + n) of a drm_reads handle that has a replica on the embedder's device -> out (host, n x 128). */
+int drm_embed_reads(drm_embedder *e, const drm_reads *reads, int64_t first, int64_t n, float *out);
+/* Windows first_id, first_id + id_step, ... (n of them; find_sequence ids, src/utils/post_processor.cpp:47-66) of a
+ * reference with a replica on the embedder's device, each embedded as '<' + window + '>' like the strings
+ * format_fasta builds (src/utils/parse_inputs.cpp:340-343) -> out (host, n x 128).  A window outside the reference
+ * embeds as the empty string. */
+int drm_embed_windows(drm_embedder *e, const drm_ref *ref, uint64_t first_id, uint64_t id_step, int64_t n, float *out);
+/* Device-pointer forms (pointers on the embedder's device, work queued on `stream`): */
+int drm_embed_device(drm_embedder *e, const char *seq_flat_dev, const int64_t *seq_off_dev, int64_t first, int64_t n,
+                     float *out_dev, void *stream);
+int drm_embed_windows_device(drm_embedder *e, const drm_ref *ref, uint64_t first_id, uint64_t id_step, int64_t n,
+                             float *out_dev, void *stream);
+
 /* ------------------------------------------------------------------ sharded-index merge */
 /* D_all/I_all: n_shards x n x k (the all-gathered per-shard results, each row ascending, I already
  * offset to global ids); writes the global top-k per read to D_out/I_out (n x k), ordered by (D, I). */

@@ -18,7 +18,9 @@
 //   preprocess_fastq         src/utils/parse_inputs.cpp:1077-1112 (format_fastq :843-950)
 //   save_results             src/utils/utils.cpp:264-334
 //   save_config/load_config  src/utils/utils.cpp:505-597
+//   Preprocessor::preprocess src/inference/preprocess.cpp:20-42 (3-mer tokeniser of the embedder)
 #include "post_processor.hpp"
+#include "preprocess.hpp"
 #include <cstdint>
 #include <cstdio>
 #include <cstring>
@@ -234,6 +236,22 @@ int64_t ref_load_config_size(const char *config_file, const char *key)
         if (!std::holds_alternative<size_t>(it->second)) return -2;
         return (int64_t)std::get<size_t>(it->second);
     } catch (const std::exception &e) { g_err = e.what(); return -3; }
+}
+
+// tokens: n x max_len uint16, rows padded with 0 like Vectorizer::prepareBatch does (src/inference/vectorize.cpp:345-366).
+// Only call this with sequences of >= 2 bases from {A,C,G,T,a,c,g,t}: anything else indexes past the reference's
+// 96-entry table (src/inference/preprocess.hpp hashToken / preprocess.cpp:28-41).
+int ref_tokenize(const char *flat, const int64_t *off, int64_t n, int max_len, uint16_t *tokens)
+{
+    try {
+        Preprocessor pre;
+        for (int64_t i = 0; i < n; ++i) {
+            const std::string s(flat + off[i], (size_t)(off[i + 1] - off[i]));
+            const std::vector<uint16_t> t = pre.preprocess(s, (unsigned)max_len);
+            for (int j = 0; j < max_len; ++j) tokens[i * max_len + j] = j < (int)t.size() ? t[(size_t)j] : 0;
+        }
+        return 0;
+    } catch (const std::exception &e) { g_err = e.what(); return -1; }
 }
 
 }  // extern "C"

@@ -1,0 +1,122 @@
+"""GPU parity tests for the embedder through the C-ABI: the CUDA path against the committed golden
+vectors (reference tokeniser + torch.nn.GRU on the reference's weights) and against oracle/embed_oracle.py on seeded
+inputs.  Floating point: the network runs in fp32 on fp16-exact weights; outputs lie in (-1, 1) and differ from the
+oracle only by summation order and the exp/tanh implementations - the tolerance is 2e-4 absolute."""
+import numpy as np
+import pytest
+
+import deepreadmapper_b200 as drm
+from oracle import embed_oracle as EO
+
+import embed_util as U
+
+pytestmark = pytest.mark.gpu
+TOL = 2e-4
+
+
+@pytest.fixture(scope="module")
+def gold():
+    return U.load_golden()
+
+
+def _random_seqs(g, n, lo, hi, alphabet=b"ACGT", decorate=0.5):
+    out = []
+    for _ in range(n):
+        s = bytes(g.choice(np.frombuffer(alphabet, np.uint8), int(g.integers(lo, hi + 1))))
+        if g.random() < decorate:
+            s = b"<" + s + b">"
+        out.append(s)
+    return out
+
+
+def test_reference_weights_against_golden(gold):
+    v = drm.Vectorizer(weights=gold["weights"])
+    got = v.vectorize(gold["seqs"])
+    assert got.shape == gold["embeddings"].shape
+    assert float(np.abs(got - gold["embeddings"]).max()) < TOL
+    # every golden tokeniser sequence too, against the oracle
+    want = EO.embed(gold["tok_seqs"], gold["weights"])
+    assert float(np.abs(v.vectorize(gold["tok_seqs"]) - want).max()) < TOL
+    v.close()
+
+
+def test_ragged_and_undefined_sequences_against_oracle():
+    w = EO.random_weights(11)
+    g = np.random.default_rng(12)
+    seqs = [b"", b"A", b"AC", b"<A>", b"NN", b"ACGTNACGT" * 20, b"<ACGNNT>"]
+    seqs += _random_seqs(g, 20, 2, 300) + _random_seqs(g, 18, 100, 160, alphabet=b"ACGTacgtN")
+    assert len(seqs) % 16 != 0  # a partly filled last CTA
+    v = drm.Vectorizer(weights=w)
+    got = v.vectorize(seqs)
+    want = EO.embed(seqs, w)
+    assert float(np.abs(got - want).max()) < TOL
+    assert v.vectorize([]).shape == (0, 128)
+    one = v.vectorize(seqs[9:10])
+    assert float(np.abs(one - want[9:10]).max()) < TOL
+    v.close()
+
+
+def test_more_sequences_than_one_pass():
+    import torch
+    sms = torch.cuda.get_device_properties(0).multi_processor_count
+    n = sms * 16 * 4 + 37  # one full pass of the scratch + a short second one
+    w = EO.random_weights(21)
+    g = np.random.default_rng(22)
+    seqs = _random_seqs(g, n, 100, 152, decorate=1.0)
+    v = drm.Vectorizer(weights=w)
+    got = v.vectorize(seqs)
+    # sequences are independent: check the first and last CTAs of both passes and a random sample in between
+    pick = np.unique(np.concatenate([np.arange(0, 48), np.arange(n - 37 - 48, n), g.integers(0, n, 96)]))
+    want = EO.embed([seqs[i] for i in pick], w)
+    assert float(np.abs(got[pick] - want).max()) < TOL
+    assert np.isfinite(got).all() and float(np.abs(got).max()) <= 1.0
+    v.close()
+
+
+def test_shorter_max_len():
+    w = EO.random_weights(31)
+    g = np.random.default_rng(32)
+    seqs = _random_seqs(g, 33, 2, 40)
+    v = drm.Vectorizer(weights=w, max_len=16)
+    assert float(np.abs(v.vectorize(seqs) - EO.embed(seqs, w, max_len=16)).max()) < TOL
+    v.close()
+
+
+def test_reads_handle_windows_and_ir_file(tmp_path):
+    w = EO.random_weights(41)
+    g = np.random.default_rng(42)
+    v = drm.Vectorizer(weights=w)
+    # FASTQ parsed on the device -> embedded in place (reads are held as '<' + sequence + '>')
+    raw = _random_seqs(g, 40, 30, 150, decorate=0.0)
+    fastq = b"".join(b"@r%d\n%s\n+\n%s\n" % (i, s, b"I" * len(s)) for i, s in enumerate(raw))
+    reads = drm.Reads(fastq)
+    want = EO.embed([b"<" + s + b">" for s in raw], w)
+    assert float(np.abs(v.vectorize_reads(reads) - want).max()) < TOL
+    assert float(np.abs(v.vectorize_reads(reads, first=7, n=12) - want[7:19]).max()) < TOL
+    reads.close()
+    # reference windows by find_sequence id (id / 2 = position, id % 2 = reverse complement), one id past the end
+    genome = bytes(g.choice(np.frombuffer(b"ACGTN", np.uint8), 400, p=[0.245, 0.245, 0.245, 0.245, 0.02]))
+    ref_len = 150
+    ref = drm.Reference(genome=genome, ref_len=ref_len)
+    comp = bytes.maketrans(b"ACGTN", b"TGCAN")
+    n_pos = len(genome) - ref_len + 1
+    ids = [3 + 5 * i for i in range(2 * n_pos // 5 + 1)]
+    strings = []
+    for i in ids:
+        p = i // 2
+        if p + ref_len > len(genome):
+            strings.append(b"")
+            continue
+        win = genome[p:p + ref_len]
+        strings.append(b"<" + (win.translate(comp)[::-1] if i % 2 else win) + b">")
+    assert strings[-1] == b"" and strings[-2] != b""
+    got = v.vectorize_windows(ref, 3, 5, len(ids))
+    assert float(np.abs(got - EO.embed(strings, w)).max()) < TOL
+    ref.close()
+    # the same weights through an IR pair on disk
+    xml = U.write_ir(str(tmp_path / "model"), w)
+    v2 = drm.Vectorizer(model_path=xml)
+    seqs = _random_seqs(g, 20, 100, 152, decorate=1.0)
+    assert np.array_equal(v2.vectorize(seqs), v.vectorize(seqs))
+    v2.close()
+    v.close()
