@@ -8,6 +8,7 @@
 //   post_process_sw_static / post_process_sw_dynamic      includes/utils/post_processor.hpp:79-103
 //   sw_reranker                                           includes/utils/reranker.hpp:19-23
 //   calc_sw_score                                         includes/utils/metrics.hpp:22
+//   Vectorizer                                            includes/inference/vectorize.hpp:14-56, src/inference/vectorize.cpp:4-141
 //   load_config / save_config / save_results / read_file  includes/utils/utils.hpp:53-115
 //   reverse_complement / extract_FASTA_sequence / preprocess_fasta / preprocess_fastq   includes/utils/parse_inputs.hpp
 // Errors are std::runtime_error with the reference's messages; main catches once and prints "Error: <what>".
@@ -24,11 +25,14 @@
 
 struct drm_index;
 struct drm_ref;
+struct drm_embedder;
 
 // includes/utils/config.hpp:6-57 (only the constants the path uses)
 namespace Config {
 namespace Build { constexpr int DIM = 128; constexpr int M_PQ = 8; constexpr int NBITS = 8; constexpr int M = 16; constexpr int EFC = 200;
                   constexpr float SAMPLE_RATE = 0.5f; }
+namespace Inference { constexpr const char MODEL_PATH[] = "models/finetuned_sgn33-new-a-Apr6.xml"; constexpr size_t BATCH_SIZE = 100;
+                      constexpr size_t MAX_LEN = 123; constexpr size_t MODEL_OUT_SIZE = 128; }
 namespace Search { constexpr int EF = 128; constexpr int K = 128; constexpr int K_CLUSTERS = 5; }
 }  // namespace Config
 
@@ -63,6 +67,25 @@ int64_t stage_device_inputs(faiss::IndexHNSWPQ *index, const std::string &fastq_
 void write_sam_aligned(const std::string &sam_file, const std::string &ref_name, const std::string &genome, size_t ref_len,
                        const std::vector<std::string> &query_seqs, const std::vector<std::string> &query_ids, const std::vector<int> &sw_scores,
                        const std::vector<size_t> &sw_ids, size_t k, size_t n_out);
+
+// The embedder: tokeniser + network on the GPU (csrc/embed_kernel.cu).  model_path = the OpenVINO IR .xml the reference
+// loads (the .bin beside it); batch_size is accepted for compatibility (the device batches by itself).
+class Vectorizer {
+public:
+    Vectorizer(const std::string &model_path = Config::Inference::MODEL_PATH, size_t batch_size = Config::Inference::BATCH_SIZE,
+               size_t max_len = Config::Inference::MAX_LEN, size_t model_out_size = Config::Inference::MODEL_OUT_SIZE);
+    ~Vectorizer();
+    Vectorizer(const Vectorizer &) = delete;
+    Vectorizer &operator=(const Vectorizer &) = delete;
+    std::vector<std::vector<float>> vectorize(const std::vector<std::string> &input, bool verbose = false);
+    // flat form for large batches: out = input.size() x 128 row-major
+    void vectorize_flat(const std::vector<std::string> &input, std::vector<float> &out);
+private:
+    drm_embedder *handle_ = nullptr;
+    size_t model_out_size_;
+};
+// DRM_MODEL if set, else Config::Inference::MODEL_PATH (relative to the working directory, like the reference).
+std::string embedder_model_path();
 
 int calc_sw_score(const std::string &seq1, const std::string &seq2);
 

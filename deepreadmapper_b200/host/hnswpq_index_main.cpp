@@ -4,8 +4,9 @@
 //
 // writes <prefix>/<prefix>.index (FAISS "IHNp" layout) and <prefix>/config.txt with the reference's keys
 // (index_type, stride, ref_len, n_vects, dim, M_hnsw, EFC, M_pq, nbits, index_file; src/hnswpq/index.cpp:289-304).
-// The embedder is outside this build, so a sequence reference needs its embeddings beside it as `<ref file>.npy`;
-// a .npy reference is used as-is, like the reference does (:236-265).  Training set = evenly strided
+// A sequence reference is cut into windows by read_file(ref, ref_len, stride) and embedded on the GPU like the reference
+// does with OpenVINO (:266-282; model = $DRM_MODEL or models/finetuned_sgn33-new-a-Apr6.xml), unless its embeddings sit
+// beside it as `<ref file>.npy`; a .npy reference is used as-is (:236-265).  Training set = evenly strided
 // Config::Build::SAMPLE_RATE sample (create_training_set, :57-84,99).
 #include <cstdlib>
 #include <algorithm>
@@ -39,23 +40,36 @@ int main(int argc, char *argv[])
         const int EFC = argc >= 9 ? std::stoi(argv[8]) : Config::Build::EFC;
 
         std::string emb_file = ref_file;
-        if (std::filesystem::path(ref_file).extension().string() != ".npy") {
-            emb_file = ref_file + ".npy";
-            if (!std::filesystem::exists(emb_file))
-                throw std::runtime_error("Embeddings not found: " + emb_file + " (the embedder is outside this build; run the reference's `inference` tool)");
+        if (std::filesystem::path(ref_file).extension().string() != ".npy") emb_file = ref_file + ".npy";
+        npy::Array arr;
+        std::vector<float> emb_store;
+        size_t n = 0, d = 0;
+        const float *x = nullptr;
+        if (std::filesystem::exists(emb_file)) {
+            std::cout << "[BUILD INDEX] Loading embeddings directly from .npy file: " << emb_file << std::endl;
+            arr = npy::load(emb_file);
+            if (arr.shape.size() != 2) {
+                std::cerr << "Error: Expected 2D array in .npy file" << std::endl;
+                return 1;
+            }
+            if (arr.kind != 'f' || arr.word_size != 4 || arr.fortran_order) throw std::runtime_error("Error: embeddings must be C-order float32 ('<f4')");
+            n = arr.shape[0]; d = arr.shape[1];
+            x = reinterpret_cast<const float *>(arr.data.data());
+            std::cout << "[BUILD INDEX] Loaded " << n << " embeddings of dimension " << d << std::endl;
+        } else {
+            const std::string model_path = embedder_model_path();
+            if (emb_file == ref_file || !std::filesystem::exists(model_path))
+                throw std::runtime_error("Embeddings not found: " + emb_file + ", and no embedder model at " + model_path + " (set DRM_MODEL=<model.xml>)");
+            std::cout << "[BUILD INDEX] Reading sequences from file: " << ref_file << std::endl;
+            std::vector<std::string> ref_sequences = read_file(ref_file, ref_len, stride).first;
+            if (ref_sequences.empty()) throw std::runtime_error("No sequences found in file: " + ref_file);
+            std::cout << "[BUILD INDEX] Vectorizing " << ref_sequences.size() << " sequences on the GPU..." << std::endl;
+            Vectorizer vectorizer(model_path);
+            vectorizer.vectorize_flat(ref_sequences, emb_store);
+            n = ref_sequences.size(); d = Config::Inference::MODEL_OUT_SIZE;
+            x = emb_store.data();
         }
-        std::cout << "[BUILD INDEX] Loading embeddings directly from .npy file: " << emb_file << std::endl;
-        npy::Array arr = npy::load(emb_file);
-        if (arr.shape.size() != 2) {
-            std::cerr << "Error: Expected 2D array in .npy file" << std::endl;
-            return 1;
-        }
-        if (arr.kind != 'f' || arr.word_size != 4 || arr.fortran_order) throw std::runtime_error("Error: embeddings must be C-order float32 ('<f4')");
-        const size_t n = arr.shape[0], d = arr.shape[1];
-        std::cout << "[BUILD INDEX] Loaded " << n << " embeddings of dimension " << d << std::endl;
         if (n == 0) throw std::runtime_error("No sequences found in file: " + ref_file);
-        const float *x = reinterpret_cast<const float *>(arr.data.data());
-
         std::cout << "[BUILD INDEX] Saving index config to folder: " << index_prefix << std::endl;
         std::unordered_map<std::string, ConfigValue> config = {
             {"index_type", std::string("HNSWPQ")}, {"stride", stride}, {"ref_len", ref_len}, {"n_vects", n}, {"dim", d},

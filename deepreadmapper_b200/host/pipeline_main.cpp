@@ -6,8 +6,10 @@
 // Same positional arguments, defaults, file layout (<prefix>/<basename>.index, <prefix>/config.txt), error messages and
 // outputs (<output_dir>/indices.npy '<u8', distances.npy '<f4' = the RAW search output, src/main.cpp:371-384).
 // Differences, all additive:
-//   * the embedder (OpenVINO BiLSTM) is outside this build: a sequence query file needs its embeddings as
-//     `<query file>.npy` (or env DRM_QUERY_EMB=<file.npy>); a bare .npy query = the reference's search-only behaviour;
+//   * a sequence query file is embedded on the GPU (Vectorizer over csrc/embed_kernel.cu; model = $DRM_MODEL or the
+//     reference's models/finetuned_sgn33-new-a-Apr6.xml relative to the working directory) unless its embeddings are
+//     supplied as `<query file>.npy` (or env DRM_QUERY_EMB=<file.npy>); a bare .npy query = the reference's search-only
+//     behaviour;
 //   * the rerank is the Smith-Waterman variant the reference has implemented but commented out (src/main.cpp:333-341);
 //     its result goes to NEW files sw_scores.npy ('<i4', n x K) and sw_indices.npy ('<u8', n x K); DRM_RERANK=none skips it;
 //   * both modes rerank from the cleaned genome on the device: use_dynamic=0 applies the static bound rule (number of
@@ -87,14 +89,37 @@ int main(int argc, char *argv[])
             }
             const char *env = getenv("DRM_QUERY_EMB");
             emb_file = env ? env : query_input_file + ".npy";
-            if (!std::filesystem::exists(emb_file))
-                throw std::runtime_error("Embeddings not found: " + emb_file + " (the embedder is outside this build; run the reference's `inference` tool)");
         }
-        npy::Array arr = npy::load(emb_file);
-        if (arr.shape.size() != 2) throw std::runtime_error("Error: Expected 2D array in .npy file");
-        if (arr.kind != 'f' || arr.word_size != 4 || arr.fortran_order) throw std::runtime_error("Error: embeddings must be C-order float32 ('<f4')");
-        const size_t num_queries = arr.shape[0], dim = arr.shape[1];
-        std::cout << "[MAIN] Loaded " << num_queries << " embeddings of dimension " << dim << std::endl;
+        npy::Array arr;
+        std::vector<float> emb_store;
+        const float *emb = nullptr;
+        size_t num_queries = 0, dim = 0;
+        if (is_npy || std::filesystem::exists(emb_file)) {
+            arr = npy::load(emb_file);
+            if (arr.shape.size() != 2) throw std::runtime_error("Error: Expected 2D array in .npy file");
+            if (arr.kind != 'f' || arr.word_size != 4 || arr.fortran_order) throw std::runtime_error("Error: embeddings must be C-order float32 ('<f4')");
+            num_queries = arr.shape[0]; dim = arr.shape[1];
+            emb = reinterpret_cast<const float *>(arr.data.data());
+            std::cout << "[MAIN] Loaded " << num_queries << " embeddings of dimension " << dim << std::endl;
+        } else {
+            // the reference's INFERENCE STEP (src/main.cpp:246-268), on the GPU
+            const std::string model_path = embedder_model_path();
+            if (!std::filesystem::exists(model_path))
+                throw std::runtime_error("Embeddings not found: " + emb_file + ", and no embedder model at " + model_path + " (set DRM_MODEL=<model.xml>)");
+            std::cout << "[MAIN] INFERENCE STEP" << std::endl;
+            const auto ti = Clock::now();
+            if (query_sequences.empty()) std::tie(query_sequences, query_ids) = read_file(query_input_file);
+            if (query_sequences.empty()) {
+                std::cerr << "No query_sequences found in input file!" << std::endl;
+                return 1;
+            }
+            Vectorizer vectorizer(model_path);
+            vectorizer.vectorize_flat(query_sequences, emb_store);
+            num_queries = query_sequences.size(); dim = Config::Inference::MODEL_OUT_SIZE;
+            emb = emb_store.data();
+            std::cout << "[MAIN] Inference completed" << std::endl;
+            std::cout << "[MAIN] Inference time: " << ms_since(ti) << " ms" << std::endl << std::endl;
+        }
         if (!is_npy && !device_inputs && query_sequences.size() != num_queries) throw std::runtime_error("Error: number of embeddings differs from the number of query sequences");
         std::string ref_genome;
         if (device_inputs) {
@@ -124,11 +149,11 @@ int main(int argc, char *argv[])
         std::vector<int> sw_scores;
         std::vector<size_t> sw_ids;
         if (device_inputs) {
-            stage_device_inputs(alg_hnsw, query_input_file, ref_seqs_file, reinterpret_cast<const float *>(arr.data.data()), (int64_t)num_queries,
+            stage_device_inputs(alg_hnsw, query_input_file, ref_seqs_file, emb, (int64_t)num_queries,
                                 (int)dim, k_clusters, ef, use_dynamic ? 1 : 0, ref_len, stride, (size_t)k, (size_t)k_clusters, I, D, sw_scores, sw_ids);
             std::cout << "[MAIN] HNSW search + SW rerank time (one call, device-side inputs): " << ms_since(t0) << " ms" << std::endl << std::endl;
         } else {
-            faiss_search_flat(alg_hnsw, reinterpret_cast<const float *>(arr.data.data()), (int64_t)num_queries, (int)dim, k_clusters, ef, I, D);
+            faiss_search_flat(alg_hnsw, emb, (int64_t)num_queries, (int)dim, k_clusters, ef, I, D);
             std::cout << "[MAIN] HNSW search time: " << ms_since(t0) << " ms" << std::endl << std::endl;
         }
         delete alg_hnsw;

@@ -398,3 +398,47 @@ void write_sam_aligned(const std::string &sam_file, const std::string &ref_name,
     }
     fclose(f);
 }
+
+// ---------------------------------------------------------------------------------------------------------------------
+// Vectorizer (src/inference/vectorize.cpp:4-141) over drm_embedder_open_ir / drm_embed
+Vectorizer::Vectorizer(const std::string &model_path, size_t, size_t max_len, size_t model_out_size) : model_out_size_(model_out_size)
+{
+    if (max_len != Config::Inference::MAX_LEN || model_out_size != Config::Inference::MODEL_OUT_SIZE)
+        throw std::runtime_error("Vectorizer: the model takes 123 tokens and gives 128 values");
+    std::string bin = model_path;
+    const size_t dot = bin.rfind('.');
+    if (dot != std::string::npos) bin.erase(dot);
+    bin += ".bin";
+    if (drm_embedder_open_ir(model_path.c_str(), bin.c_str(), 0, &handle_) != DRM_OK) throw std::runtime_error(drm_last_error());
+}
+
+Vectorizer::~Vectorizer() { if (handle_) drm_embedder_close(handle_); }
+
+void Vectorizer::vectorize_flat(const std::vector<std::string> &input, std::vector<float> &out)
+{
+    std::vector<int64_t> off(input.size() + 1, 0);
+    for (size_t i = 0; i < input.size(); ++i) off[i + 1] = off[i] + (int64_t)input[i].size();
+    std::string flat;
+    flat.reserve((size_t)off.back());
+    for (const std::string &s : input) flat += s;
+    out.assign(input.size() * model_out_size_, 0.0f);
+    if (input.empty()) return;
+    if (drm_embed(handle_, flat.data(), off.data(), (int64_t)input.size(), out.data()) != DRM_OK) throw std::runtime_error(drm_last_error());
+}
+
+std::vector<std::vector<float>> Vectorizer::vectorize(const std::vector<std::string> &input, bool verbose)
+{
+    if (verbose) std::cout << "[Inference] Vectorizing " << input.size() << " sequences..." << std::endl;
+    std::vector<float> flat;
+    vectorize_flat(input, flat);
+    std::vector<std::vector<float>> out(input.size());
+    for (size_t i = 0; i < input.size(); ++i) out[i].assign(flat.begin() + (long)(i * model_out_size_), flat.begin() + (long)((i + 1) * model_out_size_));
+    if (verbose) std::cout << "[Inference] Vectorization completed successfully!" << std::endl;
+    return out;
+}
+
+std::string embedder_model_path()
+{
+    const char *env = std::getenv("DRM_MODEL");
+    return env ? std::string(env) : std::string(Config::Inference::MODEL_PATH);
+}

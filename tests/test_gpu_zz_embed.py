@@ -120,3 +120,66 @@ def test_reads_handle_windows_and_ir_file(tmp_path):
     assert np.array_equal(v2.vectorize(seqs), v.vectorize(seqs))
     v2.close()
     v.close()
+
+
+def test_cli_from_sequence_files_only(tmp_path):
+    """hnswpq_index on a FASTA and pipeline on a FASTQ with no .npy beside either: both embed on the GPU through the
+    model named by DRM_MODEL, like the reference's binaries do through OpenVINO (src/hnswpq/index.cpp:266-282,
+    src/main.cpp:246-268)."""
+    import os
+    import subprocess
+    from oracle import bindings as ob
+    root = U.ROOT
+    w = EO.random_weights(51)
+    xml = U.write_ir(str(tmp_path / "model"), w)
+    g = np.random.default_rng(52)
+    genome = bytes(g.choice(np.frombuffer(b"ACGT", np.uint8), 3000))
+    ref_len = 150
+    with open(tmp_path / "ref.fna", "wb") as f:
+        f.write(b"> synthetic\n" + b"\n".join(genome[i:i + 70] for i in range(0, len(genome), 70)) + b"\n")
+    comp = bytes.maketrans(b"ACGT", b"TGCA")
+    reads = []
+    for i in range(48):
+        p = int(g.integers(0, len(genome) - ref_len))
+        r = bytearray(genome[p:p + ref_len])
+        for j in g.integers(0, ref_len, 3):
+            r[j] = b"ACGT"[int(g.integers(0, 4))]
+        r = bytes(r)
+        reads.append(r.translate(comp)[::-1] if i % 2 else r)
+    with open(tmp_path / "reads.fastq", "wb") as f:
+        for i, r in enumerate(reads):
+            f.write(b"@r%d\n%s\n+\n%s\n" % (i, r, b"I" * len(r)))
+    env = dict(os.environ, DRM_MODEL=xml)
+    r = subprocess.run([os.path.join(root, "build/bin/hnswpq_index"), "ref.fna", "idx1", "150", "1", "8", "8", "16", "64"], cwd=tmp_path,
+                       capture_output=True, text=True, env=env)
+    assert r.returncode == 0, r.stderr + r.stdout
+    assert "Vectorizing" in r.stdout
+    n_pos = len(genome) - ref_len + 1
+    oix = ob.OracleIndex(str(tmp_path / "idx1" / "idx1.index"))
+    assert oix.ntotal == 2 * n_pos and oix.d == 128
+    # the vectors behind the codes are the windows in the reference's order (forward, reverse complement per position)
+    v = drm.Vectorizer(model_path=xml)
+    wins = []
+    for p in range(n_pos):
+        win = genome[p:p + ref_len]
+        wins += [b"<" + win + b">", b"<" + win.translate(comp)[::-1] + b">"]
+    E = v.vectorize(wins)
+    cent, codes, _ = oix.arrays()
+    dec = np.concatenate([cent[m][codes[:, m]] for m in range(cent.shape[0])], axis=1)
+    right = float(((dec - E) ** 2).sum(1).mean())
+    wrong = float(((dec - np.roll(E, 1, axis=0)) ** 2).sum(1).mean())
+    assert right < 0.5 * wrong, (right, wrong)
+    # pipeline without reads.fastq.npy: INFERENCE STEP on the GPU, then search + rerank; raw search output = the oracle's
+    out = tmp_path / "out"
+    r = subprocess.run([os.path.join(root, "build/bin/pipeline"), "idx1", "reads.fastq", "ref.fna", "64", "16", "16", str(out), "1"], cwd=tmp_path,
+                       capture_output=True, text=True, env=env)
+    assert r.returncode == 0, r.stderr + r.stdout
+    assert "INFERENCE STEP" in r.stdout
+    Q = v.vectorize([b"<" + x + b">" for x in reads])
+    v.close()
+    I, D = np.load(out / "indices.npy"), np.load(out / "distances.npy")
+    D0, I0, _ = oix.search(Q, 16, 64, tie_rule=1)
+    assert np.array_equal(I.astype(np.int64), I0) and np.array_equal(D.view(np.uint32), D0.view(np.uint32))
+    S, SI = np.load(out / "sw_scores.npy"), np.load(out / "sw_indices.npy")
+    rc, s0, i0, _ = ob.post_process_sw(1, I0, genome, len(genome), 150, ["<" + x.decode() + ">" for x in reads], 1, 16, 16)
+    assert rc == 0 and np.array_equal(S, s0) and np.array_equal(SI, i0)
