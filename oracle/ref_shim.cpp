@@ -18,6 +18,9 @@
 //   preprocess_fastq         src/utils/parse_inputs.cpp:1077-1112 (format_fastq :843-950)
 //   save_results             src/utils/utils.cpp:264-334
 //   save_config/load_config  src/utils/utils.cpp:505-597
+//   post_process_l2_static   src/utils/post_processor.cpp:1023-1162 (batch_reranker src/utils/reranker.cpp:98-196)
+//   post_process_l2_dynamic  src/utils/post_processor.cpp:552-748
+//   calc_l2_dist             src/utils/metrics.cpp:47-61
 //   Preprocessor::preprocess src/inference/preprocess.cpp:20-42 (3-mer tokeniser of the embedder)
 #include "post_processor.hpp"
 #include "preprocess.hpp"
@@ -29,10 +32,22 @@
 #include <unistd.h>
 #include <fcntl.h>
 
-// The L2 rerank variants reference Vectorizer::vectorize; they are never called from here.
-std::vector<std::vector<float>> Vectorizer::vectorize(const std::vector<std::string> &, bool)
+// The L2 rerank variants call Vectorizer::vectorize.  OpenVINO is absent, so the embedder behind them is a callback the
+// test installs (oracle/embed_oracle.py): everything else those functions do - flattening, find_sequences with
+// de-duplication, query boundaries, batch_reranker, calc_l2_dist, partial_sort - is the reference's own code.
+extern "C" typedef void (*ref_vectorize_cb)(const char *flat, const int64_t *off, int64_t n, float *out);
+static ref_vectorize_cb g_vectorize = nullptr;
+std::vector<std::vector<float>> Vectorizer::vectorize(const std::vector<std::string> &input, bool)
 {
-    throw std::runtime_error("Vectorizer is not available in the oracle build");
+    if (!g_vectorize) throw std::runtime_error("Vectorizer is not available in the oracle build (no callback installed)");
+    std::string flat;
+    std::vector<int64_t> off(input.size() + 1, 0);
+    for (size_t i = 0; i < input.size(); ++i) { flat += input[i]; off[i + 1] = (int64_t)flat.size(); }
+    std::vector<float> out(input.size() * 128);
+    g_vectorize(flat.data(), off.data(), (int64_t)input.size(), out.data());
+    std::vector<std::vector<float>> res(input.size());
+    for (size_t i = 0; i < input.size(); ++i) res[i].assign(out.begin() + (long)(i * 128), out.begin() + (long)((i + 1) * 128));
+    return res;
 }
 
 namespace {
@@ -250,6 +265,52 @@ int ref_tokenize(const char *flat, const int64_t *off, int64_t n, int max_len, u
             const std::vector<uint16_t> t = pre.preprocess(s, (unsigned)max_len);
             for (int j = 0; j < max_len; ++j) tokens[i * max_len + j] = j < (int)t.size() ? t[(size_t)j] : 0;
         }
+        return 0;
+    } catch (const std::exception &e) { g_err = e.what(); return -1; }
+}
+
+void ref_set_vectorizer(ref_vectorize_cb cb) { g_vectorize = cb; }
+
+float ref_calc_l2_dist(const float *a, const float *b, int64_t d)
+{
+    return calc_l2_dist(std::vector<float>(a, a + d), std::vector<float>(b, b + d));
+}
+
+// The reference's L2 rerank stage with the installed embedder callback.  mode 0 = static (ref_flat = n_ref strings of
+// ref_w bytes each, as read_file returns them), mode 1 = dynamic (ref_flat = genome of n_ref bytes).  q_emb: n x 128.
+// Outputs: *out_count values in out_scores / out_ids (n x k when every query has enough candidates).
+int ref_post_process_l2(int mode, const int64_t *neighbors, const float *distances, int64_t n, int64_t k_in,
+                        const char *ref_flat, int64_t n_ref, int64_t ref_w, int64_t ref_len,
+                        const char *q_flat, const int64_t *q_off, const float *q_emb,
+                        int64_t stride, int64_t k, int64_t k_clusters,
+                        float *out_scores, uint64_t *out_ids, int64_t *out_count)
+{
+    try {
+        Quiet quiet;
+        std::vector<std::vector<long int>> nb((size_t)n);
+        std::vector<std::vector<float>> dist((size_t)n), qe((size_t)n);
+        for (int64_t i = 0; i < n; ++i) {
+            nb[(size_t)i].assign(neighbors + i * k_in, neighbors + (i + 1) * k_in);
+            dist[(size_t)i].assign(distances + i * k_in, distances + (i + 1) * k_in);
+            qe[(size_t)i].assign(q_emb + i * 128, q_emb + (i + 1) * 128);
+        }
+        auto queries = unflatten(q_flat, q_off, n);
+        // the functions only pass the Vectorizer through to Vectorizer::vectorize above, which does not touch `this`
+        alignas(Vectorizer) static unsigned char storage[sizeof(Vectorizer)];
+        Vectorizer &vec = *reinterpret_cast<Vectorizer *>(storage);
+        std::vector<std::string> seqs; std::vector<float> scores; std::vector<size_t> ids;
+        if (mode == 0) {
+            std::vector<std::string> ref((size_t)n_ref);
+            for (int64_t i = 0; i < n_ref; ++i) ref[(size_t)i].assign(ref_flat + i * ref_w, (size_t)ref_w);
+            std::tie(seqs, scores, ids) = post_process_l2_static<long int>(nb, dist, ref, queries, (size_t)ref_len, (size_t)stride,
+                                                                          (size_t)k, qe, vec, (size_t)k_clusters);
+        } else {
+            std::string genome(ref_flat, (size_t)n_ref);
+            std::tie(seqs, scores, ids) = post_process_l2_dynamic<long int>(nb, dist, genome, queries, (size_t)ref_len, (size_t)stride,
+                                                                           (size_t)k, qe, vec, (size_t)k_clusters);
+        }
+        *out_count = (int64_t)scores.size();
+        for (size_t i = 0; i < scores.size(); ++i) { out_scores[i] = scores[i]; out_ids[i] = ids[i]; }
         return 0;
     } catch (const std::exception &e) { g_err = e.what(); return -1; }
 }
