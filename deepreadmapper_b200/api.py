@@ -37,7 +37,7 @@ EXPORTS = ["drm_last_error", "drm_device_count", "drm_version", "drm_index_open"
            "drm_reads_open_fastq", "drm_reads_close", "drm_reads_info", "drm_reads_copy_out", "drm_reads_device",
            "drm_search_rerank_reads", "drm_sw_align", "drm_embedder_open_ir", "drm_embedder_open_raw", "drm_embedder_close",
            "drm_embedder_ir_info", "drm_tokenize", "drm_embed", "drm_embed_reads", "drm_embed_windows", "drm_embed_device",
-           "drm_embed_windows_device"]
+           "drm_embed_windows_device", "drm_l2_rerank", "drm_l2_plan_host", "drm_l2_select_host"]
 
 
 def lib_path() -> str:
@@ -96,6 +96,9 @@ def lib():
         L.drm_embed_windows.argtypes = [vp, vp, C.c_uint64, C.c_uint64, i64, vp]
         L.drm_embed_device.argtypes = [vp, vp, vp, i64, i64, vp, vp]
         L.drm_embed_windows_device.argtypes = [vp, vp, C.c_uint64, C.c_uint64, i64, vp, vp]
+        L.drm_l2_rerank.argtypes = [vp, vp, i32, vp, vp, i64, i64, vp, i64, i64, i64, vp, vp, C.POINTER(i64)]
+        L.drm_l2_plan_host.argtypes = [i32, vp, i64, i64, i64, i64, i64, C.c_uint64, vp, vp, vp, vp]
+        L.drm_l2_select_host.argtypes = [vp, i64, i64, vp]
         _lib = L
     return _lib
 
@@ -500,3 +503,52 @@ class Vectorizer:
 
     def vectorize_windows_device(self, ref: "Reference", first_id, id_step, n, out_ptr, stream=0):
         _check(lib().drm_embed_windows_device(self._h, ref._h, first_id, id_step, n, out_ptr, stream))
+
+
+# ---- L2 rerank stage (the reference's post_process_l2_* variants) -----------------------------------------------------
+def l2_plan_host(mode, neighbors, stride, k, k_clusters, bound):
+    """The candidate bookkeeping of post_process_l2_static (mode 0) / _dynamic (mode 1) on the host:
+    dict(unique, map, starts, k_out, passthrough, take)."""
+    nb = np.ascontiguousarray(neighbors, dtype=np.int64)
+    n, k_in = nb.shape
+    info = np.zeros(5, dtype=np.int64)
+    _check(lib().drm_l2_plan_host(mode, nb.ctypes.data, n, k_in, stride, k, k_clusters, bound, info.ctypes.data, None, None, None))
+    unique = np.zeros(int(info[0]), dtype=np.uint64)
+    mp = np.zeros(int(info[1]), dtype=np.uint32)
+    starts = np.zeros(n + 1, dtype=np.int64)
+    if not info[3]:
+        _check(lib().drm_l2_plan_host(mode, nb.ctypes.data, n, k_in, stride, k, k_clusters, bound, info.ctypes.data,
+                                      unique.ctypes.data, mp.ctypes.data, starts.ctypes.data))
+    return dict(unique=unique, map=mp, starts=starts, k_out=int(info[2]), passthrough=bool(info[3]), take=int(info[4]))
+
+
+def l2_select_host(dist, k):
+    """std::partial_sort(idx, idx + k, idx + n, dist[a] < dist[b]) as the kernel runs it: the first k indices."""
+    d = np.ascontiguousarray(dist, dtype=np.float32)
+    idx = np.zeros(len(d), dtype=np.int64)
+    _check(lib().drm_l2_select_host(d.ctypes.data, len(d), k, idx.ctypes.data))
+    return idx[:k]
+
+
+def _post_process_l2(mode, vectorizer, ref, neighbors, distances, query_embeddings, stride, k, k_clusters):
+    nb = np.ascontiguousarray(neighbors, dtype=np.int64)
+    ds = np.ascontiguousarray(distances, dtype=np.float32)
+    qe = np.ascontiguousarray(query_embeddings, dtype=np.float32)
+    n, k_in = nb.shape
+    cap = n * max(k, k_clusters, 1)
+    scores = np.zeros(cap, dtype=np.float32)
+    ids = np.zeros(cap, dtype=np.uint64)
+    cnt = C.c_int64(0)
+    _check(lib().drm_l2_rerank(vectorizer._h, ref._h, mode, nb.ctypes.data, ds.ctypes.data, n, k_in, qe.ctypes.data, stride, k, k_clusters,
+                               scores.ctypes.data, ids.ctypes.data, C.byref(cnt)))
+    return scores[:cnt.value].copy(), ids[:cnt.value].copy()
+
+
+def post_process_l2_dynamic(neighbors, distances, ref: "Reference", query_embeddings, vectorizer: "Vectorizer", stride, k, k_clusters=5):
+    """post_process_l2_dynamic (src/utils/post_processor.cpp:552-748): (scores, dense ids), flat."""
+    return _post_process_l2(1, vectorizer, ref, neighbors, distances, query_embeddings, stride, k, k_clusters)
+
+
+def post_process_l2_static(neighbors, distances, ref: "Reference", query_embeddings, vectorizer: "Vectorizer", stride, k, k_clusters=5):
+    """post_process_l2_static (src/utils/post_processor.cpp:1023-1162): (scores, ids), k_clusters per query, flat."""
+    return _post_process_l2(0, vectorizer, ref, neighbors, distances, query_embeddings, stride, k, k_clusters)

@@ -891,4 +891,93 @@ int drm_embed_windows_device(drm_embedder *e, const drm_ref *ref, uint64_t first
     return launch_embed(e->dev, src, 0, n, out_dev, static_cast<cudaStream_t>(stream));
 }
 
+/* ------------------------------------------------------------------ L2 rerank stage */
+int drm_l2_plan_host(int mode, const int64_t *neighbors, int64_t n, int64_t k_in, int64_t stride, int64_t k, int64_t k_clusters,
+                     uint64_t bound, int64_t *info, uint64_t *unique, uint32_t *map, int64_t *starts)
+{
+    if (!neighbors || !info) return fail(DRM_EINVAL, "null argument");
+    L2Plan plan;
+    const int rc = l2_plan(mode, neighbors, n, k_in, stride, k, k_clusters, bound, plan);
+    if (rc != DRM_OK) return rc;
+    info[0] = (int64_t)plan.unique.size(); info[1] = (int64_t)plan.map.size(); info[2] = plan.k_out;
+    info[3] = plan.passthrough ? 1 : 0; info[4] = plan.take;
+    if (unique) std::copy(plan.unique.begin(), plan.unique.end(), unique);
+    if (map) std::copy(plan.map.begin(), plan.map.end(), map);
+    if (starts) std::copy(plan.starts.begin(), plan.starts.end(), starts);
+    return DRM_OK;
+}
+
+int drm_l2_select_host(const float *dist, int64_t n, int64_t k, int64_t *idx)
+{
+    if (!dist || !idx || n < 0 || k < 0) return fail(DRM_EINVAL, "bad arguments to drm_l2_select_host");
+    l2_select_host(dist, n, k, idx);
+    return DRM_OK;
+}
+
+int drm_l2_rerank(drm_embedder *e, drm_ref *ref, int mode, const int64_t *neighbors, const float *distances, int64_t n, int64_t k_in,
+                  const float *q_emb, int64_t stride, int64_t k, int64_t k_clusters, float *out_scores, uint64_t *out_ids,
+                  int64_t *out_count)
+{
+    if (!e || !ref) return fail(DRM_EINVAL, "null handle");
+    if (!out_count) return fail(DRM_EINVAL, "null count output");
+    *out_count = 0;
+    if (n <= 0) return DRM_OK;
+    if (!neighbors || !distances || !q_emb || !out_scores || !out_ids || (mode != 0 && mode != 1)) return fail(DRM_EINVAL, "bad arguments to drm_l2_rerank");
+    const DeviceRef *dr = ref_on_device(ref, e->dev.device);
+    if (!dr) return fail(DRM_EINVAL, "the reference has no replica on the embedder's device");
+    if (mode == 1 && dr->form != 0) return fail(DRM_EINVAL, "dynamic mode needs a genome reference (drm_ref_open_genome)");
+    // bound: dynamic = genome length in bases; static = number of ref_seqs (rows of the window table, or the dense windows of the genome)
+    uint64_t bound;
+    if (mode == 1 || dr->form == 1) bound = (uint64_t)dr->len;
+    else bound = dr->len >= dr->ref_len ? 2ull * (uint64_t)(dr->len - dr->ref_len + 1) : 0;
+    L2Plan plan;
+    int rc = l2_plan(mode, neighbors, n, k_in, stride, k, k_clusters, bound, plan);
+    if (rc != DRM_OK) return rc;
+    if (plan.passthrough) {
+        for (int64_t q = 0; q < n; ++q)
+            for (int64_t j = 0; j < plan.take; ++j) {
+                out_scores[*out_count] = distances[q * k_in + j];
+                out_ids[*out_count] = (uint64_t)neighbors[q * k_in + j];
+                ++*out_count;
+            }
+        return DRM_OK;
+    }
+    const int64_t U = (int64_t)plan.unique.size(), F = (int64_t)plan.map.size(), ko = plan.k_out;
+    if (ko < 1) return fail(DRM_EINVAL, "k must be >= 1");
+    DRM_CUDA_TRY(cudaSetDevice(e->dev.device));
+    DevBuf d_ids, d_map, d_starts, d_q, d_emb, d_dist, d_idx, d_od, d_or, d_cnt;
+    if ((rc = d_ids.alloc((size_t)U * 8)) || (rc = d_map.alloc((size_t)F * 4)) || (rc = d_starts.alloc((size_t)(n + 1) * 8)) ||
+        (rc = d_q.alloc((size_t)n * 128 * 4)) || (rc = d_emb.alloc((size_t)U * 128 * 4)) || (rc = d_dist.alloc((size_t)F * 4)) ||
+        (rc = d_idx.alloc((size_t)F * 8)) || (rc = d_od.alloc((size_t)n * ko * 4)) || (rc = d_or.alloc((size_t)n * ko * 4)) ||
+        (rc = d_cnt.alloc((size_t)n * 8))) return rc;
+    if (U) DRM_CUDA_TRY(cudaMemcpy(d_ids.p, plan.unique.data(), (size_t)U * 8, cudaMemcpyHostToDevice));
+    if (F) DRM_CUDA_TRY(cudaMemcpy(d_map.p, plan.map.data(), (size_t)F * 4, cudaMemcpyHostToDevice));
+    DRM_CUDA_TRY(cudaMemcpy(d_starts.p, plan.starts.data(), (size_t)(n + 1) * 8, cudaMemcpyHostToDevice));
+    DRM_CUDA_TRY(cudaMemcpy(d_q.p, q_emb, (size_t)n * 128 * 4, cudaMemcpyHostToDevice));
+    EmbedSource src;
+    src.mode = 1; src.cls = dr->data; src.form = dr->form; src.ref_n = dr->len; src.ref_len = dr->ref_len;
+    src.ids = d_ids.as<unsigned long long>();
+    src.decorate = mode == 0 ? 1 : 0;  // ref_seqs hold '<' window '>' strings; find_sequence returns the bare window
+    if ((rc = launch_embed(e->dev, src, 0, U, d_emb.as<float>(), 0)) != DRM_OK) return rc;
+    if ((rc = launch_l2_rerank(d_emb.as<float>(), d_map.as<uint32_t>(), d_starts.as<int64_t>(), d_q.as<float>(), n, (int)ko, d_dist.as<float>(),
+                               d_idx.as<int64_t>(), d_od.as<float>(), d_or.as<uint32_t>(), d_cnt.as<int64_t>(), 0)) != DRM_OK) return rc;
+    std::vector<float> od((size_t)(n * ko));
+    std::vector<uint32_t> orow((size_t)(n * ko));
+    std::vector<int64_t> cnt((size_t)n);
+    DRM_CUDA_TRY(cudaMemcpy(od.data(), d_od.p, od.size() * 4, cudaMemcpyDeviceToHost));
+    DRM_CUDA_TRY(cudaMemcpy(orow.data(), d_or.p, orow.size() * 4, cudaMemcpyDeviceToHost));
+    DRM_CUDA_TRY(cudaMemcpy(cnt.data(), d_cnt.p, cnt.size() * 8, cudaMemcpyDeviceToHost));
+    for (int64_t q = 0; q < n; ++q) {
+        if (cnt[(size_t)q] == 0) continue;  // batch_reranker returns empty vectors for a query without candidates
+        if (cnt[(size_t)q] < 0)
+            return fail(DRM_ENOTENOUGH, "Not enough candidates (" + std::to_string(-cnt[(size_t)q] - 1) + " < " + std::to_string(ko) + ") for query " + std::to_string(q));
+        for (int64_t j = 0; j < ko; ++j) {
+            out_scores[*out_count] = od[(size_t)(q * ko + j)];
+            out_ids[*out_count] = plan.unique[orow[(size_t)(q * ko + j)]];
+            ++*out_count;
+        }
+    }
+    return DRM_OK;
+}
+
 }  // extern "C"

@@ -156,15 +156,40 @@ struct DeviceEmbedder {
     float *out = nullptr;  // [chunk][128] staging for host-pointer calls
 };
 struct EmbedSource {
-    int mode = 0;  // 0: byte strings flat/off; 1: '<' + reference window + '>' by window id (find_sequence ids)
+    int mode = 0;  // 0: byte strings flat/off; 1: reference windows by window id (find_sequence ids)
     const char *flat = nullptr; const int64_t *off = nullptr;
     const uint8_t *cls = nullptr; int form = 0; int64_t ref_n = 0; int ref_len = 0;  // DeviceRef::data
-    unsigned long long first_id = 0, id_step = 1;
+    unsigned long long first_id = 0, id_step = 1;   // window i has id first_id + i * id_step ...
+    const unsigned long long *ids = nullptr;        // ... unless an id list (device) is given
+    int decorate = 1;  // 1: '<' + window + '>' (the strings format_fasta builds); 0: the bare window find_sequence returns
 };
 int embedder_upload(const EmbedWeightsHost &w, int device, int max_len, DeviceEmbedder &e);
 void embedder_free(DeviceEmbedder &e);
 // Embeds sequences [first, first + n) of `src` into out_dev (n x 128 floats on the embedder's device).
 void tokenize_host(const char *flat, const int64_t *off, int64_t n, int T, uint16_t *tokens);
 int launch_embed(DeviceEmbedder &e, const EmbedSource &src, int64_t first, int64_t n, float *out_dev, cudaStream_t stream);
+
+// ---------------------------------------------------------------------------------------------
+// L2 rerank stage (post_process_l2_static / _dynamic + batch_reranker; l2_plan.cpp, l2_kernel.cu)
+struct L2Plan {
+    int64_t n = 0, k_out = 0;
+    bool passthrough = false;            // dynamic variant on a dense index: search order and distances pass through
+    int64_t take = 0;                    // ... the first `take` neighbours of every query
+    std::vector<uint64_t> unique;        // window ids to embed (dynamic: find_sequence ids; static: rows of ref_seqs)
+    std::vector<uint32_t> map;           // flat candidate list -> row of `unique`
+    std::vector<int64_t> starts;         // n + 1 slice boundaries into the flat list, as the reference computes them
+};
+// mode 0 = static (bound = number of ref_seqs), 1 = dynamic (bound = genome length).  DRM_OK or an error with the
+// reference's message.
+int l2_plan(int mode, const int64_t *neighbors, int64_t n, int64_t k_in, int64_t stride, int64_t k, int64_t k_clusters,
+            uint64_t bound, L2Plan &plan);
+// libstdc++ std::partial_sort(idx, idx + k, idx + n, dist[a] < dist[b]) on the host (the code the kernel runs)
+void l2_select_host(const float *dist, int64_t n, int64_t k, int64_t *idx);
+// emb: unique windows' embeddings [U][128]; map/starts as in L2Plan (device copies); q: [n][128]; dist_scr / idx_scr: one
+// entry per flat candidate.  Writes k distances + rows of `unique` per query (n x k) and counts[q] = k, 0 (no
+// candidates) or -(number of candidates) - 1 when there are fewer than k.
+int launch_l2_rerank(const float *emb, const uint32_t *map, const int64_t *starts, const float *q, int64_t n, int k,
+                     float *dist_scr, int64_t *idx_scr, float *out_dist, uint32_t *out_rows, int64_t *counts,
+                     cudaStream_t stream);
 
 }  // namespace drm

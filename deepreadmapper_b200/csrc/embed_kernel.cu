@@ -32,6 +32,7 @@ struct SrcDev {
     const char *flat; const long long *off;
     const uint8_t *cls; int form; long long ref_n; int ref_len;
     unsigned long long first_id, id_step;
+    const unsigned long long *ids; int decorate;
 };
 
 // char2Val after tolower (includes/inference/preprocess.hpp:9-25) with '<' and '>' kept apart
@@ -48,25 +49,25 @@ __host__ __device__ __forceinline__ int byte_code(unsigned char c)
 
 struct SeqView {
     const unsigned char *bytes;  // mode 0
-    const uint8_t *win; bool rc; int ref_len;  // mode 1
+    const uint8_t *win; bool rc; int ref_len; int dec;  // mode 1 (dec = 1: '<' and '>' around the window)
     int n;
 };
 
 __host__ __device__ __forceinline__ SeqView seq_view(const SrcDev &s, long long i)
 {
     SeqView v;
-    v.bytes = nullptr; v.win = nullptr; v.rc = false; v.ref_len = s.ref_len; v.n = 0;
+    v.bytes = nullptr; v.win = nullptr; v.rc = false; v.ref_len = s.ref_len; v.dec = s.decorate ? 1 : 0; v.n = 0;
     if (s.mode == 0) {
         v.bytes = reinterpret_cast<const unsigned char *>(s.flat) + s.off[i];
         v.n = (int)(s.off[i + 1] - s.off[i]);
     } else {  // find_sequence (src/utils/post_processor.cpp:47-66) wrapped in PREFIX / POSTFIX (src/utils/parse_inputs.cpp:340-343)
-        const unsigned long long id = s.first_id + (unsigned long long)i * s.id_step;
+        const unsigned long long id = s.ids ? s.ids[i] : s.first_id + (unsigned long long)i * s.id_step;
         if (s.form == 1) {
-            if (id < (unsigned long long)s.ref_n) { v.win = s.cls + id * (unsigned long long)s.ref_len; v.n = s.ref_len + 2; }
+            if (id < (unsigned long long)s.ref_n) { v.win = s.cls + id * (unsigned long long)s.ref_len; v.n = s.ref_len + 2 * v.dec; }
         } else {
             const unsigned long long pos = id >> 1;
             if (pos + (unsigned long long)s.ref_len <= (unsigned long long)s.ref_n) {
-                v.win = s.cls + pos; v.rc = (id & 1) != 0; v.n = s.ref_len + 2;
+                v.win = s.cls + pos; v.rc = (id & 1) != 0; v.n = s.ref_len + 2 * v.dec;
             }
         }
     }
@@ -76,9 +77,11 @@ __host__ __device__ __forceinline__ SeqView seq_view(const SrcDev &s, long long 
 __host__ __device__ __forceinline__ int seq_code(const SeqView &v, int j)
 {
     if (v.bytes) return byte_code(v.bytes[j]);
-    if (j == 0) return CODE_LT;
-    if (j == v.n - 1) return CODE_GT;
-    const int b = j - 1;
+    if (v.dec) {
+        if (j == 0) return CODE_LT;
+        if (j == v.n - 1) return CODE_GT;
+    }
+    const int b = j - v.dec;
     const int c = v.rc ? v.win[v.ref_len - 1 - b] : v.win[b];  // base classes 0..3 = A,C,G,T; 4 = N; 7 = other
     if (c > 3) return 7;
     return v.rc ? 3 - c : c;
@@ -260,7 +263,7 @@ template <class T> int upload(const std::vector<T> &h, T **d)
 void tokenize_host(const char *flat, const int64_t *off, int64_t n, int T, uint16_t *tokens)
 {
     SrcDev s{};
-    s.mode = 0; s.flat = flat; s.off = reinterpret_cast<const long long *>(off);
+    s.mode = 0; s.decorate = 1; s.flat = flat; s.off = reinterpret_cast<const long long *>(off);
     for (int64_t i = 0; i < n; ++i) {
         const SeqView v = seq_view(s, i);
         for (int t = 0; t < T; ++t) {
@@ -341,6 +344,7 @@ int launch_embed(DeviceEmbedder &e, const EmbedSource &src, int64_t first, int64
     s.mode = src.mode; s.flat = src.flat; s.off = reinterpret_cast<const long long *>(src.off);
     s.cls = src.cls; s.form = src.form; s.ref_n = src.ref_n; s.ref_len = src.ref_len;
     s.first_id = src.first_id; s.id_step = src.id_step;
+    s.ids = src.ids; s.decorate = src.decorate;
     for (int64_t done = 0; done < n; done += e.chunk) {
         const int64_t m = (n - done) < e.chunk ? (n - done) : e.chunk;
         const unsigned blocks = (unsigned)((m + ES - 1) / ES);

@@ -205,6 +205,27 @@ int drm_embed_device(drm_embedder *e, const char *seq_flat_dev, const int64_t *s
 int drm_embed_windows_device(drm_embedder *e, const drm_ref *ref, uint64_t first_id, uint64_t id_step, int64_t n,
                              float *out_dev, void *stream);
 
+/* ------------------------------------------------------------------ L2 rerank stage (embedding distance) */
+/* post_process_l2_static (mode 0, src/utils/post_processor.cpp:1023-1162) / post_process_l2_dynamic (mode 1, :552-748)
+ * with batch_reranker (src/utils/reranker.cpp:98-196): the candidates of every query are expanded from its search
+ * labels, their windows embedded on the device (de-duplicated), ranked by calc_l2_dist (src/utils/metrics.cpp:47-61) to
+ * the query's embedding with std::partial_sort's order.  neighbors / distances: n x k_in search output (host); q_emb:
+ * n x 128 (host).  Outputs are FLAT like the reference's final vectors: k values per query in the dynamic variant,
+ * k_clusters in the static one (what the reference passes to batch_reranker), queries without candidates contribute
+ * nothing; capacity n * max(k, k_clusters); *out_count = values written.  On a dense index (stride 1) the dynamic
+ * variant passes the first k search results through, like the reference.  The reference's flat slice arithmetic is kept
+ * (DESIGN.md); inputs for which it would read past its candidate list are refused with DRM_EINVAL.
+ * STATUS: host planning and selection code are tested on the CPU; the device path has not yet run on hardware. */
+int drm_l2_rerank(drm_embedder *e, drm_ref *ref, int mode, const int64_t *neighbors, const float *distances, int64_t n, int64_t k_in,
+                  const float *q_emb, int64_t stride, int64_t k, int64_t k_clusters, float *out_scores, uint64_t *out_ids,
+                  int64_t *out_count);
+/* Host-only pieces of the above, exposed for tests: the candidate plan (info[0..4] = unique windows, flat candidates,
+ * results per query, pass-through flag, pass-through count; arrays nullable, sized from a first call) and the
+ * partial_sort order (idx: n entries, the first k are the selection). */
+int drm_l2_plan_host(int mode, const int64_t *neighbors, int64_t n, int64_t k_in, int64_t stride, int64_t k, int64_t k_clusters,
+                     uint64_t bound, int64_t *info, uint64_t *unique, uint32_t *map, int64_t *starts);
+int drm_l2_select_host(const float *dist, int64_t n, int64_t k, int64_t *idx);
+
 /* ------------------------------------------------------------------ sharded-index merge */
 /* D_all/I_all: n_shards x n x k (the all-gathered per-shard results, each row ascending, I already
  * offset to global ids); writes the global top-k per read to D_out/I_out (n x k), ordered by (D, I). */

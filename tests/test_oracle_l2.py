@@ -148,3 +148,52 @@ def test_undefined_slices_raise_in_the_oracle(env):
     q_emb = np.zeros((4, 128), np.float32)
     with pytest.raises(L2.OracleError, match="runs past"):
         L2.post_process_l2_dynamic(nb, np.zeros((4, 6), np.float32), genome, 150, 4, 8, 5, q_emb, env["embed_fn"])
+
+
+# ---- the product's host-side pieces of the L2 stage (no device needed) against the oracle ---------------------------------
+def test_product_selection_order_equals_oracle_heap_select():
+    import deepreadmapper_b200 as drm
+    g = np.random.default_rng(6)
+    for n, k in ((1, 1), (2, 2), (7, 3), (35, 10), (35, 35), (75, 12), (480, 128), (300, 1)):
+        for ties in (True, False):
+            d = (g.integers(0, 5, n) if ties else g.random(n)).astype(np.float32)
+            assert np.array_equal(drm.l2_select_host(d, k), L2.partial_sort_asc(d, k)), (n, k, ties)
+
+
+def test_product_plan_equals_oracle_bookkeeping():
+    import deepreadmapper_b200 as drm
+    g = np.random.default_rng(7)
+    n, k_in = 11, 9
+    # dynamic, sparse
+    stride, k_clusters, k, bound = 4, 5, 12, 3000
+    nb = g.integers(1, (bound - stride) // stride, (n, k_in)).astype(np.int64)
+    p = drm.l2_plan_host(1, nb, stride, k, k_clusters, bound)
+    order, mapping = L2._expand_flat(nb[:, :k_clusters].astype(np.uint64).reshape(-1), stride, bound)
+    assert p["k_out"] == k and not p["passthrough"]
+    assert p["unique"].tolist() == order and p["map"].tolist() == mapping
+    assert p["starts"].tolist() == [q * k_clusters * (2 * stride - 1) for q in range(n + 1)]
+    # dynamic, dense: pass-through of min(k, k_in) search results
+    p = drm.l2_plan_host(1, nb, 1, 5, 5, bound)
+    assert p["passthrough"] and p["take"] == 5 and p["k_out"] == 5
+    # static, dense (drops nothing here) and sparse (boundaries count `stride` per id)
+    p = drm.l2_plan_host(0, nb, 1, 5, 5, bound)
+    assert p["k_out"] == 5 and p["unique"].tolist() == nb.reshape(-1).tolist() and p["map"].tolist() == list(range(n * k_in))
+    assert p["starts"].tolist() == [q * k_in for q in range(n + 1)]
+    p = drm.l2_plan_host(0, nb, 3, 4, 4, bound)
+    order, mapping = L2._expand_flat(nb.astype(np.uint64).reshape(-1), 3, bound)
+    assert p["unique"].tolist() == order and p["map"].tolist() == mapping and p["starts"].tolist() == [q * k_in * 3 for q in range(n + 1)]
+    # errors: the guard, and slices that would leave the flat list (a clipped id)
+    with pytest.raises(drm.DrmError, match="Final k too large") as e:
+        drm.l2_plan_host(1, nb, stride, 41, 5, bound)
+    assert e.value.code == -6
+    nb2 = nb.copy(); nb2[0, 0] = 0
+    with pytest.raises(drm.DrmError, match="run past") as e:
+        drm.l2_plan_host(1, nb2, stride, k, k_clusters, bound)
+    assert e.value.code == -1
+    nb3 = nb.copy(); nb3[3, 2] = -1  # a padded search label: long -> size_t, position out of range, skipped
+    with pytest.raises(drm.DrmError, match="run past"):
+        drm.l2_plan_host(1, nb3, stride, k, k_clusters, bound)
+    # static dense with an out-of-range id: the reference's mapping keeps original positions and trips its own check
+    nb4 = nb.copy(); nb4[2, 1] = bound + 5
+    with pytest.raises(drm.DrmError, match="Invalid mapping index"):
+        drm.l2_plan_host(0, nb4, 1, 5, 5, bound)
