@@ -80,6 +80,7 @@ public:
     std::vector<std::vector<float>> vectorize(const std::vector<std::string> &input, bool verbose = false);
     // flat form for large batches: out = input.size() x 128 row-major
     void vectorize_flat(const std::vector<std::string> &input, std::vector<float> &out);
+    drm_embedder *handle() const { return handle_; }
 private:
     drm_embedder *handle_ = nullptr;
     size_t model_out_size_;
@@ -102,6 +103,21 @@ std::tuple<std::vector<std::string>, std::vector<int>, std::vector<size_t>> post
     const std::vector<std::vector<NeighborType>> &neighbors, const std::vector<std::vector<float>> &distances,
     const std::vector<std::string> &ref_seqs, const std::vector<std::string> &query_seqs, size_t ref_len, size_t stride, size_t k,
     size_t k_clusters = 5);
+
+// The L2 rerank variants (includes/utils/post_processor.hpp:118-141,170-181) over drm_l2_rerank: candidate windows are
+// embedded on the device and ranked by embedding distance.  Every query must carry the same number of neighbours.
+// (Device path awaiting its first hardware run - DESIGN.md section 4.10.)
+template <typename NeighborType>
+std::tuple<std::vector<std::string>, std::vector<float>, std::vector<size_t>> post_process_l2_dynamic(
+    const std::vector<std::vector<NeighborType>> &neighbors, const std::vector<std::vector<float>> &distances, const std::string &ref_genome,
+    const std::vector<std::string> &query_seqs, size_t ref_len, size_t stride, size_t k, const std::vector<std::vector<float>> &query_embeddings,
+    Vectorizer &vectorizer, size_t k_clusters = 5);
+
+template <typename NeighborType>
+std::tuple<std::vector<std::string>, std::vector<float>, std::vector<size_t>> post_process_l2_static(
+    const std::vector<std::vector<NeighborType>> &neighbors, const std::vector<std::vector<float>> &distances,
+    const std::vector<std::string> &ref_seqs, const std::vector<std::string> &query_seqs, size_t ref_len, size_t stride, size_t k,
+    const std::vector<std::vector<float>> &query_embeddings, Vectorizer &vectorizer, size_t k_clusters = 5);
 
 // Flat rerank for the pipeline: neighbours n x k_in (int64), returns scores / ids n x k; candidate strings are not built.
 // mode 0 = static bound rule, 1 = dynamic.  `genome` is the cleaned reference (extract_FASTA_sequence).

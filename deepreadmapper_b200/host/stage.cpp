@@ -442,3 +442,96 @@ std::string embedder_model_path()
     const char *env = std::getenv("DRM_MODEL");
     return env ? std::string(env) : std::string(Config::Inference::MODEL_PATH);
 }
+
+// ---------------------------------------------------------------------------------------------------------------------
+// post_process_l2_dynamic / post_process_l2_static (src/utils/post_processor.cpp:552-748,1023-1162) over drm_l2_rerank
+namespace {
+
+template <typename NeighborType>
+void l2_inputs(const std::vector<std::vector<NeighborType>> &neighbors, const std::vector<std::vector<float>> &distances,
+               const std::vector<std::vector<float>> &query_embeddings, std::vector<int64_t> &nb, std::vector<float> &ds, std::vector<float> &qe,
+               int64_t &k_in)
+{
+    const size_t n = query_embeddings.size();
+    if (neighbors.size() != n || distances.size() != n) throw std::runtime_error("post_process_l2: neighbors, distances and query embeddings differ in length");
+    k_in = n ? (int64_t)neighbors[0].size() : 0;
+    nb.clear(); ds.clear(); qe.clear();
+    for (size_t i = 0; i < n; ++i) {
+        if ((int64_t)neighbors[i].size() != k_in || (int64_t)distances[i].size() != k_in)
+            throw std::runtime_error("post_process_l2: every query must carry the same number of neighbours");
+        if (query_embeddings[i].size() != Config::Inference::MODEL_OUT_SIZE) throw std::runtime_error("post_process_l2: query embeddings must have 128 values");
+        for (int64_t j = 0; j < k_in; ++j) nb.push_back((int64_t)neighbors[i][(size_t)j]);  // size_t -> long keeps the bit pattern
+        ds.insert(ds.end(), distances[i].begin(), distances[i].end());
+        qe.insert(qe.end(), query_embeddings[i].begin(), query_embeddings[i].end());
+    }
+}
+
+}  // namespace
+
+template <typename NeighborType>
+std::tuple<std::vector<std::string>, std::vector<float>, std::vector<size_t>> post_process_l2_dynamic(
+    const std::vector<std::vector<NeighborType>> &neighbors, const std::vector<std::vector<float>> &distances, const std::string &ref_genome,
+    const std::vector<std::string> &, size_t ref_len, size_t stride, size_t k, const std::vector<std::vector<float>> &query_embeddings,
+    Vectorizer &vectorizer, size_t k_clusters)
+{
+    std::vector<int64_t> nb; std::vector<float> ds, qe; int64_t k_in = 0;
+    l2_inputs(neighbors, distances, query_embeddings, nb, ds, qe, k_in);
+    const int64_t n = (int64_t)query_embeddings.size();
+    std::vector<float> scores((size_t)n * std::max(k, k_clusters) + 1);
+    std::vector<uint64_t> ids(scores.size());
+    int64_t count = 0;
+    if (n && drm_l2_rerank(vectorizer.handle(), genome_ref(ref_genome, ref_len), 1, nb.data(), ds.data(), n, k_in, qe.data(), (int64_t)stride, (int64_t)k,
+                           (int64_t)k_clusters, scores.data(), ids.data(), &count) != DRM_OK)
+        throw_last();
+    std::vector<std::string> seqs((size_t)count);
+    for (int64_t i = 0; i < count; ++i) seqs[(size_t)i] = find_sequence(ref_genome, (size_t)ids[(size_t)i], ref_len);
+    scores.resize((size_t)count);
+    return {std::move(seqs), std::move(scores), std::vector<size_t>(ids.begin(), ids.begin() + count)};
+}
+
+template <typename NeighborType>
+std::tuple<std::vector<std::string>, std::vector<float>, std::vector<size_t>> post_process_l2_static(
+    const std::vector<std::vector<NeighborType>> &neighbors, const std::vector<std::vector<float>> &distances,
+    const std::vector<std::string> &ref_seqs, const std::vector<std::string> &, size_t ref_len, size_t stride, size_t k,
+    const std::vector<std::vector<float>> &query_embeddings, Vectorizer &vectorizer, size_t k_clusters)
+{
+    // ref_seqs are the '<' window '>' strings read_file returns; the device table holds the bare windows and the embedder
+    // puts the decoration back
+    static std::vector<std::string> bare;
+    static const void *bare_key = nullptr;
+    if (bare_key != ref_seqs.data() || bare.size() != ref_seqs.size()) {
+        bare.resize(ref_seqs.size());
+        for (size_t i = 0; i < ref_seqs.size(); ++i) {
+            const std::string &s = ref_seqs[i];
+            if (s.size() != ref_len + 2 || s.front() != '<' || s.back() != '>')
+                throw std::runtime_error("post_process_l2_static: reference sequences must be '<' + ref_len bases + '>'");
+            bare[i] = s.substr(1, ref_len);
+        }
+        bare_key = ref_seqs.data();
+    }
+    std::vector<int64_t> nb; std::vector<float> ds, qe; int64_t k_in = 0;
+    l2_inputs(neighbors, distances, query_embeddings, nb, ds, qe, k_in);
+    const int64_t n = (int64_t)query_embeddings.size();
+    std::vector<float> scores((size_t)n * std::max(k, k_clusters) + 1);
+    std::vector<uint64_t> ids(scores.size());
+    int64_t count = 0;
+    if (n && drm_l2_rerank(vectorizer.handle(), table_ref(bare, ref_len), 0, nb.data(), ds.data(), n, k_in, qe.data(), (int64_t)stride, (int64_t)k,
+                           (int64_t)k_clusters, scores.data(), ids.data(), &count) != DRM_OK)
+        throw_last();
+    std::vector<std::string> seqs((size_t)count);
+    for (int64_t i = 0; i < count; ++i) seqs[(size_t)i] = ref_seqs[(size_t)ids[(size_t)i]];
+    scores.resize((size_t)count);
+    return {std::move(seqs), std::move(scores), std::vector<size_t>(ids.begin(), ids.begin() + count)};
+}
+
+// explicit instantiations, as src/utils/post_processor.cpp:1176-1187
+#define DRM_L2_INST(T)                                                                                                                          \
+    template std::tuple<std::vector<std::string>, std::vector<float>, std::vector<size_t>> post_process_l2_dynamic<T>(                        \
+        const std::vector<std::vector<T>> &, const std::vector<std::vector<float>> &, const std::string &, const std::vector<std::string> &,  \
+        size_t, size_t, size_t, const std::vector<std::vector<float>> &, Vectorizer &, size_t);                                                 \
+    template std::tuple<std::vector<std::string>, std::vector<float>, std::vector<size_t>> post_process_l2_static<T>(                         \
+        const std::vector<std::vector<T>> &, const std::vector<std::vector<float>> &, const std::vector<std::string> &,                        \
+        const std::vector<std::string> &, size_t, size_t, size_t, const std::vector<std::vector<float>> &, Vectorizer &, size_t);
+DRM_L2_INST(size_t)
+DRM_L2_INST(long int)
+#undef DRM_L2_INST
