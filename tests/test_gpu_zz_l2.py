@@ -1,8 +1,9 @@
-"""L2 rerank stage on the device (drm_l2_rerank): FIRST HARDWARE RUN.  The kernels were written after the
-round's GPU budget was spent; host planning and the selection order are tested on the CPU (tests/test_oracle_l2.py), the
-device path has not run yet.  The check runs in a child process (tests/l2_gpu_check.py) so a fault cannot poison this
-session's CUDA context, and is marked xfail(strict=False): the outcome is recorded (XPASS / xfail) without deciding the
-suite, until a round with GPU time confirms it and removes the marker."""
+"""L2 rerank stage on the device (drm_l2_rerank): NOT YET RUN ON HARDWARE.  The kernels were written after
+the round's GPU budget was spent; host planning and the selection order are tested on the CPU (tests/test_oracle_l2.py).
+Until a round with GPU time has run tests/l2_gpu_check.py once, this test only runs on request
+(DRM_RUN_UNVALIDATED=1) - an unvalidated kernel is not allowed to fault on the box that measures the headline bench - and
+then in a child process, so a device fault cannot take this session's CUDA context with it.  After the first green run:
+drop the skip."""
 import os
 import subprocess
 import sys
@@ -12,7 +13,8 @@ import pytest
 pytestmark = pytest.mark.gpu
 
 
-@pytest.mark.xfail(strict=False, reason="first hardware run of the L2 rerank kernels (not yet validated on a GPU)")
+@pytest.mark.skipif(os.environ.get("DRM_RUN_UNVALIDATED") != "1",
+                    reason="L2 rerank kernels have not run on hardware yet; set DRM_RUN_UNVALIDATED=1 to run tests/l2_gpu_check.py")
 def test_l2_rerank_stage_against_oracle_first_hardware_run():
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
     r = subprocess.run([sys.executable, os.path.join(root, "tests", "l2_gpu_check.py")], capture_output=True, text=True, timeout=300)
