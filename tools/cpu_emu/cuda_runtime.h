@@ -1,0 +1,97 @@
+// TEST INFRASTRUCTURE ONLY: a stand-in for <cuda_runtime.h> that lets g++ compile this repo's simpler CUDA kernels as
+// plain C++ and run them on host threads (tools/cpu_emu/README.md).  One OS thread per CUDA thread of a block, blocks one
+// after the other; __syncthreads / __syncwarp are C++20 barriers that exited threads drop out of.  It exists so that kernel
+// logic and indexing can be checked (under AddressSanitizer too) where no GPU is available; it says nothing about
+// performance, launch limits or device-only failure modes.
+#pragma once
+#include <barrier>
+#include <cmath>
+#include <cstdint>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <functional>
+#include <memory>
+#include <thread>
+#include <vector>
+
+#define __host__
+#define __device__
+#define __global__
+#define __forceinline__ inline
+#define __restrict__
+#define __launch_bounds__(...)
+#define __shared__ static
+#define __align__(n) __attribute__((aligned(n)))
+
+struct uint3 { unsigned x, y, z; };
+struct dim3 { unsigned x = 1, y = 1, z = 1; dim3(unsigned a = 1, unsigned b = 1, unsigned c = 1) : x(a), y(b), z(c) {} };
+struct alignas(16) float4 { float x, y, z, w; };
+
+typedef int cudaError_t;
+typedef void *cudaStream_t;
+constexpr cudaError_t cudaSuccess = 0;
+enum cudaMemcpyKind { cudaMemcpyHostToDevice, cudaMemcpyDeviceToHost, cudaMemcpyDeviceToDevice };
+enum cudaDeviceAttr { cudaDevAttrMultiProcessorCount };
+inline const char *cudaGetErrorString(cudaError_t) { return "emulated"; }
+inline cudaError_t cudaMalloc(void **p, size_t n) { *p = std::malloc(n ? n : 1); return *p ? 0 : 2; }
+inline cudaError_t cudaFree(void *p) { std::free(p); return 0; }
+inline cudaError_t cudaMemcpy(void *d, const void *s, size_t n, cudaMemcpyKind) { std::memcpy(d, s, n); return 0; }
+inline cudaError_t cudaSetDevice(int) { return 0; }
+inline cudaError_t cudaGetLastError() { return 0; }
+inline cudaError_t cudaStreamSynchronize(cudaStream_t) { return 0; }
+inline cudaError_t cudaDeviceGetAttribute(int *v, cudaDeviceAttr, int) { *v = 2; return 0; }  // a 2-SM "device": small passes
+
+namespace emu {
+struct Block {
+    int live = 0;
+    std::unique_ptr<std::barrier<>> all;
+    std::vector<std::unique_ptr<std::barrier<>>> warp;
+};
+inline thread_local uint3 t_threadIdx, t_blockIdx;
+inline thread_local dim3 t_blockDim, t_gridDim;
+inline thread_local Block *t_block = nullptr;
+
+template <class F> void launch(dim3 grid, dim3 block, F &&body)
+{
+    const unsigned nthreads = block.x * block.y * block.z;
+    for (unsigned bz = 0; bz < grid.z; ++bz)
+        for (unsigned by = 0; by < grid.y; ++by)
+            for (unsigned bx = 0; bx < grid.x; ++bx) {
+                Block b;
+                b.all = std::make_unique<std::barrier<>>((std::ptrdiff_t)nthreads);
+                for (unsigned w = 0; w < (nthreads + 31) / 32; ++w)
+                    b.warp.push_back(std::make_unique<std::barrier<>>((std::ptrdiff_t)std::min(32u, nthreads - 32 * w)));
+                std::vector<std::thread> ts;
+                ts.reserve(nthreads);
+                for (unsigned t = 0; t < nthreads; ++t)
+                    ts.emplace_back([&, t] {
+                        t_threadIdx = {t % block.x, (t / block.x) % block.y, t / (block.x * block.y)};
+                        t_blockIdx = {bx, by, bz};
+                        t_blockDim = block; t_gridDim = grid; t_block = &b;
+                        body();
+                        b.all->arrive_and_drop();          // a thread that returned no longer takes part in barriers
+                        b.warp[t / 32]->arrive_and_drop();
+                    });
+                for (auto &th : ts) th.join();
+            }
+}
+}  // namespace emu
+
+#define threadIdx (emu::t_threadIdx)
+#define blockIdx (emu::t_blockIdx)
+#define blockDim (emu::t_blockDim)
+#define gridDim (emu::t_gridDim)
+
+inline void __syncthreads() { emu::t_block->all->arrive_and_wait(); }
+inline void __syncwarp(unsigned = 0xffffffffu)
+{
+    const unsigned t = threadIdx.x + threadIdx.y * blockDim.x + threadIdx.z * blockDim.x * blockDim.y;
+    emu::t_block->warp[t / 32]->arrive_and_wait();
+}
+// round-to-nearest single operations that must not be contracted: volatile keeps g++ from fusing them
+inline float __fadd_rn(float a, float b) { volatile float r = a + b; return r; }
+inline float __fsub_rn(float a, float b) { volatile float r = a - b; return r; }
+inline float __fmul_rn(float a, float b) { volatile float r = a * b; return r; }
+inline float __fsqrt_rn(float a) { return std::sqrt(a); }
+inline float __fmaf_rn(float a, float b, float c) { return std::fmaf(a, b, c); }
