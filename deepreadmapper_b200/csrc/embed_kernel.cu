@@ -15,6 +15,8 @@
 // Scratch (Y1: 63 KB, X2: 189 KB per sequence) is sized for a pass of 148 x 16 x 4 sequences (4 CTA waves).
 #include "common.h"
 
+#include <cstdlib>
+
 namespace drm {
 
 namespace {
@@ -112,7 +114,10 @@ __host__ __device__ __forceinline__ int token_slot(const SeqView &v, int t, int 
 __device__ __forceinline__ float sigmoidf_(float x) { return 1.0f / (1.0f + expf(-x)); }
 
 // LAYER 1: xp from the token table P1, writes Y1.  LAYER 2: xp from X2, writes the final states to out.
-template <int LAYER>
+// PREFETCH: the input-projection values of a step's gate phase are loaded into registers before the step's products, so
+// the global-memory latency (X2 comes from DRAM in layer 2: `long_scoreboard` 7.2 per issue in profiles/r1_ncu_embed_v1) hides
+// behind ~1300 instructions of FMA work.  Same arithmetic in the same order; chosen by DRM_EMBED_PREFETCH=1 until measured.
+template <int LAYER, bool PREFETCH>
 __global__ void __launch_bounds__(ETHREADS, 1)
 gru_kernel(const SrcDev src, const long long first, const long long n, const int T, const float *__restrict__ P1,
            const float *__restrict__ X2, const float *__restrict__ R, const float *__restrict__ bR, float *__restrict__ Y1,
@@ -141,8 +146,25 @@ gru_kernel(const SrcDev src, const long long first, const long long n, const int
     for (int k = 0; k < EH; ++k) w[k] = R[(size_t)(dir * EG + row) * EH + k];
     __syncthreads();
 
+    constexpr int GATE_ITERS = (ES * EH + EG - 1) / EG;  // (sequence, unit) pairs per thread in the gate phase
     for (int step = 0; step < T; ++step) {
         const int t = dir ? T - 1 - step : step;
+        float xz[GATE_ITERS], xr[GATE_ITERS], xh[GATE_ITERS];
+        if (PREFETCH) {
+#pragma unroll
+            for (int m = 0; m < GATE_ITERS; ++m) {
+                const int p = row + m * EG;
+                xz[m] = xr[m] = xh[m] = 0.0f;
+                if (p < ES * EH) {
+                    const int s = p / EH, i = p % EH;
+                    const long long seq = base + s;
+                    const float *xp;
+                    if (LAYER == 1) xp = P1 + (size_t)(dir * NSLOT + tok_s[s][t]) * EG;
+                    else xp = X2 + ((size_t)(seq < n ? seq : 0) * T + t) * (2 * EG) + dir * EG;
+                    xz[m] = xp[i]; xr[m] = xp[EH + i]; xh[m] = xp[2 * EH + i];
+                }
+            }
+        }
         // a = R . h for the 16 sequences, four at a time
 #pragma unroll 1
         for (int s = 0; s < ES; s += 4) {
@@ -167,18 +189,35 @@ gru_kernel(const SrcDev src, const long long first, const long long n, const int
         }
         __syncthreads();
         // gates: z = s(xz + az), r = s(xr + ar), g = tanh(xh + r (ah + bRh)), h' = (1 - z) g + z h
-        for (int p = row; p < ES * EH; p += EG) {
-            const int s = p / EH, i = p % EH;
-            const long long seq = base + s;
-            const float *xp;
-            if (LAYER == 1) xp = P1 + (size_t)(dir * NSLOT + tok_s[s][t]) * EG;
-            else xp = X2 + ((size_t)(seq < n ? seq : 0) * T + t) * (2 * EG) + dir * EG;
-            const float z = sigmoidf_(xp[i] + a_s[dir][s][i]);
-            const float r = sigmoidf_(xp[EH + i] + a_s[dir][s][EH + i]);
-            const float g = tanhf(xp[2 * EH + i] + r * (a_s[dir][s][2 * EH + i] + bR[dir * EH + i]));
-            const float hn = (1.0f - z) * g + z * h_s[dir][s][i];
-            h_s[dir][s][i] = hn;
-            if (LAYER == 1 && seq < n) Y1[((size_t)seq * T + t) * (2 * EH) + dir * EH + i] = hn;
+        if (!PREFETCH) {
+            for (int p = row; p < ES * EH; p += EG) {
+                const int s = p / EH, i = p % EH;
+                const long long seq = base + s;
+                const float *xp;
+                if (LAYER == 1) xp = P1 + (size_t)(dir * NSLOT + tok_s[s][t]) * EG;
+                else xp = X2 + ((size_t)(seq < n ? seq : 0) * T + t) * (2 * EG) + dir * EG;
+                const float z = sigmoidf_(xp[i] + a_s[dir][s][i]);
+                const float r = sigmoidf_(xp[EH + i] + a_s[dir][s][EH + i]);
+                const float g = tanhf(xp[2 * EH + i] + r * (a_s[dir][s][2 * EH + i] + bR[dir * EH + i]));
+                const float hn = (1.0f - z) * g + z * h_s[dir][s][i];
+                h_s[dir][s][i] = hn;
+                if (LAYER == 1 && seq < n) Y1[((size_t)seq * T + t) * (2 * EH) + dir * EH + i] = hn;
+            }
+        } else {
+#pragma unroll
+            for (int m = 0; m < GATE_ITERS; ++m) {
+                const int p = row + m * EG;
+                if (p < ES * EH) {
+                    const int s = p / EH, i = p % EH;
+                    const long long seq = base + s;
+                    const float z = sigmoidf_(xz[m] + a_s[dir][s][i]);
+                    const float r = sigmoidf_(xr[m] + a_s[dir][s][EH + i]);
+                    const float g = tanhf(xh[m] + r * (a_s[dir][s][2 * EH + i] + bR[dir * EH + i]));
+                    const float hn = (1.0f - z) * g + z * h_s[dir][s][i];
+                    h_s[dir][s][i] = hn;
+                    if (LAYER == 1 && seq < n) Y1[((size_t)seq * T + t) * (2 * EH) + dir * EH + i] = hn;
+                }
+            }
         }
         __syncthreads();
     }
@@ -345,13 +384,17 @@ int launch_embed(DeviceEmbedder &e, const EmbedSource &src, int64_t first, int64
     s.cls = src.cls; s.form = src.form; s.ref_n = src.ref_n; s.ref_len = src.ref_len;
     s.first_id = src.first_id; s.id_step = src.id_step;
     s.ids = src.ids; s.decorate = src.decorate;
+    const char *pf = getenv("DRM_EMBED_PREFETCH");
+    const bool prefetch = pf && pf[0] == '1';
     for (int64_t done = 0; done < n; done += e.chunk) {
         const int64_t m = (n - done) < e.chunk ? (n - done) : e.chunk;
         const unsigned blocks = (unsigned)((m + ES - 1) / ES);
-        gru_kernel<1><<<blocks, ETHREADS, 0, stream>>>(s, first + done, m, T, e.P1, nullptr, e.R1, e.bR1, e.Y1, nullptr);
+        if (prefetch) gru_kernel<1, true><<<blocks, ETHREADS, 0, stream>>>(s, first + done, m, T, e.P1, nullptr, e.R1, e.bR1, e.Y1, nullptr);
+        else gru_kernel<1, false><<<blocks, ETHREADS, 0, stream>>>(s, first + done, m, T, e.P1, nullptr, e.R1, e.bR1, e.Y1, nullptr);
         proj2_kernel<<<blocks, ETHREADS, 0, stream>>>(m, T, e.W2, e.b2, e.Y1, e.X2);
-        gru_kernel<2><<<blocks, ETHREADS, 0, stream>>>(s, first + done, m, T, nullptr, e.X2, e.R2, e.bR2, nullptr,
-                                                       out_dev + (size_t)done * 2 * EH);
+        float *dst = out_dev + (size_t)done * 2 * EH;
+        if (prefetch) gru_kernel<2, true><<<blocks, ETHREADS, 0, stream>>>(s, first + done, m, T, nullptr, e.X2, e.R2, e.bR2, nullptr, dst);
+        else gru_kernel<2, false><<<blocks, ETHREADS, 0, stream>>>(s, first + done, m, T, nullptr, e.X2, e.R2, e.bR2, nullptr, dst);
         DRM_CUDA_TRY(cudaGetLastError());
     }
     return DRM_OK;

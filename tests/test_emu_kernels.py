@@ -71,7 +71,14 @@ def _window(genome, dense_id, ref_len):
     return w.translate(comp)[::-1] if dense_id % 2 else w
 
 
-def test_embed_kernels_byte_strings(emu):
+@pytest.fixture(params=["0", "1"], ids=["default", "prefetch"])
+def prefetch(request, monkeypatch):
+    """Both code paths of gru_kernel: the default one and the DRM_EMBED_PREFETCH=1 variant (opt-in until measured)."""
+    monkeypatch.setenv("DRM_EMBED_PREFETCH", request.param)
+    return request.param
+
+
+def test_embed_kernels_byte_strings(emu, prefetch):
     w = EO.random_weights(71)
     g = np.random.default_rng(72)
     seqs = [b"", b"A", b"<ACGNNT>", b"ACGTNACGT" * 20]
@@ -87,7 +94,7 @@ def test_embed_kernels_byte_strings(emu):
     assert float(np.abs(got - EO.embed(many, w, max_len=16)).max()) < TOL
 
 
-def test_embed_kernels_window_sources(emu):
+def test_embed_kernels_window_sources(emu, prefetch):
     w = EO.random_weights(73)
     g = np.random.default_rng(74)
     genome = bytes(g.choice(np.frombuffer(b"ACGTN", np.uint8), 400, p=[0.245, 0.245, 0.245, 0.245, 0.02]))
@@ -152,7 +159,11 @@ def test_same_checks_under_address_sanitizer():
         "import sys, ctypes as C; sys.path.insert(0, %r); sys.path.insert(0, %r)\n"
         "import test_emu_kernels as T\n"
         "lib = C.CDLL(%r); lib.emu_last_error.restype = C.c_char_p\n"
-        "T.test_embed_kernels_byte_strings(lib); T.test_embed_kernels_window_sources(lib); T.test_l2_rerank_kernel(lib)\n"
+        "import os\n"
+        "for pf in ('0', '1'):\n"
+        "    os.environ['DRM_EMBED_PREFETCH'] = pf\n"
+        "    T.test_embed_kernels_byte_strings(lib, pf); T.test_embed_kernels_window_sources(lib, pf)\n"
+        "T.test_l2_rerank_kernel(lib)\n"
         "print('asan run ok')\n" % (ROOT, os.path.join(ROOT, "tests"), lib))
     env = dict(os.environ, LD_PRELOAD=asan, ASAN_OPTIONS="detect_leaks=0:abort_on_error=0")
     r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, env=env, timeout=900)

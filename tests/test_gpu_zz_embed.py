@@ -183,3 +183,19 @@ def test_cli_from_sequence_files_only(tmp_path):
     S, SI = np.load(out / "sw_scores.npy"), np.load(out / "sw_indices.npy")
     rc, s0, i0, _ = ob.post_process_sw(1, I0, genome, len(genome), 150, ["<" + x.decode() + ">" for x in reads], 1, 16, 16)
     assert rc == 0 and np.array_equal(S, s0) and np.array_equal(SI, i0)
+
+
+def test_prefetch_variant_is_bit_identical(monkeypatch):
+    """DRM_EMBED_PREFETCH=1 (input projections loaded before a step's products; opt-in until it has been timed) does the
+    same arithmetic in the same order as the default kernels."""
+    w = EO.random_weights(61)
+    g = np.random.default_rng(62)
+    seqs = _random_seqs(g, 70, 2, 200)
+    v = drm.Vectorizer(weights=w)
+    monkeypatch.setenv("DRM_EMBED_PREFETCH", "0")
+    a = v.vectorize(seqs)
+    monkeypatch.setenv("DRM_EMBED_PREFETCH", "1")
+    b = v.vectorize(seqs)
+    assert np.array_equal(a.view(np.uint32), b.view(np.uint32))
+    assert float(np.abs(b - EO.embed(seqs, w)).max()) < TOL
+    v.close()

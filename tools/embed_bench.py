@@ -57,11 +57,16 @@ def main():
 
     ms_reads = timed(lambda: v.vectorize_device(flat.data_ptr(), off.data_ptr(), 0, n, out.data_ptr()))
     chk = float(out.abs().mean().item())
+    os.environ["DRM_EMBED_PREFETCH"] = "1"  # A/B: the opt-in variant that loads a step's input projections early
+    ms_reads_pf = timed(lambda: v.vectorize_device(flat.data_ptr(), off.data_ptr(), 0, n, out.data_ptr()))
+    chk_pf = float(out.abs().mean().item())
+    os.environ["DRM_EMBED_PREFETCH"] = "0"
     ms_win = timed(lambda: v.vectorize_windows_device(ref, 0, 1, n, out.data_ptr()))
     fma = 12.1e6
     res = {"sequences": n, "reads_ms": ms_reads, "reads_per_s": n / ms_reads * 1e3, "windows_ms": ms_win,
            "windows_per_s": n / ms_win * 1e3, "fp32_tflops_reads": 2 * fma * n / ms_reads * 1e3 / 1e12,
-           "mean_abs_output": chk, "gpu": torch.cuda.get_device_name(0)}
+           "mean_abs_output": chk, "prefetch_reads_ms": ms_reads_pf, "prefetch_reads_per_s": n / ms_reads_pf * 1e3,
+           "prefetch_mean_abs_output": chk_pf, "gpu": torch.cuda.get_device_name(0)}
     print(json.dumps(res))
     os.makedirs(os.path.dirname(a.out) or ".", exist_ok=True)
     with open(a.out, "w") as f:
