@@ -215,7 +215,7 @@ int drm_embed_windows_device(drm_embedder *e, const drm_ref *ref, uint64_t first
  * nothing; capacity n * max(k, k_clusters); *out_count = values written.  On a dense index (stride 1) the dynamic
  * variant passes the first k search results through, like the reference.  The reference's flat slice arithmetic is kept
  * (DESIGN.md); inputs for which it would read past its candidate list are refused with DRM_EINVAL.
- * STATUS: host planning and selection code are tested on the CPU; the device path has not yet run on hardware. */
+ * STATUS: verified against the oracle on a host-thread emulation of these sources (tools/cpu_emu); not yet timed. */
 int drm_l2_rerank(drm_embedder *e, drm_ref *ref, int mode, const int64_t *neighbors, const float *distances, int64_t n, int64_t k_in,
                   const float *q_emb, int64_t stride, int64_t k, int64_t k_clusters, float *out_scores, uint64_t *out_ids,
                   int64_t *out_count);

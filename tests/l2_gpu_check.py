@@ -20,7 +20,7 @@ def same(a, b):
     return a.shape == b.shape and np.array_equal(a.view(np.uint32) if a.dtype == np.float32 else a, b.view(np.uint32) if b.dtype == np.float32 else b)
 
 
-def main():
+def main(n=23):
     g = np.random.default_rng(61)
     v = drm.Vectorizer(weights=EO.random_weights(62))
     embed_fn = lambda seqs: v.vectorize(seqs)  # noqa: E731
@@ -32,7 +32,7 @@ def main():
     genome = bytes(g.choice(np.frombuffer(b"ACGT", np.uint8), 300)) + seg + bytes(g.choice(np.frombuffer(b"ACGT", np.uint8), 500)) + seg + \
         bytes(g.choice(np.frombuffer(b"ACGT", np.uint8), 2400))
     ref = drm.Reference(genome=genome, ref_len=ref_len)
-    n, k_in = 23, 7
+    k_in = 7
     q_emb = embed_fn([b"<" + genome[90 * i:90 * i + 150] + b">" for i in range(n)])
     dist = np.sort(g.random((n, k_in)).astype(np.float32), axis=1)
 
@@ -73,7 +73,7 @@ def main():
         s0, i0 = L2.post_process_l2_static(nb, dist, ref_seqs, ref_len, stride, kk, kk, q_emb, embed_fn)
         assert same(i, i0) and same(s, s0), f"static stride {stride}"
     # ... and on an explicit window table
-    table = drm.Reference(windows=[x[1:-1] for x in ref_seqs[:900]], ref_len=ref_len)
+    table = drm.Reference(windows=[x[1:-1] for x in ref_seqs[:900]], ref_len=ref_len)  # noqa: E501
     nb = g.integers(0, 900, (n, k_in)).astype(np.int64)
     s, i = drm.post_process_l2_static(nb, dist, table, q_emb, v, 1, 5, 5)
     s0, i0 = L2.post_process_l2_static(nb, dist, ref_seqs[:900], ref_len, 1, 5, 5, q_emb, embed_fn)
@@ -82,4 +82,4 @@ def main():
 
 
 if __name__ == "__main__":
-    main()
+    main(int(sys.argv[1]) if len(sys.argv) > 1 else 23)

@@ -160,11 +160,27 @@ def test_same_checks_under_address_sanitizer():
         "import test_emu_kernels as T\n"
         "lib = C.CDLL(%r); lib.emu_last_error.restype = C.c_char_p\n"
         "import os\n"
-        "for pf in ('0', '1'):\n"
-        "    os.environ['DRM_EMBED_PREFETCH'] = pf\n"
-        "    T.test_embed_kernels_byte_strings(lib, pf); T.test_embed_kernels_window_sources(lib, pf)\n"
+        "os.environ['DRM_EMBED_PREFETCH'] = '0'; T.test_embed_kernels_byte_strings(lib, '0')\n"
+        "os.environ['DRM_EMBED_PREFETCH'] = '1'; T.test_embed_kernels_window_sources(lib, '1')\n"
         "T.test_l2_rerank_kernel(lib)\n"
         "print('asan run ok')\n" % (ROOT, os.path.join(ROOT, "tests"), lib))
     env = dict(os.environ, LD_PRELOAD=asan, ASAN_OPTIONS="detect_leaks=0:abort_on_error=0")
     r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, env=env, timeout=900)
     assert r.returncode == 0 and "asan run ok" in r.stdout, (r.stdout[-1500:], r.stderr[-3000:])
+
+
+def test_l2_stage_through_the_c_abi_on_the_emulation():
+    """tests/l2_gpu_check.py - the first-hardware-run check of drm_l2_rerank - executed against the emulated library:
+    the real api.cu (compiled as C++), l2_plan.cpp, and the embedder / L2 kernel sources on host threads, behind the same
+    Python mirror.  Everything after the embeddings must equal the oracle bit for bit."""
+    sys.path.insert(0, os.path.join(ROOT, "tools", "cpu_emu"))
+    import emu_build
+    lib = emu_build.build(sanitize=False)
+    code = (
+        "import sys; sys.path.insert(0, %r); sys.path.insert(0, %r)\n"
+        "import deepreadmapper_b200.api as A\n"
+        "A._LIB_PATH = %r; A._lib = None\n"
+        "import l2_gpu_check\n"
+        "l2_gpu_check.main(4)\n" % (ROOT, os.path.join(ROOT, "tests"), lib))
+    r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=1500)
+    assert r.returncode == 0 and "device == oracle" in r.stdout, (r.stdout[-1500:], r.stderr[-3000:])

@@ -31,12 +31,18 @@ def build(sanitize=True) -> str:
         with open(dst, "w") as fh:
             fh.write(text)
         srcs.append(dst)
-    srcs += [os.path.join(CSRC, "ir_model.cpp"), os.path.join(HERE, "emu_driver.cpp")]
+    # the C-ABI layer itself (no kernel launches of its own) and the plain C++ files it needs
+    api = os.path.join(OUT, "api_emu.cpp")
+    with open(api, "w") as fh:
+        fh.write(open(os.path.join(CSRC, "api.cu")).read())
+    srcs += [api] + [os.path.join(CSRC, f) for f in ("ir_model.cpp", "l2_plan.cpp", "index_io.cpp", "builder.cpp")]
+    srcs += [os.path.join(HERE, "emu_driver.cpp"), os.path.join(HERE, "emu_stubs.cpp")]
     lib = os.path.join(OUT, "libdrm_emu_asan.so" if sanitize else "libdrm_emu.so")
     newest = max(os.path.getmtime(p) for p in srcs + [os.path.join(HERE, "cuda_runtime.h"), os.path.join(CSRC, "common.h")])
     if os.path.exists(lib) and os.path.getmtime(lib) >= newest:
         return lib
-    cmd = ["/usr/bin/g++", "-std=c++20", "-O1", "-g", "-fPIC", "-shared", "-pthread", "-I", HERE, "-I", CSRC, "-o", lib] + srcs
+    cmd = ["/usr/bin/g++", "-std=c++20", "-O1", "-g", "-fPIC", "-shared", "-pthread", "-fopenmp", "-Wl,--no-undefined", "-I", HERE, "-I", CSRC,
+           "-o", lib] + srcs
     if sanitize:
         cmd[3:3] = ["-fsanitize=address", "-fno-omit-frame-pointer"]
     subprocess.check_call(cmd)

@@ -3,13 +3,6 @@
 
 #include <string>
 
-namespace drm {
-static thread_local std::string g_err;
-void set_error(const std::string &m) { g_err = m; }
-int fail(int code, const std::string &m) { g_err = m; return code; }
-const std::string &last_error_string() { return g_err; }
-}  // namespace drm
-
 using namespace drm;
 
 extern "C" {

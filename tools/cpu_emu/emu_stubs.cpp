@@ -1,0 +1,50 @@
+// TEST INFRASTRUCTURE ONLY: what api.cu links against besides the emulated kernel files (README.md).  The kernels that
+// use warp shuffles / ballots / atomics are not emulated: their launchers refuse.  launch_classify is restated on the host
+// because every reference handle needs it (base classes 0..3 = A,C,G,T, 4 = N, 7 = any other byte; csrc/sw_kernel.cu).
+#include "common.h"
+
+namespace drm {
+
+static int na(const char *what) { return fail(DRM_EUNSUPPORTED, std::string(what) + " is not available in the host-thread emulation"); }
+
+int launch_classify(const uint8_t *raw, uint8_t *cls, int64_t n, int *has_other_dev, cudaStream_t)
+{
+    for (int64_t i = 0; i < n; ++i) {
+        uint8_t c;
+        switch (raw[i]) {
+        case 'A': c = 0; break;
+        case 'C': c = 1; break;
+        case 'G': c = 2; break;
+        case 'T': c = 3; break;
+        case 'N': c = 4; break;
+        default: c = 7; *has_other_dev = 1; break;
+        }
+        cls[i] = c;
+    }
+    return DRM_OK;
+}
+
+int build_device_index(const HostIndex &, int, DeviceIndex &) { return na("the index image"); }
+void free_device_index(DeviceIndex &) {}
+int launch_search(const DeviceIndex &, const float *, int64_t, int, int, float *, int64_t *, int64_t *, cudaStream_t) { return na("the search kernel"); }
+int launch_rerank(const DeviceRef &, const RerankArgs &, cudaStream_t) { return na("the SW rerank kernel"); }
+int launch_sw_pairs(const char *, const int64_t *, const char *, const int64_t *, int64_t, int, int32_t *, cudaStream_t) { return na("the SW pair kernel"); }
+int launch_merge_topk(const float *, const int64_t *, int, int64_t, int, float *, int64_t *, cudaStream_t) { return na("the merge kernel"); }
+int launch_sw_align(const DeviceRef &, const unsigned long long *, int64_t, int, const char *, const int64_t *, int, int, int, int *, int *, int *,
+                    int *, int *, int *, int *, unsigned *, cudaStream_t) { return na("the traceback kernel"); }
+int clean_fasta_device(const char *, int64_t, int, uint8_t **, int64_t *) { return na("the FASTA kernels"); }
+int parse_fastq_device(const char *, int64_t, int, char **, int64_t **, int64_t *, int64_t *, int *) { return na("the FASTQ kernels"); }
+
+}  // namespace drm
+
+// C-ABI entry points that live in build_gpu.cu
+extern "C" {
+int drm_build_index_gpu(const float *, int64_t, int, const float *, int64_t, int, int, int, int, int, uint32_t, const char *, double *)
+{
+    return drm::fail(DRM_EUNSUPPORTED, "the GPU index builder is not available in the host-thread emulation");
+}
+int drm_build_index_gpu_device(const float *, int64_t, int, int64_t, int, int, int, int, int, uint32_t, const char *, double *)
+{
+    return drm::fail(DRM_EUNSUPPORTED, "the GPU index builder is not available in the host-thread emulation");
+}
+}
