@@ -69,18 +69,23 @@ struct Block {
     int live = 0;
     std::unique_ptr<std::barrier<>> all;
     std::vector<std::unique_ptr<std::barrier<>>> warp;
+    std::vector<unsigned long long> slots;  // 32 exchange slots per warp (shuffles, votes)
+    std::vector<unsigned char> dyn;         // dynamic shared memory of the block
 };
 inline thread_local uint3 t_threadIdx, t_blockIdx;
 inline thread_local dim3 t_blockDim, t_gridDim;
 inline thread_local Block *t_block = nullptr;
 
-template <class F> void launch(dim3 grid, dim3 block, F &&body)
+inline void *dyn_smem();
+template <class F> void launch(dim3 grid, dim3 block, size_t smem, F &&body)
 {
     const unsigned nthreads = block.x * block.y * block.z;
     for (unsigned bz = 0; bz < grid.z; ++bz)
         for (unsigned by = 0; by < grid.y; ++by)
             for (unsigned bx = 0; bx < grid.x; ++bx) {
                 Block b;
+                b.slots.assign(((nthreads + 31) / 32) * 32, 0ull);
+                b.dyn.assign(smem + 16, 0);
                 b.all = std::make_unique<std::barrier<>>((std::ptrdiff_t)nthreads);
                 for (unsigned w = 0; w < (nthreads + 31) / 32; ++w)
                     b.warp.push_back(std::make_unique<std::barrier<>>((std::ptrdiff_t)std::min(32u, nthreads - 32 * w)));
@@ -92,11 +97,35 @@ template <class F> void launch(dim3 grid, dim3 block, F &&body)
                         t_blockIdx = {bx, by, bz};
                         t_blockDim = block; t_gridDim = grid; t_block = &b;
                         body();
+                        b.slots[t] = 0;                    // ... nor in votes
                         b.all->arrive_and_drop();          // a thread that returned no longer takes part in barriers
                         b.warp[t / 32]->arrive_and_drop();
                     });
                 for (auto &th : ts) th.join();
             }
+}
+inline void *dyn_smem() { return t_block->dyn.data(); }
+inline unsigned flat_tid() { return t_threadIdx.x + t_threadIdx.y * t_blockDim.x + t_threadIdx.z * t_blockDim.x * t_blockDim.y; }
+inline void warp_sync() { t_block->warp[flat_tid() / 32]->arrive_and_wait(); }
+// every lane publishes a 64-bit value, then reads the lane it wants; lanes that already returned keep their last value
+inline unsigned long long exchange(unsigned long long mine, int src_lane)
+{
+    const unsigned t = flat_tid(), base = (t / 32) * 32;
+    t_block->slots[t] = mine;
+    warp_sync();
+    const unsigned long long r = (src_lane >= 0 && src_lane < 32 && base + (unsigned)src_lane < t_block->slots.size()) ? t_block->slots[base + src_lane] : mine;
+    warp_sync();
+    return r;
+}
+template <class T> inline T shfl(T v, int src_lane)
+{
+    static_assert(sizeof(T) <= 8, "shuffle of at most 64 bits");
+    unsigned long long bits = 0;
+    std::memcpy(&bits, &v, sizeof(T));
+    bits = exchange(bits, src_lane);
+    T r;
+    std::memcpy(&r, &bits, sizeof(T));
+    return r;
 }
 }  // namespace emu
 
@@ -117,3 +146,62 @@ inline float __fsub_rn(float a, float b) { volatile float r = a - b; return r; }
 inline float __fmul_rn(float a, float b) { volatile float r = a * b; return r; }
 inline float __fsqrt_rn(float a) { return std::sqrt(a); }
 inline float __fmaf_rn(float a, float b, float c) { return std::fmaf(a, b, c); }
+
+// ---- warp collectives (every live lane of the warp must call them, as with a full mask on the device) ----
+template <class T> inline T __shfl_sync(unsigned, T v, int src, int = 32) { return emu::shfl(v, src & 31); }
+template <class T> inline T __shfl_xor_sync(unsigned, T v, int m, int = 32) { return emu::shfl(v, (int)((emu::flat_tid() & 31) ^ (unsigned)m)); }
+template <class T> inline T __shfl_up_sync(unsigned, T v, unsigned d, int = 32)
+{
+    const int lane = (int)(emu::flat_tid() & 31);
+    return emu::shfl(v, lane - (int)d >= 0 ? lane - (int)d : lane);
+}
+template <class T> inline T __shfl_down_sync(unsigned, T v, unsigned d, int = 32)
+{
+    const int lane = (int)(emu::flat_tid() & 31);
+    return emu::shfl(v, lane + (int)d < 32 ? lane + (int)d : lane);
+}
+inline unsigned __ballot_sync(unsigned, int pred)
+{
+    const unsigned t = emu::flat_tid(), base = (t / 32) * 32;
+    emu::t_block->slots[t] = pred ? 1ull : 0ull;
+    emu::warp_sync();
+    unsigned r = 0;
+    for (unsigned l = 0; l < 32 && base + l < emu::t_block->slots.size(); ++l) r |= (unsigned)(emu::t_block->slots[base + l] & 1ull) << l;
+    emu::warp_sync();
+    emu::t_block->slots[t] = 0;  // a lane that returns later must not keep voting
+    return r;
+}
+inline int __any_sync(unsigned m, int pred) { return __ballot_sync(m, pred) != 0; }
+inline int __all_sync(unsigned m, int pred) { return __ballot_sync(m, !pred) == 0; }
+// ---- bit helpers ----
+inline int __popc(unsigned v) { return __builtin_popcount(v); }
+inline int __popcll(unsigned long long v) { return __builtin_popcountll(v); }
+inline int __ffs(int v) { return __builtin_ffs(v); }
+inline int __clz(int v) { return v ? __builtin_clz((unsigned)v) : 32; }
+inline unsigned __float_as_uint(float f) { unsigned u; std::memcpy(&u, &f, 4); return u; }
+inline float __uint_as_float(unsigned u) { float f; std::memcpy(&f, &u, 4); return f; }
+inline int __float_as_int(float f) { int u; std::memcpy(&u, &f, 4); return u; }
+inline float __int_as_float(int u) { float f; std::memcpy(&f, &u, 4); return f; }
+template <class T> inline T __ldg(const T *p) { return *p; }
+// ---- atomics (real ones: the emulated threads are OS threads) ----
+template <class T> inline T atomicAdd(T *p, T v) { return __atomic_fetch_add(p, v, __ATOMIC_SEQ_CST); }
+template <class T> inline T atomicExch(T *p, T v) { return __atomic_exchange_n(p, v, __ATOMIC_SEQ_CST); }
+template <class T> inline T atomicCAS(T *p, T cmp, T v) { __atomic_compare_exchange_n(p, &cmp, v, false, __ATOMIC_SEQ_CST, __ATOMIC_SEQ_CST); return cmp; }
+template <class T> inline T atomicMin(T *p, T v)
+{
+    T old = __atomic_load_n(p, __ATOMIC_SEQ_CST);
+    while (v < old && !__atomic_compare_exchange_n(p, &old, v, false, __ATOMIC_SEQ_CST, __ATOMIC_SEQ_CST)) {}
+    return old;
+}
+template <class T> inline T atomicMax(T *p, T v)
+{
+    T old = __atomic_load_n(p, __ATOMIC_SEQ_CST);
+    while (v > old && !__atomic_compare_exchange_n(p, &old, v, false, __ATOMIC_SEQ_CST, __ATOMIC_SEQ_CST)) {}
+    return old;
+}
+inline void __threadfence() { __atomic_thread_fence(__ATOMIC_SEQ_CST); }
+// ---- launch attributes: accepted and ignored ----
+enum cudaFuncAttribute { cudaFuncAttributeMaxDynamicSharedMemorySize };
+template <class K> inline cudaError_t cudaFuncSetAttribute(K, cudaFuncAttribute, int) { return 0; }
+using std::max;
+using std::min;

@@ -8,6 +8,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(os.path.dirname(HERE))
 CSRC = os.path.join(ROOT, "deepreadmapper_b200", "csrc")
 OUT = os.path.join(ROOT, "build", "emu")
+EMULATED = ("embed_kernel.cu", "l2_kernel.cu", "align_kernel.cu", "merge_kernel.cu")
 LAUNCH = re.compile(r"([A-Za-z_]\w*(?:<[^<>;]*>)?)\s*<<<(.*?)>>>\s*\((.*?)\);", re.S)
 
 
@@ -15,17 +16,20 @@ def transform(src: str) -> str:
     def repl(m):
         name, cfg, args = m.group(1), m.group(2), m.group(3)
         parts = [p.strip() for p in cfg.split(",")]
-        return f"emu::launch(dim3({parts[0]}), dim3({parts[1]}), [&] {{ {name}({args}); }});"
+        smem = parts[2] if len(parts) > 2 else "0"
+        return f"emu::launch(dim3({parts[0]}), dim3({parts[1]}), (size_t)({smem}), [&] {{ {name}({args}); }});"
     out, n = LAUNCH.subn(repl, src)
     if n == 0:
         raise SystemExit("no kernel launch found")
+    # dynamic shared memory: `extern __shared__ T name[];` becomes a pointer to the block's buffer
+    out = re.sub(r"extern\s+__shared__\s+([\w ]+?)\s+(\w+)\[\];", r"\1 *\2 = static_cast<\1 *>(emu::dyn_smem());", out)
     return out
 
 
 def build(sanitize=True) -> str:
     os.makedirs(OUT, exist_ok=True)
     srcs = []
-    for f in ("embed_kernel.cu", "l2_kernel.cu"):
+    for f in EMULATED:
         text = transform(open(os.path.join(CSRC, f)).read())
         dst = os.path.join(OUT, f.replace(".cu", "_emu.cpp"))
         with open(dst, "w") as fh:

@@ -29,9 +29,6 @@ void free_device_index(DeviceIndex &) {}
 int launch_search(const DeviceIndex &, const float *, int64_t, int, int, float *, int64_t *, int64_t *, cudaStream_t) { return na("the search kernel"); }
 int launch_rerank(const DeviceRef &, const RerankArgs &, cudaStream_t) { return na("the SW rerank kernel"); }
 int launch_sw_pairs(const char *, const int64_t *, const char *, const int64_t *, int64_t, int, int32_t *, cudaStream_t) { return na("the SW pair kernel"); }
-int launch_merge_topk(const float *, const int64_t *, int, int64_t, int, float *, int64_t *, cudaStream_t) { return na("the merge kernel"); }
-int launch_sw_align(const DeviceRef &, const unsigned long long *, int64_t, int, const char *, const int64_t *, int, int, int, int *, int *, int *,
-                    int *, int *, int *, int *, unsigned *, cudaStream_t) { return na("the traceback kernel"); }
 int clean_fasta_device(const char *, int64_t, int, uint8_t **, int64_t *) { return na("the FASTA kernels"); }
 int parse_fastq_device(const char *, int64_t, int, char **, int64_t **, int64_t *, int64_t *, int *) { return na("the FASTQ kernels"); }
 
