@@ -11,6 +11,13 @@ if ROOT not in sys.path:
 
 def pytest_configure(config):
     config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box with -m gpu)")
+    # tools/cpu_emu: DRM_EMU_LIB=<libdrm_emu*.so> points the Python mirror at the host-thread emulation, so that -m gpu test
+    # files whose kernels are emulated can be run where there is no GPU (tests/test_emu_kernels.py does this in a child)
+    emu = os.environ.get("DRM_EMU_LIB")
+    if emu:
+        import deepreadmapper_b200.api as api
+        api._LIB_PATH = emu
+        api._lib = None
 
 
 @pytest.fixture(scope="session")

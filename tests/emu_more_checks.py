@@ -1,6 +1,6 @@
 """Run by tests/test_emu_kernels.py in a child interpreter whose Python mirror points at the emulated library
-(tools/cpu_emu): the traceback kernel (csrc/align_kernel.cu) and the shard-merge kernel (csrc/merge_kernel.cu) - warp
-shuffles, dynamic shared memory - on host threads, against the oracle / numpy.  Both kernels pass on hardware
+(tools/cpu_emu): the traceback kernel (csrc/align_kernel.cu), the shard-merge kernel (csrc/merge_kernel.cu) and the FASTA /
+FASTQ kernels (csrc/input_kernels.cu) - warp shuffles, atomics, dynamic shared memory - on host threads, against the oracle / numpy.  Both kernels pass on hardware
 (tests/test_gpu_align.py, tests/test_gpu_parity.py::test_merge_topk); here their source additionally runs under
 AddressSanitizer when the sanitised library is preloaded."""
 import os
@@ -80,6 +80,21 @@ def check_merge():
     print("merge kernel ok")
 
 
+def check_input():
+    """csrc/input_kernels.cu (tile counts, hierarchical scan, ordered writes; shuffles, atomics) on two small files."""
+    fasta = b">h with ACGT letters\r\nacgtnRYKM\r\nACGT\r\n>contig2 GATTACA\nTTTTNN"
+    body = fasta[fasta.index(b"\n") + 1:]
+    want = bytes(c for c in body.upper() if c in b"ACGTN")  # extract_FASTA_sequence: first line dropped, the rest filtered
+    assert drm.fasta_clean(fasta) == want, (drm.fasta_clean(fasta), want)
+    fastq = b"@r0 x\nACGTN\n+\nIIIII\n@r1\nGG\n+\nII\n@r2\n\n+\n\n@r3\nTTTTTTTT\n+\nIIIIIIII"
+    lines = fastq.split(b"\n")
+    reads = drm.Reads(fastq)
+    assert reads.sequences() == [b"<" + lines[4 * r + 1] + b">" for r in range(4)], reads.sequences()
+    reads.close()
+    print("input kernels ok")
+
+
 if __name__ == "__main__":
     check_align()
     check_merge()
+    check_input()

@@ -186,7 +186,7 @@ def test_l2_stage_through_the_c_abi_on_the_emulation():
     assert r.returncode == 0 and "device == oracle" in r.stdout, (r.stdout[-1500:], r.stderr[-3000:])
 
 
-def test_align_and_merge_kernels_on_the_emulation_under_asan():
+def test_align_merge_and_input_kernels_on_the_emulation_under_asan():
     """csrc/align_kernel.cu and csrc/merge_kernel.cu (warp shuffles, dynamic shared memory) through the C ABI on host
     threads, AddressSanitizer preloaded: tests/emu_more_checks.py."""
     sys.path.insert(0, os.path.join(ROOT, "tools", "cpu_emu"))
@@ -200,7 +200,7 @@ def test_align_and_merge_kernels_on_the_emulation_under_asan():
         "import deepreadmapper_b200.api as A\n"
         "A._LIB_PATH = %r; A._lib = None\n"
         "import emu_more_checks as M\n"
-        "M.check_align(); M.check_merge()\n" % (ROOT, os.path.join(ROOT, "tests"), lib))
+        "M.check_align(); M.check_merge(); M.check_input()\n" % (ROOT, os.path.join(ROOT, "tests"), lib))
     env = dict(os.environ, LD_PRELOAD=asan, ASAN_OPTIONS="detect_leaks=0:abort_on_error=0")
     r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, env=env, timeout=1500)
-    assert r.returncode == 0 and "align kernel ok" in r.stdout and "merge kernel ok" in r.stdout, (r.stdout[-1500:], r.stderr[-3000:])
+    assert r.returncode == 0 and all(x in r.stdout for x in ("align kernel ok", "merge kernel ok", "input kernels ok")), (r.stdout[-1500:], r.stderr[-3000:])

@@ -40,6 +40,7 @@ inline cudaError_t cudaMemcpy(void *d, const void *s, size_t n, cudaMemcpyKind) 
 inline cudaError_t cudaSetDevice(int) { return 0; }
 inline cudaError_t cudaGetLastError() { return 0; }
 inline cudaError_t cudaStreamSynchronize(cudaStream_t) { return 0; }
+inline cudaError_t cudaDeviceSynchronize() { return 0; }
 inline cudaError_t cudaDeviceGetAttribute(int *v, cudaDeviceAttr, int) { *v = 2; return 0; }  // a 2-SM "device": small passes
 // what the C-ABI layer (api.cu) uses on top: everything synchronous, one "device"
 typedef void *cudaEvent_t;

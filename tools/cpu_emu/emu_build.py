@@ -8,7 +8,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(os.path.dirname(HERE))
 CSRC = os.path.join(ROOT, "deepreadmapper_b200", "csrc")
 OUT = os.path.join(ROOT, "build", "emu")
-EMULATED = ("embed_kernel.cu", "l2_kernel.cu", "align_kernel.cu", "merge_kernel.cu")
+EMULATED = ("embed_kernel.cu", "l2_kernel.cu", "align_kernel.cu", "merge_kernel.cu", "input_kernels.cu")
 LAUNCH = re.compile(r"([A-Za-z_]\w*(?:<[^<>;]*>)?)\s*<<<(.*?)>>>\s*\((.*?)\);", re.S)
 
 

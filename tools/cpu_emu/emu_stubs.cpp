@@ -29,8 +29,6 @@ void free_device_index(DeviceIndex &) {}
 int launch_search(const DeviceIndex &, const float *, int64_t, int, int, float *, int64_t *, int64_t *, cudaStream_t) { return na("the search kernel"); }
 int launch_rerank(const DeviceRef &, const RerankArgs &, cudaStream_t) { return na("the SW rerank kernel"); }
 int launch_sw_pairs(const char *, const int64_t *, const char *, const int64_t *, int64_t, int, int32_t *, cudaStream_t) { return na("the SW pair kernel"); }
-int clean_fasta_device(const char *, int64_t, int, uint8_t **, int64_t *) { return na("the FASTA kernels"); }
-int parse_fastq_device(const char *, int64_t, int, char **, int64_t **, int64_t *, int64_t *, int *) { return na("the FASTQ kernels"); }
 
 }  // namespace drm
 
