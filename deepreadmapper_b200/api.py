@@ -549,6 +549,9 @@ def post_process_l2_dynamic(neighbors, distances, ref: "Reference", query_embedd
     return _post_process_l2(1, vectorizer, ref, neighbors, distances, query_embeddings, stride, k, k_clusters)
 
 
-def post_process_l2_static(neighbors, distances, ref: "Reference", query_embeddings, vectorizer: "Vectorizer", stride, k, k_clusters=5):
-    """post_process_l2_static (src/utils/post_processor.cpp:1023-1162): (scores, ids), k_clusters per query, flat."""
-    return _post_process_l2(0, vectorizer, ref, neighbors, distances, query_embeddings, stride, k, k_clusters)
+def post_process_l2_static(neighbors, distances, ref: "Reference", query_embeddings, vectorizer: "Vectorizer", stride, k, k_clusters=5,
+                           decorated=True):
+    """post_process_l2_static (src/utils/post_processor.cpp:1023-1162): (scores, ids), k_clusters per query, flat.
+    decorated=True: ref_seqs are '<' window '>' strings; False: the bare windows read_file(..., lookup_mode=true) returns, which
+    is what the reference's main passes (src/main.cpp:190) - candidates are then embedded undecorated (device mode 2)."""
+    return _post_process_l2(0 if decorated else 2, vectorizer, ref, neighbors, distances, query_embeddings, stride, k, k_clusters)

@@ -922,7 +922,7 @@ int drm_l2_rerank(drm_embedder *e, drm_ref *ref, int mode, const int64_t *neighb
     if (!out_count) return fail(DRM_EINVAL, "null count output");
     *out_count = 0;
     if (n <= 0) return DRM_OK;
-    if (!neighbors || !distances || !q_emb || !out_scores || !out_ids || (mode != 0 && mode != 1)) return fail(DRM_EINVAL, "bad arguments to drm_l2_rerank");
+    if (!neighbors || !distances || !q_emb || !out_scores || !out_ids || (mode < 0 || mode > 2)) return fail(DRM_EINVAL, "bad arguments to drm_l2_rerank");
     const DeviceRef *dr = ref_on_device(ref, e->dev.device);
     if (!dr) return fail(DRM_EINVAL, "the reference has no replica on the embedder's device");
     if (mode == 1 && dr->form != 0) return fail(DRM_EINVAL, "dynamic mode needs a genome reference (drm_ref_open_genome)");
@@ -931,7 +931,7 @@ int drm_l2_rerank(drm_embedder *e, drm_ref *ref, int mode, const int64_t *neighb
     if (mode == 1 || dr->form == 1) bound = (uint64_t)dr->len;
     else bound = dr->len >= dr->ref_len ? 2ull * (uint64_t)(dr->len - dr->ref_len + 1) : 0;
     L2Plan plan;
-    int rc = l2_plan(mode, neighbors, n, k_in, stride, k, k_clusters, bound, plan);
+    int rc = l2_plan(mode == 2 ? 0 : mode, neighbors, n, k_in, stride, k, k_clusters, bound, plan);  // mode 2 = static bookkeeping, bare windows
     if (rc != DRM_OK) return rc;
     if (plan.passthrough) {
         for (int64_t q = 0; q < n; ++q)
@@ -957,7 +957,7 @@ int drm_l2_rerank(drm_embedder *e, drm_ref *ref, int mode, const int64_t *neighb
     EmbedSource src;
     src.mode = 1; src.cls = dr->data; src.form = dr->form; src.ref_n = dr->len; src.ref_len = dr->ref_len;
     src.ids = d_ids.as<unsigned long long>();
-    src.decorate = mode == 0 ? 1 : 0;  // ref_seqs hold '<' window '>' strings; find_sequence returns the bare window
+    src.decorate = mode == 0 ? 1 : 0;  // mode 0: ref_seqs hold '<' window '>' strings; find_sequence (1) and lookup-mode tables (2) give bare windows
     if ((rc = launch_embed(e->dev, src, 0, U, d_emb.as<float>(), 0)) != DRM_OK) return rc;
     if ((rc = launch_l2_rerank(d_emb.as<float>(), d_map.as<uint32_t>(), d_starts.as<int64_t>(), d_q.as<float>(), n, (int)ko, d_dist.as<float>(),
                                d_idx.as<int64_t>(), d_od.as<float>(), d_or.as<uint32_t>(), d_cnt.as<int64_t>(), 0)) != DRM_OK) return rc;

@@ -125,6 +125,12 @@ void post_process_sw_flat(int mode, const std::string &genome, size_t ref_len, c
                           const std::vector<std::string> &query_seqs, size_t stride, size_t k, size_t k_clusters, std::vector<int> &scores,
                           std::vector<size_t> &ids);
 
+// Flat L2 rerank for the pipeline (DRM_RERANK=l2): mode 1 = post_process_l2_dynamic over `genome`, mode 0 =
+// post_process_l2_static over `ref_windows` (bare lookup-mode windows, or '<' window '>' strings).  dists / ids are flat, like the reference's final vectors.
+void post_process_l2_flat(int mode, const std::string &genome, const std::vector<std::string> &ref_windows, size_t ref_len,
+                          const std::vector<faiss::idx_t> &I, const std::vector<float> &D, int64_t n, int64_t k_in, const float *q_emb,
+                          Vectorizer &vectorizer, size_t stride, size_t k, size_t k_clusters, std::vector<float> &dists, std::vector<size_t> &ids);
+
 // ---- parse_inputs
 std::string reverse_complement(const std::string &seq);
 std::string extract_FASTA_sequence(const std::string &fasta_file);

@@ -6,6 +6,8 @@
 //   formats_tool genome <path> <out.txt>
 //   formats_tool config <config_in.txt> <folder_out>        (load_config -> save_config)
 //   formats_tool npyinfo <file.npy>
+//   formats_tool l2flat <mode 0|1> <ref: FASTA (mode 1) | window file for read_file (mode 0)> <ref_len> <I.npy i8> <D.npy f4> <Q.npy f4>
+//                <stride> <k> <k_clusters> <dists_out.npy> <ids_out.npy>     (pipeline's DRM_RERANK=l2 stage; model = $DRM_MODEL)
 #include <fstream>
 #include <iostream>
 #include <sstream>
@@ -58,6 +60,30 @@ int main(int argc, char *argv[])
             std::cout << a.kind << a.word_size << " fortran=" << a.fortran_order << " shape=";
             for (size_t s : a.shape) std::cout << s << ",";
             std::cout << " bytes=" << a.data.size() << std::endl;
+            return 0;
+        }
+        if (cmd == "l2flat" && argc == 13) {
+            const int mode = std::stoi(argv[2]);
+            const size_t ref_len = std::stoull(argv[4]);
+            const npy::Array ia = npy::load(argv[5]), da = npy::load(argv[6]), qa = npy::load(argv[7]);
+            if (ia.shape.size() != 2 || ia.shape != da.shape || qa.shape.size() != 2 || qa.shape[0] != ia.shape[0] || ia.word_size != 8 || da.word_size != 4)
+                throw std::runtime_error("l2flat: I (n x k_in, i8), D (n x k_in, f4), Q (n x 128, f4)");
+            const faiss::idx_t *ip = reinterpret_cast<const faiss::idx_t *>(ia.data.data());
+            const float *dp = reinterpret_cast<const float *>(da.data.data());
+            std::vector<faiss::idx_t> I(ip, ip + ia.shape[0] * ia.shape[1]);
+            std::vector<float> D(dp, dp + I.size());
+            std::string genome;
+            std::vector<std::string> windows;
+            if (mode == 1) genome = extract_FASTA_sequence(argv[3]);
+            else windows = read_file(argv[3], ref_len, 1, true).first;
+            Vectorizer vectorizer(embedder_model_path());
+            std::vector<float> dists;
+            std::vector<size_t> ids;
+            post_process_l2_flat(mode, genome, windows, ref_len, I, D, (int64_t)ia.shape[0], (int64_t)ia.shape[1],
+                                 reinterpret_cast<const float *>(qa.data.data()), vectorizer, std::stoull(argv[8]), std::stoull(argv[9]),
+                                 std::stoull(argv[10]), dists, ids);
+            npy::save(argv[11], dists.data(), {dists.size()});
+            npy::save(argv[12], ids.data(), {ids.size()});
             return 0;
         }
         std::cerr << "usage: see the header of formats_tool.cpp" << std::endl;

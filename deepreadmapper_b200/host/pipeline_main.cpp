@@ -12,7 +12,10 @@
 //     behaviour;
 //   * the rerank is the Smith-Waterman variant the reference has implemented but commented out (src/main.cpp:333-341);
 //     its result goes to NEW files sw_scores.npy ('<i4', n x K) and sw_indices.npy ('<u8', n x K); DRM_RERANK=none skips it;
-//   * both modes rerank from the cleaned genome on the device: use_dynamic=0 applies the static bound rule (number of
+//   * DRM_RERANK=l2 runs the reference's ACTIVE post-process instead (post_process_l2_dynamic / _static, src/main.cpp:313-331)
+//     over drm_l2_rerank: candidate windows embedded and ranked by L2 distance on the device; result in NEW flat files
+//     l2_distances.npy ('<f4') and l2_indices.npy ('<u8'), laid out like the reference's final_dists / final_ids;
+//   * both SW modes rerank from the cleaned genome on the device: use_dynamic=0 applies the static bound rule (number of
 //     dense windows), use_dynamic=1 the dynamic one (genome length) - the two rules of find_sequences.
 #include <chrono>
 #include <cstdlib>
@@ -63,6 +66,9 @@ int main(int argc, char *argv[])
         const bool use_dynamic = argc >= 9 ? std::stoi(argv[8]) != 0 : false;
         const char *rr = getenv("DRM_RERANK");
         const bool rerank = !(rr && !strcmp(rr, "none"));
+        // DRM_RERANK=l2: the reference's active post-process (post_process_l2_dynamic / _static, src/main.cpp:313-331) on the
+        // device instead of the Smith-Waterman rerank its main keeps commented out (src/main.cpp:333-341)
+        const bool rerank_l2 = rr && !strcmp(rr, "l2");
 
         std::cout << "[MAIN] PIPELINE CONFIG:" << std::endl;
         std::cout << "[MAIN] Input file: " << query_input_file << std::endl;
@@ -78,7 +84,7 @@ int main(int argc, char *argv[])
         // reference's host parsing and the two separate stages).
         const std::string qext = std::filesystem::path(query_input_file).extension().string();
         const char *input_mode = getenv("DRM_INPUT");
-        const bool device_inputs = !is_npy && rerank && (qext == ".fastq" || qext == ".fq") && !(input_mode && !strcmp(input_mode, "host"));
+        const bool device_inputs = !is_npy && rerank && !rerank_l2 && (qext == ".fastq" || qext == ".fq") && !(input_mode && !strcmp(input_mode, "host"));
         if (!is_npy) {
             if (!device_inputs) {
                 std::tie(query_sequences, query_ids) = read_file(query_input_file);
@@ -122,7 +128,12 @@ int main(int argc, char *argv[])
         }
         if (!is_npy && !device_inputs && query_sequences.size() != num_queries) throw std::runtime_error("Error: number of embeddings differs from the number of query sequences");
         std::string ref_genome;
-        if (device_inputs) {
+        std::vector<std::string> ref_sequences;
+        if (rerank_l2 && !is_npy && !use_dynamic) {
+            std::cout << "[MAIN] Using STATIC fetching for reference sequences" << std::endl;
+            ref_sequences = read_file(ref_seqs_file, ref_len, 1, true).first;
+            std::cout << "[MAIN] Loaded " << ref_sequences.size() << " reference sequences from " << ref_seqs_file << std::endl;
+        } else if (device_inputs) {
             std::cout << "[MAIN] Reads and reference are parsed on the device (" << (use_dynamic ? "DYNAMIC" : "STATIC") << " bound rule)" << std::endl;
         } else if (!is_npy && rerank) {
             std::cout << "[MAIN] Using " << (use_dynamic ? "DYNAMIC" : "STATIC") << " fetching for reference sequences" << std::endl;
@@ -148,6 +159,8 @@ int main(int argc, char *argv[])
         std::vector<float> D;
         std::vector<int> sw_scores;
         std::vector<size_t> sw_ids;
+        std::vector<float> l2_dists;
+        std::vector<size_t> l2_ids;
         if (device_inputs) {
             stage_device_inputs(alg_hnsw, query_input_file, ref_seqs_file, emb, (int64_t)num_queries,
                                 (int)dim, k_clusters, ef, use_dynamic ? 1 : 0, ref_len, stride, (size_t)k, (size_t)k_clusters, I, D, sw_scores, sw_ids);
@@ -163,6 +176,13 @@ int main(int argc, char *argv[])
         t0 = Clock::now();
         if (device_inputs) {
             std::cout << "[MAIN] Post-processing ran inside the search call" << std::endl;
+        } else if (!is_npy && rerank_l2) {
+            const std::string model_path = embedder_model_path();
+            if (!std::filesystem::exists(model_path)) throw std::runtime_error("DRM_RERANK=l2 needs the embedder model (" + model_path + "; set DRM_MODEL=<model.xml>)");
+            Vectorizer vectorizer(model_path);
+            post_process_l2_flat(use_dynamic ? 1 : 0, ref_genome, ref_sequences, ref_len, I, D, (int64_t)num_queries, k_clusters, emb, vectorizer, stride,
+                                 (size_t)k, (size_t)k_clusters, l2_dists, l2_ids);
+            std::cout << "[MAIN] L2 rerank: " << l2_ids.size() << " final candidates" << std::endl;
         } else if (!is_npy && rerank) {
             post_process_sw_flat(use_dynamic ? 1 : 0, ref_genome, ref_len, I, (int64_t)num_queries, k_clusters, query_sequences, stride, (size_t)k,
                                  (size_t)k_clusters, sw_scores, sw_ids);
@@ -183,6 +203,10 @@ int main(int argc, char *argv[])
         if (!sw_scores.empty()) {
             npy::save(output_dir + "/sw_scores.npy", sw_scores.data(), {num_queries, (size_t)k});
             npy::save(output_dir + "/sw_indices.npy", sw_ids.data(), {num_queries, (size_t)k});
+        }
+        if (!l2_ids.empty()) {  // flat, like the reference's final_dists / final_ids (queries without candidates contribute nothing)
+            npy::save(output_dir + "/l2_distances.npy", l2_dists.data(), {l2_dists.size()});
+            npy::save(output_dir + "/l2_indices.npy", l2_ids.data(), {l2_ids.size()});
         }
         // SAM with real alignments (the reference's write_sam call is commented out, src/main.cpp:395): DRM_SAM=<n> writes the
         // first n reranked windows of every read to <output_dir>/alignments.sam.

@@ -495,11 +495,13 @@ std::tuple<std::vector<std::string>, std::vector<float>, std::vector<size_t>> po
     const std::vector<std::string> &ref_seqs, const std::vector<std::string> &, size_t ref_len, size_t stride, size_t k,
     const std::vector<std::vector<float>> &query_embeddings, Vectorizer &vectorizer, size_t k_clusters)
 {
-    // ref_seqs are the '<' window '>' strings read_file returns; the device table holds the bare windows and the embedder
-    // puts the decoration back
+    // ref_seqs are either the '<' window '>' strings read_file returns (the device table holds the bare windows and the embedder
+    // puts the decoration back: device mode 0) or the bare windows of read_file(..., lookup_mode = true), which the reference's
+    // main passes (src/main.cpp:190) and embeds as they are: device mode 2
+    const bool lookup_windows = !ref_seqs.empty() && ref_seqs[0].size() == ref_len;
     static std::vector<std::string> bare;
     static const void *bare_key = nullptr;
-    if (bare_key != ref_seqs.data() || bare.size() != ref_seqs.size()) {
+    if (!lookup_windows && (bare_key != ref_seqs.data() || bare.size() != ref_seqs.size())) {
         bare.resize(ref_seqs.size());
         for (size_t i = 0; i < ref_seqs.size(); ++i) {
             const std::string &s = ref_seqs[i];
@@ -515,13 +517,52 @@ std::tuple<std::vector<std::string>, std::vector<float>, std::vector<size_t>> po
     std::vector<float> scores((size_t)n * std::max(k, k_clusters) + 1);
     std::vector<uint64_t> ids(scores.size());
     int64_t count = 0;
-    if (n && drm_l2_rerank(vectorizer.handle(), table_ref(bare, ref_len), 0, nb.data(), ds.data(), n, k_in, qe.data(), (int64_t)stride, (int64_t)k,
+    if (n && drm_l2_rerank(vectorizer.handle(), table_ref(lookup_windows ? ref_seqs : bare, ref_len), lookup_windows ? 2 : 0, nb.data(), ds.data(), n, k_in, qe.data(), (int64_t)stride, (int64_t)k,
                            (int64_t)k_clusters, scores.data(), ids.data(), &count) != DRM_OK)
         throw_last();
     std::vector<std::string> seqs((size_t)count);
     for (int64_t i = 0; i < count; ++i) seqs[(size_t)i] = ref_seqs[(size_t)ids[(size_t)i]];
     scores.resize((size_t)count);
     return {std::move(seqs), std::move(scores), std::vector<size_t>(ids.begin(), ids.begin() + count)};
+}
+
+// Flat form for `pipeline` (DRM_RERANK=l2): the reference's main calls post_process_l2_dynamic / _static right after the
+// search (src/main.cpp:313-331).  mode 1 = dynamic over the cleaned genome, mode 0 = static over the window table
+// that read_file(ref_seqs_file, ref_len, 1, true) returns (bare windows, embedded undecorated like the reference does).  Output is flat like the reference's final vectors.
+void post_process_l2_flat(int mode, const std::string &genome, const std::vector<std::string> &ref_windows, size_t ref_len,
+                          const std::vector<faiss::idx_t> &I, const std::vector<float> &D, int64_t n, int64_t k_in, const float *q_emb,
+                          Vectorizer &vectorizer, size_t stride, size_t k, size_t k_clusters, std::vector<float> &dists, std::vector<size_t> &ids)
+{
+    static std::vector<std::string> bare;
+    drm_ref *ref = nullptr;
+    if (mode == 1) {
+        ref = genome_ref(genome, ref_len);
+    } else {
+        // read_file(..., lookup_mode = true) - what the reference's main passes (src/main.cpp:190) - returns bare windows, which
+        // the reference then embeds as they are: device mode 2.  A decorated table ('<' window '>') is device mode 0.
+        const bool decorated = !ref_windows.empty() && ref_windows[0].size() == ref_len + 2;
+        if (decorated) {
+            bare.resize(ref_windows.size());
+            for (size_t i = 0; i < ref_windows.size(); ++i) {
+                const std::string &s = ref_windows[i];
+                if (s.size() != ref_len + 2 || s.front() != '<' || s.back() != '>')
+                    throw std::runtime_error("post_process_l2_static: reference sequences must be '<' + ref_len bases + '>'");
+                bare[i] = s.substr(1, ref_len);
+            }
+            ref = table_ref(bare, ref_len);
+        } else {
+            ref = table_ref(ref_windows, ref_len);
+            mode = 2;
+        }
+    }
+    dists.assign((size_t)n * std::max(k, k_clusters) + 1, 0.0f);
+    std::vector<uint64_t> u(dists.size());
+    int64_t count = 0;
+    if (n && drm_l2_rerank(vectorizer.handle(), ref, mode, I.data(), D.data(), n, k_in, q_emb, (int64_t)stride, (int64_t)k, (int64_t)k_clusters,
+                           dists.data(), u.data(), &count) != DRM_OK)
+        throw_last();
+    dists.resize((size_t)count);
+    ids.assign(u.begin(), u.begin() + count);
 }
 
 // explicit instantiations, as src/utils/post_processor.cpp:1176-1187

@@ -215,6 +215,9 @@ int drm_embed_windows_device(drm_embedder *e, const drm_ref *ref, uint64_t first
  * nothing; capacity n * max(k, k_clusters); *out_count = values written.  On a dense index (stride 1) the dynamic
  * variant passes the first k search results through, like the reference.  The reference's flat slice arithmetic is kept
  * (DESIGN.md); inputs for which it would read past its candidate list are refused with DRM_EINVAL.
+ * mode 2 = the static variant over BARE windows: the reference's own callers hand post_process_l2_static the table
+ * read_file(ref_seqs_file, ref_len, 1, lookup_mode = true) returns (src/main.cpp:190, src/test_postprocess.cpp:139), whose
+ * strings carry no '<' '>' (src/utils/parse_inputs.cpp:345-349), so candidates are embedded undecorated.
  * STATUS: verified against the oracle on a host-thread emulation of these sources (tools/cpu_emu); not yet timed. */
 int drm_l2_rerank(drm_embedder *e, drm_ref *ref, int mode, const int64_t *neighbors, const float *distances, int64_t n, int64_t k_in,
                   const float *q_emb, int64_t stride, int64_t k, int64_t k_clusters, float *out_scores, uint64_t *out_ids,

@@ -186,6 +186,25 @@ def test_l2_stage_through_the_c_abi_on_the_emulation():
     assert r.returncode == 0 and "device == oracle" in r.stdout, (r.stdout[-1500:], r.stderr[-3000:])
 
 
+def test_pipeline_l2_stage_host_code_on_the_emulation():
+    """tests/l2_pipeline_check.py on the emulated library: the C++ host code behind `pipeline`'s DRM_RERANK=l2
+    (post_process_l2_flat via `formats_tool l2flat`, LD_PRELOAD = the emulation) equals the oracle bit for bit, dynamic and
+    static (bare lookup-mode windows, device mode 2)."""
+    if not os.path.exists(os.path.join(ROOT, "build", "bin", "formats_tool")):
+        pytest.skip("host binaries not built (python -c 'import __graft_entry__ as g; g.build()')")
+    sys.path.insert(0, os.path.join(ROOT, "tools", "cpu_emu"))
+    import emu_build
+    lib = emu_build.build(sanitize=False)
+    code = (
+        "import sys; sys.path.insert(0, %r); sys.path.insert(0, %r)\n"
+        "import deepreadmapper_b200.api as A\n"
+        "A._LIB_PATH = %r; A._lib = None\n"
+        "import l2_pipeline_check\n"
+        "l2_pipeline_check.main(4, %r)\n" % (ROOT, os.path.join(ROOT, "tests"), lib, lib))
+    r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=1500)
+    assert r.returncode == 0 and "host code == oracle" in r.stdout, (r.stdout[-1500:], r.stderr[-3000:])
+
+
 def test_align_merge_and_input_kernels_on_the_emulation_under_asan():
     """csrc/align_kernel.cu and csrc/merge_kernel.cu (warp shuffles, dynamic shared memory) through the C ABI on host
     threads, AddressSanitizer preloaded: tests/emu_more_checks.py."""

@@ -19,3 +19,13 @@ def test_l2_rerank_stage_against_oracle():
     print(r.stdout[-2000:])
     print(r.stderr[-4000:])
     assert r.returncode == 0 and "device == oracle" in r.stdout, r.stderr[-2000:]
+
+
+def test_pipeline_l2_stage_host_code_against_oracle():
+    """post_process_l2_flat (what `pipeline` runs under DRM_RERANK=l2) through `formats_tool l2flat`: dynamic over a FASTA
+    genome, static over the bare lookup-mode window table (device mode 2).  Same child-process arrangement."""
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, os.path.join(root, "tests", "l2_pipeline_check.py")], capture_output=True, text=True, timeout=300)
+    print(r.stdout[-2000:])
+    print(r.stderr[-4000:])
+    assert r.returncode == 0 and "host code == oracle" in r.stdout, r.stderr[-2000:]
