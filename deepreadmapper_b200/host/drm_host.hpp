@@ -140,6 +140,9 @@ std::pair<std::vector<std::string>, std::vector<std::string>> read_file(const st
 std::string find_sequence(const std::string &ref_genome, size_t id, size_t ref_len);
 
 // ---- utils
+// write_sam (src/utils/utils.cpp:336-403): the reference's writer with its pseudo MAPQ / CIGAR; n_results = final_seqs.size().
+void write_sam(size_t n_results, const std::vector<std::string> &query_seqs, const std::vector<std::string> &query_ids,
+               const std::vector<size_t> &sequence_ids, const std::string &ref_name, int ref_len, size_t k, const std::string &output_file);
 using ConfigValue = std::variant<size_t, float, std::string>;
 int save_config(const std::unordered_map<std::string, ConfigValue> &config, const std::string &folder_path, const std::string &config_file = "config.txt");
 std::unordered_map<std::string, ConfigValue> load_config(const std::string &config_file);

@@ -329,3 +329,29 @@ std::pair<std::vector<std::string>, std::vector<std::string>> read_file(const st
     }
     return {std::move(lines), {}};
 }
+
+// ------------------------------------------------------------------------------------------ write_sam
+// The reference's SAM writer (src/utils/utils.cpp:336-403; write_sam_streaming :405-503 writes the same lines batch by
+// batch): one line per (query, rank) with FLAG = secondary (256) from rank 1 on | reverse strand (16) for odd dense ids,
+// POS = id / 2 + 1, and the reference's pseudo fields - MAPQ 60, CIGAR "<read length>M", no mate, QUAL "*".
+// `n_results` is final_seqs.size() there: ranks past it are not written.
+void write_sam(size_t n_results, const std::vector<std::string> &query_seqs, const std::vector<std::string> &query_ids,
+               const std::vector<size_t> &sequence_ids, const std::string &ref_name, int ref_len, size_t k, const std::string &output_file)
+{
+    std::ofstream out(output_file, std::ios::binary);
+    std::string buf = "@HD\tVN:1.0\tSO:unsorted\n@SQ\tSN:" + ref_name + "\tLN:" + std::to_string(ref_len) + "\n";
+    for (size_t q = 0; q < query_seqs.size(); ++q) {
+        const std::string &raw = query_seqs[q];
+        const std::string read = raw.size() > 2 ? raw.substr(1, raw.size() - 2) : raw;  // '<' ... '>' off
+        const std::string name = q < query_ids.size() && !query_ids[q].empty() ? query_ids[q] : "S1/" + std::to_string(q + 1) + "/0";
+        const std::string tail = "\t60\t" + std::to_string(read.size()) + "M\t*\t0\t0\t" + read + "\t*\n";
+        for (size_t r = 0; r < k && q * k + r < n_results; ++r) {
+            const size_t id = sequence_ids[q * k + r];
+            const int flag = (r ? 256 : 0) | (id & 1 ? 16 : 0);
+            buf += name; buf += '\t'; buf += std::to_string(flag); buf += '\t'; buf += ref_name; buf += '\t';
+            buf += std::to_string(id / 2 + 1); buf += tail;
+        }
+        if (buf.size() > (1u << 20)) { out.write(buf.data(), (std::streamsize)buf.size()); buf.clear(); }
+    }
+    out.write(buf.data(), (std::streamsize)buf.size());
+}

@@ -6,6 +6,7 @@
 //   formats_tool genome <path> <out.txt>
 //   formats_tool config <config_in.txt> <folder_out>        (load_config -> save_config)
 //   formats_tool npyinfo <file.npy>
+//   formats_tool sam <reads.fastq> <ids.bin u64> <n_results> <ref_name> <ref_len> <k> <out.sam>      (write_sam)
 //   formats_tool l2flat <mode 0|1> <ref: FASTA (mode 1) | window file for read_file (mode 0)> <ref_len> <I.npy i8> <D.npy f4> <Q.npy f4>
 //                <stride> <k> <k_clusters> <dists_out.npy> <ids_out.npy>     (pipeline's DRM_RERANK=l2 stage; model = $DRM_MODEL)
 #include <fstream>
@@ -60,6 +61,13 @@ int main(int argc, char *argv[])
             std::cout << a.kind << a.word_size << " fortran=" << a.fortran_order << " shape=";
             for (size_t s : a.shape) std::cout << s << ",";
             std::cout << " bytes=" << a.data.size() << std::endl;
+            return 0;
+        }
+        if (cmd == "sam" && argc == 9) {
+            auto [seqs, names] = read_file(argv[2]);
+            const auto ib = slurp_bin(argv[3]);
+            const size_t *ip = reinterpret_cast<const size_t *>(ib.data());
+            write_sam(std::stoull(argv[4]), seqs, names, std::vector<size_t>(ip, ip + ib.size() / 8), argv[5], std::stoi(argv[6]), std::stoull(argv[7]), argv[8]);
             return 0;
         }
         if (cmd == "l2flat" && argc == 13) {

@@ -41,7 +41,7 @@ int main(int argc, char *argv[])
         std::cerr << "  - K: Optional number of nearest neighbors to return (default: " << Config::Search::K << ")" << std::endl;
         std::cerr << "  - output_dir: Optional output directory (default: current directory)" << std::endl;
         std::cerr << "  - use_dynamic: Optional flag to load reference sequences dynamically (1) or statically (0). Default: 0" << std::endl;
-        std::cerr << "  - use_streaming: accepted for compatibility; SAM streaming belongs to the L2 rerank, which is out of scope" << std::endl;
+        std::cerr << "  - use_streaming: with DRM_RERANK=l2 and use_dynamic=1, writes <output_dir>/results.sam instead of the .npy files (1). Default: 0" << std::endl;
         return 1;
     }
     try {
@@ -64,6 +64,7 @@ int main(int argc, char *argv[])
         else if (argc >= 7) k_clusters = std::stoi(argv[6]);
         const std::string output_dir = argc >= 8 ? argv[7] : ".";
         const bool use_dynamic = argc >= 9 ? std::stoi(argv[8]) != 0 : false;
+        const bool use_streaming = argc >= 10 ? std::stoi(argv[9]) != 0 : false;
         const char *rr = getenv("DRM_RERANK");
         const bool rerank = !(rr && !strcmp(rr, "none"));
         // DRM_RERANK=l2: the reference's active post-process (post_process_l2_dynamic / _static, src/main.cpp:313-331) on the
@@ -195,7 +196,16 @@ int main(int argc, char *argv[])
         std::cout << "[MAIN] OUTPUT SAVING STEP" << std::endl;
         t0 = Clock::now();
         std::filesystem::create_directories(output_dir);
-        {
+        // post_process_l2_dynamic_streaming (src/main.cpp:316-320, :408-411): the L2 result goes to results.sam in the reference's
+        // write_sam format and the normal output saving is skipped.  (The reference rewrites the file batch by batch; the lines
+        // are the same.)
+        const bool sam_only = rerank_l2 && use_dynamic && use_streaming && !is_npy;
+        if (sam_only) {
+            const std::string sam_file = output_dir + "/results.sam";
+            std::cout << "[MAIN] Using STREAMING output to SAM file: " << sam_file << std::endl;
+            write_sam(l2_ids.size(), query_sequences, query_ids, l2_ids, "ref", (int)ref_len, (size_t)k, sam_file);
+            std::cout << "[MAIN] Skip normal output saving since streaming output is used." << std::endl;
+        } else {
             std::vector<size_t> u(I.begin(), I.end());  // long -> size_t: -1 becomes 2^64-1 (src/utils/utils.cpp:323-330)
             npy::save(output_dir + "/indices.npy", u.data(), {num_queries, (size_t)k_clusters});
             npy::save(output_dir + "/distances.npy", D.data(), {num_queries, (size_t)k_clusters});
@@ -204,7 +214,7 @@ int main(int argc, char *argv[])
             npy::save(output_dir + "/sw_scores.npy", sw_scores.data(), {num_queries, (size_t)k});
             npy::save(output_dir + "/sw_indices.npy", sw_ids.data(), {num_queries, (size_t)k});
         }
-        if (!l2_ids.empty()) {  // flat, like the reference's final_dists / final_ids (queries without candidates contribute nothing)
+        if (!l2_ids.empty() && !sam_only) {  // flat, like the reference's final_dists / final_ids (queries without candidates contribute nothing)
             npy::save(output_dir + "/l2_distances.npy", l2_dists.data(), {l2_dists.size()});
             npy::save(output_dir + "/l2_indices.npy", l2_ids.data(), {l2_ids.size()});
         }

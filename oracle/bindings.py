@@ -120,6 +120,9 @@ def ref():
                                            C.POINTER(C.c_int64), C.POINTER(C.c_int64), C.POINTER(C.c_int64)]
         L.ref_save_results.restype = C.c_int
         L.ref_save_results.argtypes = [_i64p, _f32p, C.c_int64, C.c_int64, C.c_int64, C.c_char_p, C.c_char_p]
+        if hasattr(L, "ref_write_sam"):
+            L.ref_write_sam.restype = C.c_int
+            L.ref_write_sam.argtypes = [C.c_char_p, C.c_void_p, C.c_int64, C.c_int64, C.c_char_p, C.c_int, C.c_int64, C.c_char_p]
         L.ref_save_config.restype = C.c_int
         L.ref_save_config.argtypes = [C.c_char_p] + [C.c_uint64] * 8 + [C.c_char_p]
         L.ref_load_config_size.restype = C.c_int64

@@ -227,6 +227,20 @@ int ref_save_results(const int64_t *neighbors, const float *distances, int64_t n
     } catch (const std::exception &e) { g_err = e.what(); return -1; }
 }
 
+// write_sam (src/utils/utils.cpp:336-403) on the reads of a FASTQ file parsed by the reference's own read_file.
+int ref_write_sam(const char *fastq, const uint64_t *ids, int64_t n_ids, int64_t n_results, const char *ref_name, int ref_len, int64_t k,
+                  const char *out_file)
+{
+    try {
+        auto [seqs, names] = read_file(fastq);
+        std::vector<std::string> final_seqs((size_t)n_results);
+        std::vector<float> final_scores((size_t)n_results, 0.0f);
+        std::vector<size_t> sequence_ids(ids, ids + n_ids);
+        write_sam(final_seqs, final_scores, seqs, names, sequence_ids, ref_name, ref_len, (size_t)k, out_file);
+        return 0;
+    } catch (const std::exception &e) { g_err = e.what(); return -1; }
+}
+
 // Writes the key set hnswpq_index writes (src/hnswpq/index.cpp:289-302) through the reference's save_config.
 int ref_save_config(const char *folder, uint64_t stride, uint64_t ref_len, uint64_t n_vects, uint64_t dim,
                     uint64_t M_hnsw, uint64_t EFC, uint64_t M_pq, uint64_t nbits, const char *index_file)

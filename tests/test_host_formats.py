@@ -54,6 +54,28 @@ def test_save_results_files_are_byte_identical_to_the_reference(tool, R, tmp_pat
         assert np.array_equal(np.load(mine[1]), D[:, :k])
 
 
+def test_sam_file_is_byte_identical_to_the_reference(tool, R, tmp_path):
+    """write_sam (src/utils/utils.cpp:336-403): FLAG / POS from the dense id, pseudo MAPQ and CIGAR, '<' '>' stripped from
+    SEQ, FASTQ names as QNAME; fewer results than n x k cut the tail; an empty result list leaves the header only."""
+    if not hasattr(R, "ref_write_sam"):
+        pytest.skip("oracle/_ref predates ref_write_sam (rebuild with /root/reference present)")
+    rng = np.random.default_rng(5)
+    fq = tmp_path / "reads.fastq"
+    with open(fq, "w") as f:
+        for i, ln in enumerate([150, 150, 97, 1, 151, 150, 33]):
+            f.write("@read%d extra words\n%s\n+\n%s\n" % (i, "".join(rng.choice(list("ACGTN"), ln)), "I" * ln))
+    n = 7
+    for k, n_results in [(4, 28), (1, 7), (5, 23), (3, 0), (2, 14)]:
+        ids = rng.integers(0, 2 * 10 ** 7, n * k).astype(np.uint64)
+        ids.tofile(tmp_path / "ids.bin")
+        mine, ref = str(tmp_path / "mine.sam"), str(tmp_path / "ref.sam")
+        subprocess.check_call([tool, "sam", str(fq), str(tmp_path / "ids.bin"), str(n_results), "ref", "150", str(k), mine], stdout=subprocess.DEVNULL)
+        assert R.ref_write_sam(str(fq).encode(), ids.ctypes.data, len(ids), n_results, b"ref", 150, k, ref.encode()) == 0
+        a, b = open(mine, "rb").read(), open(ref, "rb").read()
+        assert a == b, (k, n_results)
+        assert a.count(b"\n") == 2 + min(n_results, n * k)
+
+
 def test_npy_reader_accepts_numpy_and_cnpy_headers(tool, tmp_path):
     a = np.arange(24, dtype=np.float32).reshape(6, 4)
     np.save(tmp_path / "a.npy", a)
