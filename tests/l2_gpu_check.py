@@ -78,6 +78,13 @@ def main(n=23):
     s, i = drm.post_process_l2_static(nb, dist, table, q_emb, v, 1, 5, 5)
     s0, i0 = L2.post_process_l2_static(nb, dist, ref_seqs[:900], ref_len, 1, 5, 5, q_emb, embed_fn)
     assert same(i, i0) and same(s, s0), "static table"
+    # ... and the same table the way the reference's main loads it (read_file in lookup mode: bare windows, embedded undecorated)
+    bare_seqs = [x[1:-1] for x in ref_seqs[:900]]
+    s, i = drm.post_process_l2_static(nb, dist, table, q_emb, v, 1, 5, 5, decorated=False)
+    s0, i0 = L2.post_process_l2_static(nb, dist, bare_seqs, ref_len, 1, 5, 5, q_emb, embed_fn)
+    assert same(i, i0) and same(s, s0), "static table, bare windows (mode 2)"
+    sd, _ = drm.post_process_l2_static(nb, dist, table, q_emb, v, 1, 5, 5)
+    assert not same(s, sd), "decoration must change the embeddings"
     print("L2 rerank stage: device == oracle")
 
 
