@@ -549,6 +549,8 @@ void post_process_l2_flat(int mode, const std::string &genome, const std::vector
                     throw std::runtime_error("post_process_l2_static: reference sequences must be '<' + ref_len bases + '>'");
                 bare[i] = s.substr(1, ref_len);
             }
+            // `bare` is reused between calls, so its address says nothing about its content: drop the cached device table
+            if (g_ref.h && g_ref.form == 1 && g_ref.key == bare.data()) { drm_ref_close(g_ref.h); g_ref.h = nullptr; }
             ref = table_ref(bare, ref_len);
         } else {
             ref = table_ref(ref_windows, ref_len);
