@@ -11,7 +11,7 @@ BINDIR    := build/bin
 OBJDIR    := build/obj
 
 LIB       := $(LIBDIR)/libdrm_cuda.so
-CU_SRCS   := $(CSRC)/api.cu $(CSRC)/search_kernel.cu $(CSRC)/sw_kernel.cu $(CSRC)/merge_kernel.cu $(CSRC)/index_image.cu $(CSRC)/build_gpu.cu $(CSRC)/input_kernels.cu $(CSRC)/align_kernel.cu $(CSRC)/embed_kernel.cu $(CSRC)/l2_kernel.cu
+CU_SRCS   := $(CSRC)/api.cu $(CSRC)/search_kernel.cu $(CSRC)/search_exact.cu $(CSRC)/sw_kernel.cu $(CSRC)/merge_kernel.cu $(CSRC)/shards.cu $(CSRC)/index_image.cu $(CSRC)/build_gpu.cu $(CSRC)/input_kernels.cu $(CSRC)/align_kernel.cu $(CSRC)/embed_kernel.cu $(CSRC)/l2_kernel.cu
 CPP_SRCS  := $(CSRC)/index_io.cpp $(CSRC)/builder.cpp $(CSRC)/ir_model.cpp $(CSRC)/l2_plan.cpp
 CU_OBJS   := $(patsubst $(CSRC)/%.cu,$(OBJDIR)/%.o,$(CU_SRCS))
 CPP_OBJS  := $(patsubst $(CSRC)/%.cpp,$(OBJDIR)/%.o,$(CPP_SRCS))

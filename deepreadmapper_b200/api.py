@@ -37,7 +37,18 @@ EXPORTS = ["drm_last_error", "drm_device_count", "drm_version", "drm_index_open"
            "drm_reads_open_fastq", "drm_reads_close", "drm_reads_info", "drm_reads_copy_out", "drm_reads_device",
            "drm_search_rerank_reads", "drm_sw_align", "drm_embedder_open_ir", "drm_embedder_open_raw", "drm_embedder_close",
            "drm_embedder_ir_info", "drm_tokenize", "drm_embed", "drm_embed_reads", "drm_embed_windows", "drm_embed_device",
-           "drm_embed_windows_device", "drm_l2_rerank", "drm_l2_plan_host", "drm_l2_select_host"]
+           "drm_embed_windows_device", "drm_l2_rerank", "drm_l2_plan_host", "drm_l2_select_host",
+           "drm_shards_open", "drm_shards_unique_id", "drm_shards_open_rank", "drm_shards_close", "drm_shards_info", "drm_shards_search_rerank",
+           "drm_shards_step_device", "drm_shards_stats"]
+
+
+class ShardStats(C.Structure):
+    _fields_ = [("search_ms", C.c_double), ("exchange_ms", C.c_double), ("merge_ms", C.c_double), ("rerank_ms", C.c_double),
+                ("nhops0", C.c_int64), ("nhops_up", C.c_int64), ("ndis_eval", C.c_int64), ("bytes_received", C.c_int64),
+                ("steps", C.c_int64)]
+
+
+XCHG_ALLGATHER, XCHG_ALLTOALL, XCHG_FUSED = 0, 1, 2
 
 
 def lib_path() -> str:
@@ -99,6 +110,17 @@ def lib():
         L.drm_l2_rerank.argtypes = [vp, vp, i32, vp, vp, i64, i64, vp, i64, i64, i64, vp, vp, C.POINTER(i64)]
         L.drm_l2_plan_host.argtypes = [i32, vp, i64, i64, i64, i64, i64, C.c_uint64, vp, vp, vp, vp]
         L.drm_l2_select_host.argtypes = [vp, i64, i64, vp]
+        L.drm_shards_open.argtypes = [C.POINTER(C.c_char_p), vp, C.POINTER(i32), i32, C.POINTER(vp)]
+        L.drm_shards_unique_id.argtypes = [vp]
+        L.drm_shards_open_rank.argtypes = [C.c_char_p, i64, i32, i32, i32, vp, C.POINTER(vp)]
+        L.drm_shards_close.argtypes = [vp]
+        L.drm_shards_close.restype = None
+        L.drm_shards_info.argtypes = [vp, vp]
+        L.drm_shards_search_rerank.argtypes = [vp, vp, i32, vp, i64, i32, i32, i32, vp, vp, i64, i64, i64, i32, i64, vp, vp, vp, vp,
+                                               C.POINTER(ShardStats)]
+        L.drm_shards_step_device.argtypes = [vp, i32, vp, i64, i32, i32, i32, i32, vp, C.POINTER(vp), C.POINTER(vp), C.POINTER(i64),
+                                             C.POINTER(i64), C.POINTER(vp)]
+        L.drm_shards_stats.argtypes = [vp, i32, i32, C.POINTER(ShardStats)]
         _lib = L
     return _lib
 
@@ -555,3 +577,83 @@ def post_process_l2_static(neighbors, distances, ref: "Reference", query_embeddi
     decorated=True: ref_seqs are '<' window '>' strings; False: the bare windows read_file(..., lookup_mode=true) returns, which
     is what the reference's main passes (src/main.cpp:190) - candidates are then embedded undecorated (device mode 2)."""
     return _post_process_l2(0 if decorated else 2, vectorizer, ref, neighbors, distances, query_embeddings, stride, k, k_clusters)
+
+
+# ---- position-sharded index (BASELINE.json configs[4]; SURVEY.md §8e) ------------------------------------------------
+class Shards:
+    """One HNSW-PQ graph per GPU, windows cut by position (drm_shards_*).  Either all shards in this process
+    (index_files / id_lo / devices lists: one host thread per GPU inside the calls) or this process's shard of a
+    rank-per-process job (rank / world / unique_id as handed out by Shards.unique_id() on rank 0)."""
+
+    def __init__(self, index_files, id_lo, devices, rank=None, world=None, unique_id=None):
+        h = C.c_void_p()
+        if rank is None:
+            files = (C.c_char_p * len(index_files))(*[os.fsencode(f) for f in index_files])
+            lo = np.ascontiguousarray(id_lo, dtype=np.int64)
+            arr, n = _devs(devices)
+            assert n == len(index_files) == len(lo)
+            _check(lib().drm_shards_open(files, lo.ctypes.data, arr, n, C.byref(h)))
+        else:
+            uid = C.create_string_buffer(bytes(unique_id) if unique_id else b"\0" * 128, 128)
+            _check(lib().drm_shards_open_rank(os.fsencode(index_files), int(id_lo), int(devices), int(rank), int(world), C.addressof(uid), C.byref(h)))
+        self._h = h
+        info = np.zeros(9, dtype=np.int64)
+        _check(lib().drm_shards_info(h, info.ctypes.data))
+        (self.world, self.n_local, self.one_process, self.peer_ok, self.ntotal_local, self.device_bytes, self.rank, self.id_lo,
+         self.nccl_version) = (int(v) for v in info)
+
+    @staticmethod
+    def unique_id() -> bytes:
+        buf = C.create_string_buffer(128)
+        _check(lib().drm_shards_unique_id(C.addressof(buf)))
+        return buf.raw
+
+    def close(self):
+        if getattr(self, "_h", None):
+            lib().drm_shards_close(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def search_rerank(self, q, k_search, ef, exchange=XCHG_FUSED, chunk=0, ref=None, mode=1, reads=None, stride=1, k=None, k_clusters=None,
+                      D=None, I=None, sw_scores=None, sw_ids=None):
+        """Host buffers in, host buffers out.  reads = (flat bytes or address, int64 offsets) when ref is given.
+        Returns (D, I, sw_scores | None, sw_ids | None, stats dict of local rank 0)."""
+        q = np.ascontiguousarray(q, dtype=np.float32)
+        n, d = q.shape
+        D = np.full((n, k_search), np.nan, np.float32) if D is None else D
+        I = np.full((n, k_search), -2, np.int64) if I is None else I
+        st = ShardStats()
+        if ref is not None:
+            k = k_search if k is None else k
+            k_clusters = k_search if k_clusters is None else k_clusters
+            flat, off = reads
+            keep = flat
+            qf = flat if isinstance(flat, int) else C.cast(C.c_char_p(keep), C.c_void_p).value
+            off = np.ascontiguousarray(off, dtype=np.int64)
+            sw_scores = np.zeros((n, k), np.int32) if sw_scores is None else sw_scores
+            sw_ids = np.zeros((n, k), np.uint64) if sw_ids is None else sw_ids
+            _check(lib().drm_shards_search_rerank(self._h, ref._h, mode, q.ctypes.data, n, d, k_search, ef, qf, off.ctypes.data, stride, k, k_clusters,
+                                                  exchange, chunk, D.ctypes.data, I.ctypes.data, sw_scores.ctypes.data, sw_ids.ctypes.data, C.byref(st)))
+        else:
+            _check(lib().drm_shards_search_rerank(self._h, None, 0, q.ctypes.data, n, d, k_search, ef, None, None, 1, k_search, k_search,
+                                                  exchange, chunk, D.ctypes.data, I.ctypes.data, None, None, C.byref(st)))
+        return D, I, sw_scores, sw_ids, {f: getattr(st, f) for f, _ in ShardStats._fields_}
+
+    def step_device(self, q_ptr, n, d, k, ef, exchange=XCHG_FUSED, local_rank=0):
+        """One chunk, device buffers (rank-per-process model): returns (D_ptr, I_ptr, slice_lo, slice_n, stream) - the merged
+        lists of this rank's slice of the chunk, enqueued on the handle's stream."""
+        Dp, Ip, st = C.c_void_p(), C.c_void_p(), C.c_void_p()
+        lo, cnt = C.c_int64(0), C.c_int64(0)
+        _check(lib().drm_shards_step_device(self._h, local_rank, q_ptr, n, d, k, ef, exchange, None, C.byref(Dp), C.byref(Ip), C.byref(lo), C.byref(cnt),
+                                            C.byref(st)))
+        return Dp.value, Ip.value, lo.value, cnt.value, st.value
+
+    def stats(self, reset=False, local_rank=0):
+        st = ShardStats()
+        _check(lib().drm_shards_stats(self._h, local_rank, 1 if reset else 0, C.byref(st)))
+        return {f: getattr(st, f) for f, _ in ShardStats._fields_}

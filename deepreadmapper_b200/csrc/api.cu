@@ -10,47 +10,6 @@
 #include <mutex>
 #include <thread>
 
-// Per-replica workspace of drm_search_rerank, kept in the index handle so that repeated calls reuse their streams,
-// device buffers and pinned offset staging instead of paying cudaMalloc / cudaFree on every call.
-struct StageSlot {
-    cudaStream_t s = nullptr;
-    void *q = nullptr, *D = nullptr, *I = nullptr, *qs = nullptr, *qo = nullptr, *sc = nullptr, *id = nullptr;
-    int64_t *off = nullptr;  // pinned host: chunk-relative read offsets
-};
-struct StageWorkspace {
-    static constexpr int NSLOT = 3;
-    StageSlot slot[NSLOT];
-    void *cnt = nullptr, *dmin = nullptr;
-    size_t cap_q = 0, cap_D = 0, cap_I = 0, cap_qs = 0, cap_qo = 0, cap_sc = 0, cap_id = 0;
-    std::mutex mu;
-};
-
-struct drm_index {
-    std::vector<drm::DeviceIndex> rep;
-    std::vector<std::unique_ptr<StageWorkspace>> ws;  // one per replica, created on first use
-    int64_t info[12];
-};
-
-struct drm_ref {
-    std::vector<drm::DeviceRef> rep;
-};
-
-// FASTQ reads parsed on the device (input_kernels.cu): one copy per replica.
-struct ReadsRep {
-    int device = -1;
-    char *flat = nullptr;     // '<' + sequence + '>' of every read, back to back
-    int64_t *off = nullptr;   // n + 1 offsets into flat
-};
-struct drm_reads {
-    std::vector<ReadsRep> rep;
-    int64_t n = 0, bytes = 0;
-    int max_len = 0;
-};
-
-struct drm_embedder {
-    drm::DeviceEmbedder dev;
-};
-
 namespace {
 
 using namespace drm;

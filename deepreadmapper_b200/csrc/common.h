@@ -3,6 +3,8 @@
 #include <cuda_runtime.h>
 #include <cstdint>
 #include <cstdio>
+#include <memory>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -89,6 +91,23 @@ void free_device_index(DeviceIndex &dx);
 // Kernel launchers (search_kernel.cu)
 int launch_search(const DeviceIndex &dx, const float *q_dev, int64_t n, int k, int ef, float *D_dev, int64_t *I_dev,
                   int64_t *counters_dev, cudaStream_t stream);
+// FAISS-exact kernel (search_exact.cu): same contract; launch_search routes to it when the shape is supported
+bool search_exact_supports(const DeviceIndex &dx, int k, int ef);
+int launch_search_exact(const DeviceIndex &dx, const float *q_dev, int64_t n, int k, int ef, float *D_dev, int64_t *I_dev,
+                        int64_t *counters_dev, cudaStream_t stream);
+// Position-sharded search (shards.cu): labels leave the kernel already global (+ id_add), and with a dispatch table the
+// kernel's epilogue writes every read's list straight into the buffers of the rank that merges that read - local memory
+// or a peer GPU's over NVLink - so the exchange step of the sharded path is fused into the search.
+constexpr int MAX_SHARDS = 16;
+struct SearchDispatch {
+    int world = 0, my_shard = 0;
+    long long slice_cap = 0;              // rows of one (shard, owner) block in the owner's buffers
+    long long slice_lo[MAX_SHARDS + 1];   // owner o merges reads [slice_lo[o], slice_lo[o + 1]) of this launch
+    float *D_peer[MAX_SHARDS];            // owner o's list buffers [world][slice_cap][k] (this shard writes block my_shard)
+    long long *I_peer[MAX_SHARDS];
+};
+int launch_search_exact_ex(const DeviceIndex &dx, const float *q_dev, int64_t n, int k, int ef, float *D_dev, int64_t *I_dev,
+                           int64_t *counters_dev, cudaStream_t stream, int64_t id_add, const SearchDispatch *disp);
 
 // ---------------------------------------------------------------------------------------------
 // Reference windows on the device (sw_kernel.cu)
@@ -117,7 +136,7 @@ int launch_rerank(const DeviceRef &r, const RerankArgs &a, cudaStream_t stream);
 int launch_sw_pairs(const char *a_flat, const int64_t *a_off, const char *b_flat, const int64_t *b_off, int64_t n,
                     int max_len_b, int32_t *scores, cudaStream_t stream);
 int launch_merge_topk(const float *D_all, const int64_t *I_all, int n_shards, int64_t n, int k, float *D_out,
-                      int64_t *I_out, cudaStream_t stream);
+                      int64_t *I_out, cudaStream_t stream, int64_t shard_stride = -1 /* rows between two shards' blocks; -1 = n */);
 int launch_classify(const uint8_t *raw, uint8_t *cls, int64_t n, int *has_other_dev, cudaStream_t stream);
 
 // SW with traceback (align_kernel.cu); every pointer is a device pointer.
@@ -193,3 +212,47 @@ int launch_l2_rerank(const float *emb, const uint32_t *map, const int64_t *start
                      cudaStream_t stream);
 
 }  // namespace drm
+
+// ---------------------------------------------------------------------------------------------
+// The opaque handles of include/drm_b200.h (global namespace, C linkage names), shared by api.cu and shards.cu.
+// Per-replica workspace of drm_search_rerank, kept in the index handle so that repeated calls reuse their streams,
+// device buffers and pinned offset staging instead of paying cudaMalloc / cudaFree on every call.
+struct StageSlot {
+    cudaStream_t s = nullptr;
+    void *q = nullptr, *D = nullptr, *I = nullptr, *qs = nullptr, *qo = nullptr, *sc = nullptr, *id = nullptr;
+    int64_t *off = nullptr;  // pinned host: chunk-relative read offsets
+};
+struct StageWorkspace {
+    static constexpr int NSLOT = 3;
+    StageSlot slot[NSLOT];
+    void *cnt = nullptr, *dmin = nullptr;
+    size_t cap_q = 0, cap_D = 0, cap_I = 0, cap_qs = 0, cap_qo = 0, cap_sc = 0, cap_id = 0;
+    std::mutex mu;
+};
+
+struct drm_index {
+    std::vector<drm::DeviceIndex> rep;
+    std::vector<std::unique_ptr<StageWorkspace>> ws;  // one per replica, created on first use
+    int64_t info[12];
+};
+
+struct drm_ref {
+    std::vector<drm::DeviceRef> rep;
+};
+
+// FASTQ reads parsed on the device (input_kernels.cu): one copy per replica.
+struct ReadsRep {
+    int device = -1;
+    char *flat = nullptr;     // '<' + sequence + '>' of every read, back to back
+    int64_t *off = nullptr;   // n + 1 offsets into flat
+};
+struct drm_reads {
+    std::vector<ReadsRep> rep;
+    int64_t n = 0, bytes = 0;
+    int max_len = 0;
+};
+
+struct drm_embedder {
+    drm::DeviceEmbedder dev;
+};
+

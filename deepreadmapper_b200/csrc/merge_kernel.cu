@@ -15,13 +15,13 @@ struct Key { unsigned d; u64 id; };
 __device__ __forceinline__ bool key_less(unsigned d1, u64 i1, unsigned d2, u64 i2) { return d1 < d2 || (d1 == d2 && i1 < i2); }
 
 __global__ void merge_topk_kernel(const float *__restrict__ D_all, const long long *__restrict__ I_all, int n_shards,
-                                  long long n, int k, float *__restrict__ D_out, long long *__restrict__ I_out)
+                                  long long n, int k, float *__restrict__ D_out, long long *__restrict__ I_out, long long shard_stride)
 {
     const long long r = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const int lane = threadIdx.x & 31;
     if (r >= n) return;
-    const float *Ds = D_all + ((size_t)lane * n + r) * k;
-    const long long *Is = I_all + ((size_t)lane * n + r) * k;
+    const float *Ds = D_all + ((size_t)lane * shard_stride + r) * k;
+    const long long *Is = I_all + ((size_t)lane * shard_stride + r) * k;
     int head = 0;
     const bool owner = lane < n_shards;
     // unfilled slots (-1) compare as the largest id, so they sort after every real entry
@@ -51,14 +51,14 @@ __global__ void merge_topk_kernel(const float *__restrict__ D_all, const long lo
 }  // namespace
 
 int launch_merge_topk(const float *D_all, const int64_t *I_all, int n_shards, int64_t n, int k, float *D_out,
-                      int64_t *I_out, cudaStream_t stream)
+                      int64_t *I_out, cudaStream_t stream, int64_t shard_stride)
 {
     if (n <= 0 || k <= 0) return DRM_OK;
     if (n_shards < 1 || n_shards > 32) return fail(DRM_EINVAL, "merge supports 1..32 shards");
     const int warps_per_cta = 8;
     long long ctas = (n + warps_per_cta - 1) / warps_per_cta;
     merge_topk_kernel<<<(unsigned)ctas, warps_per_cta * 32, 0, stream>>>(D_all, reinterpret_cast<const long long *>(I_all), n_shards, n, k,
-                                                                       D_out, reinterpret_cast<long long *>(I_out));
+                                                                       D_out, reinterpret_cast<long long *>(I_out), shard_stride < 0 ? n : shard_stride);
     DRM_CUDA_TRY(cudaGetLastError());
     return DRM_OK;
 }

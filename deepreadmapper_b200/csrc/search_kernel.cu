@@ -23,6 +23,13 @@
 #include <cfloat>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
+
+#ifdef DRM_EMU
+#define DRM_PREFETCH_L2(ptr) ((void)(ptr))
+#else
+#define DRM_PREFETCH_L2(ptr) asm volatile("prefetch.global.L2 [%0];" ::"l"(ptr))
+#endif
 
 namespace drm {
 
@@ -221,7 +228,7 @@ __global__ void __launch_bounds__(WARPS_PER_CTA * 32) hnswpq_search_kernel(const
                 if (m) {
                     unsigned nv = (unsigned)(__shfl_sync(FULL, kk, __ffs(m) - 1) & 0xffffffffu) >> 1;
                     const uint8_t *nrow = p.rows0 + (size_t)nv * p.row0_bytes;
-                    if (lane * 128 < p.row0_bytes) asm volatile("prefetch.global.L2 [%0];" ::"l"(nrow + lane * 128));
+                    if (lane * 128 < p.row0_bytes) DRM_PREFETCH_L2(nrow + lane * 128);
                 }
             }
             __syncwarp();
@@ -278,6 +285,7 @@ __global__ void __launch_bounds__(WARPS_PER_CTA * 32) hnswpq_search_kernel(const
                         if (i > pin) pool[i] = tmp;
                         __syncwarp();
                     }
+                    __syncwarp();  // every lane has finished its duplicate test on pool[pin] (lanes are not in lockstep)
                     if (lane == 0) pool[pin] = kin;
                     __syncwarp();
                     size = nsz;
@@ -524,7 +532,7 @@ __global__ void __launch_bounds__(WARPS_PER_CTA * 32, VIS > 512 ? 5 : 6) hnswpq_
                         const int lb = (rest && p.prefetch_depth > 1) ? __ffs(rest) - 1 : -1;
                         if (lane == la || lane == lb) {
                             const uint8_t *prow = p.rows0 + (size_t)((unsigned)(mine & 0xffffffffu) >> 1) * p.row0_bytes;
-                            for (int o = 0; o < p.row0_bytes; o += 128) asm volatile("prefetch.global.L2 [%0];" ::"l"(prow + o));
+                            for (int o = 0; o < p.row0_bytes; o += 128) DRM_PREFETCH_L2(prow + o);
                         }
                     }
                 } else spec_v = 0xffffffffu;
@@ -686,7 +694,7 @@ __global__ void __launch_bounds__(WARPS_PER_CTA * 32, VIS > 512 ? 5 : 6) hnswpq_
                 const int lb = q ? __ffs(q) - 1 : -1;
                 if (lane == la || lane == lb) {
                     const uint8_t *prow = p.rows0 + (size_t)((unsigned)(mine & 0xffffffffu) >> 1) * p.row0_bytes;
-                    for (int o = 0; o < p.row0_bytes; o += 128) asm volatile("prefetch.global.L2 [%0];" ::"l"(prow + o));
+                    for (int o = 0; o < p.row0_bytes; o += 128) DRM_PREFETCH_L2(prow + o);
                 }
             }
             ++nhops0;
@@ -862,6 +870,7 @@ int launch_t(const SearchParams &p, size_t smem, int device, cudaStream_t stream
 // Work counters: a ring of 1024 slots per device so that launches in flight on different streams never share one.
 static unsigned *g_work_counter[64] = {nullptr};
 static std::atomic<unsigned> g_work_slot[64];
+static std::once_flag g_work_once[64];
 
 int launch_search(const DeviceIndex &dx, const float *q_dev, int64_t n, int k, int ef, float *D_dev, int64_t *I_dev,
                   int64_t *counters_dev, cudaStream_t stream)
@@ -869,6 +878,14 @@ int launch_search(const DeviceIndex &dx, const float *q_dev, int64_t n, int k, i
     if (n <= 0) return fail(DRM_EEMPTY, "Query data is empty");
     if (k <= 0 || ef <= 0) return fail(DRM_EINVAL, "k and ef must be positive");
     if (n > 0xfffffff0ll) return fail(DRM_EINVAL, "more than 2^32 queries in one call");
+    // Default: the FAISS-exact kernel (search_exact.cu: FAISS's own tie behaviour).  DRM_SEARCH_KERNEL = reg | smem | pair selects
+    // one of the canonical-order kernels below (ties ordered by (distance, id); equal to FAISS up to distance ties) for A/B runs;
+    // shapes outside the exact kernel (k > 256) also land here.
+    {
+        const char *force = getenv("DRM_SEARCH_KERNEL");
+        const bool canonical = force && (!strcmp(force, "reg") || !strcmp(force, "smem") || !strcmp(force, "pair"));
+        if (!canonical && search_exact_supports(dx, k, ef)) return launch_search_exact(dx, q_dev, n, k, ef, D_dev, I_dev, counters_dev, stream);
+    }
     if (dx.ksub != 256) return fail(DRM_EUNSUPPORTED, "only nbits == 8 product quantizers are supported by the search kernel");
     if (dx.W0 > 64 || dx.Wu > 32) return fail(DRM_EUNSUPPORTED, "M_hnsw > 32 is not supported by the search kernel");
     if (dx.code_size != 8 && dx.code_size != 16) return fail(DRM_EUNSUPPORTED, "only M_pq of 8 or 16 (nbits 8) is supported by the search kernel");
@@ -876,7 +893,11 @@ int launch_search(const DeviceIndex &dx, const float *q_dev, int64_t n, int k, i
     const int cap_alloc = (cap + 31) / 32 * 32;
     if (cap > 2048) return fail(DRM_EUNSUPPORTED, "max(ef, k) above 2048 is not supported");
     if (dx.device < 0 || dx.device >= 64) return fail(DRM_EINVAL, "bad device ordinal");
-    if (!g_work_counter[dx.device]) DRM_CUDA_TRY(cudaMalloc(&g_work_counter[dx.device], 1024 * sizeof(unsigned)));
+    {
+        cudaError_t aerr = cudaSuccess;
+        std::call_once(g_work_once[dx.device], [&] { aerr = cudaMalloc(&g_work_counter[dx.device], 1024 * sizeof(unsigned)); });
+        if (aerr != cudaSuccess || !g_work_counter[dx.device]) return fail(DRM_ECUDA, "cudaMalloc of the search work counters failed");
+    }
     unsigned *work = g_work_counter[dx.device] + (g_work_slot[dx.device].fetch_add(1) & 1023u);
     DRM_CUDA_TRY(cudaMemsetAsync(work, 0, sizeof(unsigned), stream));
 

@@ -235,6 +235,57 @@ int drm_l2_select_host(const float *dist, int64_t n, int64_t k, int64_t *idx);
 int drm_merge_topk_device(int device, const float *D_all, const int64_t *I_all, int n_shards, int64_t n, int k,
                           float *D_out, int64_t *I_out, void *stream);
 
+/* ------------------------------------------------------------------ position-sharded index (one HNSW-PQ graph per GPU) */
+/* For a reference too large for one GPU (BASELINE.json configs[4]; SURVEY.md §8b `shard_mode = 1`, §8e): the windows are
+ * cut by position into W shards, each its own IHNp file with labels local to the shard (id_lo = the shard's first global
+ * window id).  One call stands where the reference makes one faiss_search call on one index (src/main.cpp:236-237,278):
+ * every read is searched on every shard, the per-shard top-k lists meet on the GPU that owns the read (each chunk of reads
+ * is dealt out in W contiguous slices), which merges them by (distance, id) and - in drm_shards_search_rerank - SW-reranks
+ * its slice from its replica of the reference windows (post_process_sw_*, src/utils/post_processor.cpp:357-549).
+ * A sharded search explores W graphs with ef each, so it is NOT result-identical to one big graph; it equals the CPU
+ * oracle run the same sharded way.  The three exchange modes return identical bits:                                    */
+#define DRM_XCHG_ALLGATHER 0 /* ncclAllGather of every rank's lists, then merge the slice: W x chunk x k x 12 B per GPU   */
+#define DRM_XCHG_ALLTOALL 1  /* grouped ncclSend/ncclRecv: a GPU receives only the lists it merges, chunk x k x 12 B      */
+#define DRM_XCHG_FUSED 2     /* the search kernel writes each list into its owner's merge buffer (peer memory over NVLink)
+                              * as the read finishes; the only collective left is a 4-byte all-reduce per chunk (barrier). */
+typedef struct drm_shards drm_shards;
+typedef struct drm_shard_stats {
+    double search_ms, exchange_ms, merge_ms, rerank_ms; /* device time of this rank's stages, summed over its steps        */
+    int64_t nhops0, nhops_up, ndis_eval;               /* this shard's search counters                                     */
+    int64_t bytes_received;                            /* list bytes that arrived from OTHER ranks                         */
+    int64_t steps;
+} drm_shard_stats;
+
+/* One process drives all W GPUs (one host thread per GPU inside the calls): shard g = index_files[g] on devices[g] (all
+ * distinct).  NCCL (ncclCommInitAll) is loaded with dlopen at this point; DRM_EUNSUPPORTED if W > 1 and it is missing.   */
+int drm_shards_open(const char *const *index_files, const int64_t *id_lo, const int *devices, int n_shards, drm_shards **out);
+/* One process per GPU (torchrun, mpirun): rank 0 obtains the 128-byte ncclUniqueId, the launcher's own channel carries it
+ * to the other ranks, every rank opens its shard.                                                                         */
+int drm_shards_unique_id(void *id128);
+int drm_shards_open_rank(const char *index_file, int64_t id_lo, int device, int rank, int world, const void *id128, drm_shards **out);
+void drm_shards_close(drm_shards *h);
+/* info[0..8] = world, local ranks, one-process model, peer mapping usable, local vectors, local image bytes, first local
+ * rank, its id_lo, NCCL version code                                                                                       */
+int drm_shards_info(const drm_shards *h, int64_t *info);
+/* HOST buffers.  q: n x d embeddings (every rank reads all of them); D / I: n x k_search global top-k (nullable); with a
+ * reference handle that has a replica on every shard's device and non-NULL sw_* the SW rerank runs on the merged labels
+ * exactly as drm_sw_rerank would (sw_scores / sw_ids: n x k).  In the one-process model all rows are written; in the
+ * rank-per-process model only this rank's rows (slices of every chunk) are.  chunk = reads per exchange step (0 = 262144). */
+int drm_shards_search_rerank(drm_shards *h, drm_ref *ref, int mode, const float *q, int64_t n, int d, int k_search, int ef,
+                             const char *q_flat, const int64_t *q_off, int64_t stride, int64_t k, int64_t k_clusters,
+                             int exchange, int64_t chunk, float *D, int64_t *I, int32_t *sw_scores, uint64_t *sw_ids,
+                             drm_shard_stats *stats);
+/* DEVICE buffers, one chunk, one local rank (rank-per-process model): q_dev = the chunk's n x d embeddings on this rank's
+ * GPU.  Enqueues search -> exchange -> merge on the handle's stream (*step_stream) and returns the merged lists of this
+ * rank's slice [slice_lo, slice_lo + slice_n) of the chunk: device pointers owned by the handle, valid until the
+ * next-but-one step.  The caller orders its own work after *step_stream.                                                  */
+int drm_shards_step_device(drm_shards *h, int local_rank, const float *q_dev, int64_t n, int d, int k, int ef, int exchange,
+                           void *reserved, const float **D_merged, const int64_t **I_merged, int64_t *slice_lo,
+                           int64_t *slice_n, void **step_stream);
+/* Synchronises the rank's stream and reports (optionally resets) its accumulated stage times and counters.  Stage times are
+ * accumulated by drm_shards_search_rerank; after drm_shards_step_device time the stages with events on *step_stream.       */
+int drm_shards_stats(drm_shards *h, int local_rank, int reset, drm_shard_stats *st);
+
 /* ------------------------------------------------------------------ index build (host, OpenMP) */
 /* build_faiss_index (src/hnswpq/index.cpp:86-193): train the product quantizer on `train`
  * (n_train x d; NULL = use x), encode x (n x d), build the HNSW graph with efConstruction = efc and

@@ -344,6 +344,10 @@ void search_one(const OrcIndex &ix, const float *x, int k, int efSearch, int tie
 // hop expands - i.e. how often a kernel that evaluated two rows at once could keep both results without changing the
 // search (orc_spec2_counters).
 static std::atomic<long long> g_spec2_yes{0}, g_spec2_total{0};
+// Analysis counter (tools only): queries of the canonical search in which at least one decision compared two EQUAL
+// distances (pop order among equal minima, a candidate equal to the worst kept distance, an eviction among equal worst
+// distances) - the only places where FAISS's rule can decide differently (orc_tie_counters).
+static std::atomic<long long> g_tie_queries{0}, g_tie_total{0};
 
 void search_one_canonical(const OrcIndex &ix, const float *x, int k, int efSearch, VisitedTable &vt,
                           std::vector<float> &T, float *D, int64_t *I, Stats &st)
@@ -376,11 +380,17 @@ void search_one_canonical(const OrcIndex &ix, const float *x, int k, int efSearc
     pool.reserve(cap + 1);
     pool.push_back({d_nearest, nearest, false});
     vt.set(nearest);
+    bool tie_event = false;
     for (;;) {
         size_t cur = 0;
         while (cur < pool.size() && pool[cur].expanded) ++cur;
         if (cur == pool.size()) break;
         const float d0 = pool[cur].d;
+        {   // tie analysis (a): another unexpanded entry at the same distance
+            size_t nx = cur + 1;
+            while (nx < pool.size() && pool[nx].expanded) ++nx;
+            if (nx < pool.size() && pool[nx].d == d0) tie_event = true;
+        }
         const int32_t v0 = pool[cur].id;
         pool[cur].expanded = true;
         {   // spec-2 analysis: was this hop's vertex the runner-up of the previous hop?
@@ -403,15 +413,23 @@ void search_one_canonical(const OrcIndex &ix, const float *x, int k, int efSearc
             vt.set(v1);
             float dd = adc_dis(ix, T.data(), v1);
             st.ndis++;
+            if (pool.size() == cap && dd == pool.back().d) tie_event = true;                       // (b) equal to the worst kept
+            if (pool.size() >= (size_t)k && dd == pool[(size_t)k - 1].d) tie_event = true;          // (c) equal to the k-th result
             if (pool.size() == cap && !less(dd, v1, pool.back().d, pool.back().id)) continue;
             size_t pos = 0;
             while (pos < pool.size() && less(pool[pos].d, pool[pos].id, dd, v1)) ++pos;
             pool.insert(pool.begin() + (ptrdiff_t)pos, Ent{dd, v1, false});
-            if (pool.size() > cap) pool.pop_back();
+            if (pool.size() > cap) {
+                if (pool[cap].d == pool[cap - 1].d) tie_event = true;                               // (b) eviction among equal worst
+                pool.pop_back();
+            }
+            if (pool.size() > (size_t)k && pool[(size_t)k].d == pool[(size_t)k - 1].d) tie_event = true;  // (c) result cut inside a tie class
         }
         st.nhops++;
     }
     vt.advance();
+    g_tie_total++;
+    if (tie_event) g_tie_queries++;
     for (size_t j = 0; j < pool.size() && j < (size_t)k; ++j) { D[j] = pool[j].d; I[j] = pool[j].id; }
 }
 
@@ -424,6 +442,12 @@ void orc_spec2_counters(int64_t *out, int reset)
 {
     out[0] = g_spec2_yes.load(); out[1] = g_spec2_total.load();
     if (reset) { g_spec2_yes = 0; g_spec2_total = 0; }
+}
+
+void orc_tie_counters(int64_t *out, int reset)
+{
+    out[0] = g_tie_queries.load(); out[1] = g_tie_total.load();
+    if (reset) { g_tie_queries = 0; g_tie_total = 0; }
 }
 
 void *orc_index_read(const char *path)

@@ -223,3 +223,24 @@ def test_align_merge_and_input_kernels_on_the_emulation_under_asan():
     env = dict(os.environ, LD_PRELOAD=asan, ASAN_OPTIONS="detect_leaks=0:abort_on_error=0")
     r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, env=env, timeout=1500)
     assert r.returncode == 0 and all(x in r.stdout for x in ("align kernel ok", "merge kernel ok", "input kernels ok")), (r.stdout[-1500:], r.stderr[-3000:])
+
+
+def test_search_kernels_on_the_emulation_under_asan():
+    """csrc/search_exact.cu (the default, FAISS-exact kernel), csrc/search_kernel.cu (canonical-order kernels) and
+    csrc/index_image.cu on host threads, AddressSanitizer preloaded: tests/emu_search_check.py.  The exact kernel must equal
+    the oracle's FAISS-rule search (tie_rule 0) bit for bit - ids and fp32 distances - the others the canonical rule."""
+    sys.path.insert(0, os.path.join(ROOT, "tools", "cpu_emu"))
+    import emu_build
+    lib = emu_build.build(sanitize=True)
+    asan = subprocess.run(["/usr/bin/g++", "-print-file-name=libasan.so"], capture_output=True, text=True).stdout.strip()
+    if not os.path.isabs(asan) or not os.path.exists(asan):
+        pytest.skip("libasan not found")
+    code = (
+        "import sys; sys.path.insert(0, %r); sys.path.insert(0, %r)\n"
+        "import deepreadmapper_b200.api as A\n"
+        "A._LIB_PATH = %r; A._lib = None\n"
+        "import emu_search_check as M\n"
+        "M.main()\n" % (ROOT, os.path.join(ROOT, "tests"), lib))
+    env = dict(os.environ, LD_PRELOAD=asan, ASAN_OPTIONS="detect_leaks=0:abort_on_error=0")
+    r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, env=env, timeout=1500)
+    assert r.returncode == 0 and "search kernels == oracle" in r.stdout, (r.stdout[-1500:], r.stderr[-3000:])

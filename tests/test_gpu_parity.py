@@ -204,17 +204,26 @@ def mid_index(tmp_path_factory):
     return p, synth.embed_reads(reads), ids
 
 
-@pytest.fixture(params=["reg", "reg_vis1024", "reg_novis", "smem", "pair"])
+@pytest.fixture(params=["exact", "exact_vis1024", "exact_novis", "exact_nora", "exact_pfa", "reg", "reg_vis1024", "reg_novis", "smem", "pair"])
 def search_variant(request, monkeypatch):
-    """Every search kernel (register pool with the 512- / 1024-slot visited cache or none, shared-memory pool) must return the oracle's bits."""
-    monkeypatch.setenv("DRM_SEARCH_KERNEL", request.param if request.param in ("smem", "pair") else "reg")
-    monkeypatch.setenv("DRM_SEARCH_VIS", {"reg_novis": "0", "reg_vis1024": "1024"}.get(request.param, "512"))
-    return request.param
+    """exact* = the default kernel (search_exact.cu: FAISS's own tie behaviour, oracle tie_rule 0) with the 512- / 1024-slot
+    visited cache or none, without the register read-ahead, with the accept-time L2 prefetch; reg* / smem / pair = the
+    canonical-order kernels of search_kernel.cu (oracle tie_rule 1).  Each must return its oracle's bits."""
+    v = request.param
+    monkeypatch.setenv("DRM_SEARCH_KERNEL", v if v in ("smem", "pair") else "reg" if v.startswith("reg") else "exact")
+    monkeypatch.setenv("DRM_SEARCH_VIS", "0" if v.endswith("novis") else "1024" if v.endswith("vis1024") else "512")
+    monkeypatch.setenv("DRM_SEARCH_RA", "0" if v == "exact_nora" else "1")
+    monkeypatch.setenv("DRM_SEARCH_PFA", "1" if v == "exact_pfa" else "0")
+    return v
 
 
-def _check_search(drm, ob, path, Q, k, ef):
+def _tie_rule_of(variant):
+    return 0 if variant.startswith("exact") else 1
+
+
+def _check_search(drm, ob, path, Q, k, ef, tie_rule=0):
     oix = ob.OracleIndex(path)
-    D0, I0, st = oix.search(Q, k, ef, tie_rule=1)
+    D0, I0, st = oix.search(Q, k, ef, tie_rule=tie_rule)
     ix = drm.Index(path)
     D1, I1, gst = ix.search(Q, k, ef, return_stats=True)
     ix.close()
@@ -227,7 +236,7 @@ def _check_search(drm, ob, path, Q, k, ef):
 
 def test_search_config1_bit_exact(drm, ob, small_index, search_variant):
     path, Q = small_index
-    oix, D, I = _check_search(drm, ob, path, Q, 128, 128)
+    oix, D, I = _check_search(drm, ob, path, Q, 128, 128, _tie_rule_of(search_variant))
     # invariants that do not depend on the oracle's traversal: ascending D, unique ids, D == dis(I)
     assert (np.diff(D, axis=1) >= 0).all()
     for i in range(0, len(Q), 7):
@@ -236,22 +245,35 @@ def test_search_config1_bit_exact(drm, ob, small_index, search_variant):
         assert np.array_equal(oix.adc_distances(Q[i], I[i]).view(np.uint32), D[i].view(np.uint32))
 
 
-@pytest.mark.parametrize("k,ef", [(128, 128), (8, 32), (32, 64), (128, 512), (64, 256), (200, 128), (1, 16)])
+@pytest.mark.parametrize("k,ef", [(128, 128), (8, 32), (32, 64), (128, 512), (64, 256), (200, 128), (1, 16), (100, 128), (256, 256)])
 def test_search_ef_k_sweep_bit_exact(drm, ob, mid_index, k, ef, search_variant):
     path, Q, _ = mid_index
-    _check_search(drm, ob, path, Q[:1500], k, ef)
+    _check_search(drm, ob, path, Q[:1500], k, ef, _tie_rule_of(search_variant))
 
 
-def test_search_overlap_with_faiss_tie_rule(drm, ob, mid_index):
-    """north_star: recall@K overlap with the reference >= 0.99; rows that differ do so only through PQ-distance ties."""
-    path, Q, _ = mid_index
-    oix = ob.OracleIndex(path)
-    D0, I0, _ = oix.search(Q, 128, 128, tie_rule=0)
-    ix = drm.Index(path)
-    D1, I1 = ix.search(Q, 128, 128)
-    ix.close()
-    overlap = np.mean([len(set(I0[i].tolist()) & set(I1[i].tolist())) / 128 for i in range(len(Q))])
-    assert overlap >= 0.99, overlap
+def test_search_north_star_tie_rule(drm, ob, mid_index, small_index, monkeypatch):
+    """north_star: 'Returned indices are identical except where PQ distances tie within 1e-5 relative; recall@K overlap
+    >= 0.99.'  oracle/parity.py states the rule; rows violating it must be 0.  The default kernel reproduces FAISS's own
+    tie behaviour (restatement, tie_rule 0), so its rows are not merely within the rule but IDENTICAL.  The canonical-order
+    kernels (DRM_SEARCH_KERNEL=reg) resolve ties by id: they stay above the 0.99 overlap but 1-3 % of their rows break the
+    strict rule on this tie-heavy index - which is why they are no longer the default."""
+    from oracle import parity
+    for path, Q in (small_index, mid_index[:2]):
+        oix = ob.OracleIndex(path)
+        for k, ef in ((128, 128), (32, 64)):
+            D0, I0, _ = oix.search(Q, k, ef, tie_rule=0)
+            monkeypatch.delenv("DRM_SEARCH_KERNEL", raising=False)
+            ix = drm.Index(path)
+            D1, I1 = ix.search(Q, k, ef)
+            rep = parity.tie_rule_report(D0, I0, D1, I1)
+            assert rep["rows_violating"] == 0 and rep["rows_differing"] == 0 and rep["overlap"] == 1.0, rep
+            monkeypatch.setenv("DRM_SEARCH_KERNEL", "reg")
+            D2, I2 = ix.search(Q, k, ef)
+            ix.close()
+            monkeypatch.delenv("DRM_SEARCH_KERNEL", raising=False)
+            rep2 = parity.tie_rule_report(D0, I0, D2, I2)
+            assert rep2["overlap"] >= 0.98, rep2
+            print(f"[tie rule] k={k} ef={ef}: default kernel {rep}; canonical kernel {rep2}")
 
 
 def test_search_errors(drm, small_index):
@@ -370,7 +392,7 @@ def test_cli_hnswpq_index_then_pipeline_config1(drm, ob, fixtures, tmp_path):
         I, D = np.load(out / "indices.npy"), np.load(out / "distances.npy")
         assert I.dtype == np.dtype("<u8") and D.dtype == np.dtype("<f4") and I.shape == D.shape == (len(reads), 32)
         oix = ob.OracleIndex(str(tmp_path / "idx1" / "idx1.index"))
-        D0, I0, _ = oix.search(Q, 32, 64, tie_rule=1)
+        D0, I0, _ = oix.search(Q, 32, 64, tie_rule=0)
         assert np.array_equal(I.astype(np.int64), I0) and np.array_equal(D.view(np.uint32), D0.view(np.uint32))
         S, SI = np.load(out / "sw_scores.npy"), np.load(out / "sw_indices.npy")
         assert S.dtype == np.dtype("<i4") and SI.dtype == np.dtype("<u8")
@@ -414,7 +436,7 @@ def test_sharded_index_search_and_merge_vs_sharded_oracle(drm, ob, tmp_path):
         ix.close()
         Ds.append(D)
         Is.append(I)
-        D0, I0, _ = ob.OracleIndex(path).search(Q, k, ef, tie_rule=1)
+        D0, I0, _ = ob.OracleIndex(path).search(Q, k, ef, tie_rule=0)
         Do.append(D0)
         Io.append(np.where(I0 >= 0, I0 + lo, -1))
         assert np.array_equal(I.cpu().numpy(), Io[-1]) and np.array_equal(D.cpu().numpy().view(np.uint32), D0.view(np.uint32))

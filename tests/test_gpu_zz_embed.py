@@ -178,7 +178,7 @@ def test_cli_from_sequence_files_only(tmp_path):
     Q = v.vectorize([b"<" + x + b">" for x in reads])
     v.close()
     I, D = np.load(out / "indices.npy"), np.load(out / "distances.npy")
-    D0, I0, _ = oix.search(Q, 16, 64, tie_rule=1)
+    D0, I0, _ = oix.search(Q, 16, 64, tie_rule=0)
     assert np.array_equal(I.astype(np.int64), I0) and np.array_equal(D.view(np.uint32), D0.view(np.uint32))
     S, SI = np.load(out / "sw_scores.npy"), np.load(out / "sw_indices.npy")
     rc, s0, i0, _ = ob.post_process_sw(1, I0, genome, len(genome), 150, ["<" + x.decode() + ">" for x in reads], 1, 16, 16)

@@ -27,6 +27,10 @@
 struct uint3 { unsigned x, y, z; };
 struct dim3 { unsigned x = 1, y = 1, z = 1; dim3(unsigned a = 1, unsigned b = 1, unsigned c = 1) : x(a), y(b), z(c) {} };
 struct alignas(16) float4 { float x, y, z, w; };
+struct alignas(8) uint2 { unsigned x, y; };
+struct alignas(16) uint4 { unsigned x, y, z, w; };
+inline uint2 make_uint2(unsigned x, unsigned y) { return uint2{x, y}; }
+inline uint4 make_uint4(unsigned x, unsigned y, unsigned z, unsigned w) { return uint4{x, y, z, w}; }
 
 typedef int cudaError_t;
 typedef void *cudaStream_t;
@@ -173,6 +177,43 @@ inline unsigned __ballot_sync(unsigned, int pred)
     return r;
 }
 inline int __any_sync(unsigned m, int pred) { return __ballot_sync(m, pred) != 0; }
+inline unsigned __match_any_sync(unsigned, int v)
+{
+    const unsigned t = emu::flat_tid(), base = (t / 32) * 32;
+    emu::t_block->slots[t] = (unsigned long long)(unsigned)v | (1ull << 40);  // bit 40: this lane takes part
+    emu::warp_sync();
+    unsigned r = 0;
+    for (unsigned l = 0; l < 32 && base + l < emu::t_block->slots.size(); ++l)
+        if (emu::t_block->slots[base + l] == ((unsigned long long)(unsigned)v | (1ull << 40))) r |= 1u << l;
+    emu::warp_sync();
+    emu::t_block->slots[t] = 0;
+    return r;
+}
+// warp reductions (REDUX on the device): every live lane contributes; lanes that already returned contribute their last value
+template <class F> inline unsigned emu_reduce(unsigned v, F f)
+{
+    const unsigned t = emu::flat_tid(), base = (t / 32) * 32;
+    emu::t_block->slots[t] = v;
+    emu::warp_sync();
+    unsigned r = v;
+    for (unsigned l = 0; l < 32 && base + l < emu::t_block->slots.size(); ++l) r = f(r, (unsigned)emu::t_block->slots[base + l]);
+    emu::warp_sync();
+    emu::t_block->slots[t] = 0;
+    return r;
+}
+inline unsigned __reduce_min_sync(unsigned, unsigned v) { return emu_reduce(v, [](unsigned a, unsigned b) { return a < b ? a : b; }); }
+inline unsigned __reduce_max_sync(unsigned, unsigned v) { return emu_reduce(v, [](unsigned a, unsigned b) { return a > b ? a : b; }); }
+inline unsigned __reduce_add_sync(unsigned, unsigned v)
+{
+    const unsigned t = emu::flat_tid(), base = (t / 32) * 32;
+    emu::t_block->slots[t] = v;
+    emu::warp_sync();
+    unsigned r = 0;
+    for (unsigned l = 0; l < 32 && base + l < emu::t_block->slots.size(); ++l) r += (unsigned)emu::t_block->slots[base + l];
+    emu::warp_sync();
+    emu::t_block->slots[t] = 0;
+    return r;
+}
 inline int __all_sync(unsigned m, int pred) { return __ballot_sync(m, !pred) == 0; }
 // ---- bit helpers ----
 inline int __popc(unsigned v) { return __builtin_popcount(v); }
@@ -186,6 +227,7 @@ inline float __int_as_float(int u) { float f; std::memcpy(&f, &u, 4); return f; 
 template <class T> inline T __ldg(const T *p) { return *p; }
 // ---- atomics (real ones: the emulated threads are OS threads) ----
 template <class T> inline T atomicAdd(T *p, T v) { return __atomic_fetch_add(p, v, __ATOMIC_SEQ_CST); }
+template <class T> inline T atomicOr(T *p, T v) { return __atomic_fetch_or(p, v, __ATOMIC_SEQ_CST); }
 template <class T> inline T atomicExch(T *p, T v) { return __atomic_exchange_n(p, v, __ATOMIC_SEQ_CST); }
 template <class T> inline T atomicCAS(T *p, T cmp, T v) { __atomic_compare_exchange_n(p, &cmp, v, false, __ATOMIC_SEQ_CST, __ATOMIC_SEQ_CST); return cmp; }
 template <class T> inline T atomicMin(T *p, T v)
@@ -201,8 +243,10 @@ template <class T> inline T atomicMax(T *p, T v)
     return old;
 }
 inline void __threadfence() { __atomic_thread_fence(__ATOMIC_SEQ_CST); }
+inline void __threadfence_system() { __atomic_thread_fence(__ATOMIC_SEQ_CST); }
 // ---- launch attributes: accepted and ignored ----
 enum cudaFuncAttribute { cudaFuncAttributeMaxDynamicSharedMemorySize };
 template <class K> inline cudaError_t cudaFuncSetAttribute(K, cudaFuncAttribute, int) { return 0; }
+template <class K> inline cudaError_t cudaOccupancyMaxActiveBlocksPerMultiprocessor(int *n, K, int, size_t) { *n = 1; return 0; }
 using std::max;
 using std::min;

@@ -8,7 +8,8 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(os.path.dirname(HERE))
 CSRC = os.path.join(ROOT, "deepreadmapper_b200", "csrc")
 OUT = os.path.join(ROOT, "build", "emu")
-EMULATED = ("embed_kernel.cu", "l2_kernel.cu", "align_kernel.cu", "merge_kernel.cu", "input_kernels.cu")
+EMULATED = ("embed_kernel.cu", "l2_kernel.cu", "align_kernel.cu", "merge_kernel.cu", "input_kernels.cu", "index_image.cu", "search_kernel.cu",
+            "search_exact.cu")
 LAUNCH = re.compile(r"([A-Za-z_]\w*(?:<[^<>;]*>)?)\s*<<<(.*?)>>>\s*\((.*?)\);", re.S)
 
 
@@ -22,7 +23,7 @@ def transform(src: str) -> str:
     if n == 0:
         raise SystemExit("no kernel launch found")
     # dynamic shared memory: `extern __shared__ T name[];` becomes a pointer to the block's buffer
-    out = re.sub(r"extern\s+__shared__\s+([\w ]+?)\s+(\w+)\[\];", r"\1 *\2 = static_cast<\1 *>(emu::dyn_smem());", out)
+    out = re.sub(r"extern\s+__shared__\s+(?:__align__\(\d+\)\s+)?([\w ]+?)\s+(\w+)\[\];", r"\1 *\2 = static_cast<\1 *>(emu::dyn_smem());", out)
     return out
 
 
@@ -45,7 +46,7 @@ def build(sanitize=True) -> str:
     newest = max(os.path.getmtime(p) for p in srcs + [os.path.join(HERE, "cuda_runtime.h"), os.path.join(CSRC, "common.h")])
     if os.path.exists(lib) and os.path.getmtime(lib) >= newest:
         return lib
-    cmd = ["/usr/bin/g++", "-std=c++20", "-O1", "-g", "-fPIC", "-shared", "-pthread", "-fopenmp", "-Wl,--no-undefined", "-I", HERE, "-I", CSRC,
+    cmd = ["/usr/bin/g++", "-std=c++20", "-O1", "-g", "-fPIC", "-shared", "-pthread", "-fopenmp", "-DDRM_EMU", "-Wl,--no-undefined", "-I", HERE, "-I", CSRC,
            "-o", lib] + srcs
     if sanitize:
         cmd[3:3] = ["-fsanitize=address", "-fno-omit-frame-pointer"]

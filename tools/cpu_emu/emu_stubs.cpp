@@ -1,5 +1,5 @@
-// TEST INFRASTRUCTURE ONLY: what api.cu links against besides the emulated kernel files (README.md).  The kernels that
-// use warp shuffles / ballots / atomics are not emulated: their launchers refuse.  launch_classify is restated on the host
+// TEST INFRASTRUCTURE ONLY: what api.cu links against besides the emulated kernel files (README.md).  The SW rerank kernels
+// (s16x2 video intrinsics) and the GPU builder are not emulated: their launchers refuse.  launch_classify is restated on the host
 // because every reference handle needs it (base classes 0..3 = A,C,G,T, 4 = N, 7 = any other byte; csrc/sw_kernel.cu).
 #include "common.h"
 
@@ -24,9 +24,6 @@ int launch_classify(const uint8_t *raw, uint8_t *cls, int64_t n, int *has_other_
     return DRM_OK;
 }
 
-int build_device_index(const HostIndex &, int, DeviceIndex &) { return na("the index image"); }
-void free_device_index(DeviceIndex &) {}
-int launch_search(const DeviceIndex &, const float *, int64_t, int, int, float *, int64_t *, int64_t *, cudaStream_t) { return na("the search kernel"); }
 int launch_rerank(const DeviceRef &, const RerankArgs &, cudaStream_t) { return na("the SW rerank kernel"); }
 int launch_sw_pairs(const char *, const int64_t *, const char *, const int64_t *, int64_t, int, int32_t *, cudaStream_t) { return na("the SW pair kernel"); }
 
