@@ -10,8 +10,13 @@ candidate windows with Smith-Waterman.  One "step" = one pass of the path over t
   e2e     the same through the host-buffer C-ABI call drm_search_rerank (pinned host memory, copies inside)
   --impl reference   the reference's CPU path on the host cores (FAISS-rule search restatement + the reference's
                      own post_process_sw compiled unmodified when oracle/_ref is present), bounded sample
-N > 1: launched by torchrun, one rank per GPU, index replicated, reads sharded (each rank has its own batch):
-no data-path collective, weak scaling.
+N > 1: launched by torchrun, one rank per GPU.  The headline line is the reads-sharded arm (index replicated, each rank its
+own batch: no data-path collective, weak scaling).  The same line then carries a `sharded` section: the index cut by POSITION
+into N shards (one HNSW-PQ graph per GPU, BASELINE.json configs[4] at E. coli size), every read searched on every shard, the
+per-shard top-K lists exchanged over NVLink and merged on the GPU that owns the read, SW rerank on the owner - through the
+library's own data plane (drm_shards_*, csrc/shards.cu) in its three exchange modes (fused peer-memory dispatch from the
+search kernel, NCCL all-to-all, NCCL all-gather), strong scaling.  `--workload sharded` runs only that arm;
+DRM_BENCH_CHR=1 makes it the chromosome-scale configuration (250 Mbp random genome, ~500 M vectors over the GPUs).
 """
 import argparse
 import json
@@ -79,6 +84,8 @@ def parse():
                          "sharded = configs[4] scaled down (index sharded by position, all-gather + merge); "
                          "sparse = configs[2] (stride-8 index, K_clusters=32, window expansion + SW, use_dynamic 0 and 1)")
     ap.add_argument("--chunk", type=int, default=262144, help="reads per exchange step of the sharded workload")
+    ap.add_argument("--build-only", action="store_true", help="build and cache the workload's index file, then exit (used by --impl reference)")
+    ap.add_argument("--no-sharded", action="store_true", help="N > 1: skip the position-sharded section")
     return ap.parse_args()
 
 
@@ -103,31 +110,26 @@ def make_genome(args):
 
 
 def build_index_file(args, genome, path, device, stride=1, seed=1234, threads=None):
-    """hnswpq_index's job for one genome (slice): surrogate embeddings of every window, then the index file.  With a CUDA
-    device the embeddings stay on it and the GPU builder makes the file; the host OpenMP builder is used when asked for
-    (--builder cpu), when there is no device, or - loudly - when the GPU build fails.  Returns (n_vectors, 'gpu'|'cpu')."""
+    """hnswpq_index's job for one genome (slice): surrogate embeddings of every window, then the index file.  The GPU builder
+    makes the file from device-resident embeddings; the host OpenMP builder runs ONLY when asked for (--builder cpu).  A failed
+    GPU build is an error, not a fallback.  Returns (n_vectors, 'gpu'|'cpu')."""
     import deepreadmapper_b200 as drm
     from deepreadmapper_b200 import synth
     tmp = path + f".tmp{os.getpid()}"
-    if device is not None and getattr(args, "builder", "gpu") == "gpu":
+    if getattr(args, "builder", "gpu") == "gpu":
+        if device is None:
+            raise SystemExit("the index is built on the GPU (use --builder cpu for the host OpenMP builder)")
         import torch
         E = synth.embed_windows_torch(genome, device, stride=stride, return_device=True)
-        try:
-            tim = drm.build_index_gpu_device(E.data_ptr(), E.shape[0], E.shape[1], tmp, train_step=2, M_pq=8, nbits=8, M_hnsw=16,
-                                             efc=args.efc, device=torch.device(device).index or 0, seed=seed)
-            os.replace(tmp, path)
-            nv = int(E.shape[0])
-            log(f"GPU index build of {nv} vectors (EFC={args.efc}): " + ", ".join(f"{k} {v:.2f}s" for k, v in tim.items()))
-            del E
-            torch.cuda.empty_cache()
-            return nv, "gpu"
-        except drm.DrmError as e:
-            log(f"GPU index build FAILED ({e}); falling back to the host builder")
-            E = E.cpu().numpy()
-    elif device is not None:
-        E = synth.embed_windows_torch(genome, device, stride=stride)
-    else:
-        E = synth.embed_windows(genome, stride=stride)
+        tim = drm.build_index_gpu_device(E.data_ptr(), E.shape[0], E.shape[1], tmp, train_step=2, M_pq=8, nbits=8, M_hnsw=16,
+                                         efc=args.efc, device=torch.device(device).index or 0, seed=seed)
+        os.replace(tmp, path)
+        nv = int(E.shape[0])
+        log(f"GPU index build of {nv} vectors (EFC={args.efc}): " + ", ".join(f"{k} {v:.2f}s" for k, v in tim.items()))
+        del E
+        torch.cuda.empty_cache()
+        return nv, "gpu"
+    E = synth.embed_windows_torch(genome, device, stride=stride) if device is not None else synth.embed_windows(genome, stride=stride)
     th = threads or host_threads()
     log(f"host index build of {E.shape[0]} vectors (EFC={args.efc}) on {th} threads")
     drm.build_index(E, tmp, M_pq=8, nbits=8, M_hnsw=16, efc=args.efc, seed=seed, threads=th)
@@ -194,16 +196,37 @@ class ClockSampler:
         return out
 
 
+def faiss_real_search(index_path, qs, threads):
+    """SURVEY §7 / BASELINE.md §3 run-time probe: if a real FAISS is importable on this box, the search leg of the CPU arm IS
+    faiss.IndexHNSWPQ::search on the same index file (read by faiss.read_index).  Returns (D, I) or None."""
+    from oracle import faiss_probe
+    if not faiss_probe.probe()["python"]:
+        return None
+    import faiss
+    faiss.omp_set_num_threads(threads)
+    index = faiss.read_index(index_path)
+    index.hnsw.efSearch = EF
+    return index.search(np.ascontiguousarray(qs, dtype=np.float32), K)
+
+
 def cpu_reference_run(args, genome, index_path, reads, Q, n_sample, threads):
-    """The reference's CPU path on a bounded sample: FAISS-rule (tie_rule 0) HNSW-PQ search restatement, OpenMP over
-    queries with all host threads, then SW rerank - oracle/_ref (the reference's post_process_sw_dynamic, unmodified)
-    when present, else the oracle's C port.  Returns (reads/sec, seconds, kind, per-query counters)."""
+    """The reference's CPU path on a bounded sample: HNSW-PQ search - real FAISS when the run-time probe finds one, else the
+    FAISS-rule (tie_rule 0) restatement - OpenMP over queries with all host threads, then SW rerank - oracle/_ref (the
+    reference's post_process_sw_dynamic, unmodified) when present, else the oracle's C port.  Returns (reads/sec, seconds,
+    kind, per-query counters of the restatement, results)."""
     from oracle import bindings as ob
     oix = ob.OracleIndex(index_path)
     qs = Q[:n_sample]
     seqs = [bytes(r) for r in reads[:n_sample]]
     t0 = time.perf_counter()
-    D, I, st = oix.search(qs, K, EF, tie_rule=0, threads=threads)
+    real = faiss_real_search(index_path, qs, threads)
+    if real is not None:
+        t1 = time.perf_counter()
+        D, I = real
+        _, _, st = oix.search(qs, K, EF, tie_rule=0, threads=threads)  # counters for the byte model (untimed)
+        t0 = time.perf_counter() - (t1 - t0)
+    else:
+        D, I, st = oix.search(qs, K, EF, tie_rule=0, threads=threads)
     t1 = time.perf_counter()
     use_ref = ob.have_ref()
     rc, s, ids, _ = ob.post_process_sw(1, I, genome, len(genome), REF_LEN, seqs, 1, K, K, threads=threads, use_ref=use_ref)
@@ -226,21 +249,25 @@ def base_config(args, n_gpus):
 
 
 def run_reference(args):
+    """The reference's CPU implementation of the path on the host cores.  This process never maps libdrm_cuda.so: the cached
+    index file (hnswpq_index's job, outside the timed path) is built by a CHILD process (`bench.py --build-only`) when the
+    "ours" arm has not left it in the cache already; everything timed here is oracle/ (+ oracle/_ref, + real FAISS if found)."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return 0
     threads = host_threads()
     genome = make_genome(args)
-    dev = None
-    try:
-        import torch
-        if torch.cuda.is_available():
-            dev = "cuda:0"
-    except Exception:
-        pass
-    index_path, _ = ensure_index(args, genome, dev)
+    index_path = workload_paths(args)
+    if not os.path.exists(index_path):
+        log("index file not cached: building it in a child process (the timed loop below stays CPU-only)")
+        env = {k: v for k, v in os.environ.items() if k not in ("RANK", "WORLD_SIZE", "LOCAL_RANK", "MASTER_ADDR", "MASTER_PORT")}
+        subprocess.check_call([sys.executable, os.path.abspath(__file__), "--build-only", "--genome-bases", str(args.genome_bases), "--efc", str(args.efc),
+                               "--cache", args.cache, "--builder", args.builder], env=env, stdout=sys.stderr)
     n_sample = args.cpu_sample or 600 * threads
+    from deepreadmapper_b200 import synth  # pure numpy generators; the C library is not loaded by this import
     reads, truth, Q = make_reads(genome, n_sample, seed=7)
+    from oracle import faiss_probe
+    probe = faiss_probe.probe()
     times = []
     kind = "port"
     for it in range(args.warmup + args.steps):
@@ -250,15 +277,27 @@ def run_reference(args):
             times.append(ts + tw)
     ms = 1e3 * float(np.mean(times))
     value = n_sample / (ms / 1e3)
-    sample = (f"{n_sample} reads per step (same generator as the GPU arm); search = CPU restatement of FAISS IndexHNSWPQ::search "
-              f"(FAISS itself is not installable here), SW = " + ("the reference's post_process_sw_dynamic compiled unmodified (oracle/_ref)"
-                                                                  if kind == "reference" else "oracle C port of calc_sw_score/sw_reranker"))
+    skind = faiss_probe.search_kind(probe)
+    sample = (f"{n_sample} reads per step (same generator as the GPU arm); search leg = "
+              + ("real faiss.IndexHNSWPQ::search" if skind == "faiss" else "CPU restatement of FAISS IndexHNSWPQ::search (FAISS not found by the run-time probe)")
+              + f", OpenMP over queries, {threads} threads; SW leg = "
+              + ("the reference's post_process_sw_dynamic compiled unmodified (oracle/_ref), its hard-coded num_threads(128) on %d cores" % threads
+                 if kind == "reference" else "oracle C port of calc_sw_score/sw_reranker, %d threads" % threads))
+    loaded = sorted({ln.split()[-1] for ln in open("/proc/self/maps") if ln.rstrip().endswith(".so") and "/repo" in ln})
     line = {"impl": "reference", "metric": METRIC, "value": value, "unit": "reads/s", "n_gpus": args.gpus, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f32 ADC distances + int32 SW", "data": "synthetic", "config": base_config(args, args.gpus),
-            "cpu_baseline": {"value": value, "unit": "reads/s", "cores": threads, "kind": kind, "sample": sample},
-            "e2e": {"value": value, "unit": "reads/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}
+            "cpu_baseline": {"value": value, "unit": "reads/s", "cores": threads, "kind": kind, "search_kind": skind, "faiss_probe": probe, "sample": sample},
+            "e2e": {"value": value, "unit": "reads/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0,
+            "repo_shared_objects_mapped": loaded}
     emit(line)
+    return 0
+
+
+def run_build_only(args):
+    import torch
+    genome = make_genome(args)
+    ensure_index(args, genome, "cuda:0" if torch.cuda.is_available() else None)
     return 0
 
 
@@ -366,6 +405,11 @@ def run_ours(args):
     # the two arms must agree bit for bit
     assert torch.equal(hI, dI.cpu()) and torch.equal(hS, dS.cpu()) and torch.equal(hIds, dIds.cpu()), "e2e arm differs from the device arm"
 
+    # ---------------- N > 1: the position-sharded data plane on the same box (every rank takes part)
+    sharded_section = None
+    if world > 1 and not args.no_sharded:
+        sharded_section = sharded_arm(args, genome, ref, rank, world, local, dist, dense_reads_per_s_per_gpu=n / (total_ms / args.steps / 1e3))
+
     t = torch.tensor([total_ms, e2e_s * 1e3, search_ms, sw_ms], dtype=torch.float64, device="cuda")
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -403,14 +447,32 @@ def run_ours(args):
         threads = host_threads()
         ns = args.cpu_sample or 600 * threads
         rps, (ts, tw), kind, counters, (D0, I0, s0, ids0) = cpu_reference_run(args, genome, index_path, reads, Q, ns, threads)
-        overlap = float(np.mean([len(set(I0[i].tolist()) & set(hI[i].tolist())) / K for i in range(ns)]))
+        from oracle import bindings as ob
+        from oracle import faiss_probe, parity
+        probe = faiss_probe.probe()
+        # north_star rule on the sample (oracle/parity.py): rows that differ from the reference-rule result by more than a
+        # PQ-distance tie must be 0; the default kernel reproduces FAISS's own tie behaviour, so rows are IDENTICAL
+        rep = parity.tie_rule_report(D0, I0, hD[:ns].numpy(), hI[:ns].numpy())
         # SW parity on the sample: rerank the CPU labels on the GPU -> must equal the CPU rerank bit for bit
         s1, ids1 = ref.rerank(1, I0, [bytes(r) for r in reads[:ns]], 1, K, K)
         sw_equal = bool(np.array_equal(s1, s0) and np.array_equal(ids1, ids0))
-        cpu = {"value": rps, "unit": "reads/s", "cores": threads, "kind": kind,
-               "sample": f"{ns} reads of the same batch: search {ts:.2f}s (FAISS-rule CPU restatement, {threads} threads) + SW {tw:.2f}s "
-                         f"({'reference post_process_sw_dynamic unmodified' if kind == 'reference' else 'oracle C port'})",
-               "recall_overlap_vs_reference_rule": overlap, "sw_bit_exact_on_sample": sw_equal}
+        cpu = {"value": rps, "unit": "reads/s", "cores": threads, "kind": kind, "search_kind": faiss_probe.search_kind(probe), "faiss_probe": probe,
+               "sample": f"{ns} reads of the same batch: search {ts:.2f}s ({'real FAISS' if probe['python'] else 'FAISS-rule CPU restatement'}, {threads} threads) + SW {tw:.2f}s "
+                         f"({'reference post_process_sw_dynamic unmodified, num_threads(128)' if kind == 'reference' else 'oracle C port'})",
+               "search_rows": rep["rows"], "search_rows_identical": rep["rows_identical"], "search_rows_violating_tie_rule": rep["rows_violating"],
+               "recall_overlap_vs_reference_rule": rep["overlap"], "sw_bit_exact_on_sample": sw_equal}
+        # how good is the graph itself: recall@K against the exact ADC scan (brute force over all codes) and level-0 out-degree
+        try:
+            oix = ob.OracleIndex(index_path)
+            nq = min(256, ns)
+            De, Ie = oix.adc_scan(Q[:nq], K, threads=threads)
+            got = hI[:nq].numpy()
+            line["recall_at_k_vs_exact_adc"] = float(np.mean([len(set(Ie[i].tolist()) & set(got[i].tolist())) / K for i in range(nq)]))
+            line["graph"] = {k2: v for k2, v in oix.arrays()[2].items()}
+            line["graph"]["queries_in_recall_sample"] = nq
+        except Exception as e:  # measurement extra, never fatal
+            line["recall_at_k_vs_exact_adc"] = None
+            log("exact ADC recall skipped:", e)
         line["cpu_baseline"] = cpu
         bytes_per_read = 128 * counters["nhops"] + 64 * counters["nhops_up"] + 8 * counters["ndis"] + 512 + 1536
         line["oracle_counters_per_read"] = counters
@@ -419,10 +481,10 @@ def run_ours(args):
     ach = bytes_per_read * n / (search_ms / 1e3) / 1e9
     # DRAM traffic per launch: dram__bytes_read.sum + dram__bytes_write.sum of one `ncu --set full` capture of each kernel on this
     # workload at 131072 reads (profiles/r1_ncu_*_v8.txt), scaled to this launch's read count
-    NCU_DRAM_BYTES_PER_READ = {"search": (7.248743e9 + 200.942e6) / 131072, "sw": (164.082e6 + 125.740e6) / 131072}
-    line["roofline_search"] = {"kernel": "hnswpq_search_reg_kernel", "bound": "hbm", "achieved": ach, "peak": hbm_peak, "unit": "GB/s",
+    NCU_DRAM_BYTES_PER_READ = {"search": (7.241585e9 + 202.415e6) / 131072, "sw": (164.082e6 + 125.740e6) / 131072}
+    line["roofline_search"] = {"kernel": "hnswpq_search_exact_kernel", "bound": "hbm", "achieved": ach, "peak": hbm_peak, "unit": "GB/s",
                                "frac": ach / hbm_peak, "traffic": NCU_DRAM_BYTES_PER_READ["search"] * n, "peak_source": peak_src,
-                               "traffic_source": "ncu capture at 131072 reads, scaled by reads (profiles/r1_ncu_hnswpq_search_reg_kernel_v8.txt)",
+                               "traffic_source": "ncu capture at 131072 reads, scaled by reads (profiles/r2_ncu_search_exact_v2.txt)",
                                "algorithmic_bytes_per_read": bytes_per_read, "ms_per_launch": search_ms}
     # issue roofline of the recurrence: 3.5 math instructions per s16x2 cell PAIR (add, max3, clamp, half a best-max3)
     # spread over the alu and fma pipes, each measured at 64 lanes/clk/SM (profiles/r1_ubench_pipes.txt) -> 2*64/3.5 pairs/clk/SM
@@ -442,24 +504,201 @@ def run_ours(args):
                         "cells_per_launch": cells, "ms_per_step": sw_ms,
                         "hbm_view": {"bound": "hbm", "achieved": sw_gbps, "peak": hbm_peak, "unit": "GB/s", "frac": sw_gbps / hbm_peak,
                                      "algorithmic_bytes_per_read": sw_bytes_per_read}}
+    if sharded_section is not None:
+        line["sharded"] = sharded_section
     emit(line)
     if world > 1:
         dist.destroy_process_group()
     return 0
 
 
+def sharded_arm(args, genome, ref, rank, world, local, dist, dense_reads_per_s_per_gpu=None, reads_total=None):
+    """The position-sharded workload through the library's data plane (drm_shards_open_rank / drm_shards_step_device /
+    drm_shards_search_rerank).  Rank g holds the windows [lo_g, hi_g) as its own HNSW-PQ graph; every rank sees the SAME read
+    batch (reads_total reads, strong scaling); per chunk: search on every shard -> lists to the owner of each read (fused
+    peer-memory dispatch | NCCL all-to-all | NCCL all-gather) -> merge -> SW rerank of the owner's slice.  Returns the
+    section dict on rank 0 (None elsewhere).  Collective: every rank must call it."""
+    import torch
+
+    import deepreadmapper_b200 as drm
+    from deepreadmapper_b200 import sharded, synth
+
+    n = int(reads_total or args.reads)
+    n_windows = 2 * (len(genome) - REF_LEN + 1)
+    bounds = sharded.shard_bounds(n_windows, world)
+    lo, hi = bounds[rank]
+    os.makedirs(args.cache, exist_ok=True)
+    paths = [os.path.join(args.cache, f"shard_g{len(genome)}_efc{args.efc}_{args.builder}_w{world}_r{r}.index") for r in range(world)]
+    t0 = time.time()
+    if not os.path.exists(paths[rank]):
+        sub = genome[lo // 2: hi // 2 + REF_LEN - 1]
+        nv, who = build_index_file(args, sub, paths[rank], f"cuda:{local}", seed=1234 + rank, threads=max(1, host_threads() // world))
+        assert nv == hi - lo, (nv, lo, hi)
+    build_s = time.time() - t0
+    barrier = (lambda: dist.barrier()) if world > 1 else (lambda: None)
+    barrier()
+    uid = [drm.Shards.unique_id() if (rank == 0 and world > 1) else None]
+    if world > 1:
+        dist.broadcast_object_list(uid, src=0)
+    sh = drm.Shards(paths[rank], lo, local, rank=rank, world=world, unique_id=uid[0])
+    log(f"rank {rank}: shard [{lo}, {hi}) on device ({sh.device_bytes / 1e9:.2f} GB image), built in {build_s:.1f}s, NCCL {sh.nccl_version}, peer mapping {bool(sh.peer_ok)}")
+    reads, truth, Q = make_reads(genome, n, seed=7)  # the same batch on every rank
+    q_off = np.arange(n + 1, dtype=np.int64) * REF_LEN
+    dQ = torch.from_numpy(Q).cuda()
+    dreads = torch.from_numpy(reads.reshape(-1)).cuda()
+    doff = torch.from_numpy(q_off).cuda()
+    chunks = sharded.read_chunks(n, args.chunk)
+    my_rows = sum((c1 - c0) * (rank + 1) // world - (c1 - c0) * rank // world for c0, c1 in chunks)
+    dS = torch.empty((max(my_rows, 1), K), dtype=torch.int32, device="cuda")
+    dIds = torch.empty((max(my_rows, 1), K), dtype=torch.int64, device="cuda")
+    dmin = torch.full((1,), 2**31 - 1, dtype=torch.int32, device="cuda")
+    dcells = torch.zeros(1, dtype=torch.int64, device="cuda")
+    keep = {}
+
+    def step(mode, profile=None):
+        out = 0
+        for c0, c1 in chunks:
+            Dp, Ip, slo, cnt, sp = sh.step_device(dQ[c0:c1].data_ptr(), c1 - c0, Q.shape[1], K, EF, mode)
+            if profile is not None:
+                es = torch.cuda.ExternalStream(sp)
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record(es)
+            if cnt > 0:
+                ref.rerank_device(1, Ip, cnt, K, dreads.data_ptr(), doff[c0 + slo:].data_ptr(), REF_LEN, 1, K, K,
+                                  dS[out:].data_ptr(), dIds[out:].data_ptr(), 0, dmin.data_ptr(), dcells.data_ptr(), sp)
+            if profile is not None:
+                e1.record(es)
+                sh.stats()  # synchronises the handle's stream and adds this step's search / exchange / merge times
+                profile["sw_ms"] += e0.elapsed_time(e1)
+            if c0 == 0:
+                keep["first"] = (Dp, Ip, slo, cnt, sp)
+            out += cnt
+        return keep["first"][4]
+
+    def sync():
+        sh.stats()  # cudaStreamSynchronize on the handle's stream
+
+    modes = [("fused", drm.XCHG_FUSED), ("alltoall", drm.XCHG_ALLTOALL), ("allgather", drm.XCHG_ALLGATHER)] if world > 1 else [("single", drm.XCHG_FUSED)]
+    results = {}
+    clocks = None
+    for mi, (name, mode) in enumerate(modes):
+        steps = args.steps if mi == 0 else max(2, min(args.steps, 3))
+        for _ in range(args.warmup if mi == 0 else max(1, min(args.warmup, 2))):
+            step(mode)
+        sync()
+        es = torch.cuda.ExternalStream(keep["first"][4])
+        barrier()
+        torch.cuda.synchronize()
+        sampler = ClockSampler(local) if (rank == 0 and mi == 0) else None
+        e_a, e_b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        t1 = time.perf_counter()
+        e_a.record(es)
+        for _ in range(steps):
+            step(mode)
+        e_b.record(es)
+        sync()
+        wall_ms = (time.perf_counter() - t1) * 1e3
+        barrier()
+        if sampler:
+            clocks = sampler.stop()
+        dev_ms = e_a.elapsed_time(e_b) / steps
+        # per-stage split: one more pass with a synchronisation after every chunk (so stage times can be read off)
+        sh.stats(reset=True)
+        prof = {"sw_ms": 0.0}
+        step(mode, profile=prof)
+        st = sh.stats(reset=True)
+        t = torch.tensor([dev_ms, wall_ms / steps, st["search_ms"], st["exchange_ms"], st["merge_ms"], prof["sw_ms"]], dtype=torch.float64, device="cuda")
+        rx = torch.tensor([float(st["bytes_received"])], dtype=torch.float64, device="cuda")
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            dist.all_reduce(rx, op=dist.ReduceOp.MAX)
+        tv = [float(v) for v in t.cpu()]
+        results[name] = {"reads_per_s": n / (tv[0] / 1e3), "ms_per_step": tv[0], "wall_ms_per_step": tv[1],
+                         "stages_ms_max_over_ranks": {"search": tv[2], "exchange": tv[3], "merge": tv[4], "sw_rerank": tv[5]},
+                         "list_bytes_received_per_rank_per_step": float(rx.item()),
+                         "exchange_gb_per_s_per_rank": (float(rx.item()) / (tv[3] / 1e3) / 1e9) if (tv[3] > 0 and name != "fused") else None,
+                         "steps": steps}
+    assert int(dmin.item()) >= K, "rerank saw fewer than K candidates"
+
+    # ---------------- parity on a sample: this rank's first slice against the oracle run the same sharded way
+    checks = {}
+    c0, c1 = chunks[0]
+    Dp, Ip, slo, cnt, sp = sh.step_device(dQ[c0:c1].data_ptr(), c1 - c0, Q.shape[1], K, EF, modes[0][1])
+    if cnt > 0:
+        ref.rerank_device(1, Ip, cnt, K, dreads.data_ptr(), doff[c0 + slo:].data_ptr(), REF_LEN, 1, K, K, dS.data_ptr(), dIds.data_ptr(), 0, dmin.data_ptr(),
+                          dcells.data_ptr(), sp)
+    sync()
+    ns = int(min(cnt, 512 if len(genome) <= 8_000_000 else 128))
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import shards_util as SU
+    from oracle import bindings as ob
+    from cuda import cudart
+    hDm = np.empty((ns, K), np.float32)
+    hIm = np.empty((ns, K), np.int64)
+    d2h = cudart.cudaMemcpyKind.cudaMemcpyDeviceToHost
+    assert cudart.cudaMemcpy(hDm.ctypes.data, Dp, ns * K * 4, d2h)[0] == cudart.cudaError_t.cudaSuccess
+    assert cudart.cudaMemcpy(hIm.ctypes.data, Ip, ns * K * 8, d2h)[0] == cudart.cudaError_t.cudaSuccess
+    rows = np.arange(slo, slo + ns)
+    th = max(1, host_threads() // world)
+    D0, I0 = SU.oracle_sharded_search(ob, paths, [b[0] for b in bounds], Q[rows], K, EF, threads=th)
+    checks["merged_lists_bit_exact_vs_sharded_oracle"] = bool(np.array_equal(hIm, I0) and np.array_equal(hDm.view(np.uint32), D0.view(np.uint32)))
+    rc, s0, i0, _ = ob.post_process_sw(1, I0, genome, len(genome), REF_LEN, [bytes(r) for r in reads[rows]], 1, K, K, threads=th, use_ref=ob.have_ref())
+    checks["sw_bit_exact_vs_reference_on_sample"] = bool(rc == 0 and np.array_equal(dS[:ns].cpu().numpy(), s0) and np.array_equal(dIds[:ns].cpu().numpy().astype(np.uint64), i0))
+    checks["sample_rows"] = ns
+    checks["merged_top1_is_planted_position"] = float((hIm[:, 0] >> 1 == (truth[rows] >> 1)).mean())
+    ok = torch.tensor([float(checks["merged_lists_bit_exact_vs_sharded_oracle"]), float(checks["sw_bit_exact_vs_reference_on_sample"])], device="cuda")
+    if world > 1:
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+    checks["all_ranks_bit_exact"] = bool(ok.min().item() == 1.0)
+
+    # ---------------- end to end through the host-buffer call (pinned host memory, copies inside the timed region)
+    hQ = torch.from_numpy(Q).pin_memory()
+    hreads = torch.from_numpy(reads.reshape(-1)).pin_memory()
+    hD = torch.empty((n, K), dtype=torch.float32).pin_memory()
+    hI = torch.empty((n, K), dtype=torch.int64).pin_memory()
+    hS = torch.empty((n, K), dtype=torch.int32).pin_memory()
+    hIds = torch.empty((n, K), dtype=torch.int64).pin_memory()
+
+    def e2e_step():
+        return sh.search_rerank(hQ.numpy(), K, EF, exchange=modes[0][1], chunk=args.chunk, ref=ref, mode=1, reads=(hreads.data_ptr(), q_off), stride=1, k=K,
+                                k_clusters=K, D=hD.numpy(), I=hI.numpy(), sw_scores=hS.numpy(), sw_ids=hIds.numpy().view(np.uint64))
+
+    e2e_step()
+    barrier()
+    t1 = time.perf_counter()
+    e2e_steps = max(2, min(args.steps, 3))
+    for _ in range(e2e_steps):
+        e2e_step()
+    te = torch.tensor([(time.perf_counter() - t1) * 1e3 / e2e_steps], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(te, op=dist.ReduceOp.MAX)
+    e2e_ms = float(te.item())
+    sh.close()
+    if rank != 0:
+        return None
+    best = results[modes[0][0]]
+    section = {"workload": ("configs[4] chromosome scale" if len(genome) > 100_000_000 else "configs[4] at E. coli size") +
+                           ": reference windows cut by position into one HNSW-PQ graph per GPU, every read searched on every shard, per-shard top-K lists "
+                           "exchanged over NVLink and merged on the GPU that owns the read, SW rerank on the owner",
+               "genome_bases": len(genome), "n_vectors": n_windows, "shards": world, "vectors_per_shard": hi - lo, "EF": EF, "K": K, "EFC": args.efc,
+               "reads_total": n, "chunk_reads": args.chunk, "scaling": "strong", "value": best["reads_per_s"], "unit": "reads/s", "ms_per_step": best["ms_per_step"],
+               "exchange_modes": results,
+               "e2e": {"value": n / (e2e_ms / 1e3), "unit": "reads/s", "mode": modes[0][0], "h2d_bytes_per_step_per_rank": int(Q.nbytes + (reads.nbytes + q_off.nbytes) // world),
+                       "d2h_bytes_per_step_per_rank": int(n // world * K * (4 + 8 + 4 + 8))},
+               "checks": checks, "clocks": clocks, "index_build_s_per_shard": build_s,
+               "vs_dense_reads_sharded_per_gpu": (best["reads_per_s"] / dense_reads_per_s_per_gpu) if dense_reads_per_s_per_gpu else None,
+               "note": "every GPU searches every read (that is what position sharding means), so search time does not shrink with N; only the merge and "
+                       "the SW rerank are divided by N.  strong-scaling efficiency = vs_dense_reads_sharded_per_gpu / N"}
+    return section
+
+
 def run_sharded(args):
-    """configs[4] (size set by --genome-bases; the default is the E. coli-sized genome, --genome-bases 31250000 at N = 1 is
-    one of the eight 62.5 M-vector shards of the 250 Mbp configuration): the reference windows are split by position
-    into WORLD shards (one HNSW-PQ graph per GPU), every rank searches every read of a chunk against its shard, the
-    per-shard top-K lists are exchanged with ONE all-gather (NCCL over NVLink) and merged per read by the CUDA merge
-    kernel; the SW rerank of the merged candidates is read-sharded again (genome replicated).  Total work is fixed as
-    N grows ("strong")."""
+    """Only the position-sharded arm (BASELINE.json configs[4]); DRM_BENCH_CHR=1 = the chromosome-scale configuration: a
+    250 Mbp random genome (both strands: ~500 M vectors, 62.5 M per GPU at N = 8) and 2 M reads per step."""
     import torch
     import torch.distributed as dist
 
     import deepreadmapper_b200 as drm
-    from deepreadmapper_b200 import sharded, synth
 
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -468,88 +707,18 @@ def run_sharded(args):
     if world > 1:
         import datetime
         dist.init_process_group("nccl", timeout=datetime.timedelta(minutes=60), device_id=torch.device(f"cuda:{local}"))
-    barrier = (lambda: dist.barrier()) if world > 1 else (lambda: None)
+    chr_scale = os.environ.get("DRM_BENCH_CHR") == "1"
+    if chr_scale:
+        args.genome_bases = int(os.environ.get("DRM_BENCH_CHR_BASES", 250_000_000))
+        args.reads = int(os.environ.get("DRM_BENCH_CHR_READS", 2_000_000))
     genome = make_genome(args)
-    n_windows = 2 * (len(genome) - REF_LEN + 1)
-    lo, hi = sharded.shard_bounds(n_windows, world)[rank]
-    os.makedirs(args.cache, exist_ok=True)
-    path = os.path.join(args.cache, f"shard_g{args.genome_bases}_efc{args.efc}_{args.builder}_w{world}_r{rank}.index")
-    if not os.path.exists(path):
-        t0 = time.time()
-        sub = genome[lo // 2: hi // 2 + REF_LEN - 1]
-        nv, who = build_index_file(args, sub, path, f"cuda:{local}", seed=1234 + rank, threads=max(1, host_threads() // world))
-        assert nv == hi - lo, (nv, lo, hi)
-        log(f"rank {rank}: shard [{lo}, {hi}) built in {time.time() - t0:.1f}s")
-    barrier()
-    ix = drm.Index(path, devices=[local])
     ref = drm.Reference(genome=genome, ref_len=REF_LEN, devices=[local])
-    n = args.reads
-    reads, truth, Q = make_reads(genome, n, seed=7)  # the same batch on every rank
-    q_off = np.arange(n + 1, dtype=np.int64) * REF_LEN
-    dQ = torch.from_numpy(Q).cuda()
-    dreads = torch.from_numpy(reads.reshape(-1)).cuda()
-    doff = torch.from_numpy(q_off).cuda()
-    searcher = sharded.ShardedSearcher(ix, lo, local)
-    stream = torch.cuda.current_stream()
-    chunks = sharded.read_chunks(n, args.chunk)
-    my_rows = sum(sharded.read_slice(c1 - c0, rank, world)[1] - sharded.read_slice(c1 - c0, rank, world)[0] for c0, c1 in chunks)
-    dS = torch.empty((max(my_rows, 1), K), dtype=torch.int32, device="cuda")
-    dIds = torch.empty((max(my_rows, 1), K), dtype=torch.int64, device="cuda")
-    dmin = torch.full((1,), 2**31 - 1, dtype=torch.int32, device="cuda")
-    dcells = torch.zeros(1, dtype=torch.int64, device="cuda")
-    keep = {}
-
-    def step():
-        out = 0
-        for c0, c1 in chunks:
-            D, I = searcher.search_chunk(dQ[c0:c1], K, EF)
-            a, b = sharded.read_slice(c1 - c0, rank, world)
-            if b > a:
-                ref.rerank_device(1, I[a:b].data_ptr(), b - a, K, dreads.data_ptr(), doff[c0 + a:].data_ptr(), REF_LEN, 1, K, K,
-                                  dS[out:].data_ptr(), dIds[out:].data_ptr(), 0, dmin.data_ptr(), dcells.data_ptr(), stream.cuda_stream)
-                out += b - a
-            keep["first"] = (D, I) if c0 == 0 else keep.get("first")
-
-    for _ in range(args.warmup):
-        step()
-    torch.cuda.synchronize()
-    dcells.zero_()
-    barrier()
-    torch.cuda.synchronize()
-    sampler = ClockSampler(local) if rank == 0 else None
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record(stream)
-    for _ in range(args.steps):
-        step()
-    e1.record(stream)
-    torch.cuda.synchronize()
-    barrier()
-    clocks = sampler.stop() if sampler else None
-    t = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device="cuda")
-    cells = dcells.to(torch.float64)
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        dist.all_reduce(cells, op=dist.ReduceOp.SUM)
-    assert int(dmin.item()) >= K
-    D0, I0 = keep["first"]
-    I0c = I0[:2048].cpu().numpy()
-    D0c = D0[:2048].cpu().numpy()
-    ok_sorted = bool((np.diff(D0c, axis=1) >= 0).all())
-    uniq = bool(all(len(set(r[r >= 0].tolist())) == int((r >= 0).sum()) for r in I0c))
-    top1 = float((I0c[:, 0] >> 1 == (truth[:2048] >> 1)).mean())
+    section = sharded_arm(args, genome, ref, rank, world, local, dist)
     if rank == 0:
-        ms = float(t.item()) / args.steps
-        line = {"metric": METRIC, "value": n / (ms / 1e3), "unit": "reads/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-                "ms_per_step": ms, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32 ADC distances + s16x2 SW",
-                "data": "synthetic",
-                "config": {"workload": "configs[4] scaled down: reference windows sharded by position over the GPUs (one HNSW-PQ graph per GPU), "
-                                       "every read searched on every shard, per-shard top-K all-gathered (NCCL) and merged on the device, SW rerank read-sharded",
-                           "genome_bases": args.genome_bases, "n_vectors": n_windows, "shards": world, "EF": EF, "K": K, "EFC": args.efc,
-                           "reads_total": n, "chunk_reads": args.chunk,
-                           "all_gather_bytes_per_rank_per_chunk": int(min(args.chunk, n)) * K * 12},
-                "gpu_launches": int(args.steps * len(chunks) * (2 + 3 * ((args.chunk // world + 131071) // 131072))), "clocks": clocks,
-                "sw_gcups": float(cells.item()) / args.steps / (ms / 1e3) / 1e9,
-                "checks": {"merged_rows_sorted": ok_sorted, "merged_ids_unique": uniq, "merged_top1_is_planted_position": top1}}
+        line = {"metric": METRIC, "value": section["value"], "unit": "reads/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+                "ms_per_step": section["ms_per_step"], "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+                "dtype": "f32 ADC distances + s16x2 SW", "data": "synthetic", "config": {"workload": section["workload"]},
+                "e2e": section["e2e"], "clocks": section["clocks"], "sharded": section}
         emit(line)
     if world > 1:
         dist.destroy_process_group()
@@ -660,6 +829,8 @@ def run_sparse(args):
 if __name__ == "__main__":
     a = parse()
     own_stdout()
+    if a.build_only:
+        sys.exit(run_build_only(a))
     if a.impl == "reference":
         sys.exit(run_reference(a))
     sys.exit(run_sharded(a) if a.workload == "sharded" else run_sparse(a) if a.workload == "sparse" else run_ours(a))

@@ -266,16 +266,23 @@ __device__ __forceinline__ void c_heap_pop(uint2 *C2, int k, int lane)
         }
         Bw[t] = __ballot_sync(FULL, first);
     }
-    int i = 1, mine = 1, L = 0;
-#pragma unroll 1
-    for (int j = 1; (i << 1) <= k; ++j) {
-        unsigned w = Bw[0];
+    // the path of larger children, read off the bits: node i -> 2i + (first ? 0 : 1).  Unrolled to the depth of a 64 * NB heap.
+    unsigned nB[NB];
 #pragma unroll
-        for (int t = 1; t < NB; ++t)
-            if (((i - 1) >> 5) == t) w = Bw[t];
-        i = (i << 1) + (((w >> ((i - 1) & 31)) & 1u) ? 0 : 1);
-        if (lane == j) mine = i;
-        L = j;
+    for (int t = 0; t < NB; ++t) nB[t] = ~Bw[t];
+    constexpr int DEPTH = NB == 1 ? 6 : NB == 2 ? 7 : 8;
+    int i = 1, mine = 1, L = 0;
+#pragma unroll
+    for (int j = 1; j <= DEPTH; ++j) {
+        if ((i << 1) <= k) {
+            unsigned w = nB[0];
+#pragma unroll
+            for (int t = 1; t < NB; ++t)
+                if (((i - 1) >> 5) == t) w = nB[t];
+            i = (i << 1) + (int)((w >> ((i - 1) & 31)) & 1u);
+            if (lane == j) mine = i;
+            L = j;
+        }
     }
     const uint2 v = C2[k];
     uint2 e = make_uint2(0u, 0u);
@@ -294,11 +301,12 @@ template <int NSR, bool FULLK>
 __device__ __forceinline__ void r_insert(unsigned (&rh)[NSR], unsigned (&rl)[NSR], unsigned &rthr, unsigned kd, unsigned kid, int lane, int k,
                                          int max_lane, int max_slot)
 {
+    const u64 kin = ((u64)kd << 32) | kid;
     bool lt[NSR];
 #pragma unroll
-    for (int s = 0; s < NSR; ++s) lt[s] = rh[s] < kd || (rh[s] == kd && rl[s] < kid);
+    for (int s = 0; s < NSR; ++s) lt[s] = (((u64)rh[s] << 32) | rl[s]) < kin;
     const unsigned ph = __shfl_up_sync(FULL, rh[NSR - 1], 1), pl = __shfl_up_sync(FULL, rl[NSR - 1], 1);
-    const bool plt = lane == 0 || ph < kd || (ph == kd && pl < kid);
+    const bool plt = lane == 0 || (((u64)ph << 32) | pl) < kin;
 #pragma unroll
     for (int s = NSR - 1; s >= 1; --s) {
         rh[s] = lt[s] ? rh[s] : (lt[s - 1] ? kd : rh[s - 1]);

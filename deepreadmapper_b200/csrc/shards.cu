@@ -110,6 +110,7 @@ struct ShardRank {
     cudaEvent_t ev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};           // stage boundaries of the last step
     double ms_search = 0, ms_xchg = 0, ms_merge = 0, ms_rerank = 0;
     int64_t bytes_rx = 0;
+    bool times_pending = false;  // the last step's stage events have not been added to the sums yet
 };
 
 void free_rank_buffers(ShardRank &r)
@@ -230,6 +231,7 @@ int rank_step(drm_shards *h, ShardRank &r, const float *q_dev, int64_t n, int k,
     if (rc != DRM_OK) return rc;
     const int slot = (int)(r.step & 1);
     ++r.step;
+    r.times_pending = true;
     const int64_t lo = slice_lo(n, r.rank, W), cnt = slice_lo(n, r.rank + 1, W) - lo;
     *lo_out = lo; *cnt_out = cnt;
     DRM_CUDA_TRY(cudaEventRecord(r.ev[0], r.s));
@@ -295,6 +297,7 @@ int rank_step(drm_shards *h, ShardRank &r, const float *q_dev, int64_t n, int k,
 
 void add_stage_times(ShardRank &r, bool with_rerank)
 {
+    r.times_pending = false;
     float a = 0, b = 0, c = 0, d = 0;
     cudaEventElapsedTime(&a, r.ev[0], r.ev[1]);
     cudaEventElapsedTime(&b, r.ev[1], r.ev[2]);
@@ -483,6 +486,7 @@ int drm_shards_stats(drm_shards *h, int local_rank, int reset, drm_shard_stats *
     ShardRank &r = *h->local[(size_t)local_rank];
     DRM_CUDA_TRY(cudaSetDevice(r.device));
     DRM_CUDA_TRY(cudaStreamSynchronize(r.s));
+    if (r.times_pending) add_stage_times(r, false);  // a drm_shards_step_device step (search / exchange / merge only)
     int64_t c[4] = {0, 0, 0, 0};
     DRM_CUDA_TRY(cudaMemcpy(c, r.counters, sizeof c, cudaMemcpyDeviceToHost));
     st->search_ms = r.ms_search; st->exchange_ms = r.ms_xchg; st->merge_ms = r.ms_merge; st->rerank_ms = r.ms_rerank;

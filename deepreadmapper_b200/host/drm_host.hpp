@@ -26,6 +26,7 @@
 struct drm_index;
 struct drm_ref;
 struct drm_embedder;
+struct drm_shards;
 
 // includes/utils/config.hpp:6-57 (only the constants the path uses)
 namespace Config {
@@ -52,6 +53,22 @@ IndexHNSWPQ *read_index(const char *index_file);
 
 std::pair<std::vector<std::vector<faiss::idx_t>>, std::vector<std::vector<float>>> faiss_search(
     faiss::IndexHNSWPQ *index, const std::vector<std::vector<float>> &query_data, int k = Config::Search::K, int ef = Config::Search::EF);
+
+// Position-sharded index (additive; BASELINE.json configs[4]): one IHNp file per GPU, written by `hnswpq_index` under
+// DRM_SHARDS=<W> as <prefix>/<basename>.shard<g>.index with the config keys n_shards and shard_<g>_id_lo.  One call where the
+// reference calls faiss_search once (src/main.cpp:278): every shard searches every read, the per-shard lists are merged on
+// the GPU that owns the read, and - when `genome` is not empty - that GPU SW-reranks its reads.  exchange = DRM_XCHG from
+// the environment ("allgather" | "alltoall" | "fused", default fused).
+struct ShardedIndex {
+    drm_shards *handle = nullptr;
+    int world = 0;
+    std::vector<int> devices;
+    ~ShardedIndex();
+};
+ShardedIndex *read_index_sharded(const std::string &index_prefix, const std::unordered_map<std::string, std::variant<size_t, float, std::string>> &config);
+void sharded_search_rerank_flat(ShardedIndex *index, const float *q, int64_t n, int d, int k_search, int ef, int mode, const std::string &genome,
+                                size_t ref_len, const std::vector<std::string> &query_seqs, size_t stride, size_t k, size_t k_clusters,
+                                std::vector<faiss::idx_t> &I, std::vector<float> &D, std::vector<int> &sw_scores, std::vector<size_t> &sw_ids);
 
 // Flat form used by the pipeline for large batches (no nested vectors): q is n x d row-major.
 void faiss_search_flat(faiss::IndexHNSWPQ *index, const float *q, int64_t n, int d, int k, int ef, std::vector<faiss::idx_t> &I, std::vector<float> &D);

@@ -15,6 +15,9 @@
 //   * DRM_RERANK=l2 runs the reference's ACTIVE post-process instead (post_process_l2_dynamic / _static, src/main.cpp:313-331)
 //     over drm_l2_rerank: candidate windows embedded and ranked by L2 distance on the device; result in NEW flat files
 //     l2_distances.npy ('<f4') and l2_indices.npy ('<u8'), laid out like the reference's final_dists / final_ids;
+//   * an index built with DRM_SHARDS=<W> (config key n_shards; BASELINE.json configs[4]) is searched position-sharded over W
+//     GPUs: one drm_shards_search_rerank call (search on every shard, lists exchanged over NVLink - DRM_XCHG=fused|alltoall|
+//     allgather - merged and SW-reranked on the GPU that owns the read);
 //   * both SW modes rerank from the cleaned genome on the device: use_dynamic=0 applies the static bound rule (number of
 //     dense windows), use_dynamic=1 the dynamic one (genome length) - the two rules of find_sequences.
 #include <chrono>
@@ -85,7 +88,9 @@ int main(int argc, char *argv[])
         // reference's host parsing and the two separate stages).
         const std::string qext = std::filesystem::path(query_input_file).extension().string();
         const char *input_mode = getenv("DRM_INPUT");
-        const bool device_inputs = !is_npy && rerank && !rerank_l2 && (qext == ".fastq" || qext == ".fq") && !(input_mode && !strcmp(input_mode, "host"));
+        const bool sharded = config.count("n_shards") && std::holds_alternative<size_t>(config["n_shards"]) && std::get<size_t>(config["n_shards"]) > 1;
+        if (sharded && rerank_l2) throw std::runtime_error("DRM_RERANK=l2 is not available on a position-sharded index");
+        const bool device_inputs = !sharded && !is_npy && rerank && !rerank_l2 && (qext == ".fastq" || qext == ".fq") && !(input_mode && !strcmp(input_mode, "host"));
         if (!is_npy) {
             if (!device_inputs) {
                 std::tie(query_sequences, query_ids) = read_file(query_input_file);
@@ -149,8 +154,15 @@ int main(int argc, char *argv[])
         std::cout << "[MAIN] Index file: " << index_file << std::endl;
         std::cout << "[MAIN] EF: " << ef << std::endl;
         t0 = Clock::now();
-        if (!std::filesystem::exists(index_file)) throw std::runtime_error("Index file does not exist: " + index_file);
-        faiss::IndexHNSWPQ *alg_hnsw = faiss::read_index(index_file.c_str());
+        faiss::IndexHNSWPQ *alg_hnsw = nullptr;
+        ShardedIndex *alg_shards = nullptr;
+        if (sharded) {
+            alg_shards = read_index_sharded(index_prefix, config);
+            std::cout << "[MAIN] Position-sharded index: " << alg_shards->world << " shards, one per GPU" << std::endl;
+        } else {
+            if (!std::filesystem::exists(index_file)) throw std::runtime_error("Index file does not exist: " + index_file);
+            alg_hnsw = faiss::read_index(index_file.c_str());
+        }
         std::cout << "[MAIN] Index loading time: " << ms_since(t0) << " ms" << std::endl << std::endl;
 
         // ---------------- search
@@ -162,7 +174,14 @@ int main(int argc, char *argv[])
         std::vector<size_t> sw_ids;
         std::vector<float> l2_dists;
         std::vector<size_t> l2_ids;
-        if (device_inputs) {
+        bool rerank_done = false;
+        if (sharded) {
+            const bool with_sw = !is_npy && rerank;
+            sharded_search_rerank_flat(alg_shards, emb, (int64_t)num_queries, (int)dim, k_clusters, ef, use_dynamic ? 1 : 0, with_sw ? ref_genome : std::string(),
+                                       ref_len, query_sequences, stride, (size_t)k, (size_t)k_clusters, I, D, sw_scores, sw_ids);
+            rerank_done = with_sw;
+            std::cout << "[MAIN] Sharded HNSW search" << (with_sw ? " + SW rerank" : "") << " time (one call): " << ms_since(t0) << " ms" << std::endl << std::endl;
+        } else if (device_inputs) {
             stage_device_inputs(alg_hnsw, query_input_file, ref_seqs_file, emb, (int64_t)num_queries,
                                 (int)dim, k_clusters, ef, use_dynamic ? 1 : 0, ref_len, stride, (size_t)k, (size_t)k_clusters, I, D, sw_scores, sw_ids);
             std::cout << "[MAIN] HNSW search + SW rerank time (one call, device-side inputs): " << ms_since(t0) << " ms" << std::endl << std::endl;
@@ -171,11 +190,12 @@ int main(int argc, char *argv[])
             std::cout << "[MAIN] HNSW search time: " << ms_since(t0) << " ms" << std::endl << std::endl;
         }
         delete alg_hnsw;
+        delete alg_shards;
 
         // ---------------- post-processing (Smith-Waterman rerank)
         std::cout << "[MAIN] POST-PROCESSING STEP" << std::endl;
         t0 = Clock::now();
-        if (device_inputs) {
+        if (device_inputs || rerank_done) {
             std::cout << "[MAIN] Post-processing ran inside the search call" << std::endl;
         } else if (!is_npy && rerank_l2) {
             const std::string model_path = embedder_model_path();
@@ -184,7 +204,7 @@ int main(int argc, char *argv[])
             post_process_l2_flat(use_dynamic ? 1 : 0, ref_genome, ref_sequences, ref_len, I, D, (int64_t)num_queries, k_clusters, emb, vectorizer, stride,
                                  (size_t)k, (size_t)k_clusters, l2_dists, l2_ids);
             std::cout << "[MAIN] L2 rerank: " << l2_ids.size() << " final candidates" << std::endl;
-        } else if (!is_npy && rerank) {
+        } else if (!is_npy && rerank && !sharded) {
             post_process_sw_flat(use_dynamic ? 1 : 0, ref_genome, ref_len, I, (int64_t)num_queries, k_clusters, query_sequences, stride, (size_t)k,
                                  (size_t)k_clusters, sw_scores, sw_ids);
         } else {

@@ -1,6 +1,8 @@
 // The two stages of the hot path behind the reference's own C++ signatures, over the C ABI (include/drm_b200.h).
 // No arithmetic of the path happens here: these functions flatten the STL containers the reference passes around,
 // call libdrm_cuda.so, and rebuild the containers the reference returns.
+#include <filesystem>
+#include <variant>
 #include "drm_host.hpp"
 
 #include <algorithm>
@@ -43,10 +45,28 @@ void flatten(const std::vector<std::string> &v, std::string &flat, std::vector<i
     for (const auto &s : v) flat += s;
 }
 
-// One reference handle is kept alive between calls: the pipeline reranks against the same genome / window table.
+// One reference handle is kept alive between calls: the pipeline reranks against the same genome / window table.  The
+// cache is keyed on the CONTENT (length + 64-bit hash of every byte), never on an address: a caller may refill a buffer
+// in place, or a freed vector may come back at the same address with other windows in it.
+uint64_t content_hash(const char *p, size_t n, uint64_t h)
+{
+    const uint64_t m = 0x9e3779b97f4a7c15ull;
+    size_t i = 0;
+    for (; i + 8 <= n; i += 8) {
+        uint64_t w;
+        memcpy(&w, p + i, 8);
+        h = (h ^ w) * m;
+        h ^= h >> 29;
+    }
+    uint64_t tail = 0;
+    if (i < n) memcpy(&tail, p + i, n - i);
+    h = (h ^ tail ^ (uint64_t)n) * m;
+    return h ^ (h >> 32);
+}
+
 struct RefCache {
     drm_ref *h = nullptr;
-    const void *key = nullptr;
+    uint64_t hash = 0;
     size_t len = 0, ref_len = 0;
     int form = -1;
     ~RefCache() { if (h) drm_ref_close(h); }
@@ -54,27 +74,33 @@ struct RefCache {
 
 drm_ref *genome_ref(const std::string &genome, size_t ref_len)
 {
-    if (g_ref.h && g_ref.form == 0 && g_ref.key == genome.data() && g_ref.len == genome.size() && g_ref.ref_len == ref_len) return g_ref.h;
+    const uint64_t hs = content_hash(genome.data(), genome.size(), 1);
+    if (g_ref.h && g_ref.form == 0 && g_ref.hash == hs && g_ref.len == genome.size() && g_ref.ref_len == ref_len) return g_ref.h;
     if (g_ref.h) { drm_ref_close(g_ref.h); g_ref.h = nullptr; }
     const std::vector<int> devs = device_list();
     if (drm_ref_open_genome(genome.data(), (int64_t)genome.size(), (int)ref_len, devs.data(), (int)devs.size(), &g_ref.h) != DRM_OK) throw_last();
-    g_ref.form = 0; g_ref.key = genome.data(); g_ref.len = genome.size(); g_ref.ref_len = ref_len;
+    g_ref.form = 0; g_ref.hash = hs; g_ref.len = genome.size(); g_ref.ref_len = ref_len;
     return g_ref.h;
 }
 
-drm_ref *table_ref(const std::vector<std::string> &ref_seqs, size_t ref_len)
+// strip = 1: the strings are '<' + window + '>' and the device table holds the bare windows
+drm_ref *table_ref(const std::vector<std::string> &ref_seqs, size_t ref_len, size_t strip = 0)
 {
-    if (g_ref.h && g_ref.form == 1 && g_ref.key == ref_seqs.data() && g_ref.len == ref_seqs.size() && g_ref.ref_len == ref_len) return g_ref.h;
+    uint64_t hs = 2 + strip;
+    for (const auto &s : ref_seqs) {
+        if (s.size() != ref_len + 2 * strip || (strip && (s.front() != '<' || s.back() != '>')))
+            throw std::runtime_error(strip ? "post_process_l2_static: reference sequences must be '<' + ref_len bases + '>'"
+                                           : "post_process_sw_static: reference windows must all be ref_len long");
+        hs = content_hash(s.data() + strip, ref_len, hs);
+    }
+    if (g_ref.h && g_ref.form == 1 && g_ref.hash == hs && g_ref.len == ref_seqs.size() && g_ref.ref_len == ref_len) return g_ref.h;
     if (g_ref.h) { drm_ref_close(g_ref.h); g_ref.h = nullptr; }
     std::string flat;
     flat.reserve(ref_seqs.size() * ref_len);
-    for (const auto &s : ref_seqs) {
-        if (s.size() != ref_len) throw std::runtime_error("post_process_sw_static: reference windows must all be ref_len long");
-        flat += s;
-    }
+    for (const auto &s : ref_seqs) flat.append(s, strip, ref_len);
     const std::vector<int> devs = device_list();
     if (drm_ref_open_windows(flat.data(), (int64_t)ref_seqs.size(), (int)ref_len, devs.data(), (int)devs.size(), &g_ref.h) != DRM_OK) throw_last();
-    g_ref.form = 1; g_ref.key = ref_seqs.data(); g_ref.len = ref_seqs.size(); g_ref.ref_len = ref_len;
+    g_ref.form = 1; g_ref.hash = hs; g_ref.len = ref_seqs.size(); g_ref.ref_len = ref_len;
     return g_ref.h;
 }
 
@@ -143,6 +169,75 @@ IndexHNSWPQ *read_index(const char *index_file)
 }
 
 }  // namespace faiss
+
+// ------------------------------------------------------------------------------------------ position-sharded index
+ShardedIndex::~ShardedIndex() { if (handle) drm_shards_close(handle); }
+
+ShardedIndex *read_index_sharded(const std::string &index_prefix, const std::unordered_map<std::string, std::variant<size_t, float, std::string>> &config)
+{
+    auto get = [&](const std::string &key) -> size_t {
+        auto it = config.find(key);
+        if (it == config.end() || !std::holds_alternative<size_t>(it->second)) throw std::runtime_error("config.txt: missing key " + key + " (index not built with DRM_SHARDS)");
+        return std::get<size_t>(it->second);
+    };
+    const size_t W = get("n_shards");
+    const std::string base = std::filesystem::path(index_prefix).filename().string();
+    std::vector<std::string> files;
+    std::vector<int64_t> lo;
+    for (size_t g = 0; g < W; ++g) {
+        files.push_back(index_prefix + "/" + base + ".shard" + std::to_string(g) + ".index");
+        if (!std::filesystem::exists(files.back())) throw std::runtime_error("Index file does not exist: " + files.back());
+        lo.push_back((int64_t)get("shard_" + std::to_string(g) + "_id_lo"));
+    }
+    std::vector<int> devs = device_list();
+    if (devs.size() < W) throw std::runtime_error("the index has " + std::to_string(W) + " position shards but only " + std::to_string(devs.size()) + " GPU(s) are visible");
+    devs.resize(W);
+    std::vector<const char *> cfiles;
+    for (auto &f : files) cfiles.push_back(f.c_str());
+    drm_shards *h = nullptr;
+    if (drm_shards_open(cfiles.data(), lo.data(), devs.data(), (int)W, &h) != DRM_OK) throw_last();
+    auto *ix = new ShardedIndex;
+    ix->handle = h; ix->world = (int)W; ix->devices = devs;
+    return ix;
+}
+
+void sharded_search_rerank_flat(ShardedIndex *index, const float *q, int64_t n, int d, int k_search, int ef, int mode, const std::string &genome,
+                                size_t ref_len, const std::vector<std::string> &query_seqs, size_t stride, size_t k, size_t k_clusters,
+                                std::vector<faiss::idx_t> &I, std::vector<float> &D, std::vector<int> &sw_scores, std::vector<size_t> &sw_ids)
+{
+    if (!index || !index->handle) throw std::runtime_error("faiss_search: null index");
+    if (n <= 0) throw std::runtime_error("Query data is empty");
+    int exchange = DRM_XCHG_FUSED;
+    if (const char *e = getenv("DRM_XCHG")) {
+        const std::string v = e;
+        if (v == "allgather") exchange = DRM_XCHG_ALLGATHER;
+        else if (v == "alltoall") exchange = DRM_XCHG_ALLTOALL;
+        else if (v != "fused") throw std::runtime_error("DRM_XCHG must be allgather, alltoall or fused");
+    }
+    I.resize((size_t)n * k_search);
+    D.resize((size_t)n * k_search);
+    const bool rerank = !genome.empty();
+    drm_ref *ref = nullptr;
+    std::string flat;
+    std::vector<int64_t> off;
+    if (rerank) {
+        if ((int64_t)query_seqs.size() != n) throw std::runtime_error("Error: number of embeddings differs from the number of query sequences");
+        if (drm_ref_open_genome(genome.data(), (int64_t)genome.size(), (int)ref_len, index->devices.data(), (int)index->devices.size(), &ref) != DRM_OK) throw_last();
+        off.resize((size_t)n + 1, 0);
+        size_t total = 0;
+        for (auto &sq : query_seqs) total += sq.size();
+        flat.reserve(total);
+        for (int64_t i = 0; i < n; ++i) { flat += query_seqs[(size_t)i]; off[(size_t)i + 1] = (int64_t)flat.size(); }
+        sw_scores.resize((size_t)n * k);
+        sw_ids.resize((size_t)n * k);
+    }
+    static_assert(sizeof(size_t) == sizeof(uint64_t), "size_t is 64-bit");
+    const int rc = drm_shards_search_rerank(index->handle, ref, mode, q, n, d, k_search, ef, rerank ? flat.data() : nullptr, rerank ? off.data() : nullptr,
+                                            (int64_t)stride, (int64_t)k, (int64_t)k_clusters, exchange, 0, D.data(), I.data(),
+                                            rerank ? sw_scores.data() : nullptr, rerank ? reinterpret_cast<uint64_t *>(sw_ids.data()) : nullptr, nullptr);
+    if (ref) drm_ref_close(ref);
+    if (rc != DRM_OK) throw_last();
+}
 
 void faiss_search_flat(faiss::IndexHNSWPQ *index, const float *q, int64_t n, int d, int k, int ef, std::vector<faiss::idx_t> &I, std::vector<float> &D)
 {
@@ -499,25 +594,13 @@ std::tuple<std::vector<std::string>, std::vector<float>, std::vector<size_t>> po
     // puts the decoration back: device mode 0) or the bare windows of read_file(..., lookup_mode = true), which the reference's
     // main passes (src/main.cpp:190) and embeds as they are: device mode 2
     const bool lookup_windows = !ref_seqs.empty() && ref_seqs[0].size() == ref_len;
-    static std::vector<std::string> bare;
-    static const void *bare_key = nullptr;
-    if (!lookup_windows && (bare_key != ref_seqs.data() || bare.size() != ref_seqs.size())) {
-        bare.resize(ref_seqs.size());
-        for (size_t i = 0; i < ref_seqs.size(); ++i) {
-            const std::string &s = ref_seqs[i];
-            if (s.size() != ref_len + 2 || s.front() != '<' || s.back() != '>')
-                throw std::runtime_error("post_process_l2_static: reference sequences must be '<' + ref_len bases + '>'");
-            bare[i] = s.substr(1, ref_len);
-        }
-        bare_key = ref_seqs.data();
-    }
     std::vector<int64_t> nb; std::vector<float> ds, qe; int64_t k_in = 0;
     l2_inputs(neighbors, distances, query_embeddings, nb, ds, qe, k_in);
     const int64_t n = (int64_t)query_embeddings.size();
     std::vector<float> scores((size_t)n * std::max(k, k_clusters) + 1);
     std::vector<uint64_t> ids(scores.size());
     int64_t count = 0;
-    if (n && drm_l2_rerank(vectorizer.handle(), table_ref(lookup_windows ? ref_seqs : bare, ref_len), lookup_windows ? 2 : 0, nb.data(), ds.data(), n, k_in, qe.data(), (int64_t)stride, (int64_t)k,
+    if (n && drm_l2_rerank(vectorizer.handle(), table_ref(ref_seqs, ref_len, lookup_windows ? 0 : 1), lookup_windows ? 2 : 0, nb.data(), ds.data(), n, k_in, qe.data(), (int64_t)stride, (int64_t)k,
                            (int64_t)k_clusters, scores.data(), ids.data(), &count) != DRM_OK)
         throw_last();
     std::vector<std::string> seqs((size_t)count);
@@ -533,7 +616,6 @@ void post_process_l2_flat(int mode, const std::string &genome, const std::vector
                           const std::vector<faiss::idx_t> &I, const std::vector<float> &D, int64_t n, int64_t k_in, const float *q_emb,
                           Vectorizer &vectorizer, size_t stride, size_t k, size_t k_clusters, std::vector<float> &dists, std::vector<size_t> &ids)
 {
-    static std::vector<std::string> bare;
     drm_ref *ref = nullptr;
     if (mode == 1) {
         ref = genome_ref(genome, ref_len);
@@ -541,21 +623,8 @@ void post_process_l2_flat(int mode, const std::string &genome, const std::vector
         // read_file(..., lookup_mode = true) - what the reference's main passes (src/main.cpp:190) - returns bare windows, which
         // the reference then embeds as they are: device mode 2.  A decorated table ('<' window '>') is device mode 0.
         const bool decorated = !ref_windows.empty() && ref_windows[0].size() == ref_len + 2;
-        if (decorated) {
-            bare.resize(ref_windows.size());
-            for (size_t i = 0; i < ref_windows.size(); ++i) {
-                const std::string &s = ref_windows[i];
-                if (s.size() != ref_len + 2 || s.front() != '<' || s.back() != '>')
-                    throw std::runtime_error("post_process_l2_static: reference sequences must be '<' + ref_len bases + '>'");
-                bare[i] = s.substr(1, ref_len);
-            }
-            // `bare` is reused between calls, so its address says nothing about its content: drop the cached device table
-            if (g_ref.h && g_ref.form == 1 && g_ref.key == bare.data()) { drm_ref_close(g_ref.h); g_ref.h = nullptr; }
-            ref = table_ref(bare, ref_len);
-        } else {
-            ref = table_ref(ref_windows, ref_len);
-            mode = 2;
-        }
+        ref = table_ref(ref_windows, ref_len, decorated ? 1 : 0);
+        if (!decorated) mode = 2;
     }
     dists.assign((size_t)n * std::max(k, k_clusters) + 1, 0.0f);
     std::vector<uint64_t> u(dists.size());

@@ -200,16 +200,26 @@ template <class TI> size_t heap_reorder(size_t k, float *val, TI *ids)
     return nel;
 }
 
+// analysis counters (tools only), see orc_tie_counters
+static std::atomic<long long> g_tie_queries{0}, g_tie_total{0}, g_tie_popped_queries{0};
+
 // ---- HNSW::MinimaxHeap ----
 struct MinimaxHeap {
     int n, k = 0, nvalid = 0;
     std::vector<int32_t> ids;
     std::vector<float> dis;
     explicit MinimaxHeap(int n_) : n(n_), ids((size_t)n_), dis((size_t)n_) {}
+    int tie_evict = 0, tie_evict_popped = 0;  // analysis: evictions whose worst distance is shared / shared with a popped entry
     void push(int32_t i, float v)
     {
         if (k == n) {
             if (v >= dis[0]) return;
+            {
+                bool tie = false, popped = ids[0] == -1;
+                for (int c = 1; c <= 2 && c < k; ++c)
+                    if (dis[(size_t)c] == dis[0]) { tie = true; popped = popped || ids[(size_t)c] == -1; }
+                if (tie) { tie_evict++; if (popped) { tie_evict_popped++; } }
+            }
             if (ids[0] != -1) --nvalid;
             heap_pop<int32_t>((size_t)k--, dis.data(), ids.data());
         }
@@ -328,6 +338,9 @@ void search_one(const OrcIndex &ix, const float *x, int k, int efSearch, int tie
     }
     vt.advance();
     heap_reorder<int64_t>((size_t)k, D, I);
+    g_tie_total++;
+    if (cand.tie_evict) g_tie_queries++;
+    if (cand.tie_evict_popped) g_tie_popped_queries++;
 }
 
 // CANONICAL tie rule (tie_rule = 1): the same search, but every comparison that FAISS makes on the
@@ -347,7 +360,7 @@ static std::atomic<long long> g_spec2_yes{0}, g_spec2_total{0};
 // Analysis counter (tools only): queries of the canonical search in which at least one decision compared two EQUAL
 // distances (pop order among equal minima, a candidate equal to the worst kept distance, an eviction among equal worst
 // distances) - the only places where FAISS's rule can decide differently (orc_tie_counters).
-static std::atomic<long long> g_tie_queries{0}, g_tie_total{0};
+
 
 void search_one_canonical(const OrcIndex &ix, const float *x, int k, int efSearch, VisitedTable &vt,
                           std::vector<float> &T, float *D, int64_t *I, Stats &st)
@@ -446,8 +459,8 @@ void orc_spec2_counters(int64_t *out, int reset)
 
 void orc_tie_counters(int64_t *out, int reset)
 {
-    out[0] = g_tie_queries.load(); out[1] = g_tie_total.load();
-    if (reset) { g_tie_queries = 0; g_tie_total = 0; }
+    out[0] = g_tie_queries.load(); out[1] = g_tie_total.load(); out[2] = g_tie_popped_queries.load();
+    if (reset) { g_tie_queries = 0; g_tie_total = 0; g_tie_popped_queries = 0; }
 }
 
 void *orc_index_read(const char *path)

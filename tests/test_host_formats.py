@@ -149,13 +149,34 @@ def test_config_txt_round_trip_with_the_reference(tool, R, tmp_path):
 
 
 def test_hnswpq_index_cli_writes_the_reference_layout(R, ob, tmp_path):
-    """hnswpq_index <emb.npy> <prefix> <ref_len> ... -> <prefix>/<prefix>.index + config.txt (host OpenMP build, no GPU)."""
+    """hnswpq_index <emb.npy> <prefix> <ref_len> ... -> <prefix>/<prefix>.index + config.txt.  The CLI builds on the GPU and has
+    no silent fallback: without a device it fails loudly unless DRM_BUILD=cpu opts into the host OpenMP builder (used here);
+    DRM_SHARDS=<W> writes W position shards and the config keys `pipeline` reads."""
     from deepreadmapper_b200 import synth
     g = synth.random_genome(3000, 5)
     np.save(tmp_path / "ref.npy", synth.embed_windows(g))
     exe = os.path.join(BIN, "hnswpq_index")
-    r = subprocess.run([exe, "ref.npy", "myidx", "150", "1", "8", "8", "16", "40"], cwd=tmp_path, capture_output=True, text=True)
+    import deepreadmapper_b200 as drm
+    env_cpu = dict(os.environ, DRM_BUILD="cpu")
+    if drm.lib().drm_device_count() == 0:
+        env_none = {k: v for k, v in os.environ.items() if k != "DRM_BUILD"}
+        r = subprocess.run([exe, "ref.npy", "myidx", "150", "1", "8", "8", "16", "40"], cwd=tmp_path, capture_output=True, text=True, env=env_none)
+        assert r.returncode == 1 and "no CUDA device" in r.stderr and "DRM_BUILD=cpu" in r.stderr
+    r = subprocess.run([exe, "ref.npy", "myidx", "150", "1", "8", "8", "16", "40"], cwd=tmp_path, capture_output=True, text=True, env=env_cpu)
     assert r.returncode == 0, r.stderr
+    # position shards: 3 files with local labels + n_shards / shard_<g>_id_lo in config.txt
+    r = subprocess.run([exe, "ref.npy", "shidx", "150", "1", "8", "8", "16", "40"], cwd=tmp_path, capture_output=True, text=True, env=dict(env_cpu, DRM_SHARDS="3"))
+    assert r.returncode == 0, r.stderr
+    scfg = str(tmp_path / "shidx" / "config.txt").encode()
+    assert R.ref_load_config_size(scfg, b"n_shards") == 3 and R.ref_load_config_size(scfg, b"shard_0_id_lo") == 0
+    n_all, tot = 2 * (3000 - 149), 0
+    for g_ in range(3):
+        lo = R.ref_load_config_size(scfg, b"shard_%d_id_lo" % g_)
+        assert lo % 2 == 0 and lo == 2 * (((n_all + 1) // 2) * g_ // 3)
+        so = ob.OracleIndex(str(tmp_path / "shidx" / f"shidx.shard{g_}.index"))
+        assert so.validate() == 0
+        tot += so.ntotal
+    assert tot == n_all
     cfg = str(tmp_path / "myidx" / "config.txt").encode()
     assert R.ref_load_config_size(cfg, b"ref_len") == 150 and R.ref_load_config_size(cfg, b"stride") == 1
     assert R.ref_load_config_size(cfg, b"n_vects") == 2 * (3000 - 149) and R.ref_load_config_size(cfg, b"EFC") == 40

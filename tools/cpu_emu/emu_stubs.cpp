@@ -40,3 +40,20 @@ int drm_build_index_gpu_device(const float *, int64_t, int, int64_t, int, int, i
     return drm::fail(DRM_EUNSUPPORTED, "the GPU index builder is not available in the host-thread emulation");
 }
 }
+
+// C-ABI entry points of shards.cu (NCCL, peer memory): not emulated
+extern "C" {
+static int no_shards() { return drm::fail(DRM_EUNSUPPORTED, "the position-sharded data plane (NCCL / peer memory) is not available in the host-thread emulation"); }
+int drm_shards_open(const char *const *, const int64_t *, const int *, int, drm_shards **) { return no_shards(); }
+int drm_shards_unique_id(void *) { return no_shards(); }
+int drm_shards_open_rank(const char *, int64_t, int, int, int, const void *, drm_shards **) { return no_shards(); }
+void drm_shards_close(drm_shards *) {}
+int drm_shards_info(const drm_shards *, int64_t *) { return no_shards(); }
+int drm_shards_search_rerank(drm_shards *, drm_ref *, int, const float *, int64_t, int, int, int, const char *, const int64_t *, int64_t, int64_t, int64_t, int,
+                             int64_t, float *, int64_t *, int32_t *, uint64_t *, drm_shard_stats *) { return no_shards(); }
+int drm_shards_step_device(drm_shards *, int, const float *, int64_t, int, int, int, int, void *, const float **, const int64_t **, int64_t *, int64_t *, void **)
+{
+    return no_shards();
+}
+int drm_shards_stats(drm_shards *, int, int, drm_shard_stats *) { return no_shards(); }
+}
