@@ -580,12 +580,32 @@ def post_process_l2_static(neighbors, distances, ref: "Reference", query_embeddi
 
 
 # ---- position-sharded index (BASELINE.json configs[4]) ------------------------------------------------
+def _prefer_bundled_nccl():
+    """libdrm_cuda.so dlopens NCCL at first use (an already loaded libnccl.so.2, else $DRM_NCCL_LIB, else the system one).  In a
+    Python process that will ALSO import torch, the NCCL that torch was built against (the nvidia-nccl wheel) has to be the one
+    in the process - torch fails to import on top of an older libnccl.so.2 - so point DRM_NCCL_LIB at the wheel's library when it
+    exists and nothing else was asked for.  No torch import happens here."""
+    if os.environ.get("DRM_NCCL_LIB"):
+        return
+    import importlib.util
+    try:
+        spec = importlib.util.find_spec("nvidia.nccl")
+    except (ImportError, ValueError):
+        spec = None
+    for base in (list(spec.submodule_search_locations) if spec and spec.submodule_search_locations else []):
+        cand = os.path.join(base, "lib", "libnccl.so.2")
+        if os.path.exists(cand):
+            os.environ["DRM_NCCL_LIB"] = cand
+            return
+
+
 class Shards:
     """One HNSW-PQ graph per GPU, windows cut by position (drm_shards_*).  Either all shards in this process
     (index_files / id_lo / devices lists: one host thread per GPU inside the calls) or this process's shard of a
     rank-per-process job (rank / world / unique_id as handed out by Shards.unique_id() on rank 0)."""
 
     def __init__(self, index_files, id_lo, devices, rank=None, world=None, unique_id=None):
+        _prefer_bundled_nccl()
         h = C.c_void_p()
         if rank is None:
             files = (C.c_char_p * len(index_files))(*[os.fsencode(f) for f in index_files])
@@ -604,6 +624,7 @@ class Shards:
 
     @staticmethod
     def unique_id() -> bytes:
+        _prefer_bundled_nccl()
         buf = C.create_string_buffer(128)
         _check(lib().drm_shards_unique_id(C.addressof(buf)))
         return buf.raw

@@ -116,7 +116,7 @@ __device__ __forceinline__ float sigmoidf_(float x) { return 1.0f / (1.0f + expf
 // LAYER 1: xp from the token table P1, writes Y1.  LAYER 2: xp from X2, writes the final states to out.
 // PREFETCH: the input-projection values of a step's gate phase are loaded into registers before the step's products, so
 // the global-memory latency (X2 comes from DRAM in layer 2: `long_scoreboard` 7.2 per issue in profiles/r1_ncu_embed_v1) hides
-// behind ~1300 instructions of FMA work.  Same arithmetic in the same order; chosen by DRM_EMBED_PREFETCH=1 until measured.
+// behind ~1300 instructions of FMA work.  Same arithmetic in the same order (bit-identical); the default since it was measured (+45 %), DRM_EMBED_PREFETCH=0 turns it off.
 template <int LAYER, bool PREFETCH>
 __global__ void __launch_bounds__(ETHREADS, 1)
 gru_kernel(const SrcDev src, const long long first, const long long n, const int T, const float *__restrict__ P1,
@@ -384,8 +384,9 @@ int launch_embed(DeviceEmbedder &e, const EmbedSource &src, int64_t first, int64
     s.cls = src.cls; s.form = src.form; s.ref_n = src.ref_n; s.ref_len = src.ref_len;
     s.first_id = src.first_id; s.id_step = src.id_step;
     s.ids = src.ids; s.decorate = src.decorate;
+    // default ON: 1.04 M sequences/s against 0.72 M without (profiles/r2_embed_bench_prefetch.json); DRM_EMBED_PREFETCH=0 for A/B
     const char *pf = getenv("DRM_EMBED_PREFETCH");
-    const bool prefetch = pf && pf[0] == '1';
+    const bool prefetch = !(pf && pf[0] == '0');
     for (int64_t done = 0; done < n; done += e.chunk) {
         const int64_t m = (n - done) < e.chunk ? (n - done) : e.chunk;
         const unsigned blocks = (unsigned)((m + ES - 1) / ES);

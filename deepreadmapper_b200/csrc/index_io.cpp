@@ -137,6 +137,30 @@ int read_index_file(const char *path, HostIndex &ix)
                  (size_t)ix.max_level + 1 < ix.cum.size() + 0 && ix.levels[(size_t)ix.entry_point] == ix.max_level + 1;
         }
         if (!ok) { rc = fail(DRM_EIO, std::string(path) + ": inconsistent array lengths in index file"); break; }
+        // One validation pass over levels, offsets and neighbours: a corrupt (or hostile) file must not turn into
+        // out-of-bounds device reads in the search kernel.  Cheap next to the upload.
+        const int64_t n = ix.ntotal;
+        const size_t n_cum = ix.cum.size();
+        bool cum_ok = true;
+        for (size_t l = 1; l < n_cum; ++l) cum_ok = cum_ok && ix.cum[l] >= ix.cum[l - 1];
+        int bad = cum_ok ? 0 : 1;
+#pragma omp parallel for schedule(static) reduction(| : bad)
+        for (int64_t v = 0; v < n; ++v) {
+            const int32_t lv = ix.levels[(size_t)v];
+            if (lv < 1 || (size_t)lv >= n_cum) { bad |= 2; continue; }
+            const uint64_t o0 = ix.offsets[(size_t)v], o1 = ix.offsets[(size_t)v + 1];
+            if (o1 < o0 || o1 - o0 != (uint64_t)ix.cum[(size_t)lv] || o1 > ix.neighbors.size()) { bad |= 4; continue; }
+            for (uint64_t j = o0; j < o1; ++j) {
+                const int32_t u = ix.neighbors[j];
+                if (u < -1 || u >= n) { bad |= 8; break; }
+            }
+        }
+        if (bad) {
+            rc = fail(DRM_EIO, std::string(path) + ": index file fails validation (" + ((bad & 1) ? "cum_nneighbor_per_level not monotone; " : "") +
+                                   ((bad & 2) ? "vertex level out of range; " : "") + ((bad & 4) ? "offsets do not match levels; " : "") +
+                                   ((bad & 8) ? "neighbour id outside [-1, ntotal); " : "") + ")");
+            break;
+        }
     } while (false);
     fclose(f);
     return rc;

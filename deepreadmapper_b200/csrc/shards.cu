@@ -58,12 +58,15 @@ NcclApi &nccl()
     std::lock_guard<std::mutex> lk(mu);
     if (a.tried) return a;
     a.tried = true;
+    // An NCCL that the process has loaded already (a PyTorch process carries its own, newer one) wins: two different
+    // libnccl.so.2 in one process do not mix.  Otherwise DRM_NCCL_LIB, then the system library.
+    a.h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL | RTLD_NOLOAD);
     const char *names[] = {getenv("DRM_NCCL_LIB"), "libnccl.so.2", "libnccl.so"};
     for (const char *nm : names) {
+        if (a.h) break;
         if (!nm || !*nm) continue;
         a.h = dlopen(nm, RTLD_NOW | RTLD_GLOBAL);
-        if (a.h) break;
-        a.err = dlerror();
+        if (!a.h) a.err = dlerror();
     }
     if (!a.h) { a.err = "NCCL not found (" + a.err + "); set DRM_NCCL_LIB"; return a; }
 #define LOAD(field, sym)                                                             \
@@ -103,14 +106,23 @@ struct ShardRank {
     std::vector<void *> ipc_open;                                                // cudaIpcOpenMemHandle results to close
     bool p2p_ready = false;
     int64_t *counters = nullptr;                                                 // nhops0, nhops_up, ndis (device)
-    // rerank staging of the host-buffer call
-    char *rq = nullptr; int64_t *rqo = nullptr; int32_t *rsc = nullptr; uint64_t *rid = nullptr; int32_t *rmin = nullptr;
+    // rerank staging of the host-buffer call: two sets, so that chunk c + 1 is computed while chunk c's results go home
+    char *rq[2] = {nullptr, nullptr}; int64_t *rqo[2] = {nullptr, nullptr}; int32_t *rsc[2] = {nullptr, nullptr}; uint64_t *rid[2] = {nullptr, nullptr};
+    int64_t *rel_h[2] = {nullptr, nullptr};                                      // pinned host: chunk-relative read offsets
+    int32_t *rmin = nullptr;
     size_t cap_rq = 0, cap_rqo = 0, cap_rout = 0;
+    cudaStream_t s_out = nullptr;                                                // device -> host copies of finished slices
+    cudaEvent_t out_done[2] = {nullptr, nullptr}, rel_copied[2] = {nullptr, nullptr}, res_ready[2] = {nullptr, nullptr};
     int64_t step = 0;
-    cudaEvent_t ev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};           // stage boundaries of the last step
+    // stage boundaries of the last EV_SETS steps (search | exchange | merge | rerank); harvested lazily into the sums
+    static constexpr int EV_SETS = 8;
+    cudaEvent_t evr[EV_SETS][5] = {};
+    cudaEvent_t *ev = evr[0];
+    bool ev_pending[EV_SETS] = {};
+    int ev_last[EV_SETS] = {};
+    int ev_cur = 0;
     double ms_search = 0, ms_xchg = 0, ms_merge = 0, ms_rerank = 0;
     int64_t bytes_rx = 0;
-    bool times_pending = false;  // the last step's stage events have not been added to the sums yet
 };
 
 void free_rank_buffers(ShardRank &r)
@@ -125,6 +137,25 @@ void free_rank_buffers(ShardRank &r)
     cudaFree(r.D_loc); cudaFree(r.I_loc); cudaFree(r.D_ag); cudaFree(r.I_ag);
     r.D_loc = nullptr; r.I_loc = nullptr; r.D_ag = nullptr; r.I_ag = nullptr;
     r.cap_chunk = 0; r.cap_k = 0; r.cap_mode = -1; r.p2p_ready = false;
+}
+
+void harvest_stage_times(ShardRank &r, int set)
+{
+    if (!r.ev_pending[set]) return;
+    r.ev_pending[set] = false;
+    cudaEvent_t *e = r.evr[set];
+    if (cudaEventSynchronize(e[r.ev_last[set]]) != cudaSuccess) { cudaGetLastError(); return; }
+    float a = 0, b = 0, c = 0, d = 0;
+    cudaEventElapsedTime(&a, e[0], e[1]);
+    cudaEventElapsedTime(&b, e[1], e[2]);
+    cudaEventElapsedTime(&c, e[2], e[3]);
+    if (r.ev_last[set] == 4) cudaEventElapsedTime(&d, e[3], e[4]);
+    r.ms_search += a; r.ms_xchg += b; r.ms_merge += c; r.ms_rerank += d;
+}
+
+void harvest_all(ShardRank &r)
+{
+    for (int i = 0; i < ShardRank::EV_SETS; ++i) harvest_stage_times(r, i);
 }
 
 }  // namespace
@@ -230,8 +261,12 @@ int rank_step(drm_shards *h, ShardRank &r, const float *q_dev, int64_t n, int k,
     int rc = ensure_buffers(h, r, std::max<int64_t>(n, r.cap_chunk), k, r.dx.d, mode);
     if (rc != DRM_OK) return rc;
     const int slot = (int)(r.step & 1);
+    r.ev_cur = (int)(r.step % ShardRank::EV_SETS);
+    harvest_stage_times(r, r.ev_cur);  // the set used EV_SETS steps ago: long finished
+    r.ev = r.evr[r.ev_cur];
+    r.ev_pending[r.ev_cur] = true;
+    r.ev_last[r.ev_cur] = 3;
     ++r.step;
-    r.times_pending = true;
     const int64_t lo = slice_lo(n, r.rank, W), cnt = slice_lo(n, r.rank + 1, W) - lo;
     *lo_out = lo; *cnt_out = cnt;
     DRM_CUDA_TRY(cudaEventRecord(r.ev[0], r.s));
@@ -295,17 +330,6 @@ int rank_step(drm_shards *h, ShardRank &r, const float *q_dev, int64_t n, int k,
     return DRM_OK;
 }
 
-void add_stage_times(ShardRank &r, bool with_rerank)
-{
-    r.times_pending = false;
-    float a = 0, b = 0, c = 0, d = 0;
-    cudaEventElapsedTime(&a, r.ev[0], r.ev[1]);
-    cudaEventElapsedTime(&b, r.ev[1], r.ev[2]);
-    cudaEventElapsedTime(&c, r.ev[2], r.ev[3]);
-    if (with_rerank) cudaEventElapsedTime(&d, r.ev[3], r.ev[4]);
-    r.ms_search += a; r.ms_xchg += b; r.ms_merge += c; r.ms_rerank += d;
-}
-
 int open_rank_common(ShardRank &r, const char *file, int64_t id_lo, int device, int rank, int world)
 {
     HostIndex hix;
@@ -321,7 +345,14 @@ int open_rank_common(ShardRank &r, const char *file, int64_t id_lo, int device, 
         DRM_CUDA_TRY(cudaEventCreateWithFlags(&r.q_ready[b], cudaEventDisableTiming));
         DRM_CUDA_TRY(cudaEventCreateWithFlags(&r.q_free[b], cudaEventDisableTiming));
     }
-    for (auto &e : r.ev) DRM_CUDA_TRY(cudaEventCreate(&e));
+    for (auto &set : r.evr)
+        for (auto &e : set) DRM_CUDA_TRY(cudaEventCreate(&e));
+    DRM_CUDA_TRY(cudaStreamCreateWithFlags(&r.s_out, cudaStreamNonBlocking));
+    for (int b = 0; b < 2; ++b) {
+        DRM_CUDA_TRY(cudaEventCreateWithFlags(&r.out_done[b], cudaEventDisableTiming));
+        DRM_CUDA_TRY(cudaEventCreateWithFlags(&r.rel_copied[b], cudaEventDisableTiming));
+        DRM_CUDA_TRY(cudaEventCreateWithFlags(&r.res_ready[b], cudaEventDisableTiming));
+    }
     DRM_CUDA_TRY(cudaMalloc(&r.flag, sizeof(int)));
     DRM_CUDA_TRY(cudaMemset(r.flag, 0, sizeof(int)));
     DRM_CUDA_TRY(cudaMalloc(&r.counters, 4 * sizeof(int64_t)));
@@ -354,15 +385,25 @@ void drm_shards_close(drm_shards *h)
     if (!h) return;
     for (auto &up : h->local) {
         ShardRank &r = *up;
-        if (r.device >= 0) { cudaSetDevice(r.device); if (r.s) cudaStreamSynchronize(r.s); }
+        if (r.device >= 0) { cudaSetDevice(r.device); if (r.s) cudaStreamSynchronize(r.s); if (r.s_out) cudaStreamSynchronize(r.s_out); }
     }
     for (auto &up : h->local) {
         ShardRank &r = *up;
         free_rank_buffers(r);
         if (r.comm && nccl().h) nccl().CommDestroy(r.comm);
-        cudaFree(r.flag); cudaFree(r.counters); cudaFree(r.rq); cudaFree(r.rqo); cudaFree(r.rsc); cudaFree(r.rid); cudaFree(r.rmin);
-        for (int b = 0; b < 2; ++b) { if (r.q_ready[b]) cudaEventDestroy(r.q_ready[b]); if (r.q_free[b]) cudaEventDestroy(r.q_free[b]); }
-        for (auto &e : r.ev) if (e) cudaEventDestroy(e);
+        cudaFree(r.flag); cudaFree(r.counters); cudaFree(r.rmin);
+        for (int b = 0; b < 2; ++b) {
+            cudaFree(r.rq[b]); cudaFree(r.rqo[b]); cudaFree(r.rsc[b]); cudaFree(r.rid[b]);
+            if (r.rel_h[b]) cudaFreeHost(r.rel_h[b]);
+            if (r.q_ready[b]) cudaEventDestroy(r.q_ready[b]);
+            if (r.q_free[b]) cudaEventDestroy(r.q_free[b]);
+            if (r.out_done[b]) cudaEventDestroy(r.out_done[b]);
+            if (r.rel_copied[b]) cudaEventDestroy(r.rel_copied[b]);
+            if (r.res_ready[b]) cudaEventDestroy(r.res_ready[b]);
+        }
+        for (auto &set : r.evr)
+            for (auto &e : set) if (e) cudaEventDestroy(e);
+        if (r.s_out) cudaStreamDestroy(r.s_out);
         if (r.s) cudaStreamDestroy(r.s);
         if (r.s_copy) cudaStreamDestroy(r.s_copy);
         free_device_index(r.dx);
@@ -486,7 +527,7 @@ int drm_shards_stats(drm_shards *h, int local_rank, int reset, drm_shard_stats *
     ShardRank &r = *h->local[(size_t)local_rank];
     DRM_CUDA_TRY(cudaSetDevice(r.device));
     DRM_CUDA_TRY(cudaStreamSynchronize(r.s));
-    if (r.times_pending) add_stage_times(r, false);  // a drm_shards_step_device step (search / exchange / merge only)
+    harvest_all(r);
     int64_t c[4] = {0, 0, 0, 0};
     DRM_CUDA_TRY(cudaMemcpy(c, r.counters, sizeof c, cudaMemcpyDeviceToHost));
     st->search_ms = r.ms_search; st->exchange_ms = r.ms_xchg; st->merge_ms = r.ms_merge; st->rerank_ms = r.ms_rerank;
@@ -545,6 +586,30 @@ int drm_shards_search_rerank(drm_shards *h, drm_ref *ref, int mode, const float 
         (void)W;
         const int32_t big = 0x7fffffff;
         DRM_CUDA_TRY(cudaMemcpyAsync(r.rmin, &big, sizeof big, cudaMemcpyHostToDevice, r.s));
+        if (rerank) {  // staging for the largest slice of this call, two sets
+            size_t need_rq = 0, need_rows = 0;
+            for (int64_t c0 = 0; c0 < n; c0 += chunk) {
+                const int64_t nc = std::min(chunk, n - c0);
+                const int64_t lo = slice_lo(nc, r.rank, r.world), cnt = slice_lo(nc, r.rank + 1, r.world) - lo;
+                need_rows = std::max(need_rows, (size_t)cnt);
+                need_rq = std::max(need_rq, (size_t)(q_off[c0 + lo + cnt] - q_off[c0 + lo]));
+            }
+            if (need_rq + 16 > r.cap_rq || need_rows + 1 > r.cap_rqo || need_rows * (size_t)k > r.cap_rout) {
+                DRM_CUDA_TRY(cudaStreamSynchronize(r.s));
+                DRM_CUDA_TRY(cudaStreamSynchronize(r.s_out));
+                r.cap_rq = std::max(r.cap_rq, need_rq + 4096); r.cap_rqo = std::max(r.cap_rqo, need_rows + 64); r.cap_rout = std::max(r.cap_rout, need_rows * (size_t)k + 64);
+                for (int b = 0; b < 2; ++b) {
+                    cudaFree(r.rq[b]); cudaFree(r.rqo[b]); cudaFree(r.rsc[b]); cudaFree(r.rid[b]);
+                    if (r.rel_h[b]) cudaFreeHost(r.rel_h[b]);
+                    r.rq[b] = nullptr; r.rqo[b] = nullptr; r.rsc[b] = nullptr; r.rid[b] = nullptr; r.rel_h[b] = nullptr;
+                    DRM_CUDA_TRY(cudaMalloc(&r.rq[b], r.cap_rq));
+                    DRM_CUDA_TRY(cudaMalloc(&r.rqo[b], r.cap_rqo * sizeof(int64_t)));
+                    DRM_CUDA_TRY(cudaMalloc(&r.rsc[b], r.cap_rout * sizeof(int32_t)));
+                    DRM_CUDA_TRY(cudaMalloc(&r.rid[b], r.cap_rout * sizeof(uint64_t)));
+                    DRM_CUDA_TRY(cudaHostAlloc(&r.rel_h[b], r.cap_rqo * sizeof(int64_t), cudaHostAllocDefault));
+                }
+            }
+        }
         int64_t c_idx = 0;
         for (int64_t c0 = 0; c0 < n; c0 += chunk, ++c_idx) {
             const int64_t nc = std::min(chunk, n - c0);
@@ -554,43 +619,45 @@ int drm_shards_search_rerank(drm_shards *h, drm_ref *ref, int mode, const float 
             DRM_CUDA_TRY(cudaMemcpyAsync(r.q[qb], q + (size_t)c0 * d, (size_t)nc * d * sizeof(float), cudaMemcpyHostToDevice, r.s_copy));
             DRM_CUDA_TRY(cudaEventRecord(r.q_ready[qb], r.s_copy));
             DRM_CUDA_TRY(cudaStreamWaitEvent(r.s, r.q_ready[qb], 0));
+            // the merge buffers and the rerank outputs this step will overwrite: their copies home (two steps ago) must be done
+            const int ob = (int)(r.step & 1);
+            DRM_CUDA_TRY(cudaStreamWaitEvent(r.s, r.out_done[ob], 0));
             const float *Dm = nullptr; const int64_t *Im = nullptr;
             int64_t lo = 0, cnt = 0;
             rc = rank_step(h, r, r.q[qb], nc, k_search, ef, exchange, &Dm, &Im, &lo, &cnt);
             if (rc != DRM_OK) return rc;
             DRM_CUDA_TRY(cudaEventRecord(r.q_free[qb], r.s));
+            const int64_t g0 = c0 + lo;
             if (cnt > 0 && rerank) {
-                const int64_t g0 = c0 + lo;
                 const int64_t b0 = q_off[g0], b1 = q_off[g0 + cnt];
-                if ((size_t)(b1 - b0) + 16 > r.cap_rq) { cudaFree(r.rq); r.rq = nullptr; r.cap_rq = (size_t)(b1 - b0) * 5 / 4 + 4096; DRM_CUDA_TRY(cudaMalloc(&r.rq, r.cap_rq)); }
-                if ((size_t)(cnt + 1) > r.cap_rqo) { cudaFree(r.rqo); r.rqo = nullptr; r.cap_rqo = (size_t)(cnt + 1) * 5 / 4 + 64; DRM_CUDA_TRY(cudaMalloc(&r.rqo, r.cap_rqo * sizeof(int64_t))); }
-                if ((size_t)cnt * k > r.cap_rout) {
-                    cudaFree(r.rsc); cudaFree(r.rid); r.rsc = nullptr; r.rid = nullptr;
-                    r.cap_rout = (size_t)cnt * k * 5 / 4 + 64;
-                    DRM_CUDA_TRY(cudaMalloc(&r.rsc, r.cap_rout * sizeof(int32_t)));
-                    DRM_CUDA_TRY(cudaMalloc(&r.rid, r.cap_rout * sizeof(uint64_t)));
-                }
-                std::vector<int64_t> rel((size_t)cnt + 1);
+                DRM_CUDA_TRY(cudaEventSynchronize(r.rel_copied[ob]));  // the host staging of two steps ago has been read
+                int64_t *rel = r.rel_h[ob];
                 int maxlen = 0;
-                for (int64_t i = 0; i <= cnt; ++i) rel[(size_t)i] = q_off[g0 + i] - b0;
-                for (int64_t i = 0; i < cnt; ++i) maxlen = std::max<int>(maxlen, (int)(rel[(size_t)i + 1] - rel[(size_t)i]));
-                DRM_CUDA_TRY(cudaMemcpyAsync(r.rq, q_flat + b0, (size_t)(b1 - b0), cudaMemcpyHostToDevice, r.s));
-                DRM_CUDA_TRY(cudaMemcpyAsync(r.rqo, rel.data(), (size_t)(cnt + 1) * sizeof(int64_t), cudaMemcpyHostToDevice, r.s));
-                DRM_CUDA_TRY(cudaStreamSynchronize(r.s));  // `rel` is a stack-lifetime staging vector
-                RerankArgs a{mode, Im, cnt, (int64_t)k_search, r.rq, r.rqo, maxlen, stride, k, k_clusters, r.rsc, r.rid, nullptr, r.rmin, nullptr};
+                for (int64_t i = 0; i <= cnt; ++i) rel[i] = q_off[g0 + i] - b0;
+                for (int64_t i = 0; i < cnt; ++i) maxlen = std::max<int>(maxlen, (int)(rel[i + 1] - rel[i]));
+                DRM_CUDA_TRY(cudaMemcpyAsync(r.rq[ob], q_flat + b0, (size_t)(b1 - b0), cudaMemcpyHostToDevice, r.s));
+                DRM_CUDA_TRY(cudaMemcpyAsync(r.rqo[ob], rel, (size_t)(cnt + 1) * sizeof(int64_t), cudaMemcpyHostToDevice, r.s));
+                DRM_CUDA_TRY(cudaEventRecord(r.rel_copied[ob], r.s));
+                RerankArgs a{mode, Im, cnt, (int64_t)k_search, r.rq[ob], r.rqo[ob], maxlen, stride, k, k_clusters, r.rsc[ob], r.rid[ob], nullptr, r.rmin, nullptr};
                 rc = launch_rerank(*dref, a, r.s);
                 if (rc != DRM_OK) return rc;
                 DRM_CUDA_TRY(cudaEventRecord(r.ev[4], r.s));
-                DRM_CUDA_TRY(cudaMemcpyAsync(sw_scores + (size_t)g0 * k, r.rsc, (size_t)cnt * k * sizeof(int32_t), cudaMemcpyDeviceToHost, r.s));
-                DRM_CUDA_TRY(cudaMemcpyAsync(sw_ids + (size_t)g0 * k, r.rid, (size_t)cnt * k * sizeof(uint64_t), cudaMemcpyDeviceToHost, r.s));
-            } else {
-                DRM_CUDA_TRY(cudaEventRecord(r.ev[4], r.s));
+                r.ev_last[r.ev_cur] = 4;
             }
-            if (cnt > 0 && D) DRM_CUDA_TRY(cudaMemcpyAsync(D + (size_t)(c0 + lo) * k_search, Dm, (size_t)cnt * k_search * sizeof(float), cudaMemcpyDeviceToHost, r.s));
-            if (cnt > 0 && I) DRM_CUDA_TRY(cudaMemcpyAsync(I + (size_t)(c0 + lo) * k_search, Im, (size_t)cnt * k_search * sizeof(int64_t), cudaMemcpyDeviceToHost, r.s));
-            DRM_CUDA_TRY(cudaStreamSynchronize(r.s));
-            add_stage_times(r, rerank);
+            // results go home on their own stream while the next chunk is searched
+            DRM_CUDA_TRY(cudaEventRecord(r.res_ready[ob], r.s));
+            DRM_CUDA_TRY(cudaStreamWaitEvent(r.s_out, r.res_ready[ob], 0));
+            if (cnt > 0 && rerank) {
+                DRM_CUDA_TRY(cudaMemcpyAsync(sw_scores + (size_t)g0 * k, r.rsc[ob], (size_t)cnt * k * sizeof(int32_t), cudaMemcpyDeviceToHost, r.s_out));
+                DRM_CUDA_TRY(cudaMemcpyAsync(sw_ids + (size_t)g0 * k, r.rid[ob], (size_t)cnt * k * sizeof(uint64_t), cudaMemcpyDeviceToHost, r.s_out));
+            }
+            if (cnt > 0 && D) DRM_CUDA_TRY(cudaMemcpyAsync(D + (size_t)g0 * k_search, Dm, (size_t)cnt * k_search * sizeof(float), cudaMemcpyDeviceToHost, r.s_out));
+            if (cnt > 0 && I) DRM_CUDA_TRY(cudaMemcpyAsync(I + (size_t)g0 * k_search, Im, (size_t)cnt * k_search * sizeof(int64_t), cudaMemcpyDeviceToHost, r.s_out));
+            DRM_CUDA_TRY(cudaEventRecord(r.out_done[ob], r.s_out));
         }
+        DRM_CUDA_TRY(cudaStreamSynchronize(r.s));
+        DRM_CUDA_TRY(cudaStreamSynchronize(r.s_out));
+        harvest_all(r);
         if (rerank) {
             int32_t m = 0x7fffffff;
             DRM_CUDA_TRY(cudaMemcpy(&m, r.rmin, sizeof m, cudaMemcpyDeviceToHost));

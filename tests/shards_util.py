@@ -26,7 +26,9 @@ def oracle_sharded_search(ob, paths, los, Q, k, ef, threads=0):
     """The reference path run the sharded way on the CPU: (D, I) n x k, ordered by (distance, id), -1 / FLT_MAX padded."""
     Ds, Is = [], []
     for path, lo in zip(paths, los):
-        D0, I0, _ = ob.OracleIndex(path).search(Q, k, ef, tie_rule=0, threads=threads)
+        oix = ob.OracleIndex(path)
+        D0, I0, _ = oix.search(Q, k, ef, tie_rule=0, threads=threads)
+        oix.close()  # one shard in host memory at a time (a chromosome-scale shard file is 11 GB)
         Ds.append(D0)
         Is.append(np.where(I0 >= 0, I0 + lo, -1))
     Da, Ia = np.concatenate(Ds, axis=1), np.concatenate(Is, axis=1)
