@@ -17,6 +17,7 @@ using namespace drm;
 struct DevBuf {  // RAII device allocation on the current device
     void *p = nullptr;
     ~DevBuf() { if (p) cudaFree(p); }
+    void release() { if (p) cudaFree(p); p = nullptr; }
     int alloc(size_t bytes) { DRM_CUDA_TRY(cudaMalloc(&p, bytes ? bytes : 16)); return DRM_OK; }
     template <class T> T *as() { return static_cast<T *>(p); }
 };
@@ -901,40 +902,76 @@ int drm_l2_rerank(drm_embedder *e, drm_ref *ref, int mode, const int64_t *neighb
             }
         return DRM_OK;
     }
-    const int64_t U = (int64_t)plan.unique.size(), F = (int64_t)plan.map.size(), ko = plan.k_out;
+    const int64_t U = (int64_t)plan.unique.size(), ko = plan.k_out;
     if (ko < 1) return fail(DRM_EINVAL, "k must be >= 1");
     DRM_CUDA_TRY(cudaSetDevice(e->dev.device));
+    // The plan (the reference's one flat candidate list for ALL queries, de-duplicated windows) stays on the host; the device
+    // works through it in QUERY BATCHES bounded by a memory budget, like post_process_l2_dynamic_streaming batches its queries:
+    // a batch embeds only the windows its own slices reference (a window's embedding does not depend on who else asks for it,
+    // so the result is the same) and reuses the buffers of the previous batch.  Budget: DRM_L2_BATCH_CANDS flat candidates per
+    // batch (default 8 M: <= 4 GB of embeddings + 0.1 GB of scratch).
+    int64_t max_flat = 8ll << 20;
+    if (const char *ev = getenv("DRM_L2_BATCH_CANDS")) max_flat = std::max<int64_t>(1, atoll(ev));
+    std::vector<int32_t> local_of((size_t)U, -1);   // global unique row -> row of this batch's embedding table
+    std::vector<uint64_t> b_ids;
+    std::vector<uint32_t> b_map, b_rows;
+    std::vector<int64_t> b_starts;
     DevBuf d_ids, d_map, d_starts, d_q, d_emb, d_dist, d_idx, d_od, d_or, d_cnt;
-    if ((rc = d_ids.alloc((size_t)U * 8)) || (rc = d_map.alloc((size_t)F * 4)) || (rc = d_starts.alloc((size_t)(n + 1) * 8)) ||
-        (rc = d_q.alloc((size_t)n * 128 * 4)) || (rc = d_emb.alloc((size_t)U * 128 * 4)) || (rc = d_dist.alloc((size_t)F * 4)) ||
-        (rc = d_idx.alloc((size_t)F * 8)) || (rc = d_od.alloc((size_t)n * ko * 4)) || (rc = d_or.alloc((size_t)n * ko * 4)) ||
-        (rc = d_cnt.alloc((size_t)n * 8))) return rc;
-    if (U) DRM_CUDA_TRY(cudaMemcpy(d_ids.p, plan.unique.data(), (size_t)U * 8, cudaMemcpyHostToDevice));
-    if (F) DRM_CUDA_TRY(cudaMemcpy(d_map.p, plan.map.data(), (size_t)F * 4, cudaMemcpyHostToDevice));
-    DRM_CUDA_TRY(cudaMemcpy(d_starts.p, plan.starts.data(), (size_t)(n + 1) * 8, cudaMemcpyHostToDevice));
-    DRM_CUDA_TRY(cudaMemcpy(d_q.p, q_emb, (size_t)n * 128 * 4, cudaMemcpyHostToDevice));
-    EmbedSource src;
-    src.mode = 1; src.cls = dr->data; src.form = dr->form; src.ref_n = dr->len; src.ref_len = dr->ref_len;
-    src.ids = d_ids.as<unsigned long long>();
-    src.decorate = mode == 0 ? 1 : 0;  // mode 0: ref_seqs hold '<' window '>' strings; find_sequence (1) and lookup-mode tables (2) give bare windows
-    if ((rc = launch_embed(e->dev, src, 0, U, d_emb.as<float>(), 0)) != DRM_OK) return rc;
-    if ((rc = launch_l2_rerank(d_emb.as<float>(), d_map.as<uint32_t>(), d_starts.as<int64_t>(), d_q.as<float>(), n, (int)ko, d_dist.as<float>(),
-                               d_idx.as<int64_t>(), d_od.as<float>(), d_or.as<uint32_t>(), d_cnt.as<int64_t>(), 0)) != DRM_OK) return rc;
-    std::vector<float> od((size_t)(n * ko));
-    std::vector<uint32_t> orow((size_t)(n * ko));
-    std::vector<int64_t> cnt((size_t)n);
-    DRM_CUDA_TRY(cudaMemcpy(od.data(), d_od.p, od.size() * 4, cudaMemcpyDeviceToHost));
-    DRM_CUDA_TRY(cudaMemcpy(orow.data(), d_or.p, orow.size() * 4, cudaMemcpyDeviceToHost));
-    DRM_CUDA_TRY(cudaMemcpy(cnt.data(), d_cnt.p, cnt.size() * 8, cudaMemcpyDeviceToHost));
-    for (int64_t q = 0; q < n; ++q) {
-        if (cnt[(size_t)q] == 0) continue;  // batch_reranker returns empty vectors for a query without candidates
-        if (cnt[(size_t)q] < 0)
-            return fail(DRM_ENOTENOUGH, "Not enough candidates (" + std::to_string(-cnt[(size_t)q] - 1) + " < " + std::to_string(ko) + ") for query " + std::to_string(q));
-        for (int64_t j = 0; j < ko; ++j) {
-            out_scores[*out_count] = od[(size_t)(q * ko + j)];
-            out_ids[*out_count] = plan.unique[orow[(size_t)(q * ko + j)]];
-            ++*out_count;
+    size_t cap_u = 0, cap_f = 0, cap_n = 0;
+    std::vector<float> od;
+    std::vector<uint32_t> orow;
+    std::vector<int64_t> cnt;
+    for (int64_t q0 = 0; q0 < n;) {
+        int64_t q1 = q0 + 1;
+        while (q1 < n && plan.starts[(size_t)q1 + 1] - plan.starts[(size_t)q0] <= max_flat) ++q1;
+        const int64_t nb = q1 - q0, f0 = plan.starts[(size_t)q0], fb = plan.starts[(size_t)q1] - f0;
+        b_ids.clear(); b_rows.clear();
+        b_map.resize((size_t)fb);
+        b_starts.resize((size_t)nb + 1);
+        for (int64_t i = 0; i <= nb; ++i) b_starts[(size_t)i] = plan.starts[(size_t)(q0 + i)] - f0;
+        for (int64_t j = 0; j < fb; ++j) {
+            const uint32_t g = plan.map[(size_t)(f0 + j)];
+            int32_t l = local_of[g];
+            if (l < 0) { l = (int32_t)b_ids.size(); local_of[g] = l; b_ids.push_back(plan.unique[g]); b_rows.push_back(g); }
+            b_map[(size_t)j] = (uint32_t)l;
         }
+        for (uint32_t g : b_rows) local_of[g] = -1;
+        const int64_t ub = (int64_t)b_ids.size();
+        if ((size_t)ub > cap_u || (size_t)fb > cap_f || (size_t)nb > cap_n) {  // grow (first batch sizes the rest: batches are cut to one budget)
+            cap_u = std::max(cap_u, (size_t)ub + (size_t)ub / 8 + 16); cap_f = std::max(cap_f, (size_t)fb + 16); cap_n = std::max(cap_n, (size_t)nb + 16);
+            DRM_CUDA_TRY(cudaDeviceSynchronize());
+            d_ids.release(); d_map.release(); d_starts.release(); d_q.release(); d_emb.release(); d_dist.release(); d_idx.release(); d_od.release();
+            d_or.release(); d_cnt.release();
+            if ((rc = d_ids.alloc(cap_u * 8)) || (rc = d_map.alloc(cap_f * 4)) || (rc = d_starts.alloc((cap_n + 1) * 8)) || (rc = d_q.alloc(cap_n * 128 * 4)) ||
+                (rc = d_emb.alloc(cap_u * 128 * 4)) || (rc = d_dist.alloc(cap_f * 4)) || (rc = d_idx.alloc(cap_f * 4)) || (rc = d_od.alloc(cap_n * ko * 4)) ||
+                (rc = d_or.alloc(cap_n * ko * 4)) || (rc = d_cnt.alloc(cap_n * 8))) return rc;
+        }
+        if (ub) DRM_CUDA_TRY(cudaMemcpy(d_ids.p, b_ids.data(), (size_t)ub * 8, cudaMemcpyHostToDevice));
+        if (fb) DRM_CUDA_TRY(cudaMemcpy(d_map.p, b_map.data(), (size_t)fb * 4, cudaMemcpyHostToDevice));
+        DRM_CUDA_TRY(cudaMemcpy(d_starts.p, b_starts.data(), (size_t)(nb + 1) * 8, cudaMemcpyHostToDevice));
+        DRM_CUDA_TRY(cudaMemcpy(d_q.p, q_emb + (size_t)q0 * 128, (size_t)nb * 128 * 4, cudaMemcpyHostToDevice));
+        EmbedSource src;
+        src.mode = 1; src.cls = dr->data; src.form = dr->form; src.ref_n = dr->len; src.ref_len = dr->ref_len;
+        src.ids = d_ids.as<unsigned long long>();
+        src.decorate = mode == 0 ? 1 : 0;  // mode 0: ref_seqs hold '<' window '>' strings; find_sequence (1) and lookup-mode tables (2) give bare windows
+        if (ub && (rc = launch_embed(e->dev, src, 0, ub, d_emb.as<float>(), 0)) != DRM_OK) return rc;
+        if ((rc = launch_l2_rerank(d_emb.as<float>(), d_map.as<uint32_t>(), d_starts.as<int64_t>(), d_q.as<float>(), nb, (int)ko, d_dist.as<float>(),
+                                   d_idx.as<int64_t>(), d_od.as<float>(), d_or.as<uint32_t>(), d_cnt.as<int64_t>(), 0)) != DRM_OK) return rc;
+        od.resize((size_t)(nb * ko)); orow.resize((size_t)(nb * ko)); cnt.resize((size_t)nb);
+        DRM_CUDA_TRY(cudaMemcpy(od.data(), d_od.p, od.size() * 4, cudaMemcpyDeviceToHost));
+        DRM_CUDA_TRY(cudaMemcpy(orow.data(), d_or.p, orow.size() * 4, cudaMemcpyDeviceToHost));
+        DRM_CUDA_TRY(cudaMemcpy(cnt.data(), d_cnt.p, cnt.size() * 8, cudaMemcpyDeviceToHost));
+        for (int64_t q = 0; q < nb; ++q) {
+            if (cnt[(size_t)q] == 0) continue;  // batch_reranker returns empty vectors for a query without candidates
+            if (cnt[(size_t)q] < 0)
+                return fail(DRM_ENOTENOUGH, "Not enough candidates (" + std::to_string(-cnt[(size_t)q] - 1) + " < " + std::to_string(ko) + ") for query " + std::to_string(q0 + q));
+            for (int64_t j = 0; j < ko; ++j) {
+                out_scores[*out_count] = od[(size_t)(q * ko + j)];
+                out_ids[*out_count] = b_ids[orow[(size_t)(q * ko + j)]];
+                ++*out_count;
+            }
+        }
+        q0 = q1;
     }
     return DRM_OK;
 }

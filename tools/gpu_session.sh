@@ -55,6 +55,8 @@ ncu_sw)
   ncu_kernel sw_rerank_profile r2_ncu_sw python bench.py --steps 1 --warmup 0 --skip-cpu --reads 131072 ;;
 embed_ab)
   timeout 300 python tools/embed_bench.py > $O/embed_bench.json 2> $O/embed_bench.log; tail -3 $O/embed_bench.log; cat $O/embed_bench.json ;;
+overlap)
+  timeout 600 python tools/overlap_probe.py > $O/overlap_probe.log 2>&1; tail -12 $O/overlap_probe.log ;;
 l2bench)
   timeout 600 python tools/l2_bench.py > $O/l2_bench.json 2> $O/l2_bench.log; tail -3 $O/l2_bench.log; cat $O/l2_bench.json ;;
 sharded)
