@@ -39,7 +39,7 @@ EXPORTS = ["drm_last_error", "drm_device_count", "drm_version", "drm_index_open"
            "drm_embedder_ir_info", "drm_tokenize", "drm_embed", "drm_embed_reads", "drm_embed_windows", "drm_embed_device",
            "drm_embed_windows_device", "drm_l2_rerank", "drm_l2_plan_host", "drm_l2_select_host",
            "drm_shards_open", "drm_shards_unique_id", "drm_shards_open_rank", "drm_shards_close", "drm_shards_info", "drm_shards_search_rerank",
-           "drm_shards_step_device", "drm_shards_stats"]
+           "drm_shards_step_device", "drm_shards_stats", "drm_l2_last_timing"]
 
 
 class ShardStats(C.Structure):
@@ -110,6 +110,7 @@ def lib():
         L.drm_l2_rerank.argtypes = [vp, vp, i32, vp, vp, i64, i64, vp, i64, i64, i64, vp, vp, C.POINTER(i64)]
         L.drm_l2_plan_host.argtypes = [i32, vp, i64, i64, i64, i64, i64, C.c_uint64, vp, vp, vp, vp]
         L.drm_l2_select_host.argtypes = [vp, i64, i64, vp]
+        L.drm_l2_last_timing.argtypes = [vp]
         L.drm_shards_open.argtypes = [C.POINTER(C.c_char_p), vp, C.POINTER(i32), i32, C.POINTER(vp)]
         L.drm_shards_unique_id.argtypes = [vp]
         L.drm_shards_open_rank.argtypes = [C.c_char_p, i64, i32, i32, i32, vp, C.POINTER(vp)]
@@ -528,6 +529,13 @@ class Vectorizer:
 
 
 # ---- L2 rerank stage (the reference's post_process_l2_* variants) -----------------------------------------------------
+def l2_last_timing():
+    """{plan_ms, embed_ms, rank_ms, other_ms, batches} of this thread's last drm_l2_rerank call."""
+    t = np.zeros(5, dtype=np.float64)
+    _check(lib().drm_l2_last_timing(t.ctypes.data))
+    return dict(zip(("plan_ms", "embed_ms", "rank_ms", "other_ms", "batches"), t.tolist()))
+
+
 def l2_plan_host(mode, neighbors, stride, k, k_clusters, bound):
     """The candidate bookkeeping of post_process_l2_static (mode 0) / _dynamic (mode 1) on the host:
     dict(unique, map, starts, k_out, passthrough, take)."""

@@ -874,6 +874,15 @@ int drm_l2_select_host(const float *dist, int64_t n, int64_t k, int64_t *idx)
     return DRM_OK;
 }
 
+static thread_local double g_l2_ms[5] = {0, 0, 0, 0, 0};  // plan (host), embed, distance + selection, copies + bookkeeping, batches
+
+int drm_l2_last_timing(double *ms5)
+{
+    if (!ms5) return fail(DRM_EINVAL, "null output");
+    for (int i = 0; i < 5; ++i) ms5[i] = g_l2_ms[i];
+    return DRM_OK;
+}
+
 int drm_l2_rerank(drm_embedder *e, drm_ref *ref, int mode, const int64_t *neighbors, const float *distances, int64_t n, int64_t k_in,
                   const float *q_emb, int64_t stride, int64_t k, int64_t k_clusters, float *out_scores, uint64_t *out_ids,
                   int64_t *out_count)
@@ -891,8 +900,13 @@ int drm_l2_rerank(drm_embedder *e, drm_ref *ref, int mode, const int64_t *neighb
     if (mode == 1 || dr->form == 1) bound = (uint64_t)dr->len;
     else bound = dr->len >= dr->ref_len ? 2ull * (uint64_t)(dr->len - dr->ref_len + 1) : 0;
     L2Plan plan;
+    for (double &v : g_l2_ms) v = 0;
+    const auto t_plan = std::chrono::steady_clock::now();
     int rc = l2_plan(mode == 2 ? 0 : mode, neighbors, n, k_in, stride, k, k_clusters, bound, plan);  // mode 2 = static bookkeeping, bare windows
     if (rc != DRM_OK) return rc;
+    g_l2_ms[0] = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_plan).count();
+    const auto t_all = std::chrono::steady_clock::now();
+    cudaEvent_t ev_a = nullptr, ev_b = nullptr, ev_c = nullptr;
     if (plan.passthrough) {
         for (int64_t q = 0; q < n; ++q)
             for (int64_t j = 0; j < plan.take; ++j) {
@@ -905,6 +919,8 @@ int drm_l2_rerank(drm_embedder *e, drm_ref *ref, int mode, const int64_t *neighb
     const int64_t U = (int64_t)plan.unique.size(), ko = plan.k_out;
     if (ko < 1) return fail(DRM_EINVAL, "k must be >= 1");
     DRM_CUDA_TRY(cudaSetDevice(e->dev.device));
+    DRM_CUDA_TRY(cudaEventCreate(&ev_a)); DRM_CUDA_TRY(cudaEventCreate(&ev_b)); DRM_CUDA_TRY(cudaEventCreate(&ev_c));
+    struct EvGuard { cudaEvent_t &a, &b, &c; ~EvGuard() { if (a) cudaEventDestroy(a); if (b) cudaEventDestroy(b); if (c) cudaEventDestroy(c); } } ev_guard{ev_a, ev_b, ev_c};
     // The plan (the reference's one flat candidate list for ALL queries, de-duplicated windows) stays on the host; the device
     // works through it in QUERY BATCHES bounded by a memory budget, like post_process_l2_dynamic_streaming batches its queries:
     // a batch embeds only the windows its own slices reference (a window's embedding does not depend on who else asks for it,
@@ -954,9 +970,12 @@ int drm_l2_rerank(drm_embedder *e, drm_ref *ref, int mode, const int64_t *neighb
         src.mode = 1; src.cls = dr->data; src.form = dr->form; src.ref_n = dr->len; src.ref_len = dr->ref_len;
         src.ids = d_ids.as<unsigned long long>();
         src.decorate = mode == 0 ? 1 : 0;  // mode 0: ref_seqs hold '<' window '>' strings; find_sequence (1) and lookup-mode tables (2) give bare windows
+        DRM_CUDA_TRY(cudaEventRecord(ev_a, 0));
         if (ub && (rc = launch_embed(e->dev, src, 0, ub, d_emb.as<float>(), 0)) != DRM_OK) return rc;
+        DRM_CUDA_TRY(cudaEventRecord(ev_b, 0));
         if ((rc = launch_l2_rerank(d_emb.as<float>(), d_map.as<uint32_t>(), d_starts.as<int64_t>(), d_q.as<float>(), nb, (int)ko, d_dist.as<float>(),
                                    d_idx.as<int64_t>(), d_od.as<float>(), d_or.as<uint32_t>(), d_cnt.as<int64_t>(), 0)) != DRM_OK) return rc;
+        DRM_CUDA_TRY(cudaEventRecord(ev_c, 0));
         od.resize((size_t)(nb * ko)); orow.resize((size_t)(nb * ko)); cnt.resize((size_t)nb);
         DRM_CUDA_TRY(cudaMemcpy(od.data(), d_od.p, od.size() * 4, cudaMemcpyDeviceToHost));
         DRM_CUDA_TRY(cudaMemcpy(orow.data(), d_or.p, orow.size() * 4, cudaMemcpyDeviceToHost));
@@ -971,8 +990,15 @@ int drm_l2_rerank(drm_embedder *e, drm_ref *ref, int mode, const int64_t *neighb
                 ++*out_count;
             }
         }
+        {
+            float m1 = 0, m2 = 0;
+            cudaEventElapsedTime(&m1, ev_a, ev_b);
+            cudaEventElapsedTime(&m2, ev_b, ev_c);
+            g_l2_ms[1] += m1; g_l2_ms[2] += m2; g_l2_ms[4] += 1;
+        }
         q0 = q1;
     }
+    g_l2_ms[3] = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_all).count() - g_l2_ms[1] - g_l2_ms[2];
     return DRM_OK;
 }
 

@@ -222,6 +222,9 @@ int drm_embed_windows_device(drm_embedder *e, const drm_ref *ref, uint64_t first
 int drm_l2_rerank(drm_embedder *e, drm_ref *ref, int mode, const int64_t *neighbors, const float *distances, int64_t n, int64_t k_in,
                   const float *q_emb, int64_t stride, int64_t k, int64_t k_clusters, float *out_scores, uint64_t *out_ids,
                   int64_t *out_count);
+/* Stage times of this thread's last drm_l2_rerank call: ms5 = {candidate plan on the host, embedder kernels, distance +
+ * selection kernels, copies and host bookkeeping, number of query batches}.  Measurement aid (tools/l2_bench.py). */
+int drm_l2_last_timing(double *ms5);
 /* Host-only pieces of the above, exposed for tests: the candidate plan (info[0..4] = unique windows, flat candidates,
  * results per query, pass-through flag, pass-through count; arrays nullable, sized from a first call) and the
  * partial_sort order (idx: n entries, the first k are the selection). */

@@ -1,0 +1,127 @@
+#!/usr/bin/env python
+"""Throughput of the L2 rerank stage - the post-process the reference's `main` actually runs (src/main.cpp:312-331,
+src/utils/post_processor.cpp:552-748, src/utils/reranker.cpp:98-196) - on BASELINE.json configs[2]: E. coli-sized genome,
+stride-8 sparse labels, K_clusters = 32 labels per read -> up to 32 x 15 = 480 dense windows per read, de-duplicated,
+embedded on the device and ranked by embedding distance; final K = 128.
+
+  GPU arm   drm_l2_rerank through the Python mirror (host buffers), stage split from drm_l2_last_timing:
+            plan (host) | embed | distance + selection | copies
+  CPU arm   the reference's own post_process_l2_dynamic compiled unmodified (oracle/_ref) on a bounded sample of the same
+            reads, with Vectorizer::vectorize routed to the DEVICE embedder (the reference's embedder is OpenVINO, absent
+            here): it times what the reference computes itself - candidate bookkeeping, calc_l2_dist, partial_sort - and
+            doubles as a size-realistic parity check (ids and fp32 distance bits must be equal).
+Random weights of the model's architecture unless $DRM_MODEL points at the reference's IR (throughput does not depend on
+the values).  usage: python tools/l2_bench.py [--reads N] [--cpu-sample M]"""
+import argparse
+import ctypes as C
+import json
+import os
+import sys
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+
+def main():
+    import deepreadmapper_b200 as drm
+    from deepreadmapper_b200 import synth
+    from oracle import bindings as OB
+    from oracle import embed_oracle as EO
+
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--reads", type=int, default=20000)
+    ap.add_argument("--cpu-sample", type=int, default=1000)
+    ap.add_argument("--genome-bases", type=int, default=4_641_652)
+    ap.add_argument("--stride", type=int, default=8)
+    ap.add_argument("--k-clusters", type=int, default=32)
+    ap.add_argument("--k", type=int, default=128)
+    ap.add_argument("--reps", type=int, default=3)
+    ap.add_argument("--out", default="gpurun_out/l2_bench.json")
+    a = ap.parse_args()
+    rng = np.random.default_rng(5)
+    genome = synth.random_genome(a.genome_bases, 42)
+    model = os.environ.get("DRM_MODEL")
+    v = drm.Vectorizer(model_path=model) if model and os.path.exists(model) else drm.Vectorizer(weights=EO.random_weights(62))
+    ref = drm.Reference(genome=genome, ref_len=150)
+    n, stride, kc, k = a.reads, a.stride, a.k_clusters, a.k
+    reads, truth = synth.simulate_reads(genome, n)
+    # sparse labels the way a stride-8 search returns them: ids around the read's true window (dense id / stride), plus random ones.
+    # The dynamic variant only reaches dense ids below the genome length (src/utils/post_processor.cpp:117-121), like the reference.
+    hi = (len(genome) - stride) // stride
+    centre = np.minimum((truth // stride), hi - kc - 1)
+    nb = np.empty((n, kc), np.int64)
+    near = kc // 2
+    nb[:, :near] = np.clip(centre[:, None] + np.arange(-(near // 2), near - near // 2)[None, :], 1, hi - 1)
+    nb[:, near:] = rng.integers(1, hi, (n, kc - near))
+    dist = np.sort(rng.random((n, kc)).astype(np.float32), axis=1)
+    q_emb = v.vectorize([b"<" + bytes(r) + b">" for r in reads])
+    res = {"reads": n, "stride": stride, "k_clusters": kc, "k": k, "genome_bases": len(genome)}
+    best = None
+    for rep in range(a.reps + 1):
+        t0 = time.perf_counter()
+        s, ids = drm.post_process_l2_dynamic(nb, dist, ref, q_emb, v, stride, k, kc)
+        wall = (time.perf_counter() - t0) * 1e3
+        tm = drm.api.l2_last_timing()
+        tm["wall_ms"] = wall
+        if rep and (best is None or wall < best["wall_ms"]):
+            best = tm
+    res["gpu"] = best
+    res["gpu"]["reads_per_s"] = n / (best["wall_ms"] / 1e3)
+    res["gpu"]["device_reads_per_s"] = n / ((best["embed_ms"] + best["rank_ms"]) / 1e3)
+    res["candidates_per_read_final"] = len(ids) / n
+    print(json.dumps(res["gpu"]), flush=True)
+
+    # ---- CPU arm: the compiled reference on a sample, embeddings from the device embedder
+    if OB.have_ref():
+        m = min(a.cpu_sample, n)
+        CB = C.CFUNCTYPE(None, C.c_char_p, C.POINTER(C.c_int64), C.c_int64, C.POINTER(C.c_float))
+        spent = {"embed_s": 0.0, "windows": 0}
+
+        def cb(flat, off, cnt, out):
+            offs = [off[i] for i in range(cnt + 1)]
+            raw = C.string_at(flat, offs[-1]) if offs[-1] else b""
+            t1 = time.perf_counter()
+            e = v.vectorize([raw[offs[i]:offs[i + 1]] for i in range(cnt)])
+            spent["embed_s"] += time.perf_counter() - t1
+            spent["windows"] += cnt
+            C.memmove(out, e.ctypes.data, e.nbytes)
+
+        keep = CB(cb)
+        R = OB.ref()
+        R.ref_set_vectorizer.argtypes = [CB]
+        R.ref_set_vectorizer.restype = None
+        R.ref_set_vectorizer(keep)
+        R.ref_post_process_l2.restype = C.c_int
+        R.ref_post_process_l2.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_char_p, C.c_int64, C.c_int64, C.c_int64,
+                                          C.c_char_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_int64, C.c_void_p, C.c_void_p, C.POINTER(C.c_int64)]
+        q_flat = b"<ACGT>" * m
+        q_off = np.arange(m + 1, dtype=np.int64) * 6
+        cap = m * max(k, kc) + 8
+        sc = np.zeros(cap, np.float32); idr = np.zeros(cap, np.uint64); cnt = C.c_int64(0)
+        nbm, dm, qm = np.ascontiguousarray(nb[:m]), np.ascontiguousarray(dist[:m]), np.ascontiguousarray(q_emb[:m])
+        t0 = time.perf_counter()
+        rc = R.ref_post_process_l2(1, nbm.ctypes.data, dm.ctypes.data, m, kc, genome, len(genome), 0, 150, q_flat, q_off.ctypes.data, qm.ctypes.data,
+                                   stride, k, kc, sc.ctypes.data, idr.ctypes.data, C.byref(cnt))
+        total = time.perf_counter() - t0
+        R.ref_set_vectorizer(C.cast(None, CB))
+        assert rc == 0, R.ref_last_error()
+        own = total - spent["embed_s"]
+        s_m, i_m = drm.post_process_l2_dynamic(nbm, dm, ref, qm, v, stride, k, kc)
+        equal = bool(cnt.value == len(i_m) and np.array_equal(idr[:cnt.value], i_m) and np.array_equal(sc[:cnt.value].view(np.uint32), s_m.view(np.uint32)))
+        res["cpu_reference"] = {"sample_reads": m, "total_s": total, "embed_callback_s": spent["embed_s"], "windows_embedded": spent["windows"],
+                                "own_work_s": own, "reads_per_s_excluding_embedder": m / own, "cores": os.cpu_count(),
+                                "note": "reference post_process_l2_dynamic compiled unmodified (oracle/_ref); its Vectorizer is routed to the device embedder, "
+                                        "whose time is excluded: the figure is the reference's own bookkeeping + calc_l2_dist + partial_sort",
+                                "device_equals_reference_on_sample": equal}
+        print(json.dumps(res["cpu_reference"]), flush=True)
+        assert equal, "device L2 rerank differs from the compiled reference on the sample"
+    os.makedirs(os.path.dirname(a.out) or ".", exist_ok=True)
+    json.dump(res, open(a.out, "w"), indent=1)
+    print(json.dumps(res))
+
+
+if __name__ == "__main__":
+    main()
