@@ -60,6 +60,9 @@ struct ExactParams {
     int c_words;          // 32-bit words of shared memory per warp for the candidate heap
     int readahead;        // 1: read the row of the runner-up candidate into registers while this row is processed
     int prefetch_accept;  // 1: L2-prefetch the row of every vertex accepted into the candidate heap
+    int tma;              // 1: rows arrive through the bulk-copy engine (cp.async.bulk + mbarrier) into a per-warp staging buffer,
+                          //    and the accept-time prefetch is one cp.async.bulk.prefetch.L2 instead of one prefetch per line
+    int row_stage_bytes;  // per-warp staging: row bytes rounded to 16, + 16 for the mbarrier (0 when tma is off)
     float *D;
     long long *I;
     u64 *counters;
@@ -337,11 +340,25 @@ __global__ void __launch_bounds__(XWARPS * 32, 5) hnswpq_search_exact_kernel(con
     constexpr int VIS_SLOTS = VIS > 0 ? VIS : 1;
     const size_t t_bytes = (size_t)p.M * 256 * sizeof(float);
     constexpr int BLOOM_WORDS = VIS > 0 ? 32 : 0;  // 1024-bit filter of the vertices the tag cache has lost
-    const size_t per_warp = t_bytes + (size_t)p.c_words * 4 + (size_t)VIS * 2 + BLOOM_WORDS * 4;
+    const size_t per_warp = t_bytes + (size_t)p.c_words * 4 + (size_t)VIS * 2 + BLOOM_WORDS * 4 + (size_t)p.row_stage_bytes;
     float *T = reinterpret_cast<float *>(smem_raw + warp * per_warp);
     uint2 *C2 = reinterpret_cast<uint2 *>(smem_raw + warp * per_warp + t_bytes);  // entry j at C2[j], j = 1 .. cap (+1 spare)
     unsigned short *vis = reinterpret_cast<unsigned short *>(smem_raw + warp * per_warp + t_bytes + (size_t)p.c_words * 4);
     unsigned *bloom = reinterpret_cast<unsigned *>(smem_raw + warp * per_warp + t_bytes + (size_t)p.c_words * 4 + (size_t)VIS * 2);
+    // bulk-copy row staging (p.tma): [row bytes][8-byte mbarrier]; one copy in flight per warp, phase bit flips per use
+    unsigned char *rowbuf = smem_raw + warp * per_warp + t_bytes + (size_t)p.c_words * 4 + (size_t)VIS * 2 + BLOOM_WORDS * 4;
+    unsigned tma_phase = 0;
+#ifndef DRM_EMU
+    const unsigned rowbuf_s = (unsigned)__cvta_generic_to_shared(rowbuf);
+    const unsigned bar_s = rowbuf_s + (unsigned)p.row_stage_bytes - 16u;
+    if (p.tma) {
+        if (lane == 0) {
+            asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar_s) : "memory");
+            asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        }
+        __syncwarp();
+    }
+#endif
     const int cap = p.cap, k = p.k;
     const int max_lane = (k - 1) / NSR, max_slot = (k - 1) % NSR;
 
@@ -424,6 +441,34 @@ __global__ void __launch_bounds__(XWARPS * 32, 5) hnswpq_search_exact_kernel(con
             }
             int nid; XCode<CS> code;
             if (v0 == spec_v) { nid = nid_s; code = code_s; }
+#ifndef DRM_EMU
+            else if (p.tma) {
+                // the whole fused row (contiguous, 16-byte aligned: the regular access of this kernel) in ONE bulk copy issued by one lane
+                const uint8_t *row = p.rows0 + (size_t)v0 * p.row0_bytes;
+                if (lane == 0) {
+                    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // the buffer was last touched by ordinary loads
+                    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar_s), "r"(p.row0_bytes) : "memory");
+                    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(rowbuf_s), "l"(row),
+                                 "r"(p.row0_bytes), "r"(bar_s)
+                                 : "memory");
+                }
+                unsigned done = 0;
+                do {
+                    asm volatile("{\n\t.reg .pred P1;\n\tmbarrier.try_wait.parity.shared::cta.b64 P1, [%1], %2;\n\tselp.b32 %0, 1, 0, P1;\n\t}"
+                                 : "=r"(done)
+                                 : "r"(bar_s), "r"(tma_phase)
+                                 : "memory");
+                } while (!done);
+                tma_phase ^= 1u;
+                nid = lane < p.W0 ? reinterpret_cast<const int *>(rowbuf)[lane] : -1;
+                code.v = {};
+                if (lane < p.W0) {
+                    if (CS == 8) { const uint2 t = *reinterpret_cast<const uint2 *>(rowbuf + p.c0_off + 8 * lane); code.v.x = t.x; code.v.y = t.y; }
+                    else code = *reinterpret_cast<const XCode<CS> *>(rowbuf + p.c0_off + CS * lane);
+                }
+                __syncwarp();  // every lane has read its slot before the next copy may land
+            }
+#endif
             else {
                 const uint8_t *row = p.rows0 + (size_t)v0 * p.row0_bytes;
                 nid = lane < p.W0 ? __ldg(reinterpret_cast<const int *>(row) + lane) : -1;
@@ -508,7 +553,12 @@ __global__ void __launch_bounds__(XWARPS * 32, 5) hnswpq_search_exact_kernel(con
                 ++nvalid;
                 if (csize == cap) root_d = C2[1].x;
 #ifndef DRM_EMU
-                if (p.prefetch_accept && lane < 3) {
+                if (p.tma) {
+                    if (p.prefetch_accept && lane == 0) {
+                        const uint8_t *prow = p.rows0 + (size_t)kid * p.row0_bytes;
+                        asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(prow), "r"(p.row0_bytes) : "memory");
+                    }
+                } else if (p.prefetch_accept && lane < 3) {
                     const uint8_t *prow = p.rows0 + (size_t)kid * p.row0_bytes + lane * 128;
                     if (lane * 128 < p.row0_bytes) asm volatile("prefetch.global.L2 [%0];" ::"l"(prow));
                 }
@@ -547,7 +597,7 @@ template <int CS, int NSR, bool FULLK, int VIS, int CL>
 int launch_exact_tfvc(const ExactParams &p, int device, cudaStream_t stream)
 {
     auto kern = hnswpq_search_exact_kernel<CS, NSR, FULLK, VIS, CL>;
-    const size_t smem = (size_t)XWARPS * ((size_t)p.M * 256 * sizeof(float) + (size_t)p.c_words * 4 + (size_t)VIS * 2 + (VIS > 0 ? 128 : 0));
+    const size_t smem = (size_t)XWARPS * ((size_t)p.M * 256 * sizeof(float) + (size_t)p.c_words * 4 + (size_t)VIS * 2 + (VIS > 0 ? 128 : 0) + (size_t)p.row_stage_bytes);
     DRM_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int per_sm = 0, sms = 0;
     DRM_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, XWARPS * 32, smem));
@@ -635,6 +685,10 @@ int launch_search_exact_ex(const DeviceIndex &dx, const float *q_dev, int64_t n,
     p.readahead = 0; p.prefetch_accept = 1;  // A/B on B200 (profiles/r2_ab_search_exact.txt): accept-time L2 prefetch beats the register read-ahead
     if (const char *e = getenv("DRM_SEARCH_RA")) p.readahead = atoi(e) != 0;
     if (const char *e = getenv("DRM_SEARCH_PFA")) p.prefetch_accept = atoi(e) != 0;
+    p.tma = 0;
+    if (const char *e = getenv("DRM_SEARCH_TMA")) p.tma = atoi(e) != 0;
+    if (p.row0_bytes % 16) p.tma = 0;  // the bulk-copy engine moves multiples of 16 bytes
+    p.row_stage_bytes = p.tma ? (p.row0_bytes + 15) / 16 * 16 + 16 : 0;
     p.D = D_dev; p.I = reinterpret_cast<long long *>(I_dev);
     p.counters = reinterpret_cast<u64 *>(counters_dev);
     p.next_query = work;

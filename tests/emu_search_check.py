@@ -12,7 +12,7 @@ import tempfile
 import numpy as np
 
 
-def main(n_reads=16, genome_bases=1000):
+def main(n_reads=16, genome_bases=1000, light=False):
     import deepreadmapper_b200 as drm
     from deepreadmapper_b200 import synth
     from oracle import bindings as ob
@@ -26,6 +26,8 @@ def main(n_reads=16, genome_bases=1000):
     ix = drm.Index(path, devices=[0])
     cases = [("exact", "512", "1", (128, 128)), ("exact", "0", "0", (8, 32)), ("exact", "512", "1", (200, 128)), ("exact", "1024", "1", (100, 128)),
              ("exact", "512", "1", (64, 300)), ("reg", "512", "1", (128, 128)), ("smem", "512", "1", (200, 128)), ("pair", "512", "1", (32, 64))]
+    if light:
+        cases = [cases[0], cases[2]]  # exact kernel: k == ef and k > ef (count_below); the canonical kernels run under DRM_EMU_FULL=1
     for kern, vis, ra, (k, ef) in cases:
         os.environ.update(DRM_SEARCH_KERNEL=kern, DRM_SEARCH_VIS=vis, DRM_SEARCH_RA=ra)
         D1, I1, st1 = ix.search(Q, k, ef, return_stats=True)

