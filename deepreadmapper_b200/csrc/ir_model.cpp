@@ -10,7 +10,9 @@
 #include <cstring>
 #include <fstream>
 #include <map>
+#include <new>
 #include <sstream>
+#include <stdexcept>
 
 namespace drm {
 
@@ -71,7 +73,24 @@ std::vector<int64_t> parse_shape(const std::string &s)
 
 }  // namespace
 
+static int read_ir_model_impl(const char *xml_path, const char *bin_path, EmbedWeightsHost &w);
+
+// The parser uses std::stoi / stoll / stoull and container .at() on file contents; nothing may be thrown through the C ABI
+// (drm_embedder_open_ir, drm_embedder_ir_info), so every exception becomes DRM_EIO here.
 int read_ir_model(const char *xml_path, const char *bin_path, EmbedWeightsHost &w)
+{
+    try {
+        return read_ir_model_impl(xml_path, bin_path, w);
+    } catch (const std::bad_alloc &) {
+        return fail(DRM_EIO, "IR: a tensor size in the .xml does not fit in memory");
+    } catch (const std::exception &e) {
+        return fail(DRM_EIO, std::string("IR: malformed number or attribute in the .xml (") + e.what() + ")");
+    } catch (...) {
+        return fail(DRM_EIO, "IR: malformed .xml");
+    }
+}
+
+static int read_ir_model_impl(const char *xml_path, const char *bin_path, EmbedWeightsHost &w)
 {
     std::ifstream xf(xml_path, std::ios::binary);
     if (!xf) return fail(DRM_EIO, std::string("cannot open ") + xml_path);
@@ -134,13 +153,15 @@ int read_ir_model(const char *xml_path, const char *bin_path, EmbedWeightsHost &
         for (size_t i = 0; i < dims.size(); ++i) {
             if (want[i] >= 0 && dims[i] != want[i])
                 return fail(DRM_EUNSUPPORTED, std::string("IR: unexpected shape for ") + what + " (" + sh->second + ")");
+            if (dims[i] <= 0 || dims[i] > ((int64_t)1 << 32) || count > ((int64_t)1 << 40) / dims[i])
+                return fail(DRM_EIO, std::string("IR: bad dimension in the shape of ") + what + " (" + sh->second + ")");
             count *= dims[i];
         }
         if (dim0) *dim0 = dims[0];
         const uint64_t off = std::stoull(of->second), size = std::stoull(sz->second);
         const int esz = et->second == "f16" ? 2 : et->second == "f32" ? 4 : 0;
         if (!esz) return fail(DRM_EUNSUPPORTED, std::string("IR: ") + what + " is " + et->second + ", expected f16 or f32");
-        if (size != (uint64_t)count * esz || off + size > blob.size())
+        if (size != (uint64_t)count * esz || off > blob.size() || size > blob.size() - off)
             return fail(DRM_EIO, std::string("IR: ") + what + " does not fit the .bin file");
         out.resize((size_t)count);
         const char *p = blob.data() + off;

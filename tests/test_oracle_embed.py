@@ -83,6 +83,32 @@ def test_ir_reader_rejects_other_architectures(tmp_path):
     assert e.value.code == -2
 
 
+def test_ir_reader_survives_malformed_numbers(tmp_path):
+    """Attributes that std::stoull / stoll / stoi refuse, sizes that overflow, negative and zero dimensions: an error code,
+    never an exception through the C ABI (which would end the process under ctypes)."""
+    import re
+    w = EO.random_weights(5)
+    xml = U.write_ir(str(tmp_path / "m"), w)
+    text = open(xml).read()
+    m_off, m_shape = re.search(r'offset="(\d+)"', text), re.search(r'shape="7638, 64"', text)
+    assert m_off and m_shape
+    cases = [text.replace(m_off.group(0), 'offset="abc"', 1),
+             text.replace(m_off.group(0), 'offset="99999999999999999999999999"', 1),
+             text.replace(m_off.group(0), 'offset="18446744073709551615"', 1),
+             text.replace(m_shape.group(0), 'shape="x, 64"'),
+             text.replace(m_shape.group(0), 'shape="-1, 64"'),
+             text.replace(m_shape.group(0), 'shape="0, 64"'),
+             text.replace(m_shape.group(0), 'shape="4611686018427387904, 64"'),
+             re.sub(r'<layer id="(\d+)"', '<layer id="q\\1"', text, count=1),
+             re.sub(r'from-layer="(\d+)"', 'from-layer="?"', text, count=1)]
+    for i, bad in enumerate(cases):
+        assert bad != text, i
+        open(xml, "w").write(bad)
+        with pytest.raises(drm.DrmError) as e:
+            drm.embedder_ir_info(xml, xml[:-4] + ".bin")
+        assert e.value.code in (-2, -4), (i, e.value.code, str(e.value))
+
+
 @pytest.mark.skipif(not os.path.exists(REF_MODEL + ".xml"), reason="needs /root/reference (build container only)")
 def test_ir_reader_on_the_reference_model(gold):
     vocab, counts, sums = drm.embedder_ir_info(REF_MODEL + ".xml", REF_MODEL + ".bin")
