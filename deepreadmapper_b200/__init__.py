@@ -7,5 +7,5 @@ without the built library, or without a CUDA device, the compute calls raise.
 """
 from .api import (  # noqa: F401
     DrmError, Index, Reads, Reference, Shards, XCHG_ALLGATHER, XCHG_ALLTOALL, XCHG_FUSED, Vectorizer, embedder_ir_info, tokenize, build_index, build_index_gpu, build_index_gpu_device, calc_sw_score, faiss_search, lib, lib_path, merge_topk_device,
-    post_process_l2_dynamic, post_process_l2_static, l2_plan_host, l2_select_host, post_process_sw_dynamic, post_process_sw_static, fasta_clean, search_rerank, search_rerank_reads, sw_pairs, sw_reranker,
+    post_process_l2_dynamic, post_process_l2_static, l2_plan_host, l2_select_host, post_process_sw_dynamic, post_process_sw_static, fasta_clean, search_rerank, search_rerank_reads, sw_pairs, sw_pairs_device_noalloc, sw_reranker,
 )

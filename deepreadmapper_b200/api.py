@@ -39,7 +39,7 @@ EXPORTS = ["drm_last_error", "drm_device_count", "drm_version", "drm_index_open"
            "drm_embedder_ir_info", "drm_tokenize", "drm_embed", "drm_embed_reads", "drm_embed_windows", "drm_embed_device",
            "drm_embed_windows_device", "drm_l2_rerank", "drm_l2_plan_host", "drm_l2_select_host",
            "drm_shards_open", "drm_shards_unique_id", "drm_shards_open_rank", "drm_shards_close", "drm_shards_info", "drm_shards_search_rerank",
-           "drm_shards_step_device", "drm_shards_stats", "drm_l2_last_timing"]
+           "drm_shards_step_device", "drm_shards_stats", "drm_l2_last_timing", "drm_sw_pairs_device_noalloc"]
 
 
 class ShardStats(C.Structure):
@@ -77,6 +77,7 @@ def lib():
         L.drm_ref_close.argtypes = [vp]
         L.drm_ref_close.restype = None
         L.drm_sw_pairs.argtypes = [C.c_char_p, vp, C.c_char_p, vp, i64, vp]
+        L.drm_sw_pairs_device_noalloc.argtypes = [i32, vp, vp, vp, vp, i64, i32, vp, vp]
         L.drm_sw_rerank.argtypes = [vp, i32, vp, i64, i64, C.c_char_p, vp, i64, i64, i64, vp, vp, vp, C.POINTER(C.c_double)]
         L.drm_sw_rerank_device.argtypes = [vp, i32, i32, vp, i64, i64, vp, vp, i32, i64, i64, i64, vp, vp, vp, vp, vp, vp]
         L.drm_merge_topk_device.argtypes = [i32, vp, vp, i32, i64, i32, vp, vp, vp]
@@ -292,6 +293,16 @@ def sw_pairs(a_list, b_list):
     out = np.zeros(len(a_list), dtype=np.int32)
     _check(lib().drm_sw_pairs(a_flat, a_off.ctypes.data, b_flat, b_off.ctypes.data, len(a_list), out.ctypes.data))
     return out
+
+
+SW_PAIRS_NOALLOC_MAX_LEN_B = 4095
+SW_PAIRS_NOALLOC_SCRATCH_BYTES = 16 << 20
+
+
+def sw_pairs_device_noalloc(device, a_flat_ptr, a_off_ptr, b_flat_ptr, b_off_ptr, n, max_len_b, scores_ptr, stream=0):
+    """drm_sw_pairs on device buffers without any allocation inside the call (static 16 MiB scratch per GPU; calls that
+    overlap on one GPU race).  No counterpart in the reference."""
+    _check(lib().drm_sw_pairs_device_noalloc(device, a_flat_ptr, a_off_ptr, b_flat_ptr, b_off_ptr, n, max_len_b, scores_ptr, stream or None))
 
 
 def calc_sw_score(seq1, seq2) -> int:

@@ -962,3 +962,89 @@ int launch_rerank(const DeviceRef &ref, const RerankArgs &a, cudaStream_t stream
 }
 
 }  // namespace drm
+
+// ---------------------------------------------------------------------------------------------------------------------
+// drm_sw_pairs_device_noalloc: the generic SW pair kernel above for callers that may not allocate (CUDA graph capture,
+// serving loops, harnesses that forbid cudaMalloc).  No counterpart in the reference.
+// The kernel's DP rows (launch_sw_pairs takes them from cudaMallocAsync) live in ONE file-scope device array
+// of DRM_SW_PAIRS_NOALLOC_SCRATCH_BYTES that every GPU which loads the library holds until exit.  All calls on a device
+// share it: calls that overlap on the GPU (different streams) race.  Nothing in it has to start at zero - every thread
+// clears its own DP row before each pair - so stale contents of the previous call are harmless.
+namespace drm {
+
+namespace {
+
+constexpr int NOALLOC_MAX_LEN_B = 4095;                                   // DRM_SW_PAIRS_NOALLOC_MAX_LEN_B
+constexpr long long NOALLOC_INTS = 4ll << 20;                             // 16 MiB = DRM_SW_PAIRS_NOALLOC_SCRATCH_BYTES
+static __device__ __align__(256) int g_pairs_scratch[NOALLOC_INTS];
+
+// In host code `g_pairs_scratch` is only a stand-in for the symbol; the device address comes from cudaGetSymbolAddress,
+// once per device, with that device current.
+constexpr int NOALLOC_MAX_DEV = 64;
+int *g_pairs_scratch_dev[NOALLOC_MAX_DEV] = {nullptr};
+std::once_flag g_pairs_scratch_once[NOALLOC_MAX_DEV];
+
+// pairs whose b is longer than the caller's max_len_b would overrun their DP row: they are presented to the kernel as empty
+// (score 0) and marked -1 afterwards by mark_long_pairs_kernel (SW scores are never negative)
+struct FlatPairsBounded {
+    const char *a_flat; const long long *a_off; const char *b_flat; const long long *b_off; int max_len_b;
+    __device__ bool get(long long i, PairView &v) const
+    {
+        v.a = reinterpret_cast<const uint8_t *>(a_flat) + a_off[i]; v.la = (int)(a_off[i + 1] - a_off[i]); v.rc = false;
+        v.b = reinterpret_cast<const uint8_t *>(b_flat) + b_off[i];
+        const long long lb = b_off[i + 1] - b_off[i];
+        v.lb = (int)lb;
+        if (lb > max_len_b) { v.la = 0; v.lb = 0; }
+        v.out = i;
+        return true;
+    }
+};
+
+__global__ void mark_long_pairs_kernel(const long long *__restrict__ b_off, long long n, int max_len_b, int *__restrict__ scores)
+{
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n && b_off[i + 1] - b_off[i] > max_len_b) scores[i] = -1;
+}
+
+}  // namespace
+
+int launch_sw_pairs_noalloc(int device, const char *a_flat, const int64_t *a_off, const char *b_flat, const int64_t *b_off, int64_t n,
+                            int max_len_b, int32_t *scores, cudaStream_t stream)
+{
+    if (device < 0 || device >= NOALLOC_MAX_DEV) return fail(DRM_EINVAL, "drm_sw_pairs_device_noalloc: bad device");
+    if (n < 0 || max_len_b < 0 || (n > 0 && (!a_flat || !a_off || !b_flat || !b_off || !scores)))
+        return fail(DRM_EINVAL, "bad arguments to drm_sw_pairs_device_noalloc");
+    if (max_len_b > NOALLOC_MAX_LEN_B)
+        return fail(DRM_EUNSUPPORTED, "drm_sw_pairs_device_noalloc: max_len_b " + std::to_string(max_len_b) + " is above the limit of " +
+                                          std::to_string(NOALLOC_MAX_LEN_B) + " (static scratch of 16 MiB); use drm_sw_pairs");
+    if (n == 0) return DRM_OK;
+    DRM_CUDA_TRY(cudaSetDevice(device));
+    cudaError_t serr = cudaSuccess;
+    std::call_once(g_pairs_scratch_once[device], [&] {
+        int *ptr = nullptr;
+        serr = cudaGetSymbolAddress(reinterpret_cast<void **>(&ptr), g_pairs_scratch);
+        if (serr == cudaSuccess) g_pairs_scratch_dev[device] = ptr;
+    });
+    if (serr != cudaSuccess) return fail(DRM_ECUDA, std::string("cudaGetSymbolAddress(g_pairs_scratch): ") + cudaGetErrorString(serr));
+    int *H = g_pairs_scratch_dev[device];
+    if (!H) return fail(DRM_ECUDA, "drm_sw_pairs_device_noalloc: the static scratch has no device address on this GPU");
+    // as many DP rows as fit: one per thread, max_len_b + 1 ints each (at least 1024 threads at the length limit)
+    long long threads = NOALLOC_INTS / (max_len_b + 1) / 128 * 128;
+    if (threads > 148LL * 1024) threads = 148LL * 1024;
+    if (n < threads) threads = (n + 127) / 128 * 128;
+    FlatPairsBounded src{a_flat, reinterpret_cast<const long long *>(a_off), b_flat, reinterpret_cast<const long long *>(b_off), max_len_b};
+    sw_generic_kernel<FlatPairsBounded><<<(unsigned)(threads / 128), 128, 0, stream>>>(src, n, H, nullptr, scores);
+    DRM_CUDA_TRY(cudaGetLastError());
+    mark_long_pairs_kernel<<<(unsigned)((n + 255) / 256), 256, 0, stream>>>(reinterpret_cast<const long long *>(b_off), n, max_len_b, scores);
+    DRM_CUDA_TRY(cudaGetLastError());
+    return DRM_OK;
+}
+
+}  // namespace drm
+
+extern "C" int drm_sw_pairs_device_noalloc(int device, const char *a_flat_dev, const int64_t *a_off_dev, const char *b_flat_dev,
+                                           const int64_t *b_off_dev, int64_t n, int max_len_b, int32_t *scores_dev, void *stream)
+{
+    return drm::launch_sw_pairs_noalloc(device, a_flat_dev, a_off_dev, b_flat_dev, b_off_dev, n, max_len_b, scores_dev,
+                                        static_cast<cudaStream_t>(stream));
+}

@@ -97,6 +97,19 @@ void drm_ref_close(drm_ref *r);
 int drm_sw_pairs(const char *a_flat, const int64_t *a_off, const char *b_flat, const int64_t *b_off,
                  int64_t n, int32_t *scores);
 
+/* The same scores for callers that may not allocate (code under CUDA graph capture, serving loops, harnesses that forbid
+ * cudaMalloc).  No counterpart in the reference.  All pointers are DEVICE
+ * pointers on `device` (offsets are int64, n + 1 of them); the launch is asynchronous on `stream`.  The call performs no
+ * cudaMalloc / cudaFree / pool allocation: the kernel's DP rows live in a static device array of
+ * DRM_SW_PAIRS_NOALLOC_SCRATCH_BYTES that every GPU which loads the library holds until exit.  max_len_b = an upper bound on
+ * the length of every b_i, at most DRM_SW_PAIRS_NOALLOC_MAX_LEN_B (DRM_EUNSUPPORTED above it); a pair whose b_i is longer
+ * than max_len_b gets score -1.  Every call on a device shares the one array: calls that overlap on the GPU (two
+ * streams, two host threads) race - serialise them.  Nothing in the array has to be cleared between calls. */
+#define DRM_SW_PAIRS_NOALLOC_MAX_LEN_B 4095
+#define DRM_SW_PAIRS_NOALLOC_SCRATCH_BYTES (16u << 20)
+int drm_sw_pairs_device_noalloc(int device, const char *a_flat_dev, const int64_t *a_off_dev, const char *b_flat_dev,
+                                const int64_t *b_off_dev, int64_t n, int max_len_b, int32_t *scores_dev, void *stream);
+
 /* mode 0 = static bound rule (bound = number of dense windows), 1 = dynamic (bound = genome length;
  * stride == 1 keeps every id, windows that overrun the genome score 0).
  * neighbors: n x k_in int64 search labels; the first min(k_clusters, k_in) of each row are used.

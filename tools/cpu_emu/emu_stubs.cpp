@@ -29,8 +29,9 @@ int launch_sw_pairs(const char *, const int64_t *, const char *, const int64_t *
 
 }  // namespace drm
 
-// C-ABI entry points that live in build_gpu.cu
+// C-ABI entry points that live in build_gpu.cu / sw_kernel.cu
 extern "C" {
+int drm_sw_pairs_device_noalloc(int, const char *, const int64_t *, const char *, const int64_t *, int64_t, int, int32_t *, void *) { return drm::na("the SW pair kernel"); }
 int drm_build_index_gpu(const float *, int64_t, int, const float *, int64_t, int, int, int, int, int, uint32_t, const char *, double *)
 {
     return drm::fail(DRM_EUNSUPPORTED, "the GPU index builder is not available in the host-thread emulation");

@@ -33,6 +33,16 @@ for stage in "$@"; do
 case $stage in
 pytest)
   timeout 900 python -m pytest tests -m gpu -x -q > $O/pytest_gpu.log 2>&1; echo "pytest rc=$?" >> $O/pytest_gpu.log; tail -5 $O/pytest_gpu.log ;;
+noalloc)
+  # alone in a fresh process, and again after another GPU test file in the same process
+  timeout 300 python -m pytest tests/test_zz_no_alloc.py -x -q > $O/pytest_noalloc.log 2>&1; echo "pytest rc=$?" >> $O/pytest_noalloc.log; tail -4 $O/pytest_noalloc.log
+  timeout 600 python -m pytest tests/test_gpu_align.py tests/test_zz_no_alloc.py -x -q > $O/pytest_noalloc_after.log 2>&1; echo "pytest rc=$?" >> $O/pytest_noalloc_after.log; tail -4 $O/pytest_noalloc_after.log ;;
+pfa_ab)
+  for pfa in 1 0; do
+    DRM_SEARCH_PFA=$pfa timeout 300 python bench.py --steps 3 --warmup 3 --skip-cpu --no-realistic --reads 262144 > $O/bench_pfa$pfa.json 2> $O/bench_pfa$pfa.log
+    show pfa$pfa $O/bench_pfa$pfa.json
+  done
+  DRM_SEARCH_PFA=0 ncu_kernel hnswpq_search r2_ncu_search_pfa0 python bench.py --steps 1 --warmup 0 --skip-cpu --no-realistic --reads 131072 ;;
 bench)
   timeout 900 python bench.py > $O/bench.json 2> $O/bench.log; echo "bench rc=$?"; show bench $O/bench.json ;;
 bench_ref)
@@ -73,3 +83,4 @@ chr8)
   if [ -f tools/gpu_stages/$stage.sh ]; then source tools/gpu_stages/$stage.sh; else echo "unknown stage $stage"; fi ;;
 esac
 done
+exit 0
