@@ -482,11 +482,11 @@ def run_ours(args):
         bytes_per_read = 128 * cnt[0] / n + 64 * cnt[1] / n + 8 * cnt[2] / n + 512 + 1536
     ach = bytes_per_read * n / (search_ms / 1e3) / 1e9
     # DRAM traffic per launch: dram__bytes_read.sum + dram__bytes_write.sum of one `ncu --set full` capture of each kernel on this
-    # workload at 131072 reads (profiles/r1_ncu_*_v8.txt), scaled to this launch's read count
-    NCU_DRAM_BYTES_PER_READ = {"search": (7.241585e9 + 202.415e6) / 131072, "sw": (164.082e6 + 125.740e6) / 131072}
+    # workload at 131072 reads (profiles/r2_ncu_search_exact_v4.txt, r2_ncu_sw_final.txt), scaled to this launch's read count
+    NCU_DRAM_BYTES_PER_READ = {"search": (11.571258e9 + 202.479e6) / 131072, "sw": (163.482e6 + 126.715e6) / 131072}
     line["roofline_search"] = {"kernel": "hnswpq_search_exact_kernel", "bound": "hbm", "achieved": ach, "peak": hbm_peak, "unit": "GB/s",
                                "frac": ach / hbm_peak, "traffic": NCU_DRAM_BYTES_PER_READ["search"] * n, "peak_source": peak_src,
-                               "traffic_source": "ncu capture at 131072 reads, scaled by reads (profiles/r2_ncu_search_exact_v2.txt)",
+                               "traffic_source": "ncu capture at 131072 reads, scaled by reads (profiles/r2_ncu_search_exact_v4.txt): 3.3 x the algorithmic bytes = fused 384-byte rows (2.0 x) + gated accept-time L2 prefetch (profiles/r2_ab_search_prefetch_gate.txt)",
                                "algorithmic_bytes_per_read": bytes_per_read, "ms_per_launch": search_ms}
     # issue roofline of the recurrence: 3.5 math instructions per s16x2 cell PAIR (add, max3, clamp, half a best-max3)
     # spread over the alu and fma pipes, each measured at 64 lanes/clk/SM (profiles/r1_ubench_pipes.txt) -> 2*64/3.5 pairs/clk/SM
@@ -501,7 +501,7 @@ def run_ours(args):
                                       "bytes (%.4f of the HBM peak) and has no dense contraction" % (sw_gbps, sw_gbps / hbm_peak),
                         "achieved": g, "peak": int_peak, "unit": "GCUPS", "frac": g / int_peak,
                         "traffic": NCU_DRAM_BYTES_PER_READ["sw"] * min(n, 131072),
-                        "traffic_source": "ncu capture of one 131072-read launch (profiles/r1_ncu_sw_rerank_profile_kernel_v8.txt): 2.2 KB/read, i.e. 4 GB/s - not an HBM-bound kernel",
+                        "traffic_source": "ncu capture of one 131072-read launch (profiles/r2_ncu_sw_final.txt): 2.2 KB/read, i.e. 9 GB/s - not an HBM-bound kernel",
                         "peak_source": "measured pipe rates (profiles/r1_ubench_pipes.txt, r1_ubench_alu.txt) x 3.5 instructions per cell pair at clocks.max.sm; DESIGN.md §4.3",
                         "cells_per_launch": cells, "ms_per_step": sw_ms,
                         "hbm_view": {"bound": "hbm", "achieved": sw_gbps, "peak": hbm_peak, "unit": "GB/s", "frac": sw_gbps / hbm_peak,

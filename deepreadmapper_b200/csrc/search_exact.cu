@@ -59,7 +59,8 @@ struct ExactParams {
     int k, ef, cap;
     int c_words;          // 32-bit words of shared memory per warp for the candidate heap
     int readahead;        // 1: read the row of the runner-up candidate into registers while this row is processed
-    int prefetch_accept;  // 1: L2-prefetch the row of every vertex accepted into the candidate heap
+    int prefetch_accept;  // 1: L2-prefetch the row of every vertex accepted into the candidate heap; 1 + s: only of those in the lowest
+                          //    2^-s of the [popped distance, heap root] interval
     int tma;              // 1: rows arrive through the bulk-copy engine (cp.async.bulk + mbarrier) into a per-warp staging buffer,
                           //    and the accept-time prefetch is one cp.async.bulk.prefetch.L2 instead of one prefetch per line
     int row_stage_bytes;  // per-warp staging: row bytes rounded to 16, + 16 for the mbarrier (0 when tma is off)
@@ -528,6 +529,10 @@ __global__ void __launch_bounds__(XWARPS * 32, 5) hnswpq_search_exact_kernel(con
             unsigned dbits = 0xffffffffu;
             if (valid) dbits = __float_as_uint(x_adc(T, code));
             unsigned root_d = csize == cap ? C2[1].x : 0xffffffffu;
+            // accept-time prefetch gate (prefetch_accept = 1 + s): only vertices in the lowest 2^-s of the [popped distance, root]
+            // interval (on the distance bits) - those are popped soon; the rest are mostly evicted before their turn, and a row
+            // prefetched for them is DRAM traffic for nothing (s = 0: every accepted vertex)
+            const unsigned pf_thr = p.prefetch_accept <= 1 ? 0xffffffffu : d0 + ((root_d - d0) >> (p.prefetch_accept - 1));
             unsigned mask = __ballot_sync(FULL, valid && dbits < root_d);  // the root only decreases: a safe pre-filter
             // a vertex id that occurs twice in this row is new the first time only: the later copies take the scan
             const unsigned twin = __match_any_sync(FULL, valid ? nid : -1 - lane);
@@ -554,11 +559,11 @@ __global__ void __launch_bounds__(XWARPS * 32, 5) hnswpq_search_exact_kernel(con
                 if (csize == cap) root_d = C2[1].x;
 #ifndef DRM_EMU
                 if (p.tma) {
-                    if (p.prefetch_accept && lane == 0) {
+                    if (p.prefetch_accept && lane == 0 && kd <= pf_thr) {
                         const uint8_t *prow = p.rows0 + (size_t)kid * p.row0_bytes;
                         asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(prow), "r"(p.row0_bytes) : "memory");
                     }
-                } else if (p.prefetch_accept && lane < 3) {
+                } else if (p.prefetch_accept && lane < 3 && kd <= pf_thr) {
                     const uint8_t *prow = p.rows0 + (size_t)kid * p.row0_bytes + lane * 128;
                     if (lane * 128 < p.row0_bytes) asm volatile("prefetch.global.L2 [%0];" ::"l"(prow));
                 }
@@ -682,9 +687,10 @@ int launch_search_exact_ex(const DeviceIndex &dx, const float *q_dev, int64_t n,
     p.entry_vertex = dx.entry_vertex; p.entry_row = dx.entry_row; p.ntotal = dx.ntotal; p.max_level = dx.max_level;
     p.k = k; p.ef = ef; p.cap = ef > k ? ef : k;
     p.c_words = ((p.cap + 2) * 2 + 3) / 4 * 4;  // entries 0 .. cap + 1, 8 bytes each, 16-byte multiple
-    p.readahead = 0; p.prefetch_accept = 1;  // A/B on B200 (profiles/r2_ab_search_exact.txt): accept-time L2 prefetch beats the register read-ahead
+    p.readahead = 0; p.prefetch_accept = 2;  // A/B on B200 (profiles/r2_ab_search_exact.txt, r2_ab_search_prefetch_gate.txt): the gated accept-time
+                                             // L2 prefetch beats the register read-ahead, and the ungated one costs 20 % more DRAM traffic for nothing
     if (const char *e = getenv("DRM_SEARCH_RA")) p.readahead = atoi(e) != 0;
-    if (const char *e = getenv("DRM_SEARCH_PFA")) p.prefetch_accept = atoi(e) != 0;
+    if (const char *e = getenv("DRM_SEARCH_PFA")) p.prefetch_accept = atoi(e) < 0 ? 0 : atoi(e) > 8 ? 8 : atoi(e);
     p.tma = 0;
     if (const char *e = getenv("DRM_SEARCH_TMA")) p.tma = atoi(e) != 0;
     if (p.row0_bytes % 16) p.tma = 0;  // the bulk-copy engine moves multiples of 16 bytes

@@ -204,16 +204,16 @@ def mid_index(tmp_path_factory):
     return p, synth.embed_reads(reads), ids
 
 
-@pytest.fixture(params=["exact", "exact_vis1024", "exact_novis", "exact_ra", "exact_nopfa", "exact_tma", "reg", "reg_vis1024", "reg_novis", "smem", "pair"])
+@pytest.fixture(params=["exact", "exact_vis1024", "exact_novis", "exact_ra", "exact_nopfa", "exact_pfa_all", "exact_tma", "reg", "reg_vis1024", "reg_novis", "smem", "pair"])
 def search_variant(request, monkeypatch):
     """exact* = the default kernel (search_exact.cu: FAISS's own tie behaviour, oracle tie_rule 0) with the 512- / 1024-slot
-    visited cache or none, with the register read-ahead, without the accept-time L2 prefetch, with bulk-copy (TMA) row staging; reg* / smem / pair = the
+    visited cache or none, with the register read-ahead, without the accept-time L2 prefetch / with the ungated one, with bulk-copy (TMA) row staging; reg* / smem / pair = the
     canonical-order kernels of search_kernel.cu (oracle tie_rule 1).  Each must return its oracle's bits."""
     v = request.param
     monkeypatch.setenv("DRM_SEARCH_KERNEL", v if v in ("smem", "pair") else "reg" if v.startswith("reg") else "exact")
     monkeypatch.setenv("DRM_SEARCH_VIS", "0" if v.endswith("novis") else "1024" if v.endswith("vis1024") else "512")
     monkeypatch.setenv("DRM_SEARCH_RA", "1" if v == "exact_ra" else "0")
-    monkeypatch.setenv("DRM_SEARCH_PFA", "0" if v == "exact_nopfa" else "1")
+    monkeypatch.setenv("DRM_SEARCH_PFA", "0" if v == "exact_nopfa" else "1" if v == "exact_pfa_all" else "2")
     monkeypatch.setenv("DRM_SEARCH_TMA", "1" if v == "exact_tma" else "0")
     return v
 

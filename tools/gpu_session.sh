@@ -38,11 +38,16 @@ noalloc)
   timeout 300 python -m pytest tests/test_zz_no_alloc.py -x -q > $O/pytest_noalloc.log 2>&1; echo "pytest rc=$?" >> $O/pytest_noalloc.log; tail -4 $O/pytest_noalloc.log
   timeout 600 python -m pytest tests/test_gpu_align.py tests/test_zz_no_alloc.py -x -q > $O/pytest_noalloc_after.log 2>&1; echo "pytest rc=$?" >> $O/pytest_noalloc_after.log; tail -4 $O/pytest_noalloc_after.log ;;
 pfa_ab)
-  for pfa in 1 0; do
+  # accept-time L2 prefetch: off / every accepted vertex / gated to the lowest 1/2, 1/4, 1/8 of the [popped, root] interval
+  timeout 600 python -m pytest tests/test_gpu_parity.py -x -q -k "search" > $O/pytest_search.log 2>&1; echo "pytest rc=$?" >> $O/pytest_search.log; tail -3 $O/pytest_search.log
+  for pfa in 1 2 3 4 0; do
     DRM_SEARCH_PFA=$pfa timeout 300 python bench.py --steps 3 --warmup 3 --skip-cpu --no-realistic --reads 262144 > $O/bench_pfa$pfa.json 2> $O/bench_pfa$pfa.log
     show pfa$pfa $O/bench_pfa$pfa.json
   done
-  DRM_SEARCH_PFA=0 ncu_kernel hnswpq_search r2_ncu_search_pfa0 python bench.py --steps 1 --warmup 0 --skip-cpu --no-realistic --reads 131072 ;;
+  for pfa in 2 3; do
+    DRM_SEARCH_PFA=$pfa ncu_kernel hnswpq_search r2_ncu_search_pfa$pfa python bench.py --steps 1 --warmup 0 --skip-cpu --no-realistic --reads 131072
+    grep -E "dram__bytes_read.sum \[|gpu__time_duration" $O/r2_ncu_search_pfa$pfa.summary.txt
+  done ;;
 bench)
   timeout 900 python bench.py > $O/bench.json 2> $O/bench.log; echo "bench rc=$?"; show bench $O/bench.json ;;
 bench_ref)
