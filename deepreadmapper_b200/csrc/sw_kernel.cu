@@ -273,7 +273,11 @@ constexpr int PTAB_ENTRIES = 25 * PGROUPS * 8;
 // ALU_EVERY picks the mix so that the alu and fma pipes (each one warp instruction per 2 clocks per SMSP) carry
 // equal shares:  1 = every clamp on the alu pipe (integer form throughout), 0 = every clamp on the fma pipe,
 // n >= 2 = every n-th clamp on the alu pipe, the rest on the fma pipe.
-template <int ALU_EVERY>
+// POFF: the staged rows of a window pair are ONE array of 16-bit byte offsets into the table ((5a + b) * PGROUPS * 8 * 16,
+// precomputed by the staging pass) instead of two class bytes, so the per-row table address is one LDS.U16 + one add.
+// UNR: rows per trip of the row loop.  ptxas renames the H registers from row to row (operand bank conflicts) and restores the
+// mapping with moves at the end of the trip: 9 moves per row at 2 rows per trip, 5 at 8.
+template <int ALU_EVERY, bool POFF = false, int UNR = 2>
 __device__ __forceinline__ unsigned sw_quad_profile(const uint8_t *rowA, const uint8_t *rowB, int rows, const uint4 *tab, int lane, unsigned one)
 {
     constexpr bool F32ADD = ALU_EVERY >= 100;  // ALU_EVERY = 100 + n: the add runs as an fp32 FADD, clamp mix n as below
@@ -286,11 +290,13 @@ __device__ __forceinline__ unsigned sw_quad_profile(const uint8_t *rowA, const u
     unsigned best = 0, last_out = 0, prev_recv = 0;
     const unsigned NEG1 = 0xffffffffu;
     const unsigned H_ONE = 0x3c003c00u, H_NEGULP = 0x80018001u;  // (1.0h, 1.0h), (-2^-24, -2^-24)
-#pragma unroll 2
+    const unsigned short *poff = reinterpret_cast<const unsigned short *>(rowA) + (3 - l);
+#pragma unroll UNR
     for (int t = 0; t < rows + 3; ++t) {
         unsigned recv = __shfl_up_sync(FULL, last_out, 1, 4);
         if (l == 0) recv = 0;
-        const uint4 *prow = tslot + (5u * rowA[t - l + 3] + rowB[t - l + 3]) * (PGROUPS * 8);
+        const uint4 *prow = POFF ? reinterpret_cast<const uint4 *>(reinterpret_cast<const unsigned char *>(tslot) + poff[t])
+                                 : tslot + (5u * rowA[t - l + 3] + rowB[t - l + 3]) * (PGROUPS * 8);
         unsigned diag = prev_recv, left = recv, mprev = 0;
 #pragma unroll
         for (int g = 0; g < PGROUPS; ++g) {
@@ -430,10 +436,36 @@ template <int THREADS> __device__ __forceinline__ int block_exclusive_scan(int *
     return total;
 }
 
+// Four consecutive rows rr0 .. rr0 + 3 of window `id` as class bytes (0..3; 4 = matches nothing: outside the window, N, or an
+// id whose window overruns the reference).  Reads the two aligned words that cover the four source bases (the class array
+// carries 16 bytes of padding either side), funnel-shifts them into place, and for a reverse-complement id reverses the
+// bytes and complements them (c ^ 3).
+__device__ __forceinline__ unsigned stage_classes4(const RerankDev &p, u64 id, int rows, int rr0)
+{
+    if (!window_valid(p, id)) return 0x04040404u;
+    const bool rc = p.form == 0 && (id & 1);
+    const uint8_t *src = p.form == 1 ? p.ref + id * (u64)rows : p.ref + (id >> 1);
+    const uint8_t *a = rc ? src + (rows - 4 - rr0) : src + rr0;  // lowest source address of the four
+    const unsigned long long ai = reinterpret_cast<unsigned long long>(a);
+    const unsigned *aw = reinterpret_cast<const unsigned *>(ai & ~3ull);
+    const unsigned lo = __ldg(aw), hi = __ldg(aw + 1);
+    unsigned v = __funnelshift_r(lo, hi, ((unsigned)ai & 3u) * 8u);
+    if (rc) v = __byte_perm(v, 0u, 0x0123) ^ 0x03030303u;
+    const unsigned big = ((v >> 2) & 0x01010101u) * 0xffu;  // bytes holding a class >= 4 (N, other)
+    v = (v & ~big) | (0x04040404u & big);
+    if (rr0 < 0 || rr0 + 4 > rows) {
+#pragma unroll
+        for (int b = 0; b < 4; ++b)
+            if ((unsigned)(rr0 + b) >= (unsigned)rows) v = (v & ~(0xffu << (8 * b))) | (4u << (8 * b));
+    }
+    return v;
+}
+
 // Dynamic shared memory layout (bytes): tab | sel[2 * PAIRS][selw] (one byte row per candidate) | cand[C] | first[take] | count[take+1]
 // THREADS = 256 (2 CTAs / SM, 128 candidates per pass) or 128 (4 CTAs / SM, 64 per pass).
 // DENSE: ask ptxas for 768 instead of 512 resident threads per SM (80 instead of 117 registers: 3 CTAs of 256 per SM).
-template <int RPI, int ALU_EVERY, int THREADS, bool DENSE>
+// POFF (one row per iteration only): sel holds, per window PAIR, one row of 16-bit table offsets (sw_quad_profile) - the same bytes.
+template <int RPI, int ALU_EVERY, int THREADS, bool DENSE, bool POFF = false, int UNR = 2>
 __global__ void __launch_bounds__(THREADS, (DENSE ? 768 : 512) / THREADS) sw_rerank_profile_kernel(const RerankDev p, int selw, unsigned one, int *fb_list, int *fb_n)
 {
     constexpr int PAIRS = THREADS / 4;
@@ -510,7 +542,27 @@ __global__ void __launch_bounds__(THREADS, (DENSE ? 768 : 512) / THREADS) sw_rer
         // nothing (outside the window, N, or an id whose window overruns the reference).  A task reads the two aligned words
         // that cover its four source bases (the class array carries 16 bytes of padding either side), funnel-shifts them
         // into place, and for a reverse-complement id reverses the bytes and complements them (c ^ 3).
-        {
+        if (POFF) {
+            // one task = four rows of a PAIR: offsets (5a + b) * 1280 of the pair's table rows, four 16-bit values
+            const int ntask = npairs * wpr;
+            int c = tid / wpr, w = tid - c * wpr;
+            const int dc = THREADS / wpr, dw = THREADS - dc * wpr;
+#pragma unroll 2
+            for (int e = tid; e < ntask; e += THREADS) {
+                const int ca = c0 + 2 * c;
+                const int rr0 = 4 * w - PAD;
+                const unsigned va = stage_classes4(p, s_cand[ca], rows, rr0);
+                const unsigned vb = ca + 1 < nc ? stage_classes4(p, s_cand[ca + 1], rows, rr0) : 0x04040404u;
+                const unsigned ab = va * 5u + vb;  // per byte <= 24: no carries
+                constexpr unsigned ROWB = PGROUPS * 8 * sizeof(uint4);  // 1280: 24 * 1280 fits 16 bits
+                uint2 o;
+                o.x = __byte_perm(ab, 0u, 0x4140) * ROWB;
+                o.y = __byte_perm(ab, 0u, 0x4342) * ROWB;
+                *reinterpret_cast<uint2 *>(s_sel + (size_t)c * 2 * selw + 8 * w) = o;
+                c += dc; w += dw;
+                if (w >= wpr) { w -= wpr; ++c; }
+            }
+        } else {
             const int ntask = 2 * npairs * wpr;
             int c = tid / wpr, w = tid - c * wpr;
             const int dc = THREADS / wpr, dw = THREADS - dc * wpr;
@@ -549,7 +601,7 @@ __global__ void __launch_bounds__(THREADS, (DENSE ? 768 : 512) / THREADS) sw_rer
         if ((tid >> 5) * 8 < npairs) {
             const int pp = pair < npairs ? pair : 0;
             const uint8_t *rowA = s_sel + (size_t)(2 * pp) * selw, *rowB = rowA + selw;
-            unsigned best = RPI == 2 ? sw_quad_profile2<ALU_EVERY>(rowA, rowB, rows, tab, lane) : sw_quad_profile<ALU_EVERY>(rowA, rowB, rows, tab, lane, one);
+            unsigned best = RPI == 2 ? sw_quad_profile2<ALU_EVERY>(rowA, rowB, rows, tab, lane) : sw_quad_profile<ALU_EVERY, POFF, UNR>(rowA, rowB, rows, tab, lane, one);
             if ((lane & 3) == 0 && pair < npairs) {
                 int sa = (int)(short)(best & 0xffffu) - 1, sb = (int)(short)(best >> 16) - 1;
                 int ca = c0 + 2 * pair;
@@ -868,8 +920,8 @@ int launch_rerank(const DeviceRef &ref, const RerankArgs &a, cudaStream_t stream
     // per iteration: 10 / 11 / 12 / 14 = none / every / every 2nd / every 4th clamp of the second row on the alu pipe.
     // DRM_SW_KERNEL overrides the default, for A/B measurements and the parity tests.
     static const struct { const char *name; int v; } kVariants[] = {{"prmt", 0}, {"profile", 1}, {"profile16", 2}, {"blend2", 3},
-        {"blend4", 4}, {"r2a0", 10}, {"r2a1", 11}, {"r2a2", 12}, {"r2a4", 14}, {"f32p16", 20}, {"f32b2", 21}, {"f32b4", 22}, {"f32b3", 23}};
-    int variant = 4;  // blend4 + the 80-register build: profiles/r1_ab_v7_sw_dense.txt
+        {"blend4", 4}, {"blend4o", 5}, {"blend4o4", 6}, {"blend4o8", 7}, {"blend4u8", 8}, {"blend3o8", 9}, {"r2a0", 10}, {"r2a1", 11}, {"r2a2", 12}, {"r2a4", 14}, {"f32p16", 20}, {"f32b2", 21}, {"f32b4", 22}, {"f32b3", 23}};
+    int variant = 9;  // blend3o8 + the 80-register build: profiles/r1_ab_v7_sw_dense.txt, profiles/r2_ab_sw_rowloop.txt
     if (const char *e = getenv("DRM_SW_KERNEL"))
         for (const auto &kv : kVariants)
             if (!strcmp(e, kv.name)) variant = kv.v;
@@ -900,30 +952,35 @@ int launch_rerank(const DeviceRef &ref, const RerankArgs &a, cudaStream_t stream
         if (fast && variant != 0) {
             p.ref = ref.data;
             DRM_CUDA_TRY(cudaMemsetAsync(fb, 0, sizeof(int), stream));
-#define DRM_PROFILE_LAUNCH_T(R, A, T, DN)                                                                                                 \
-    do {                                                                                                                                   \
-        DRM_CUDA_TRY(cudaFuncSetAttribute(sw_rerank_profile_kernel<R, A, T, DN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)psmem)); \
-        sw_rerank_profile_kernel<R, A, T, DN><<<(unsigned)nb, T, psmem, stream>>>(p, selw, 1u, fb + 1, fb);                                \
+#define DRM_PROFILE_LAUNCH_T(R, A, T, DN, PO, UN)                                                                                               \
+    do {                                                                                                                                       \
+        DRM_CUDA_TRY(cudaFuncSetAttribute(sw_rerank_profile_kernel<R, A, T, DN, PO, UN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)psmem)); \
+        sw_rerank_profile_kernel<R, A, T, DN, PO, UN><<<(unsigned)nb, T, psmem, stream>>>(p, selw, 1u, fb + 1, fb);                                \
     } while (0)
-#define DRM_PROFILE_LAUNCH(R, A)                                            \
-    do {                                                                    \
-        if (pthreads == 128) DRM_PROFILE_LAUNCH_T(R, A, 128, false);        \
-        else if (pdense) DRM_PROFILE_LAUNCH_T(R, A, 256, true);             \
-        else DRM_PROFILE_LAUNCH_T(R, A, 256, false);                        \
+#define DRM_PROFILE_LAUNCH(R, A, PO, UN)                                        \
+    do {                                                                        \
+        if (pthreads == 128) DRM_PROFILE_LAUNCH_T(R, A, 128, false, PO, UN);       \
+        else if (pdense) DRM_PROFILE_LAUNCH_T(R, A, 256, true, PO, UN);            \
+        else DRM_PROFILE_LAUNCH_T(R, A, 256, false, PO, UN);                       \
     } while (0)
             switch (variant) {
-            case 1: DRM_PROFILE_LAUNCH(1, 1); break;
-            case 2: DRM_PROFILE_LAUNCH(1, 0); break;
-            case 3: DRM_PROFILE_LAUNCH(1, 2); break;
-            case 4: DRM_PROFILE_LAUNCH(1, 4); break;
-            case 20: DRM_PROFILE_LAUNCH(1, 100); break;
-            case 21: DRM_PROFILE_LAUNCH(1, 102); break;
-            case 22: DRM_PROFILE_LAUNCH(1, 104); break;
-            case 23: DRM_PROFILE_LAUNCH(1, 103); break;
-            case 10: DRM_PROFILE_LAUNCH(2, 0); break;
-            case 11: DRM_PROFILE_LAUNCH(2, 1); break;
-            case 12: DRM_PROFILE_LAUNCH(2, 2); break;
-            default: DRM_PROFILE_LAUNCH(2, 4); break;
+            case 1: DRM_PROFILE_LAUNCH(1, 1, false, 2); break;
+            case 2: DRM_PROFILE_LAUNCH(1, 0, false, 2); break;
+            case 3: DRM_PROFILE_LAUNCH(1, 2, false, 2); break;
+            case 4: DRM_PROFILE_LAUNCH(1, 4, false, 2); break;
+            case 5: DRM_PROFILE_LAUNCH(1, 4, true, 2); break;
+            case 6: DRM_PROFILE_LAUNCH(1, 4, true, 4); break;
+            case 7: DRM_PROFILE_LAUNCH(1, 4, true, 8); break;
+            case 8: DRM_PROFILE_LAUNCH(1, 4, false, 8); break;
+            case 9: DRM_PROFILE_LAUNCH(1, 3, true, 8); break;
+            case 20: DRM_PROFILE_LAUNCH(1, 100, false, 2); break;
+            case 21: DRM_PROFILE_LAUNCH(1, 102, false, 2); break;
+            case 22: DRM_PROFILE_LAUNCH(1, 104, false, 2); break;
+            case 23: DRM_PROFILE_LAUNCH(1, 103, false, 2); break;
+            case 10: DRM_PROFILE_LAUNCH(2, 0, false, 2); break;
+            case 11: DRM_PROFILE_LAUNCH(2, 1, false, 2); break;
+            case 12: DRM_PROFILE_LAUNCH(2, 2, false, 2); break;
+            default: DRM_PROFILE_LAUNCH(2, 4, false, 2); break;
             }
 #undef DRM_PROFILE_LAUNCH_T
 #undef DRM_PROFILE_LAUNCH

@@ -65,7 +65,7 @@ def test_sw_pairs_random_vs_oracle(drm, ob):
     assert drm.sw_pairs(a, b).tolist() == ob.sw_pairs(a, b).tolist()
 
 
-@pytest.fixture(params=["default", "prmt", "profile", "profile16", "blend2", "blend4", "r2a0", "r2a1", "r2a2", "r2a4", "f32p16", "f32b2", "f32b3", "f32b4"])
+@pytest.fixture(params=["default", "prmt", "profile", "profile16", "blend2", "blend4", "blend4o", "blend4o4", "blend4o8", "blend4u8", "blend3o8", "r2a0", "r2a1", "r2a2", "r2a4", "f32p16", "f32b2", "f32b3", "f32b4"])
 def sw_variant(request, monkeypatch):
     """Every rerank parity test runs on the three SW kernel variants (DESIGN.md "SW kernels")."""
     if request.param == "default":
