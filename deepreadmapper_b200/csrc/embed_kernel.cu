@@ -15,7 +15,10 @@
 // Scratch (Y1: 63 KB, X2: 189 KB per sequence) is sized for a pass of 148 x 16 x 4 sequences (4 CTA waves).
 #include "common.h"
 
+#include <cuda_fp16.h>
+
 #include <cstdlib>
+#include <cstring>
 
 namespace drm {
 
@@ -296,6 +299,286 @@ template <class T> int upload(const std::vector<T> &h, T **d)
     return DRM_OK;
 }
 
+
+#ifndef DRM_EMU
+// ---------------------------------------------------------------------------------------------------------------------
+// Tensor-core form of the recurrences (tcgen05 + TMEM; DRM_EMBED_TC=0 selects the fp32 kernels above).
+//
+// One CTA = 128 sequences x ONE direction; thread s owns sequence s of the tile (= row s of the accumulator = TMEM lane s).
+// Per step the gate pre-activations of all 128 sequences are ONE product on the 5th-generation tensor cores,
+//     D[128 seq x gates] (fp32, TMEM)  =  A[128 seq x K] (fp16, shared)  .  B[gates x K]^T (fp16, shared)
+// issued by one thread (tcgen05.mma.cta_group::1.kind::f16, M = 128), completion signalled through tcgen05.commit on an
+// mbarrier; every thread then reads its row back with tcgen05.ld.32x32b, applies the gates in fp32 and writes its new state
+// into the A operand of the next step.
+//   * The weights are fp16-exact in the reference's model (IR constants are f16), so B is exact.  The activations are fp32
+//     values in (-1, 1): they enter as hi + lo with hi = fp16(h), lo = fp16(h - hi), two products accumulated into the same
+//     TMEM columns - a 22-bit significand, absolute error below 2^-24 per term; measured against the fp32 kernels in
+//     tests/test_gpu_zz_embed.py.
+//   * Layer 1: K = 64 (R1 . h); the input projection is the per-token table P1, gathered in the epilogue.  N = 192.
+//   * Layer 2: K = 128 + 64: [y1_t | h].  The input projection W2 . y1_t is FUSED into the step's product, so X2 (189 KB per
+//     sequence) is never written: rows z, r take the whole K (N = 128); the candidate gate keeps its two halves apart because
+//     r multiplies only the recurrent half: rows h over K = 0..127 (N = 64) and over K = 128..191 (N = 64) -> 256 columns.
+//   * Operand layout in shared memory (K-major, no swizzle; the canonical UMMA "interleave" layout): 16-byte chunk
+//     (row r, k-group g = k / 8) at g * rows * 16 + r * 16  ->  8 rows x 16 B core matrices are contiguous (SBO = 128 B),
+//     consecutive k-groups are rows * 16 B apart (LBO).  Thread s writes chunk (s, g): consecutive threads, consecutive
+//     16-byte words, no bank conflicts.
+//   * Layer 1 hands its states to layer 2 already split: Y1h[seq][t][hi 128 | lo 128] halves (512 B per step, the same bytes
+//     as fp32 states).
+constexpr int TC_M = 128;                 // sequences per CTA
+constexpr int TC_K1 = EH, TC_K2 = 2 * EH + EH;
+constexpr int TC_COLS = 256;              // TMEM columns per CTA (power of two >= 192 / 256)
+
+__device__ __forceinline__ unsigned smem_u32(const void *p) { return (unsigned)__cvta_generic_to_shared(p); }
+
+// shared-memory matrix descriptor: start address, leading (k-group) and stride (8-row group) byte offsets in 16-byte units,
+// descriptor version 1 (sm_100), no swizzle
+__device__ __forceinline__ unsigned long long umma_desc(unsigned saddr, unsigned lbo_bytes, unsigned sbo_bytes)
+{
+    return (unsigned long long)((saddr >> 4) & 0x3fffu) | ((unsigned long long)((lbo_bytes >> 4) & 0x3fffu) << 16) |
+           ((unsigned long long)((sbo_bytes >> 4) & 0x3fffu) << 32) | (1ull << 46);
+}
+// instruction descriptor, kind::f16: D = fp32, A = B = fp16, both K-major, dense; N >> 3 at bit 17, M >> 4 at bit 24
+__host__ __device__ constexpr unsigned umma_idesc(int m, int n) { return (1u << 4) | ((unsigned)(n >> 3) << 17) | ((unsigned)(m >> 4) << 24); }
+
+__device__ __forceinline__ void umma_f16(unsigned d_tmem, unsigned long long adesc, unsigned long long bdesc, unsigned idesc, unsigned accumulate)
+{
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\ttcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+                 ::"r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+}
+__device__ __forceinline__ void tmem_ld16(unsigned taddr, float (&v)[16])
+{
+    unsigned r[16];
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]), "=r"(r[9]),
+                   "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+                 : "r"(taddr));
+#pragma unroll
+    for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
+}
+__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+
+__device__ __forceinline__ float tc_sigmoid(float x) { return __fdividef(1.0f, 1.0f + __expf(-x)); }
+__device__ __forceinline__ float tc_tanh(float x) { return 2.0f * __fdividef(1.0f, 1.0f + __expf(-2.0f * x)) - 1.0f; }
+
+// h -> (hi, lo) fp16 pair, packed two values per word
+__device__ __forceinline__ void split2(float a, float b, unsigned &hi, unsigned &lo)
+{
+    const __half ah = __float2half_rn(a), bh = __float2half_rn(b);
+    const __half al = __float2half_rn(a - __half2float(ah)), bl = __float2half_rn(b - __half2float(bh));
+    hi = (unsigned)__half_as_ushort(ah) | ((unsigned)__half_as_ushort(bh) << 16);
+    lo = (unsigned)__half_as_ushort(al) | ((unsigned)__half_as_ushort(bl) << 16);
+}
+
+// Dynamic shared memory: Bw [K/8][192][16 B] | Ah [K/8][128][16 B] | Al [K/8][128][16 B] | bias floats | tokens (layer 1) | mbarrier, TMEM address
+template <int LAYER> struct TcLayout {
+    static constexpr int K = LAYER == 1 ? TC_K1 : TC_K2;
+    static constexpr int KG = K / 8;
+    static constexpr int B_BYTES = KG * EG * 16;
+    static constexpr int A_BYTES = KG * TC_M * 16;
+    static constexpr int BIAS_FLOATS = LAYER == 1 ? EH : EG + EH;
+    static constexpr int OFF_AH = B_BYTES, OFF_AL = B_BYTES + A_BYTES, OFF_BIAS = B_BYTES + 2 * A_BYTES;
+    static constexpr int OFF_TOK = OFF_BIAS + BIAS_FLOATS * 4;
+    static constexpr int OFF_BAR = OFF_TOK + (LAYER == 1 ? ET_MAX * TC_M : 0);
+    static constexpr int BYTES = OFF_BAR + 16;
+};
+
+template <int LAYER>
+__global__ void __launch_bounds__(TC_M, 1)
+gru_tc_kernel(const SrcDev src, const long long first, const long long n, const int T, const float *__restrict__ P1,
+              const uint4 *__restrict__ Bw_g, const float *__restrict__ bias_g, const __half *__restrict__ Y1h_in,
+              __half *__restrict__ Y1h_out, float *__restrict__ out)
+{
+    using L = TcLayout<LAYER>;
+    extern __shared__ __align__(1024) unsigned char tsm[];
+    uint4 *Bw = reinterpret_cast<uint4 *>(tsm);
+    uint4 *Ah = reinterpret_cast<uint4 *>(tsm + L::OFF_AH);
+    uint4 *Al = reinterpret_cast<uint4 *>(tsm + L::OFF_AL);
+    float *bias = reinterpret_cast<float *>(tsm + L::OFF_BIAS);   // layer 1: bR[64]; layer 2: b2[192] | bR[64]
+    unsigned char *tok = tsm + L::OFF_TOK;                          // [t][s]
+    unsigned long long *bar = reinterpret_cast<unsigned long long *>(tsm + L::OFF_BAR);
+    unsigned *tmem_slot = reinterpret_cast<unsigned *>(tsm + L::OFF_BAR + 8);
+
+    const int tid = threadIdx.x, warp = tid >> 5;
+    const int dir = blockIdx.x & 1;
+    const long long seq = (long long)(blockIdx.x >> 1) * TC_M + tid;  // inside the pass
+    const bool live = seq < n;
+
+    // ---- one-time set-up: weights of this direction, biases, zero state, tokens, mbarrier, TMEM columns
+    {
+        const uint4 *g = Bw_g + (size_t)dir * (L::B_BYTES / 16);
+        for (int p = tid; p < L::B_BYTES / 16; p += TC_M) Bw[p] = __ldg(g + p);
+        for (int p = tid; p < L::BIAS_FLOATS; p += TC_M) bias[p] = bias_g[dir * L::BIAS_FLOATS + p];
+        const uint4 z4 = make_uint4(0u, 0u, 0u, 0u);
+        for (int p = tid; p < 2 * L::A_BYTES / 16; p += TC_M) Ah[p] = z4;  // Ah and Al are adjacent
+    }
+    if (LAYER == 1) {
+        SeqView v = seq_view(src, first + (live ? seq : 0));
+        if (!live) v.n = 0;
+        for (int t = 0; t < T; ++t) tok[t * TC_M + tid] = (unsigned char)token_slot(v, t, T);
+    }
+    const unsigned bar_s = smem_u32(bar);
+    if (tid == 0) {
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar_s) : "memory");
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 0) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(TC_COLS) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const unsigned tmem = *tmem_slot;
+    const unsigned trow = tmem + ((unsigned)(warp * 32) << 16);  // this warp's 32 lanes
+
+    const unsigned ah_s = smem_u32(Ah), al_s = smem_u32(Al), bw_s = smem_u32(Bw);
+    constexpr unsigned A_LBO = TC_M * 16, B_LBO = EG * 16, SBO = 128;
+
+    float h[EH];
+#pragma unroll
+    for (int i = 0; i < EH; ++i) h[i] = 0.0f;
+
+    unsigned phase = 0;
+    for (int step = 0; step < T; ++step) {
+        const int t = dir ? T - 1 - step : step;
+        if (LAYER == 2) {  // this step's input: the layer-1 states of both directions at time t, already split hi | lo
+            const uint4 *y = reinterpret_cast<const uint4 *>(Y1h_in + ((size_t)(live ? seq : 0) * T + t) * (4 * EH));
+#pragma unroll
+            for (int g = 0; g < 2 * EH / 8; ++g) {
+                Ah[g * TC_M + tid] = __ldg(y + g);
+                Al[g * TC_M + tid] = __ldg(y + 2 * EH / 8 + g);
+            }
+        }
+        // generic-proxy writes of A (this step's input, last step's state) -> visible to the tensor core's async proxy
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");  // the reads of D below precede the next product
+        __syncthreads();
+        if (tid == 0) {
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            if (LAYER == 1) {
+                constexpr unsigned idesc = umma_idesc(TC_M, EG);
+#pragma unroll
+                for (int half = 0; half < 2; ++half)
+#pragma unroll
+                    for (int ks = 0; ks < TC_K1 / 16; ++ks)
+                        umma_f16(tmem, umma_desc((half ? al_s : ah_s) + ks * 2 * A_LBO, A_LBO, SBO), umma_desc(bw_s + ks * 2 * B_LBO, B_LBO, SBO), idesc,
+                                 (half | ks) ? 1u : 0u);
+            } else {
+                constexpr unsigned idesc_zr = umma_idesc(TC_M, 2 * EH), idesc_h = umma_idesc(TC_M, EH);
+#pragma unroll
+                for (int half = 0; half < 2; ++half) {
+                    const unsigned a_s = half ? al_s : ah_s;
+#pragma unroll
+                    for (int ks = 0; ks < TC_K2 / 16; ++ks) {
+                        const unsigned long long ad = umma_desc(a_s + ks * 2 * A_LBO, A_LBO, SBO);
+                        // rows z, r (0..127) over the whole K -> columns 0..127
+                        umma_f16(tmem, ad, umma_desc(bw_s + ks * 2 * B_LBO, B_LBO, SBO), idesc_zr, (half | ks) ? 1u : 0u);
+                        // rows h (128..191): the input half (K < 128) -> columns 128..191, the recurrent half -> columns 192..255
+                        const unsigned long long bd = umma_desc(bw_s + ks * 2 * B_LBO + 2 * EH * 16, B_LBO, SBO);
+                        if (ks < 2 * EH / 16) umma_f16(tmem + 2 * EH, ad, bd, idesc_h, (half | ks) ? 1u : 0u);
+                        else umma_f16(tmem + 3 * EH, ad, bd, idesc_h, (half | (ks - 2 * EH / 16)) ? 1u : 0u);
+                    }
+                }
+            }
+            asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar_s) : "memory");
+        }
+        {   // wait for the products of this step
+            unsigned done = 0, spins = 0;
+            do {
+                asm volatile("{\n\t.reg .pred P1;\n\tmbarrier.try_wait.parity.shared::cta.b64 P1, [%1], %2;\n\tselp.b32 %0, 1, 0, P1;\n\t}"
+                             : "=r"(done) : "r"(bar_s), "r"(phase) : "memory");
+                if (!done && ++spins > (1u << 24)) __trap();  // a product that never completes must not hang the GPU
+            } while (!done);
+            phase ^= 1u;
+        }
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+
+        // ---- gates, 16 units at a time: z = s(xz + az), r = s(xr + ar), g = tanh(xh + r (ah + bRh)), h' = (1 - z) g + z h
+        const float *xp = LAYER == 1 ? P1 + (size_t)(dir * NSLOT + tok[t * TC_M + tid]) * EG : nullptr;
+        const float *bRh = LAYER == 1 ? bias : bias + EG;
+        __half *yout = nullptr;
+        if (LAYER == 1) yout = Y1h_out + ((size_t)(live ? seq : 0) * T + t) * (4 * EH) + dir * EH;
+        constexpr int HK0 = LAYER == 1 ? 0 : 2 * EH / 8;  // first k-group of the state inside A
+#pragma unroll
+        for (int c = 0; c < EH / 16; ++c) {
+            float az[16], ar[16], ah[16], xh[16];
+            tmem_ld16(trow + 16 * c, az);
+            tmem_ld16(trow + EH + 16 * c, ar);
+            if (LAYER == 1) {
+                tmem_ld16(trow + 2 * EH + 16 * c, ah);
+            } else {
+                tmem_ld16(trow + 2 * EH + 16 * c, xh);
+                tmem_ld16(trow + 3 * EH + 16 * c, ah);
+            }
+            tmem_ld_wait();
+            if (LAYER == 1) {
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    const float4 vz = __ldg(reinterpret_cast<const float4 *>(xp + 16 * c) + q);
+                    const float4 vr = __ldg(reinterpret_cast<const float4 *>(xp + EH + 16 * c) + q);
+                    const float4 vh = __ldg(reinterpret_cast<const float4 *>(xp + 2 * EH + 16 * c) + q);
+                    az[4 * q] += vz.x; az[4 * q + 1] += vz.y; az[4 * q + 2] += vz.z; az[4 * q + 3] += vz.w;
+                    ar[4 * q] += vr.x; ar[4 * q + 1] += vr.y; ar[4 * q + 2] += vr.z; ar[4 * q + 3] += vr.w;
+                    xh[4 * q] = vh.x; xh[4 * q + 1] = vh.y; xh[4 * q + 2] = vh.z; xh[4 * q + 3] = vh.w;
+                }
+            } else {
+#pragma unroll
+                for (int j = 0; j < 16; ++j) {
+                    az[j] += bias[16 * c + j];
+                    ar[j] += bias[EH + 16 * c + j];
+                    xh[j] += bias[2 * EH + 16 * c + j];
+                }
+            }
+            unsigned hi[8], lo[8];
+#pragma unroll
+            for (int j = 0; j < 16; ++j) {
+                const int i = 16 * c + j;
+                const float z = tc_sigmoid(az[j]);
+                const float r = tc_sigmoid(ar[j]);
+                const float g = tc_tanh(xh[j] + r * (ah[j] + bRh[i]));
+                h[i] = (1.0f - z) * g + z * h[i];
+            }
+#pragma unroll
+            for (int j = 0; j < 8; ++j) split2(h[16 * c + 2 * j], h[16 * c + 2 * j + 1], hi[j], lo[j]);
+            Ah[(HK0 + 2 * c) * TC_M + tid] = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+            Ah[(HK0 + 2 * c + 1) * TC_M + tid] = make_uint4(hi[4], hi[5], hi[6], hi[7]);
+            Al[(HK0 + 2 * c) * TC_M + tid] = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+            Al[(HK0 + 2 * c + 1) * TC_M + tid] = make_uint4(lo[4], lo[5], lo[6], lo[7]);
+            if (LAYER == 1 && live) {
+                uint4 *yo = reinterpret_cast<uint4 *>(yout + 16 * c);
+                yo[0] = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+                yo[1] = make_uint4(hi[4], hi[5], hi[6], hi[7]);
+                uint4 *yl = reinterpret_cast<uint4 *>(yout + 2 * EH + 16 * c);
+                yl[0] = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+                yl[1] = make_uint4(lo[4], lo[5], lo[6], lo[7]);
+            }
+        }
+    }
+    if (LAYER == 2 && live) {
+        float4 *o = reinterpret_cast<float4 *>(out + (size_t)seq * (2 * EH) + dir * EH);
+#pragma unroll
+        for (int q = 0; q < EH / 4; ++q) o[q] = make_float4(h[4 * q], h[4 * q + 1], h[4 * q + 2], h[4 * q + 3]);
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(TC_COLS) : "memory");
+}
+
+// fp16 image of a weight matrix in the operand layout above: rows x K (row-major fp32, fp16-exact) -> [K/8][rows][8 halves];
+// `k0` places it at k-group k0 / 8 of a wider operand
+bool tc_pack(const float *Wm, int rows, int K, int k0, int rows_total, std::vector<uint16_t> &img)
+{
+    bool exact = true;
+    for (int r = 0; r < rows; ++r)
+        for (int k = 0; k < K; ++k) {
+            const float v = Wm[(size_t)r * K + k];
+            const __half hv = __float2half_rn(v);
+            if (__half2float(hv) != v) exact = false;
+            img[((size_t)((k0 + k) / 8) * rows_total + r) * 8 + (k0 + k) % 8] = __half_as_ushort(hv);
+        }
+    return exact;
+}
+#endif  // DRM_EMU
 }  // namespace
 
 // The tokeniser on the host (same code as the kernel's prologue): n x T vocabulary ids, 0-padded.
@@ -348,18 +631,83 @@ int embedder_upload(const EmbedWeightsHost &w, int device, int max_len, DeviceEm
     if ((rc = upload(b2, &e.b2)) != DRM_OK) return rc;
     if ((rc = upload(w.R2, &e.R2)) != DRM_OK) return rc;
     if ((rc = upload(bR2, &e.bR2)) != DRM_OK) return rc;
+#ifndef DRM_EMU
+    {   // operand images for the tensor-core form
+        std::vector<uint16_t> b1((size_t)2 * (TC_K1 / 8) * EG * 8, 0), b2i((size_t)2 * (TC_K2 / 8) * EG * 8, 0);
+        std::vector<float> bias2((size_t)2 * (EG + EH));
+        bool exact = true;
+        for (int dir = 0; dir < 2; ++dir) {
+            std::vector<uint16_t> img1((size_t)(TC_K1 / 8) * EG * 8, 0), img2((size_t)(TC_K2 / 8) * EG * 8, 0);
+            exact &= tc_pack(w.R1.data() + (size_t)dir * EG * EH, EG, EH, 0, EG, img1);
+            exact &= tc_pack(w.W2.data() + (size_t)dir * EG * 2 * EH, EG, 2 * EH, 0, EG, img2);
+            exact &= tc_pack(w.R2.data() + (size_t)dir * EG * EH, EG, EH, 2 * EH, EG, img2);
+            std::memcpy(b1.data() + (size_t)dir * img1.size(), img1.data(), img1.size() * 2);
+            std::memcpy(b2i.data() + (size_t)dir * img2.size(), img2.data(), img2.size() * 2);
+            for (int row = 0; row < EG; ++row) bias2[(size_t)dir * (EG + EH) + row] = b2[dir * EG + row];
+            for (int i = 0; i < EH; ++i) bias2[(size_t)dir * (EG + EH) + EG + i] = bR2[dir * EH + i];
+        }
+        e.tc_exact = exact;
+        if ((rc = upload(b1, &e.Bw1)) != DRM_OK) return rc;
+        if ((rc = upload(b2i, &e.Bw2)) != DRM_OK) return rc;
+        if ((rc = upload(bias2, &e.bias2)) != DRM_OK) return rc;
+    }
+#endif
     return DRM_OK;
 }
 
 void embedder_free(DeviceEmbedder &e)
 {
     if (e.device >= 0) cudaSetDevice(e.device);
-    for (float **p : {&e.P1, &e.R1, &e.bR1, &e.W2, &e.b2, &e.R2, &e.bR2, &e.Y1, &e.X2, &e.out}) {
+    for (float **p : {&e.P1, &e.R1, &e.bR1, &e.W2, &e.b2, &e.R2, &e.bR2, &e.Y1, &e.X2, &e.out, &e.bias2}) {
+        if (*p) cudaFree(*p);
+        *p = nullptr;
+    }
+    for (uint16_t **p : {&e.Bw1, &e.Bw2, &e.Y1h}) {
         if (*p) cudaFree(*p);
         *p = nullptr;
     }
     e.chunk = 0;
+    e.chunk_tc = 0;
 }
+
+#ifndef DRM_EMU
+// The tensor-core form: layer 1 (two CTAs per SM: 128 sequences x one direction each), then layer 2 with its input projection
+// fused into the step's product (one CTA per SM).  Passes of sms x 128 x 2 sequences; scratch = the layer-1 states as fp16
+// hi | lo pairs (63 KB per sequence, 2.4 GB per pass).
+static int launch_embed_tc(DeviceEmbedder &e, const EmbedSource &src, int64_t first, int64_t n, float *out_dev, cudaStream_t stream, int sms)
+{
+    const int T = e.max_len;
+    const int64_t full_pass = (int64_t)sms * TC_M * 2;
+    const int64_t want = n < full_pass ? ((n + TC_M - 1) / TC_M) * TC_M : full_pass;
+    if (want > e.chunk_tc) {
+        DRM_CUDA_TRY(cudaStreamSynchronize(stream));
+        if (e.Y1h) cudaFree(e.Y1h);
+        e.Y1h = nullptr; e.chunk_tc = 0;
+        DRM_CUDA_TRY(cudaMalloc(reinterpret_cast<void **>(&e.Y1h), (size_t)want * T * 4 * EH * sizeof(uint16_t)));
+        e.chunk_tc = want;
+    }
+    SrcDev s;
+    s.mode = src.mode; s.flat = src.flat; s.off = reinterpret_cast<const long long *>(src.off);
+    s.cls = src.cls; s.form = src.form; s.ref_n = src.ref_n; s.ref_len = src.ref_len;
+    s.first_id = src.first_id; s.id_step = src.id_step;
+    s.ids = src.ids; s.decorate = src.decorate;
+    // layer 1 asks for more shared memory than it uses so that exactly two CTAs (2 x 256 TMEM columns) share an SM
+    constexpr int SM1 = TcLayout<1>::BYTES > 80 * 1024 ? TcLayout<1>::BYTES : 80 * 1024, SM2 = TcLayout<2>::BYTES;
+    DRM_CUDA_TRY(cudaFuncSetAttribute(gru_tc_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, SM1));
+    DRM_CUDA_TRY(cudaFuncSetAttribute(gru_tc_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, SM2));
+    for (int64_t done = 0; done < n; done += e.chunk_tc) {
+        const int64_t m = (n - done) < e.chunk_tc ? (n - done) : e.chunk_tc;
+        const unsigned blocks = (unsigned)((m + TC_M - 1) / TC_M) * 2;
+        gru_tc_kernel<1><<<blocks, TC_M, SM1, stream>>>(s, first + done, m, T, e.P1, reinterpret_cast<const uint4 *>(e.Bw1), e.bR1, nullptr,
+                                                         reinterpret_cast<__half *>(e.Y1h), nullptr);
+        DRM_CUDA_TRY(cudaGetLastError());
+        gru_tc_kernel<2><<<blocks, TC_M, SM2, stream>>>(s, first + done, m, T, nullptr, reinterpret_cast<const uint4 *>(e.Bw2), e.bias2,
+                                                         reinterpret_cast<const __half *>(e.Y1h), nullptr, out_dev + (size_t)done * 2 * EH);
+        DRM_CUDA_TRY(cudaGetLastError());
+    }
+    return DRM_OK;
+}
+#endif
 
 int launch_embed(DeviceEmbedder &e, const EmbedSource &src, int64_t first, int64_t n, float *out_dev, cudaStream_t stream)
 {
@@ -368,6 +716,15 @@ int launch_embed(DeviceEmbedder &e, const EmbedSource &src, int64_t first, int64
     const int T = e.max_len;
     int sms = 148;
     DRM_CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, e.device));
+#ifndef DRM_EMU
+    {
+        // default ON since it was measured (profiles/r2_embed_bench_tc.json: 5.1 M sequences/s against 1.05 M, outputs within 4e-6 of
+        // the fp32 kernels); DRM_EMBED_TC=0 selects the fp32 kernels, which also serve weights that are not fp16 numbers
+        const char *tc = getenv("DRM_EMBED_TC");
+        const bool use_tc = e.tc_exact && !(tc && tc[0] == '0');
+        if (use_tc) return launch_embed_tc(e, src, first, n, out_dev, stream, sms);
+    }
+#endif
     const int64_t full_pass = (int64_t)sms * ES * 4;  // 4 CTA waves
     const int64_t want = n < full_pass ? ((n + ES - 1) / ES) * ES : full_pass;
     if (want > e.chunk) {  // scratch grows to the largest pass seen (<= 2.4 GB)

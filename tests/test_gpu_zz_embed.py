@@ -19,6 +19,14 @@ def gold():
     return U.load_golden()
 
 
+@pytest.fixture(autouse=True, params=["fp32", "tc"])
+def embed_form(request, monkeypatch):
+    """Every test runs on both forms of the recurrences: the fp32 CUDA-core kernels and the tensor-core form (tcgen05 + TMEM,
+    fp16 hi + lo activations on fp16-exact weights).  Same tolerance for both."""
+    monkeypatch.setenv("DRM_EMBED_TC", "1" if request.param == "tc" else "0")
+    return request.param
+
+
 def _random_seqs(g, n, lo, hi, alphabet=b"ACGT", decorate=0.5):
     out = []
     for _ in range(n):
@@ -56,10 +64,10 @@ def test_ragged_and_undefined_sequences_against_oracle():
     v.close()
 
 
-def test_more_sequences_than_one_pass():
+def test_more_sequences_than_one_pass(embed_form):
     import torch
     sms = torch.cuda.get_device_properties(0).multi_processor_count
-    n = sms * 16 * 4 + 37  # one full pass of the scratch + a short second one
+    n = (sms * 128 * 2 if embed_form == "tc" else sms * 16 * 4) + 37  # one full pass of the scratch + a short second one
     w = EO.random_weights(21)
     g = np.random.default_rng(22)
     seqs = _random_seqs(g, n, 100, 152, decorate=1.0)
@@ -192,6 +200,7 @@ def test_prefetch_variant_is_bit_identical(monkeypatch):
     g = np.random.default_rng(62)
     seqs = _random_seqs(g, 70, 2, 200)
     v = drm.Vectorizer(weights=w)
+    monkeypatch.setenv("DRM_EMBED_TC", "0")  # both runs on the fp32 kernels, whatever form the fixture selected
     monkeypatch.setenv("DRM_EMBED_PREFETCH", "0")
     a = v.vectorize(seqs)
     monkeypatch.setenv("DRM_EMBED_PREFETCH", "1")
@@ -199,3 +208,23 @@ def test_prefetch_variant_is_bit_identical(monkeypatch):
     assert np.array_equal(a.view(np.uint32), b.view(np.uint32))
     assert float(np.abs(b - EO.embed(seqs, w)).max()) < TOL
     v.close()
+
+
+def test_tensor_core_form_against_fp32_kernels(monkeypatch, gold):
+    """The tensor-core form against the fp32 kernels on the reference's own weights and on random weights: same inputs, both
+    within TOL of the oracle, and the two forms within 5e-5 of each other (hi + lo activations carry 22 bits)."""
+    g = np.random.default_rng(72)
+    for w, seqs in ((gold["weights"], list(gold["seqs"]) + _random_seqs(g, 150, 100, 152, decorate=1.0)),
+                    (EO.random_weights(71), _random_seqs(g, 300, 2, 200))):
+        v = drm.Vectorizer(weights=w)
+        monkeypatch.setenv("DRM_EMBED_TC", "0")
+        a = v.vectorize(seqs)
+        monkeypatch.setenv("DRM_EMBED_TC", "1")
+        b = v.vectorize(seqs)
+        b2 = v.vectorize(seqs)
+        v.close()
+        want = EO.embed(seqs, w)
+        d_ab, d_bo = float(np.abs(a - b).max()), float(np.abs(b - want).max())
+        print(f"tensor-core vs fp32 kernels: max abs diff {d_ab:.3g}; vs oracle {d_bo:.3g}")
+        assert np.array_equal(b.view(np.uint32), b2.view(np.uint32))  # deterministic
+        assert d_bo < TOL and d_ab < 5e-5

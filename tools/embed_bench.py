@@ -55,18 +55,33 @@ def main():
             ms.append(e0.elapsed_time(e1))
         return float(np.median(ms))
 
+    # the fp32 (CUDA-core) kernels: without and with the early load of a step's input projections
+    os.environ["DRM_EMBED_TC"] = "0"
+    os.environ["DRM_EMBED_PREFETCH"] = "0"
     ms_reads = timed(lambda: v.vectorize_device(flat.data_ptr(), off.data_ptr(), 0, n, out.data_ptr()))
     chk = float(out.abs().mean().item())
-    os.environ["DRM_EMBED_PREFETCH"] = "1"  # A/B: the opt-in variant that loads a step's input projections early
+    os.environ["DRM_EMBED_PREFETCH"] = "1"
     ms_reads_pf = timed(lambda: v.vectorize_device(flat.data_ptr(), off.data_ptr(), 0, n, out.data_ptr()))
     chk_pf = float(out.abs().mean().item())
-    os.environ["DRM_EMBED_PREFETCH"] = "0"
+    ref_out = out.clone()
     ms_win = timed(lambda: v.vectorize_windows_device(ref, 0, 1, n, out.data_ptr()))
+    # the tensor-core form (tcgen05 + TMEM; gru_tc_kernel)
+    os.environ["DRM_EMBED_TC"] = "1"
+    ms_reads_tc = timed(lambda: v.vectorize_device(flat.data_ptr(), off.data_ptr(), 0, n, out.data_ptr()))
+    chk_tc = float(out.abs().mean().item())
+    tc_max_diff = float((out - ref_out).abs().max().item())
+    ms_win_tc = timed(lambda: v.vectorize_windows_device(ref, 0, 1, n, out.data_ptr()))
+    os.environ.pop("DRM_EMBED_TC")
+    os.environ.pop("DRM_EMBED_PREFETCH")
     fma = 12.1e6
     res = {"sequences": n, "reads_ms": ms_reads, "reads_per_s": n / ms_reads * 1e3, "windows_ms": ms_win,
            "windows_per_s": n / ms_win * 1e3, "fp32_tflops_reads": 2 * fma * n / ms_reads * 1e3 / 1e12,
            "mean_abs_output": chk, "prefetch_reads_ms": ms_reads_pf, "prefetch_reads_per_s": n / ms_reads_pf * 1e3,
-           "prefetch_mean_abs_output": chk_pf, "gpu": torch.cuda.get_device_name(0)}
+           "prefetch_mean_abs_output": chk_pf,
+           "tc_reads_ms": ms_reads_tc, "tc_reads_per_s": n / ms_reads_tc * 1e3, "tc_windows_ms": ms_win_tc,
+           "tc_windows_per_s": n / ms_win_tc * 1e3, "tc_mean_abs_output": chk_tc, "tc_max_abs_diff_vs_fp32": tc_max_diff,
+           "tc_equivalent_tflops_reads": 2 * fma * n / ms_reads_tc * 1e3 / 1e12,
+           "gpu": torch.cuda.get_device_name(0)}
     print(json.dumps(res))
     os.makedirs(os.path.dirname(a.out) or ".", exist_ok=True)
     with open(a.out, "w") as f:
