@@ -15,7 +15,9 @@
 // Scratch (Y1: 63 KB, X2: 189 KB per sequence) is sized for a pass of 148 x 16 x 4 sequences (4 CTA waves).
 #include "common.h"
 
+#ifndef DRM_EMU
 #include <cuda_fp16.h>
+#endif
 
 #include <cstdlib>
 #include <cstring>
@@ -326,7 +328,8 @@ template <class T> int upload(const std::vector<T> &h, T **d)
 //     as fp32 states).
 constexpr int TC_M = 128;                 // sequences per CTA
 constexpr int TC_K1 = EH, TC_K2 = 2 * EH + EH;
-constexpr int TC_COLS = 256;              // TMEM columns per CTA (power of two >= 192 / 256)
+constexpr int TC_COLS1 = 256;             // TMEM columns per CTA, layer 1 (192 used; two CTAs per SM)
+constexpr int TC_COLS2 = 512;             // layer 2: two accumulator sets of 256 (one CTA per SM)
 
 __device__ __forceinline__ unsigned smem_u32(const void *p) { return (unsigned)__cvta_generic_to_shared(p); }
 
@@ -357,16 +360,31 @@ __device__ __forceinline__ void tmem_ld16(unsigned taddr, float (&v)[16])
 }
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 
-__device__ __forceinline__ float tc_sigmoid(float x) { return __fdividef(1.0f, 1.0f + __expf(-x)); }
-__device__ __forceinline__ float tc_tanh(float x) { return 2.0f * __fdividef(1.0f, 1.0f + __expf(-2.0f * x)) - 1.0f; }
+// The gate nonlinearities on the SFU, flush-to-zero forms (the plain __expf / division lower to range checks and rescaling
+// around MUFU that the clamped arguments here never need): 2^x and 1/x to 1-2 ulp.
+__device__ __forceinline__ float ex2_ftz(float x) { float y; asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
+__device__ __forceinline__ float rcp_ftz(float x) { float y; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
+constexpr float TC_L2E = 1.4426950408889634f;
+// z = s(x), r = s(y) with ONE reciprocal: with A = 1 + e^-x, B = 1 + e^-y:  s(x) = B / (A B), s(y) = A / (A B).  The exponent is capped
+// at 2^40 so that the product stays finite (moves a result by less than 1e-12); a large positive argument gives e^-x = 0, s = 1.
+__device__ __forceinline__ void gate_zr(float x, float y, float &sx, float &sy)
+{
+    const float A = 1.0f + ex2_ftz(fminf(x * -TC_L2E, 40.0f)), B = 1.0f + ex2_ftz(fminf(y * -TC_L2E, 40.0f));
+    const float t = rcp_ftz(A * B);
+    sx = t * B;
+    sy = t * A;
+}
+// tanh(u) = 2 / (1 + e^-2u) - 1
+__device__ __forceinline__ float tc_tanh(float u) { return fmaf(2.0f, rcp_ftz(1.0f + ex2_ftz(fminf(u * (-2.0f * TC_L2E), 40.0f))), -1.0f); }
 
 // h -> (hi, lo) fp16 pair, packed two values per word
 __device__ __forceinline__ void split2(float a, float b, unsigned &hi, unsigned &lo)
 {
-    const __half ah = __float2half_rn(a), bh = __float2half_rn(b);
-    const __half al = __float2half_rn(a - __half2float(ah)), bl = __float2half_rn(b - __half2float(bh));
-    hi = (unsigned)__half_as_ushort(ah) | ((unsigned)__half_as_ushort(bh) << 16);
-    lo = (unsigned)__half_as_ushort(al) | ((unsigned)__half_as_ushort(bl) << 16);
+    const __half2 h2 = __floats2half2_rn(a, b);
+    const float2 f = __half22float2(h2);
+    const __half2 l2 = __floats2half2_rn(a - f.x, b - f.y);
+    hi = *reinterpret_cast<const unsigned *>(&h2);
+    lo = *reinterpret_cast<const unsigned *>(&l2);
 }
 
 // Dynamic shared memory: Bw [K/8][192][16 B] | Ah [K/8][128][16 B] | Al [K/8][128][16 B] | bias floats | tokens (layer 1) | mbarrier, TMEM address
@@ -382,13 +400,18 @@ template <int LAYER> struct TcLayout {
     static constexpr int BYTES = OFF_BAR + 16;
 };
 
-template <int LAYER>
-__global__ void __launch_bounds__(TC_M, 1)
+// TPS = threads per sequence: 1 (128 threads) or 2 (256 threads: warps w and w + 4 read the same 32 TMEM lanes - the hardware
+// ties a warp to lanes 32 (w % 4) .. + 31 - and each owns 32 of the 64 hidden units, so the gate phase has twice the warps to hide
+// the SFU and TMEM latencies behind).
+template <int LAYER, int TPS>
+__global__ void __launch_bounds__(TC_M * TPS, LAYER == 1 ? 2 : 1)
 gru_tc_kernel(const SrcDev src, const long long first, const long long n, const int T, const float *__restrict__ P1,
               const uint4 *__restrict__ Bw_g, const float *__restrict__ bias_g, const __half *__restrict__ Y1h_in,
               __half *__restrict__ Y1h_out, float *__restrict__ out)
 {
     using L = TcLayout<LAYER>;
+    constexpr int NT = TC_M * TPS;
+    constexpr int UNITS = EH / TPS;  // hidden units per thread
     extern __shared__ __align__(1024) unsigned char tsm[];
     uint4 *Bw = reinterpret_cast<uint4 *>(tsm);
     uint4 *Ah = reinterpret_cast<uint4 *>(tsm + L::OFF_AH);
@@ -399,22 +422,23 @@ gru_tc_kernel(const SrcDev src, const long long first, const long long n, const 
     unsigned *tmem_slot = reinterpret_cast<unsigned *>(tsm + L::OFF_BAR + 8);
 
     const int tid = threadIdx.x, warp = tid >> 5;
+    const int row = tid & (TC_M - 1), part = tid / TC_M;  // sequence of the tile, which share of its hidden units
     const int dir = blockIdx.x & 1;
-    const long long seq = (long long)(blockIdx.x >> 1) * TC_M + tid;  // inside the pass
+    const long long seq = (long long)(blockIdx.x >> 1) * TC_M + row;  // inside the pass
     const bool live = seq < n;
 
     // ---- one-time set-up: weights of this direction, biases, zero state, tokens, mbarrier, TMEM columns
     {
         const uint4 *g = Bw_g + (size_t)dir * (L::B_BYTES / 16);
-        for (int p = tid; p < L::B_BYTES / 16; p += TC_M) Bw[p] = __ldg(g + p);
-        for (int p = tid; p < L::BIAS_FLOATS; p += TC_M) bias[p] = bias_g[dir * L::BIAS_FLOATS + p];
+        for (int p = tid; p < L::B_BYTES / 16; p += NT) Bw[p] = __ldg(g + p);
+        for (int p = tid; p < L::BIAS_FLOATS; p += NT) bias[p] = bias_g[dir * L::BIAS_FLOATS + p];
         const uint4 z4 = make_uint4(0u, 0u, 0u, 0u);
-        for (int p = tid; p < 2 * L::A_BYTES / 16; p += TC_M) Ah[p] = z4;  // Ah and Al are adjacent
+        for (int p = tid; p < 2 * L::A_BYTES / 16; p += NT) Ah[p] = z4;  // Ah and Al are adjacent
     }
     if (LAYER == 1) {
         SeqView v = seq_view(src, first + (live ? seq : 0));
         if (!live) v.n = 0;
-        for (int t = 0; t < T; ++t) tok[t * TC_M + tid] = (unsigned char)token_slot(v, t, T);
+        for (int t = part; t < T; t += TPS) tok[t * TC_M + row] = (unsigned char)token_slot(v, t, T);
     }
     const unsigned bar_s = smem_u32(bar);
     if (tid == 0) {
@@ -422,34 +446,83 @@ gru_tc_kernel(const SrcDev src, const long long first, const long long n, const 
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 0) {
-        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(TC_COLS) : "memory");
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(LAYER == 1 ? TC_COLS1 : TC_COLS2) : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
     }
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     const unsigned tmem = *tmem_slot;
-    const unsigned trow = tmem + ((unsigned)(warp * 32) << 16);  // this warp's 32 lanes
+    const unsigned trow = tmem + ((unsigned)((warp & 3) * 32) << 16);  // this warp's 32 lanes
 
     const unsigned ah_s = smem_u32(Ah), al_s = smem_u32(Al), bw_s = smem_u32(Bw);
     constexpr unsigned A_LBO = TC_M * 16, B_LBO = EG * 16, SBO = 128;
 
-    float h[EH];
+    float h[UNITS];
 #pragma unroll
-    for (int i = 0; i < EH; ++i) h[i] = 0.0f;
+    for (int i = 0; i < UNITS; ++i) h[i] = 0.0f;
+
+    // Layer 2 runs as a two-stage pipeline over two accumulator sets: the INPUT half of step t + 1 (y1_{t+1} . W2: 32 of the 48
+    // products, and the only part that reads global memory) is issued while the gates of step t are applied; only the recurrent half
+    // (h_t . R2, 16 products) sits between the gates of two consecutive steps.
+    auto y_src = [&](int tt) { return reinterpret_cast<const uint4 *>(Y1h_in + ((size_t)(live ? seq : 0) * T + tt) * (4 * EH)) + (TPS == 2 ? part * (2 * EH / 8) : 0); };
+    constexpr int YV = (TPS == 2 ? 1 : 2) * (2 * EH / 8);  // 16-byte words of y1 this thread moves per step
+    auto y_store = [&](const uint4 (&v)[YV]) {
+        if (TPS == 2) {
+            uint4 *dst = part ? Al : Ah;
+#pragma unroll
+            for (int g = 0; g < 2 * EH / 8; ++g) dst[g * TC_M + row] = v[g];
+        } else {
+#pragma unroll
+            for (int g = 0; g < 2 * EH / 8; ++g) { Ah[g * TC_M + row] = v[g]; Al[g * TC_M + row] = v[2 * EH / 8 + g]; }
+        }
+    };
+    auto issue_y = [&](unsigned dcol) {  // input half of a step into accumulator set dcol: z, r columns start here
+        constexpr unsigned idesc_zr = umma_idesc(TC_M, 2 * EH), idesc_h = umma_idesc(TC_M, EH);
+#pragma unroll
+        for (int half = 0; half < 2; ++half)
+#pragma unroll
+            for (int ks = 0; ks < 2 * EH / 16; ++ks) {
+                const unsigned long long ad = umma_desc((half ? al_s : ah_s) + ks * 2 * A_LBO, A_LBO, SBO);
+                umma_f16(tmem + dcol, ad, umma_desc(bw_s + ks * 2 * B_LBO, B_LBO, SBO), idesc_zr, (half | ks) ? 1u : 0u);
+                umma_f16(tmem + dcol + 2 * EH, ad, umma_desc(bw_s + ks * 2 * B_LBO + 2 * EH * 16, B_LBO, SBO), idesc_h, (half | ks) ? 1u : 0u);
+            }
+    };
+    auto issue_h = [&](unsigned dcol) {  // recurrent half: accumulates onto z, r; starts the h-recurrent columns
+        constexpr unsigned idesc_zr = umma_idesc(TC_M, 2 * EH), idesc_h = umma_idesc(TC_M, EH);
+#pragma unroll
+        for (int half = 0; half < 2; ++half)
+#pragma unroll
+            for (int ks = 2 * EH / 16; ks < TC_K2 / 16; ++ks) {
+                const unsigned long long ad = umma_desc((half ? al_s : ah_s) + ks * 2 * A_LBO, A_LBO, SBO);
+                umma_f16(tmem + dcol, ad, umma_desc(bw_s + ks * 2 * B_LBO, B_LBO, SBO), idesc_zr, 1u);
+                umma_f16(tmem + dcol + 3 * EH, ad, umma_desc(bw_s + ks * 2 * B_LBO + 2 * EH * 16, B_LBO, SBO), idesc_h, (half | (ks - 2 * EH / 16)) ? 1u : 0u);
+            }
+    };
+    if (LAYER == 2) {
+        uint4 v[YV];
+        const uint4 *y = y_src(dir ? T - 1 : 0);
+#pragma unroll
+        for (int g = 0; g < YV; ++g) v[g] = __ldg(y + g);
+        y_store(v);
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        __syncthreads();
+        if (tid == 0) {
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            issue_y(0u);
+        }
+    }
 
     unsigned phase = 0;
     for (int step = 0; step < T; ++step) {
         const int t = dir ? T - 1 - step : step;
-        if (LAYER == 2) {  // this step's input: the layer-1 states of both directions at time t, already split hi | lo
-            const uint4 *y = reinterpret_cast<const uint4 *>(Y1h_in + ((size_t)(live ? seq : 0) * T + t) * (4 * EH));
+        const unsigned dcol = LAYER == 2 ? (unsigned)(step & 1) * 256u : 0u;
+        if (LAYER == 1 && step + 1 < T) {  // the next step's row of the token table into L1 (768 bytes = 6 lines)
+            const unsigned char *pn = reinterpret_cast<const unsigned char *>(P1 + (size_t)(dir * NSLOT + tok[(dir ? t - 1 : t + 1) * TC_M + row]) * EG);
 #pragma unroll
-            for (int g = 0; g < 2 * EH / 8; ++g) {
-                Ah[g * TC_M + tid] = __ldg(y + g);
-                Al[g * TC_M + tid] = __ldg(y + 2 * EH / 8 + g);
-            }
+            for (int q = 0; q < 6 / TPS; ++q) asm volatile("prefetch.global.L1 [%0];" ::"l"(pn + 128 * (q * TPS + part)));
         }
-        // generic-proxy writes of A (this step's input, last step's state) -> visible to the tensor core's async proxy
+        // generic-proxy writes of A (last step's state) -> visible to the tensor core's async proxy
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
         asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");  // the reads of D below precede the next product
         __syncthreads();
@@ -464,25 +537,18 @@ gru_tc_kernel(const SrcDev src, const long long first, const long long n, const 
                         umma_f16(tmem, umma_desc((half ? al_s : ah_s) + ks * 2 * A_LBO, A_LBO, SBO), umma_desc(bw_s + ks * 2 * B_LBO, B_LBO, SBO), idesc,
                                  (half | ks) ? 1u : 0u);
             } else {
-                constexpr unsigned idesc_zr = umma_idesc(TC_M, 2 * EH), idesc_h = umma_idesc(TC_M, EH);
-#pragma unroll
-                for (int half = 0; half < 2; ++half) {
-                    const unsigned a_s = half ? al_s : ah_s;
-#pragma unroll
-                    for (int ks = 0; ks < TC_K2 / 16; ++ks) {
-                        const unsigned long long ad = umma_desc(a_s + ks * 2 * A_LBO, A_LBO, SBO);
-                        // rows z, r (0..127) over the whole K -> columns 0..127
-                        umma_f16(tmem, ad, umma_desc(bw_s + ks * 2 * B_LBO, B_LBO, SBO), idesc_zr, (half | ks) ? 1u : 0u);
-                        // rows h (128..191): the input half (K < 128) -> columns 128..191, the recurrent half -> columns 192..255
-                        const unsigned long long bd = umma_desc(bw_s + ks * 2 * B_LBO + 2 * EH * 16, B_LBO, SBO);
-                        if (ks < 2 * EH / 16) umma_f16(tmem + 2 * EH, ad, bd, idesc_h, (half | ks) ? 1u : 0u);
-                        else umma_f16(tmem + 3 * EH, ad, bd, idesc_h, (half | (ks - 2 * EH / 16)) ? 1u : 0u);
-                    }
-                }
+                issue_h(dcol);
             }
             asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar_s) : "memory");
         }
-        {   // wait for the products of this step
+        uint4 ynext[YV];
+        const bool more = LAYER == 2 && step + 1 < T;
+        if (more) {  // the next step's input travels from L2 / DRAM while the recurrent products run
+            const uint4 *y = y_src(dir ? t - 1 : t + 1);
+#pragma unroll
+            for (int g = 0; g < YV; ++g) ynext[g] = __ldg(y + g);
+        }
+        {   // wait for the products of this step (the commit covers the input half issued one step earlier too)
             unsigned done = 0, spins = 0;
             do {
                 asm volatile("{\n\t.reg .pred P1;\n\tmbarrier.try_wait.parity.shared::cta.b64 P1, [%1], %2;\n\tselp.b32 %0, 1, 0, P1;\n\t}"
@@ -492,23 +558,41 @@ gru_tc_kernel(const SrcDev src, const long long first, const long long n, const 
             phase ^= 1u;
         }
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        if (LAYER == 2 && more) {  // every earlier product is complete: the input half of A is free for the next step
+            y_store(ynext);
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+            __syncthreads();
+            if (tid == 0) {
+                asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                issue_y(dcol ^ 256u);
+            }
+        }
+        const unsigned tacc = trow + dcol;
 
         // ---- gates, 16 units at a time: z = s(xz + az), r = s(xr + ar), g = tanh(xh + r (ah + bRh)), h' = (1 - z) g + z h
-        const float *xp = LAYER == 1 ? P1 + (size_t)(dir * NSLOT + tok[t * TC_M + tid]) * EG : nullptr;
+        const float *xp = LAYER == 1 ? P1 + (size_t)(dir * NSLOT + tok[t * TC_M + row]) * EG : nullptr;
         const float *bRh = LAYER == 1 ? bias : bias + EG;
         __half *yout = nullptr;
         if (LAYER == 1) yout = Y1h_out + ((size_t)(live ? seq : 0) * T + t) * (4 * EH) + dir * EH;
         constexpr int HK0 = LAYER == 1 ? 0 : 2 * EH / 8;  // first k-group of the state inside A
 #pragma unroll
-        for (int c = 0; c < EH / 16; ++c) {
+        for (int cc = 0; cc < UNITS / 16; ++cc) {
+            const int c = cc + part * (UNITS / 16);  // 16-unit chunk of the hidden state
             float az[16], ar[16], ah[16], xh[16];
-            tmem_ld16(trow + 16 * c, az);
-            tmem_ld16(trow + EH + 16 * c, ar);
+            tmem_ld16(tacc + 16 * c, az);
+            tmem_ld16(tacc + EH + 16 * c, ar);
             if (LAYER == 1) {
-                tmem_ld16(trow + 2 * EH + 16 * c, ah);
+                tmem_ld16(tacc + 2 * EH + 16 * c, ah);
             } else {
-                tmem_ld16(trow + 2 * EH + 16 * c, xh);
-                tmem_ld16(trow + 3 * EH + 16 * c, ah);
+                tmem_ld16(tacc + 2 * EH + 16 * c, xh);
+                tmem_ld16(tacc + 3 * EH + 16 * c, ah);
+            }
+            if (LAYER == 1) {  // the gathered input projection travels while the TMEM loads complete
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    const float4 vh = __ldg(reinterpret_cast<const float4 *>(xp + 2 * EH + 16 * c) + q);
+                    xh[4 * q] = vh.x; xh[4 * q + 1] = vh.y; xh[4 * q + 2] = vh.z; xh[4 * q + 3] = vh.w;
+                }
             }
             tmem_ld_wait();
             if (LAYER == 1) {
@@ -516,10 +600,8 @@ gru_tc_kernel(const SrcDev src, const long long first, const long long n, const 
                 for (int q = 0; q < 4; ++q) {
                     const float4 vz = __ldg(reinterpret_cast<const float4 *>(xp + 16 * c) + q);
                     const float4 vr = __ldg(reinterpret_cast<const float4 *>(xp + EH + 16 * c) + q);
-                    const float4 vh = __ldg(reinterpret_cast<const float4 *>(xp + 2 * EH + 16 * c) + q);
                     az[4 * q] += vz.x; az[4 * q + 1] += vz.y; az[4 * q + 2] += vz.z; az[4 * q + 3] += vz.w;
                     ar[4 * q] += vr.x; ar[4 * q + 1] += vr.y; ar[4 * q + 2] += vr.z; ar[4 * q + 3] += vr.w;
-                    xh[4 * q] = vh.x; xh[4 * q + 1] = vh.y; xh[4 * q + 2] = vh.z; xh[4 * q + 3] = vh.w;
                 }
             } else {
 #pragma unroll
@@ -532,18 +614,17 @@ gru_tc_kernel(const SrcDev src, const long long first, const long long n, const 
             unsigned hi[8], lo[8];
 #pragma unroll
             for (int j = 0; j < 16; ++j) {
-                const int i = 16 * c + j;
-                const float z = tc_sigmoid(az[j]);
-                const float r = tc_sigmoid(ar[j]);
-                const float g = tc_tanh(xh[j] + r * (ah[j] + bRh[i]));
-                h[i] = (1.0f - z) * g + z * h[i];
+                float z, r;
+                gate_zr(az[j], ar[j], z, r);
+                const float g = tc_tanh(xh[j] + r * (ah[j] + bRh[16 * c + j]));
+                h[16 * cc + j] = (1.0f - z) * g + z * h[16 * cc + j];
             }
 #pragma unroll
-            for (int j = 0; j < 8; ++j) split2(h[16 * c + 2 * j], h[16 * c + 2 * j + 1], hi[j], lo[j]);
-            Ah[(HK0 + 2 * c) * TC_M + tid] = make_uint4(hi[0], hi[1], hi[2], hi[3]);
-            Ah[(HK0 + 2 * c + 1) * TC_M + tid] = make_uint4(hi[4], hi[5], hi[6], hi[7]);
-            Al[(HK0 + 2 * c) * TC_M + tid] = make_uint4(lo[0], lo[1], lo[2], lo[3]);
-            Al[(HK0 + 2 * c + 1) * TC_M + tid] = make_uint4(lo[4], lo[5], lo[6], lo[7]);
+            for (int j = 0; j < 8; ++j) split2(h[16 * cc + 2 * j], h[16 * cc + 2 * j + 1], hi[j], lo[j]);
+            Ah[(HK0 + 2 * c) * TC_M + row] = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+            Ah[(HK0 + 2 * c + 1) * TC_M + row] = make_uint4(hi[4], hi[5], hi[6], hi[7]);
+            Al[(HK0 + 2 * c) * TC_M + row] = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+            Al[(HK0 + 2 * c + 1) * TC_M + row] = make_uint4(lo[4], lo[5], lo[6], lo[7]);
             if (LAYER == 1 && live) {
                 uint4 *yo = reinterpret_cast<uint4 *>(yout + 16 * c);
                 yo[0] = make_uint4(hi[0], hi[1], hi[2], hi[3]);
@@ -555,13 +636,13 @@ gru_tc_kernel(const SrcDev src, const long long first, const long long n, const 
         }
     }
     if (LAYER == 2 && live) {
-        float4 *o = reinterpret_cast<float4 *>(out + (size_t)seq * (2 * EH) + dir * EH);
+        float4 *o = reinterpret_cast<float4 *>(out + (size_t)seq * (2 * EH) + dir * EH + part * UNITS);
 #pragma unroll
-        for (int q = 0; q < EH / 4; ++q) o[q] = make_float4(h[4 * q], h[4 * q + 1], h[4 * q + 2], h[4 * q + 3]);
+        for (int q = 0; q < UNITS / 4; ++q) o[q] = make_float4(h[4 * q], h[4 * q + 1], h[4 * q + 2], h[4 * q + 3]);
     }
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
-    if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(TC_COLS) : "memory");
+    if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(LAYER == 1 ? TC_COLS1 : TC_COLS2) : "memory");
 }
 
 // fp16 image of a weight matrix in the operand layout above: rows x K (row-major fp32, fp16-exact) -> [K/8][rows][8 halves];
@@ -692,17 +773,26 @@ static int launch_embed_tc(DeviceEmbedder &e, const EmbedSource &src, int64_t fi
     s.first_id = src.first_id; s.id_step = src.id_step;
     s.ids = src.ids; s.decorate = src.decorate;
     // layer 1 asks for more shared memory than it uses so that exactly two CTAs (2 x 256 TMEM columns) share an SM
-    constexpr int SM1 = TcLayout<1>::BYTES > 80 * 1024 ? TcLayout<1>::BYTES : 80 * 1024, SM2 = TcLayout<2>::BYTES;
-    DRM_CUDA_TRY(cudaFuncSetAttribute(gru_tc_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, SM1));
-    DRM_CUDA_TRY(cudaFuncSetAttribute(gru_tc_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, SM2));
+    // (78 KB + 1 KB of driver shared memory, twice, stays inside the 164 KB carve-out step and leaves 92 KB of L1 for the token table)
+    constexpr int SM1 = TcLayout<1>::BYTES > 78 * 1024 ? TcLayout<1>::BYTES : 78 * 1024, SM2 = TcLayout<2>::BYTES;
+    // threads per sequence in the gate phase, per layer: DRM_EMBED_TC_TPS = "<layer 1><layer 2>" (A/B; default "22")
+    int tps1 = 2, tps2 = 2;
+    if (const char *ev = getenv("DRM_EMBED_TC_TPS")) {
+        if (ev[0] == '1') tps1 = 1;
+        if (ev[0] && ev[1] == '1') tps2 = 1;
+    }
+    auto k1 = tps1 == 2 ? gru_tc_kernel<1, 2> : gru_tc_kernel<1, 1>;
+    auto k2 = tps2 == 2 ? gru_tc_kernel<2, 2> : gru_tc_kernel<2, 1>;
+    DRM_CUDA_TRY(cudaFuncSetAttribute(k1, cudaFuncAttributeMaxDynamicSharedMemorySize, SM1));
+    DRM_CUDA_TRY(cudaFuncSetAttribute(k2, cudaFuncAttributeMaxDynamicSharedMemorySize, SM2));
     for (int64_t done = 0; done < n; done += e.chunk_tc) {
         const int64_t m = (n - done) < e.chunk_tc ? (n - done) : e.chunk_tc;
         const unsigned blocks = (unsigned)((m + TC_M - 1) / TC_M) * 2;
-        gru_tc_kernel<1><<<blocks, TC_M, SM1, stream>>>(s, first + done, m, T, e.P1, reinterpret_cast<const uint4 *>(e.Bw1), e.bR1, nullptr,
-                                                         reinterpret_cast<__half *>(e.Y1h), nullptr);
+        k1<<<blocks, TC_M * tps1, SM1, stream>>>(s, first + done, m, T, e.P1, reinterpret_cast<const uint4 *>(e.Bw1), e.bR1, nullptr,
+                                                  reinterpret_cast<__half *>(e.Y1h), nullptr);
         DRM_CUDA_TRY(cudaGetLastError());
-        gru_tc_kernel<2><<<blocks, TC_M, SM2, stream>>>(s, first + done, m, T, nullptr, reinterpret_cast<const uint4 *>(e.Bw2), e.bias2,
-                                                         reinterpret_cast<const __half *>(e.Y1h), nullptr, out_dev + (size_t)done * 2 * EH);
+        k2<<<blocks, TC_M * tps2, SM2, stream>>>(s, first + done, m, T, nullptr, reinterpret_cast<const uint4 *>(e.Bw2), e.bias2,
+                                                  reinterpret_cast<const __half *>(e.Y1h), nullptr, out_dev + (size_t)done * 2 * EH);
         DRM_CUDA_TRY(cudaGetLastError());
     }
     return DRM_OK;
