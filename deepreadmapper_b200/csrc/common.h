@@ -174,9 +174,11 @@ struct DeviceEmbedder {
     float *X2 = nullptr;   // [chunk][max_len][2][192] layer-2 input projections
     float *out = nullptr;  // [chunk][128] staging for host-pointer calls
     // tensor-core form (embed_kernel.cu, gru_tc_kernel): fp16 operand images of the recurrent weights
-    uint16_t *Bw1 = nullptr;    // [2][8][192][8]   R1 per direction, [k-group][row][8 halves]
+    uint16_t *Bw1 = nullptr;    // [2][16][192][8]  [W1 | R1] per direction, [k-group][row][8 halves]
     uint16_t *Bw2 = nullptr;    // [2][24][192][8]  [W2 | R2] per direction
-    float *bias2 = nullptr;     // [2][192 + 64]    b2 | bR2 per direction
+    uint16_t *emb16 = nullptr;  // [97][64]         the embedding rows the tokeniser can select
+    float *bias1 = nullptr;     // [2][192 + 64]    input biases | recurrent bias of the candidate gate, per direction
+    float *bias2 = nullptr;     // [2][192 + 64]
     uint16_t *Y1h = nullptr;    // [chunk_tc][max_len][hi 128 | lo 128] layer-1 states as fp16 pairs
     int64_t chunk_tc = 0;
     bool tc_exact = false;      // every recurrent weight is an fp16 number (true for the reference's IR): the tensor-core form is exact in B

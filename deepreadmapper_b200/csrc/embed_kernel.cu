@@ -327,7 +327,7 @@ template <class T> int upload(const std::vector<T> &h, T **d)
 //   * Layer 1 hands its states to layer 2 already split: Y1h[seq][t][hi 128 | lo 128] halves (512 B per step, the same bytes
 //     as fp32 states).
 constexpr int TC_M = 128;                 // sequences per CTA
-constexpr int TC_K1 = EH, TC_K2 = 2 * EH + EH;
+constexpr int TC_K1 = EH + EH, TC_K2 = 2 * EH + EH;  // [x_t | h]: layer 1 x = the token embedding (64), layer 2 x = y1_t (128)
 constexpr int TC_COLS1 = 256;             // TMEM columns per CTA, layer 1 (192 used; two CTAs per SM)
 constexpr int TC_COLS2 = 512;             // layer 2: two accumulator sets of 256 (one CTA per SM)
 
@@ -387,16 +387,24 @@ __device__ __forceinline__ void split2(float a, float b, unsigned &hi, unsigned 
     lo = *reinterpret_cast<const unsigned *>(&l2);
 }
 
-// Dynamic shared memory: Bw [K/8][192][16 B] | Ah [K/8][128][16 B] | Al [K/8][128][16 B] | bias floats | tokens (layer 1) | mbarrier, TMEM address
+// Both layers are the same step: gate pre-activations = [x_t | h] . [W | R]^T with K = KX + 64.
+//   layer 1: x_t = the token's embedding row (64 fp16 numbers, exact: the table is f16 in the IR), copied from a 97-row copy of
+//            the table in shared memory - the recurrence never touches global memory for its input;
+//   layer 2: x_t = y1_t (128 values, hi | lo).
+// Dynamic shared memory: Bw [K/8][192][16 B] | Ah [K/8][128][16 B] | Al [(layer 1: 8, the state only) K/8][128][16 B] | bias floats |
+// embedding rows (layer 1) | mbarrier, TMEM address
 template <int LAYER> struct TcLayout {
-    static constexpr int K = LAYER == 1 ? TC_K1 : TC_K2;
-    static constexpr int KG = K / 8;
+    static constexpr int KX = LAYER == 1 ? EH : 2 * EH;
+    static constexpr int K = KX + EH;
+    static constexpr int KG = K / 8, KGX = KX / 8;
+    static constexpr int AL_H0 = LAYER == 1 ? 0 : KGX;          // k-group of the state inside Al
     static constexpr int B_BYTES = KG * EG * 16;
-    static constexpr int A_BYTES = KG * TC_M * 16;
-    static constexpr int BIAS_FLOATS = LAYER == 1 ? EH : EG + EH;
-    static constexpr int OFF_AH = B_BYTES, OFF_AL = B_BYTES + A_BYTES, OFF_BIAS = B_BYTES + 2 * A_BYTES;
-    static constexpr int OFF_TOK = OFF_BIAS + BIAS_FLOATS * 4;
-    static constexpr int OFF_BAR = OFF_TOK + (LAYER == 1 ? ET_MAX * TC_M : 0);
+    static constexpr int AH_BYTES = KG * TC_M * 16;
+    static constexpr int AL_BYTES = (AL_H0 + EH / 8) * TC_M * 16;
+    static constexpr int BIAS_FLOATS = EG + EH;                  // input biases z, r, h | recurrent bias of h
+    static constexpr int OFF_AH = B_BYTES, OFF_AL = OFF_AH + AH_BYTES, OFF_BIAS = OFF_AL + AL_BYTES;
+    static constexpr int OFF_EMB = OFF_BIAS + BIAS_FLOATS * 4;
+    static constexpr int OFF_BAR = OFF_EMB + (LAYER == 1 ? NSLOT * EH * 2 : 0);
     static constexpr int BYTES = OFF_BAR + 16;
 };
 
@@ -405,19 +413,20 @@ template <int LAYER> struct TcLayout {
 // the SFU and TMEM latencies behind).
 template <int LAYER, int TPS>
 __global__ void __launch_bounds__(TC_M * TPS, LAYER == 1 ? 2 : 1)
-gru_tc_kernel(const SrcDev src, const long long first, const long long n, const int T, const float *__restrict__ P1,
+gru_tc_kernel(const SrcDev src, const long long first, const long long n, const int T, const uint4 *__restrict__ emb_g,
               const uint4 *__restrict__ Bw_g, const float *__restrict__ bias_g, const __half *__restrict__ Y1h_in,
               __half *__restrict__ Y1h_out, float *__restrict__ out)
 {
     using L = TcLayout<LAYER>;
     constexpr int NT = TC_M * TPS;
     constexpr int UNITS = EH / TPS;  // hidden units per thread
+    constexpr int KSX = L::KX / 16, KS = L::K / 16;  // products (K = 16 each) of the input half, of the whole step
     extern __shared__ __align__(1024) unsigned char tsm[];
     uint4 *Bw = reinterpret_cast<uint4 *>(tsm);
     uint4 *Ah = reinterpret_cast<uint4 *>(tsm + L::OFF_AH);
     uint4 *Al = reinterpret_cast<uint4 *>(tsm + L::OFF_AL);
-    float *bias = reinterpret_cast<float *>(tsm + L::OFF_BIAS);   // layer 1: bR[64]; layer 2: b2[192] | bR[64]
-    unsigned char *tok = tsm + L::OFF_TOK;                          // [t][s]
+    float *bias = reinterpret_cast<float *>(tsm + L::OFF_BIAS);
+    uint4 *embs = reinterpret_cast<uint4 *>(tsm + L::OFF_EMB);     // [slot][8 x 16 B]
     unsigned long long *bar = reinterpret_cast<unsigned long long *>(tsm + L::OFF_BAR);
     unsigned *tmem_slot = reinterpret_cast<unsigned *>(tsm + L::OFF_BAR + 8);
 
@@ -427,26 +436,26 @@ gru_tc_kernel(const SrcDev src, const long long first, const long long n, const 
     const long long seq = (long long)(blockIdx.x >> 1) * TC_M + row;  // inside the pass
     const bool live = seq < n;
 
-    // ---- one-time set-up: weights of this direction, biases, zero state, tokens, mbarrier, TMEM columns
+    // ---- one-time set-up: weights of this direction, biases, embedding rows, zero state, mbarrier, TMEM columns
     {
         const uint4 *g = Bw_g + (size_t)dir * (L::B_BYTES / 16);
         for (int p = tid; p < L::B_BYTES / 16; p += NT) Bw[p] = __ldg(g + p);
         for (int p = tid; p < L::BIAS_FLOATS; p += NT) bias[p] = bias_g[dir * L::BIAS_FLOATS + p];
+        if (LAYER == 1)
+            for (int p = tid; p < NSLOT * EH * 2 / 16; p += NT) embs[p] = __ldg(emb_g + p);
         const uint4 z4 = make_uint4(0u, 0u, 0u, 0u);
-        for (int p = tid; p < 2 * L::A_BYTES / 16; p += NT) Ah[p] = z4;  // Ah and Al are adjacent
+        for (int p = tid; p < (L::AH_BYTES + L::AL_BYTES) / 16; p += NT) Ah[p] = z4;  // Ah and Al are adjacent
     }
-    if (LAYER == 1) {
-        SeqView v = seq_view(src, first + (live ? seq : 0));
-        if (!live) v.n = 0;
-        for (int t = part; t < T; t += TPS) tok[t * TC_M + row] = (unsigned char)token_slot(v, t, T);
-    }
+    SeqView sv = seq_view(src, first + (live ? seq : 0));  // layer 1: tokens are recomputed per step (3 byte reads + a hash)
+    if (!live) sv.n = 0;
     const unsigned bar_s = smem_u32(bar);
     if (tid == 0) {
         asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar_s) : "memory");
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
+    constexpr int TCOLS = LAYER == 1 ? TC_COLS1 : TC_COLS2;
     if (warp == 0) {
-        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(LAYER == 1 ? TC_COLS1 : TC_COLS2) : "memory");
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(TCOLS) : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
     }
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
@@ -457,16 +466,34 @@ gru_tc_kernel(const SrcDev src, const long long first, const long long n, const 
 
     const unsigned ah_s = smem_u32(Ah), al_s = smem_u32(Al), bw_s = smem_u32(Bw);
     constexpr unsigned A_LBO = TC_M * 16, B_LBO = EG * 16, SBO = 128;
+    constexpr unsigned idesc_zr = umma_idesc(TC_M, 2 * EH), idesc_h = umma_idesc(TC_M, EH);
 
-    float h[UNITS];
+    // input half of a step into accumulator set dcol: starts the z, r columns (0..127) and the h-input columns (128..191)
+    auto issue_x = [&](unsigned dcol) {
 #pragma unroll
-    for (int i = 0; i < UNITS; ++i) h[i] = 0.0f;
-
-    // Layer 2 runs as a two-stage pipeline over two accumulator sets: the INPUT half of step t + 1 (y1_{t+1} . W2: 32 of the 48
-    // products, and the only part that reads global memory) is issued while the gates of step t are applied; only the recurrent half
-    // (h_t . R2, 16 products) sits between the gates of two consecutive steps.
+        for (int half = 0; half < (LAYER == 1 ? 1 : 2); ++half)  // layer 1's input is exact in fp16: no lo half
+#pragma unroll
+            for (int ks = 0; ks < KSX; ++ks) {
+                const unsigned long long ad = umma_desc((half ? al_s : ah_s) + ks * 2 * A_LBO, A_LBO, SBO);
+                umma_f16(tmem + dcol, ad, umma_desc(bw_s + ks * 2 * B_LBO, B_LBO, SBO), idesc_zr, (half | ks) ? 1u : 0u);
+                umma_f16(tmem + dcol + 2 * EH, ad, umma_desc(bw_s + ks * 2 * B_LBO + 2 * EH * 16, B_LBO, SBO), idesc_h, (half | ks) ? 1u : 0u);
+            }
+    };
+    // recurrent half: accumulates onto z, r; starts the h-recurrent columns (192..255)
+    auto issue_h = [&](unsigned dcol) {
+#pragma unroll
+        for (int half = 0; half < 2; ++half)
+#pragma unroll
+            for (int ks = KSX; ks < KS; ++ks) {
+                const unsigned a_s = half ? al_s + (L::AL_H0 * 8 / 16 + (ks - KSX)) * 2 * A_LBO : ah_s + ks * 2 * A_LBO;
+                const unsigned long long ad = umma_desc(a_s, A_LBO, SBO);
+                umma_f16(tmem + dcol, ad, umma_desc(bw_s + ks * 2 * B_LBO, B_LBO, SBO), idesc_zr, 1u);
+                umma_f16(tmem + dcol + 3 * EH, ad, umma_desc(bw_s + ks * 2 * B_LBO + 2 * EH * 16, B_LBO, SBO), idesc_h, (half | (ks - KSX)) ? 1u : 0u);
+            }
+    };
+    // layer 2: the 16-byte words of y1_t this thread moves (TPS = 2: one thread the hi halves, the other the lo halves)
     auto y_src = [&](int tt) { return reinterpret_cast<const uint4 *>(Y1h_in + ((size_t)(live ? seq : 0) * T + tt) * (4 * EH)) + (TPS == 2 ? part * (2 * EH / 8) : 0); };
-    constexpr int YV = (TPS == 2 ? 1 : 2) * (2 * EH / 8);  // 16-byte words of y1 this thread moves per step
+    constexpr int YV = LAYER == 2 ? (TPS == 2 ? 1 : 2) * (2 * EH / 8) : 1;
     auto y_store = [&](const uint4 (&v)[YV]) {
         if (TPS == 2) {
             uint4 *dst = part ? Al : Ah;
@@ -477,77 +504,71 @@ gru_tc_kernel(const SrcDev src, const long long first, const long long n, const 
             for (int g = 0; g < 2 * EH / 8; ++g) { Ah[g * TC_M + row] = v[g]; Al[g * TC_M + row] = v[2 * EH / 8 + g]; }
         }
     };
-    auto issue_y = [&](unsigned dcol) {  // input half of a step into accumulator set dcol: z, r columns start here
-        constexpr unsigned idesc_zr = umma_idesc(TC_M, 2 * EH), idesc_h = umma_idesc(TC_M, EH);
+    // layer 1: the embedding row of token (sequence, tt) into the input half of A
+    auto x_store = [&](int slot) {
+        const uint4 *e = embs + slot * (EH / 8);
 #pragma unroll
-        for (int half = 0; half < 2; ++half)
-#pragma unroll
-            for (int ks = 0; ks < 2 * EH / 16; ++ks) {
-                const unsigned long long ad = umma_desc((half ? al_s : ah_s) + ks * 2 * A_LBO, A_LBO, SBO);
-                umma_f16(tmem + dcol, ad, umma_desc(bw_s + ks * 2 * B_LBO, B_LBO, SBO), idesc_zr, (half | ks) ? 1u : 0u);
-                umma_f16(tmem + dcol + 2 * EH, ad, umma_desc(bw_s + ks * 2 * B_LBO + 2 * EH * 16, B_LBO, SBO), idesc_h, (half | ks) ? 1u : 0u);
-            }
+        for (int g = 0; g < EH / 8 / TPS; ++g) Ah[(g * TPS + part) * TC_M + row] = e[g * TPS + part];
     };
-    auto issue_h = [&](unsigned dcol) {  // recurrent half: accumulates onto z, r; starts the h-recurrent columns
-        constexpr unsigned idesc_zr = umma_idesc(TC_M, 2 * EH), idesc_h = umma_idesc(TC_M, EH);
+
+    float h[UNITS];
 #pragma unroll
-        for (int half = 0; half < 2; ++half)
-#pragma unroll
-            for (int ks = 2 * EH / 16; ks < TC_K2 / 16; ++ks) {
-                const unsigned long long ad = umma_desc((half ? al_s : ah_s) + ks * 2 * A_LBO, A_LBO, SBO);
-                umma_f16(tmem + dcol, ad, umma_desc(bw_s + ks * 2 * B_LBO, B_LBO, SBO), idesc_zr, 1u);
-                umma_f16(tmem + dcol + 3 * EH, ad, umma_desc(bw_s + ks * 2 * B_LBO + 2 * EH * 16, B_LBO, SBO), idesc_h, (half | (ks - 2 * EH / 16)) ? 1u : 0u);
-            }
-    };
+    for (int i = 0; i < UNITS; ++i) h[i] = 0.0f;
+
+    // Layer 2 runs as a two-stage pipeline over two accumulator sets: the INPUT half of step t + 1 (y1_{t+1} . W2: 32 of the 48
+    // products, and the only part that reads global memory) is issued while the gates of step t are applied; only the recurrent half
+    // (h_t . R2, 16 products) sits between the gates of two consecutive steps.  Layer 1 (two CTAs per SM, one accumulator set each)
+    // issues both halves together; the other CTA's gate phase covers them.
     if (LAYER == 2) {
         uint4 v[YV];
         const uint4 *y = y_src(dir ? T - 1 : 0);
 #pragma unroll
         for (int g = 0; g < YV; ++g) v[g] = __ldg(y + g);
         y_store(v);
+        for (int a = 1; a <= 3 && a < T; ++a) {
+            const unsigned char *yp = reinterpret_cast<const unsigned char *>(y_src(dir ? T - 1 - a : a));
+            asm volatile("prefetch.global.L2 [%0];" ::"l"(yp));
+            asm volatile("prefetch.global.L2 [%0];" ::"l"(yp + 128));
+            if (TPS == 1) { asm volatile("prefetch.global.L2 [%0];" ::"l"(yp + 256)); asm volatile("prefetch.global.L2 [%0];" ::"l"(yp + 384)); }
+        }
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
         __syncthreads();
         if (tid == 0) {
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-            issue_y(0u);
+            issue_x(0u);
         }
     }
 
     unsigned phase = 0;
+    int slot = LAYER == 1 ? token_slot(sv, dir ? T - 1 : 0, T) : 0;
     for (int step = 0; step < T; ++step) {
         const int t = dir ? T - 1 - step : step;
         const unsigned dcol = LAYER == 2 ? (unsigned)(step & 1) * 256u : 0u;
-        if (LAYER == 1 && step + 1 < T) {  // the next step's row of the token table into L1 (768 bytes = 6 lines)
-            const unsigned char *pn = reinterpret_cast<const unsigned char *>(P1 + (size_t)(dir * NSLOT + tok[(dir ? t - 1 : t + 1) * TC_M + row]) * EG);
+        if (LAYER == 1) x_store(slot);
+        uint4 ynext[YV];
+        const bool more = LAYER == 2 && step + 1 < T;
+        if (more) {  // the next step's input (prefetched into L2 three steps ago) travels while the recurrent products run
+            const uint4 *y = y_src(dir ? t - 1 : t + 1);
 #pragma unroll
-            for (int q = 0; q < 6 / TPS; ++q) asm volatile("prefetch.global.L1 [%0];" ::"l"(pn + 128 * (q * TPS + part)));
+            for (int g = 0; g < YV; ++g) ynext[g] = __ldg(y + g);
+            if (step + 4 < T) {  // and the one three steps further leaves DRAM now
+                const unsigned char *yp = reinterpret_cast<const unsigned char *>(y_src(dir ? t - 4 : t + 4));
+                asm volatile("prefetch.global.L2 [%0];" ::"l"(yp));
+                asm volatile("prefetch.global.L2 [%0];" ::"l"(yp + 128));
+                if (TPS == 1) { asm volatile("prefetch.global.L2 [%0];" ::"l"(yp + 256)); asm volatile("prefetch.global.L2 [%0];" ::"l"(yp + 384)); }
+            }
         }
-        // generic-proxy writes of A (last step's state) -> visible to the tensor core's async proxy
+        // generic-proxy writes of A (this step's input, last step's state) -> visible to the tensor core's async proxy
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
         asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");  // the reads of D below precede the next product
         __syncthreads();
         if (tid == 0) {
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-            if (LAYER == 1) {
-                constexpr unsigned idesc = umma_idesc(TC_M, EG);
-#pragma unroll
-                for (int half = 0; half < 2; ++half)
-#pragma unroll
-                    for (int ks = 0; ks < TC_K1 / 16; ++ks)
-                        umma_f16(tmem, umma_desc((half ? al_s : ah_s) + ks * 2 * A_LBO, A_LBO, SBO), umma_desc(bw_s + ks * 2 * B_LBO, B_LBO, SBO), idesc,
-                                 (half | ks) ? 1u : 0u);
-            } else {
-                issue_h(dcol);
-            }
+            if (LAYER == 1) issue_x(dcol);
+            issue_h(dcol);
             asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar_s) : "memory");
         }
-        uint4 ynext[YV];
-        const bool more = LAYER == 2 && step + 1 < T;
-        if (more) {  // the next step's input travels from L2 / DRAM while the recurrent products run
-            const uint4 *y = y_src(dir ? t - 1 : t + 1);
-#pragma unroll
-            for (int g = 0; g < YV; ++g) ynext[g] = __ldg(y + g);
-        }
+        if (LAYER == 1 && step + 1 < T) slot = token_slot(sv, dir ? t - 1 : t + 1, T);  // the next token, while the products run
         {   // wait for the products of this step (the commit covers the input half issued one step earlier too)
             unsigned done = 0, spins = 0;
             do {
@@ -564,67 +585,39 @@ gru_tc_kernel(const SrcDev src, const long long first, const long long n, const 
             __syncthreads();
             if (tid == 0) {
                 asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-                issue_y(dcol ^ 256u);
+                issue_x(dcol ^ 256u);
             }
         }
         const unsigned tacc = trow + dcol;
 
         // ---- gates, 16 units at a time: z = s(xz + az), r = s(xr + ar), g = tanh(xh + r (ah + bRh)), h' = (1 - z) g + z h
-        const float *xp = LAYER == 1 ? P1 + (size_t)(dir * NSLOT + tok[t * TC_M + row]) * EG : nullptr;
-        const float *bRh = LAYER == 1 ? bias : bias + EG;
+        // (columns 0..127 hold xz + az and xr + ar already summed by the tensor core, 128..191 xh, 192..255 ah; biases added here)
         __half *yout = nullptr;
         if (LAYER == 1) yout = Y1h_out + ((size_t)(live ? seq : 0) * T + t) * (4 * EH) + dir * EH;
-        constexpr int HK0 = LAYER == 1 ? 0 : 2 * EH / 8;  // first k-group of the state inside A
 #pragma unroll
         for (int cc = 0; cc < UNITS / 16; ++cc) {
             const int c = cc + part * (UNITS / 16);  // 16-unit chunk of the hidden state
             float az[16], ar[16], ah[16], xh[16];
             tmem_ld16(tacc + 16 * c, az);
             tmem_ld16(tacc + EH + 16 * c, ar);
-            if (LAYER == 1) {
-                tmem_ld16(tacc + 2 * EH + 16 * c, ah);
-            } else {
-                tmem_ld16(tacc + 2 * EH + 16 * c, xh);
-                tmem_ld16(tacc + 3 * EH + 16 * c, ah);
-            }
-            if (LAYER == 1) {  // the gathered input projection travels while the TMEM loads complete
-#pragma unroll
-                for (int q = 0; q < 4; ++q) {
-                    const float4 vh = __ldg(reinterpret_cast<const float4 *>(xp + 2 * EH + 16 * c) + q);
-                    xh[4 * q] = vh.x; xh[4 * q + 1] = vh.y; xh[4 * q + 2] = vh.z; xh[4 * q + 3] = vh.w;
-                }
-            }
+            tmem_ld16(tacc + 2 * EH + 16 * c, xh);
+            tmem_ld16(tacc + 3 * EH + 16 * c, ah);
             tmem_ld_wait();
-            if (LAYER == 1) {
-#pragma unroll
-                for (int q = 0; q < 4; ++q) {
-                    const float4 vz = __ldg(reinterpret_cast<const float4 *>(xp + 16 * c) + q);
-                    const float4 vr = __ldg(reinterpret_cast<const float4 *>(xp + EH + 16 * c) + q);
-                    az[4 * q] += vz.x; az[4 * q + 1] += vz.y; az[4 * q + 2] += vz.z; az[4 * q + 3] += vz.w;
-                    ar[4 * q] += vr.x; ar[4 * q + 1] += vr.y; ar[4 * q + 2] += vr.z; ar[4 * q + 3] += vr.w;
-                }
-            } else {
-#pragma unroll
-                for (int j = 0; j < 16; ++j) {
-                    az[j] += bias[16 * c + j];
-                    ar[j] += bias[EH + 16 * c + j];
-                    xh[j] += bias[2 * EH + 16 * c + j];
-                }
-            }
             unsigned hi[8], lo[8];
 #pragma unroll
             for (int j = 0; j < 16; ++j) {
+                const int i = 16 * c + j;
                 float z, r;
-                gate_zr(az[j], ar[j], z, r);
-                const float g = tc_tanh(xh[j] + r * (ah[j] + bRh[16 * c + j]));
+                gate_zr(az[j] + bias[i], ar[j] + bias[EH + i], z, r);
+                const float g = tc_tanh(xh[j] + bias[2 * EH + i] + r * (ah[j] + bias[EG + i]));
                 h[16 * cc + j] = (1.0f - z) * g + z * h[16 * cc + j];
             }
 #pragma unroll
             for (int j = 0; j < 8; ++j) split2(h[16 * cc + 2 * j], h[16 * cc + 2 * j + 1], hi[j], lo[j]);
-            Ah[(HK0 + 2 * c) * TC_M + row] = make_uint4(hi[0], hi[1], hi[2], hi[3]);
-            Ah[(HK0 + 2 * c + 1) * TC_M + row] = make_uint4(hi[4], hi[5], hi[6], hi[7]);
-            Al[(HK0 + 2 * c) * TC_M + row] = make_uint4(lo[0], lo[1], lo[2], lo[3]);
-            Al[(HK0 + 2 * c + 1) * TC_M + row] = make_uint4(lo[4], lo[5], lo[6], lo[7]);
+            Ah[(L::KGX + 2 * c) * TC_M + row] = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+            Ah[(L::KGX + 2 * c + 1) * TC_M + row] = make_uint4(hi[4], hi[5], hi[6], hi[7]);
+            Al[(L::AL_H0 + 2 * c) * TC_M + row] = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+            Al[(L::AL_H0 + 2 * c + 1) * TC_M + row] = make_uint4(lo[4], lo[5], lo[6], lo[7]);
             if (LAYER == 1 && live) {
                 uint4 *yo = reinterpret_cast<uint4 *>(yout + 16 * c);
                 yo[0] = make_uint4(hi[0], hi[1], hi[2], hi[3]);
@@ -642,7 +635,7 @@ gru_tc_kernel(const SrcDev src, const long long first, const long long n, const 
     }
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
-    if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(LAYER == 1 ? TC_COLS1 : TC_COLS2) : "memory");
+    if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(TCOLS) : "memory");
 }
 
 // fp16 image of a weight matrix in the operand layout above: rows x K (row-major fp32, fp16-exact) -> [K/8][rows][8 halves];
@@ -715,22 +708,41 @@ int embedder_upload(const EmbedWeightsHost &w, int device, int max_len, DeviceEm
 #ifndef DRM_EMU
     {   // operand images for the tensor-core form
         std::vector<uint16_t> b1((size_t)2 * (TC_K1 / 8) * EG * 8, 0), b2i((size_t)2 * (TC_K2 / 8) * EG * 8, 0);
-        std::vector<float> bias2((size_t)2 * (EG + EH));
+        std::vector<float> bias1((size_t)2 * (EG + EH)), bias2((size_t)2 * (EG + EH));
         bool exact = true;
         for (int dir = 0; dir < 2; ++dir) {
             std::vector<uint16_t> img1((size_t)(TC_K1 / 8) * EG * 8, 0), img2((size_t)(TC_K2 / 8) * EG * 8, 0);
-            exact &= tc_pack(w.R1.data() + (size_t)dir * EG * EH, EG, EH, 0, EG, img1);
+            exact &= tc_pack(w.W1.data() + (size_t)dir * EG * EH, EG, EH, 0, EG, img1);
+            exact &= tc_pack(w.R1.data() + (size_t)dir * EG * EH, EG, EH, EH, EG, img1);
             exact &= tc_pack(w.W2.data() + (size_t)dir * EG * 2 * EH, EG, 2 * EH, 0, EG, img2);
             exact &= tc_pack(w.R2.data() + (size_t)dir * EG * EH, EG, EH, 2 * EH, EG, img2);
             std::memcpy(b1.data() + (size_t)dir * img1.size(), img1.data(), img1.size() * 2);
             std::memcpy(b2i.data() + (size_t)dir * img2.size(), img2.data(), img2.size() * 2);
-            for (int row = 0; row < EG; ++row) bias2[(size_t)dir * (EG + EH) + row] = b2[dir * EG + row];
-            for (int i = 0; i < EH; ++i) bias2[(size_t)dir * (EG + EH) + EG + i] = bR2[dir * EH + i];
+            for (int row = 0; row < EG; ++row) {
+                bias1[(size_t)dir * (EG + EH) + row] = w.B1[(size_t)dir * 4 * EH + row];
+                bias2[(size_t)dir * (EG + EH) + row] = b2[dir * EG + row];
+            }
+            for (int i = 0; i < EH; ++i) {
+                bias1[(size_t)dir * (EG + EH) + EG + i] = bR1[dir * EH + i];
+                bias2[(size_t)dir * (EG + EH) + EG + i] = bR2[dir * EH + i];
+            }
+        }
+        // the 97 embedding rows the tokeniser can select (slot 0 = the pad id), as fp16: row-major, 128 bytes each
+        std::vector<uint16_t> emb16((size_t)NSLOT * EH);
+        for (int slot = 0; slot < NSLOT; ++slot) {
+            const float *x = w.emb.data() + (size_t)(slot == 0 ? 0 : slot_token_id(slot - 1)) * EH;
+            for (int k = 0; k < EH; ++k) {
+                const __half hv = __float2half_rn(x[k]);
+                if (__half2float(hv) != x[k]) exact = false;
+                emb16[(size_t)slot * EH + k] = __half_as_ushort(hv);
+            }
         }
         e.tc_exact = exact;
         if ((rc = upload(b1, &e.Bw1)) != DRM_OK) return rc;
         if ((rc = upload(b2i, &e.Bw2)) != DRM_OK) return rc;
+        if ((rc = upload(bias1, &e.bias1)) != DRM_OK) return rc;
         if ((rc = upload(bias2, &e.bias2)) != DRM_OK) return rc;
+        if ((rc = upload(emb16, &e.emb16)) != DRM_OK) return rc;
     }
 #endif
     return DRM_OK;
@@ -739,11 +751,11 @@ int embedder_upload(const EmbedWeightsHost &w, int device, int max_len, DeviceEm
 void embedder_free(DeviceEmbedder &e)
 {
     if (e.device >= 0) cudaSetDevice(e.device);
-    for (float **p : {&e.P1, &e.R1, &e.bR1, &e.W2, &e.b2, &e.R2, &e.bR2, &e.Y1, &e.X2, &e.out, &e.bias2}) {
+    for (float **p : {&e.P1, &e.R1, &e.bR1, &e.W2, &e.b2, &e.R2, &e.bR2, &e.Y1, &e.X2, &e.out, &e.bias1, &e.bias2}) {
         if (*p) cudaFree(*p);
         *p = nullptr;
     }
-    for (uint16_t **p : {&e.Bw1, &e.Bw2, &e.Y1h}) {
+    for (uint16_t **p : {&e.Bw1, &e.Bw2, &e.Y1h, &e.emb16}) {
         if (*p) cudaFree(*p);
         *p = nullptr;
     }
@@ -772,9 +784,8 @@ static int launch_embed_tc(DeviceEmbedder &e, const EmbedSource &src, int64_t fi
     s.cls = src.cls; s.form = src.form; s.ref_n = src.ref_n; s.ref_len = src.ref_len;
     s.first_id = src.first_id; s.id_step = src.id_step;
     s.ids = src.ids; s.decorate = src.decorate;
-    // layer 1 asks for more shared memory than it uses so that exactly two CTAs (2 x 256 TMEM columns) share an SM
-    // (78 KB + 1 KB of driver shared memory, twice, stays inside the 164 KB carve-out step and leaves 92 KB of L1 for the token table)
-    constexpr int SM1 = TcLayout<1>::BYTES > 78 * 1024 ? TcLayout<1>::BYTES : 78 * 1024, SM2 = TcLayout<2>::BYTES;
+    // layer 1: 110 KB per CTA, two CTAs (2 x 256 TMEM columns) per SM; layer 2: 170 KB and all 512 columns, one CTA per SM
+    constexpr int SM1 = TcLayout<1>::BYTES, SM2 = TcLayout<2>::BYTES;
     // threads per sequence in the gate phase, per layer: DRM_EMBED_TC_TPS = "<layer 1><layer 2>" (A/B; default "22")
     int tps1 = 2, tps2 = 2;
     if (const char *ev = getenv("DRM_EMBED_TC_TPS")) {
@@ -788,8 +799,8 @@ static int launch_embed_tc(DeviceEmbedder &e, const EmbedSource &src, int64_t fi
     for (int64_t done = 0; done < n; done += e.chunk_tc) {
         const int64_t m = (n - done) < e.chunk_tc ? (n - done) : e.chunk_tc;
         const unsigned blocks = (unsigned)((m + TC_M - 1) / TC_M) * 2;
-        k1<<<blocks, TC_M * tps1, SM1, stream>>>(s, first + done, m, T, e.P1, reinterpret_cast<const uint4 *>(e.Bw1), e.bR1, nullptr,
-                                                  reinterpret_cast<__half *>(e.Y1h), nullptr);
+        k1<<<blocks, TC_M * tps1, SM1, stream>>>(s, first + done, m, T, reinterpret_cast<const uint4 *>(e.emb16), reinterpret_cast<const uint4 *>(e.Bw1),
+                                                  e.bias1, nullptr, reinterpret_cast<__half *>(e.Y1h), nullptr);
         DRM_CUDA_TRY(cudaGetLastError());
         k2<<<blocks, TC_M * tps2, SM2, stream>>>(s, first + done, m, T, nullptr, reinterpret_cast<const uint4 *>(e.Bw2), e.bias2,
                                                   reinterpret_cast<const __half *>(e.Y1h), nullptr, out_dev + (size_t)done * 2 * EH);
