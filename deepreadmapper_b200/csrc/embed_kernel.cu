@@ -398,7 +398,11 @@ template <int LAYER> struct TcLayout {
     static constexpr int K = KX + EH;
     static constexpr int KG = K / 8, KGX = KX / 8;
     static constexpr int AL_H0 = LAYER == 1 ? 0 : KGX;          // k-group of the state inside Al
-    static constexpr int B_BYTES = KG * EG * 16;
+    // weights: the input half Bx [KX/8][BX_ROWS][16 B] (layer 2: rows z, r, 64 ZERO rows, h - one N = 256 product per k-step writes
+    // xz, xr, clears the h-recurrent columns and writes xh), then the recurrent half Bh [8][192][16 B] (rows z, r, h: one N = 192 product)
+    static constexpr int BX_ROWS = LAYER == 1 ? EG : EG + EH;
+    static constexpr int BX_BYTES = KGX * BX_ROWS * 16, BH_BYTES = (EH / 8) * EG * 16;
+    static constexpr int B_BYTES = BX_BYTES + BH_BYTES;
     static constexpr int AH_BYTES = KG * TC_M * 16;
     static constexpr int AL_BYTES = (AL_H0 + EH / 8) * TC_M * 16;
     static constexpr int BIAS_FLOATS = EG + EH;                  // input biases z, r, h | recurrent bias of h
@@ -465,44 +469,60 @@ gru_tc_kernel(const SrcDev src, const long long first, const long long n, const 
     const unsigned trow = tmem + ((unsigned)((warp & 3) * 32) << 16);  // this warp's 32 lanes
 
     const unsigned ah_s = smem_u32(Ah), al_s = smem_u32(Al), bw_s = smem_u32(Bw);
-    constexpr unsigned A_LBO = TC_M * 16, B_LBO = EG * 16, SBO = 128;
-    constexpr unsigned idesc_zr = umma_idesc(TC_M, 2 * EH), idesc_h = umma_idesc(TC_M, EH);
-
-    // input half of a step into accumulator set dcol: starts the z, r columns (0..127) and the h-input columns (128..191)
+    constexpr unsigned A_LBO = TC_M * 16, BX_LBO = L::BX_ROWS * 16, BH_LBO = EG * 16, SBO = 128;
+    const unsigned bh_s = bw_s + L::BX_BYTES;
+    // Accumulator columns of a set: z 0..63 | r 64..127 | h recurrent 128..191 | h input 192..255.  A tcgen05.mma of this shape
+    // (M = 128, K = 16) occupies the tensor pipe for ~190 clocks whether N is 64 or 128 (ncu: hmma cycles per product), so the step
+    // is issued as FEW, WIDE products.
+    constexpr unsigned idesc_256 = umma_idesc(TC_M, 4 * EH), idesc_192 = umma_idesc(TC_M, 3 * EH), idesc_128 = umma_idesc(TC_M, 2 * EH),
+                       idesc_64 = umma_idesc(TC_M, EH);
+    // input half of a step into accumulator set dcol
     auto issue_x = [&](unsigned dcol) {
 #pragma unroll
         for (int half = 0; half < (LAYER == 1 ? 1 : 2); ++half)  // layer 1's input is exact in fp16: no lo half
 #pragma unroll
             for (int ks = 0; ks < KSX; ++ks) {
                 const unsigned long long ad = umma_desc((half ? al_s : ah_s) + ks * 2 * A_LBO, A_LBO, SBO);
-                umma_f16(tmem + dcol, ad, umma_desc(bw_s + ks * 2 * B_LBO, B_LBO, SBO), idesc_zr, (half | ks) ? 1u : 0u);
-                umma_f16(tmem + dcol + 2 * EH, ad, umma_desc(bw_s + ks * 2 * B_LBO + 2 * EH * 16, B_LBO, SBO), idesc_h, (half | ks) ? 1u : 0u);
+                if (LAYER == 2) {  // rows z, r, zero, h -> all 256 columns; the first product of the step overwrites
+                    umma_f16(tmem + dcol, ad, umma_desc(bw_s + ks * 2 * BX_LBO, BX_LBO, SBO), idesc_256, (half | ks) ? 1u : 0u);
+                } else {           // 110 KB budget, no room for zero rows: z, r and the input half of h as two products
+                    umma_f16(tmem + dcol, ad, umma_desc(bw_s + ks * 2 * BX_LBO, BX_LBO, SBO), idesc_128, ks ? 1u : 0u);
+                    umma_f16(tmem + dcol + 3 * EH, ad, umma_desc(bw_s + ks * 2 * BX_LBO + 2 * EH * 16, BX_LBO, SBO), idesc_64, ks ? 1u : 0u);
+                }
             }
     };
-    // recurrent half: accumulates onto z, r; starts the h-recurrent columns (192..255)
+    // recurrent half: rows z, r, h accumulate onto columns 0..191 (layer 1: its first product starts the h-recurrent columns itself)
     auto issue_h = [&](unsigned dcol) {
 #pragma unroll
         for (int half = 0; half < 2; ++half)
 #pragma unroll
-            for (int ks = KSX; ks < KS; ++ks) {
-                const unsigned a_s = half ? al_s + (L::AL_H0 * 8 / 16 + (ks - KSX)) * 2 * A_LBO : ah_s + ks * 2 * A_LBO;
+            for (int ks = 0; ks < EH / 16; ++ks) {
+                const unsigned a_s = half ? al_s + (L::AL_H0 + 2 * ks) * A_LBO : ah_s + (L::KGX + 2 * ks) * A_LBO;
                 const unsigned long long ad = umma_desc(a_s, A_LBO, SBO);
-                umma_f16(tmem + dcol, ad, umma_desc(bw_s + ks * 2 * B_LBO, B_LBO, SBO), idesc_zr, 1u);
-                umma_f16(tmem + dcol + 3 * EH, ad, umma_desc(bw_s + ks * 2 * B_LBO + 2 * EH * 16, B_LBO, SBO), idesc_h, (half | (ks - KSX)) ? 1u : 0u);
+                if (LAYER == 1 && half == 0 && ks == 0) {
+                    umma_f16(tmem + dcol, ad, umma_desc(bh_s, BH_LBO, SBO), idesc_128, 1u);
+                    umma_f16(tmem + dcol + 2 * EH, ad, umma_desc(bh_s + 2 * EH * 16, BH_LBO, SBO), idesc_64, 0u);
+                } else {
+                    umma_f16(tmem + dcol, ad, umma_desc(bh_s + ks * 2 * BH_LBO, BH_LBO, SBO), idesc_192, 1u);
+                }
             }
     };
-    // layer 2: the 16-byte words of y1_t this thread moves (TPS = 2: one thread the hi halves, the other the lo halves)
-    auto y_src = [&](int tt) { return reinterpret_cast<const uint4 *>(Y1h_in + ((size_t)(live ? seq : 0) * T + tt) * (4 * EH)) + (TPS == 2 ? part * (2 * EH / 8) : 0); };
-    constexpr int YV = LAYER == 2 ? (TPS == 2 ? 1 : 2) * (2 * EH / 8) : 1;
+    // layer 2: thread `part` of a sequence moves words [part * YV, (part + 1) * YV) of the 32 16-byte words of y1_t (hi 0..15 | lo 16..31)
+    constexpr int YV = LAYER == 2 ? 4 * EH / 8 / TPS : 1;
+    auto y_src = [&](int tt) { return reinterpret_cast<const uint4 *>(Y1h_in + ((size_t)(live ? seq : 0) * T + tt) * (4 * EH)) + part * YV; };
     auto y_store = [&](const uint4 (&v)[YV]) {
-        if (TPS == 2) {
-            uint4 *dst = part ? Al : Ah;
 #pragma unroll
-            for (int g = 0; g < 2 * EH / 8; ++g) dst[g * TC_M + row] = v[g];
-        } else {
-#pragma unroll
-            for (int g = 0; g < 2 * EH / 8; ++g) { Ah[g * TC_M + row] = v[g]; Al[g * TC_M + row] = v[2 * EH / 8 + g]; }
+        for (int g = 0; g < YV; ++g) {
+            const int w = part * YV + g;  // TPS >= 2: a thread's words are all hi or all lo, the branch is uniform per warp
+            if (w < 2 * EH / 8) Ah[w * TC_M + row] = v[g];
+            else Al[(w - 2 * EH / 8) * TC_M + row] = v[g];
         }
+    };
+    auto y_prefetch = [&](int tt) {  // 512 bytes = 4 lines per sequence and step, shared out over the sequence's threads
+        const unsigned char *yp = reinterpret_cast<const unsigned char *>(Y1h_in + ((size_t)(live ? seq : 0) * T + tt) * (4 * EH));
+        constexpr int LP = TPS >= 4 ? 1 : 4 / TPS;  // lines per thread
+#pragma unroll
+        for (int q = 0; q < LP; ++q) asm volatile("prefetch.global.L2 [%0];" ::"l"(yp + 128 * ((part * LP + q) & 3)));
     };
     // layer 1: the embedding row of token (sequence, tt) into the input half of A
     auto x_store = [&](int slot) {
@@ -525,12 +545,7 @@ gru_tc_kernel(const SrcDev src, const long long first, const long long n, const 
 #pragma unroll
         for (int g = 0; g < YV; ++g) v[g] = __ldg(y + g);
         y_store(v);
-        for (int a = 1; a <= 3 && a < T; ++a) {
-            const unsigned char *yp = reinterpret_cast<const unsigned char *>(y_src(dir ? T - 1 - a : a));
-            asm volatile("prefetch.global.L2 [%0];" ::"l"(yp));
-            asm volatile("prefetch.global.L2 [%0];" ::"l"(yp + 128));
-            if (TPS == 1) { asm volatile("prefetch.global.L2 [%0];" ::"l"(yp + 256)); asm volatile("prefetch.global.L2 [%0];" ::"l"(yp + 384)); }
-        }
+        for (int a = 1; a <= 3 && a < T; ++a) y_prefetch(dir ? T - 1 - a : a);
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
         __syncthreads();
         if (tid == 0) {
@@ -551,12 +566,7 @@ gru_tc_kernel(const SrcDev src, const long long first, const long long n, const 
             const uint4 *y = y_src(dir ? t - 1 : t + 1);
 #pragma unroll
             for (int g = 0; g < YV; ++g) ynext[g] = __ldg(y + g);
-            if (step + 4 < T) {  // and the one three steps further leaves DRAM now
-                const unsigned char *yp = reinterpret_cast<const unsigned char *>(y_src(dir ? t - 4 : t + 4));
-                asm volatile("prefetch.global.L2 [%0];" ::"l"(yp));
-                asm volatile("prefetch.global.L2 [%0];" ::"l"(yp + 128));
-                if (TPS == 1) { asm volatile("prefetch.global.L2 [%0];" ::"l"(yp + 256)); asm volatile("prefetch.global.L2 [%0];" ::"l"(yp + 384)); }
-            }
+            if (step + 4 < T) y_prefetch(dir ? t - 4 : t + 4);  // and the one three steps further leaves DRAM now
         }
         // generic-proxy writes of A (this step's input, last step's state) -> visible to the tensor core's async proxy
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
@@ -574,7 +584,7 @@ gru_tc_kernel(const SrcDev src, const long long first, const long long n, const 
             do {
                 asm volatile("{\n\t.reg .pred P1;\n\tmbarrier.try_wait.parity.shared::cta.b64 P1, [%1], %2;\n\tselp.b32 %0, 1, 0, P1;\n\t}"
                              : "=r"(done) : "r"(bar_s), "r"(phase) : "memory");
-                if (!done && ++spins > (1u << 24)) __trap();  // a product that never completes must not hang the GPU
+                if (!done && ++spins > (1u << 27)) __trap();  // a product that never completes must not hang the GPU
             } while (!done);
             phase ^= 1u;
         }
@@ -591,7 +601,7 @@ gru_tc_kernel(const SrcDev src, const long long first, const long long n, const 
         const unsigned tacc = trow + dcol;
 
         // ---- gates, 16 units at a time: z = s(xz + az), r = s(xr + ar), g = tanh(xh + r (ah + bRh)), h' = (1 - z) g + z h
-        // (columns 0..127 hold xz + az and xr + ar already summed by the tensor core, 128..191 xh, 192..255 ah; biases added here)
+        // (columns 0..127 hold xz + az and xr + ar already summed by the tensor core, 128..191 ah, 192..255 xh; biases added here)
         __half *yout = nullptr;
         if (LAYER == 1) yout = Y1h_out + ((size_t)(live ? seq : 0) * T + t) * (4 * EH) + dir * EH;
 #pragma unroll
@@ -600,8 +610,8 @@ gru_tc_kernel(const SrcDev src, const long long first, const long long n, const 
             float az[16], ar[16], ah[16], xh[16];
             tmem_ld16(tacc + 16 * c, az);
             tmem_ld16(tacc + EH + 16 * c, ar);
-            tmem_ld16(tacc + 2 * EH + 16 * c, xh);
-            tmem_ld16(tacc + 3 * EH + 16 * c, ah);
+            tmem_ld16(tacc + 2 * EH + 16 * c, ah);
+            tmem_ld16(tacc + 3 * EH + 16 * c, xh);
             tmem_ld_wait();
             unsigned hi[8], lo[8];
 #pragma unroll
@@ -638,9 +648,9 @@ gru_tc_kernel(const SrcDev src, const long long first, const long long n, const 
     if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(TCOLS) : "memory");
 }
 
-// fp16 image of a weight matrix in the operand layout above: rows x K (row-major fp32, fp16-exact) -> [K/8][rows][8 halves];
-// `k0` places it at k-group k0 / 8 of a wider operand
-bool tc_pack(const float *Wm, int rows, int K, int k0, int rows_total, std::vector<uint16_t> &img)
+// fp16 image of a weight matrix in the operand layout above: rows x K (row-major fp32, fp16-exact) -> [K/8][rows_total][8 halves]
+// at `img`; rows from 128 on (the candidate gate) land `h_shift` rows further down (64 where the zero rows sit in between)
+bool tc_pack(const float *Wm, int rows, int K, int rows_total, int h_shift, uint16_t *img)
 {
     bool exact = true;
     for (int r = 0; r < rows; ++r)
@@ -648,7 +658,7 @@ bool tc_pack(const float *Wm, int rows, int K, int k0, int rows_total, std::vect
             const float v = Wm[(size_t)r * K + k];
             const __half hv = __float2half_rn(v);
             if (__half2float(hv) != v) exact = false;
-            img[((size_t)((k0 + k) / 8) * rows_total + r) * 8 + (k0 + k) % 8] = __half_as_ushort(hv);
+            img[((size_t)(k / 8) * rows_total + r + (r >= 2 * EH ? h_shift : 0)) * 8 + k % 8] = __half_as_ushort(hv);
         }
     return exact;
 }
@@ -707,17 +717,16 @@ int embedder_upload(const EmbedWeightsHost &w, int device, int max_len, DeviceEm
     if ((rc = upload(bR2, &e.bR2)) != DRM_OK) return rc;
 #ifndef DRM_EMU
     {   // operand images for the tensor-core form
-        std::vector<uint16_t> b1((size_t)2 * (TC_K1 / 8) * EG * 8, 0), b2i((size_t)2 * (TC_K2 / 8) * EG * 8, 0);
+        constexpr size_t IMG1 = TcLayout<1>::B_BYTES / 2, IMG2 = TcLayout<2>::B_BYTES / 2;  // halves per direction
+        std::vector<uint16_t> b1(2 * IMG1, 0), b2i(2 * IMG2, 0);
         std::vector<float> bias1((size_t)2 * (EG + EH)), bias2((size_t)2 * (EG + EH));
         bool exact = true;
         for (int dir = 0; dir < 2; ++dir) {
-            std::vector<uint16_t> img1((size_t)(TC_K1 / 8) * EG * 8, 0), img2((size_t)(TC_K2 / 8) * EG * 8, 0);
-            exact &= tc_pack(w.W1.data() + (size_t)dir * EG * EH, EG, EH, 0, EG, img1);
-            exact &= tc_pack(w.R1.data() + (size_t)dir * EG * EH, EG, EH, EH, EG, img1);
-            exact &= tc_pack(w.W2.data() + (size_t)dir * EG * 2 * EH, EG, 2 * EH, 0, EG, img2);
-            exact &= tc_pack(w.R2.data() + (size_t)dir * EG * EH, EG, EH, 2 * EH, EG, img2);
-            std::memcpy(b1.data() + (size_t)dir * img1.size(), img1.data(), img1.size() * 2);
-            std::memcpy(b2i.data() + (size_t)dir * img2.size(), img2.data(), img2.size() * 2);
+            uint16_t *i1 = b1.data() + dir * IMG1, *i2 = b2i.data() + dir * IMG2;
+            exact &= tc_pack(w.W1.data() + (size_t)dir * EG * EH, EG, EH, TcLayout<1>::BX_ROWS, 0, i1);
+            exact &= tc_pack(w.R1.data() + (size_t)dir * EG * EH, EG, EH, EG, 0, i1 + TcLayout<1>::BX_BYTES / 2);
+            exact &= tc_pack(w.W2.data() + (size_t)dir * EG * 2 * EH, EG, 2 * EH, TcLayout<2>::BX_ROWS, EH, i2);
+            exact &= tc_pack(w.R2.data() + (size_t)dir * EG * EH, EG, EH, EG, 0, i2 + TcLayout<2>::BX_BYTES / 2);
             for (int row = 0; row < EG; ++row) {
                 bias1[(size_t)dir * (EG + EH) + row] = w.B1[(size_t)dir * 4 * EH + row];
                 bias2[(size_t)dir * (EG + EH) + row] = b2[dir * EG + row];
@@ -786,14 +795,15 @@ static int launch_embed_tc(DeviceEmbedder &e, const EmbedSource &src, int64_t fi
     s.ids = src.ids; s.decorate = src.decorate;
     // layer 1: 110 KB per CTA, two CTAs (2 x 256 TMEM columns) per SM; layer 2: 170 KB and all 512 columns, one CTA per SM
     constexpr int SM1 = TcLayout<1>::BYTES, SM2 = TcLayout<2>::BYTES;
-    // threads per sequence in the gate phase, per layer: DRM_EMBED_TC_TPS = "<layer 1><layer 2>" (A/B; default "22")
-    int tps1 = 2, tps2 = 2;
+    // threads per sequence in the gate phase, per layer: DRM_EMBED_TC_TPS = "<layer 1><layer 2>" (A/B; layer 1: 1 or 2, two CTAs per
+    // SM; layer 2: 1, 2 or 4, one CTA per SM)
+    int tps1 = 2, tps2 = 2;  // four threads per sequence in layer 2 measured no faster (the step is bound by its tensor products)
     if (const char *ev = getenv("DRM_EMBED_TC_TPS")) {
         if (ev[0] == '1') tps1 = 1;
-        if (ev[0] && ev[1] == '1') tps2 = 1;
+        if (ev[0] && (ev[1] == '1' || ev[1] == '2' || ev[1] == '4')) tps2 = ev[1] - '0';
     }
     auto k1 = tps1 == 2 ? gru_tc_kernel<1, 2> : gru_tc_kernel<1, 1>;
-    auto k2 = tps2 == 2 ? gru_tc_kernel<2, 2> : gru_tc_kernel<2, 1>;
+    auto k2 = tps2 == 4 ? gru_tc_kernel<2, 4> : tps2 == 2 ? gru_tc_kernel<2, 2> : gru_tc_kernel<2, 1>;
     DRM_CUDA_TRY(cudaFuncSetAttribute(k1, cudaFuncAttributeMaxDynamicSharedMemorySize, SM1));
     DRM_CUDA_TRY(cudaFuncSetAttribute(k2, cudaFuncAttributeMaxDynamicSharedMemorySize, SM2));
     for (int64_t done = 0; done < n; done += e.chunk_tc) {
