@@ -9,6 +9,7 @@
 #include "common.h"
 
 #include <algorithm>
+#include <cstdlib>
 #include <vector>
 
 namespace drm {
@@ -16,35 +17,56 @@ namespace drm {
 namespace {
 
 // the sparse branch of find_sequences: unique ids in order of first appearance + the flat mapping into them.
-// The position -> row index is an open-addressing table (linear probing, power-of-two capacity at most half full): the
-// reference's std::unordered_map gives the same rows - they are numbered by first appearance - at a third of the speed,
-// and this loop is what is left of the stage's time once the windows embed on the tensor cores.
+// The reference keeps position -> row in a std::unordered_map; the rows are numbered by first appearance, so any exact
+// position index gives the same result.  An expansion touches 2 * stride - 1 CONSECUTIVE positions, so a direct table indexed by
+// position (4 bytes per position below `bound`: 37 MB for E. coli, used up to 2^29 positions) walks memory sequentially where a
+// hash scatters; above that an open-addressing table (linear probing, at most half full).  This loop is what is left of the
+// stage's host time once the windows embed on the tensor cores.
 int expand_flat(const uint64_t *ids, int64_t n_ids, uint64_t stride, uint64_t bound, L2Plan &plan)
 {
     const uint64_t worst = (uint64_t)n_ids * (2 * stride - 1);  // every expanded position distinct
-    const uint64_t most = std::min(worst, bound);                // distinct positions: all below `bound`
-    uint64_t cap = 1024;
-    while (cap < 2 * most && cap < (1ull << 33)) cap <<= 1;
-    std::vector<uint64_t> keys(cap, ~0ull);  // ~0 = empty (a position is below `bound` <= 2^64 - 1)
-    std::vector<uint32_t> rows(cap);
-    const uint64_t mask = cap - 1;
     plan.map.reserve((size_t)worst);
+    const char *tb = getenv("DRM_L2_PLAN_TABLE");  // "hash" forces the hashed table (A/B, tests)
+    const bool direct = bound <= (1ull << 29) && !(tb && tb[0] == 'h');
+    std::vector<uint32_t> row_of;          // direct: row + 1 of a position, 0 = not seen
+    std::vector<uint64_t> keys;            // hashed: ~0 = empty (a position is below `bound` <= 2^64 - 1)
+    std::vector<uint32_t> rows;
+    uint64_t mask = 0;
+    if (direct) row_of.assign((size_t)bound, 0u);
+    else {
+        const uint64_t most = std::min(worst, bound);  // distinct positions: all below `bound`
+        uint64_t cap = 1024;
+        while (cap < 2 * most && cap < (1ull << 33)) cap <<= 1;
+        keys.assign((size_t)cap, ~0ull);
+        rows.resize((size_t)cap);
+        mask = cap - 1;
+    }
     for (int64_t j = 0; j < n_ids; ++j) {
         const uint64_t p = ids[j] * stride;  // size_t arithmetic: wraps like the reference
         if (p >= bound) continue;
         const uint64_t start = p >= stride - 1 ? p - stride + 1 : 0;
         const uint64_t end = std::min(p + stride, bound);
         for (uint64_t pos = start; pos < end; ++pos) {
-            uint64_t slot = (pos * 0x9e3779b97f4a7c15ull) >> 20 & mask;
-            while (keys[slot] != pos && keys[slot] != ~0ull) slot = (slot + 1) & mask;
             uint32_t row;
-            if (keys[slot] == ~0ull) {
-                if (plan.unique.size() >= 0xffffffffull) return fail(DRM_EUNSUPPORTED, "more than 2^32 - 1 unique candidate windows");
-                row = (uint32_t)plan.unique.size();
-                keys[slot] = pos;
-                rows[slot] = row;
-                plan.unique.push_back(pos);
-            } else row = rows[slot];
+            if (direct) {
+                uint32_t &slot = row_of[(size_t)pos];
+                if (slot == 0) {
+                    if (plan.unique.size() >= 0xfffffffeull) return fail(DRM_EUNSUPPORTED, "more than 2^32 - 2 unique candidate windows");
+                    plan.unique.push_back(pos);
+                    slot = (uint32_t)plan.unique.size();
+                }
+                row = slot - 1;
+            } else {
+                uint64_t slot = ((pos * 0x9e3779b97f4a7c15ull) >> 20) & mask;
+                while (keys[slot] != pos && keys[slot] != ~0ull) slot = (slot + 1) & mask;
+                if (keys[slot] == ~0ull) {
+                    if (plan.unique.size() >= 0xffffffffull) return fail(DRM_EUNSUPPORTED, "more than 2^32 - 1 unique candidate windows");
+                    row = (uint32_t)plan.unique.size();
+                    keys[slot] = pos;
+                    rows[slot] = row;
+                    plan.unique.push_back(pos);
+                } else row = rows[slot];
+            }
             plan.map.push_back(row);
         }
     }

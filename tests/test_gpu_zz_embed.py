@@ -228,3 +228,21 @@ def test_tensor_core_form_against_fp32_kernels(monkeypatch, gold):
         print(f"tensor-core vs fp32 kernels: max abs diff {d_ab:.3g}; vs oracle {d_bo:.3g}")
         assert np.array_equal(b.view(np.uint32), b2.view(np.uint32))  # deterministic
         assert d_bo < TOL and d_ab < 5e-5
+
+
+@pytest.mark.parametrize("tps", ["11", "12", "21", "24"])
+def test_tensor_core_form_threads_per_sequence(monkeypatch, tps):
+    """The gate phase with 1 / 2 / 4 threads per sequence (DRM_EMBED_TC_TPS = layer 1, layer 2; default 22): same products, same
+    per-unit arithmetic, so the outputs are bit-identical to the default's."""
+    w = EO.random_weights(81)
+    g = np.random.default_rng(82)
+    seqs = _random_seqs(g, 300, 2, 200)
+    v = drm.Vectorizer(weights=w)
+    monkeypatch.setenv("DRM_EMBED_TC", "1")
+    monkeypatch.delenv("DRM_EMBED_TC_TPS", raising=False)
+    a = v.vectorize(seqs)
+    monkeypatch.setenv("DRM_EMBED_TC_TPS", tps)
+    b = v.vectorize(seqs)
+    v.close()
+    assert np.array_equal(a.view(np.uint32), b.view(np.uint32))
+    assert float(np.abs(b - EO.embed(seqs, w)).max()) < TOL

@@ -160,8 +160,11 @@ def test_product_selection_order_equals_oracle_heap_select():
             assert np.array_equal(drm.l2_select_host(d, k), L2.partial_sort_asc(d, k)), (n, k, ties)
 
 
-def test_product_plan_equals_oracle_bookkeeping():
+@pytest.mark.parametrize("table", ["direct", "hash"])
+def test_product_plan_equals_oracle_bookkeeping(table, monkeypatch):
+    """Both position tables of l2_plan (direct by position - the default below 2^29 positions - and open addressing)."""
     import deepreadmapper_b200 as drm
+    monkeypatch.setenv("DRM_L2_PLAN_TABLE", table)
     g = np.random.default_rng(7)
     n, k_in = 11, 9
     # dynamic, sparse
