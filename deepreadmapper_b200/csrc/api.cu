@@ -4,6 +4,7 @@
 #include "common.h"
 
 #include <algorithm>
+#include <atomic>
 #include <cstring>
 #include <chrono>
 #include <memory>
@@ -106,6 +107,8 @@ int open_ref(const char *bytes, int64_t len_bytes, int64_t len, int form, int re
     *out = nullptr;
     if (!bytes || len < 0 || ref_len <= 0 || n_dev < 1 || !devices) return fail(DRM_EINVAL, "bad reference arguments");
     drm_ref *r = new drm_ref();
+    static std::atomic<uint64_t> next_uid{1};
+    r->uid = next_uid.fetch_add(1);
     for (int i = 0; i < n_dev; ++i) {
         DeviceRef dr;
         dr.device = devices[i]; dr.form = form; dr.ref_len = ref_len; dr.len = len;
@@ -746,6 +749,10 @@ int drm_embedder_open_raw(const uint16_t *emb, int vocab, const uint16_t *W1, co
 void drm_embedder_close(drm_embedder *e)
 {
     if (!e) return;
+    if (e->wcache.emb) {
+        if (e->dev.device >= 0) cudaSetDevice(e->dev.device);
+        cudaFree(e->wcache.emb);
+    }
     embedder_free(e->dev);
     delete e;
 }
@@ -901,8 +908,24 @@ int drm_l2_rerank(drm_embedder *e, drm_ref *ref, int mode, const int64_t *neighb
     else bound = dr->len >= dr->ref_len ? 2ull * (uint64_t)(dr->len - dr->ref_len + 1) : 0;
     L2Plan plan;
     for (double &v : g_l2_ms) v = 0;
+    // Window cache: a window's embedding depends on its id alone, and every candidate id lies below `bound`.  Once a call's flat
+    // candidate list is as long as the reference has windows (one E. coli batch of 20 000 reads lists twice that), embedding ALL
+    // `bound` windows once - 0.5 s and 2.4 GB for E. coli - is cheaper than embedding each batch's share, and later calls on the
+    // same reference embed nothing at all: the kernels read candidate rows straight from the cache by window id, and the host
+    // plan skips its de-duplication pass.  Same values as the per-batch path (the embedder treats sequences independently).
+    // DRM_L2_CACHE_GB = budget (default 16, 0 = off); DRM_L2_CACHE_SHARE = flat candidates per window that trigger the build
+    // (default 1; tests: 0 = always).
+    double cache_gb = 16.0, share = 1.0;
+    if (const char *ev = getenv("DRM_L2_CACHE_GB")) cache_gb = atof(ev);
+    if (const char *ev = getenv("DRM_L2_CACHE_SHARE")) share = atof(ev);
+    const int decorate = mode == 0 ? 1 : 0;  // mode 0: ref_seqs hold '<' window '>' strings; find_sequence (1) and lookup-mode tables (2) give bare windows
+    drm_embedder::WindowCache &wc = e->wcache;
+    const bool cache_fits = bound > 0 && bound < 0xffffffffull && (double)bound * 512.0 <= cache_gb * 1073741824.0;
+    const bool cache_hit = cache_fits && wc.emb && wc.ref_uid == ref->uid && wc.decorate == decorate && wc.n == bound;
+    const double flat_est = (double)n * (double)std::min(mode == 1 ? k_clusters : k_in, k_in) * (double)(mode == 1 ? 2 * stride - 1 : stride);
+    const bool use_cache = cache_hit || (cache_fits && flat_est >= share * (double)bound);
     const auto t_plan = std::chrono::steady_clock::now();
-    int rc = l2_plan(mode == 2 ? 0 : mode, neighbors, n, k_in, stride, k, k_clusters, bound, plan);  // mode 2 = static bookkeeping, bare windows
+    int rc = l2_plan(mode == 2 ? 0 : mode, neighbors, n, k_in, stride, k, k_clusters, bound, plan, use_cache);  // mode 2 = static bookkeeping, bare windows
     if (rc != DRM_OK) return rc;
     g_l2_ms[0] = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_plan).count();
     const auto t_all = std::chrono::steady_clock::now();
@@ -928,6 +951,21 @@ int drm_l2_rerank(drm_embedder *e, drm_ref *ref, int mode, const int64_t *neighb
     // batch (default 8 M: <= 4 GB of embeddings + 0.1 GB of scratch).
     int64_t max_flat = 8ll << 20;
     if (const char *ev = getenv("DRM_L2_BATCH_CANDS")) max_flat = std::max<int64_t>(1, atoll(ev));
+    if (use_cache && !cache_hit) {
+        if (wc.emb) { cudaFree(wc.emb); wc = drm_embedder::WindowCache(); }
+        DRM_CUDA_TRY(cudaMalloc(reinterpret_cast<void **>(&wc.emb), (size_t)bound * 128 * sizeof(float)));
+        EmbedSource all;
+        all.mode = 1; all.cls = dr->data; all.form = dr->form; all.ref_n = dr->len; all.ref_len = dr->ref_len;
+        all.first_id = 0; all.id_step = 1; all.ids = nullptr; all.decorate = decorate;
+        DRM_CUDA_TRY(cudaEventRecord(ev_a, 0));
+        if ((rc = launch_embed(e->dev, all, 0, (int64_t)bound, wc.emb, 0)) != DRM_OK) { cudaFree(wc.emb); wc = drm_embedder::WindowCache(); return rc; }
+        DRM_CUDA_TRY(cudaEventRecord(ev_b, 0));
+        DRM_CUDA_TRY(cudaEventSynchronize(ev_b));
+        float mb = 0;
+        cudaEventElapsedTime(&mb, ev_a, ev_b);
+        g_l2_ms[1] += mb;
+        wc.ref_uid = ref->uid; wc.decorate = decorate; wc.n = bound;
+    }
     std::vector<int32_t> local_of((size_t)U, -1);   // global unique row -> row of this batch's embedding table
     std::vector<uint64_t> b_ids;
     std::vector<uint32_t> b_map, b_rows;
@@ -945,13 +983,18 @@ int drm_l2_rerank(drm_embedder *e, drm_ref *ref, int mode, const int64_t *neighb
         b_map.resize((size_t)fb);
         b_starts.resize((size_t)nb + 1);
         for (int64_t i = 0; i <= nb; ++i) b_starts[(size_t)i] = plan.starts[(size_t)(q0 + i)] - f0;
-        for (int64_t j = 0; j < fb; ++j) {
-            const uint32_t g = plan.map[(size_t)(f0 + j)];
-            int32_t l = local_of[g];
-            if (l < 0) { l = (int32_t)b_ids.size(); local_of[g] = l; b_ids.push_back(plan.unique[g]); b_rows.push_back(g); }
-            b_map[(size_t)j] = (uint32_t)l;
+        if (use_cache) {  // candidate rows = window ids into the cache: no per-batch table, nothing to embed
+            if (plan.direct_ids) std::memcpy(b_map.data(), plan.map.data() + f0, (size_t)fb * sizeof(uint32_t));
+            else for (int64_t j = 0; j < fb; ++j) b_map[(size_t)j] = (uint32_t)plan.unique[plan.map[(size_t)(f0 + j)]];
+        } else {
+            for (int64_t j = 0; j < fb; ++j) {
+                const uint32_t g = plan.map[(size_t)(f0 + j)];
+                int32_t l = local_of[g];
+                if (l < 0) { l = (int32_t)b_ids.size(); local_of[g] = l; b_ids.push_back(plan.unique[g]); b_rows.push_back(g); }
+                b_map[(size_t)j] = (uint32_t)l;
+            }
+            for (uint32_t g : b_rows) local_of[g] = -1;
         }
-        for (uint32_t g : b_rows) local_of[g] = -1;
         const int64_t ub = (int64_t)b_ids.size();
         if ((size_t)ub > cap_u || (size_t)fb > cap_f || (size_t)nb > cap_n) {  // grow (first batch sizes the rest: batches are cut to one budget)
             cap_u = std::max(cap_u, (size_t)ub + (size_t)ub / 8 + 16); cap_f = std::max(cap_f, (size_t)fb + 16); cap_n = std::max(cap_n, (size_t)nb + 16);
@@ -969,11 +1012,11 @@ int drm_l2_rerank(drm_embedder *e, drm_ref *ref, int mode, const int64_t *neighb
         EmbedSource src;
         src.mode = 1; src.cls = dr->data; src.form = dr->form; src.ref_n = dr->len; src.ref_len = dr->ref_len;
         src.ids = d_ids.as<unsigned long long>();
-        src.decorate = mode == 0 ? 1 : 0;  // mode 0: ref_seqs hold '<' window '>' strings; find_sequence (1) and lookup-mode tables (2) give bare windows
+        src.decorate = decorate;
         DRM_CUDA_TRY(cudaEventRecord(ev_a, 0));
         if (ub && (rc = launch_embed(e->dev, src, 0, ub, d_emb.as<float>(), 0)) != DRM_OK) return rc;
         DRM_CUDA_TRY(cudaEventRecord(ev_b, 0));
-        if ((rc = launch_l2_rerank(d_emb.as<float>(), d_map.as<uint32_t>(), d_starts.as<int64_t>(), d_q.as<float>(), nb, (int)ko, d_dist.as<float>(),
+        if ((rc = launch_l2_rerank(use_cache ? wc.emb : d_emb.as<float>(), d_map.as<uint32_t>(), d_starts.as<int64_t>(), d_q.as<float>(), nb, (int)ko, d_dist.as<float>(),
                                    d_idx.as<int64_t>(), d_od.as<float>(), d_or.as<uint32_t>(), d_cnt.as<int64_t>(), 0)) != DRM_OK) return rc;
         DRM_CUDA_TRY(cudaEventRecord(ev_c, 0));
         od.resize((size_t)(nb * ko)); orow.resize((size_t)(nb * ko)); cnt.resize((size_t)nb);
@@ -986,7 +1029,7 @@ int drm_l2_rerank(drm_embedder *e, drm_ref *ref, int mode, const int64_t *neighb
                 return fail(DRM_ENOTENOUGH, "Not enough candidates (" + std::to_string(-cnt[(size_t)q] - 1) + " < " + std::to_string(ko) + ") for query " + std::to_string(q0 + q));
             for (int64_t j = 0; j < ko; ++j) {
                 out_scores[*out_count] = od[(size_t)(q * ko + j)];
-                out_ids[*out_count] = b_ids[orow[(size_t)(q * ko + j)]];
+                out_ids[*out_count] = use_cache ? (uint64_t)orow[(size_t)(q * ko + j)] : b_ids[orow[(size_t)(q * ko + j)]];
                 ++*out_count;
             }
         }

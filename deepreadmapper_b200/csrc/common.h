@@ -206,11 +206,13 @@ struct L2Plan {
     std::vector<uint64_t> unique;        // window ids to embed (dynamic: find_sequence ids; static: rows of ref_seqs)
     std::vector<uint32_t> map;           // flat candidate list -> row of `unique`
     std::vector<int64_t> starts;         // n + 1 slice boundaries into the flat list, as the reference computes them
+    bool direct_ids = false;             // asked for by the caller (all window ids below 2^32, embeddings of every window at hand):
+                                         // `map` holds the window ids themselves, `unique` stays empty - no de-duplication pass
 };
 // mode 0 = static (bound = number of ref_seqs), 1 = dynamic (bound = genome length).  DRM_OK or an error with the
 // reference's message.
 int l2_plan(int mode, const int64_t *neighbors, int64_t n, int64_t k_in, int64_t stride, int64_t k, int64_t k_clusters,
-            uint64_t bound, L2Plan &plan);
+            uint64_t bound, L2Plan &plan, bool direct_ids = false);
 // libstdc++ std::partial_sort(idx, idx + k, idx + n, dist[a] < dist[b]) on the host (the code the kernel runs)
 void l2_select_host(const float *dist, int64_t n, int64_t k, int64_t *idx);
 // emb: unique windows' embeddings [U][128]; map/starts as in L2Plan (device copies); q: [n][128]; dist_scr / idx_scr: one
@@ -247,6 +249,7 @@ struct drm_index {
 
 struct drm_ref {
     std::vector<drm::DeviceRef> rep;
+    uint64_t uid = 0;  // process-unique, never reused: what caches of derived data key on (an address can be reused after a close)
 };
 
 // FASTQ reads parsed on the device (input_kernels.cu): one copy per replica.
@@ -263,5 +266,13 @@ struct drm_reads {
 
 struct drm_embedder {
     drm::DeviceEmbedder dev;
+    // drm_l2_rerank: embeddings of EVERY window id of one reference ([n][128] floats on dev.device), built the first time a call
+    // references a sizeable share of them and reused by later calls on the same reference (keyed on drm_ref::uid and the window form)
+    struct WindowCache {
+        uint64_t ref_uid = 0;
+        int decorate = -1;
+        uint64_t n = 0;
+        float *emb = nullptr;
+    } wcache;
 };
 

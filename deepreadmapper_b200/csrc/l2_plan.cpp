@@ -26,6 +26,16 @@ int expand_flat(const uint64_t *ids, int64_t n_ids, uint64_t stride, uint64_t bo
 {
     const uint64_t worst = (uint64_t)n_ids * (2 * stride - 1);  // every expanded position distinct
     plan.map.reserve((size_t)worst);
+    if (plan.direct_ids) {  // the caller has every window's embedding: the flat list carries the window ids, nothing to index
+        for (int64_t j = 0; j < n_ids; ++j) {
+            const uint64_t p = ids[j] * stride;
+            if (p >= bound) continue;
+            const uint64_t start = p >= stride - 1 ? p - stride + 1 : 0;
+            const uint64_t end = std::min(p + stride, bound);
+            for (uint64_t pos = start; pos < end; ++pos) plan.map.push_back((uint32_t)pos);
+        }
+        return DRM_OK;
+    }
     const char *tb = getenv("DRM_L2_PLAN_TABLE");  // "hash" forces the hashed table (A/B, tests)
     const bool direct = bound <= (1ull << 29) && !(tb && tb[0] == 'h');
     std::vector<uint32_t> row_of;          // direct: row + 1 of a position, 0 = not seen
@@ -76,10 +86,11 @@ int expand_flat(const uint64_t *ids, int64_t n_ids, uint64_t stride, uint64_t bo
 }  // namespace
 
 int l2_plan(int mode, const int64_t *neighbors, int64_t n, int64_t k_in, int64_t stride, int64_t k, int64_t k_clusters,
-            uint64_t bound, L2Plan &plan)
+            uint64_t bound, L2Plan &plan, bool direct_ids)
 {
     plan = L2Plan();
     plan.n = n;
+    plan.direct_ids = direct_ids && bound < 0xffffffffull && !(mode != 1 && stride == 1);  // (the static 1-to-1 lookup has no index to skip)
     if (n <= 0 || k_in <= 0 || stride < 1 || k < 0 || k_clusters < 0) return fail(DRM_EINVAL, "bad arguments to the L2 rerank");
     int64_t per_slice;  // flat candidates the reference attributes to one query
     std::vector<uint64_t> ids;

@@ -13,9 +13,18 @@ import pytest
 pytestmark = pytest.mark.gpu
 
 
-def test_l2_rerank_stage_against_oracle():
+@pytest.mark.parametrize("cache", ["default", "always", "off"])
+def test_l2_rerank_stage_against_oracle(cache):
+    """With the window-embedding cache forced (DRM_L2_CACHE_SHARE=0: every call builds or reuses it; the check switches between
+    references and between decorated / bare windows on one embedder, so the cache key is exercised), under the default rule,
+    and without it (DRM_L2_CACHE_GB=0: every batch embeds its own windows)."""
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-    r = subprocess.run([sys.executable, os.path.join(root, "tests", "l2_gpu_check.py")], capture_output=True, text=True, timeout=300)
+    env = dict(os.environ)
+    if cache == "always":
+        env["DRM_L2_CACHE_SHARE"] = "0"
+    elif cache == "off":
+        env["DRM_L2_CACHE_GB"] = "0"
+    r = subprocess.run([sys.executable, os.path.join(root, "tests", "l2_gpu_check.py")], capture_output=True, text=True, timeout=300, env=env)
     print(r.stdout[-2000:])
     print(r.stderr[-4000:])
     assert r.returncode == 0 and "device == oracle" in r.stdout, r.stderr[-2000:]
