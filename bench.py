@@ -595,6 +595,9 @@ def realistic_section(args, genome, ref, local, hbm_peak):
     sec = {"workload": "same genome and reads as the headline, embedded by the reference's network (weights of models/finetuned_sgn33-new-a-Apr6.xml from "
                        "tests/golden/embedder_golden.npz) on the device; index by the GPU builder; EF = K = 128",
            "n_vectors": n_win, "reads": n, "windows_embed_s": embed_s, "index_build_s": build_s, "reads_embed_s": q_embed_s,
+           "embedder": {"form": "fp32 CUDA-core kernels" if os.environ.get("DRM_EMBED_TC") == "0" else "tensor cores (tcgen05.mma + TMEM; DESIGN.md 4.9)",
+                        "windows_per_s": (n_win / embed_s) if embed_s > 0 else None, "reads_per_s": n / q_embed_s if q_embed_s > 0 else None},
+           "reads_per_s_with_embedding": n / ((search_ms + sw_ms) / 1e3 + q_embed_s),
            "stages_ms": {"search": search_ms, "sw_rerank": sw_ms}, "reads_per_s": n / ((search_ms + sw_ms) / 1e3),
            "kernel_counters_per_read": {"nhops0": float(cnt[0]), "nhops_up": float(cnt[1]), "ndis_eval": float(cnt[2])},
            "search_top1_is_planted_position": float((I[:, 0] >> 1 == pos_t).mean()),

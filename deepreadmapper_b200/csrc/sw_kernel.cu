@@ -854,6 +854,28 @@ __global__ void expand_kernel(const RerankDev p)
     if (p.cells) atomicAdd(p.cells, (u64)nc * (u64)p.ref_len * (u64)(p.q_off[r + 1] - p.q_off[r]));
 }
 
+// Stream-ordered scratch that is returned to the pool on every way out of a launch function (an early DRM_CUDA_TRY return included).
+struct AsyncScratch {
+    cudaStream_t stream;
+    void *p[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+    int n = 0;
+    explicit AsyncScratch(cudaStream_t s) : stream(s) {}
+    AsyncScratch(const AsyncScratch &) = delete;
+    AsyncScratch &operator=(const AsyncScratch &) = delete;
+    template <class T> cudaError_t alloc(T **out, size_t bytes)
+    {
+        void *q = nullptr;
+        const cudaError_t e = cudaMallocAsync(&q, bytes ? bytes : 16, stream);
+        if (e == cudaSuccess) p[n++] = q;
+        *out = static_cast<T *>(q);
+        return e;
+    }
+    ~AsyncScratch()
+    {
+        for (int i = 0; i < n; ++i) cudaFreeAsync(p[i], stream);
+    }
+};
+
 }  // namespace
 
 int launch_classify(const uint8_t *raw, uint8_t *cls, int64_t n, int *has_other_dev, cudaStream_t stream)
@@ -871,12 +893,12 @@ int launch_sw_pairs(const char *a_flat, const int64_t *a_off, const char *b_flat
 {
     if (n <= 0) return DRM_OK;
     long long threads = n < 148LL * 1024 ? (n + 127) / 128 * 128 : 148LL * 1024;
+    AsyncScratch scratch(stream);
     int *H = nullptr;
-    DRM_CUDA_TRY(cudaMallocAsync(&H, (size_t)threads * (size_t)(max_len_b + 1) * sizeof(int), stream));
+    DRM_CUDA_TRY(scratch.alloc(&H, (size_t)threads * (size_t)(max_len_b + 1) * sizeof(int)));
     FlatPairs src{a_flat, reinterpret_cast<const long long *>(a_off), b_flat, reinterpret_cast<const long long *>(b_off)};
     sw_generic_kernel<FlatPairs><<<(unsigned)(threads / 128), 128, 0, stream>>>(src, n, H, nullptr, scores);
     DRM_CUDA_TRY(cudaGetLastError());
-    DRM_CUDA_TRY(cudaFreeAsync(H, stream));
     return DRM_OK;
 }
 
@@ -909,12 +931,13 @@ int launch_rerank(const DeviceRef &ref, const RerankArgs &a, cudaStream_t stream
     const long long batch_max = 131072;
     short *scr_scores = nullptr; u64 *scr_ids = nullptr; int *ncand_tmp = nullptr; int *H = nullptr;
     const long long B = a.n < batch_max ? a.n : batch_max;
-    DRM_CUDA_TRY(cudaMallocAsync(&scr_scores, (size_t)B * C * sizeof(short), stream));
-    DRM_CUDA_TRY(cudaMallocAsync(&scr_ids, (size_t)B * C * sizeof(u64), stream));
-    if (!a.n_cands) DRM_CUDA_TRY(cudaMallocAsync(&ncand_tmp, (size_t)a.n * sizeof(int), stream));
+    AsyncScratch scratch(stream);  // freed (stream-ordered) on every return below
+    DRM_CUDA_TRY(scratch.alloc(&scr_scores, (size_t)B * C * sizeof(short)));
+    DRM_CUDA_TRY(scratch.alloc(&scr_ids, (size_t)B * C * sizeof(u64)));
+    if (!a.n_cands) DRM_CUDA_TRY(scratch.alloc(&ncand_tmp, (size_t)a.n * sizeof(int)));
     int *n_cands = a.n_cands ? a.n_cands : ncand_tmp;
     const long long gthreads = 148LL * 1024;
-    if (!fast) DRM_CUDA_TRY(cudaMallocAsync(&H, (size_t)gthreads * (size_t)(a.max_qlen + 1) * sizeof(int), stream));
+    if (!fast) DRM_CUDA_TRY(scratch.alloc(&H, (size_t)gthreads * (size_t)(a.max_qlen + 1) * sizeof(int)));
     // Kernel variant: 0 = PRMT lookup; query-profile kernels, one row per iteration: 1 = clamps on the alu
     // pipe (integer form), 2 = clamps on the fma pipe (fp16 form), 3 / 4 = every 2nd / 4th clamp on the alu pipe; two rows
     // per iteration: 10 / 11 / 12 / 14 = none / every / every 2nd / every 4th clamp of the second row on the alu pipe.
@@ -936,7 +959,7 @@ int launch_rerank(const DeviceRef &ref, const RerankArgs &a, cudaStream_t stream
                          (size_t)take * sizeof(u64) + (size_t)(take + 1) * sizeof(int) + 16;
     int *fb = nullptr;  // [0] = count, [1..] = reads handed back by the profile kernel
     if (fast && variant != 0) {
-        DRM_CUDA_TRY(cudaMallocAsync(&fb, (size_t)(B + 1) * sizeof(int), stream));
+        DRM_CUDA_TRY(scratch.alloc(&fb, (size_t)(B + 1) * sizeof(int)));
     }
     if (a.k > 0) {
         DRM_CUDA_TRY(cudaMemsetAsync(a.out_scores, 0, (size_t)a.n * a.k * sizeof(int32_t), stream));
@@ -1010,11 +1033,6 @@ int launch_rerank(const DeviceRef &ref, const RerankArgs &a, cudaStream_t stream
             DRM_CUDA_TRY(cudaGetLastError());
         }
     }
-    DRM_CUDA_TRY(cudaFreeAsync(scr_scores, stream));
-    DRM_CUDA_TRY(cudaFreeAsync(scr_ids, stream));
-    if (ncand_tmp) DRM_CUDA_TRY(cudaFreeAsync(ncand_tmp, stream));
-    if (H) DRM_CUDA_TRY(cudaFreeAsync(H, stream));
-    if (fb) DRM_CUDA_TRY(cudaFreeAsync(fb, stream));
     return DRM_OK;
 }
 
