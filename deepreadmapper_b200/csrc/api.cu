@@ -923,7 +923,16 @@ int drm_l2_rerank(drm_embedder *e, drm_ref *ref, int mode, const int64_t *neighb
     const bool cache_fits = bound > 0 && bound < 0xffffffffull && (double)bound * 512.0 <= cache_gb * 1073741824.0;
     const bool cache_hit = cache_fits && wc.emb && wc.ref_uid == ref->uid && wc.decorate == decorate && wc.n == bound;
     const double flat_est = (double)n * (double)std::min(mode == 1 ? k_clusters : k_in, k_in) * (double)(mode == 1 ? 2 * stride - 1 : stride);
-    const bool use_cache = cache_hit || (cache_fits && flat_est >= share * (double)bound);
+    bool use_cache = cache_hit || (cache_fits && flat_est >= share * (double)bound && !(mode == 1 && stride == 1));
+    if (use_cache && !cache_hit) {  // room for the table first: without it the call takes the per-batch path, as before
+        DRM_CUDA_TRY(cudaSetDevice(e->dev.device));
+        if (wc.emb) { cudaFree(wc.emb); wc = drm_embedder::WindowCache(); }
+        float *fresh = nullptr;
+        if (cudaMalloc(reinterpret_cast<void **>(&fresh), (size_t)bound * 128 * sizeof(float)) != cudaSuccess) {
+            cudaGetLastError();
+            use_cache = false;
+        } else wc.emb = fresh;  // owned by the handle from here on; its key is set once it is filled
+    }
     const auto t_plan = std::chrono::steady_clock::now();
     int rc = l2_plan(mode == 2 ? 0 : mode, neighbors, n, k_in, stride, k, k_clusters, bound, plan, use_cache);  // mode 2 = static bookkeeping, bare windows
     if (rc != DRM_OK) return rc;
@@ -952,8 +961,6 @@ int drm_l2_rerank(drm_embedder *e, drm_ref *ref, int mode, const int64_t *neighb
     int64_t max_flat = 8ll << 20;
     if (const char *ev = getenv("DRM_L2_BATCH_CANDS")) max_flat = std::max<int64_t>(1, atoll(ev));
     if (use_cache && !cache_hit) {
-        if (wc.emb) { cudaFree(wc.emb); wc = drm_embedder::WindowCache(); }
-        DRM_CUDA_TRY(cudaMalloc(reinterpret_cast<void **>(&wc.emb), (size_t)bound * 128 * sizeof(float)));
         EmbedSource all;
         all.mode = 1; all.cls = dr->data; all.form = dr->form; all.ref_n = dr->len; all.ref_len = dr->ref_len;
         all.first_id = 0; all.id_step = 1; all.ids = nullptr; all.decorate = decorate;

@@ -2,7 +2,8 @@
 // bidirectional GRU (hidden 64) -> 128-d vector = [layer-2 forward final state | layer-2 backward final state].
 // Replaces Vectorizer::vectorize (src/inference/vectorize.cpp:34-141: Preprocessor::preprocess src/inference/preprocess.cpp:20-42,
 // prepareBatch :345-366, OpenVINO inference of models/finetuned_sgn33-new-a-Apr6.xml src/inference/fast_model.cpp:3-224).
-// CPU restatement: oracle/embed_oracle.py.  fp32 arithmetic on the model's fp16-exact weights.
+// CPU restatement: oracle/embed_oracle.py.  Two forms of the recurrences: the tensor-core form further down (tcgen05.mma + TMEM,
+// gru_tc_kernel; the default) and the fp32 CUDA-core kernels described next (DRM_EMBED_TC=0, and weights that are not fp16 numbers).
 //
 // Work per sequence (T = 123 steps): layer-1 recurrence 2 x T x 192 x 64 FMA, layer-2 input projection
 // 2 x T x 192 x 128, layer-2 recurrence 2 x T x 192 x 64  = 12.1 M FMA; the layer-1 input projection is a table
@@ -316,10 +317,13 @@ template <class T> int upload(const std::vector<T> &h, T **d)
 //     values in (-1, 1): they enter as hi + lo with hi = fp16(h), lo = fp16(h - hi), two products accumulated into the same
 //     TMEM columns - a 22-bit significand, absolute error below 2^-24 per term; measured against the fp32 kernels in
 //     tests/test_gpu_zz_embed.py.
-//   * Layer 1: K = 64 (R1 . h); the input projection is the per-token table P1, gathered in the epilogue.  N = 192.
-//   * Layer 2: K = 128 + 64: [y1_t | h].  The input projection W2 . y1_t is FUSED into the step's product, so X2 (189 KB per
-//     sequence) is never written: rows z, r take the whole K (N = 128); the candidate gate keeps its two halves apart because
-//     r multiplies only the recurrent half: rows h over K = 0..127 (N = 64) and over K = 128..191 (N = 64) -> 256 columns.
+//   * A = [x_t | h], B = [W | R].  Layer 1: x_t = the token's embedding row (64 fp16 numbers, exact: the table is f16 in the IR),
+//     copied from a 97-row copy of the table in shared memory, K = 64 + 64 - the tensor core does W1 . emb[token], the fp32
+//     kernels' per-token table P1 and its gather are not used.  Layer 2: x_t = y1_t (hi | lo), K = 128 + 64: the input projection
+//     W2 . y1_t is FUSED into the step's product, X2 (189 KB per sequence) is never written.
+//   * Accumulator columns of a step: z 0..63 | r 64..127 (W x + R h summed by the tensor core) | the candidate gate's recurrent
+//     half 128..191 | its input half 192..255 (apart because r multiplies only the recurrent one).  Issued as few, wide products
+//     (N = 192 / 256); see the issue_x / issue_h lambdas.
 //   * Operand layout in shared memory (K-major, no swizzle; the canonical UMMA "interleave" layout): 16-byte chunk
 //     (row r, k-group g = k / 8) at g * rows * 16 + r * 16  ->  8 rows x 16 B core matrices are contiguous (SBO = 128 B),
 //     consecutive k-groups are rows * 16 B apart (LBO).  Thread s writes chunk (s, g): consecutive threads, consecutive
