@@ -483,7 +483,7 @@ def run_ours(args):
     ach = bytes_per_read * n / (search_ms / 1e3) / 1e9
     # DRAM traffic per launch: dram__bytes_read.sum + dram__bytes_write.sum of one `ncu --set full` capture of each kernel on this
     # workload at 131072 reads (profiles/r2_ncu_search_exact_v4.txt, r2_ncu_sw_final.txt), scaled to this launch's read count
-    NCU_DRAM_BYTES_PER_READ = {"search": (11.571258e9 + 202.479e6) / 131072, "sw": (163.482e6 + 126.715e6) / 131072}
+    NCU_DRAM_BYTES_PER_READ = {"search": (11.571258e9 + 202.479e6) / 131072, "sw": (162.925e6 + 130.203e6) / 131072}
     line["roofline_search"] = {"kernel": "hnswpq_search_exact_kernel", "bound": "hbm", "achieved": ach, "peak": hbm_peak, "unit": "GB/s",
                                "frac": ach / hbm_peak, "traffic": NCU_DRAM_BYTES_PER_READ["search"] * n, "peak_source": peak_src,
                                "traffic_source": "ncu capture at 131072 reads, scaled by reads (profiles/r2_ncu_search_exact_v4.txt): 3.3 x the algorithmic bytes = fused 384-byte rows (2.0 x) + gated accept-time L2 prefetch (profiles/r2_ab_search_prefetch_gate.txt)",

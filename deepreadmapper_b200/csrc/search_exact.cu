@@ -608,6 +608,12 @@ int launch_exact_tfvc(const ExactParams &p, int device, cudaStream_t stream)
     DRM_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, XWARPS * 32, smem));
     DRM_CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device));
     if (per_sm < 1) return fail(DRM_EUNSUPPORTED, "search kernel does not fit on an SM with these parameters");
+    // DRM_SEARCH_CTAS_PER_SM: fewer persistent CTAs per SM than fit, so that another kernel's CTAs (the SW rerank of the previous
+    // chunk, on another stream) can share the SMs with this one (tools/overlap_probe.py)
+    if (const char *ev = getenv("DRM_SEARCH_CTAS_PER_SM")) {
+        const int cap_sm = atoi(ev);
+        if (cap_sm >= 1 && cap_sm < per_sm) per_sm = cap_sm;
+    }
     long long want = (p.n + XWARPS - 1) / XWARPS;
     long long grid = (long long)per_sm * sms;
     if (want < grid) grid = want;

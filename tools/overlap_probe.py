@@ -23,6 +23,7 @@ def main():
     ap.add_argument("--reads", type=int, default=1_000_000)
     ap.add_argument("--chunks", type=int, nargs="+", default=[1, 4, 8, 16])
     ap.add_argument("--reps", type=int, default=3)
+    ap.add_argument("--caps", type=int, nargs="*", default=[1, 2, 3])
     ap.add_argument("--out", default="gpurun_out/overlap_probe.json")
     a = ap.parse_args()
     args = argparse.Namespace(genome_bases=bench.GENOME_BASES, efc=200, builder="gpu", cache=os.environ.get("DRM_CACHE", "/tmp/drm_b200_cache"))
@@ -40,19 +41,25 @@ def main():
     dI = torch.empty((n, K), dtype=torch.int64, device="cuda")
     dS = torch.empty((n, K), dtype=torch.int32, device="cuda")
     dIds = torch.empty((n, K), dtype=torch.int64, device="cuda")
-    s1, s2 = torch.cuda.Stream(), torch.cuda.Stream()
+    s1, s2 = torch.cuda.Stream(priority=-1), torch.cuda.Stream()  # the search stream has the higher priority: its (capped) grid gets its SM slots first
     res = {}
     ref_out = None
     for C in a.chunks:
         bounds = [(n * c // C, n * (c + 1) // C) for c in range(C)]
-        for mode in ("serial", "overlap"):
+        for mode in ("serial", "overlap") + tuple(f"overlap_cap{c}" for c in a.caps if C > 1):
+            # overlap_capN: the persistent search kernel takes only N CTAs per SM (5 fit), so the SW CTAs of the previous chunk stay resident beside it
+            if mode.startswith("overlap_cap"):
+                os.environ["DRM_SEARCH_CTAS_PER_SM"] = mode[len("overlap_cap"):]
+            else:
+                os.environ.pop("DRM_SEARCH_CTAS_PER_SM", None)
+
             def run():
                 evs = []
                 for (c0, c1) in bounds:
                     ssearch = s1
-                    srer = s2 if mode == "overlap" else s1
+                    srer = s2 if mode != "serial" else s1
                     ix.search_device(dQ[c0:c1].data_ptr(), c1 - c0, K, EF, dD[c0:c1].data_ptr(), dI[c0:c1].data_ptr(), 0, ssearch.cuda_stream)
-                    if mode == "overlap":
+                    if mode != "serial":
                         e = torch.cuda.Event()
                         e.record(ssearch)
                         srer.wait_event(e)
@@ -64,7 +71,7 @@ def main():
             t0.record(s1)
             for _ in range(a.reps):
                 run()
-            if mode == "overlap":
+            if mode != "serial":
                 e = torch.cuda.Event()
                 e.record(s2)
                 s1.wait_event(e)
@@ -76,7 +83,7 @@ def main():
                 ref_out = out
             same = all(np.array_equal(x, y) for x, y in zip(ref_out, out))
             res[f"chunks{C}_{mode}"] = {"ms": ms, "reads_per_s": n / (ms / 1e3), "identical": bool(same)}
-            print(f"chunks={C:3d} {mode:8s} {ms:8.2f} ms  {n / (ms / 1e3) / 1e6:.3f} M reads/s  identical={same}", flush=True)
+            print(f"chunks={C:3d} {mode:13s} {ms:8.2f} ms  {n / (ms / 1e3) / 1e6:.3f} M reads/s  identical={same}", flush=True)
     os.makedirs(os.path.dirname(a.out), exist_ok=True)
     json.dump(res, open(a.out, "w"), indent=1)
 
