@@ -280,9 +280,11 @@ __device__ __forceinline__ void c_heap_pop(uint2 *C2, int k, int lane)
     for (int j = 1; j <= DEPTH; ++j) {
         if ((i << 1) <= k) {
             unsigned w = nB[0];
+            if (j > 5) {  // a node at depth j - 1 <= 4 is one of the first 31: its bit is in word 0 (j is a compile-time constant here)
 #pragma unroll
-            for (int t = 1; t < NB; ++t)
-                if (((i - 1) >> 5) == t) w = nB[t];
+                for (int t = 1; t < NB; ++t)
+                    if (((i - 1) >> 5) == t) w = nB[t];
+            }
             i = (i << 1) + (int)((w >> ((i - 1) & 31)) & 1u);
             if (lane == j) mine = i;
             L = j;
