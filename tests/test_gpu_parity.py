@@ -204,10 +204,10 @@ def mid_index(tmp_path_factory):
     return p, synth.embed_reads(reads), ids
 
 
-@pytest.fixture(params=["exact", "exact_vis1024", "exact_novis", "exact_ra", "exact_nopfa", "exact_pfa_all", "exact_tma", "reg", "reg_vis1024", "reg_novis", "smem", "pair"])
+@pytest.fixture(params=["exact", "exact_vis1024", "exact_novis", "exact_ra", "exact_nopfa", "exact_pfa_all", "exact_tma", "exact_cap2", "reg", "reg_vis1024", "reg_novis", "smem", "pair"])
 def search_variant(request, monkeypatch):
     """exact* = the default kernel (search_exact.cu: FAISS's own tie behaviour, oracle tie_rule 0) with the 512- / 1024-slot
-    visited cache or none, with the register read-ahead, without the accept-time L2 prefetch / with the ungated one, with bulk-copy (TMA) row staging; reg* / smem / pair = the
+    visited cache or none, with the register read-ahead, without the accept-time L2 prefetch / with the ungated one, with bulk-copy (TMA) row staging, with a capped grid; reg* / smem / pair = the
     canonical-order kernels of search_kernel.cu (oracle tie_rule 1).  Each must return its oracle's bits."""
     v = request.param
     monkeypatch.setenv("DRM_SEARCH_KERNEL", v if v in ("smem", "pair") else "reg" if v.startswith("reg") else "exact")
@@ -215,6 +215,10 @@ def search_variant(request, monkeypatch):
     monkeypatch.setenv("DRM_SEARCH_RA", "1" if v == "exact_ra" else "0")
     monkeypatch.setenv("DRM_SEARCH_PFA", "0" if v == "exact_nopfa" else "1" if v == "exact_pfa_all" else "2")
     monkeypatch.setenv("DRM_SEARCH_TMA", "1" if v == "exact_tma" else "0")
+    if v == "exact_cap2":  # two persistent CTAs per SM instead of the five that fit (the grid used when the SW rerank shares the SMs)
+        monkeypatch.setenv("DRM_SEARCH_CTAS_PER_SM", "2")
+    else:
+        monkeypatch.delenv("DRM_SEARCH_CTAS_PER_SM", raising=False)
     return v
 
 
