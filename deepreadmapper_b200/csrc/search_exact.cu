@@ -61,6 +61,7 @@ struct ExactParams {
     int readahead;        // 1: read the row of the runner-up candidate into registers while this row is processed
     int prefetch_accept;  // 1: L2-prefetch the row of every vertex accepted into the candidate heap; 1 + s: only of those in the lowest
                           //    2^-s of the [popped distance, heap root] interval
+    int prefetch_l1;      // 1: the accept-time prefetch targets L1 instead of L2 (DRM_SEARCH_PFL1, A/B)
     int tma;              // 1: rows arrive through the bulk-copy engine (cp.async.bulk + mbarrier) into a per-warp staging buffer,
                           //    and the accept-time prefetch is one cp.async.bulk.prefetch.L2 instead of one prefetch per line
     int row_stage_bytes;  // per-warp staging: row bytes rounded to 16, + 16 for the mbarrier (0 when tma is off)
@@ -567,7 +568,10 @@ __global__ void __launch_bounds__(XWARPS * 32, 5) hnswpq_search_exact_kernel(con
                     }
                 } else if (p.prefetch_accept && lane < 3 && kd <= pf_thr) {
                     const uint8_t *prow = p.rows0 + (size_t)kid * p.row0_bytes + lane * 128;
-                    if (lane * 128 < p.row0_bytes) asm volatile("prefetch.global.L2 [%0];" ::"l"(prow));
+                    if (lane * 128 < p.row0_bytes) {
+                        if (p.prefetch_l1) asm volatile("prefetch.global.L1 [%0];" ::"l"(prow));
+                        else asm volatile("prefetch.global.L2 [%0];" ::"l"(prow));
+                    }
                 }
 #endif
             }
@@ -699,6 +703,8 @@ int launch_search_exact_ex(const DeviceIndex &dx, const float *q_dev, int64_t n,
                                              // L2 prefetch beats the register read-ahead, and the ungated one costs 20 % more DRAM traffic for nothing
     if (const char *e = getenv("DRM_SEARCH_RA")) p.readahead = atoi(e) != 0;
     if (const char *e = getenv("DRM_SEARCH_PFA")) p.prefetch_accept = atoi(e) < 0 ? 0 : atoi(e) > 8 ? 8 : atoi(e);
+    p.prefetch_l1 = 0;
+    if (const char *e = getenv("DRM_SEARCH_PFL1")) p.prefetch_l1 = atoi(e) != 0;
     p.tma = 0;
     if (const char *e = getenv("DRM_SEARCH_TMA")) p.tma = atoi(e) != 0;
     if (p.row0_bytes % 16) p.tma = 0;  // the bulk-copy engine moves multiples of 16 bytes
