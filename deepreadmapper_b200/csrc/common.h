@@ -179,7 +179,7 @@ struct DeviceEmbedder {
     uint16_t *emb16 = nullptr;  // [97][64]         the embedding rows the tokeniser can select
     float *bias1 = nullptr;     // [2][192 + 64]    input biases | recurrent bias of the candidate gate, per direction
     float *bias2 = nullptr;     // [2][192 + 64]
-    uint16_t *Y1h = nullptr;    // [chunk_tc][max_len][hi 128 | lo 128] layer-1 states as fp16 pairs
+    uint16_t *Y1h = nullptr;    // [chunk_tc / 128][max_len][hi | lo][16 k-groups][128 rows][8 halves]: layer-1 states as the next layer's operand images
     int64_t chunk_tc = 0;
     bool tc_exact = false;      // every recurrent weight is an fp16 number (true for the reference's IR): the tensor-core form is exact in B
 };

@@ -20,6 +20,7 @@
 #include <cuda_fp16.h>
 #endif
 
+#include <cstdio>
 #include <cstdlib>
 #include <cstring>
 
@@ -328,8 +329,8 @@ template <class T> int upload(const std::vector<T> &h, T **d)
 //     (row r, k-group g = k / 8) at g * rows * 16 + r * 16  ->  8 rows x 16 B core matrices are contiguous (SBO = 128 B),
 //     consecutive k-groups are rows * 16 B apart (LBO).  Thread s writes chunk (s, g): consecutive threads, consecutive
 //     16-byte words, no bank conflicts.
-//   * Layer 1 hands its states to layer 2 already split: Y1h[seq][t][hi 128 | lo 128] halves (512 B per step, the same bytes
-//     as fp32 states).
+//   * Layer 1 hands its states to layer 2 already split into hi | lo halves AND already in the operand layout: Y1h is the A-operand
+//     image of every (tile of 128 sequences, step), 64 KB each - the bytes of the fp32 states; layer 2 copies images, it gathers nothing.
 constexpr int TC_M = 128;                 // sequences per CTA
 constexpr int TC_K1 = EH + EH, TC_K2 = 2 * EH + EH;  // [x_t | h]: layer 1 x = the token embedding (64), layer 2 x = y1_t (128)
 constexpr int TC_COLS1 = 256;             // TMEM columns per CTA, layer 1 (192 used; two CTAs per SM)
@@ -402,9 +403,9 @@ template <int LAYER> struct TcLayout {
     static constexpr int K = KX + EH;
     static constexpr int KG = K / 8, KGX = KX / 8;
     static constexpr int AL_H0 = LAYER == 1 ? 0 : KGX;          // k-group of the state inside Al
-    // weights: the input half Bx [KX/8][BX_ROWS][16 B] (layer 2: rows z, r, 64 ZERO rows, h - one N = 256 product per k-step writes
-    // xz, xr, clears the h-recurrent columns and writes xh), then the recurrent half Bh [8][192][16 B] (rows z, r, h: one N = 192 product)
-    static constexpr int BX_ROWS = LAYER == 1 ? EG : EG + EH;
+    // weights: the input half Bx [KX/8][192][16 B] with its rows in the order h, z, r (one N = 192 product per k-step lands xh | xz | xr on
+    // columns 0..191), then the recurrent half Bh [8][192][16 B] with rows z, r, h (one N = 192 product lands on columns 64..255)
+    static constexpr int BX_ROWS = EG;
     static constexpr int BX_BYTES = KGX * BX_ROWS * 16, BH_BYTES = (EH / 8) * EG * 16;
     static constexpr int B_BYTES = BX_BYTES + BH_BYTES;
     static constexpr int AH_BYTES = KG * TC_M * 16;
@@ -419,14 +420,20 @@ template <int LAYER> struct TcLayout {
 // TPS = threads per sequence: 1 (128 threads) or 2 (256 threads: warps w and w + 4 read the same 32 TMEM lanes - the hardware
 // ties a warp to lanes 32 (w % 4) .. + 31 - and each owns 32 of the 64 hidden units, so the gate phase has twice the warps to hide
 // the SFU and TMEM latencies behind).
-template <int LAYER, int TPS>
+template <int LAYER, int TPS, bool PROF = false>
 __global__ void __launch_bounds__(TC_M * TPS, LAYER == 1 ? 2 : 1)
 gru_tc_kernel(const SrcDev src, const long long first, const long long n, const int T, const uint4 *__restrict__ emb_g,
               const uint4 *__restrict__ Bw_g, const float *__restrict__ bias_g, const __half *__restrict__ Y1h_in,
-              __half *__restrict__ Y1h_out, float *__restrict__ out)
+              __half *__restrict__ Y1h_out, float *__restrict__ out, unsigned long long *__restrict__ phase_clk)
 {
     using L = TcLayout<LAYER>;
     constexpr int NT = TC_M * TPS;
+    // phase_clk != nullptr (DRM_EMBED_TC_PHASES=1, profiling only): thread 0 of CTA 0 sums the clocks it spends per step in
+    // 0 staging + barrier, 1 issuing the products, 2 waiting for them, 3 restaging the next input (layer 2), 4 the gate phase
+    unsigned long long pc[5] = {0, 0, 0, 0, 0};
+    const bool prof = PROF && phase_clk != nullptr && blockIdx.x == 0 && threadIdx.x == 0;  // (a separate instantiation: the counters cost registers)
+    long long tprev = prof ? clock64() : 0;
+#define TC_PHASE(i) do { if (prof) { const long long tn = clock64(); pc[i] += (unsigned long long)(tn - tprev); tprev = tn; } } while (0)
     constexpr int UNITS = EH / TPS;  // hidden units per thread
     constexpr int KSX = L::KX / 16, KS = L::K / 16;  // products (K = 16 each) of the input half, of the whole step
     extern __shared__ __align__(1024) unsigned char tsm[];
@@ -475,27 +482,24 @@ gru_tc_kernel(const SrcDev src, const long long first, const long long n, const 
     const unsigned ah_s = smem_u32(Ah), al_s = smem_u32(Al), bw_s = smem_u32(Bw);
     constexpr unsigned A_LBO = TC_M * 16, BX_LBO = L::BX_ROWS * 16, BH_LBO = EG * 16, SBO = 128;
     const unsigned bh_s = bw_s + L::BX_BYTES;
-    // Accumulator columns of a set: z 0..63 | r 64..127 | h recurrent 128..191 | h input 192..255.  A tcgen05.mma of this shape
-    // (M = 128, K = 16) occupies the tensor pipe for ~190 clocks whether N is 64 or 128 (ncu: hmma cycles per product), so the step
-    // is issued as FEW, WIDE products.
-    constexpr unsigned idesc_256 = umma_idesc(TC_M, 4 * EH), idesc_192 = umma_idesc(TC_M, 3 * EH), idesc_128 = umma_idesc(TC_M, 2 * EH),
-                       idesc_64 = umma_idesc(TC_M, EH);
+    // Accumulator columns of a set: h input (xh) 0..63 | z 64..127 | r 128..191 | h recurrent 192..255.  The input half's rows are
+    // stored h, z, r and the recurrent half's z, r, h, so EACH half is one N = 192 product per k-step onto a contiguous column range
+    // (0..191 and 64..255) and the two overlap exactly on z and r, where W x and R h are to be summed.  (A tcgen05.mma of this shape
+    // - M = 128, K = 16 - keeps the tensor pipe busy in proportion to N and costs issue / completion latency per instruction: few,
+    // wide products, and no padding columns.)  Only the step's first recurrent product is split in two: z, r accumulate onto the
+    // input half's result while the h-recurrent columns start from zero.
+    constexpr unsigned idesc_192 = umma_idesc(TC_M, 3 * EH), idesc_128 = umma_idesc(TC_M, 2 * EH), idesc_64 = umma_idesc(TC_M, EH);
+    constexpr unsigned COL_XH = 0, COL_Z = EH, COL_R = 2 * EH, COL_HN = 3 * EH;
     // input half of a step into accumulator set dcol
     auto issue_x = [&](unsigned dcol) {
 #pragma unroll
         for (int half = 0; half < (LAYER == 1 ? 1 : 2); ++half)  // layer 1's input is exact in fp16: no lo half
 #pragma unroll
-            for (int ks = 0; ks < KSX; ++ks) {
-                const unsigned long long ad = umma_desc((half ? al_s : ah_s) + ks * 2 * A_LBO, A_LBO, SBO);
-                if (LAYER == 2) {  // rows z, r, zero, h -> all 256 columns; the first product of the step overwrites
-                    umma_f16(tmem + dcol, ad, umma_desc(bw_s + ks * 2 * BX_LBO, BX_LBO, SBO), idesc_256, (half | ks) ? 1u : 0u);
-                } else {           // 110 KB budget, no room for zero rows: z, r and the input half of h as two products
-                    umma_f16(tmem + dcol, ad, umma_desc(bw_s + ks * 2 * BX_LBO, BX_LBO, SBO), idesc_128, ks ? 1u : 0u);
-                    umma_f16(tmem + dcol + 3 * EH, ad, umma_desc(bw_s + ks * 2 * BX_LBO + 2 * EH * 16, BX_LBO, SBO), idesc_64, ks ? 1u : 0u);
-                }
-            }
+            for (int ks = 0; ks < KSX; ++ks)
+                umma_f16(tmem + dcol + COL_XH, umma_desc((half ? al_s : ah_s) + ks * 2 * A_LBO, A_LBO, SBO), umma_desc(bw_s + ks * 2 * BX_LBO, BX_LBO, SBO),
+                         idesc_192, (half | ks) ? 1u : 0u);
     };
-    // recurrent half: rows z, r, h accumulate onto columns 0..191 (layer 1: its first product starts the h-recurrent columns itself)
+    // recurrent half
     auto issue_h = [&](unsigned dcol) {
 #pragma unroll
         for (int half = 0; half < 2; ++half)
@@ -503,30 +507,36 @@ gru_tc_kernel(const SrcDev src, const long long first, const long long n, const 
             for (int ks = 0; ks < EH / 16; ++ks) {
                 const unsigned a_s = half ? al_s + (L::AL_H0 + 2 * ks) * A_LBO : ah_s + (L::KGX + 2 * ks) * A_LBO;
                 const unsigned long long ad = umma_desc(a_s, A_LBO, SBO);
-                if (LAYER == 1 && half == 0 && ks == 0) {
-                    umma_f16(tmem + dcol, ad, umma_desc(bh_s, BH_LBO, SBO), idesc_128, 1u);
-                    umma_f16(tmem + dcol + 2 * EH, ad, umma_desc(bh_s + 2 * EH * 16, BH_LBO, SBO), idesc_64, 0u);
+                if (half == 0 && ks == 0) {
+                    umma_f16(tmem + dcol + COL_Z, ad, umma_desc(bh_s, BH_LBO, SBO), idesc_128, 1u);
+                    umma_f16(tmem + dcol + COL_HN, ad, umma_desc(bh_s + 2 * EH * 16, BH_LBO, SBO), idesc_64, 0u);
                 } else {
-                    umma_f16(tmem + dcol, ad, umma_desc(bh_s + ks * 2 * BH_LBO, BH_LBO, SBO), idesc_192, 1u);
+                    umma_f16(tmem + dcol + COL_Z, ad, umma_desc(bh_s + ks * 2 * BH_LBO, BH_LBO, SBO), idesc_192, 1u);
                 }
             }
     };
-    // layer 2: thread `part` of a sequence moves words [part * YV, (part + 1) * YV) of the 32 16-byte words of y1_t (hi 0..15 | lo 16..31)
-    constexpr int YV = LAYER == 2 ? 4 * EH / 8 / TPS : 1;
-    auto y_src = [&](int tt) { return reinterpret_cast<const uint4 *>(Y1h_in + ((size_t)(live ? seq : 0) * T + tt) * (4 * EH)) + part * YV; };
+    // Y1h is laid out as the A-operand IMAGE of every (tile, step): [tile][t][hi | lo][k-group 0..15][row 0..127] 16-byte words,
+    // 64 KB per (tile, step).  Layer 1 writes word (g, row) from thread `row`: consecutive threads, consecutive words.  Layer 2 copies
+    // the image as it is: thread tid moves words tid, tid + NT, ...: coalesced loads, conflict-free stores, no transposition.
+    // (A per-sequence layout made both sides 16-byte gathers across 128 lines per warp instruction: the restaging of the next
+    // input was a third of layer 2's step - DRM_EMBED_TC_PHASES=1 prints the clocks per phase.)
+    constexpr int YWORDS = 2 * (2 * EH / 8) * TC_M;          // 4096 words per (tile, step): hi image, then lo image
+    constexpr int YV = LAYER == 2 ? YWORDS / NT : 1;         // words per thread
+    const size_t tile = blockIdx.x >> 1;
+    auto y_src = [&](int tt) { return reinterpret_cast<const uint4 *>(Y1h_in) + (tile * T + tt) * YWORDS + tid; };
     auto y_store = [&](const uint4 (&v)[YV]) {
 #pragma unroll
-        for (int g = 0; g < YV; ++g) {
-            const int w = part * YV + g;  // TPS >= 2: a thread's words are all hi or all lo, the branch is uniform per warp
-            if (w < 2 * EH / 8) Ah[w * TC_M + row] = v[g];
-            else Al[(w - 2 * EH / 8) * TC_M + row] = v[g];
+        for (int j = 0; j < YV; ++j) {
+            const int w = tid + NT * j;  // j is a compile-time constant: hi or lo is decided per unrolled copy
+            if (NT * j < YWORDS / 2) Ah[w] = v[j];
+            else Al[w - YWORDS / 2] = v[j];
         }
     };
-    auto y_prefetch = [&](int tt) {  // 512 bytes = 4 lines per sequence and step, shared out over the sequence's threads
-        const unsigned char *yp = reinterpret_cast<const unsigned char *>(Y1h_in + ((size_t)(live ? seq : 0) * T + tt) * (4 * EH));
-        constexpr int LP = TPS >= 4 ? 1 : 4 / TPS;  // lines per thread
+    auto y_prefetch = [&](int tt) {  // 64 KB = 512 lines per (tile, step), shared out over the CTA's threads
+        const unsigned char *yp = reinterpret_cast<const unsigned char *>(reinterpret_cast<const uint4 *>(Y1h_in) + (tile * T + tt) * YWORDS);
+        constexpr int LP = 512 / NT;  // lines per thread
 #pragma unroll
-        for (int q = 0; q < LP; ++q) asm volatile("prefetch.global.L2 [%0];" ::"l"(yp + 128 * ((part * LP + q) & 3)));
+        for (int q = 0; q < LP; ++q) asm volatile("prefetch.global.L2 [%0];" ::"l"(yp + 128 * (tid * LP + q)));
     };
     // layer 1: the embedding row of token (sequence, tt) into the input half of A
     auto x_store = [&](int slot) {
@@ -547,7 +557,7 @@ gru_tc_kernel(const SrcDev src, const long long first, const long long n, const 
         uint4 v[YV];
         const uint4 *y = y_src(dir ? T - 1 : 0);
 #pragma unroll
-        for (int g = 0; g < YV; ++g) v[g] = __ldg(y + g);
+        for (int g = 0; g < YV; ++g) v[g] = __ldg(y + NT * g);
         y_store(v);
         for (int a = 1; a <= 3 && a < T; ++a) y_prefetch(dir ? T - 1 - a : a);
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
@@ -569,19 +579,21 @@ gru_tc_kernel(const SrcDev src, const long long first, const long long n, const 
         if (more) {  // the next step's input (prefetched into L2 three steps ago) travels while the recurrent products run
             const uint4 *y = y_src(dir ? t - 1 : t + 1);
 #pragma unroll
-            for (int g = 0; g < YV; ++g) ynext[g] = __ldg(y + g);
+            for (int g = 0; g < YV; ++g) ynext[g] = __ldg(y + NT * g);
             if (step + 4 < T) y_prefetch(dir ? t - 4 : t + 4);  // and the one three steps further leaves DRAM now
         }
         // generic-proxy writes of A (this step's input, last step's state) -> visible to the tensor core's async proxy
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
         asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");  // the reads of D below precede the next product
         __syncthreads();
+        TC_PHASE(0);
         if (tid == 0) {
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
             if (LAYER == 1) issue_x(dcol);
             issue_h(dcol);
             asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar_s) : "memory");
         }
+        TC_PHASE(1);
         if (LAYER == 1 && step + 1 < T) slot = token_slot(sv, dir ? t - 1 : t + 1, T);  // the next token, while the products run
         {   // wait for the products of this step (the commit covers the input half issued one step earlier too)
             unsigned done = 0, spins = 0;
@@ -593,6 +605,7 @@ gru_tc_kernel(const SrcDev src, const long long first, const long long n, const 
             phase ^= 1u;
         }
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        TC_PHASE(2);
         if (LAYER == 2 && more) {  // every earlier product is complete: the input half of A is free for the next step
             y_store(ynext);
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
@@ -602,20 +615,21 @@ gru_tc_kernel(const SrcDev src, const long long first, const long long n, const 
                 issue_x(dcol ^ 256u);
             }
         }
+        TC_PHASE(3);
         const unsigned tacc = trow + dcol;
 
         // ---- gates, 16 units at a time: z = s(xz + az), r = s(xr + ar), g = tanh(xh + r (ah + bRh)), h' = (1 - z) g + z h
-        // (columns 0..127 hold xz + az and xr + ar already summed by the tensor core, 128..191 ah, 192..255 xh; biases added here)
-        __half *yout = nullptr;
-        if (LAYER == 1) yout = Y1h_out + ((size_t)(live ? seq : 0) * T + t) * (4 * EH) + dir * EH;
+        // (the z and r columns hold xz + az and xr + ar already summed by the tensor core; biases added here)
+        uint4 *yout = nullptr;  // layer 1: this (tile, step)'s image, word (k-group dir * 8, row)
+        if (LAYER == 1) yout = reinterpret_cast<uint4 *>(Y1h_out) + (tile * T + t) * YWORDS + (size_t)(dir * (EH / 8)) * TC_M + row;
 #pragma unroll
         for (int cc = 0; cc < UNITS / 16; ++cc) {
             const int c = cc + part * (UNITS / 16);  // 16-unit chunk of the hidden state
             float az[16], ar[16], ah[16], xh[16];
-            tmem_ld16(tacc + 16 * c, az);
-            tmem_ld16(tacc + EH + 16 * c, ar);
-            tmem_ld16(tacc + 2 * EH + 16 * c, ah);
-            tmem_ld16(tacc + 3 * EH + 16 * c, xh);
+            tmem_ld16(tacc + COL_Z + 16 * c, az);
+            tmem_ld16(tacc + COL_R + 16 * c, ar);
+            tmem_ld16(tacc + COL_HN + 16 * c, ah);
+            tmem_ld16(tacc + COL_XH + 16 * c, xh);
             tmem_ld_wait();
             unsigned hi[8], lo[8];
 #pragma unroll
@@ -632,16 +646,20 @@ gru_tc_kernel(const SrcDev src, const long long first, const long long n, const 
             Ah[(L::KGX + 2 * c + 1) * TC_M + row] = make_uint4(hi[4], hi[5], hi[6], hi[7]);
             Al[(L::AL_H0 + 2 * c) * TC_M + row] = make_uint4(lo[0], lo[1], lo[2], lo[3]);
             Al[(L::AL_H0 + 2 * c + 1) * TC_M + row] = make_uint4(lo[4], lo[5], lo[6], lo[7]);
-            if (LAYER == 1 && live) {
-                uint4 *yo = reinterpret_cast<uint4 *>(yout + 16 * c);
-                yo[0] = make_uint4(hi[0], hi[1], hi[2], hi[3]);
-                yo[1] = make_uint4(hi[4], hi[5], hi[6], hi[7]);
-                uint4 *yl = reinterpret_cast<uint4 *>(yout + 2 * EH + 16 * c);
-                yl[0] = make_uint4(lo[0], lo[1], lo[2], lo[3]);
-                yl[1] = make_uint4(lo[4], lo[5], lo[6], lo[7]);
+            if (LAYER == 1) {  // (rows beyond the pass's last sequence are written too: the image is copied whole)
+                yout[(2 * c) * TC_M] = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+                yout[(2 * c + 1) * TC_M] = make_uint4(hi[4], hi[5], hi[6], hi[7]);
+                yout[YWORDS / 2 + (2 * c) * TC_M] = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+                yout[YWORDS / 2 + (2 * c + 1) * TC_M] = make_uint4(lo[4], lo[5], lo[6], lo[7]);
             }
         }
+        TC_PHASE(4);
     }
+    if (prof) {
+#pragma unroll
+        for (int i = 0; i < 5; ++i) phase_clk[(LAYER - 1) * 5 + i] = pc[i];
+    }
+#undef TC_PHASE
     if (LAYER == 2 && live) {
         float4 *o = reinterpret_cast<float4 *>(out + (size_t)seq * (2 * EH) + dir * EH + part * UNITS);
 #pragma unroll
@@ -652,9 +670,9 @@ gru_tc_kernel(const SrcDev src, const long long first, const long long n, const 
     if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(TCOLS) : "memory");
 }
 
-// fp16 image of a weight matrix in the operand layout above: rows x K (row-major fp32, fp16-exact) -> [K/8][rows_total][8 halves]
-// at `img`; rows from 128 on (the candidate gate) land `h_shift` rows further down (64 where the zero rows sit in between)
-bool tc_pack(const float *Wm, int rows, int K, int rows_total, int h_shift, uint16_t *img)
+// fp16 image of a weight matrix in the operand layout above: rows x K (row-major fp32, fp16-exact) -> [K/8][192][8 halves] at
+// `img`; row r lands at (r + rot) mod 192 (rot = 64 turns the gate order z, r, h into h, z, r)
+bool tc_pack(const float *Wm, int rows, int K, int rot, uint16_t *img)
 {
     bool exact = true;
     for (int r = 0; r < rows; ++r)
@@ -662,7 +680,7 @@ bool tc_pack(const float *Wm, int rows, int K, int rows_total, int h_shift, uint
             const float v = Wm[(size_t)r * K + k];
             const __half hv = __float2half_rn(v);
             if (__half2float(hv) != v) exact = false;
-            img[((size_t)(k / 8) * rows_total + r + (r >= 2 * EH ? h_shift : 0)) * 8 + k % 8] = __half_as_ushort(hv);
+            img[((size_t)(k / 8) * rows + (r + rot) % rows) * 8 + k % 8] = __half_as_ushort(hv);
         }
     return exact;
 }
@@ -727,10 +745,10 @@ int embedder_upload(const EmbedWeightsHost &w, int device, int max_len, DeviceEm
         bool exact = true;
         for (int dir = 0; dir < 2; ++dir) {
             uint16_t *i1 = b1.data() + dir * IMG1, *i2 = b2i.data() + dir * IMG2;
-            exact &= tc_pack(w.W1.data() + (size_t)dir * EG * EH, EG, EH, TcLayout<1>::BX_ROWS, 0, i1);
-            exact &= tc_pack(w.R1.data() + (size_t)dir * EG * EH, EG, EH, EG, 0, i1 + TcLayout<1>::BX_BYTES / 2);
-            exact &= tc_pack(w.W2.data() + (size_t)dir * EG * 2 * EH, EG, 2 * EH, TcLayout<2>::BX_ROWS, EH, i2);
-            exact &= tc_pack(w.R2.data() + (size_t)dir * EG * EH, EG, EH, EG, 0, i2 + TcLayout<2>::BX_BYTES / 2);
+            exact &= tc_pack(w.W1.data() + (size_t)dir * EG * EH, EG, EH, EH, i1);
+            exact &= tc_pack(w.R1.data() + (size_t)dir * EG * EH, EG, EH, 0, i1 + TcLayout<1>::BX_BYTES / 2);
+            exact &= tc_pack(w.W2.data() + (size_t)dir * EG * 2 * EH, EG, 2 * EH, EH, i2);
+            exact &= tc_pack(w.R2.data() + (size_t)dir * EG * EH, EG, EH, 0, i2 + TcLayout<2>::BX_BYTES / 2);
             for (int row = 0; row < EG; ++row) {
                 bias1[(size_t)dir * (EG + EH) + row] = w.B1[(size_t)dir * 4 * EH + row];
                 bias2[(size_t)dir * (EG + EH) + row] = b2[dir * EG + row];
@@ -808,17 +826,35 @@ static int launch_embed_tc(DeviceEmbedder &e, const EmbedSource &src, int64_t fi
     }
     auto k1 = tps1 == 2 ? gru_tc_kernel<1, 2> : gru_tc_kernel<1, 1>;
     auto k2 = tps2 == 4 ? gru_tc_kernel<2, 4> : tps2 == 2 ? gru_tc_kernel<2, 2> : gru_tc_kernel<2, 1>;
+    const char *pe = getenv("DRM_EMBED_TC_PHASES");
+    const bool phases = pe && pe[0] == '1' && tps1 == 2 && tps2 == 2;
+    if (phases) { k1 = gru_tc_kernel<1, 2, true>; k2 = gru_tc_kernel<2, 2, true>; }
     DRM_CUDA_TRY(cudaFuncSetAttribute(k1, cudaFuncAttributeMaxDynamicSharedMemorySize, SM1));
     DRM_CUDA_TRY(cudaFuncSetAttribute(k2, cudaFuncAttributeMaxDynamicSharedMemorySize, SM2));
+    // DRM_EMBED_TC_PHASES=1 (profiling only): CTA 0's clocks per phase of a step, printed after the (synchronised) call
+    unsigned long long *phase_clk = nullptr;
+    if (phases) {
+        DRM_CUDA_TRY(cudaMalloc(reinterpret_cast<void **>(&phase_clk), 10 * sizeof(unsigned long long)));
+        DRM_CUDA_TRY(cudaMemsetAsync(phase_clk, 0, 10 * sizeof(unsigned long long), stream));
+    }
     for (int64_t done = 0; done < n; done += e.chunk_tc) {
         const int64_t m = (n - done) < e.chunk_tc ? (n - done) : e.chunk_tc;
         const unsigned blocks = (unsigned)((m + TC_M - 1) / TC_M) * 2;
         k1<<<blocks, TC_M * tps1, SM1, stream>>>(s, first + done, m, T, reinterpret_cast<const uint4 *>(e.emb16), reinterpret_cast<const uint4 *>(e.Bw1),
-                                                  e.bias1, nullptr, reinterpret_cast<__half *>(e.Y1h), nullptr);
+                                                  e.bias1, nullptr, reinterpret_cast<__half *>(e.Y1h), nullptr, phase_clk);
         DRM_CUDA_TRY(cudaGetLastError());
         k2<<<blocks, TC_M * tps2, SM2, stream>>>(s, first + done, m, T, nullptr, reinterpret_cast<const uint4 *>(e.Bw2), e.bias2,
-                                                  reinterpret_cast<const __half *>(e.Y1h), nullptr, out_dev + (size_t)done * 2 * EH);
+                                                  reinterpret_cast<const __half *>(e.Y1h), nullptr, out_dev + (size_t)done * 2 * EH, phase_clk);
         DRM_CUDA_TRY(cudaGetLastError());
+    }
+    if (phase_clk) {
+        unsigned long long h[10];
+        DRM_CUDA_TRY(cudaStreamSynchronize(stream));
+        DRM_CUDA_TRY(cudaMemcpy(h, phase_clk, sizeof(h), cudaMemcpyDeviceToHost));
+        cudaFree(phase_clk);
+        for (int l = 0; l < 2; ++l)
+            fprintf(stderr, "[embed tc] layer %d, CTA 0, clocks per step: stage+barrier %.0f, issue %.0f, wait %.0f, restage %.0f, gates %.0f\n", l + 1,
+                    (double)h[l * 5] / T, (double)h[l * 5 + 1] / T, (double)h[l * 5 + 2] / T, (double)h[l * 5 + 3] / T, (double)h[l * 5 + 4] / T);
     }
     return DRM_OK;
 }

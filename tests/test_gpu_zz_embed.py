@@ -81,12 +81,15 @@ def test_more_sequences_than_one_pass(embed_form):
     v.close()
 
 
-def test_shorter_max_len():
+@pytest.mark.parametrize("max_len", [16, 2, 3, 5, 128])
+def test_other_max_len(max_len):
+    """Step counts around the tensor-core form's pipeline depths (layer 2 loads one step and prefetches four steps ahead), and the
+    largest the kernels take."""
     w = EO.random_weights(31)
     g = np.random.default_rng(32)
-    seqs = _random_seqs(g, 33, 2, 40)
-    v = drm.Vectorizer(weights=w, max_len=16)
-    assert float(np.abs(v.vectorize(seqs) - EO.embed(seqs, w, max_len=16)).max()) < TOL
+    seqs = _random_seqs(g, 133, 2, 160)
+    v = drm.Vectorizer(weights=w, max_len=max_len)
+    assert float(np.abs(v.vectorize(seqs) - EO.embed(seqs, w, max_len=max_len)).max()) < TOL
     v.close()
 
 

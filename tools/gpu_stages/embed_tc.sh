@@ -1,7 +1,7 @@
 # tensor-core embedder: parity on the default form (+ the L2 stage on top of it), threads-per-sequence A/B, one ncu capture per kernel
 timeout 600 python -m pytest tests/test_gpu_zz_embed.py tests/test_gpu_zz_l2.py -x -q -s > $O/pytest_embed.log 2>&1; echo "pytest rc=$?" >> $O/pytest_embed.log
 tail -4 $O/pytest_embed.log
-for tps in 24 22; do
+for tps in 22 24; do
   DRM_EMBED_TC_TPS=$tps timeout 300 python tools/embed_bench.py --out $O/embed_bench_tps$tps.json > $O/embed_bench_tps$tps.out 2> $O/embed_bench_tps$tps.log
   python - $tps $O/embed_bench_tps$tps.json <<'PY'
 import json, sys
