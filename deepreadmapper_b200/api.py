@@ -547,9 +547,12 @@ def l2_last_timing():
     return dict(zip(("plan_ms", "embed_ms", "rank_ms", "other_ms", "batches"), t.tolist()))
 
 
-def l2_plan_host(mode, neighbors, stride, k, k_clusters, bound):
+def l2_plan_host(mode, neighbors, stride, k, k_clusters, bound, direct_ids=False):
     """The candidate bookkeeping of post_process_l2_static (mode 0) / _dynamic (mode 1) on the host:
-    dict(unique, map, starts, k_out, passthrough, take)."""
+    dict(unique, map, starts, k_out, passthrough, take).  direct_ids: the plan drm_l2_rerank makes when the window cache applies -
+    `map` carries the window ids themselves and `unique` stays empty (no de-duplication pass)."""
+    if direct_ids:
+        mode = -1 - mode
     nb = np.ascontiguousarray(neighbors, dtype=np.int64)
     n, k_in = nb.shape
     info = np.zeros(5, dtype=np.int64)

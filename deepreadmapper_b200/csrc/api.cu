@@ -864,7 +864,9 @@ int drm_l2_plan_host(int mode, const int64_t *neighbors, int64_t n, int64_t k_in
 {
     if (!neighbors || !info) return fail(DRM_EINVAL, "null argument");
     L2Plan plan;
-    const int rc = l2_plan(mode, neighbors, n, k_in, stride, k, k_clusters, bound, plan);
+    // a negative mode asks for the plan drm_l2_rerank makes when every window's embedding is at hand: -1 - mode, window ids in `map`
+    const bool direct = mode < 0;
+    const int rc = l2_plan(direct ? -1 - mode : mode, neighbors, n, k_in, stride, k, k_clusters, bound, plan, direct);
     if (rc != DRM_OK) return rc;
     info[0] = (int64_t)plan.unique.size(); info[1] = (int64_t)plan.map.size(); info[2] = plan.k_out;
     info[3] = plan.passthrough ? 1 : 0; info[4] = plan.take;

@@ -246,7 +246,8 @@ int drm_l2_rerank(drm_embedder *e, drm_ref *ref, int mode, const int64_t *neighb
 int drm_l2_last_timing(double *ms5);
 /* Host-only pieces of the above, exposed for tests: the candidate plan (info[0..4] = unique windows, flat candidates,
  * results per query, pass-through flag, pass-through count; arrays nullable, sized from a first call) and the
- * partial_sort order (idx: n entries, the first k are the selection). */
+ * partial_sort order (idx: n entries, the first k are the selection).  mode -1 / -2 = the dynamic / static plan with the
+ * window ids themselves in `map` (what drm_l2_rerank uses when the window cache applies). */
 int drm_l2_plan_host(int mode, const int64_t *neighbors, int64_t n, int64_t k_in, int64_t stride, int64_t k, int64_t k_clusters,
                      uint64_t bound, int64_t *info, uint64_t *unique, uint32_t *map, int64_t *starts);
 int drm_l2_select_host(const float *dist, int64_t n, int64_t k, int64_t *idx);

@@ -185,6 +185,11 @@ def test_product_plan_equals_oracle_bookkeeping(table, monkeypatch):
     p = drm.l2_plan_host(0, nb, 3, 4, 4, bound)
     order, mapping = L2._expand_flat(nb.astype(np.uint64).reshape(-1), 3, bound)
     assert p["unique"].tolist() == order and p["map"].tolist() == mapping and p["starts"].tolist() == [q * k_in * 3 for q in range(n + 1)]
+    # the plan made when every window's embedding is cached: the flat list carries the window ids, same order, same boundaries
+    for mode, st, kk, kc in ((1, stride, k, k_clusters), (0, 3, 4, 4)):
+        a = drm.l2_plan_host(mode, nb, st, kk, kc, bound)
+        b = drm.l2_plan_host(mode, nb, st, kk, kc, bound, direct_ids=True)
+        assert len(b["unique"]) == 0 and b["map"].tolist() == a["unique"][a["map"]].tolist() and b["starts"].tolist() == a["starts"].tolist()
     # errors: the guard, and slices that would leave the flat list (a clipped id)
     with pytest.raises(drm.DrmError, match="Final k too large") as e:
         drm.l2_plan_host(1, nb, stride, 41, 5, bound)
