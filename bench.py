@@ -621,9 +621,54 @@ def realistic_section(args, genome, ref, local, hbm_peak):
     except Exception as e:
         sec["oracle_error"] = str(e)
     ix.close()
+    try:
+        sec["l2_stage"] = l2_stage_record(drm, v, ref, genome, truth, dQ, n)
+    except Exception as e:  # an extra record must never cost the section
+        sec["l2_stage"] = {"error": f"{type(e).__name__}: {e}"}
     v.close()
     sec["section_wall_s"] = time.time() - t_all
     return sec
+
+
+def l2_stage_record(drm, v, ref, genome, truth, dQ, n_reads):
+    """The reference's LIVE post-process (src/main.cpp:312-331: post_process_l2_dynamic + batch_reranker) through drm_l2_rerank on
+    configs[2]-shaped labels: stride 8, K_clusters 32 -> 480 candidate windows per read, ranked by embedding distance (DESIGN.md
+    4.10).  Labels are synthetic sparse ids around each read's true window plus random ones (what a stride-8 search returns);
+    the query embeddings are the section's.  First call = includes embedding every window of the reference once (the window
+    cache); warm call = the steady state.  Checked against oracle/l2_oracle.py on a sample, embeddings on both sides from the
+    device embedder: ids and fp32 distance bits."""
+    from oracle import l2_oracle as L2
+    m, stride, kc, k = min(20000, n_reads), 8, 32, 128
+    rng = np.random.default_rng(5)
+    hi = (len(genome) - stride) // stride
+    centre = np.minimum(truth[:m] // stride, hi - kc - 1)
+    nb = np.empty((m, kc), np.int64)
+    near = kc // 2
+    nb[:, :near] = np.clip(centre[:, None] + np.arange(-(near // 2), near - near // 2)[None, :], 1, hi - 1)
+    nb[:, near:] = rng.integers(1, hi, (m, kc - near))
+    dist = np.sort(rng.random((m, kc)).astype(np.float32), axis=1)
+    q_emb = np.ascontiguousarray(dQ[:m].cpu().numpy())
+    rec = {"workload": "stride 8, K_clusters 32, k 128: 480 candidate windows per read; labels synthetic (true window +- 8 sparse ids, 16 random)", "reads": m}
+    walls = []
+    for call in range(4):  # call 0 builds the window cache; the steady state is the best of the next three (as tools/l2_bench.py reports it)
+        t0 = time.perf_counter()
+        s, ids = drm.post_process_l2_dynamic(nb, dist, ref, q_emb, v, stride, k, kc)
+        wall = time.perf_counter() - t0
+        tm = drm.api.l2_last_timing()
+        r = {"reads_per_s": m / wall, "wall_ms": wall * 1e3, **{kk: float(x) for kk, x in tm.items()}}
+        walls.append(wall * 1e3)
+        if call == 0:
+            rec["first_call"] = r
+        elif "warm_call" not in rec or r["wall_ms"] < rec["warm_call"]["wall_ms"]:
+            rec["warm_call"] = r
+    rec["wall_ms_of_each_call"] = walls
+    ms = 24
+    s1, i1 = drm.post_process_l2_dynamic(nb[:ms], dist[:ms], ref, q_emb[:ms], v, stride, k, kc)
+    s0, i0 = L2.post_process_l2_dynamic(nb[:ms], dist[:ms], bytes(genome), REF_LEN, stride, k, kc, q_emb[:ms], lambda seqs: v.vectorize(seqs))
+    rec["sample_reads"] = ms
+    rec["device_equals_oracle_on_sample"] = bool(np.array_equal(i1, i0) and np.array_equal(s1.view(np.uint32), s0.view(np.uint32)))
+    rec["results_per_read"] = len(ids) / m
+    return rec
 
 
 def sharded_arm(args, genome, ref, rank, world, local, dist, dense_reads_per_s_per_gpu=None, reads_total=None):
