@@ -989,12 +989,13 @@ int drm_l2_rerank(drm_embedder *e, drm_ref *ref, int mode, const int64_t *neighb
         while (q1 < n && plan.starts[(size_t)q1 + 1] - plan.starts[(size_t)q0] <= max_flat) ++q1;
         const int64_t nb = q1 - q0, f0 = plan.starts[(size_t)q0], fb = plan.starts[(size_t)q1] - f0;
         b_ids.clear(); b_rows.clear();
-        b_map.resize((size_t)fb);
+        const bool map_in_place = use_cache && plan.direct_ids;  // the plan's own flat list is what the device needs
+        if (!map_in_place) b_map.resize((size_t)fb);
         b_starts.resize((size_t)nb + 1);
         for (int64_t i = 0; i <= nb; ++i) b_starts[(size_t)i] = plan.starts[(size_t)(q0 + i)] - f0;
         if (use_cache) {  // candidate rows = window ids into the cache: no per-batch table, nothing to embed
-            if (plan.direct_ids) std::memcpy(b_map.data(), plan.map.data() + f0, (size_t)fb * sizeof(uint32_t));
-            else for (int64_t j = 0; j < fb; ++j) b_map[(size_t)j] = (uint32_t)plan.unique[plan.map[(size_t)(f0 + j)]];
+            if (!plan.direct_ids)
+                for (int64_t j = 0; j < fb; ++j) b_map[(size_t)j] = (uint32_t)plan.unique[plan.map[(size_t)(f0 + j)]];
         } else {
             for (int64_t j = 0; j < fb; ++j) {
                 const uint32_t g = plan.map[(size_t)(f0 + j)];
@@ -1015,7 +1016,7 @@ int drm_l2_rerank(drm_embedder *e, drm_ref *ref, int mode, const int64_t *neighb
                 (rc = d_or.alloc(cap_n * ko * 4)) || (rc = d_cnt.alloc(cap_n * 8))) return rc;
         }
         if (ub) DRM_CUDA_TRY(cudaMemcpy(d_ids.p, b_ids.data(), (size_t)ub * 8, cudaMemcpyHostToDevice));
-        if (fb) DRM_CUDA_TRY(cudaMemcpy(d_map.p, b_map.data(), (size_t)fb * 4, cudaMemcpyHostToDevice));
+        if (fb) DRM_CUDA_TRY(cudaMemcpy(d_map.p, map_in_place ? plan.map.data() + f0 : b_map.data(), (size_t)fb * 4, cudaMemcpyHostToDevice));
         DRM_CUDA_TRY(cudaMemcpy(d_starts.p, b_starts.data(), (size_t)(nb + 1) * 8, cudaMemcpyHostToDevice));
         DRM_CUDA_TRY(cudaMemcpy(d_q.p, q_emb + (size_t)q0 * 128, (size_t)nb * 128 * 4, cudaMemcpyHostToDevice));
         EmbedSource src;

@@ -25,14 +25,27 @@ namespace {
 int expand_flat(const uint64_t *ids, int64_t n_ids, uint64_t stride, uint64_t bound, L2Plan &plan)
 {
     const uint64_t worst = (uint64_t)n_ids * (2 * stride - 1);  // every expanded position distinct
-    plan.map.reserve((size_t)worst);
+    if (!plan.direct_ids) plan.map.reserve((size_t)worst);
     if (plan.direct_ids) {  // the caller has every window's embedding: the flat list carries the window ids, nothing to index
+        // where each id's expansion starts in the flat list (skipped ids add nothing, clipped ones less), then all ids in parallel
+        std::vector<uint64_t> off((size_t)n_ids + 1);
+        off[0] = 0;
+        for (int64_t j = 0; j < n_ids; ++j) {
+            const uint64_t p = ids[j] * stride;
+            uint64_t cnt = 0;
+            if (p < bound) cnt = std::min(p + stride, bound) - (p >= stride - 1 ? p - stride + 1 : 0);
+            off[(size_t)j + 1] = off[(size_t)j] + cnt;
+        }
+        plan.map.resize((size_t)off[(size_t)n_ids]);
+        uint32_t *out = plan.map.data();
+#pragma omp parallel for schedule(static) if (n_ids > 65536)
         for (int64_t j = 0; j < n_ids; ++j) {
             const uint64_t p = ids[j] * stride;
             if (p >= bound) continue;
             const uint64_t start = p >= stride - 1 ? p - stride + 1 : 0;
             const uint64_t end = std::min(p + stride, bound);
-            for (uint64_t pos = start; pos < end; ++pos) plan.map.push_back((uint32_t)pos);
+            uint32_t *o = out + off[(size_t)j];
+            for (uint64_t pos = start; pos < end; ++pos) *o++ = (uint32_t)pos;
         }
         return DRM_OK;
     }

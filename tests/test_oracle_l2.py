@@ -205,3 +205,23 @@ def test_product_plan_equals_oracle_bookkeeping(table, monkeypatch):
     nb4 = nb.copy(); nb4[2, 1] = bound + 5
     with pytest.raises(drm.DrmError, match="Invalid mapping index"):
         drm.l2_plan_host(0, nb4, 1, 5, 5, bound)
+
+
+def test_direct_ids_plan_in_parallel_equals_the_indexed_plan():
+    """More than 65 536 ids: the direct-ids expansion runs its fill loop on all host threads; skipped ids (position beyond the
+    bound) and clipped ones (first windows of the genome) shift the flat list exactly as in the indexed plan."""
+    import deepreadmapper_b200 as drm
+    g = np.random.default_rng(17)
+    n, k_in, stride, kc, k, bound = 3000, 32, 8, 32, 64, 60000
+    nb = g.integers(1, bound // stride + 40, (n, k_in)).astype(np.int64)  # some ids expand beyond the bound: skipped
+    nb[::7, 3] = 0                                                          # clipped at the start
+    try:
+        a = drm.l2_plan_host(1, nb, stride, k, kc, bound)
+    except drm.DrmError as e:  # both forms refuse the same inputs
+        with pytest.raises(drm.DrmError):
+            drm.l2_plan_host(1, nb, stride, k, kc, bound, direct_ids=True)
+        assert "run past" in str(e)
+        nb = g.integers(2, bound // stride - 2, (n, k_in)).astype(np.int64)
+        a = drm.l2_plan_host(1, nb, stride, k, kc, bound)
+    b = drm.l2_plan_host(1, nb, stride, k, kc, bound, direct_ids=True)
+    assert len(b["unique"]) == 0 and np.array_equal(b["map"], a["unique"][a["map"]].astype(np.uint32)) and np.array_equal(b["starts"], a["starts"])
