@@ -453,12 +453,12 @@ __device__ __forceinline__ unsigned stage_classes4(const RerankDev &p, u64 id, i
     if (rc) v = __byte_perm(v, 0u, 0x0123) ^ 0x03030303u;
     const unsigned big = ((v >> 2) & 0x01010101u) * 0xffu;  // bytes holding a class >= 4 (N, other)
     v = (v & ~big) | (0x04040404u & big);
-    if (rr0 < 0 || rr0 + 4 > rows) {
-#pragma unroll
-        for (int b = 0; b < 4; ++b)
-            if ((unsigned)(rr0 + b) >= (unsigned)rows) v = (v & ~(0xffu << (8 * b))) | (4u << (8 * b));
-    }
-    return v;
+    // rows outside [0, rows) match nothing: `lead` bytes at the low end, `trail` at the high end (0 for every interior word), as one
+    // branch-free mask - the clamped funnel shifts give 0 for a shift of 32 (this fix-up was a predicated per-byte loop run by
+    // every task: 6 % of the kernel's source-attributed instructions)
+    const int lead = min(max(-rr0, 0), 4), trail = min(max(rr0 + 4 - rows, 0), 4);
+    const unsigned keep = __funnelshift_lc(0u, 0xffffffffu, 8u * (unsigned)lead) & __funnelshift_rc(0xffffffffu, 0u, 8u * (unsigned)trail);
+    return (v & keep) | (0x04040404u & ~keep);
 }
 
 // Dynamic shared memory layout (bytes): tab | sel[2 * PAIRS][selw] (one byte row per candidate) | cand[C] | first[take] | count[take+1]
