@@ -337,7 +337,7 @@ __device__ __forceinline__ void r_insert(unsigned (&rh)[NSR], unsigned (&rl)[NSR
 
 // CL: the candidate capacity is at most 32 * CL (scans unrolled, warp-parallel sift-down); 0 = any capacity up to 2048.
 template <int CS, int NSR, bool FULLK, int VIS, int CL>
-__global__ void __launch_bounds__(XWARPS * 32, 5) hnswpq_search_exact_kernel(const ExactParams p)
+__global__ void __launch_bounds__(XWARPS * 32, VIS ? 5 : 6) hnswpq_search_exact_kernel(const ExactParams p)
 {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
