@@ -370,17 +370,20 @@ __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.
 __device__ __forceinline__ float ex2_ftz(float x) { float y; asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
 __device__ __forceinline__ float rcp_ftz(float x) { float y; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
 constexpr float TC_L2E = 1.4426950408889634f;
+// The gate phase is bound by its instruction count (two warps per scheduler: profiles/r2_ab_embed_ws.txt), so every argument
+// arrives already in the exponent's units: px = -log2(e) x, pu = -2 log2(e) u, each ONE fma from the accumulator (the biases are
+// scaled when they are staged).
 // z = s(x), r = s(y) with ONE reciprocal: with A = 1 + e^-x, B = 1 + e^-y:  s(x) = B / (A B), s(y) = A / (A B).  The exponent is capped
 // at 2^40 so that the product stays finite (moves a result by less than 1e-12); a large positive argument gives e^-x = 0, s = 1.
-__device__ __forceinline__ void gate_zr(float x, float y, float &sx, float &sy)
+__device__ __forceinline__ void gate_zr(float px, float py, float &sx, float &sy)
 {
-    const float A = 1.0f + ex2_ftz(fminf(x * -TC_L2E, 40.0f)), B = 1.0f + ex2_ftz(fminf(y * -TC_L2E, 40.0f));
+    const float A = 1.0f + ex2_ftz(fminf(px, 40.0f)), B = 1.0f + ex2_ftz(fminf(py, 40.0f));
     const float t = rcp_ftz(A * B);
     sx = t * B;
     sy = t * A;
 }
-// tanh(u) = 2 / (1 + e^-2u) - 1
-__device__ __forceinline__ float tc_tanh(float u) { return fmaf(2.0f, rcp_ftz(1.0f + ex2_ftz(fminf(u * (-2.0f * TC_L2E), 40.0f))), -1.0f); }
+// tanh(u) = 2 / (1 + e^-2u) - 1; no cap: 2^pu = +inf gives 1 / inf = 0 and tanh = -1, 2^pu = 0 gives +1
+__device__ __forceinline__ float tc_tanh(float pu) { return fmaf(2.0f, rcp_ftz(1.0f + ex2_ftz(pu)), -1.0f); }
 
 // h -> (hi, lo) fp16 pair, packed two values per word
 __device__ __forceinline__ void split2(float a, float b, unsigned &hi, unsigned &lo)
@@ -455,7 +458,8 @@ gru_tc_kernel(const SrcDev src, const long long first, const long long n, const 
     {
         const uint4 *g = Bw_g + (size_t)dir * (L::B_BYTES / 16);
         for (int p = tid; p < L::B_BYTES / 16; p += NT) Bw[p] = __ldg(g + p);
-        for (int p = tid; p < L::BIAS_FLOATS; p += NT) bias[p] = bias_g[dir * L::BIAS_FLOATS + p];
+        // biases z | r | h (input) | h (recurrent), in the units of their exponents (see gate_zr / tc_tanh)
+        for (int p = tid; p < L::BIAS_FLOATS; p += NT) bias[p] = bias_g[dir * L::BIAS_FLOATS + p] * (p < 2 * EH ? -TC_L2E : -2.0f * TC_L2E);
         if (LAYER == 1)
             for (int p = tid; p < NSLOT * EH * 2 / 16; p += NT) embs[p] = __ldg(emb_g + p);
         const uint4 z4 = make_uint4(0u, 0u, 0u, 0u);
@@ -622,7 +626,8 @@ gru_tc_kernel(const SrcDev src, const long long first, const long long n, const 
         const unsigned tacc = trow + dcol;
 
         // ---- gates, 16 units at a time: z = s(xz + az), r = s(xr + ar), g = tanh(xh + r (ah + bRh)), h' = (1 - z) g + z h
-        // (the z and r columns hold xz + az and xr + ar already summed by the tensor core; biases added here)
+        // (the z and r columns hold xz + az and xr + ar already summed by the tensor core; biases added here, 21 arithmetic
+        // instructions per unit + 3 for the hi | lo split)
         uint4 *yout = nullptr;  // layer 1: this (tile, step)'s image, word (k-group dir * 8, row)
         if (LAYER == 1) yout = reinterpret_cast<uint4 *>(Y1h_out) + (tile * T + t) * YWORDS + (size_t)(dir * (EH / 8)) * TC_M + row;
 #pragma unroll
@@ -639,9 +644,9 @@ gru_tc_kernel(const SrcDev src, const long long first, const long long n, const 
             for (int j = 0; j < 16; ++j) {
                 const int i = 16 * c + j;
                 float z, r;
-                gate_zr(az[j] + bias[i], ar[j] + bias[EH + i], z, r);
-                const float g = tc_tanh(xh[j] + bias[2 * EH + i] + r * (ah[j] + bias[EG + i]));
-                h[16 * cc + j] = (1.0f - z) * g + z * h[16 * cc + j];
+                gate_zr(fmaf(az[j], -TC_L2E, bias[i]), fmaf(ar[j], -TC_L2E, bias[EH + i]), z, r);
+                const float g = tc_tanh(fmaf(r, fmaf(ah[j], -2.0f * TC_L2E, bias[EG + i]), fmaf(xh[j], -2.0f * TC_L2E, bias[2 * EH + i])));
+                h[16 * cc + j] = fmaf(z, h[16 * cc + j] - g, g);  // (1 - z) g + z h
                 // Layer 2, XG < 16 (A/B only, DRM_EMBED_TC_XG): the next step's input products issued XG at a time every few units
                 // instead of all sixteen before the gates, so that warp 0 starts its gates with the others.  Measured SLOWER
                 // (12.4 M/s at XG = 2, 12.9 M at 4, 13.15 M at 16; profiles/r2_ab_embed_xg.txt): the issuing thread pays about
@@ -685,222 +690,6 @@ gru_tc_kernel(const SrcDev src, const long long first, const long long n, const 
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
     if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(TCOLS) : "memory");
-}
-
-// Layer 2, warp-specialised (A/B, DRM_EMBED_TC_WS=1): the same step as gru_tc_kernel<2, 2>, with the products issued by a THIRD
-// warpgroup (warp 8; warps 9-11 only lend their registers) instead of thread 0 of the gate warps.  The issuing thread pays about
-// 100 clocks per product (tools/ubench_umma.cu, profiles/r2_ab_embed_xg.txt), 1.6 k clocks per step for the next input's sixteen,
-// and in gru_tc_kernel warp 0 starts its gates that much after the other seven.  A ninth warp inside a 168-register CTA spilled
-// (DESIGN 4.9), so the registers are re-divided with setmaxnreg: 384 threads launch at 168, the issuing warpgroup drops to 56
-// and the two gate warpgroups rise to 224.  Hand-offs are mbarriers: `h_ready` / `x_ready` (one arrival per gate warp, after its
-// lanes' fence.proxy.async + __syncwarp) tell the issuer that the state / the next input image are in A; `done` is the commit.
-__device__ __forceinline__ void mbar_wait(unsigned bar_s, unsigned parity)
-{
-    unsigned done = 0, spins = 0;
-    do {
-        asm volatile("{\n\t.reg .pred P1;\n\tmbarrier.try_wait.parity.shared::cta.b64 P1, [%1], %2;\n\tselp.b32 %0, 1, 0, P1;\n\t}"
-                     : "=r"(done) : "r"(bar_s), "r"(parity) : "memory");
-        if (!done && ++spins > (1u << 27)) __trap();  // a hand-off that never comes must not hang the GPU
-    } while (!done);
-}
-__device__ __forceinline__ void mbar_arrive(unsigned bar_s)
-{
-    asm volatile("{\n\t.reg .b64 st;\n\tmbarrier.arrive.shared::cta.b64 st, [%0];\n\t}" ::"r"(bar_s) : "memory");
-}
-
-constexpr int WS_GATE_THREADS = 2 * TC_M, WS_THREADS = WS_GATE_THREADS + 128, WS_BYTES = TcLayout<2>::BYTES + 16;
-
-__global__ void __launch_bounds__(WS_THREADS, 1)
-gru_tc2_ws_kernel(const long long n, const int T, const uint4 *__restrict__ Bw_g, const float *__restrict__ bias_g,
-                  const __half *__restrict__ Y1h_in, float *__restrict__ out)
-{
-    using L = TcLayout<2>;
-    constexpr int NT = WS_GATE_THREADS, UNITS = EH / 2, KSX = L::KX / 16, NPX = 2 * KSX;
-    extern __shared__ __align__(1024) unsigned char tsm[];
-    uint4 *Bw = reinterpret_cast<uint4 *>(tsm);
-    uint4 *Ah = reinterpret_cast<uint4 *>(tsm + L::OFF_AH);
-    uint4 *Al = reinterpret_cast<uint4 *>(tsm + L::OFF_AL);
-    float *bias = reinterpret_cast<float *>(tsm + L::OFF_BIAS);
-    unsigned long long *bar = reinterpret_cast<unsigned long long *>(tsm + L::OFF_BAR);  // done | (TMEM address) | h_ready | x_ready
-    unsigned *tmem_slot = reinterpret_cast<unsigned *>(tsm + L::OFF_BAR + 8);
-
-    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    const int dir = blockIdx.x & 1;
-    {
-        const uint4 *g = Bw_g + (size_t)dir * (L::B_BYTES / 16);
-        for (int p = tid; p < L::B_BYTES / 16; p += WS_THREADS) Bw[p] = __ldg(g + p);
-        for (int p = tid; p < L::BIAS_FLOATS; p += WS_THREADS) bias[p] = bias_g[dir * L::BIAS_FLOATS + p];
-        const uint4 z4 = make_uint4(0u, 0u, 0u, 0u);
-        for (int p = tid; p < (L::AH_BYTES + L::AL_BYTES) / 16; p += WS_THREADS) Ah[p] = z4;
-    }
-    const unsigned bar_done = smem_u32(bar), bar_h = bar_done + 16, bar_x = bar_done + 24;
-    if (tid == 0) {
-        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar_done) : "memory");
-        asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar_h), "r"(NT / 32) : "memory");
-        asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar_x), "r"(NT / 32) : "memory");
-        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-    }
-    if (warp == 0) {
-        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(TC_COLS2) : "memory");
-        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
-    }
-    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-    __syncthreads();
-    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-    const unsigned tmem = *tmem_slot;
-    constexpr unsigned COL_XH = 0, COL_Z = EH, COL_R = 2 * EH, COL_HN = 3 * EH;
-
-    if (warp >= NT / 32) {
-        // ---------------- the issuing warpgroup
-        asm volatile("setmaxnreg.dec.sync.aligned.u32 56;" ::: "memory");
-        if (warp == NT / 32) {
-            const unsigned ah_s = smem_u32(Ah), al_s = smem_u32(Al), bw_s = smem_u32(Bw), bh_s = bw_s + L::BX_BYTES;
-            constexpr unsigned A_LBO = TC_M * 16, BX_LBO = L::BX_ROWS * 16, BH_LBO = EG * 16, SBO = 128;
-            constexpr unsigned idesc_192 = umma_idesc(TC_M, 3 * EH), idesc_128 = umma_idesc(TC_M, 2 * EH), idesc_64 = umma_idesc(TC_M, EH);
-            auto issue_x = [&](unsigned dcol) {
-#pragma unroll
-                for (int p = 0; p < NPX; ++p) {
-                    const int half = p / KSX, ks = p % KSX;
-                    umma_f16(tmem + dcol + COL_XH, umma_desc((half ? al_s : ah_s) + ks * 2 * A_LBO, A_LBO, SBO),
-                             umma_desc(bw_s + ks * 2 * BX_LBO, BX_LBO, SBO), idesc_192, p ? 1u : 0u);
-                }
-            };
-            auto issue_h = [&](unsigned dcol) {
-#pragma unroll
-                for (int half = 0; half < 2; ++half)
-#pragma unroll
-                    for (int ks = 0; ks < EH / 16; ++ks) {
-                        const unsigned a_s = half ? al_s + (L::AL_H0 + 2 * ks) * A_LBO : ah_s + (L::KGX + 2 * ks) * A_LBO;
-                        const unsigned long long ad = umma_desc(a_s, A_LBO, SBO);
-                        if (half == 0 && ks == 0) {
-                            umma_f16(tmem + dcol + COL_Z, ad, umma_desc(bh_s, BH_LBO, SBO), idesc_128, 1u);
-                            umma_f16(tmem + dcol + COL_HN, ad, umma_desc(bh_s + 2 * EH * 16, BH_LBO, SBO), idesc_64, 0u);
-                        } else {
-                            umma_f16(tmem + dcol + COL_Z, ad, umma_desc(bh_s + ks * 2 * BH_LBO, BH_LBO, SBO), idesc_192, 1u);
-                        }
-                    }
-            };
-            unsigned ph_h = 0, ph_x = 0;
-            mbar_wait(bar_x, ph_x); ph_x ^= 1u;   // the first input image is in A
-            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-            if (lane == 0) issue_x(0u);
-            __syncwarp();
-            for (int step = 0; step < T; ++step) {
-                const unsigned dcol = (unsigned)(step & 1) * 256u;
-                mbar_wait(bar_h, ph_h); ph_h ^= 1u;  // h_{t-1} is in A, and the gates that read this accumulator set are over
-                asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-                if (lane == 0) {
-                    issue_h(dcol);
-                    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar_done) : "memory");
-                }
-                __syncwarp();
-                if (step + 1 < T) {
-                    mbar_wait(bar_x, ph_x); ph_x ^= 1u;  // the next image is in A (stored after `done`: the products reading the last one are over)
-                    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-                    if (lane == 0) issue_x(dcol ^ 256u);
-                    __syncwarp();
-                }
-            }
-        }
-    } else {
-        // ---------------- the two gate warpgroups: thread = (sequence row, half of the hidden units)
-        asm volatile("setmaxnreg.inc.sync.aligned.u32 224;" ::: "memory");
-        const int row = tid & (TC_M - 1), part = tid / TC_M;
-        const long long seq = (long long)(blockIdx.x >> 1) * TC_M + row;
-        const bool live = seq < n;
-        const unsigned trow = tmem + ((unsigned)((warp & 3) * 32) << 16);
-        constexpr int YWORDS = 2 * (2 * EH / 8) * TC_M, YV = YWORDS / NT;
-        const size_t tile = blockIdx.x >> 1;
-        auto y_src = [&](int tt) { return reinterpret_cast<const uint4 *>(Y1h_in) + (tile * T + tt) * YWORDS + tid; };
-        auto y_store = [&](const uint4 (&v)[YV]) {
-#pragma unroll
-            for (int j = 0; j < YV; ++j) {
-                const int w = tid + NT * j;
-                if (NT * j < YWORDS / 2) Ah[w] = v[j];
-                else Al[w - YWORDS / 2] = v[j];
-            }
-        };
-        auto y_prefetch = [&](int tt) {
-            const unsigned char *yp = reinterpret_cast<const unsigned char *>(reinterpret_cast<const uint4 *>(Y1h_in) + (tile * T + tt) * YWORDS);
-            constexpr int LP = 512 / NT;
-#pragma unroll
-            for (int q = 0; q < LP; ++q) asm volatile("prefetch.global.L2 [%0];" ::"l"(yp + 128 * (tid * LP + q)));
-        };
-        // this warp's lanes have written A: make the writes visible to the tensor core's proxy, then ONE arrival per warp
-        auto hand_off = [&](unsigned bar_s) {
-            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-            asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");  // (and this warp's reads of D precede what the issuer does next)
-            __syncwarp();
-            if (lane == 0) mbar_arrive(bar_s);
-        };
-        float h[UNITS];
-#pragma unroll
-        for (int i = 0; i < UNITS; ++i) h[i] = 0.0f;
-        {
-            uint4 v[YV];
-            const uint4 *y = y_src(dir ? T - 1 : 0);
-#pragma unroll
-            for (int g = 0; g < YV; ++g) v[g] = __ldg(y + NT * g);
-            y_store(v);
-            for (int a = 1; a <= 3 && a < T; ++a) y_prefetch(dir ? T - 1 - a : a);
-            hand_off(bar_x);
-        }
-        unsigned phase = 0;
-        for (int step = 0; step < T; ++step) {
-            const int t = dir ? T - 1 - step : step;
-            const unsigned dcol = (unsigned)(step & 1) * 256u;
-            uint4 ynext[YV];
-            const bool more = step + 1 < T;
-            if (more) {
-                const uint4 *y = y_src(dir ? t - 1 : t + 1);
-#pragma unroll
-                for (int g = 0; g < YV; ++g) ynext[g] = __ldg(y + NT * g);
-                if (step + 4 < T) y_prefetch(dir ? t - 4 : t + 4);
-            }
-            hand_off(bar_h);                  // the state written by the last gate phase
-            mbar_wait(bar_done, phase); phase ^= 1u;
-            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-            if (more) {                       // every earlier product is complete: the input half of A is free
-                y_store(ynext);
-                hand_off(bar_x);
-            }
-            const unsigned tacc = trow + dcol;
-#pragma unroll
-            for (int cc = 0; cc < UNITS / 16; ++cc) {
-                const int c = cc + part * (UNITS / 16);
-                float az[16], ar[16], ah[16], xh[16];
-                tmem_ld16(tacc + COL_Z + 16 * c, az);
-                tmem_ld16(tacc + COL_R + 16 * c, ar);
-                tmem_ld16(tacc + COL_HN + 16 * c, ah);
-                tmem_ld16(tacc + COL_XH + 16 * c, xh);
-                tmem_ld_wait();
-                unsigned hi[8], lo[8];
-#pragma unroll
-                for (int j = 0; j < 16; ++j) {
-                    const int i = 16 * c + j;
-                    float z, r;
-                    gate_zr(az[j] + bias[i], ar[j] + bias[EH + i], z, r);
-                    const float g = tc_tanh(xh[j] + bias[2 * EH + i] + r * (ah[j] + bias[EG + i]));
-                    h[16 * cc + j] = (1.0f - z) * g + z * h[16 * cc + j];
-                }
-#pragma unroll
-                for (int j = 0; j < 8; ++j) split2(h[16 * cc + 2 * j], h[16 * cc + 2 * j + 1], hi[j], lo[j]);
-                Ah[(L::KGX + 2 * c) * TC_M + row] = make_uint4(hi[0], hi[1], hi[2], hi[3]);
-                Ah[(L::KGX + 2 * c + 1) * TC_M + row] = make_uint4(hi[4], hi[5], hi[6], hi[7]);
-                Al[(L::AL_H0 + 2 * c) * TC_M + row] = make_uint4(lo[0], lo[1], lo[2], lo[3]);
-                Al[(L::AL_H0 + 2 * c + 1) * TC_M + row] = make_uint4(lo[4], lo[5], lo[6], lo[7]);
-            }
-        }
-        if (live) {
-            float4 *o = reinterpret_cast<float4 *>(out + (size_t)seq * (2 * EH) + dir * EH + part * UNITS);
-#pragma unroll
-            for (int q = 0; q < UNITS / 4; ++q) o[q] = make_float4(h[4 * q], h[4 * q + 1], h[4 * q + 2], h[4 * q + 3]);
-        }
-    }
-    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-    __syncthreads();
-    if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(TC_COLS2) : "memory");
 }
 
 // fp16 image of a weight matrix in the operand layout above: rows x K (row-major fp32, fp16-exact) -> [K/8][192][8 halves] at
@@ -1064,9 +853,6 @@ static int launch_embed_tc(DeviceEmbedder &e, const EmbedSource &src, int64_t fi
         if (tps2 == 2 && atoi(xg) == 2) k2 = gru_tc_kernel<2, 2, false, 2>;
         if (tps2 == 2 && atoi(xg) == 4) k2 = gru_tc_kernel<2, 2, false, 4>;
     }
-    const char *wse = getenv("DRM_EMBED_TC_WS");  // layer 2 with the products issued by a third warpgroup (A/B)
-    const bool ws = wse && wse[0] == '1';
-    if (ws) DRM_CUDA_TRY(cudaFuncSetAttribute(gru_tc2_ws_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, WS_BYTES));
     const char *pe = getenv("DRM_EMBED_TC_PHASES");
     const bool phases = pe && pe[0] == '1' && tps1 == 2 && tps2 == 2;
     if (phases) { k1 = gru_tc_kernel<1, 2, true>; k2 = gru_tc_kernel<2, 2, true>; }
@@ -1084,12 +870,8 @@ static int launch_embed_tc(DeviceEmbedder &e, const EmbedSource &src, int64_t fi
         k1<<<blocks, TC_M * tps1, SM1, stream>>>(s, first + done, m, T, reinterpret_cast<const uint4 *>(e.emb16), reinterpret_cast<const uint4 *>(e.Bw1),
                                                   e.bias1, nullptr, reinterpret_cast<__half *>(e.Y1h), nullptr, phase_clk);
         DRM_CUDA_TRY(cudaGetLastError());
-        if (ws)
-            gru_tc2_ws_kernel<<<blocks, WS_THREADS, WS_BYTES, stream>>>(m, T, reinterpret_cast<const uint4 *>(e.Bw2), e.bias2,
-                                                                         reinterpret_cast<const __half *>(e.Y1h), out_dev + (size_t)done * 2 * EH);
-        else
-            k2<<<blocks, TC_M * tps2, SM2, stream>>>(s, first + done, m, T, nullptr, reinterpret_cast<const uint4 *>(e.Bw2), e.bias2,
-                                                      reinterpret_cast<const __half *>(e.Y1h), nullptr, out_dev + (size_t)done * 2 * EH, phase_clk);
+        k2<<<blocks, TC_M * tps2, SM2, stream>>>(s, first + done, m, T, nullptr, reinterpret_cast<const uint4 *>(e.Bw2), e.bias2,
+                                                  reinterpret_cast<const __half *>(e.Y1h), nullptr, out_dev + (size_t)done * 2 * EH, phase_clk);
         DRM_CUDA_TRY(cudaGetLastError());
     }
     if (phase_clk) {
